@@ -1,0 +1,134 @@
+// ggml-b200.h -- C-ABI of the B200 (sm_100a) hot path.
+//
+// Two surfaces, one shared library (libggml-b200.so):
+//
+//  (1) The ggml backend plugin entry points, exactly what the reference's registry dlsym()s
+//      (reference: ggml/src/ggml-backend-reg.cpp:255-272, ggml/src/ggml-backend-impl.h:215-251):
+//          ggml_backend_reg_t ggml_backend_init(void);
+//          int                ggml_backend_score(void);
+//      plus the in-tree registration symbol ggml_backend_b200_reg() (registry constructor,
+//      ggml/src/ggml-backend-reg.cpp:172-212).  Through them llama.cpp, llama-bench and
+//      test-backend-ops reach supports_op / graph_compute with no other glue.
+//
+//  (2) A flat operator API over device pointers (b200_*), one call per reference operator:
+//          b200_quantize_q8_1   <- quantize_row_q8_1        ggml/src/ggml-cpu/arch/x86/quants.c:388-490
+//          b200_mul_mat         <- ggml_compute_forward_mul_mat      ggml/src/ggml-cpu/ggml-cpu.c:1226-1418
+//          b200_mul_mat_id      <- ggml_compute_forward_mul_mat_id   ggml/src/ggml-cpu/ggml-cpu.c:1500-1700
+//          b200_flash_attn_ext  <- ggml_compute_forward_flash_attn_ext ggml/src/ggml-cpu/ops.cpp:8047-8374
+//      The plugin's graph_compute is a thin translation ggml_tensor -> b200_tensor -> these
+//      calls; parity tests and bench.py bind the same functions through ctypes.
+//
+// Tensors follow ggml conventions: ne[0] is the fastest dimension, nb[] are byte strides,
+// quantized types are stored as GGUF blocks (block_q4_0 / block_q8_0 / block_q4_K / block_q5_K /
+// block_q6_K, reference ggml/src/ggml-common.h:170-344).
+// All functions return 0 on success and a negative b200_status on failure; b200_last_error()
+// gives the message.  There is no CPU fallback: without a usable sm_100 device every call fails.
+#pragma once
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#  define B200_API __declspec(dllexport)
+#else
+#  define B200_API __attribute__((visibility("default")))
+#endif
+
+enum b200_status {
+    B200_OK               =  0,
+    B200_ERR_NO_DEVICE    = -1,   // no CUDA device / not sm_100
+    B200_ERR_CUDA         = -2,   // a CUDA runtime call failed
+    B200_ERR_UNSUPPORTED  = -3,   // type / shape combination outside the hot path
+    B200_ERR_INVALID      = -4,   // malformed arguments
+    B200_ERR_ALLOC        = -5,
+};
+
+// same numeric values as enum ggml_type (ggml/include/ggml.h:389-431)
+enum b200_type {
+    B200_TYPE_F32 = 0, B200_TYPE_F16 = 1, B200_TYPE_Q4_0 = 2, B200_TYPE_Q8_0 = 8, B200_TYPE_Q8_1 = 9,
+    B200_TYPE_Q4_K = 12, B200_TYPE_Q5_K = 13, B200_TYPE_Q6_K = 14, B200_TYPE_I32 = 26, B200_TYPE_BF16 = 30,
+};
+
+// q8_1 rounding variants
+enum b200_q8_1_variant {
+    B200_Q8_1_X86  = 0,  // ggml-cpu x86 AVX2: id = 127/amax, round-half-even, s = fp16(d*sum q)   (default, what libggml-cpu runs)
+    B200_Q8_1_REF  = 1,  // quantize_row_q8_1_ref: id = 1/(amax/127), roundf (half away), s = fp16(sum*d)
+};
+
+// device-resident strided view, ggml layout
+typedef struct b200_tensor {
+    void *  data;
+    int32_t type;       // enum b200_type
+    int32_t flags;      // bit 0: data is in the B200 repacked (SoA) weight layout
+    int64_t ne[4];
+    size_t  nb[4];
+} b200_tensor;
+#define B200_TENSOR_REPACKED 1
+
+typedef struct b200_ctx b200_ctx;   // one device + one stream + scratch arena
+
+// ---- device / context -------------------------------------------------------------------
+B200_API int          b200_device_count(void);
+B200_API const char * b200_last_error(void);
+B200_API b200_ctx *   b200_ctx_create(int device);             // NULL on failure
+B200_API void         b200_ctx_destroy(b200_ctx * ctx);
+B200_API int          b200_ctx_device(const b200_ctx * ctx);
+B200_API void *       b200_ctx_stream(const b200_ctx * ctx);   // cudaStream_t
+B200_API int          b200_ctx_synchronize(b200_ctx * ctx);
+B200_API uint64_t     b200_ctx_launch_count(const b200_ctx * ctx);   // kernels launched so far through this ctx
+
+// ---- memory ------------------------------------------------------------------------------
+B200_API void * b200_malloc(b200_ctx * ctx, size_t nbytes);    // cudaMalloc on ctx's device
+B200_API int    b200_free(b200_ctx * ctx, void * dptr);
+B200_API void * b200_host_alloc(size_t nbytes);                // pinned host memory
+B200_API int    b200_host_free(void * hptr);
+B200_API int    b200_memcpy_h2d(b200_ctx * ctx, void * dst, const void * src, size_t nbytes);   // async on ctx stream
+B200_API int    b200_memcpy_d2h(b200_ctx * ctx, void * dst, const void * src, size_t nbytes);   // async on ctx stream
+B200_API int    b200_memset(b200_ctx * ctx, void * dst, int value, size_t nbytes);
+
+// ---- operators ----------------------------------------------------------------------------
+// f32 rows [nrows][k] (row stride x_row_stride bytes) -> block_q8_1 [nrows][k/32], k % 32 == 0.
+B200_API int b200_quantize_q8_1(b200_ctx * ctx, const float * x, size_t x_row_stride, void * y,
+                                int64_t k, int64_t nrows, int variant);
+
+// dst[ne01, ne11, ne12, ne13] (f32) = w[ne00, ne01, ne02, ne03]^T * x[ne00, ne11, ne12, ne13] (f32),
+// w broadcast over dims 2,3 (ggml/src/ggml.c:3168-3203).  w: f32/f16/bf16/q4_0/q8_0/q4_K/q5_K/q6_K.
+B200_API int b200_mul_mat(b200_ctx * ctx, const b200_tensor * w, const b200_tensor * x, b200_tensor * dst);
+
+// as[K, M, n_expert], b[K, n_used|1, n_tokens] f32, ids[n_used, n_tokens] i32 -> dst[M, n_used, n_tokens]
+// (ggml/src/ggml.c:3205-3241).
+B200_API int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b200_tensor * b,
+                             const b200_tensor * ids, b200_tensor * dst);
+
+// q[DK, N, H, S] f32; k[DK, KV, Hk, Sk], v[DV, KV, Hk, Sk] f16 (strided views of the KV cache);
+// mask[KV, >=N, 1|H, 1|S] f16 or NULL; sinks[H] f32 or NULL; dst[DV, H, N, S] f32
+// (ggml/src/ggml.c:5254-5330, ggml/src/ggml-cpu/ops.cpp:8047-8272).
+B200_API int b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k,
+                                 const b200_tensor * v, const b200_tensor * mask, const b200_tensor * sinks,
+                                 b200_tensor * dst, float scale, float max_bias, float logit_softcap);
+
+// ---- load-time weight repack (SoA, TMA/128-bit friendly; DESIGN.md "HBM layout") ----------
+// nbytes of the repacked image of a [k, nrows] matrix of `type` (>= the GGUF size, 256-byte aligned).
+B200_API size_t b200_repack_size(int type, int64_t k, int64_t nrows);
+// src: GGUF blocks on the device; dst: repacked image.  unrepack is the exact inverse (get_tensor).
+B200_API int b200_repack(b200_ctx * ctx, int type, const void * src, void * dst, int64_t k, int64_t nrows);
+B200_API int b200_unrepack(b200_ctx * ctx, int type, const void * src, void * dst, int64_t k, int64_t nrows);
+
+// ---- row split (split-mode=row) helpers; reference ggml-cuda.cu:777-803 --------------------
+// rows [*row_low, *row_high) of an nrows-row weight that rank `rank` of `world` owns under `tensor_split`
+// (NULL = even), boundaries rounded down to `rounding` rows.
+B200_API int b200_split_row_range(int64_t nrows, const float * tensor_split, int world, int rank,
+                                  int64_t rounding, int64_t * row_low, int64_t * row_high);
+
+// ---- ggml plugin entry points ----------------------------------------------------------------
+struct ggml_backend_reg;
+B200_API struct ggml_backend_reg * ggml_backend_init(void);       // ggml-backend-reg.cpp:255-272
+B200_API int                       ggml_backend_score(void);
+B200_API struct ggml_backend_reg * ggml_backend_b200_reg(void);   // for a static in-tree registration
+
+#ifdef __cplusplus
+}
+#endif

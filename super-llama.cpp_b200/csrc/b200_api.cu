@@ -1,0 +1,194 @@
+// b200_api.cu -- the flat C-ABI (include/ggml-b200.h): context, memory, operator dispatch.
+// The ggml plugin (b200_backend.cpp) and the ctypes bindings (tests/, bench.py) both land here.
+#include "b200_common.cuh"
+#include <stdarg.h>
+#include <string.h>
+#include <stdlib.h>
+
+static thread_local char g_err[512] = "";
+
+void b200_set_error(const char * fmt, ...) {
+    va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof(g_err), fmt, ap); va_end(ap);
+    if (getenv("GGML_B200_DEBUG")) fprintf(stderr, "ggml-b200: %s\n", g_err);
+}
+extern "C" const char * b200_last_error(void) { return g_err; }
+
+extern "C" int b200_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    int ok = 0;
+    for (int i = 0; i < n; ++i) {
+        cudaDeviceProp prop;
+        if (cudaGetDeviceProperties(&prop, i) == cudaSuccess && prop.major == 10) ok++;   // sm_100a code only runs on cc 10.x
+    }
+    return ok == n ? n : 0;
+}
+
+extern "C" b200_ctx * b200_ctx_create(int device) {
+    const int n = b200_device_count();
+    if (device < 0 || device >= n) { b200_set_error("b200_ctx_create: device %d not available (%d sm_100 devices)", device, n); return nullptr; }
+    if (cudaSetDevice(device) != cudaSuccess) { b200_set_error("cudaSetDevice(%d) failed", device); return nullptr; }
+    b200_ctx * ctx = (b200_ctx *) calloc(1, sizeof(b200_ctx));
+    ctx->device = device;
+    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { b200_set_error("stream create failed"); free(ctx); return nullptr; }
+    cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
+    return ctx;
+}
+extern "C" void b200_ctx_destroy(b200_ctx * ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    for (int i = 0; i < 4; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
+    cudaStreamDestroy(ctx->stream);
+    free(ctx);
+}
+extern "C" int      b200_ctx_device(const b200_ctx * ctx) { return ctx->device; }
+extern "C" void *   b200_ctx_stream(const b200_ctx * ctx) { return (void *) ctx->stream; }
+extern "C" uint64_t b200_ctx_launch_count(const b200_ctx * ctx) { return ctx->launches; }
+extern "C" int      b200_ctx_synchronize(b200_ctx * ctx) {
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    return B200_OK;
+}
+
+void * b200_scratch(b200_ctx * ctx, int slot, size_t nbytes) {
+    if (ctx->scratch_size[slot] >= nbytes && ctx->scratch[slot]) return ctx->scratch[slot];
+    // growing: earlier kernels on the stream may still read the old block -> drain first (rare, sizes converge fast)
+    cudaStreamSynchronize(ctx->stream);
+    if (ctx->scratch[slot]) cudaFree(ctx->scratch[slot]);
+    size_t want = nbytes + nbytes / 2; if (want < (1u << 20)) want = 1u << 20;
+    ctx->scratch[slot] = nullptr; ctx->scratch_size[slot] = 0;
+    if (cudaMalloc(&ctx->scratch[slot], want) != cudaSuccess) { cudaGetLastError(); b200_set_error("scratch alloc of %zu bytes failed", want); return nullptr; }
+    ctx->scratch_size[slot] = want;
+    return ctx->scratch[slot];
+}
+
+extern "C" void * b200_malloc(b200_ctx * ctx, size_t nbytes) {
+    void * p = nullptr;
+    if (cudaSetDevice(ctx->device) != cudaSuccess || cudaMalloc(&p, nbytes ? nbytes : 1) != cudaSuccess) {
+        cudaGetLastError(); b200_set_error("cudaMalloc(%zu) failed", nbytes); return nullptr;
+    }
+    return p;
+}
+extern "C" int b200_free(b200_ctx * ctx, void * dptr) { B200_CUDA_TRY(cudaSetDevice(ctx->device)); B200_CUDA_TRY(cudaFree(dptr)); return B200_OK; }
+extern "C" void * b200_host_alloc(size_t nbytes) {
+    void * p = nullptr;
+    if (cudaMallocHost(&p, nbytes ? nbytes : 1) != cudaSuccess) { cudaGetLastError(); b200_set_error("cudaMallocHost(%zu) failed", nbytes); return nullptr; }
+    return p;
+}
+extern "C" int b200_host_free(void * hptr) { B200_CUDA_TRY(cudaFreeHost(hptr)); return B200_OK; }
+extern "C" int b200_memcpy_h2d(b200_ctx * ctx, void * dst, const void * src, size_t n) {
+    B200_CUDA_TRY(cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, ctx->stream)); return B200_OK;
+}
+extern "C" int b200_memcpy_d2h(b200_ctx * ctx, void * dst, const void * src, size_t n) {
+    B200_CUDA_TRY(cudaMemcpyAsync(dst, src, n, cudaMemcpyDeviceToHost, ctx->stream)); return B200_OK;
+}
+extern "C" int b200_memset(b200_ctx * ctx, void * dst, int value, size_t n) {
+    B200_CUDA_TRY(cudaMemsetAsync(dst, value, n, ctx->stream)); return B200_OK;
+}
+
+// ---- operators -----------------------------------------------------------------------------
+extern "C" int b200_quantize_q8_1(b200_ctx * ctx, const float * x, size_t x_row_stride, void * y, int64_t k, int64_t nrows, int variant) {
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    return b200_launch_quantize_q8_1(ctx, x, x_row_stride, y, k, nrows, variant);
+}
+
+static bool is_quant(int t) { return t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q4_K || t == B200_TYPE_Q5_K || t == B200_TYPE_Q6_K; }
+static bool is_float_w(int t) { return t == B200_TYPE_F32 || t == B200_TYPE_F16 || t == B200_TYPE_BF16; }
+
+static int q8_1_variant_env() {
+    static int v = -1;
+    if (v < 0) { const char * e = getenv("GGML_B200_Q8_1_REF"); v = (e && atoi(e)) ? B200_Q8_1_REF : B200_Q8_1_X86; }
+    return v;
+}
+
+extern "C" int b200_mul_mat(b200_ctx * ctx, const b200_tensor * w, const b200_tensor * x, b200_tensor * dst) {
+    if (!ctx || !w || !x || !dst) { b200_set_error("mul_mat: null argument"); return B200_ERR_INVALID; }
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    const int64_t K = w->ne[0], M = w->ne[1];
+    if (x->ne[0] != K || dst->ne[0] != M || dst->ne[1] != x->ne[1] || dst->ne[2] != x->ne[2] || dst->ne[3] != x->ne[3] ||
+        w->ne[2] <= 0 || w->ne[3] <= 0 || x->ne[2] % w->ne[2] != 0 || x->ne[3] % w->ne[3] != 0) {
+        b200_set_error("mul_mat: shape mismatch"); return B200_ERR_INVALID;
+    }
+    if (x->type != B200_TYPE_F32 || dst->type != B200_TYPE_F32 || x->nb[0] != 4 || dst->nb[0] != 4) {
+        b200_set_error("mul_mat: activations and result must be f32 with contiguous rows"); return B200_ERR_UNSUPPORTED;
+    }
+    if (M == 0 || x->ne[1] * x->ne[2] * x->ne[3] == 0) return B200_OK;
+    if (is_quant(w->type)) {
+        if (K % b200_blck_size(w->type) != 0) { b200_set_error("mul_mat: K=%lld not a multiple of the block size", (long long) K); return B200_ERR_INVALID; }
+        if (w->nb[0] != b200_type_size(w->type)) { b200_set_error("mul_mat: quantized weight rows must be contiguous"); return B200_ERR_UNSUPPORTED; }
+        const int64_t ncol = x->ne[1] * x->ne[2] * x->ne[3];
+        if (x->ne[1] > B200_GEMV_MAX_COLS && b200_gemm_supported(w, x)) return b200_launch_gemm_q(ctx, w, x, dst);
+        void * image = b200_scratch(ctx, 0, b200_q8_1_soa_size(K, ncol));
+        if (!image) return B200_ERR_ALLOC;
+        int rc = b200_launch_quantize_q8_1_soa(ctx, (const float *) x->data, x->nb[1], x->nb[2], x->nb[3], K, x->ne[1], x->ne[2], x->ne[3], image, q8_1_variant_env());
+        if (rc) return rc;
+        return b200_launch_gemv_q(ctx, w, image, x->ne[1], x->ne[2], x->ne[3], dst);
+    }
+    if (is_float_w(w->type)) return b200_launch_matmul_float(ctx, w, x, dst);
+    b200_set_error("mul_mat: weight type %d is outside the hot path", w->type);
+    return B200_ERR_UNSUPPORTED;
+}
+
+extern "C" int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids, b200_tensor * dst) {
+    if (!ctx || !as || !b || !ids || !dst) { b200_set_error("mul_mat_id: null argument"); return B200_ERR_INVALID; }
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    const int64_t K = as->ne[0], M = as->ne[1], n_used = ids->ne[0], n_tokens = ids->ne[1];
+    if (as->ne[3] != 1 || b->ne[3] != 1 || dst->ne[3] != 1 || b->ne[0] != K || b->ne[2] != n_tokens || dst->ne[0] != M ||
+        dst->ne[1] != n_used || dst->ne[2] != n_tokens || b->ne[1] <= 0 || n_used % b->ne[1] != 0 || ids->type != B200_TYPE_I32) {
+        b200_set_error("mul_mat_id: shape mismatch"); return B200_ERR_INVALID;
+    }
+    if (b->type != B200_TYPE_F32 || dst->type != B200_TYPE_F32 || b->nb[0] != 4 || dst->nb[0] != 4 || !is_quant(as->type) ||
+        as->nb[0] != b200_type_size(as->type) || K % b200_blck_size(as->type) != 0) {
+        b200_set_error("mul_mat_id: unsupported type/layout"); return B200_ERR_UNSUPPORTED;
+    }
+    if (M == 0 || n_used * n_tokens == 0) return B200_OK;
+    if (n_tokens > B200_GEMV_MAX_COLS && b200_gemm_id_supported(as, b, ids)) return b200_launch_gemm_id_q(ctx, as, b, ids, dst);
+    const int64_t ncol = b->ne[1] * n_tokens;
+    void * image = b200_scratch(ctx, 0, b200_q8_1_soa_size(K, ncol));
+    if (!image) return B200_ERR_ALLOC;
+    int rc = b200_launch_quantize_q8_1_soa(ctx, (const float *) b->data, b->nb[1], b->nb[2], b->nb[3], K, b->ne[1], n_tokens, 1, image, q8_1_variant_env());
+    if (rc) return rc;
+    return b200_launch_gemv_id_q(ctx, as, image, b->ne[1], n_tokens, ids, dst);
+}
+
+extern "C" int b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v,
+                                   const b200_tensor * mask, const b200_tensor * sinks, b200_tensor * dst,
+                                   float scale, float max_bias, float logit_softcap) {
+    if (!ctx || !q || !k || !v || !dst) { b200_set_error("flash_attn_ext: null argument"); return B200_ERR_INVALID; }
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    const int64_t DK = k->ne[0], DV = v->ne[0];
+    if (q->ne[0] != DK || v->ne[1] != k->ne[1] || dst->ne[0] != DV || dst->ne[1] != q->ne[2] || dst->ne[2] != q->ne[1] || dst->ne[3] != q->ne[3] ||
+        k->ne[2] <= 0 || q->ne[2] % k->ne[2] != 0 || q->ne[2] % v->ne[2] != 0 || q->ne[3] % k->ne[3] != 0 || q->ne[3] % v->ne[3] != 0) {
+        b200_set_error("flash_attn_ext: shape mismatch"); return B200_ERR_INVALID;
+    }
+    if (q->type != B200_TYPE_F32 || k->type != B200_TYPE_F16 || v->type != B200_TYPE_F16 || dst->type != B200_TYPE_F32 ||
+        (mask && mask->type != B200_TYPE_F16) || q->nb[0] != 4 || k->nb[0] != 2 || v->nb[0] != 2 || dst->nb[0] != 4 ||
+        DK % 64 != 0 || DV % 64 != 0 || DK > 256 || (DV != 64 && DV != 128 && DV != 256) ||
+        (k->nb[1] % 16) || (k->nb[2] % 16) || (k->nb[3] % 16) || ((uintptr_t) k->data % 16) ||
+        (v->nb[1] % 4) || (v->nb[2] % 4) || (v->nb[3] % 4) || ((uintptr_t) v->data % 4)) {
+        b200_set_error("flash_attn_ext: type/head-size/alignment outside the hot path (DK=%lld DV=%lld)", (long long) DK, (long long) DV);
+        return B200_ERR_UNSUPPORTED;
+    }
+    if (mask && (mask->ne[0] < k->ne[1] || mask->ne[1] < q->ne[1])) { b200_set_error("flash_attn_ext: mask too small"); return B200_ERR_INVALID; }
+    return b200_launch_fattn_vec(ctx, q, k, v, mask, sinks, dst, scale, max_bias, logit_softcap);
+}
+
+// ---- row split helper: ggml-cuda.cu:777-803 semantics -----------------------------------------
+extern "C" int b200_split_row_range(int64_t nrows, const float * tensor_split, int world, int rank, int64_t rounding,
+                                    int64_t * row_low, int64_t * row_high) {
+    if (world <= 0 || rank < 0 || rank >= world || rounding <= 0 || !row_low || !row_high) { b200_set_error("split_row_range: bad arguments"); return B200_ERR_INVALID; }
+    // tensor_split[i] = cumulative fraction at which device i starts (as the reference normalises it); NULL = even
+    auto start_frac = [&](int r) -> double {
+        if (r >= world) return 1.0;
+        if (!tensor_split) return (double) r / world;
+        return (double) tensor_split[r];
+    };
+    int64_t lo = rank == 0 ? 0 : (int64_t) ((float) nrows * (float) start_frac(rank));   // float product, as the reference
+    lo -= lo % rounding;
+    int64_t hi;
+    if (rank == world - 1) hi = nrows;
+    else { hi = (int64_t) ((float) nrows * (float) start_frac(rank + 1)); hi -= hi % rounding; }
+    *row_low = lo; *row_high = hi;
+    return B200_OK;
+}

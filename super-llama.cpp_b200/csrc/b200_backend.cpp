@@ -1,0 +1,380 @@
+// b200_backend.cpp -- the ggml backend plugin ("B200"): registry, devices, buffer types, buffers,
+// backend streams, supports_op and graph_compute.  It fills the reference's vtables
+// (ggml/src/ggml-backend-impl.h:17-210) and translates each ggml_tensor node into one call of the
+// flat operator API (include/ggml-b200.h).  No symbol of libggml is needed at link time, so the
+// same .so loads into llama-bench / test-backend-ops via GGML_BACKEND_PATH and into Python via ctypes.
+//
+// Ownership follows ggml-backend.cpp: ggml deletes `ggml_backend_buffer` objects itself after calling
+// free_buffer (ggml/src/ggml-backend.cpp, ggml_backend_buffer_free), so they are allocated with `new`
+// and the same layout; backends are freed through iface.free.
+#include "b200_common.cuh"
+#include "b200_glue.cuh"   // non-hot-path ops so whole llama graphs stay on the device
+#include "../../include/ggml-b200-abi.h"
+#include <string>
+#include <vector>
+#include <mutex>
+#include <string.h>
+#include <stdlib.h>
+
+#define B200_MAX_DEVICES 16
+#define B200_LOG(...) do { fprintf(stderr, "ggml-b200: " __VA_ARGS__); fputc('\n', stderr); } while (0)
+#define B200_CHECK(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { \
+        B200_LOG("%s:%d: %s failed: %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e_)); abort(); } } while (0)
+
+// ---- ggml helpers we cannot import (no link dependency on libggml-base) ------------------------
+struct type_info { size_t size; int64_t blck; };
+static const type_info k_types[GGML_TYPE_COUNT] = {            // ggml/src/ggml.c type_traits table
+    {4,1},{2,1},{18,32},{20,32},{0,0},{0,0},{22,32},{24,32},{34,32},{36,32},
+    {84,256},{110,256},{144,256},{176,256},{210,256},{292,256},{66,256},{74,256},{98,256},{50,256},
+    {18,32},{110,256},{82,256},{136,256},{1,1},{2,1},{4,1},{8,1},{8,1},{56,256},
+    {2,1},{0,0},{0,0},{0,0},{54,256},{66,256},{0,0},{0,0},{0,0},{17,32},
+};
+static size_t  t_size(int t) { return (t >= 0 && t < GGML_TYPE_COUNT) ? k_types[t].size : 0; }
+static int64_t t_blck(int t) { return (t >= 0 && t < GGML_TYPE_COUNT) ? k_types[t].blck : 0; }
+
+static size_t tensor_nbytes(const ggml_tensor * t) {           // ggml_nbytes, ggml/src/ggml.c
+    for (int i = 0; i < GGML_MAX_DIMS; ++i) if (t->ne[i] <= 0) return 0;
+    const int64_t blck = t_blck(t->type);
+    size_t n;
+    if (blck == 1) { n = t_size(t->type); for (int i = 0; i < GGML_MAX_DIMS; ++i) n += (t->ne[i] - 1) * t->nb[i]; }
+    else           { n = t->ne[0] * t->nb[0] / blck; for (int i = 1; i < GGML_MAX_DIMS; ++i) n += (t->ne[i] - 1) * t->nb[i]; }
+    return n;
+}
+static int64_t tensor_nelements(const ggml_tensor * t) { return t->ne[0] * t->ne[1] * t->ne[2] * t->ne[3]; }
+static bool tensor_is_contiguous(const ggml_tensor * t) {     // ggml_is_contiguous
+    size_t next = t_size(t->type);
+    if (t->ne[0] != t_blck(t->type) && t->nb[0] != next) return false;
+    next *= t->ne[0] / t_blck(t->type);
+    for (int i = 1; i < GGML_MAX_DIMS; ++i) { if (t->ne[i] != 1 && t->nb[i] != next) return false; next *= t->ne[i]; }
+    return true;
+}
+static bool tensor_rows_contiguous(const ggml_tensor * t) { return t->nb[0] == t_size(t->type); }
+static bool same_shape(const ggml_tensor * a, const ggml_tensor * b) {
+    return a->ne[0] == b->ne[0] && a->ne[1] == b->ne[1] && a->ne[2] == b->ne[2] && a->ne[3] == b->ne[3];
+}
+
+static b200_tensor to_b200(const ggml_tensor * t) {
+    b200_tensor r; r.data = t->data; r.type = (int32_t) t->type; r.flags = 0;
+    for (int i = 0; i < 4; ++i) { r.ne[i] = t->ne[i]; r.nb[i] = t->nb[i]; }
+    return r;
+}
+
+// ---- registry state -----------------------------------------------------------------------------
+struct b200_device_ctx {
+    int device; std::string name, description;
+    ggml_backend_buffer_type buft;          // default device buffer type
+    ggml_backend_device      dev;
+};
+struct b200_reg_ctx { std::vector<b200_device_ctx *> devices; };
+struct b200_buffer_ctx { int device; void * base; };
+struct b200_backend_ctx { int device; b200_ctx * ctx; std::string name; };
+
+static ggml_backend_reg g_reg;
+static b200_reg_ctx     g_reg_ctx;
+static ggml_backend_buffer_type g_host_buft;
+
+static bool buft_is_b200(ggml_backend_buffer_type_t buft);
+static bool buft_is_b200_host(ggml_backend_buffer_type_t buft);
+
+// ---- buffer ---------------------------------------------------------------------------------------
+static void buf_free(ggml_backend_buffer_t b) {
+    b200_buffer_ctx * c = (b200_buffer_ctx *) b->context;
+    cudaSetDevice(c->device); cudaFree(c->base); delete c;
+}
+static void * buf_get_base(ggml_backend_buffer_t b) { return ((b200_buffer_ctx *) b->context)->base; }
+static enum ggml_status buf_init_tensor(ggml_backend_buffer_t b, ggml_tensor * t) {
+    // quantized rows may be padded by get_alloc_size: zero the tail so padded reads are defined (as ggml-cuda.cu:640-656)
+    if (t->view_src == nullptr && t_blck(t->type) > 1) {
+        const size_t orig = tensor_nbytes(t), padded = b->buft->iface.get_alloc_size(b->buft, t);
+        if (padded > orig) { b200_buffer_ctx * c = (b200_buffer_ctx *) b->context; cudaSetDevice(c->device); B200_CHECK(cudaMemset((char *) t->data + orig, 0, padded - orig)); }
+    }
+    return GGML_STATUS_SUCCESS;
+}
+static void buf_memset_tensor(ggml_backend_buffer_t b, ggml_tensor * t, uint8_t v, size_t off, size_t n) {
+    b200_buffer_ctx * c = (b200_buffer_ctx *) b->context; B200_CHECK(cudaSetDevice(c->device));
+    B200_CHECK(cudaMemsetAsync((char *) t->data + off, v, n, cudaStreamPerThread)); B200_CHECK(cudaStreamSynchronize(cudaStreamPerThread));
+}
+static void buf_set_tensor(ggml_backend_buffer_t b, ggml_tensor * t, const void * data, size_t off, size_t n) {
+    b200_buffer_ctx * c = (b200_buffer_ctx *) b->context; B200_CHECK(cudaSetDevice(c->device));
+    B200_CHECK(cudaMemcpyAsync((char *) t->data + off, data, n, cudaMemcpyHostToDevice, cudaStreamPerThread)); B200_CHECK(cudaStreamSynchronize(cudaStreamPerThread));
+}
+static void buf_get_tensor(ggml_backend_buffer_t b, const ggml_tensor * t, void * data, size_t off, size_t n) {
+    b200_buffer_ctx * c = (b200_buffer_ctx *) b->context; B200_CHECK(cudaSetDevice(c->device));
+    B200_CHECK(cudaMemcpyAsync(data, (const char *) t->data + off, n, cudaMemcpyDeviceToHost, cudaStreamPerThread)); B200_CHECK(cudaStreamSynchronize(cudaStreamPerThread));
+}
+static bool buf_cpy_tensor(ggml_backend_buffer_t b, const ggml_tensor * src, ggml_tensor * dst) {
+    b200_buffer_ctx * c = (b200_buffer_ctx *) b->context;
+    if (!src->buffer || !buft_is_b200(src->buffer->buft)) return false;
+    b200_buffer_ctx * sc = (b200_buffer_ctx *) src->buffer->context;
+    B200_CHECK(cudaSetDevice(c->device));
+    if (sc->device == c->device) B200_CHECK(cudaMemcpyAsync(dst->data, src->data, tensor_nbytes(src), cudaMemcpyDeviceToDevice, cudaStreamPerThread));
+    else                         B200_CHECK(cudaMemcpyPeerAsync(dst->data, c->device, src->data, sc->device, tensor_nbytes(src), cudaStreamPerThread));
+    B200_CHECK(cudaStreamSynchronize(cudaStreamPerThread));
+    return true;
+}
+static void buf_clear(ggml_backend_buffer_t b, uint8_t v) {
+    b200_buffer_ctx * c = (b200_buffer_ctx *) b->context; B200_CHECK(cudaSetDevice(c->device));
+    B200_CHECK(cudaMemset(c->base, v, b->size));
+}
+static const ggml_backend_buffer_i k_buffer_iface = {
+    buf_free, buf_get_base, buf_init_tensor, buf_memset_tensor, buf_set_tensor, buf_get_tensor, buf_cpy_tensor, buf_clear, nullptr,
+};
+
+// ---- device buffer type ---------------------------------------------------------------------------
+static const char * buft_name(ggml_backend_buffer_type_t buft) { return ((b200_device_ctx *) buft->context)->name.c_str(); }
+static ggml_backend_buffer_t buft_alloc(ggml_backend_buffer_type_t buft, size_t size) {
+    b200_device_ctx * d = (b200_device_ctx *) buft->context;
+    if (cudaSetDevice(d->device) != cudaSuccess) return nullptr;
+    void * p = nullptr;
+    if (cudaMalloc(&p, size ? size : 1) != cudaSuccess) { cudaGetLastError(); B200_LOG("alloc of %.2f MiB on device %d failed", size / 1048576.0, d->device); return nullptr; }
+    return new ggml_backend_buffer{ k_buffer_iface, buft, new b200_buffer_ctx{ d->device, p }, size, GGML_BACKEND_BUFFER_USAGE_ANY };
+}
+static size_t buft_alignment(ggml_backend_buffer_type_t) { return 256; }
+static size_t buft_alloc_size(ggml_backend_buffer_type_t, const ggml_tensor * t) {
+    // pad quantized rows to a multiple of 512 elements so kernels may over-read a row tail (as MATRIX_ROW_PADDING, ggml-cuda common.cuh:148)
+    size_t n = tensor_nbytes(t);
+    if (t_blck(t->type) > 1 && t->view_src == nullptr && t->ne[0] % 512 != 0) n += (512 - t->ne[0] % 512) / t_blck(t->type) * t_size(t->type);
+    return n;
+}
+static bool buft_is_host(ggml_backend_buffer_type_t) { return false; }
+static const ggml_backend_buffer_type_i k_buft_iface = { buft_name, buft_alloc, buft_alignment, nullptr, buft_alloc_size, buft_is_host };
+static bool buft_is_b200(ggml_backend_buffer_type_t buft) { return buft->iface.get_name == buft_name; }
+
+// ---- pinned host buffer type ------------------------------------------------------------------------
+static void hbuf_free(ggml_backend_buffer_t b) { cudaFreeHost(b->context); }
+static void * hbuf_base(ggml_backend_buffer_t b) { return b->context; }
+static void hbuf_memset_tensor(ggml_backend_buffer_t, ggml_tensor * t, uint8_t v, size_t off, size_t n) { memset((char *) t->data + off, v, n); }
+static void hbuf_set_tensor(ggml_backend_buffer_t, ggml_tensor * t, const void * d, size_t off, size_t n) { memcpy((char *) t->data + off, d, n); }
+static void hbuf_get_tensor(ggml_backend_buffer_t, const ggml_tensor * t, void * d, size_t off, size_t n) { memcpy(d, (const char *) t->data + off, n); }
+static bool hbuf_cpy_tensor(ggml_backend_buffer_t, const ggml_tensor * src, ggml_tensor * dst) {
+    if (src->buffer && src->buffer->buft->iface.is_host && src->buffer->buft->iface.is_host(src->buffer->buft)) { memcpy(dst->data, src->data, tensor_nbytes(src)); return true; }
+    return false;
+}
+static void hbuf_clear(ggml_backend_buffer_t b, uint8_t v) { memset(b->context, v, b->size); }
+static const ggml_backend_buffer_i k_host_buffer_iface = { hbuf_free, hbuf_base, nullptr, hbuf_memset_tensor, hbuf_set_tensor, hbuf_get_tensor, hbuf_cpy_tensor, hbuf_clear, nullptr };
+static const char * hbuft_name(ggml_backend_buffer_type_t) { return "B200_Host"; }
+static ggml_backend_buffer_t hbuft_alloc(ggml_backend_buffer_type_t buft, size_t size) {
+    void * p = nullptr;
+    if (cudaMallocHost(&p, size ? size : 1) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return new ggml_backend_buffer{ k_host_buffer_iface, buft, p, size, GGML_BACKEND_BUFFER_USAGE_ANY };
+}
+static size_t hbuft_alignment(ggml_backend_buffer_type_t) { return 64; }
+static bool hbuft_is_host(ggml_backend_buffer_type_t) { return true; }
+static const ggml_backend_buffer_type_i k_hbuft_iface = { hbuft_name, hbuft_alloc, hbuft_alignment, nullptr, nullptr, hbuft_is_host };
+static bool buft_is_b200_host(ggml_backend_buffer_type_t buft) { return buft->iface.get_name == hbuft_name; }
+
+// ---- backend (stream) ---------------------------------------------------------------------------------
+static ggml_guid g_guid = { 0xb2, 0x00, 0x5a, 0x10, 0x0a, 0x67, 0x67, 0x6d, 0x6c, 0x2d, 0x62, 0x32, 0x30, 0x30, 0x00, 0x01 };
+
+static const char * be_name(ggml_backend_t be) { return ((b200_backend_ctx *) be->context)->name.c_str(); }
+static void be_free(ggml_backend_t be) {
+    b200_backend_ctx * c = (b200_backend_ctx *) be->context;
+    b200_ctx_destroy(c->ctx); delete c; delete be;
+}
+static void be_set_tensor_async(ggml_backend_t be, ggml_tensor * t, const void * data, size_t off, size_t n) {
+    b200_backend_ctx * c = (b200_backend_ctx *) be->context; B200_CHECK(cudaSetDevice(c->device));
+    B200_CHECK(cudaMemcpyAsync((char *) t->data + off, data, n, cudaMemcpyHostToDevice, c->ctx->stream));
+}
+static void be_get_tensor_async(ggml_backend_t be, const ggml_tensor * t, void * data, size_t off, size_t n) {
+    b200_backend_ctx * c = (b200_backend_ctx *) be->context; B200_CHECK(cudaSetDevice(c->device));
+    B200_CHECK(cudaMemcpyAsync(data, (const char *) t->data + off, n, cudaMemcpyDeviceToHost, c->ctx->stream));
+}
+static bool be_is_b200(ggml_backend_t be) { return be && be->iface.get_name == be_name; }
+static bool be_cpy_tensor_async(ggml_backend_t be_src, ggml_backend_t be_dst, const ggml_tensor * src, ggml_tensor * dst) {
+    if (!be_is_b200(be_src) || !be_is_b200(be_dst)) return false;
+    if (!src->buffer || !dst->buffer || !buft_is_b200(src->buffer->buft) || !buft_is_b200(dst->buffer->buft)) return false;
+    b200_backend_ctx * cs = (b200_backend_ctx *) be_src->context, * cd = (b200_backend_ctx *) be_dst->context;
+    b200_buffer_ctx * bs = (b200_buffer_ctx *) src->buffer->context, * bd = (b200_buffer_ctx *) dst->buffer->context;
+    if (cs->device != bs->device || cd->device != bd->device) return false;
+    // copy on the source stream, then make the destination stream wait for it (as ggml-cuda.cu:2700-2760)
+    B200_CHECK(cudaSetDevice(cs->device));
+    if (cs->device == cd->device) B200_CHECK(cudaMemcpyAsync(dst->data, src->data, tensor_nbytes(dst), cudaMemcpyDeviceToDevice, cs->ctx->stream));
+    else                          B200_CHECK(cudaMemcpyPeerAsync(dst->data, cd->device, src->data, cs->device, tensor_nbytes(dst), cs->ctx->stream));
+    if (be_src != be_dst) {
+        cudaEvent_t ev; B200_CHECK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        B200_CHECK(cudaEventRecord(ev, cs->ctx->stream));
+        B200_CHECK(cudaSetDevice(cd->device));
+        B200_CHECK(cudaStreamWaitEvent(cd->ctx->stream, ev, 0));
+        B200_CHECK(cudaEventDestroy(ev));
+    }
+    return true;
+}
+static void be_synchronize(ggml_backend_t be) {
+    b200_backend_ctx * c = (b200_backend_ctx *) be->context; B200_CHECK(cudaSetDevice(c->device));
+    B200_CHECK(cudaStreamSynchronize(c->ctx->stream));
+}
+
+static bool op_is_view(int op) { return op == GGML_OP_NONE || op == GGML_OP_RESHAPE || op == GGML_OP_VIEW || op == GGML_OP_PERMUTE || op == GGML_OP_TRANSPOSE; }
+
+static int compute_node(b200_ctx * ctx, ggml_tensor * node) {
+    switch ((int) node->op) {
+        case GGML_OP_MUL_MAT: {
+            b200_tensor w = to_b200(node->src[0]), x = to_b200(node->src[1]), d = to_b200(node);
+            return b200_mul_mat(ctx, &w, &x, &d);
+        }
+        case GGML_OP_MUL_MAT_ID: {
+            b200_tensor as = to_b200(node->src[0]), b = to_b200(node->src[1]), ids = to_b200(node->src[2]), d = to_b200(node);
+            return b200_mul_mat_id(ctx, &as, &b, &ids, &d);
+        }
+        case GGML_OP_FLASH_ATTN_EXT: {
+            b200_tensor q = to_b200(node->src[0]), k = to_b200(node->src[1]), v = to_b200(node->src[2]), d = to_b200(node), m, s;
+            if (node->src[3]) m = to_b200(node->src[3]);
+            if (node->src[4]) s = to_b200(node->src[4]);
+            float scale, max_bias, softcap;
+            memcpy(&scale, node->op_params + 0, 4); memcpy(&max_bias, node->op_params + 1, 4); memcpy(&softcap, node->op_params + 2, 4);
+            return b200_flash_attn_ext(ctx, &q, &k, &v, node->src[3] ? &m : nullptr, node->src[4] ? &s : nullptr, &d, scale, max_bias, softcap);
+        }
+        default:
+            return b200_glue_compute(ctx, node);
+    }
+}
+
+static enum ggml_status be_graph_compute(ggml_backend_t be, ggml_cgraph * g) {
+    b200_backend_ctx * c = (b200_backend_ctx *) be->context;
+    if (cudaSetDevice(c->device) != cudaSuccess) return GGML_STATUS_FAILED;
+    for (int i = 0; i < g->n_nodes; ++i) {
+        ggml_tensor * node = g->nodes[i];
+        if (op_is_view((int) node->op) || tensor_nelements(node) == 0) continue;
+        const int rc = compute_node(c->ctx, node);
+        if (rc != B200_OK) {
+            B200_LOG("graph_compute: node %d (%s, op %d) failed: %s", i, node->name, (int) node->op, b200_last_error());
+            return GGML_STATUS_FAILED;
+        }
+    }
+    return GGML_STATUS_SUCCESS;
+}
+
+static void be_event_record(ggml_backend_t be, ggml_backend_event_t ev) {
+    b200_backend_ctx * c = (b200_backend_ctx *) be->context; B200_CHECK(cudaSetDevice(c->device));
+    B200_CHECK(cudaEventRecord((cudaEvent_t) ev->context, c->ctx->stream));
+}
+static void be_event_wait(ggml_backend_t be, ggml_backend_event_t ev) {
+    b200_backend_ctx * c = (b200_backend_ctx *) be->context; B200_CHECK(cudaSetDevice(c->device));
+    B200_CHECK(cudaStreamWaitEvent(c->ctx->stream, (cudaEvent_t) ev->context, 0));
+}
+static const ggml_backend_i k_backend_iface = {
+    be_name, be_free, be_set_tensor_async, be_get_tensor_async, be_cpy_tensor_async, be_synchronize,
+    nullptr, nullptr, nullptr, nullptr, be_graph_compute, be_event_record, be_event_wait, nullptr,
+};
+
+// ---- device -------------------------------------------------------------------------------------------
+static const char * dev_name(ggml_backend_dev_t d) { return ((b200_device_ctx *) d->context)->name.c_str(); }
+static const char * dev_desc(ggml_backend_dev_t d) { return ((b200_device_ctx *) d->context)->description.c_str(); }
+static void dev_memory(ggml_backend_dev_t d, size_t * free_b, size_t * total_b) {
+    b200_device_ctx * c = (b200_device_ctx *) d->context;
+    *free_b = *total_b = 0;
+    if (cudaSetDevice(c->device) == cudaSuccess) cudaMemGetInfo(free_b, total_b);
+}
+static enum ggml_backend_dev_type dev_type(ggml_backend_dev_t) { return GGML_BACKEND_DEVICE_TYPE_GPU; }
+static void dev_props(ggml_backend_dev_t d, ggml_backend_dev_props * p) {
+    p->name = dev_name(d); p->description = dev_desc(d); p->type = GGML_BACKEND_DEVICE_TYPE_GPU; p->device_id = nullptr;
+    dev_memory(d, &p->memory_free, &p->memory_total);
+    p->caps.async = true; p->caps.host_buffer = true; p->caps.buffer_from_host_ptr = false; p->caps.events = true;
+}
+static ggml_backend_t dev_init_backend(ggml_backend_dev_t d, const char *) {
+    b200_device_ctx * c = (b200_device_ctx *) d->context;
+    b200_ctx * ctx = b200_ctx_create(c->device);
+    if (!ctx) { B200_LOG("init_backend: %s", b200_last_error()); return nullptr; }
+    return new ggml_backend{ &g_guid, k_backend_iface, d, new b200_backend_ctx{ c->device, ctx, c->name } };
+}
+static ggml_backend_buffer_type_t dev_buft(ggml_backend_dev_t d) { return &((b200_device_ctx *) d->context)->buft; }
+static ggml_backend_buffer_type_t dev_host_buft(ggml_backend_dev_t) { return &g_host_buft; }
+
+static bool mm_weight_ok(const ggml_tensor * w) {
+    switch ((int) w->type) {
+        case GGML_TYPE_Q4_0: case GGML_TYPE_Q8_0: case GGML_TYPE_Q4_K: case GGML_TYPE_Q5_K: case GGML_TYPE_Q6_K:
+            return tensor_rows_contiguous(w) && w->ne[0] % t_blck(w->type) == 0 &&
+                   (w->type == GGML_TYPE_Q4_K || w->type == GGML_TYPE_Q5_K ? (w->nb[1] % 16 == 0 && w->nb[2] % 16 == 0 && w->nb[3] % 16 == 0) : true);
+        case GGML_TYPE_F32: case GGML_TYPE_F16: case GGML_TYPE_BF16:
+            return tensor_rows_contiguous(w);
+    }
+    return false;
+}
+
+static bool dev_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
+    switch ((int) op->op) {
+        case GGML_OP_NONE: case GGML_OP_RESHAPE: case GGML_OP_VIEW: case GGML_OP_PERMUTE: case GGML_OP_TRANSPOSE:
+            return true;
+        case GGML_OP_MUL_MAT: {
+            const ggml_tensor * w = op->src[0], * x = op->src[1];
+            return mm_weight_ok(w) && x->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && x->nb[0] == 4 && op->nb[0] == 4 &&
+                   x->ne[2] * x->ne[3] <= 65535;
+        }
+        case GGML_OP_MUL_MAT_ID: {
+            const ggml_tensor * w = op->src[0], * x = op->src[1], * ids = op->src[2];
+            return mm_weight_ok(w) && t_blck(w->type) > 1 && x->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && ids->type == GGML_TYPE_I32 &&
+                   x->nb[0] == 4 && op->nb[0] == 4 && ids->nb[0] == 4 && ids->ne[0] * ids->ne[1] <= 65535;
+        }
+        case GGML_OP_FLASH_ATTN_EXT: {
+            const ggml_tensor * q = op->src[0], * k = op->src[1], * v = op->src[2], * m = op->src[3];
+            const int64_t DK = k->ne[0], DV = v->ne[0];
+            if (q->type != GGML_TYPE_F32 || k->type != GGML_TYPE_F16 || v->type != GGML_TYPE_F16 || op->type != GGML_TYPE_F32) return false;
+            if (m && m->type != GGML_TYPE_F16) return false;
+            if (DK % 64 != 0 || DK > 256 || (DV != 64 && DV != 128 && DV != 256)) return false;
+            if (q->nb[0] != 4 || k->nb[0] != 2 || v->nb[0] != 2) return false;
+            if (k->nb[1] % 16 || k->nb[2] % 16 || k->nb[3] % 16 || v->nb[1] % 4 || v->nb[2] % 4 || v->nb[3] % 4) return false;
+            if (q->ne[2] > 65535 || q->ne[3] > 65535) return false;
+            return true;
+        }
+        default:
+            return b200_glue_supports(op);
+    }
+}
+static bool dev_supports_buft(ggml_backend_dev_t d, ggml_backend_buffer_type_t buft) {
+    if (buft_is_b200_host(buft)) return false;   // host tensors are copied in by the scheduler
+    return buft_is_b200(buft) && buft->device == d;
+}
+static bool dev_offload_op(ggml_backend_dev_t, const ggml_tensor * op) {
+    // as ggml-cuda.cu:4493-4500: worth shipping host-resident weights over only for real batches
+    const int min_batch = 32;
+    return (op->ne[1] >= min_batch && op->op != GGML_OP_GET_ROWS) || (op->op == GGML_OP_MUL_MAT_ID && op->ne[2] >= min_batch);
+}
+static ggml_backend_event_t dev_event_new(ggml_backend_dev_t d) {
+    b200_device_ctx * c = (b200_device_ctx *) d->context; B200_CHECK(cudaSetDevice(c->device));
+    cudaEvent_t ev; B200_CHECK(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+    return new ggml_backend_event{ d, ev };
+}
+static void dev_event_free(ggml_backend_dev_t, ggml_backend_event_t ev) { cudaEventDestroy((cudaEvent_t) ev->context); delete ev; }
+static void dev_event_sync(ggml_backend_dev_t, ggml_backend_event_t ev) { B200_CHECK(cudaEventSynchronize((cudaEvent_t) ev->context)); }
+static const ggml_backend_device_i k_device_iface = {
+    dev_name, dev_desc, dev_memory, dev_type, dev_props, dev_init_backend, dev_buft, dev_host_buft, nullptr,
+    dev_supports_op, dev_supports_buft, dev_offload_op, dev_event_new, dev_event_free, dev_event_sync,
+};
+
+// ---- registry -------------------------------------------------------------------------------------------
+static const char * reg_name(ggml_backend_reg_t) { return "B200"; }
+static size_t reg_dev_count(ggml_backend_reg_t) { return g_reg_ctx.devices.size(); }
+static ggml_backend_dev_t reg_get_dev(ggml_backend_reg_t, size_t i) { return i < g_reg_ctx.devices.size() ? &g_reg_ctx.devices[i]->dev : nullptr; }
+
+static ggml_backend_feature g_features[] = { { "ARCH", "sm_100a" }, { "TCGEN05", "1" }, { "TMA", "1" }, { nullptr, nullptr } };
+static ggml_backend_feature * reg_get_features(ggml_backend_reg_t) { return g_features; }
+
+ggml_backend_buffer_type_t b200_split_buffer_type(int main_device, const float * tensor_split);   // b200_split.cpp
+
+static void * reg_proc_address(ggml_backend_reg_t, const char * name) {
+    if (!strcmp(name, "ggml_backend_get_features"))      return (void *) reg_get_features;
+    if (!strcmp(name, "ggml_backend_split_buffer_type")) return (void *) b200_split_buffer_type;
+    return nullptr;    // "ggml_backend_set_n_threads", "ggml_backend_dev_get_extra_bufts": not applicable
+}
+static const ggml_backend_reg_i k_reg_iface = { reg_name, reg_dev_count, reg_get_dev, reg_proc_address };
+
+extern "C" B200_API ggml_backend_reg_t ggml_backend_b200_reg(void) {
+    static std::once_flag once;
+    std::call_once(once, [] {
+        g_reg.api_version = GGML_BACKEND_API_VERSION; g_reg.iface = k_reg_iface; g_reg.context = &g_reg_ctx;
+        g_host_buft.iface = k_hbuft_iface; g_host_buft.device = nullptr; g_host_buft.context = nullptr;
+        const int n = b200_device_count();
+        for (int i = 0; i < n && i < B200_MAX_DEVICES; ++i) {
+            cudaDeviceProp prop; if (cudaGetDeviceProperties(&prop, i) != cudaSuccess) continue;
+            b200_device_ctx * d = new b200_device_ctx;
+            d->device = i; d->name = "B200_" + std::to_string(i); d->description = prop.name;
+            d->dev.iface = k_device_iface; d->dev.reg = &g_reg; d->dev.context = d;
+            d->buft.iface = k_buft_iface; d->buft.device = &d->dev; d->buft.context = d;
+            g_reg_ctx.devices.push_back(d);
+        }
+        if (!g_reg_ctx.devices.empty()) g_host_buft.device = &g_reg_ctx.devices[0]->dev;
+    });
+    return &g_reg;
+}
+extern "C" B200_API ggml_backend_reg_t ggml_backend_init(void) { return ggml_backend_b200_reg(); }
+extern "C" B200_API int ggml_backend_score(void) { return b200_device_count() > 0 ? 100 : 0; }

@@ -1,0 +1,109 @@
+// b200_common.cuh -- shared device/host definitions for the ggml-b200 kernels.
+// GGUF block layouts restated from the reference (ggml/src/ggml-common.h:170-344); byte-exact
+// input format, the only thing we share with ggml-cuda is the file format.
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include "../../include/ggml-b200.h"
+
+#define B200_WARP 32
+#define QK 32          // elements per q4_0 / q8_0 / q8_1 block
+#define QKK 256        // elements per K-quant super-block
+
+struct __align__(2) blk_q4_0 { __half d; uint8_t qs[16]; };                                 // 18 B
+struct __align__(2) blk_q8_0 { __half d; int8_t  qs[32]; };                                 // 34 B
+struct __align__(4) blk_q8_1 { __half d; __half s; int8_t qs[32]; };                        // 36 B
+struct __align__(4) blk_q4_K { __half d; __half dmin; uint8_t scales[12]; uint8_t qs[128]; };              // 144 B
+struct __align__(4) blk_q5_K { __half d; __half dmin; uint8_t scales[12]; uint8_t qh[32]; uint8_t qs[128]; }; // 176 B
+struct __align__(2) blk_q6_K { uint8_t ql[128]; uint8_t qh[64]; int8_t scales[16]; __half d; };            // 210 B
+static_assert(sizeof(blk_q4_0) == 18 && sizeof(blk_q8_0) == 34 && sizeof(blk_q8_1) == 36, "block size");
+static_assert(sizeof(blk_q4_K) == 144 && sizeof(blk_q5_K) == 176 && sizeof(blk_q6_K) == 210, "block size");
+
+// bytes per block / elements per block for a b200_type (0 if not a block type we know)
+static inline __host__ __device__ int b200_blck_size(int type) {
+    switch (type) {
+        case B200_TYPE_F32: case B200_TYPE_F16: case B200_TYPE_BF16: case B200_TYPE_I32: return 1;
+        case B200_TYPE_Q4_0: case B200_TYPE_Q8_0: case B200_TYPE_Q8_1: return 32;
+        case B200_TYPE_Q4_K: case B200_TYPE_Q5_K: case B200_TYPE_Q6_K: return 256;
+    }
+    return 0;
+}
+static inline __host__ __device__ size_t b200_type_size(int type) {
+    switch (type) {
+        case B200_TYPE_F32: case B200_TYPE_I32: return 4;
+        case B200_TYPE_F16: case B200_TYPE_BF16: return 2;
+        case B200_TYPE_Q4_0: return 18; case B200_TYPE_Q8_0: return 34; case B200_TYPE_Q8_1: return 36;
+        case B200_TYPE_Q4_K: return 144; case B200_TYPE_Q5_K: return 176; case B200_TYPE_Q6_K: return 210;
+    }
+    return 0;
+}
+static inline size_t b200_row_size(int type, int64_t ne0) {
+    return (size_t)(ne0 / b200_blck_size(type)) * b200_type_size(type);
+}
+
+// ---- host-side context ------------------------------------------------------------------
+struct b200_ctx {
+    int          device;
+    cudaStream_t stream;
+    int          sm_count;
+    // scratch arena for activation quantization / split-KV partials / sorted ids (grows on demand)
+    void *       scratch[4];
+    size_t       scratch_size[4];
+    uint64_t     launches;
+};
+
+void   b200_set_error(const char * fmt, ...);
+void * b200_scratch(b200_ctx * ctx, int slot, size_t nbytes);   // returns device ptr, NULL on failure
+
+#define B200_CUDA_TRY(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { \
+        b200_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e_)); return B200_ERR_CUDA; } } while (0)
+#define B200_LAUNCH_CHECK(ctx) do { (ctx)->launches++; cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) { \
+        b200_set_error("%s:%d: kernel launch -> %s", __FILE__, __LINE__, cudaGetErrorString(e_)); return B200_ERR_CUDA; } } while (0)
+
+// ---- small device helpers ------------------------------------------------------------------
+static __device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+static __device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+// streaming 128-bit load that does not pollute L1 (weights are read exactly once)
+static __device__ __forceinline__ int4 ld_stream_16(const void * p) {
+    int4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.s32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+static __device__ __forceinline__ int ld_stream_4(const void * p) {
+    int r;
+    asm volatile("ld.global.nc.L1::no_allocate.s32 %0, [%1];" : "=r"(r) : "l"(p));
+    return r;
+}
+static __device__ __forceinline__ int ld_u16x2(const void * p) {   // 4 bytes from a 2-byte aligned address
+    const uint16_t * q = (const uint16_t *) p;
+    return (int) ((uint32_t) q[0] | ((uint32_t) q[1] << 16));
+}
+
+// ---- internal launchers (defined in the .cu files) ----------------------------------------
+int b200_launch_quantize_q8_1(b200_ctx * ctx, const float * x, size_t x_row_stride, void * y, int64_t k, int64_t nrows, int variant);
+int b200_launch_quantize_q8_1_soa(b200_ctx * ctx, const float * x, size_t nb1, size_t nb2, size_t nb3,
+                                  int64_t k, int64_t ne1, int64_t ne2, int64_t ne3, void * image, int variant);
+static inline size_t b200_q8_1_soa_size(int64_t k, int64_t ncol) { return (size_t) ncol * k + (size_t) ncol * (k / 32) * 4; }
+int b200_launch_gemv_q(b200_ctx * ctx, const b200_tensor * w, const void * image, int64_t ne11, int64_t ne12, int64_t ne13, b200_tensor * dst);
+int b200_launch_gemv_id_q(b200_ctx * ctx, const b200_tensor * as, const void * image, int64_t ne11, int64_t n_tokens,
+                          const b200_tensor * ids, b200_tensor * dst);
+int b200_launch_fattn_vec(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v,
+                          const b200_tensor * mask, const b200_tensor * sinks, b200_tensor * dst,
+                          float scale, float max_bias, float softcap);
+#define B200_GEMV_MAX_COLS 8
+bool b200_gemm_supported(const b200_tensor * w, const b200_tensor * x);
+int  b200_launch_gemm_q(b200_ctx * ctx, const b200_tensor * w, const b200_tensor * x, b200_tensor * dst);
+bool b200_gemm_id_supported(const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids);
+int  b200_launch_gemm_id_q(b200_ctx * ctx, const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids, b200_tensor * dst);
+int  b200_launch_matmul_float(b200_ctx * ctx, const b200_tensor * w, const b200_tensor * x, b200_tensor * dst);

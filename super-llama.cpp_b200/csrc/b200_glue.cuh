@@ -1,0 +1,9 @@
+// b200_glue.cuh -- cheap non-hot-path ggml ops so a whole llama graph stays on the device.
+// Declarations only; kernels live in b200_glue.cu.  All take ggml-style strided views.
+#pragma once
+#include "b200_common.cuh"
+
+// returns true if (op, types, layout) is implemented by b200_glue_compute
+struct ggml_tensor;
+bool b200_glue_supports(const struct ggml_tensor * op);
+int  b200_glue_compute(b200_ctx * ctx, struct ggml_tensor * op);
