@@ -1,0 +1,483 @@
+#!/usr/bin/env python
+"""bench.py -- BASELINE.json's metric on BASELINE.json's config: llama-bench style tg128 (and pp512) tok/s of
+Llama-3-8B Q4_K_M (random-init GGUF block weights, exact Q4_K_M tensor-type mix) on N B200s.
+
+One "step" = one pass of the hot path for one decode token: every GGML_OP_MUL_MAT node of the llama graph
+(wq, wk, wv, wo, ffn_gate, ffn_up, ffn_down per layer + the output head) and the per-layer GGML_OP_FLASH_ATTN_EXT
+over the f16 KV-cache views, issued through the C-ABI of libggml-b200.so (include/ggml-b200.h) and replayed as a
+CUDA graph.  `value` is timed with CUDA events with all inputs resident in HBM; `e2e` adds, every step, the
+host->device copy of the token's embedding row from pinned memory and the device->host read of the logits.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--depth D] [--no-pp]
+
+Multi-GPU (torchrun, one rank per GPU): split-mode=row tensor parallelism -- every rank owns rows
+[row_low, row_high) of each weight (b200_split_row_range, reference ggml-cuda.cu:777-803) and the row slices are
+all-gathered with NCCL; scaling is "strong" (one model, one token stream).
+--impl reference times the reference's own ggml-cpu implementation of the same ops on the host cores
+(oracle/_ref, compiled in place from /root/reference; the oracle port if that is absent).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "super-llama.cpp_b200"))
+
+F32, F16, Q4_K, Q6_K, I32 = 0, 1, 12, 14, 26
+BLCK = {Q4_K: 256, Q6_K: 256}
+TSIZE = {Q4_K: 144, Q6_K: 210}
+
+# Llama-3-8B: n_embd, n_ff, n_head, n_head_kv, head_dim, n_layer, n_vocab
+LLAMA3_8B = dict(name="llama3-8b", n_embd=4096, n_ff=14336, n_head=32, n_head_kv=8, head_dim=128, n_layer=32, n_vocab=128256)
+
+
+def use_more_bits(i, n):       # src/llama-quant.cpp:186-188
+    return i < n // 8 or i >= 7 * n // 8 or (i - n // 8) % 3 == 2
+
+
+def q4_k_m_layer_types(cfg):
+    """tensor types llama-quantize picks for Q4_K_M (src/llama-quant.cpp:207-227,302-303,358-364)"""
+    n = cfg["n_layer"]
+    out = []
+    for i in range(n):
+        more = use_more_bits(i, n)
+        out.append(dict(wq=Q4_K, wk=Q4_K, wv=Q6_K if more else Q4_K, wo=Q4_K, gate=Q4_K, up=Q4_K, down=Q6_K if more else Q4_K))
+    return out, Q6_K   # output.weight -> q6_K
+
+
+def weight_shapes(cfg):
+    e, f, kv = cfg["n_embd"], cfg["n_ff"], cfg["n_head_kv"] * cfg["head_dim"]
+    return dict(wq=(e, e), wk=(e, kv), wv=(e, kv), wo=(e, e), gate=(e, f), up=(e, f), down=(f, e))   # (K, M)
+
+
+def wbytes(t, K, M):
+    return K // BLCK[t] * TSIZE[t] * M
+
+
+def random_blocks(rng, t, nblocks):
+    raw = rng.integers(0, 256, size=(nblocks, TSIZE[t]), dtype=np.uint8)
+    if t == Q4_K:
+        raw[:, 0:2] = (rng.uniform(0.1, 1, nblocks) * 2e-3).astype(np.float16).view(np.uint8).reshape(nblocks, 2)
+        raw[:, 2:4] = (rng.uniform(0.1, 1, nblocks) * 2e-3).astype(np.float16).view(np.uint8).reshape(nblocks, 2)
+    else:
+        raw[:, 208:210] = (rng.uniform(-1, 1, nblocks) * 1e-3).astype(np.float16).view(np.uint8).reshape(nblocks, 2)
+    return raw.reshape(-1)
+
+
+class ClockSampler:
+    """samples nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)"""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, device):
+        self.device, self.rows, self.proc = device, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = sorted(float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit())
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 7 for n, v in zip(names, r[3:7]) if v.lower().startswith("active")})
+        pw = [float(r[2]) for r in self.rows if len(r) > 2 and r[2].replace(".", "").isdigit()]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx[0] if mx else None, "reasons": reasons,
+                "power_w_max": max(pw) if pw else None, "samples": len(self.rows)}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d.get("hbm_gbs", 6650.0), d.get("bf16_tflops", 1590.0), d.get("bf16_tflops_sustained", 1400.0), "measured"
+    return 6650.0, 1590.0, 1400.0, "fallback"
+
+
+# ------------------------------------------------------------------------------------------------------------
+class HotPathModel:
+    """The hot-path nodes of one llama decode/prefill step over device-resident random-init Q4_K_M weights.
+    rank/world: split-mode=row shard (rows [lo, hi) of every weight); world == 1 is the whole model."""
+
+    def __init__(self, B, ctx, cfg, n_tokens, depth, rank=0, world=1, seed=1234, alloc=None):
+        self.B, self.ctx, self.cfg, self.N = B, ctx, cfg, n_tokens
+        self.rank, self.world = rank, world
+        rng = np.random.default_rng(seed + rank)
+        types, out_type = q4_k_m_layer_types(cfg)
+        shapes = weight_shapes(cfg)
+        pool = {t: random_blocks(rng, t, (48 << 20) // TSIZE[t]) for t in (Q4_K, Q6_K)}
+        self.weight_bytes = 0
+
+        def make_weight(t, K, M):
+            lo, hi = B.split_row_range(M, world, rank, 32) if world > 1 else (0, M)
+            ml = hi - lo
+            w = ctx.empty(t, [K, ml])
+            nb, blk = w.nbytes, TSIZE[t]
+            off = 0
+            while off < nb:                       # tile the random pool at random block-aligned offsets
+                start = int(rng.integers(0, pool[t].size // blk // 2)) * blk
+                n = min(nb - off, pool[t].size - start)
+                ctx.h2d(w.ptr + off, pool[t][start:start + n])
+                off += n
+            self.weight_bytes += nb
+            return w, lo, hi
+
+        self.layers = []
+        for lt in types:
+            self.layers.append({name: make_weight(lt[name], *shapes[name]) for name in shapes})
+        self.output = make_weight(out_type, cfg["n_embd"], cfg["n_vocab"])
+        ctx.synchronize()
+
+        e, f, hd, nh, nkv = cfg["n_embd"], cfg["n_ff"], cfg["head_dim"], cfg["n_head"], cfg["n_head_kv"]
+        kvd = nkv * hd
+        N = n_tokens
+        self.n_kv = ((depth + N + 255) // 256) * 256                      # src/llama-kv-cache.cpp:992-1006
+        self.kv_size = self.n_kv
+        alloc = alloc or (lambda t, ne: ctx.empty(t, ne))
+        # full-size activation buffers (what every rank sees after the all-gather)
+        self.x = alloc(F32, [e, N]); self.h = alloc(F32, [e, N]); self.ff = alloc(F32, [f, N])
+        self.q = alloc(F32, [e, N]); self.k = alloc(F32, [kvd, N]); self.v = alloc(F32, [kvd, N])
+        self.attn = alloc(F32, [e, N]); self.o = alloc(F32, [e, N]); self.g = alloc(F32, [f, N]); self.u = alloc(F32, [f, N])
+        self.d = alloc(F32, [e, N])
+        self.logits = alloc(F32, [cfg["n_vocab"], 1])
+        for t, scale in ((self.x, 1.0), (self.h, 1.0), (self.ff, 0.3), (self.attn, 0.5)):
+            ctx.h2d(t.ptr, (rng.standard_normal(t.ne[0] * t.ne[1]) * scale).astype(np.float32))
+        # KV cache: one [n_embd_k_gqa, kv_size] f16 buffer per layer for K and for V (heads interleaved per token row)
+        kvh = (rng.standard_normal(kvd * min(self.kv_size, 4096)) * 0.5).astype(np.float16)
+        self.kc, self.vc = [], []
+        for _ in range(cfg["n_layer"]):
+            for lst in (self.kc, self.vc):
+                c = ctx.empty(F16, [kvd, self.kv_size])
+                for off in range(0, c.nbytes, kvh.nbytes):
+                    ctx.h2d(c.ptr + off, kvh[: min(kvh.size, (c.nbytes - off) // 2)])
+                lst.append(c)
+        tok, head = kvd * 2, hd * 2
+        self.kviews = [c.view([hd, self.n_kv, nkv, 1], [2, tok, head, tok * self.kv_size]) for c in self.kc]
+        self.vviews = [c.view([hd, self.n_kv, nkv, 1], [2, tok, head, tok * self.kv_size]) for c in self.vc]
+        nm = max(8, ((N + 63) // 64) * 64)                                 # mask rows padded (GGML_KQ_MASK_PAD)
+        mask = np.zeros((nm, self.n_kv), dtype=np.float16)
+        for i in range(N):                                                  # causal: token i of the batch sees depth + i + 1 keys
+            mask[i, depth + i + 1:] = -np.inf
+        self.mask = ctx.upload(F16, [self.n_kv, nm], mask)
+        self.qview = self.q.view([hd, N, nh, 1], [4, e * 4, hd * 4, e * 4 * N])          # [head_dim, n_tokens, n_head]
+        self.attn4 = self.attn.view([hd, nh, N, 1], [4, hd * 4, e * 4, e * 4 * N])       # dst [DV, H, N]
+        self.scale = 1.0 / float(np.sqrt(hd))
+        self.kv_bytes_per_layer = 2 * self.n_kv * kvd * 2
+        ctx.synchronize()
+        self.gather = None          # set by the multi-GPU driver: gather(full_tensor, lo, hi) after a sharded matmul
+
+    def _mm(self, w, x, dst):
+        wt, lo, hi = w
+        if self.world == 1:
+            self.ctx.mul_mat(wt, x, dst)
+        else:
+            M, N = dst.ne[0], dst.ne[1]
+            local = dst.view([hi - lo, N, 1, 1], [4, M * 4, M * 4 * N, M * 4 * N], offset=lo * 4)   # rows [lo, hi) of every column
+            self.ctx.mul_mat(wt, x, local)
+            self.gather(dst, lo, hi)
+
+    def step(self):
+        """issue every MUL_MAT and FLASH_ATTN_EXT node of one llama graph evaluation on the ctx stream"""
+        c = self.ctx
+        for il, L in enumerate(self.layers):
+            self._mm(L["wq"], self.x, self.q)
+            self._mm(L["wk"], self.x, self.k)
+            self._mm(L["wv"], self.x, self.v)
+            c.flash_attn_ext(self.qview, self.kviews[il], self.vviews[il], self.mask, None, self.attn4, self.scale)
+            self._mm(L["wo"], self.attn, self.o)
+            self._mm(L["gate"], self.h, self.g)
+            self._mm(L["up"], self.h, self.u)
+            self._mm(L["down"], self.ff, self.d)
+        last = self.x if self.N == 1 else self.x.view([self.cfg["n_embd"], 1, 1, 1], self.x.nb, offset=(self.N - 1) * self.cfg["n_embd"] * 4)
+        self._mm(self.output, last, self.logits)          # output head runs for the last row only (src/models/llama.cpp:97-98)
+
+    # ---- algorithmic work --------------------------------------------------------------
+    def matmul_flops(self):
+        shapes = weight_shapes(self.cfg)
+        per_layer = sum(2 * K * M for K, M in shapes.values())
+        return self.N * per_layer * self.cfg["n_layer"] + 2 * self.cfg["n_embd"] * self.cfg["n_vocab"]
+
+    def attn_flops(self):
+        return 2 * self.cfg["n_head"] * self.N * 2 * self.cfg["head_dim"] * self.n_kv * self.cfg["n_layer"]
+
+
+# ------------------------------------------------------------------------------------------------------------
+def cpu_baseline(cfg, depth, budget_s=20.0, full_token_steps=0, warmup=1):
+    """The reference's ggml-cpu implementation of the same ops, timed on this box's host cores (oracle/_ref compiled
+    in place from /root/reference; the plain-C oracle port if that is absent).  Bounded sample: ONE transformer layer
+    of each tensor-type variant (7 MUL_MAT + FLASH_ATTN_EXT at n=1) + the output head, extrapolated to n_layer layers.
+    Returns (tok/s, kind, cores, sample description)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import oracle as O
+    cores = os.cpu_count() or 1
+    rng = np.random.default_rng(7)
+    shapes = weight_shapes(cfg)
+    types, out_type = q4_k_m_layer_types(cfg)
+    n_kv = ((depth + 1 + 255) // 256) * 256
+    if O.have_reference():
+        ref = O.Reference()
+        ops = {}
+
+        def mm(t, K, M):
+            key = (t, K, M)
+            if key not in ops:
+                op = O.ref_mm_op(ref, t, K, M, 1, cores)
+                w = op.input(0)
+                blk = random_blocks(rng, t, min(w.size // TSIZE[t], 1 << 16))
+                for off in range(0, w.size, blk.size):
+                    n = min(blk.size, w.size - off); w[off:off + n] = blk[:n]
+                op.input(1).view(np.float32)[:] = rng.standard_normal(K).astype(np.float32)
+                ops[key] = op
+            return ops[key]
+
+        fa = O.ref_fa_op(ref, cfg["head_dim"], cfg["head_dim"], 1, cfg["n_head"], n_kv, cfg["n_head_kv"], 8, 0.0884, cores)
+        fa.input(0).view(np.float32)[:] = rng.standard_normal(fa.input(0).size // 4).astype(np.float32)
+        for i in (1, 2):
+            fa.input(i).view(np.float16)[:] = (rng.standard_normal(fa.input(i).size // 2) * 0.5).astype(np.float16)
+        variants = {}
+        for lt in types:
+            variants.setdefault(tuple(sorted(lt.items())), 0)
+            variants[tuple(sorted(lt.items()))] += 1
+        total_us = 0.0
+        t_start = time.time()
+        for var, count in variants.items():
+            layer_ops = [mm(t, *shapes[name]) for name, t in var] + [fa]
+            for _ in range(3):                                      # warm-up: thread pool + page faults
+                for op in layer_ops:
+                    op.run()
+            best = None
+            for _ in range(5):
+                us = sum(op.run() for op in layer_ops)
+                best = us if best is None else min(best, us)
+                if time.time() - t_start > budget_s:
+                    break
+            total_us += best * count
+        head = mm(out_type, cfg["n_embd"], cfg["n_vocab"])
+        for _ in range(2):
+            head.run()
+        total_us += min(head.run() for _ in range(3))
+        for op in list(ops.values()) + [fa]:
+            op.free()
+        return 1e6 / total_us, "reference", cores, (f"one layer of each of the {len(variants)} Q4_K_M tensor-type variants (7 MUL_MAT + FLASH_ATTN_EXT, n=1, "
+                                                    f"n_kv={n_kv}) + output head on ggml-cpu (oracle/_ref, OpenMP, {cores} threads), best of 5, x{cfg['n_layer']} layers")
+    # port: the scalar oracle on one core, one q4_K ffn_down GEMV, scaled by bytes
+    orc = O.Oracle()
+    K, M = shapes["down"]
+    M = 512
+    w = O.random_blocks(rng, O.Q4_K, K, M)
+    x = rng.standard_normal((1, K)).astype(np.float32)
+    t0 = time.time(); orc.mul_mat(O.Q4_K, w, K, M, x, 1); dt = time.time() - t0
+    total_bytes = sum(wbytes(lt[n], *shapes[n]) for lt in types for n in shapes) + wbytes(out_type, cfg["n_embd"], cfg["n_vocab"])
+    return 1.0 / (dt * total_bytes / w.nbytes), "port", 1, f"scalar oracle, q4_K {M}x{K} GEMV on 1 core scaled by weight bytes"
+
+
+def run_reference(args):
+    cfg = LLAMA3_8B
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    t0 = time.time()
+    tps, kind, cores, sample = cpu_baseline(cfg, args.depth, budget_s=60.0)
+    line = {"impl": "reference", "metric": "tg128 tok/s (llama-bench, Llama-3-8B Q4_K_M)", "value": tps, "unit": "tok/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / tps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "int8 dot / f32 accumulate (q8_0, q8_K activations)", "data": "synthetic",
+            "config": {"workload": "llama3-8b-q4_k_m tg128 decode hot path (MUL_MAT + FLASH_ATTN_EXT nodes)", "depth": args.depth},
+            "cpu_baseline": {"value": tps, "unit": "tok/s", "cores": cores, "kind": kind, "sample": sample},
+            "e2e": {"value": tps, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0, "wall_s": time.time() - t0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import ggml_b200 as B
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = torch = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    ctx = B.Context(local)
+    cfg = LLAMA3_8B
+    hbm_gbs, tf_burst, tf_sust, peak_src = measured_peaks()
+
+    keep = []
+
+    def alloc(t, ne):
+        if world == 1:
+            return ctx.empty(t, ne)
+        buf = torch.empty(int(np.prod(ne)) * (4 if t == F32 else 2), dtype=torch.uint8, device=f"cuda:{local}")
+        keep.append(buf)
+        dt = B.DeviceTensor(ctx, t, ne, ptr=buf.data_ptr())
+        dt.torch = buf
+        return dt
+
+    tg = HotPathModel(B, ctx, cfg, 1, args.depth, rank, world, alloc=alloc)
+    if world > 1:
+        ext = torch.cuda.ExternalStream(ctx.stream, device=f"cuda:{local}")
+
+        def gather(full, lo, hi):
+            # even split (rounding 32 divides every row count here): rank r's slice sits at rows [r*m, (r+1)*m)
+            t = full.torch.view(torch.float32)
+            with torch.cuda.stream(ext):
+                dist.all_gather_into_tensor(t, t[lo:hi])        # in place: input is the rank's own slice of the output
+        tg.gather = gather
+
+    def timed(model, steps, warmup, use_graph):
+        for _ in range(max(warmup, 1)):
+            model.step()
+        ctx.synchronize()
+        graph = None
+        if use_graph:
+            ctx.graph_begin(); model.step(); graph = ctx.graph_end()
+            for _ in range(2):
+                ctx.graph_launch(graph)
+            ctx.synchronize()
+        if dist:
+            dist.barrier()
+        e0, e1 = ctx.event(), ctx.event()
+        n0 = ctx.launches
+        ctx.synchronize()
+        ctx.record(e0)
+        for _ in range(steps):
+            if graph:
+                ctx.graph_launch(graph)
+            else:
+                model.step()
+        ctx.record(e1)
+        ctx.synchronize()
+        ms = ctx.elapsed_ms(e0, e1)
+        if dist:
+            t = torch.tensor([ms], device=f"cuda:{local}"); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms = float(t.item())
+        return ms / steps, graph, ctx.launches - n0
+
+    use_graph = world == 1 and not args.no_graph
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches_before = ctx.launches
+    ms_tg, graph, eager_launches = timed(tg, args.steps, args.warmup, use_graph)
+    clocks = sampler.stop() if rank == 0 else None
+    launches_per_step = (ctx.launches - launches_before) // (max(args.warmup, 1) + (1 if use_graph else args.steps)) if use_graph else eager_launches // args.steps
+
+    # ---- e2e: same step through the public API with host buffers: H2D of the embedding row, D2H of the logits, sync per token
+    L = B.lib()
+    e = cfg["n_embd"]
+    hx = L.b200_host_alloc(e * 4); hl = L.b200_host_alloc(cfg["n_vocab"] * 4)
+    np.ctypeslib.as_array((__import__("ctypes").c_float * e).from_address(hx))[:] = np.random.default_rng(1).standard_normal(e).astype(np.float32)
+    e2e_steps = args.steps
+    ctx.synchronize()
+    if dist:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        L.b200_memcpy_h2d(ctx.h, tg.x.ptr, hx, e * 4)
+        if graph:
+            ctx.graph_launch(graph)
+        else:
+            tg.step()
+        L.b200_memcpy_d2h(ctx.h, hl, tg.logits.ptr, cfg["n_vocab"] * 4)
+        ctx.synchronize()                                   # llama-bench synchronizes after every generated token
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
+    if dist:
+        t = torch.tensor([e2e_ms], device=f"cuda:{local}"); dist.all_reduce(t, op=dist.ReduceOp.MAX); e2e_ms = float(t.item())
+
+    # ---- roofline leg: per-kernel CUDA-event times of the same step, eager, on the launching stream
+    ctx.profile(True)
+    for _ in range(3):
+        tg.step()
+    prof = ctx.profile_get()
+    ctx.profile(False)
+    gemv_ms, gemv_n = prof.get("gemv", (0.0, 0))
+    shapes = weight_shapes(cfg)
+    act_bytes = sum((K // 32) * 36 + M * 4 for lt in tg.layers for (K, M) in [shapes[n] for n in shapes]) // max(world, 1)
+    gemv_bytes_step = tg.weight_bytes + act_bytes
+    gemv_ms_step = gemv_ms / 3
+    achieved = gemv_bytes_step / (gemv_ms_step * 1e-3) / 1e9 if gemv_ms_step > 0 else 0.0
+
+    result = None
+    if rank == 0:
+        tps = 1e3 / ms_tg
+        total_bytes = tg.weight_bytes * world + tg.kv_bytes_per_layer * cfg["n_layer"]
+        result = {
+            "metric": "tg128 tok/s (llama-bench, Llama-3-8B Q4_K_M)", "value": tps, "unit": "tok/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_tg, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "int8 dp4a dot / f32 accumulate (q8_1 activations); f16 KV, f32 softmax", "data": "synthetic",
+            "config": {"workload": "llama3-8b-q4_k_m tg128: all MUL_MAT + FLASH_ATTN_EXT nodes of one decode token (32 layers + output head); glue ops not included",
+                       "tensor_types": "Q4_K_M mix: q4_K, q6_K on attn_v/ffn_down of 16 layers, q6_K output", "depth": args.depth, "n_kv": tg.n_kv,
+                       "parallelism": f"row-split tp{world}" if world > 1 else "single GPU", "cuda_graph": bool(graph),
+                       "l2": "weights 4.6 GB >> 126 MB L2, streamed once per step"},
+            "hbm_bytes_per_step": total_bytes, "hbm_frac_whole_step": total_bytes / world / (ms_tg * 1e-3) / 1e9 / hbm_gbs,
+            "roofline": {"kernel": "k_gemv (dequant-GEMV, all weight types)", "bound": "hbm", "achieved": achieved, "peak": hbm_gbs, "unit": "GB/s",
+                         "frac": achieved / hbm_gbs, "traffic": None, "peak_source": f"{peak_src} (MEASURED_PEAKS.json hbm_gbs)",
+                         "launches_per_step": gemv_n // 3, "ms_per_step": gemv_ms_step, "algorithmic_bytes_per_step": gemv_bytes_step},
+            "kernel_ms_per_step": {k: v[0] / 3 for k, v in prof.items()},
+            "e2e": {"value": 1e3 / e2e_ms, "unit": "tok/s", "h2d_bytes_per_step": e * 4, "d2h_bytes_per_step": cfg["n_vocab"] * 4, "ms_per_step": e2e_ms},
+            "gpu_launches": launches_per_step * args.steps, "gpu_launches_per_step": launches_per_step, "clocks": clocks,
+        }
+    # ---- secondary: pp512 (prefill) on one GPU
+    if world == 1 and not args.no_pp:
+        del tg
+        pp = HotPathModel(B, ctx, cfg, 512, args.depth)
+        ms_pp, _, _ = timed(pp, max(2, min(args.steps, 5)), 1, False)
+        ctx.profile(True); pp.step(); prof_pp = ctx.profile_get(); ctx.profile(False)
+        flops = pp.matmul_flops()
+        mm_ms = prof_pp.get("gemm", (0.0, 0))[0] + prof_pp.get("gemv", (0.0, 0))[0]
+        result["pp512"] = {"value": 512e3 / ms_pp, "unit": "tok/s", "ms_per_step": ms_pp, "matmul_tflop_per_step": flops / 1e12,
+                           "roofline": {"kernel": "MUL_MAT prefill kernels", "bound": "tensor", "achieved": flops / (mm_ms * 1e-3) / 1e12 if mm_ms else 0.0,
+                                        "peak": tf_sust, "unit": "TFLOP/s", "frac": (flops / (mm_ms * 1e-3) / 1e12 / tf_sust) if mm_ms else 0.0,
+                                        "peak_source": f"{peak_src} bf16_tflops_sustained"},
+                           "kernel_ms_per_step": {k: v[0] for k, v in prof_pp.items()}}
+    if rank == 0:
+        if not args.no_cpu and world == 1:
+            try:
+                v, kind, cores, sample = cpu_baseline(cfg, args.depth)
+                result["cpu_baseline"] = {"value": v, "unit": "tok/s", "cores": cores, "kind": kind, "sample": sample}
+            except Exception as ex:                      # the baseline is a reported number, never a reason to lose the GPU line
+                result["cpu_baseline"] = {"value": None, "unit": "tok/s", "cores": os.cpu_count(), "kind": "unavailable", "sample": repr(ex)}
+        print(json.dumps(result), flush=True)
+    if dist:
+        dist.barrier(); dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=128)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--depth", type=int, default=0, help="tokens already in the KV cache (llama-bench -d)")
+    ap.add_argument("--no-pp", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-graph", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

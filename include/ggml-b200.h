@@ -80,6 +80,21 @@ B200_API void *       b200_ctx_stream(const b200_ctx * ctx);   // cudaStream_t
 B200_API int          b200_ctx_synchronize(b200_ctx * ctx);
 B200_API uint64_t     b200_ctx_launch_count(const b200_ctx * ctx);   // kernels launched so far through this ctx
 
+// ---- measurement helpers (bench.py): CUDA events on the ctx stream, per-kernel-kind event profile, CUDA graphs ----
+// kernel kinds: 0 quantize_q8_1, 1 gemv, 2 gemv_id, 3 gemm, 4 fattn, 5 fattn_combine, 6 matmul_float, 7 glue, 8 mmid_sort, 9 convert
+B200_API uint64_t b200_ctx_launch_count_kind(const b200_ctx * ctx, int kind);
+B200_API int      b200_ctx_profile(b200_ctx * ctx, int enable);      // (re)start or stop bracketing every launch with events
+B200_API int      b200_ctx_profile_get(b200_ctx * ctx, int kind, double * ms_total, uint64_t * launches);   // synchronizes
+B200_API void *   b200_event_create(void);
+B200_API int      b200_event_destroy(void * ev);
+B200_API int      b200_event_record(b200_ctx * ctx, void * ev);
+B200_API int      b200_event_elapsed_ms(void * ev0, void * ev1, float * ms);     // waits for ev1
+// capture everything issued on the ctx stream between begin/end into a graph; launch replays it on the ctx stream
+B200_API int      b200_graph_begin(b200_ctx * ctx);
+B200_API void *   b200_graph_end(b200_ctx * ctx);                    // cudaGraphExec_t, NULL on failure
+B200_API int      b200_graph_launch(b200_ctx * ctx, void * graph_exec);
+B200_API int      b200_graph_destroy(void * graph_exec);
+
 // ---- memory ------------------------------------------------------------------------------
 B200_API void * b200_malloc(b200_ctx * ctx, size_t nbytes);    // cudaMalloc on ctx's device
 B200_API int    b200_free(b200_ctx * ctx, void * dptr);
@@ -109,13 +124,6 @@ B200_API int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b200_
 B200_API int b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k,
                                  const b200_tensor * v, const b200_tensor * mask, const b200_tensor * sinks,
                                  b200_tensor * dst, float scale, float max_bias, float logit_softcap);
-
-// ---- load-time weight repack (SoA, TMA/128-bit friendly; DESIGN.md "HBM layout") ----------
-// nbytes of the repacked image of a [k, nrows] matrix of `type` (>= the GGUF size, 256-byte aligned).
-B200_API size_t b200_repack_size(int type, int64_t k, int64_t nrows);
-// src: GGUF blocks on the device; dst: repacked image.  unrepack is the exact inverse (get_tensor).
-B200_API int b200_repack(b200_ctx * ctx, int type, const void * src, void * dst, int64_t k, int64_t nrows);
-B200_API int b200_unrepack(b200_ctx * ctx, int type, const void * src, void * dst, int64_t k, int64_t nrows);
 
 // ---- row split (split-mode=row) helpers; reference ggml-cuda.cu:777-803 --------------------
 // rows [*row_low, *row_high) of an nrows-row weight that rank `rank` of `world` owns under `tensor_split`

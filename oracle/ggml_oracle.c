@@ -76,6 +76,8 @@ void orc_fp16_to_fp32_row(const uint16_t * x, float * y, int64_t n) { for (int64
 static inline float bf16_to_fp32(uint16_t h) { return u2f((uint32_t) h << 16); }
 
 static inline int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+// cvtps2dq semantics: out-of-range and NaN inputs give the "integer indefinite" value 0x80000000
+static inline int cvt_x86(float r) { return (r >= -2147483648.0f && r < 2147483648.0f) ? (int) r : (int) 0x80000000u; }
 
 // ---- activation quantizers ----------------------------------------------------------------------
 // X86: ggml-cpu/arch/x86/quants.c:388-449 -- id = 127/amax, _mm256_round_ps(NEAREST) = ties-to-even,
@@ -91,10 +93,12 @@ void orc_quantize_row_q8_1(const float * x, void * vy, int64_t k, int variant) {
         int sum = 0;
         if (variant == ORC_Q8_1_X86) {
             const float id = amax != 0.0f ? 127.0f / amax : 0.0f;
-            for (int j = 0; j < QK; ++j) {
-                const int q = clampi((int) nearbyintf(x[i * QK + j] * id), -128, 127);   // default rounding mode = nearest-even
-                y[i].qs[j] = (int8_t) q; sum += q;
+            uint32_t usum = 0;                                     // the AVX2 body sums the int32 lanes BEFORE the saturating packs,
+            for (int j = 0; j < QK; ++j) {                         // and cvtps_epi32 gives 0x80000000 for inf/nan/overflow (a denormal amax)
+                const int q32 = cvt_x86(nearbyintf(x[i * QK + j] * id));   // default rounding mode = nearest-even
+                y[i].qs[j] = (int8_t) clampi(q32, -128, 127); usum += (uint32_t) q32;
             }
+            sum = (int) usum;
             y[i].s = orc_fp32_to_fp16(d * (float) sum);
         } else {
             const float id = d != 0.0f ? 1.0f / d : 0.0f;
@@ -115,7 +119,7 @@ void orc_quantize_row_q8_0(const float * x, void * vy, int64_t k) {
         const float d = amax / 127.0f;
         const float id = amax != 0.0f ? 127.0f / amax : 0.0f;
         y[i].d = orc_fp32_to_fp16(d);
-        for (int j = 0; j < QK; ++j) y[i].qs[j] = (int8_t) clampi((int) nearbyintf(x[i * QK + j] * id), -128, 127);
+        for (int j = 0; j < QK; ++j) y[i].qs[j] = (int8_t) clampi(cvt_x86(nearbyintf(x[i * QK + j] * id)), -128, 127);
     }
 }
 // ggml-quants.c:2555-2591; nearest_int() there is the 12582912.f magic-number trick = ties-to-even

@@ -12,6 +12,7 @@ void b200_set_error(const char * fmt, ...) {
     if (getenv("GGML_B200_DEBUG")) fprintf(stderr, "ggml-b200: %s\n", g_err);
 }
 extern "C" const char * b200_last_error(void) { return g_err; }
+static void prof_clear(b200_ctx * ctx);
 
 extern "C" int b200_device_count(void) {
     int n = 0;
@@ -29,7 +30,7 @@ extern "C" b200_ctx * b200_ctx_create(int device) {
     if (device < 0 || device >= n) { b200_set_error("b200_ctx_create: device %d not available (%d sm_100 devices)", device, n); return nullptr; }
     if (cudaSetDevice(device) != cudaSuccess) { b200_set_error("cudaSetDevice(%d) failed", device); return nullptr; }
     b200_ctx * ctx = (b200_ctx *) calloc(1, sizeof(b200_ctx));
-    ctx->device = device;
+    ctx->device = device; ctx->prof_open = -1;
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { b200_set_error("stream create failed"); free(ctx); return nullptr; }
     cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
     return ctx;
@@ -38,10 +39,81 @@ extern "C" void b200_ctx_destroy(b200_ctx * ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    for (int i = 0; i < 4; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
+    prof_clear(ctx); free(ctx->prof);
+    for (int i = 0; i < 8; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
     cudaStreamDestroy(ctx->stream);
     free(ctx);
 }
+// ---- per-kernel event profile ------------------------------------------------------------------
+void b200_prof_begin(b200_ctx * ctx, int kind) {
+    if (ctx->capturing) return;
+    if (ctx->prof_n == ctx->prof_cap) {
+        ctx->prof_cap = ctx->prof_cap ? ctx->prof_cap * 2 : 4096;
+        ctx->prof = (b200_prof_rec *) realloc(ctx->prof, sizeof(b200_prof_rec) * ctx->prof_cap);
+    }
+    b200_prof_rec * r = &ctx->prof[ctx->prof_n];
+    r->kind = kind;
+    if (cudaEventCreate(&r->e0) != cudaSuccess || cudaEventCreate(&r->e1) != cudaSuccess) { ctx->prof_open = -1; return; }
+    cudaEventRecord(r->e0, ctx->stream);
+    ctx->prof_open = ctx->prof_n++;
+}
+void b200_prof_end(b200_ctx * ctx) {
+    if (ctx->capturing || ctx->prof_open < 0) return;
+    cudaEventRecord(ctx->prof[ctx->prof_open].e1, ctx->stream);
+    ctx->prof_open = -1;
+}
+static void prof_clear(b200_ctx * ctx) {
+    for (int i = 0; i < ctx->prof_n; ++i) { cudaEventDestroy(ctx->prof[i].e0); cudaEventDestroy(ctx->prof[i].e1); }
+    ctx->prof_n = 0; ctx->prof_open = -1;
+}
+extern "C" int b200_ctx_profile(b200_ctx * ctx, int enable) {
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    prof_clear(ctx);
+    ctx->profile = enable ? 1 : 0;
+    return B200_OK;
+}
+extern "C" int b200_ctx_profile_get(b200_ctx * ctx, int kind, double * ms_total, uint64_t * launches) {
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    B200_CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    double t = 0.0; uint64_t n = 0;
+    for (int i = 0; i < ctx->prof_n; ++i) if (ctx->prof[i].kind == kind) {
+        float ms = 0.0f;
+        B200_CUDA_TRY(cudaEventElapsedTime(&ms, ctx->prof[i].e0, ctx->prof[i].e1));
+        t += ms; n++;
+    }
+    if (ms_total) *ms_total = t;
+    if (launches) *launches = n;
+    return B200_OK;
+}
+extern "C" uint64_t b200_ctx_launch_count_kind(const b200_ctx * ctx, int kind) { return kind >= 0 && kind < B200_K_COUNT ? ctx->launches_kind[kind] : 0; }
+
+// ---- events and graphs ---------------------------------------------------------------------------
+extern "C" void * b200_event_create(void) { cudaEvent_t e; if (cudaEventCreate(&e) != cudaSuccess) { cudaGetLastError(); return nullptr; } return (void *) e; }
+extern "C" int b200_event_destroy(void * ev) { B200_CUDA_TRY(cudaEventDestroy((cudaEvent_t) ev)); return B200_OK; }
+extern "C" int b200_event_record(b200_ctx * ctx, void * ev) { B200_CUDA_TRY(cudaEventRecord((cudaEvent_t) ev, ctx->stream)); return B200_OK; }
+extern "C" int b200_event_elapsed_ms(void * ev0, void * ev1, float * ms) {
+    B200_CUDA_TRY(cudaEventSynchronize((cudaEvent_t) ev1));
+    B200_CUDA_TRY(cudaEventElapsedTime(ms, (cudaEvent_t) ev0, (cudaEvent_t) ev1));
+    return B200_OK;
+}
+extern "C" int b200_graph_begin(b200_ctx * ctx) {
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    B200_CUDA_TRY(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
+    ctx->capturing = 1;
+    return B200_OK;
+}
+extern "C" void * b200_graph_end(b200_ctx * ctx) {
+    cudaGraph_t g = nullptr; cudaGraphExec_t ge = nullptr;
+    ctx->capturing = 0;
+    if (cudaStreamEndCapture(ctx->stream, &g) != cudaSuccess || !g) { b200_set_error("graph capture failed: %s", cudaGetErrorString(cudaGetLastError())); return nullptr; }
+    if (cudaGraphInstantiate(&ge, g, 0) != cudaSuccess) { b200_set_error("graph instantiate failed: %s", cudaGetErrorString(cudaGetLastError())); ge = nullptr; }
+    cudaGraphDestroy(g);
+    return (void *) ge;
+}
+extern "C" int b200_graph_launch(b200_ctx * ctx, void * ge) { B200_CUDA_TRY(cudaGraphLaunch((cudaGraphExec_t) ge, ctx->stream)); return B200_OK; }
+extern "C" int b200_graph_destroy(void * ge) { B200_CUDA_TRY(cudaGraphExecDestroy((cudaGraphExec_t) ge)); return B200_OK; }
+
 extern "C" int      b200_ctx_device(const b200_ctx * ctx) { return ctx->device; }
 extern "C" void *   b200_ctx_stream(const b200_ctx * ctx) { return (void *) ctx->stream; }
 extern "C" uint64_t b200_ctx_launch_count(const b200_ctx * ctx) { return ctx->launches; }
@@ -53,6 +125,7 @@ extern "C" int      b200_ctx_synchronize(b200_ctx * ctx) {
 
 void * b200_scratch(b200_ctx * ctx, int slot, size_t nbytes) {
     if (ctx->scratch_size[slot] >= nbytes && ctx->scratch[slot]) return ctx->scratch[slot];
+    if (ctx->capturing) { b200_set_error("scratch slot %d must grow to %zu bytes during graph capture: run the step once eagerly first", slot, nbytes); return nullptr; }
     // growing: earlier kernels on the stream may still read the old block -> drain first (rare, sizes converge fast)
     cudaStreamSynchronize(ctx->stream);
     if (ctx->scratch[slot]) cudaFree(ctx->scratch[slot]);

@@ -45,22 +45,40 @@ static inline size_t b200_row_size(int type, int64_t ne0) {
 }
 
 // ---- host-side context ------------------------------------------------------------------
+// kernel kinds for the per-kernel event profile (b200_ctx_profile_*), also the index of launch counters
+enum b200_kernel_kind {
+    B200_K_QUANTIZE = 0, B200_K_GEMV = 1, B200_K_GEMV_ID = 2, B200_K_GEMM = 3, B200_K_FATTN = 4, B200_K_FATTN_COMBINE = 5,
+    B200_K_MATMUL_FLOAT = 6, B200_K_GLUE = 7, B200_K_MMID_SORT = 8, B200_K_CONVERT = 9, B200_K_COUNT = 10,
+};
+struct b200_prof_rec { int kind; cudaEvent_t e0, e1; };
 struct b200_ctx {
     int          device;
     cudaStream_t stream;
     int          sm_count;
     // scratch arena for activation quantization / split-KV partials / sorted ids (grows on demand)
-    void *       scratch[4];
-    size_t       scratch_size[4];
+    void *       scratch[8];
+    size_t       scratch_size[8];
     uint64_t     launches;
+    uint64_t     launches_kind[B200_K_COUNT];
+    // optional per-kernel timing with CUDA events on the launching stream (bench.py's roofline leg)
+    int            profile;
+    b200_prof_rec * prof; int prof_n, prof_cap;
+    int            prof_open;        // index of the record whose e1 is pending, or -1
+    // CUDA graph capture state (b200_graph_*)
+    int          capturing;
 };
 
 void   b200_set_error(const char * fmt, ...);
 void * b200_scratch(b200_ctx * ctx, int slot, size_t nbytes);   // returns device ptr, NULL on failure
+void   b200_prof_begin(b200_ctx * ctx, int kind);               // no-ops unless ctx->profile
+void   b200_prof_end(b200_ctx * ctx);
 
 #define B200_CUDA_TRY(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { \
         b200_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e_)); return B200_ERR_CUDA; } } while (0)
-#define B200_LAUNCH_CHECK(ctx) do { (ctx)->launches++; cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) { \
+// every kernel launch is written   B200_LAUNCH(ctx, KIND, kernel<<<grid, block, smem, ctx->stream>>>(args));
+#define B200_LAUNCH(ctx, kind, ...) do { if ((ctx)->profile) b200_prof_begin((ctx), (kind)); __VA_ARGS__; \
+        if ((ctx)->profile) b200_prof_end(ctx); (ctx)->launches++; (ctx)->launches_kind[kind]++; \
+        cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) { \
         b200_set_error("%s:%d: kernel launch -> %s", __FILE__, __LINE__, cudaGetErrorString(e_)); return B200_ERR_CUDA; } } while (0)
 
 // ---- small device helpers ------------------------------------------------------------------

@@ -160,11 +160,10 @@ int b200_launch_fattn_vec(b200_ctx * ctx, const b200_tensor * q, const b200_tens
     dim3 grid((unsigned) p.N, (unsigned) p.H, (unsigned) q->ne[3]);
     const size_t smem = (size_t) (p.DK + FA_WARPS * p.DV + 2 * FA_WARPS) * sizeof(float);
     switch (p.DV / 64) {
-        case 1: k_fattn_vec<1><<<grid, FA_WARPS * 32, smem, ctx->stream>>>(p); break;
-        case 2: k_fattn_vec<2><<<grid, FA_WARPS * 32, smem, ctx->stream>>>(p); break;
-        case 4: k_fattn_vec<4><<<grid, FA_WARPS * 32, smem, ctx->stream>>>(p); break;
+        case 1: B200_LAUNCH(ctx, B200_K_FATTN, k_fattn_vec<1><<<grid, FA_WARPS * 32, smem, ctx->stream>>>(p)); break;
+        case 2: B200_LAUNCH(ctx, B200_K_FATTN, k_fattn_vec<2><<<grid, FA_WARPS * 32, smem, ctx->stream>>>(p)); break;
+        case 4: B200_LAUNCH(ctx, B200_K_FATTN, k_fattn_vec<4><<<grid, FA_WARPS * 32, smem, ctx->stream>>>(p)); break;
         default: b200_set_error("fattn: DV=%d unsupported", p.DV); return B200_ERR_UNSUPPORTED;
     }
-    B200_LAUNCH_CHECK(ctx);
     return B200_OK;
 }

@@ -259,16 +259,15 @@ static int launch_gemv_type(b200_ctx * ctx, gemv_args p, int ncols) {
         const int nc = ncols - c0 < 8 ? ncols - c0 : 8;
         p.col_base = c0;
         switch (nc) {
-            case 1: k_gemv<TYPE, 1, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p); break;
-            case 2: k_gemv<TYPE, 2, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p); break;
-            case 3: k_gemv<TYPE, 3, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p); break;
-            case 4: k_gemv<TYPE, 4, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p); break;
-            case 5: k_gemv<TYPE, 5, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p); break;
-            case 6: k_gemv<TYPE, 6, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p); break;
-            case 7: k_gemv<TYPE, 7, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p); break;
-            default: k_gemv<TYPE, 8, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p); break;
+            case 1: B200_LAUNCH(ctx, B200_K_GEMV, k_gemv<TYPE, 1, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p)); break;
+            case 2: B200_LAUNCH(ctx, B200_K_GEMV, k_gemv<TYPE, 2, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p)); break;
+            case 3: B200_LAUNCH(ctx, B200_K_GEMV, k_gemv<TYPE, 3, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p)); break;
+            case 4: B200_LAUNCH(ctx, B200_K_GEMV, k_gemv<TYPE, 4, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p)); break;
+            case 5: B200_LAUNCH(ctx, B200_K_GEMV, k_gemv<TYPE, 5, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p)); break;
+            case 6: B200_LAUNCH(ctx, B200_K_GEMV, k_gemv<TYPE, 6, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p)); break;
+            case 7: B200_LAUNCH(ctx, B200_K_GEMV, k_gemv<TYPE, 7, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p)); break;
+            default: B200_LAUNCH(ctx, B200_K_GEMV, k_gemv<TYPE, 8, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p)); break;
         }
-        B200_LAUNCH_CHECK(ctx);
     }
     return B200_OK;
 }
@@ -343,13 +342,12 @@ int b200_launch_gemv_id_q(b200_ctx * ctx, const b200_tensor * as, const void * i
     if (npairs > 65535) { b200_set_error("gemv_id: %lld (token, expert) pairs exceed grid.y", (long long) npairs); return B200_ERR_UNSUPPORTED; }
     dim3 grid((unsigned) ((p.M + WARPS - 1) / WARPS), (unsigned) npairs);
     switch (as->type) {
-        case B200_TYPE_Q4_K: k_gemv_id<B200_TYPE_Q4_K, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p); break;
-        case B200_TYPE_Q5_K: k_gemv_id<B200_TYPE_Q5_K, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p); break;
-        case B200_TYPE_Q6_K: k_gemv_id<B200_TYPE_Q6_K, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p); break;
-        case B200_TYPE_Q4_0: k_gemv_id<B200_TYPE_Q4_0, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p); break;
-        case B200_TYPE_Q8_0: k_gemv_id<B200_TYPE_Q8_0, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p); break;
+        case B200_TYPE_Q4_K: B200_LAUNCH(ctx, B200_K_GEMV_ID, k_gemv_id<B200_TYPE_Q4_K, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p)); break;
+        case B200_TYPE_Q5_K: B200_LAUNCH(ctx, B200_K_GEMV_ID, k_gemv_id<B200_TYPE_Q5_K, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p)); break;
+        case B200_TYPE_Q6_K: B200_LAUNCH(ctx, B200_K_GEMV_ID, k_gemv_id<B200_TYPE_Q6_K, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p)); break;
+        case B200_TYPE_Q4_0: B200_LAUNCH(ctx, B200_K_GEMV_ID, k_gemv_id<B200_TYPE_Q4_0, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p)); break;
+        case B200_TYPE_Q8_0: B200_LAUNCH(ctx, B200_K_GEMV_ID, k_gemv_id<B200_TYPE_Q8_0, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p)); break;
         default: b200_set_error("gemv_id: weight type %d unsupported", as->type); return B200_ERR_UNSUPPORTED;
     }
-    B200_LAUNCH_CHECK(ctx);
     return B200_OK;
 }

@@ -47,16 +47,15 @@ static int launch_mmf(b200_ctx * ctx, mmf_args p) {
         const int nc = (int) (p.ne11 - c0 < 8 ? p.ne11 - c0 : 8);
         p.col_base = c0;
         switch (nc) {
-            case 1: k_matmul_float<T, 1><<<grid, 128, 0, ctx->stream>>>(p); break;
-            case 2: k_matmul_float<T, 2><<<grid, 128, 0, ctx->stream>>>(p); break;
-            case 3: k_matmul_float<T, 3><<<grid, 128, 0, ctx->stream>>>(p); break;
-            case 4: k_matmul_float<T, 4><<<grid, 128, 0, ctx->stream>>>(p); break;
-            case 5: k_matmul_float<T, 5><<<grid, 128, 0, ctx->stream>>>(p); break;
-            case 6: k_matmul_float<T, 6><<<grid, 128, 0, ctx->stream>>>(p); break;
-            case 7: k_matmul_float<T, 7><<<grid, 128, 0, ctx->stream>>>(p); break;
-            default: k_matmul_float<T, 8><<<grid, 128, 0, ctx->stream>>>(p); break;
+            case 1: B200_LAUNCH(ctx, B200_K_MATMUL_FLOAT, k_matmul_float<T, 1><<<grid, 128, 0, ctx->stream>>>(p)); break;
+            case 2: B200_LAUNCH(ctx, B200_K_MATMUL_FLOAT, k_matmul_float<T, 2><<<grid, 128, 0, ctx->stream>>>(p)); break;
+            case 3: B200_LAUNCH(ctx, B200_K_MATMUL_FLOAT, k_matmul_float<T, 3><<<grid, 128, 0, ctx->stream>>>(p)); break;
+            case 4: B200_LAUNCH(ctx, B200_K_MATMUL_FLOAT, k_matmul_float<T, 4><<<grid, 128, 0, ctx->stream>>>(p)); break;
+            case 5: B200_LAUNCH(ctx, B200_K_MATMUL_FLOAT, k_matmul_float<T, 5><<<grid, 128, 0, ctx->stream>>>(p)); break;
+            case 6: B200_LAUNCH(ctx, B200_K_MATMUL_FLOAT, k_matmul_float<T, 6><<<grid, 128, 0, ctx->stream>>>(p)); break;
+            case 7: B200_LAUNCH(ctx, B200_K_MATMUL_FLOAT, k_matmul_float<T, 7><<<grid, 128, 0, ctx->stream>>>(p)); break;
+            default: B200_LAUNCH(ctx, B200_K_MATMUL_FLOAT, k_matmul_float<T, 8><<<grid, 128, 0, ctx->stream>>>(p)); break;
         }
-        B200_LAUNCH_CHECK(ctx);
     }
     return B200_OK;
 }

@@ -1,0 +1,319 @@
+"""ggml_b200.py -- Python host side of the B200 backend: ctypes over the C-ABI in include/ggml-b200.h.
+
+This mirrors the reference's operator interface for the hot path (ggml_mul_mat / ggml_mul_mat_id /
+ggml_flash_attn_ext, ggml/include/ggml.h:1403-1420,2314-2344; quantize_row_q8_1): same argument meaning,
+ggml shapes (ne[0] fastest) and byte strides.  It is used by the parity tests, smoke() and bench.py; llama.cpp
+itself reaches the same library through the ggml plugin entry points.
+
+There is NO fallback of any kind: if libggml-b200.so is missing, or no sm_100 device is present, every entry
+point raises.  Nothing here imports oracle/.
+"""
+import ctypes as C
+import os
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libggml-b200.so")
+
+F32, F16, Q4_0, Q8_0, Q8_1, Q4_K, Q5_K, Q6_K, I32, BF16 = 0, 1, 2, 8, 9, 12, 13, 14, 26, 30
+BLCK = {F32: 1, F16: 1, BF16: 1, I32: 1, Q4_0: 32, Q8_0: 32, Q8_1: 32, Q4_K: 256, Q5_K: 256, Q6_K: 256}
+TSIZE = {F32: 4, F16: 2, BF16: 2, I32: 4, Q4_0: 18, Q8_0: 34, Q8_1: 36, Q4_K: 144, Q5_K: 176, Q6_K: 210}
+Q8_1_X86, Q8_1_REF = 0, 1
+
+
+class B200Error(RuntimeError):
+    pass
+
+
+class _Tensor(C.Structure):          # struct b200_tensor
+    _fields_ = [("data", C.c_void_p), ("type", C.c_int32), ("flags", C.c_int32),
+                ("ne", C.c_int64 * 4), ("nb", C.c_size_t * 4)]
+
+
+_lib = None
+
+
+def lib():
+    """dlopen libggml-b200.so (once) and declare the C-ABI.  Raises if the extension is not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise B200Error(f"{LIB_PATH} is missing: build it with `make -C super-llama.cpp_b200` "
+                        "(or __graft_entry__.build()); there is no CPU fallback")
+    L = C.CDLL(LIB_PATH)
+    vp, i, i64, sz, f = C.c_void_p, C.c_int, C.c_int64, C.c_size_t, C.c_float
+    tp = C.POINTER(_Tensor)
+    sig = {
+        "b200_device_count": (i, []), "b200_last_error": (C.c_char_p, []),
+        "b200_ctx_create": (vp, [i]), "b200_ctx_destroy": (None, [vp]), "b200_ctx_device": (i, [vp]),
+        "b200_ctx_stream": (vp, [vp]), "b200_ctx_synchronize": (i, [vp]), "b200_ctx_launch_count": (C.c_uint64, [vp]),
+        "b200_malloc": (vp, [vp, sz]), "b200_free": (i, [vp, vp]), "b200_host_alloc": (vp, [sz]), "b200_host_free": (i, [vp]),
+        "b200_memcpy_h2d": (i, [vp, vp, vp, sz]), "b200_memcpy_d2h": (i, [vp, vp, vp, sz]), "b200_memset": (i, [vp, vp, i, sz]),
+        "b200_quantize_q8_1": (i, [vp, vp, sz, vp, i64, i64, i]),
+        "b200_mul_mat": (i, [vp, tp, tp, tp]), "b200_mul_mat_id": (i, [vp, tp, tp, tp, tp]),
+        "b200_flash_attn_ext": (i, [vp, tp, tp, tp, tp, tp, tp, f, f, f]),
+        "b200_ctx_launch_count_kind": (C.c_uint64, [vp, i]), "b200_ctx_profile": (i, [vp, i]),
+        "b200_ctx_profile_get": (i, [vp, i, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]),
+        "b200_event_create": (vp, []), "b200_event_destroy": (i, [vp]), "b200_event_record": (i, [vp, vp]),
+        "b200_event_elapsed_ms": (i, [vp, vp, C.POINTER(f)]),
+        "b200_graph_begin": (i, [vp]), "b200_graph_end": (vp, [vp]), "b200_graph_launch": (i, [vp, vp]), "b200_graph_destroy": (i, [vp]),
+        "b200_split_row_range": (i, [i64, vp, i, i, i64, C.POINTER(i64), C.POINTER(i64)]),
+        "ggml_backend_init": (vp, []), "ggml_backend_score": (i, []), "ggml_backend_b200_reg": (vp, []),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(L, name)
+        fn.restype, fn.argtypes = res, args
+    _lib = L
+    return L
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise B200Error(f"{what} failed ({rc}): {lib().b200_last_error().decode()}")
+
+
+def row_size(t, ne0):
+    return (ne0 // BLCK[t]) * TSIZE[t]
+
+
+def contiguous_strides(t, ne):
+    nb = [TSIZE[t], row_size(t, ne[0]), 0, 0]
+    nb[2] = nb[1] * ne[1]
+    nb[3] = nb[2] * ne[2]
+    return nb
+
+
+class DeviceTensor:
+    """A ggml-style strided view over device memory (struct b200_tensor)."""
+
+    def __init__(self, ctx, t, ne, nb=None, ptr=None, owner=None):
+        ne = list(ne) + [1] * (4 - len(ne))
+        self.ctx, self.type, self.ne = ctx, t, ne
+        self.nb = list(nb) if nb is not None else contiguous_strides(t, ne)
+        self.owner = owner
+        if ptr is None:
+            self.nbytes = self.span()
+            self.ptr = ctx.malloc(self.nbytes)
+            self.owner = self
+            self._owned = True
+        else:
+            self.ptr, self._owned, self.nbytes = ptr, False, self.span()
+
+    def span(self):
+        """bytes from data to the end of the last element (ggml_nbytes)."""
+        if any(n <= 0 for n in self.ne):
+            return 0
+        n = self.ne[0] * self.nb[0] // BLCK[self.type] if BLCK[self.type] > 1 else TSIZE[self.type] + (self.ne[0] - 1) * self.nb[0]
+        for d in range(1, 4):
+            n += (self.ne[d] - 1) * self.nb[d]
+        return n
+
+    def c(self):
+        t = _Tensor()
+        t.data, t.type, t.flags = self.ptr, self.type, 0
+        for d in range(4):
+            t.ne[d], t.nb[d] = self.ne[d], self.nb[d]
+        return t
+
+    def view(self, ne, nb, offset=0):
+        return DeviceTensor(self.ctx, self.type, ne, nb, ptr=self.ptr + offset, owner=self.owner or self)
+
+    def free(self):
+        if self._owned and self.ptr:
+            self.ctx.free(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class Context:
+    """One device + one stream (struct b200_ctx).  All operator calls are asynchronous on that stream."""
+
+    def __init__(self, device=0):
+        L = lib()
+        n = L.b200_device_count()
+        if n <= 0:
+            raise B200Error("no sm_100 (B200) device visible: the B200 backend has no CPU fallback")
+        self.h = L.b200_ctx_create(device)
+        if not self.h:
+            raise B200Error(L.b200_last_error().decode())
+        self.device = device
+
+    def close(self):
+        if self.h:
+            lib().b200_ctx_destroy(self.h)
+            self.h = None
+
+    # ---- memory ---------------------------------------------------------------------------------
+    def malloc(self, nbytes):
+        p = lib().b200_malloc(self.h, max(int(nbytes), 1))
+        if not p:
+            raise B200Error(lib().b200_last_error().decode())
+        return p
+
+    def free(self, p):
+        if self.h:
+            lib().b200_free(self.h, p)
+
+    def synchronize(self):
+        _check(lib().b200_ctx_synchronize(self.h), "synchronize")
+
+    @property
+    def stream(self):
+        return lib().b200_ctx_stream(self.h)
+
+    @property
+    def launches(self):
+        return int(lib().b200_ctx_launch_count(self.h))
+
+    # ---- measurement: events on the ctx stream, per-kernel event profile, CUDA graphs --------------
+    KINDS = ("quantize_q8_1", "gemv", "gemv_id", "gemm", "fattn", "fattn_combine", "matmul_float", "glue", "mmid_sort", "convert")
+
+    def event(self):
+        e = lib().b200_event_create()
+        if not e:
+            raise B200Error("event create failed")
+        return e
+
+    def record(self, ev):
+        _check(lib().b200_event_record(self.h, ev), "event_record")
+
+    @staticmethod
+    def elapsed_ms(e0, e1):
+        ms = C.c_float()
+        _check(lib().b200_event_elapsed_ms(e0, e1, C.byref(ms)), "event_elapsed")
+        return ms.value
+
+    def profile(self, enable):
+        _check(lib().b200_ctx_profile(self.h, 1 if enable else 0), "profile")
+
+    def profile_get(self):
+        """{kind: (total_ms, launches)} for the launches since profile(True)"""
+        out = {}
+        for k, name in enumerate(self.KINDS):
+            ms, n = C.c_double(), C.c_uint64()
+            _check(lib().b200_ctx_profile_get(self.h, k, C.byref(ms), C.byref(n)), "profile_get")
+            if n.value:
+                out[name] = (ms.value, n.value)
+        return out
+
+    def launches_by_kind(self):
+        return {name: int(lib().b200_ctx_launch_count_kind(self.h, k)) for k, name in enumerate(self.KINDS)}
+
+    def graph_begin(self):
+        _check(lib().b200_graph_begin(self.h), "graph_begin")
+
+    def graph_end(self):
+        g = lib().b200_graph_end(self.h)
+        if not g:
+            raise B200Error(lib().b200_last_error().decode())
+        return g
+
+    def graph_launch(self, g):
+        _check(lib().b200_graph_launch(self.h, g), "graph_launch")
+
+    def h2d(self, dptr, arr, nbytes=None):
+        arr = np.ascontiguousarray(arr)
+        _check(lib().b200_memcpy_h2d(self.h, dptr, arr.ctypes.data, arr.nbytes if nbytes is None else nbytes), "h2d")
+
+    def d2h(self, arr, dptr, nbytes=None):
+        assert arr.flags["C_CONTIGUOUS"]
+        _check(lib().b200_memcpy_d2h(self.h, arr.ctypes.data, dptr, arr.nbytes if nbytes is None else nbytes), "d2h")
+
+    def memset(self, dptr, value, nbytes):
+        _check(lib().b200_memset(self.h, dptr, value, nbytes), "memset")
+
+    def upload(self, t, ne, host, nb=None):
+        """contiguous host bytes -> new device tensor of ggml type t and shape ne."""
+        host = np.ascontiguousarray(host)
+        dt = DeviceTensor(self, t, ne, nb)
+        assert host.nbytes <= dt.nbytes, (host.nbytes, dt.nbytes)
+        self.h2d(dt.ptr, host)
+        self.synchronize()
+        return dt
+
+    def empty(self, t, ne, nb=None):
+        return DeviceTensor(self, t, ne, nb)
+
+    def download(self, dt, dtype=np.float32):
+        out = np.empty(dt.nbytes // np.dtype(dtype).itemsize, dtype=dtype)
+        self.d2h(out, dt.ptr, dt.nbytes)
+        self.synchronize()
+        return out
+
+    # ---- operators (device tensors, asynchronous) ---------------------------------------------------
+    def quantize_q8_1(self, x, y_ptr, k, nrows, row_stride=None, variant=Q8_1_X86):
+        _check(lib().b200_quantize_q8_1(self.h, x, k * 4 if row_stride is None else row_stride, y_ptr, k, nrows, variant), "quantize_q8_1")
+
+    def mul_mat(self, w, x, dst):
+        cw, cx, cd = w.c(), x.c(), dst.c()
+        _check(lib().b200_mul_mat(self.h, C.byref(cw), C.byref(cx), C.byref(cd)), "mul_mat")
+
+    def mul_mat_id(self, as_, b, ids, dst):
+        ca, cb, ci, cd = as_.c(), b.c(), ids.c(), dst.c()
+        _check(lib().b200_mul_mat_id(self.h, C.byref(ca), C.byref(cb), C.byref(ci), C.byref(cd)), "mul_mat_id")
+
+    def flash_attn_ext(self, q, k, v, mask, sinks, dst, scale, max_bias=0.0, logit_softcap=0.0):
+        cq, ck, cv, cd = q.c(), k.c(), v.c(), dst.c()
+        cm = mask.c() if mask is not None else None
+        cs = sinks.c() if sinks is not None else None
+        _check(lib().b200_flash_attn_ext(self.h, C.byref(cq), C.byref(ck), C.byref(cv),
+                                         C.byref(cm) if cm is not None else None, C.byref(cs) if cs is not None else None,
+                                         C.byref(cd), scale, max_bias, logit_softcap), "flash_attn_ext")
+
+    # ---- host-buffer convenience calls: what a user with numpy arrays calls (H2D + op + D2H) ----------
+    def quantize_q8_1_host(self, x, variant=Q8_1_X86):
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        k = x.shape[-1]
+        nrows = x.size // k
+        dx = self.upload(F32, [k, nrows], x)
+        dy = self.empty(Q8_1, [k, nrows])
+        self.quantize_q8_1(dx.ptr, dy.ptr, k, nrows, variant=variant)
+        return self.download(dy, np.uint8)
+
+    def mul_mat_host(self, t, w, K, M, x, N, ne02=1, ne03=1, ne12=1, ne13=1):
+        dw = self.upload(t, [K, M, ne02, ne03], w)
+        dx = self.upload(F32, [K, N, ne12, ne13], np.ascontiguousarray(x, dtype=np.float32))
+        dd = self.empty(F32, [M, N, ne12, ne13])
+        self.mul_mat(dw, dx, dd)
+        return self.download(dd).reshape(ne13, ne12, N, M)
+
+    def mul_mat_id_host(self, t, as_, K, M, n_expert, b, ne11, n_tokens, ids, n_used):
+        da = self.upload(t, [K, M, n_expert], as_)
+        db = self.upload(F32, [K, ne11, n_tokens], np.ascontiguousarray(b, dtype=np.float32))
+        di = self.upload(I32, [n_used, n_tokens], np.ascontiguousarray(ids, dtype=np.int32))
+        dd = self.empty(F32, [M, n_used, n_tokens])
+        self.mul_mat_id(da, db, di, dd)
+        return self.download(dd).reshape(n_tokens, n_used, M)
+
+    def flash_attn_ext_host(self, q, k, v, mask=None, sinks=None, scale=1.0, max_bias=0.0, softcap=0.0):
+        """q[S,H,N,DK] f32, k[Sk,Hk,KV,DK] f16, v[Sk,Hk,KV,DV] f16, mask[Sm,Hm,Nm,KV] f16 -> dst[S,N,H,DV]."""
+        q = np.ascontiguousarray(q, dtype=np.float32)
+        k = np.ascontiguousarray(k, dtype=np.float16); v = np.ascontiguousarray(v, dtype=np.float16)
+        S, H, N, DK = q.shape; Sk, Hk, KV, _ = k.shape; DV = v.shape[-1]
+        dq = self.upload(F32, [DK, N, H, S], q)
+        dk = self.upload(F16, [DK, KV, Hk, Sk], k)
+        dv = self.upload(F16, [DV, KV, Hk, Sk], v)
+        dm = ds = None
+        if mask is not None:
+            mask = np.ascontiguousarray(mask, dtype=np.float16); Sm, Hm, Nm, _ = mask.shape
+            dm = self.upload(F16, [KV, Nm, Hm, Sm], mask)
+        if sinks is not None:
+            ds = self.upload(F32, [H], np.ascontiguousarray(sinks, dtype=np.float32))
+        dd = self.empty(F32, [DV, H, N, S])
+        self.flash_attn_ext(dq, dk, dv, dm, ds, dd, scale, max_bias, softcap)
+        return self.download(dd).reshape(S, N, H, DV)
+
+
+def split_row_range(nrows, world, rank, rounding, tensor_split=None):
+    """rows [lo, hi) of an nrows-row weight owned by `rank` (split-mode=row; ggml-cuda.cu:777-803)."""
+    lo, hi = C.c_int64(), C.c_int64()
+    ts = None if tensor_split is None else np.ascontiguousarray(tensor_split, dtype=np.float32)
+    _check(lib().b200_split_row_range(nrows, ts.ctypes.data if ts is not None else None, world, rank, rounding,
+                                      C.byref(lo), C.byref(hi)), "split_row_range")
+    return lo.value, hi.value

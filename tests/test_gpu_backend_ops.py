@@ -1,0 +1,72 @@
+"""GPU test (-m gpu): the reference's OWN parity harness, tests/test-backend-ops.cpp, compiled unmodified from
+/root/reference into oracle/_ref/avx2/test-backend-ops (oracle/Makefile), loading our backend as a plugin through
+GGML_BACKEND_PATH (ggml/src/ggml-backend-reg.cpp:611-615) and comparing every supported case with ggml-cpu at
+NMSE < 5e-4.  This is the drop-in proof: no line of the harness or of ggml knows about ggml-b200.
+"""
+import os
+import re
+import subprocess
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HARNESS = os.path.join(ROOT, "oracle", "_ref", "avx2", "test-backend-ops")
+PLUGIN = os.path.join(ROOT, "super-llama.cpp_b200", "libggml-b200.so")
+OUT = os.path.join(ROOT, "gpurun_out")
+
+
+def run_harness(op, pattern=None, mode="test", timeout=1500):
+    if not os.path.exists(HARNESS):
+        pytest.skip("oracle/_ref/avx2/test-backend-ops not built (needs /root/reference at build time)")
+    env = dict(os.environ, GGML_BACKEND_PATH=PLUGIN)
+    cmd = [HARNESS, mode, "-b", "B200_0", "-o", op]
+    if pattern:
+        cmd += ["-p", pattern]
+    p = subprocess.run(cmd, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=timeout)
+    txt = re.sub(r"\x1b\[[0-9;]*m", "", p.stdout)
+    os.makedirs(OUT, exist_ok=True)
+    with open(os.path.join(OUT, f"test-backend-ops_{mode}_{op}.log"), "w") as f:
+        f.write(txt)
+    return p.returncode, txt
+
+
+def summarize(txt, must_support):
+    ok = len(re.findall(r": OK$", txt, re.M))
+    fail = [l for l in txt.splitlines() if re.search(r"FAIL|ERR = |NaN|inf mismatch", l)]
+    unsupported = [l for l in txt.splitlines() if "not supported" in l]
+    m = re.search(r"(\d+)/(\d+) tests passed", txt)
+    assert m, txt[-2000:]
+    passed, total = int(m.group(1)), int(m.group(2))
+    # a north-star case reported "not supported" is a coverage hole, not a pass
+    holes = [l for l in unsupported if must_support(l)]
+    return ok, passed, total, fail, holes
+
+
+NORTH_STAR_W = ("type_a=q4_0", "type_a=q8_0", "type_a=q4_K")
+
+
+def test_backend_ops_mul_mat():
+    rc, txt = run_harness("MUL_MAT")
+    must = lambda l: any(t in l for t in NORTH_STAR_W) and "type_b=f32" in l and "per=[0,1,2,3]" in l
+    ok, passed, total, fail, holes = summarize(txt, must)
+    assert rc == 0 and passed == total and not fail, "\n".join(fail[:20])
+    assert not holes, "north-star MUL_MAT cases declined by supports_op:\n" + "\n".join(holes[:20])
+    assert ok >= 100, f"only {ok} MUL_MAT cases actually ran on the device"
+
+
+def test_backend_ops_mul_mat_id():
+    rc, txt = run_harness("MUL_MAT_ID")
+    must = lambda l: any(t in l for t in NORTH_STAR_W) and "type_b=f32" in l
+    ok, passed, total, fail, holes = summarize(txt, must)
+    assert rc == 0 and passed == total and not fail, "\n".join(fail[:20])
+    assert not holes, "north-star MUL_MAT_ID cases declined:\n" + "\n".join(holes[:20])
+    assert ok >= 100, f"only {ok} MUL_MAT_ID cases ran on the device"
+
+
+def test_backend_ops_flash_attn_ext():
+    rc, txt = run_harness("FLASH_ATTN_EXT", timeout=3000)
+    must = lambda l: "type_KV=f16" in l and re.search(r"hsk=(64|128),", l) and re.search(r"hsv=(64|128),", l)
+    ok, passed, total, fail, holes = summarize(txt, must)
+    assert rc == 0 and passed == total and not fail, "\n".join(fail[:20])
+    assert not holes, "north-star FLASH_ATTN_EXT cases declined:\n" + "\n".join(holes[:20])
+    assert ok >= 300, f"only {ok} FLASH_ATTN_EXT cases ran on the device"

@@ -1,0 +1,221 @@
+"""GPU parity tests (-m gpu): the CUDA hot path, called through the C-ABI (include/ggml-b200.h via ctypes),
+against the CPU oracle on the same seeded inputs, and against the reference's committed golden vectors.
+
+Bars (BASELINE.json north_star):
+  * q8_1 activation quantization: BIT-EXACT with the reference's quantize_row_q8_1 (both rounding variants);
+  * MUL_MAT / MUL_MAT_ID / FLASH_ATTN_EXT fp32 outputs: NMSE < 5e-4 against the ggml-cpu result
+    (tests/test-backend-ops.cpp:3716-3718,3852-3854,6080-6082).  Because NMSE 5e-4 would hide an indexing bug that
+    hits a few elements, each case is ALSO compared with the oracle run in the kernel's own numerics
+    (q8_1 integer dots / fp32 attention) at NMSE < 1e-9 / 1e-6.
+"""
+import os
+import numpy as np
+import pytest
+
+import oracle as O
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+NMSE_HARNESS = 5e-4
+QTYPES = [O.Q4_0, O.Q8_0, O.Q4_K, O.Q5_K, O.Q6_K]
+
+
+@pytest.fixture(scope="module")
+def B():
+    import ggml_b200
+    return ggml_b200
+
+
+@pytest.fixture(scope="module")
+def ctx(B):
+    c = B.Context(0)          # raises without a B200: no fallback
+    yield c
+    c.close()
+
+
+@pytest.fixture(scope="module")
+def orc():
+    return O.Oracle()
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return np.load(os.path.join(ROOT, "tests", "golden", "hotpath_golden.npz"))
+
+
+# ---- q8_1 ------------------------------------------------------------------------------------------
+def test_q8_1_bit_exact_golden(ctx, gold):
+    x = gold["q8_1_x"]
+    assert np.array_equal(ctx.quantize_q8_1_host(x, 0), gold["q8_1_x86"])
+    assert np.array_equal(ctx.quantize_q8_1_host(x, 1), gold["q8_1_ref"])
+
+
+@pytest.mark.parametrize("variant", [0, 1])
+def test_q8_1_bit_exact_1e6_blocks(ctx, orc, variant):
+    rng = np.random.default_rng(100 + variant)
+    rows, k = 2048, 16384                                         # 1,048,576 blocks
+    x = (rng.standard_normal((rows, k), dtype=np.float32) * (10.0 ** rng.integers(-5, 5, (rows, 1))).astype(np.float32))
+    x[::5, :64] = np.round(x[::5, :64] * 2) / 2                   # exact .5 ties
+    x[1, :32] = 0.0
+    x[2, :32] = 1e-40                                             # denormal amax -> id = inf on x86
+    x[3, :32] = 3.0e38
+    x[4, :k] = np.float32(-1.0)
+    got = ctx.quantize_q8_1_host(x, variant)
+    want = orc.quantize_q8_1(x, variant)
+    bad = np.nonzero((got.reshape(-1, 36) != want.reshape(-1, 36)).any(1))[0]
+    assert bad.size == 0, f"{bad.size} blocks differ, first {bad[:5]}"
+
+
+def test_q8_1_strided_rows_and_empty(ctx, B, orc):
+    rng = np.random.default_rng(7)
+    x = rng.uniform(-1, 1, (6, 512)).astype(np.float32)
+    dx = ctx.upload(B.F32, [512, 6], x)
+    dy = ctx.empty(B.Q8_1, [256, 3])
+    ctx.quantize_q8_1(dx.ptr + 256 * 4, dy.ptr, 256, 3, row_stride=2 * 512 * 4)      # second half of rows 0, 2, 4
+    got = ctx.download(dy, np.uint8)
+    assert np.array_equal(got, orc.quantize_q8_1(np.ascontiguousarray(x[::2, 256:]), 0))
+    ctx.quantize_q8_1(dx.ptr, dy.ptr, 256, 0)                                          # zero rows: no-op
+    with pytest.raises(B.B200Error):
+        ctx.quantize_q8_1(dx.ptr, dy.ptr, 100, 1)                                      # k % 32 != 0
+
+
+# ---- MUL_MAT ------------------------------------------------------------------------------------------
+def _check_mm(orc, got, t, w, K, M, x, N, want_cpu=None, **bc):
+    exact = orc.mul_mat(t, w, K, M, x, N, act=O.ACT_Q8_1, **bc)
+    cpu = want_cpu if want_cpu is not None else orc.mul_mat(t, w, K, M, x, N, act=O.ACT_CPU, **bc)
+    assert np.isfinite(got).all()
+    e1, e2 = O.nmse(exact, got), O.nmse(cpu, got)
+    assert e2 < NMSE_HARNESS, f"vs ggml-cpu numerics: nmse {e2:.3e}"
+    return e1
+
+
+@pytest.mark.parametrize("t", QTYPES)
+def test_mul_mat_golden(ctx, orc, gold, t):
+    name = O.TYPE_NAMES[t]
+    x = gold["mm_x"]; N, K = x.shape
+    want = gold[f"mm_{name}"]; M = want.shape[-1]
+    got = ctx.mul_mat_host(t, gold[f"w_{name}"], K, M, x, N)
+    e = _check_mm(orc, got, t, gold[f"w_{name}"], K, M, x, N, want_cpu=want)
+    assert e < 1e-9, f"vs q8_1-path oracle: nmse {e:.3e}"
+
+
+@pytest.mark.parametrize("t", QTYPES)
+@pytest.mark.parametrize("n", [1, 2, 3, 4, 5, 6, 7, 8, 9, 16])
+def test_mul_mat_small_n(ctx, orc, t, n):
+    """m=16, n=1..9, k=256 of test-backend-ops (tests/test-backend-ops.cpp:7616-7620), random bit patterns."""
+    rng = np.random.default_rng(1000 * t + n)
+    K, M = 256, 16
+    w = O.random_blocks(rng, t, K, M)
+    x = rng.uniform(-1, 1, (n, K)).astype(np.float32)
+    got = ctx.mul_mat_host(t, w, K, M, x, n)
+    assert _check_mm(orc, got, t, w, K, M, x, n) < 1e-9
+
+
+@pytest.mark.parametrize("t", [O.Q4_0, O.Q4_K, O.Q8_0])
+@pytest.mark.parametrize("bs,nr", [((3, 2), (1, 1)), ((1, 1), (2, 2)), ((3, 1), (2, 1)), ((2, 2), (1, 2))])
+def test_mul_mat_batch_broadcast(ctx, orc, t, bs, nr):
+    rng = np.random.default_rng(17)
+    K, M, N = 256, 16, 3
+    ne02, ne03 = bs; ne12, ne13 = bs[0] * nr[0], bs[1] * nr[1]
+    w = O.random_blocks(rng, t, K, M * ne02 * ne03)
+    x = rng.uniform(-1, 1, (ne13, ne12, N, K)).astype(np.float32)
+    got = ctx.mul_mat_host(t, w, K, M, x, N, ne02, ne03, ne12, ne13)
+    assert _check_mm(orc, got, t, w, K, M, x, N, ne02=ne02, ne03=ne03, ne12=ne12, ne13=ne13) < 1e-9
+
+
+@pytest.mark.parametrize("t", [O.Q4_K, O.Q8_0])
+def test_mul_mat_permuted_activations(ctx, B, orc, t):
+    """src1 permuted (0,2,1,3) as test-backend-ops does (:7636-7684): rows contiguous, dims 1 and 2 swapped in memory."""
+    rng = np.random.default_rng(23)
+    K, M, N, ne12 = 256, 16, 4, 3
+    w = O.random_blocks(rng, t, K, M)
+    xmem = rng.uniform(-1, 1, (N, ne12, K)).astype(np.float32)               # memory order [n][i12][k]
+    dx = ctx.upload(B.F32, [K, ne12, N], xmem)
+    xv = dx.view([K, N, ne12, 1], [4, K * 4 * ne12, K * 4, K * 4 * ne12 * N])  # logical [K, N, ne12]
+    dw = ctx.upload(t, [K, M], w)
+    dd = ctx.empty(B.F32, [M, N, ne12])
+    ctx.mul_mat(dw, xv, dd)
+    got = ctx.download(dd).reshape(1, ne12, N, M)
+    xlog = np.ascontiguousarray(xmem.transpose(1, 0, 2))                      # [i12][n][k]
+    assert _check_mm(orc, got, t, w, K, M, xlog, N, ne12=ne12) < 1e-9
+
+
+@pytest.mark.parametrize("t", QTYPES)
+def test_mul_mat_decode_llama8b_ffn_down(ctx, orc, t):
+    """the BASELINE.json decode shape: m=4096, n=1, k=14336 (test-backend-ops perf case :8410-8416)"""
+    rng = np.random.default_rng(31 + t)
+    K, M = 14336, 4096
+    w = O.random_blocks(rng, t, K, M)
+    x = rng.standard_normal((1, K)).astype(np.float32)
+    got = ctx.mul_mat_host(t, w, K, M, x, 1)
+    assert _check_mm(orc, got, t, w, K, M, x, 1) < 1e-9
+
+
+@pytest.mark.parametrize("t", [O.Q4_0, O.Q4_K, O.Q8_0, O.Q6_K])
+@pytest.mark.parametrize("n", [17, 64, 512])
+def test_mul_mat_prefill(ctx, orc, t, n):
+    rng = np.random.default_rng(41 + t + n)
+    K, M = 2048, 384
+    w = O.random_blocks(rng, t, K, M)
+    x = rng.uniform(-1, 1, (n, K)).astype(np.float32)
+    got = ctx.mul_mat_host(t, w, K, M, x, n)
+    cpu = orc.mul_mat(t, w, K, M, x, n, act=O.ACT_CPU)
+    f64 = orc.mul_mat(t, w, K, M, x, n, act=O.ACT_F64)
+    assert O.nmse(cpu, got) < NMSE_HARNESS
+    assert O.nmse(f64, got) < 1e-4        # whichever activation format the prefill kernel uses, it is at least q8-accurate
+
+
+def test_mul_mat_float_weights(ctx, orc):
+    rng = np.random.default_rng(5)
+    K, M, N = 320, 24, 5
+    x = rng.uniform(-1, 1, (N, K)).astype(np.float32)
+    for t in (O.F32, O.F16, O.BF16):
+        w = O.random_blocks(rng, t, K, M, scale=1.0)
+        got = ctx.mul_mat_host(t, w, K, M, x, N)
+        assert O.nmse(orc.mul_mat(t, w, K, M, x, N, act=O.ACT_F64), got) < 1e-10
+
+
+def test_mul_mat_rejects_bad_shapes(ctx, B):
+    dw = ctx.empty(B.Q4_K, [256, 16]); dx = ctx.empty(B.F32, [512, 1]); dd = ctx.empty(B.F32, [16, 1])
+    with pytest.raises(B.B200Error):
+        ctx.mul_mat(dw, dx, dd)
+
+
+# ---- MUL_MAT_ID ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("t", [O.Q4_0, O.Q4_K, O.Q8_0])
+@pytest.mark.parametrize("ne11", [1, 2])
+def test_mul_mat_id_golden(ctx, orc, gold, t, ne11):
+    name = O.TYPE_NAMES[t]
+    want = gold[f"id_out{ne11}_{name}"]; T, U, M = want.shape
+    b = gold[f"id_b{ne11}_{name}"]; K = b.shape[-1]
+    as_, ids = gold[f"id_as_{name}"], gold[f"id_ids_{name}"]
+    got = ctx.mul_mat_id_host(t, as_, K, M, 8, b, ne11, T, ids, U)
+    assert O.nmse(want, got) < NMSE_HARNESS
+    assert O.nmse(orc.mul_mat_id(t, as_, K, M, 8, b, ne11, T, ids, U, act=O.ACT_Q8_1), got) < 1e-9
+
+
+@pytest.mark.parametrize("t", [O.Q4_0, O.Q4_K, O.Q8_0])
+@pytest.mark.parametrize("n_mats,n_used,bcast,n", [(4, 1, False, 1), (4, 2, True, 4), (8, 4, False, 5), (8, 2, True, 17),
+                                                   (8, 4, True, 32), (8, 2, False, 129), (4, 4, False, 1)])
+def test_mul_mat_id_shapes(ctx, orc, t, n_mats, n_used, bcast, n):
+    """n_mats/n_used/broadcast/n grid of test-backend-ops (:7781-7795), m=512, k=256"""
+    rng = np.random.default_rng(n_mats * 100 + n_used * 10 + n)
+    K, M = 256, 512
+    as_ = O.random_blocks(rng, t, K, M * n_mats)
+    ids = np.stack([rng.permutation(n_mats)[:n_used] for _ in range(n)]).astype(np.int32)
+    ne11 = 1 if bcast else n_used
+    b = rng.uniform(-1, 1, (n, ne11, K)).astype(np.float32)
+    got = ctx.mul_mat_id_host(t, as_, K, M, n_mats, b, ne11, n, ids, n_used)
+    assert O.nmse(orc.mul_mat_id(t, as_, K, M, n_mats, b, ne11, n, ids, n_used, act=O.ACT_CPU), got) < NMSE_HARNESS
+    if n <= 8:
+        assert O.nmse(orc.mul_mat_id(t, as_, K, M, n_mats, b, ne11, n, ids, n_used, act=O.ACT_Q8_1), got) < 1e-9
+
+
+def test_mul_mat_id_mixtral_decode(ctx, orc):
+    rng = np.random.default_rng(77)
+    K, M, E, U = 4096, 1024, 8, 2                      # a 1024-row slice of Mixtral's [4096, 14336, 8] gate tensor
+    as_ = O.random_blocks(rng, O.Q4_K, K, M * E)
+    ids = np.int32([[5, 2]])
+    b = rng.standard_normal((1, 1, K)).astype(np.float32)
+    got = ctx.mul_mat_id_host(O.Q4_K, as_, K, M, E, b, 1, 1, ids, U)
+    assert O.nmse(orc.mul_mat_id(O.Q4_K, as_, K, M, E, b, 1, 1, ids, U, act=O.ACT_Q8_1), got) < 1e-9
