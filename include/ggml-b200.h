@@ -79,6 +79,9 @@ B200_API int          b200_ctx_device(const b200_ctx * ctx);
 B200_API void *       b200_ctx_stream(const b200_ctx * ctx);   // cudaStream_t
 B200_API int          b200_ctx_synchronize(b200_ctx * ctx);
 B200_API uint64_t     b200_ctx_launch_count(const b200_ctx * ctx);   // kernels launched so far through this ctx
+// The ctx keeps the q8_1 image of the last quantized activation tensor so that matmuls sharing src1 (wq/wk/wv, gate/up)
+// quantize it once.  Writes made through this API invalidate it; call this after writing activations by other means.
+B200_API int          b200_ctx_invalidate(b200_ctx * ctx);
 
 // ---- measurement helpers (bench.py): CUDA events on the ctx stream, per-kernel-kind event profile, CUDA graphs ----
 // kernel kinds: 0 quantize_q8_1, 1 gemv, 2 gemv_id, 3 gemm, 4 fattn, 5 fattn_combine, 6 matmul_float, 7 glue, 8 mmid_sort, 9 convert

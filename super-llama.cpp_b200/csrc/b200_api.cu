@@ -143,7 +143,7 @@ extern "C" void * b200_malloc(b200_ctx * ctx, size_t nbytes) {
     }
     return p;
 }
-extern "C" int b200_free(b200_ctx * ctx, void * dptr) { B200_CUDA_TRY(cudaSetDevice(ctx->device)); B200_CUDA_TRY(cudaFree(dptr)); return B200_OK; }
+extern "C" int b200_free(b200_ctx * ctx, void * dptr) { ctx->qcache.valid = 0; B200_CUDA_TRY(cudaSetDevice(ctx->device)); B200_CUDA_TRY(cudaFree(dptr)); return B200_OK; }
 extern "C" void * b200_host_alloc(size_t nbytes) {
     void * p = nullptr;
     if (cudaMallocHost(&p, nbytes ? nbytes : 1) != cudaSuccess) { cudaGetLastError(); b200_set_error("cudaMallocHost(%zu) failed", nbytes); return nullptr; }
@@ -151,12 +151,14 @@ extern "C" void * b200_host_alloc(size_t nbytes) {
 }
 extern "C" int b200_host_free(void * hptr) { B200_CUDA_TRY(cudaFreeHost(hptr)); return B200_OK; }
 extern "C" int b200_memcpy_h2d(b200_ctx * ctx, void * dst, const void * src, size_t n) {
+    b200_note_write(ctx, dst, n);
     B200_CUDA_TRY(cudaMemcpyAsync(dst, src, n, cudaMemcpyHostToDevice, ctx->stream)); return B200_OK;
 }
 extern "C" int b200_memcpy_d2h(b200_ctx * ctx, void * dst, const void * src, size_t n) {
     B200_CUDA_TRY(cudaMemcpyAsync(dst, src, n, cudaMemcpyDeviceToHost, ctx->stream)); return B200_OK;
 }
 extern "C" int b200_memset(b200_ctx * ctx, void * dst, int value, size_t n) {
+    b200_note_write(ctx, dst, n);
     B200_CUDA_TRY(cudaMemsetAsync(dst, value, n, ctx->stream)); return B200_OK;
 }
 
@@ -164,6 +166,37 @@ extern "C" int b200_memset(b200_ctx * ctx, void * dst, int value, size_t n) {
 extern "C" int b200_quantize_q8_1(b200_ctx * ctx, const float * x, size_t x_row_stride, void * y, int64_t k, int64_t nrows, int variant) {
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
     return b200_launch_quantize_q8_1(ctx, x, x_row_stride, y, k, nrows, variant);
+}
+
+size_t b200_tensor_span(const b200_tensor * t) {                 // ggml_nbytes
+    for (int i = 0; i < 4; ++i) if (t->ne[i] <= 0) return 0;
+    const int64_t blck = b200_blck_size(t->type);
+    size_t n = blck > 1 ? (size_t) t->ne[0] * t->nb[0] / blck : b200_type_size(t->type) + (size_t) (t->ne[0] - 1) * t->nb[0];
+    for (int i = 1; i < 4; ++i) n += (size_t) (t->ne[i] - 1) * t->nb[i];
+    return n;
+}
+void b200_note_write(b200_ctx * ctx, const void * ptr, size_t nbytes) {
+    if (!ctx->qcache.valid) return;
+    const char * a = (const char *) ctx->qcache.data, * b = (const char *) ptr;
+    if (b < a + ctx->qcache.span && a < b + nbytes) ctx->qcache.valid = 0;
+}
+extern "C" int b200_ctx_invalidate(b200_ctx * ctx) { ctx->qcache.valid = 0; return B200_OK; }
+
+// q8_1 image of x in scratch slot 0, reused when the same activation tensor feeds consecutive matmuls
+static const void * quantized_activations(b200_ctx * ctx, const b200_tensor * x, int variant, int * rc) {
+    const int64_t K = x->ne[0], ncol = x->ne[1] * x->ne[2] * x->ne[3];
+    auto & qc = ctx->qcache;
+    *rc = B200_OK;
+    if (qc.valid && qc.data == x->data && qc.variant == variant && ctx->scratch[0] &&
+        !memcmp(qc.ne, x->ne, sizeof(qc.ne)) && !memcmp(qc.nb, x->nb, sizeof(qc.nb))) return ctx->scratch[0];
+    qc.valid = 0;
+    void * image = b200_scratch(ctx, 0, b200_q8_1_soa_size(K, ncol));
+    if (!image) { *rc = B200_ERR_ALLOC; return nullptr; }
+    *rc = b200_launch_quantize_q8_1_soa(ctx, (const float *) x->data, x->nb[1], x->nb[2], x->nb[3], K, x->ne[1], x->ne[2], x->ne[3], image, variant);
+    if (*rc) return nullptr;
+    qc.data = x->data; memcpy(qc.ne, x->ne, sizeof(qc.ne)); memcpy(qc.nb, x->nb, sizeof(qc.nb));
+    qc.span = b200_tensor_span(x); qc.variant = variant; qc.valid = 1;
+    return image;
 }
 
 static bool is_quant(int t) { return t == B200_TYPE_Q4_0 || t == B200_TYPE_Q8_0 || t == B200_TYPE_Q4_K || t == B200_TYPE_Q5_K || t == B200_TYPE_Q6_K; }
@@ -190,15 +223,18 @@ extern "C" int b200_mul_mat(b200_ctx * ctx, const b200_tensor * w, const b200_te
     if (is_quant(w->type)) {
         if (K % b200_blck_size(w->type) != 0) { b200_set_error("mul_mat: K=%lld not a multiple of the block size", (long long) K); return B200_ERR_INVALID; }
         if (w->nb[0] != b200_type_size(w->type)) { b200_set_error("mul_mat: quantized weight rows must be contiguous"); return B200_ERR_UNSUPPORTED; }
-        const int64_t ncol = x->ne[1] * x->ne[2] * x->ne[3];
-        if (x->ne[1] > B200_GEMV_MAX_COLS && b200_gemm_supported(w, x)) return b200_launch_gemm_q(ctx, w, x, dst);
-        void * image = b200_scratch(ctx, 0, b200_q8_1_soa_size(K, ncol));
-        if (!image) return B200_ERR_ALLOC;
-        int rc = b200_launch_quantize_q8_1_soa(ctx, (const float *) x->data, x->nb[1], x->nb[2], x->nb[3], K, x->ne[1], x->ne[2], x->ne[3], image, q8_1_variant_env());
-        if (rc) return rc;
-        return b200_launch_gemv_q(ctx, w, image, x->ne[1], x->ne[2], x->ne[3], dst);
+        int rc;
+        if (x->ne[1] > B200_GEMV_MAX_COLS && b200_gemm_supported(w, x)) rc = b200_launch_gemm_q(ctx, w, x, dst);
+        else {
+            const void * image = quantized_activations(ctx, x, q8_1_variant_env(), &rc);
+            if (!image) return rc;
+            if (b200_gemv_stream_supported(w, x->ne[1], x->ne[2], x->ne[3])) rc = b200_launch_gemv_stream(ctx, w, image, (float *) dst->data);
+            else rc = b200_launch_gemv_q(ctx, w, image, x->ne[1], x->ne[2], x->ne[3], dst);
+        }
+        b200_note_write(ctx, dst->data, b200_tensor_span(dst));
+        return rc;
     }
-    if (is_float_w(w->type)) return b200_launch_matmul_float(ctx, w, x, dst);
+    if (is_float_w(w->type)) { const int rc = b200_launch_matmul_float(ctx, w, x, dst); b200_note_write(ctx, dst->data, b200_tensor_span(dst)); return rc; }
     b200_set_error("mul_mat: weight type %d is outside the hot path", w->type);
     return B200_ERR_UNSUPPORTED;
 }
@@ -217,12 +253,12 @@ extern "C" int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b20
     }
     if (M == 0 || n_used * n_tokens == 0) return B200_OK;
     if (n_tokens > B200_GEMV_MAX_COLS && b200_gemm_id_supported(as, b, ids)) return b200_launch_gemm_id_q(ctx, as, b, ids, dst);
-    const int64_t ncol = b->ne[1] * n_tokens;
-    void * image = b200_scratch(ctx, 0, b200_q8_1_soa_size(K, ncol));
-    if (!image) return B200_ERR_ALLOC;
-    int rc = b200_launch_quantize_q8_1_soa(ctx, (const float *) b->data, b->nb[1], b->nb[2], b->nb[3], K, b->ne[1], n_tokens, 1, image, q8_1_variant_env());
-    if (rc) return rc;
-    return b200_launch_gemv_id_q(ctx, as, image, b->ne[1], n_tokens, ids, dst);
+    int rc;
+    const void * image = quantized_activations(ctx, b, q8_1_variant_env(), &rc);
+    if (!image) return rc;
+    rc = b200_launch_gemv_id_q(ctx, as, image, b->ne[1], n_tokens, ids, dst);
+    b200_note_write(ctx, dst->data, b200_tensor_span(dst));
+    return rc;
 }
 
 extern "C" int b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v,
@@ -244,7 +280,9 @@ extern "C" int b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const 
         return B200_ERR_UNSUPPORTED;
     }
     if (mask && (mask->ne[0] < k->ne[1] || mask->ne[1] < q->ne[1])) { b200_set_error("flash_attn_ext: mask too small"); return B200_ERR_INVALID; }
-    return b200_launch_fattn_vec(ctx, q, k, v, mask, sinks, dst, scale, max_bias, logit_softcap);
+    const int rc = b200_launch_fattn_vec(ctx, q, k, v, mask, sinks, dst, scale, max_bias, logit_softcap);
+    b200_note_write(ctx, dst->data, b200_tensor_span(dst));
+    return rc;
 }
 
 // ---- row split helper: ggml-cuda.cu:777-803 semantics -----------------------------------------

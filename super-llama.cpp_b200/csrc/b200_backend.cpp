@@ -173,6 +173,7 @@ static void be_free(ggml_backend_t be) {
 }
 static void be_set_tensor_async(ggml_backend_t be, ggml_tensor * t, const void * data, size_t off, size_t n) {
     b200_backend_ctx * c = (b200_backend_ctx *) be->context; B200_CHECK(cudaSetDevice(c->device));
+    b200_note_write(c->ctx, (char *) t->data + off, n);
     B200_CHECK(cudaMemcpyAsync((char *) t->data + off, data, n, cudaMemcpyHostToDevice, c->ctx->stream));
 }
 static void be_get_tensor_async(ggml_backend_t be, const ggml_tensor * t, void * data, size_t off, size_t n) {
@@ -186,6 +187,7 @@ static bool be_cpy_tensor_async(ggml_backend_t be_src, ggml_backend_t be_dst, co
     b200_backend_ctx * cs = (b200_backend_ctx *) be_src->context, * cd = (b200_backend_ctx *) be_dst->context;
     b200_buffer_ctx * bs = (b200_buffer_ctx *) src->buffer->context, * bd = (b200_buffer_ctx *) dst->buffer->context;
     if (cs->device != bs->device || cd->device != bd->device) return false;
+    b200_note_write(cd->ctx, dst->data, tensor_nbytes(dst));
     // copy on the source stream, then make the destination stream wait for it (as ggml-cuda.cu:2700-2760)
     B200_CHECK(cudaSetDevice(cs->device));
     if (cs->device == cd->device) B200_CHECK(cudaMemcpyAsync(dst->data, src->data, tensor_nbytes(dst), cudaMemcpyDeviceToDevice, cs->ctx->stream));
@@ -224,14 +226,18 @@ static int compute_node(b200_ctx * ctx, ggml_tensor * node) {
             memcpy(&scale, node->op_params + 0, 4); memcpy(&max_bias, node->op_params + 1, 4); memcpy(&softcap, node->op_params + 2, 4);
             return b200_flash_attn_ext(ctx, &q, &k, &v, node->src[3] ? &m : nullptr, node->src[4] ? &s : nullptr, &d, scale, max_bias, softcap);
         }
-        default:
-            return b200_glue_compute(ctx, node);
+        default: {
+            const int rc = b200_glue_compute(ctx, node);
+            b200_note_write(ctx, node->data, tensor_nbytes(node));
+            return rc;
+        }
     }
 }
 
 static enum ggml_status be_graph_compute(ggml_backend_t be, ggml_cgraph * g) {
     b200_backend_ctx * c = (b200_backend_ctx *) be->context;
     if (cudaSetDevice(c->device) != cudaSuccess) return GGML_STATUS_FAILED;
+    c->ctx->qcache.valid = 0;      // tensors may have been rewritten through buffer set_tensor since the last graph
     for (int i = 0; i < g->n_nodes; ++i) {
         ggml_tensor * node = g->nodes[i];
         if (op_is_view((int) node->op) || tensor_nelements(node) == 0) continue;

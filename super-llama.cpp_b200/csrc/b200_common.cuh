@@ -66,10 +66,15 @@ struct b200_ctx {
     int            prof_open;        // index of the record whose e1 is pending, or -1
     // CUDA graph capture state (b200_graph_*)
     int          capturing;
+    // the q8_1 image of the most recently quantized activation tensor (scratch slot 0): wq/wk/wv and gate/up share theirs
+    struct { const void * data; int64_t ne[4]; size_t nb[4]; size_t span; int variant; int valid; } qcache;
+    int          attr_done[8];       // per-kernel one-time cudaFuncSetAttribute flags (a ctx is bound to one device)
 };
 
 void   b200_set_error(const char * fmt, ...);
 void * b200_scratch(b200_ctx * ctx, int slot, size_t nbytes);   // returns device ptr, NULL on failure
+void   b200_note_write(b200_ctx * ctx, const void * ptr, size_t nbytes);   // invalidates the activation cache on overlap
+size_t b200_tensor_span(const b200_tensor * t);
 void   b200_prof_begin(b200_ctx * ctx, int kind);               // no-ops unless ctx->profile
 void   b200_prof_end(b200_ctx * ctx);
 
@@ -119,6 +124,8 @@ int b200_launch_gemv_id_q(b200_ctx * ctx, const b200_tensor * as, const void * i
 int b200_launch_fattn_vec(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v,
                           const b200_tensor * mask, const b200_tensor * sinks, b200_tensor * dst,
                           float scale, float max_bias, float softcap);
+bool b200_gemv_stream_supported(const b200_tensor * w, int64_t ne11, int64_t ne12, int64_t ne13);
+int  b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * w, const void * image, float * dst);
 #define B200_GEMV_MAX_COLS 8
 bool b200_gemm_supported(const b200_tensor * w, const b200_tensor * x);
 int  b200_launch_gemm_q(b200_ctx * ctx, const b200_tensor * w, const b200_tensor * x, b200_tensor * dst);

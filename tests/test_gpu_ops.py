@@ -151,6 +151,39 @@ def test_mul_mat_decode_llama8b_ffn_down(ctx, orc, t):
     assert _check_mm(orc, got, t, w, K, M, x, 1) < 1e-9
 
 
+@pytest.mark.parametrize("t", QTYPES)
+@pytest.mark.parametrize("M,K", [(1, 256), (3, 512), (5, 2304), (37, 4096), (130, 2560), (1000, 256), (4099, 1024)])
+def test_mul_mat_decode_ragged_rows(ctx, orc, t, M, K):
+    """one activation column (the streaming GEMV): odd row counts, a k-chunk tail (9, 10 blocks), more rows than warps"""
+    rng = np.random.default_rng(M * 7 + K)
+    w = O.random_blocks(rng, t, K, M)
+    x = rng.standard_normal((1, K)).astype(np.float32)
+    got = ctx.mul_mat_host(t, w, K, M, x, 1)
+    assert _check_mm(orc, got, t, w, K, M, x, 1) < 1e-9
+
+
+def test_mul_mat_shared_activation_cache(ctx, B, orc):
+    """wq/wk/wv-style reuse of one activation tensor, then an overwrite of it through the API: the cached q8_1 image
+    must be dropped (b200_ctx_invalidate semantics, include/ggml-b200.h)"""
+    rng = np.random.default_rng(99)
+    K, M = 1024, 64
+    w1, w2 = O.random_blocks(rng, O.Q4_K, K, M), O.random_blocks(rng, O.Q4_K, K, M)
+    x1 = rng.standard_normal((1, K)).astype(np.float32); x2 = rng.standard_normal((1, K)).astype(np.float32)
+    dw1, dw2 = ctx.upload(B.Q4_K, [K, M], w1), ctx.upload(B.Q4_K, [K, M], w2)
+    dx = ctx.upload(B.F32, [K, 1], x1); d1, d2 = ctx.empty(B.F32, [M, 1]), ctx.empty(B.F32, [M, 1])
+    q0 = ctx.launches_by_kind()["quantize_q8_1"]
+    ctx.mul_mat(dw1, dx, d1); ctx.mul_mat(dw2, dx, d2)
+    assert ctx.launches_by_kind()["quantize_q8_1"] == q0 + 1          # quantized once for both
+    assert O.nmse(orc.mul_mat(O.Q4_K, w2, K, M, x1, 1, act=O.ACT_Q8_1), ctx.download(d2)) < 1e-9
+    ctx.h2d(dx.ptr, x2)                                               # overwrite the activations
+    ctx.mul_mat(dw1, dx, d1)
+    assert O.nmse(orc.mul_mat(O.Q4_K, w1, K, M, x2, 1, act=O.ACT_Q8_1), ctx.download(d1)) < 1e-9
+    ctx.mul_mat(dw2, dx, dx.view([M, 1], [4, M * 4, M * 4, M * 4]))   # dst aliases the cached source: must invalidate
+    ctx.mul_mat(dw1, dx, d1)
+    x3 = ctx.download(dx).reshape(1, K)
+    assert O.nmse(orc.mul_mat(O.Q4_K, w1, K, M, x3, 1, act=O.ACT_Q8_1), ctx.download(d1)) < 1e-9
+
+
 @pytest.mark.parametrize("t", [O.Q4_0, O.Q4_K, O.Q8_0, O.Q6_K])
 @pytest.mark.parametrize("n", [17, 64, 512])
 def test_mul_mat_prefill(ctx, orc, t, n):
