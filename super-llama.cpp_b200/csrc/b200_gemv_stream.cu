@@ -16,84 +16,82 @@
 #include "b200_common.cuh"
 #include "b200_ptx.cuh"
 
-#define GS_WARPS  4
-#define GS_STAGES 6
+#define GS_WARPS  8
+#define GS_STAGES 4
 #define GS_RW     2       // rows per warp per stage
+#define GS_CB     8       // q4_K blocks per row-chunk (1152 B)
 
 struct gs_args {
-    const uint8_t * w; size_t w_nb1;        // weight rows (GGUF blocks, or the group-SoA repack for q6_K/q8_0/q4_0)
+    const uint8_t * w; size_t w_nb1;        // weight rows (raw GGUF q4_K blocks)
     const int8_t *  aq;                     // q8_1 image: quants [K]
     const __half2 * ads;                    //             (d, s) [K/32]
     float * dst;                            // [M]
-    int64_t M; int K;
+    int M; int K;
 };
 
-template <int TYPE> struct gs_traits;
-
-// ---- q4_K, raw GGUF blocks (144 B, every field 16-byte aligned) ---------------------------------------------------------
-// chunk = 8 blocks = 1152 B per row.  unit = 16 B of qs = 16 weights of sub-block 2p (low nibbles) + 16 of 2p+1 (high).
-// Shared-memory reads: lanes of a quarter-warp read 16 B at stride 144 B = 36 words -> banks 4i..4i+3: conflict-free.
-// Activation image in shared memory: plane 0 = the even q8_1 blocks, plane 1 = the odd ones, so unit U reads
-// plane0[16 U .. 16 U + 15] and plane1[16 U ..]: consecutive lanes, consecutive 16-byte words.
-template <> struct gs_traits<B200_TYPE_Q4_K> {
-    static constexpr int BLOCK_BYTES = 144, CHUNK_BLOCKS = 8, UNITS_PER_BLOCK = 8;
-    static __device__ __forceinline__ int act_dst_offset(int j, int K) {     // j = index of a 16-byte word of the natural image
-        const int blk = j >> 1;
-        return (blk & 1) * (K >> 1) + (blk >> 1) * 32 + (j & 1) * 16;
-    }
-    // one unit of one row: returns the partial dot product
-    static __device__ __forceinline__ float unit(uint32_t row_smem, int b, int c, const int4 & a0, const int4 & a1, const float2 & ds0, const float2 & ds1) {
-        const uint32_t blk = row_smem + b * 144;
-        const int4 hdr = lds128(blk);
-        const int4 q   = lds128(blk + 16 + c * 16);
-        const float2 dm = __half22float2(*(const __half2 *) &hdr.x);
-        const int p = c >> 1, j0 = 2 * p;
+// Lane -> work mapping inside one stage (a chunk of up to 8 blocks of RW rows):
+//   block b = lane & 7; iteration it in {0, 1}; c = (lane >> 3) + 4 it is the 16-byte unit of the block's qs,
+//   i.e. sub-block pair p = c >> 1 = (lane >> 4) + 2 it, half = (lane >> 3) & 1.
+// Every lane of the warp is in the same branch of get_scale_min_k4 (ggml-quants.c:703-710) for a given `it` (p < 2 for
+// it = 0, p >= 2 for it = 1), so the 6-bit scale decode is straight-line code with lane-constant shifts.
+// Shared-memory reads are conflict-free: a quarter-warp reads 8 blocks at stride 144 B = 36 words (banks 4i..4i+3).
+// The activation image is laid out in shared memory as the lanes read it:
+//   quants: plane0[c][gb] / plane1[c][gb], 16 B each -- the 16 int8 that meet the low / high nibbles of unit (gb, c);
+//   scales: ds4[p][gb] = (dA(2p), s(2p), dA(2p+1)/16, s(2p+1)) as four floats -- the /16 undoes the unshifted high
+//   nibbles (dp4a on q & 0xF0F0F0F0 yields 16 x the sum).
+template <int NR, int IT>
+static __device__ __forceinline__ void gs_q4k_unit(uint32_t blk, int cq, int sh, int shm, int half,
+                                                   const int4 & a0, const int4 & a1, const float4 & ds, float ssel,
+                                                   float (&accd)[GS_RW], float (&accm)[GS_RW]) {
+#pragma unroll
+    for (int r = 0; r < NR; ++r) {
+        const uint32_t base = blk + r * (GS_CB * 144);
+        const int4 hdr = lds128(base);
+        const int4 q   = lds128(base + 16 + (cq + 4 * IT) * 16);
         const unsigned s0 = (unsigned) hdr.y, s1 = (unsigned) hdr.z, s2 = (unsigned) hdr.w;
-        int sc0, m0, sc1, m1;                                   // get_scale_min_k4 (ggml-quants.c:703-710) on packed words
-        const int sh0 = 8 * (j0 & 3), sh1 = sh0 + 8;
-        if (p < 2) {
-            sc0 = (s0 >> sh0) & 63; m0 = (s1 >> sh0) & 63;
-            sc1 = (s0 >> sh1) & 63; m1 = (s1 >> sh1) & 63;
+        int sc0, sc1, msel;
+        if (IT == 0) {
+            sc0  = (s0 >> sh) & 63;
+            sc1  = (s0 >> (sh + 8)) & 63;
+            msel = (s1 >> shm) & 63;
         } else {
-            sc0 = ((s2 >> sh0) & 0xF) | (((s0 >> (sh0 + 6)) & 3) << 4);
-            m0  = ((s2 >> (sh0 + 4)) & 0xF) | (((s1 >> (sh0 + 6)) & 3) << 4);
-            sc1 = ((s2 >> sh1) & 0xF) | (((s0 >> (sh1 + 6)) & 3) << 4);
-            m1  = ((s2 >> (sh1 + 4)) & 0xF) | (((s1 >> (sh1 + 6)) & 3) << 4);
+            sc0  = ((s2 >> sh) & 0xF)        | (((s0 >> (sh + 6)) & 3) << 4);
+            sc1  = ((s2 >> (sh + 8)) & 0xF)  | (((s0 >> (sh + 14)) & 3) << 4);
+            msel = ((s2 >> (shm + 4)) & 0xF) | (((s1 >> (shm + 6)) & 3) << 4);
         }
         int i0 = __dp4a(q.x & 0x0F0F0F0F, a0.x, 0); i0 = __dp4a(q.y & 0x0F0F0F0F, a0.y, i0);
         i0 = __dp4a(q.z & 0x0F0F0F0F, a0.z, i0);    i0 = __dp4a(q.w & 0x0F0F0F0F, a0.w, i0);
-        int i1 = __dp4a((q.x >> 4) & 0x0F0F0F0F, a1.x, 0); i1 = __dp4a((q.y >> 4) & 0x0F0F0F0F, a1.y, i1);
-        i1 = __dp4a((q.z >> 4) & 0x0F0F0F0F, a1.z, i1);    i1 = __dp4a((q.w >> 4) & 0x0F0F0F0F, a1.w, i1);
-        float r = dm.x * ((float) sc0 * ds0.x * (float) i0 + (float) sc1 * ds1.x * (float) i1);
-        // the min term uses the whole q8_1 block sum s = d * sum(q): the even half-unit of each sub-block pair adds it
-        if ((c & 1) == 0) r -= dm.y * ((float) m0 * ds0.y + (float) m1 * ds1.y);
-        return r;
+        int i1 = dp4a_us((unsigned) q.x & 0xF0F0F0F0u, a1.x, 0); i1 = dp4a_us((unsigned) q.y & 0xF0F0F0F0u, a1.y, i1);
+        i1 = dp4a_us((unsigned) q.z & 0xF0F0F0F0u, a1.z, i1);    i1 = dp4a_us((unsigned) q.w & 0xF0F0F0F0u, a1.w, i1);
+        const float2 dm = __half22float2(*(const __half2 *) &hdr.x);
+        const float t = (float) (sc0 * i0) * ds.x + (float) (sc1 * i1) * ds.z;
+        accd[r] = fmaf(dm.x, t, accd[r]);
+        accm[r] = fmaf(dm.y, (float) msel * ssel, accm[r]);
     }
-};
+    (void) half;
+}
 
-template <int TYPE>
-__global__ void __launch_bounds__(GS_WARPS * 32) k_gemv_stream(const gs_args p) {
-    using T = gs_traits<TYPE>;
-    constexpr int CHUNK_BYTES = T::BLOCK_BYTES * T::CHUNK_BLOCKS;
+__global__ void __launch_bounds__(GS_WARPS * 32, 2) k_gemv_stream_q4k(const gs_args p) {
+    constexpr int CHUNK_BYTES = 144 * GS_CB;
     constexpr int STAGE_BYTES = CHUNK_BYTES * GS_RW;
     extern __shared__ __align__(128) uint8_t smem[];
-    // layout: [GS_WARPS][GS_STAGES][STAGE_BYTES] rings | act planes [K] | ds [K/32] half2 | mbarriers
-    uint8_t *  ring_all = smem;
-    uint8_t *  s_aq     = ring_all + GS_WARPS * GS_STAGES * STAGE_BYTES;
-    __half2 *  s_ds     = (__half2 *) (s_aq + p.K);
-    uint64_t * s_bar    = (uint64_t *) ((uint8_t *) s_ds + (p.K >> 5) * 4 + ((16 - (((p.K >> 5) * 4) & 15)) & 15));
+    // layout: [GS_WARPS][GS_STAGES][STAGE_BYTES] rings | quant planes [K] | ds4 [K/64] float4 | mbarriers
+    const int nblocks = p.K >> 8;
+    uint8_t *  s_aq  = smem + GS_WARPS * GS_STAGES * STAGE_BYTES;
+    float4 *   s_ds  = (float4 *) (s_aq + p.K);
+    uint64_t * s_bar = (uint64_t *) (s_ds + nblocks * 4);
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t ring = smem_u32(ring_all + warp * GS_STAGES * STAGE_BYTES);
+    const uint32_t ring = smem_u32(smem + warp * GS_STAGES * STAGE_BYTES);
     const uint32_t bar0 = smem_u32(s_bar + warp * GS_STAGES);
 
     // this warp's rows: an even split of [0, M) over every warp of the grid
-    const int64_t gw = (int64_t) blockIdx.x * GS_WARPS + warp, nw = (int64_t) gridDim.x * GS_WARPS;
-    const int64_t r_begin = p.M * gw / nw, r_end = p.M * (gw + 1) / nw;
-    const int nblocks = (TYPE == B200_TYPE_Q4_K || TYPE == B200_TYPE_Q5_K || TYPE == B200_TYPE_Q6_K) ? p.K / 256 : p.K / 32;
-    const int nchunks = (nblocks + T::CHUNK_BLOCKS - 1) / T::CHUNK_BLOCKS;
-    const int64_t npairs = (r_end - r_begin + GS_RW - 1) / GS_RW;
-    const int64_t nitems = npairs * nchunks;
+    const int gw = blockIdx.x * GS_WARPS + warp, nw = gridDim.x * GS_WARPS;
+    const int r_begin = (int) ((int64_t) p.M * gw / nw), r_end = (int) ((int64_t) p.M * (gw + 1) / nw);
+    const int rows = r_end - r_begin;
+    const int nchunks = (nblocks + GS_CB - 1) / GS_CB;
+    const int npairs = (rows + GS_RW - 1) / GS_RW;
+    const int nitems = npairs * nchunks;
 
     if (lane == 0) {
         for (int s = 0; s < GS_STAGES; ++s) mbar_init(bar0 + 8 * s, 1);
@@ -102,83 +100,95 @@ __global__ void __launch_bounds__(GS_WARPS * 32) k_gemv_stream(const gs_args p) 
     __syncwarp();
 
     const uint64_t policy = l2_policy_evict_first();
-    auto issue = [&](int64_t item) {                                     // lane 0 only
-        const int     s  = (int) (item % GS_STAGES);
-        const int64_t rp = item / nchunks;
-        const int     kc = (int) (item - rp * nchunks);
-        const int     cb = min(T::CHUNK_BLOCKS, nblocks - kc * T::CHUNK_BLOCKS);
-        const uint32_t bytes = (uint32_t) cb * T::BLOCK_BYTES;
-        const int64_t row0 = r_begin + rp * GS_RW;
-        const int     nr = (int) min((int64_t) GS_RW, r_end - row0);
-        mbar_arrive_expect_tx(bar0 + 8 * s, bytes * nr);
-        for (int r = 0; r < nr; ++r)
-            bulk_g2s_hint(ring + s * STAGE_BYTES + r * CHUNK_BYTES, p.w + (row0 + r) * p.w_nb1 + (size_t) kc * CHUNK_BYTES, bytes, bar0 + 8 * s, policy);
+    const uint8_t * wbase = p.w + (size_t) r_begin * p.w_nb1;
+    // producer cursor (uniform across the warp; only lane 0 issues)
+    int prp = 0, pkc = 0;
+    auto issue = [&](int stage) {
+        const int cb = min(GS_CB, nblocks - pkc * GS_CB);
+        const int nr = min(GS_RW, rows - prp * GS_RW);
+        if (lane == 0) {
+            const uint32_t bytes = (uint32_t) cb * 144, bar = bar0 + 8 * stage;
+            mbar_arrive_expect_tx(bar, bytes * nr);
+            const uint8_t * src = wbase + (size_t) (prp * GS_RW) * p.w_nb1 + (size_t) pkc * CHUNK_BYTES;
+            bulk_g2s_hint(ring + stage * STAGE_BYTES, src, bytes, bar, policy);
+            if (nr > 1) bulk_g2s_hint(ring + stage * STAGE_BYTES + CHUNK_BYTES, src + p.w_nb1, bytes, bar, policy);
+        }
+        if (++pkc == nchunks) { pkc = 0; ++prp; }
     };
-    if (lane == 0) for (int64_t i = 0; i < nitems && i < GS_STAGES; ++i) issue(i);
+    const int npro = min(nitems, GS_STAGES);
+    for (int i = 0; i < npro; ++i) issue(i);
 
-    // activation image -> shared memory, permuted into the order the lanes read it (overlaps the first bulk copies)
+    // activation image -> shared memory in lane order (overlaps the first bulk copies)
     {
         const int4 * src = (const int4 *) p.aq;
-        for (int j = threadIdx.x; j < p.K / 16; j += blockDim.x) {
-            const int4 v = src[j];
-            *(int4 *) (s_aq + T::act_dst_offset(j, p.K)) = v;
+        for (int j = threadIdx.x; j < (p.K >> 4); j += blockDim.x) {       // j: 16-byte word of the natural image
+            const int blk32 = j >> 1, hf = j & 1, gb = blk32 >> 3, sub = blk32 & 7;
+            const int c = (sub >> 1) * 2 + hf;
+            *(int4 *) (s_aq + (sub & 1) * (p.K >> 1) + (c * nblocks + gb) * 16) = src[j];
         }
-        for (int j = threadIdx.x; j < p.K / 32; j += blockDim.x) s_ds[j] = p.ads[j];
+        for (int j = threadIdx.x; j < (p.K >> 6); j += blockDim.x) {       // j: pair of q8_1 blocks
+            const int gb = j >> 2, pp = j & 3;
+            const float2 e = __half22float2(p.ads[2 * j]), o = __half22float2(p.ads[2 * j + 1]);
+            s_ds[pp * nblocks + gb] = make_float4(e.x, e.y, o.x * 0.0625f, o.y);
+        }
     }
     __syncthreads();
 
+    const int bl = lane & 7, cq = lane >> 3, half = cq & 1;
+    const int sh = 16 * (lane >> 4), shm = sh + 8 * half;
     const uint32_t aq0 = smem_u32(s_aq), aq1 = aq0 + (p.K >> 1), ads = smem_u32(s_ds);
-    float acc[GS_RW];
+    float accd[GS_RW], accm[GS_RW];
 #pragma unroll
-    for (int r = 0; r < GS_RW; ++r) acc[r] = 0.0f;
+    for (int r = 0; r < GS_RW; ++r) accd[r] = accm[r] = 0.0f;
 
-    for (int64_t item = 0; item < nitems; ++item) {
-        const int     s  = (int) (item % GS_STAGES);
-        const int64_t rp = item / nchunks;
-        const int     kc = (int) (item - rp * nchunks);
-        const int     cb = min(T::CHUNK_BLOCKS, nblocks - kc * T::CHUNK_BLOCKS);
-        const int64_t row0 = r_begin + rp * GS_RW;
-        const int     nr = (int) min((int64_t) GS_RW, r_end - row0);
-        mbar_wait(bar0 + 8 * s, (uint32_t) ((item / GS_STAGES) & 1));
+    int stage = 0, phase = 0, rp = 0, kc = 0;
+    for (int item = 0; item < nitems; ++item) {
+        const int cb = min(GS_CB, nblocks - kc * GS_CB);
+        const int nr = min(GS_RW, rows - rp * GS_RW);
+        mbar_wait(bar0 + 8 * stage, (uint32_t) phase);
 
-        const uint32_t st = ring + s * STAGE_BYTES;
-        for (int u = lane; u < cb * T::UNITS_PER_BLOCK; u += 32) {
-            const int b = u / T::UNITS_PER_BLOCK, c = u % T::UNITS_PER_BLOCK;
-            const int gb = kc * T::CHUNK_BLOCKS + b;                      // block index in the row
-            const int U  = gb * T::UNITS_PER_BLOCK + c;
-            const int4 a0 = lds128(aq0 + 16 * U), a1 = lds128(aq1 + 16 * U);
-            const int2 dsr = lds64(ads + (gb * 8 + 2 * (c >> 1)) * 4);
-            const float2 ds0 = __half22float2(*(const __half2 *) &dsr.x), ds1 = __half22float2(*(const __half2 *) &dsr.y);
+        if (bl < cb) {
+            const int gb = kc * GS_CB + bl;
+            const uint32_t blk = ring + stage * STAGE_BYTES + bl * 144;
 #pragma unroll
-            for (int r = 0; r < GS_RW; ++r)
-                if (r < nr) acc[r] += T::unit(st + r * CHUNK_BYTES, b, c, a0, a1, ds0, ds1);
+            for (int it = 0; it < 2; ++it) {
+                const int c = cq + 4 * it, pp = (lane >> 4) + 2 * it;
+                const int4 a0 = lds128(aq0 + (c * nblocks + gb) * 16), a1 = lds128(aq1 + (c * nblocks + gb) * 16);
+                const int4 dsr = lds128(ads + (pp * nblocks + gb) * 16);
+                const float4 ds = make_float4(__int_as_float(dsr.x), __int_as_float(dsr.y), __int_as_float(dsr.z), __int_as_float(dsr.w));
+                const float ssel = half ? ds.w : ds.y;
+                if (nr == GS_RW) { if (it == 0) gs_q4k_unit<GS_RW, 0>(blk, cq, sh, shm, half, a0, a1, ds, ssel, accd, accm);
+                                   else         gs_q4k_unit<GS_RW, 1>(blk, cq, sh, shm, half, a0, a1, ds, ssel, accd, accm); }
+                else             { if (it == 0) gs_q4k_unit<1, 0>(blk, cq, sh, shm, half, a0, a1, ds, ssel, accd, accm);
+                                   else         gs_q4k_unit<1, 1>(blk, cq, sh, shm, half, a0, a1, ds, ssel, accd, accm); }
+            }
         }
         __syncwarp();                                                     // every lane is done reading this stage
-        if (lane == 0 && item + GS_STAGES < nitems) issue(item + GS_STAGES);
+        if (item + GS_STAGES < nitems) issue(stage);
 
         if (kc == nchunks - 1) {
 #pragma unroll
             for (int r = 0; r < GS_RW; ++r) {
-                const float v = warp_sum(acc[r]);
-                if (lane == 0 && r < nr) p.dst[row0 + r] = v;
-                acc[r] = 0.0f;
+                const float v = warp_sum(accd[r] - accm[r]);
+                if (lane == 0 && r < nr) p.dst[r_begin + rp * GS_RW + r] = v;
+                accd[r] = accm[r] = 0.0f;
             }
-        }
+            kc = 0; ++rp;
+        } else ++kc;
+        if (++stage == GS_STAGES) { stage = 0; phase ^= 1; }
     }
 }
 
-static size_t gs_smem_bytes(int chunk_bytes, int K) {
-    size_t n = (size_t) GS_WARPS * GS_STAGES * chunk_bytes * GS_RW + K;
-    size_t ds = (size_t) (K >> 5) * 4; ds = (ds + 15) & ~(size_t) 15;
-    return n + ds + GS_WARPS * GS_STAGES * 8;
+static size_t gs_smem_bytes(int K) {
+    return (size_t) GS_WARPS * GS_STAGES * 144 * GS_CB * GS_RW + K + (size_t) (K >> 8) * 4 * 16 + GS_WARPS * GS_STAGES * 8;
 }
 
 // true when the streaming kernel can take this MUL_MAT (one activation column, 2-D weight, aligned rows)
 bool b200_gemv_stream_supported(const b200_tensor * w, int64_t ne11, int64_t ne12, int64_t ne13) {
     if (ne11 != 1 || ne12 != 1 || ne13 != 1 || w->ne[2] != 1 || w->ne[3] != 1) return false;
     if (w->type != B200_TYPE_Q4_K) return false;
-    if (((uintptr_t) w->data & 15) || (w->nb[1] & 15) || w->ne[0] % 256 != 0 || w->ne[0] > 65536) return false;
-    return gs_smem_bytes(144 * 8, (int) w->ne[0]) <= 200 * 1024;
+    if (((uintptr_t) w->data & 15) || (w->nb[1] & 15) || w->ne[0] % 256 != 0 || w->ne[0] > 32768 || w->ne[1] > (1 << 30)) return false;
+    return gs_smem_bytes((int) w->ne[0]) <= 110 * 1024;
 }
 
 int b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * w, const void * image, float * dst) {
@@ -186,17 +196,15 @@ int b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * w, const void * 
     const int K = (int) w->ne[0];
     p.w = (const uint8_t *) w->data; p.w_nb1 = w->nb[1];
     p.aq = (const int8_t *) image; p.ads = (const __half2 *) ((const int8_t *) image + K);
-    p.dst = dst; p.M = w->ne[1]; p.K = K;
-    const size_t smem = gs_smem_bytes(144 * 8, K);
+    p.dst = dst; p.M = (int) w->ne[1]; p.K = K;
+    const size_t smem = gs_smem_bytes(K);
     if (!ctx->attr_done[0]) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(k_gemv_stream<B200_TYPE_Q4_K>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        B200_CUDA_TRY(cudaFuncSetAttribute(k_gemv_stream_q4k, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
         ctx->attr_done[0] = 1;
     }
-    // enough CTAs that every warp gets >= GS_RW rows, at most 3 resident CTAs per SM
-    const int64_t want = (p.M + GS_WARPS * GS_RW - 1) / (GS_WARPS * GS_RW);
-    const int per_sm = (int) max((size_t) 1, min((size_t) 3, (size_t) (220 * 1024) / (smem + 1024)));
-    const int64_t cap = (int64_t) ctx->sm_count * per_sm;
-    const unsigned grid = (unsigned) max((int64_t) 1, min(want, cap));
-    B200_LAUNCH(ctx, B200_K_GEMV, k_gemv_stream<B200_TYPE_Q4_K><<<grid, GS_WARPS * 32, smem, ctx->stream>>>(p));
+    // persistent-style grid: two CTAs per SM, rows split evenly over all warps; fewer CTAs when there are few rows
+    const int64_t want = (p.M + GS_WARPS - 1) / GS_WARPS;
+    const unsigned grid = (unsigned) max((int64_t) 1, min(want, (int64_t) ctx->sm_count * 2));
+    B200_LAUNCH(ctx, B200_K_GEMV, k_gemv_stream_q4k<<<grid, GS_WARPS * 32, smem, ctx->stream>>>(p));
     return B200_OK;
 }

@@ -67,3 +67,10 @@ static __device__ __forceinline__ int lds32(uint32_t addr) {
 static __device__ __forceinline__ void sts128(uint32_t addr, int4 v) {
     asm volatile("st.shared.v4.s32 [%0], {%1,%2,%3,%4};" :: "r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
+
+// 4-way byte dot product, a unsigned bytes x b signed bytes (the CUDA intrinsic only offers same-sign operands)
+static __device__ __forceinline__ int dp4a_us(unsigned a, int b, int c) {
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
