@@ -116,6 +116,10 @@ B200_API int b200_quantize_q8_1(b200_ctx * ctx, const float * x, size_t x_row_st
 // w broadcast over dims 2,3 (ggml/src/ggml.c:3168-3203).  w: f32/f16/bf16/q4_0/q8_0/q4_K/q5_K/q6_K.
 B200_API int b200_mul_mat(b200_ctx * ctx, const b200_tensor * w, const b200_tensor * x, b200_tensor * dst);
 
+// n MUL_MATs sharing the activation tensor x (wq/wk/wv, ffn_gate/ffn_up in src/models/llama.cpp:40-75): same result as n
+// b200_mul_mat calls; served by one launch of the streaming GEMV when x is a single column and the weights allow it.
+B200_API int b200_mul_mat_multi(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, b200_tensor * const * dst);
+
 // as[K, M, n_expert], b[K, n_used|1, n_tokens] f32, ids[n_used, n_tokens] i32 -> dst[M, n_used, n_tokens]
 // (ggml/src/ggml.c:3205-3241).
 B200_API int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b200_tensor * b,
@@ -127,6 +131,13 @@ B200_API int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b200_
 B200_API int b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k,
                                  const b200_tensor * v, const b200_tensor * mask, const b200_tensor * sinks,
                                  b200_tensor * dst, float scale, float max_bias, float logit_softcap);
+
+// ---- load-time weight repack (DESIGN.md "HBM layout"): in place, size- and stride-preserving, exactly invertible ------
+// q6_K rows whose length is a multiple of 2048 are permuted per group of 8 blocks into a 16-byte aligned field-major
+// layout; the caller then sets B200_TENSOR_REPACKED in b200_tensor.flags.  Other types are consumed in GGUF layout.
+B200_API int b200_repack_supported(int type, int64_t k);
+B200_API int b200_repack(b200_ctx * ctx, int type, void * data, int64_t k, int64_t nrows, size_t row_stride);
+B200_API int b200_unrepack(b200_ctx * ctx, int type, void * data, int64_t k, int64_t nrows, size_t row_stride);
 
 // ---- row split (split-mode=row) helpers; reference ggml-cuda.cu:777-803 --------------------
 // rows [*row_low, *row_high) of an nrows-row weight that rank `rank` of `world` owns under `tensor_split`

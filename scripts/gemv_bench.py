@@ -34,7 +34,7 @@ for tn in a.types.split(","):
         for _ in range(nbuf):
             w = ctx.empty(t, [K, M])
             for off in range(0, wb, pool.size): ctx.h2d(w.ptr + off, pool[: min(pool.size, wb - off)])
-            ws.append(w)
+            ctx.repack(w); ws.append(w)
         x = ctx.upload(B.F32, [K, a.n], rng.standard_normal(K * a.n).astype(np.float32)); d = ctx.empty(B.F32, [M, a.n])
         for w in ws: ctx.mul_mat(w, x, d)
         ctx.synchronize()

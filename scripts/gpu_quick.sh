@@ -9,7 +9,7 @@ try:
     d=json.load(open('gpurun_out/bench.json'))
     print('tg tok/s', round(d['value'],1), 'ms', round(d['ms_per_step'],3), 'e2e', round(d['e2e']['value'],1), 'hbm_frac_step', round(d['hbm_frac_whole_step'],3))
     print('roofline', {k:(round(v,3) if isinstance(v,float) else v) for k,v in d['roofline'].items() if k in('achieved','frac','ms_per_step','launches_per_step')})
-    print('kernel ms', {k:round(v,3) for k,v in d['kernel_ms_per_step'].items()}, 'launches/step', d['gpu_launches_per_step'])
+    print('kernel ms', {k:round(v,3) for k,v in d['kernel_ms_per_step_event_bracketed'].items()}, 'launches/step', d['gpu_launches_per_step'])
     if 'pp512' in d: print('pp512', round(d['pp512']['value'],1), d['pp512']['roofline']['frac'], d['pp512']['kernel_ms_per_step'])
 except Exception as e: print('bench parse failed', e)
 PY

@@ -31,6 +31,7 @@ extern "C" b200_ctx * b200_ctx_create(int device) {
     if (cudaSetDevice(device) != cudaSuccess) { b200_set_error("cudaSetDevice(%d) failed", device); return nullptr; }
     b200_ctx * ctx = (b200_ctx *) calloc(1, sizeof(b200_ctx));
     ctx->device = device; ctx->prof_open = -1;
+    { const char * e = getenv("GGML_B200_NO_PDL"); ctx->pdl = (e && atoi(e)) ? 0 : 1; }
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { b200_set_error("stream create failed"); free(ctx); return nullptr; }
     cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
     return ctx;
@@ -225,11 +226,13 @@ extern "C" int b200_mul_mat(b200_ctx * ctx, const b200_tensor * w, const b200_te
         if (w->nb[0] != b200_type_size(w->type)) { b200_set_error("mul_mat: quantized weight rows must be contiguous"); return B200_ERR_UNSUPPORTED; }
         int rc;
         if (x->ne[1] > B200_GEMV_MAX_COLS && b200_gemm_supported(w, x)) rc = b200_launch_gemm_q(ctx, w, x, dst);
-        else {
+        else if (q8_1_variant_env() == B200_Q8_1_X86 && b200_gemv_stream_supported(w, x)) {
+            float * d = (float *) dst->data;
+            rc = b200_launch_gemv_stream(ctx, &w, 1, x, &d);            // fused quantize + TMA-streamed GEMV
+        } else {
             const void * image = quantized_activations(ctx, x, q8_1_variant_env(), &rc);
             if (!image) return rc;
-            if (b200_gemv_stream_supported(w, x->ne[1], x->ne[2], x->ne[3])) rc = b200_launch_gemv_stream(ctx, w, image, (float *) dst->data);
-            else rc = b200_launch_gemv_q(ctx, w, image, x->ne[1], x->ne[2], x->ne[3], dst);
+            rc = b200_launch_gemv_q(ctx, w, image, x->ne[1], x->ne[2], x->ne[3], dst);
         }
         b200_note_write(ctx, dst->data, b200_tensor_span(dst));
         return rc;
@@ -237,6 +240,26 @@ extern "C" int b200_mul_mat(b200_ctx * ctx, const b200_tensor * w, const b200_te
     if (is_float_w(w->type)) { const int rc = b200_launch_matmul_float(ctx, w, x, dst); b200_note_write(ctx, dst->data, b200_tensor_span(dst)); return rc; }
     b200_set_error("mul_mat: weight type %d is outside the hot path", w->type);
     return B200_ERR_UNSUPPORTED;
+}
+
+// n MUL_MATs that share src1 (wq/wk/wv, ffn_gate/ffn_up): one launch when the streaming GEMV can take them all
+extern "C" int b200_mul_mat_multi(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, b200_tensor * const * dst) {
+    if (!ctx || !w || !x || !dst || n <= 0) { b200_set_error("mul_mat_multi: bad arguments"); return B200_ERR_INVALID; }
+    bool fuse = n > 1 && n <= 3 && q8_1_variant_env() == B200_Q8_1_X86;
+    for (int i = 0; i < n && fuse; ++i) {
+        fuse = b200_gemv_stream_supported(w[i], x) && w[i]->type == w[0]->type && w[i]->ne[0] == w[0]->ne[0] && x->ne[0] == w[i]->ne[0] &&
+               dst[i]->type == B200_TYPE_F32 && dst[i]->nb[0] == 4 && dst[i]->ne[0] == w[i]->ne[1] && dst[i]->ne[1] == 1 && dst[i]->ne[2] == 1 && dst[i]->ne[3] == 1;
+    }
+    if (!fuse) {
+        for (int i = 0; i < n; ++i) { const int rc = b200_mul_mat(ctx, w[i], x, dst[i]); if (rc) return rc; }
+        return B200_OK;
+    }
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    float * d[3];
+    for (int i = 0; i < n; ++i) d[i] = (float *) dst[i]->data;
+    const int rc = b200_launch_gemv_stream(ctx, w, n, x, d);
+    for (int i = 0; i < n; ++i) b200_note_write(ctx, dst[i]->data, b200_tensor_span(dst[i]));
+    return rc;
 }
 
 extern "C" int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids, b200_tensor * dst) {

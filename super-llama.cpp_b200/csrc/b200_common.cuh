@@ -68,7 +68,8 @@ struct b200_ctx {
     int          capturing;
     // the q8_1 image of the most recently quantized activation tensor (scratch slot 0): wq/wk/wv and gate/up share theirs
     struct { const void * data; int64_t ne[4]; size_t nb[4]; size_t span; int variant; int valid; } qcache;
-    int          attr_done[8];       // per-kernel one-time cudaFuncSetAttribute flags (a ctx is bound to one device)
+    int          attr_done[8];
+    int          pdl;                // launch the streaming GEMV with programmatic dependent launch (GGML_B200_NO_PDL=1 disables)       // per-kernel one-time cudaFuncSetAttribute flags (a ctx is bound to one device)
 };
 
 void   b200_set_error(const char * fmt, ...);
@@ -113,6 +114,33 @@ static __device__ __forceinline__ int ld_u16x2(const void * p) {   // 4 bytes fr
     return (int) ((uint32_t) q[0] | ((uint32_t) q[1] << 16));
 }
 
+// ---- q8_1 block quantization, bit-exact with the reference CPU code (see b200_quantize.cu for the citations) ----
+// float -> int32 the way x86 cvtps2dq / cvttss2si do it: out-of-range (a denormal amax makes id = inf) and NaN
+// give the "integer indefinite" 0x80000000 instead of CUDA's saturation.
+static __device__ __forceinline__ int cvt_x86(float r) { return fabsf(r) < 2147483648.0f ? __float2int_rn(r) : (int) 0x80000000u; }
+
+// one warp, one block: returns this lane's quant, the block scale d (fp32) and the integer sum of quants
+template <int VARIANT>
+static __device__ __forceinline__ void q8_1_block(float v, int & q, float & d, int & isum) {
+    const float amax = warp_max(fabsf(v));
+    d = __fdiv_rn(amax, 127.0f);
+    unsigned usum;
+    if (VARIANT == B200_Q8_1_X86) {
+        const float id  = amax != 0.0f ? __fdiv_rn(127.0f, amax) : 0.0f;
+        const int   q32 = cvt_x86(rintf(__fmul_rn(v, id)));      // round-half-even, as _mm256_round_ps(NEAREST) + cvtps_epi32
+        q    = max(-128, min(127, q32));                         // packs_epi32/epi16 saturate
+        usum = (unsigned) q32;                                   // ... but the AVX2 body sums the int32 lanes before packing
+    } else {
+        const float id  = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+        const int   q32 = cvt_x86(roundf(__fmul_rn(v, id)));     // half away from zero, as roundf(); then C's (int8_t) cast
+        q    = (int) (int8_t) (q32 & 0xff);
+        usum = (unsigned) q;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) usum += __shfl_xor_sync(0xffffffffu, usum, o);
+    isum = (int) usum;
+}
+
 // ---- internal launchers (defined in the .cu files) ----------------------------------------
 int b200_launch_quantize_q8_1(b200_ctx * ctx, const float * x, size_t x_row_stride, void * y, int64_t k, int64_t nrows, int variant);
 int b200_launch_quantize_q8_1_soa(b200_ctx * ctx, const float * x, size_t nb1, size_t nb2, size_t nb3,
@@ -124,8 +152,8 @@ int b200_launch_gemv_id_q(b200_ctx * ctx, const b200_tensor * as, const void * i
 int b200_launch_fattn_vec(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v,
                           const b200_tensor * mask, const b200_tensor * sinks, b200_tensor * dst,
                           float scale, float max_bias, float softcap);
-bool b200_gemv_stream_supported(const b200_tensor * w, int64_t ne11, int64_t ne12, int64_t ne13);
-int  b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * w, const void * image, float * dst);
+bool b200_gemv_stream_supported(const b200_tensor * w, const b200_tensor * x);
+int  b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, float * const * dst);
 #define B200_GEMV_MAX_COLS 8
 bool b200_gemm_supported(const b200_tensor * w, const b200_tensor * x);
 int  b200_launch_gemm_q(b200_ctx * ctx, const b200_tensor * w, const b200_tensor * x, b200_tensor * dst);

@@ -161,6 +161,44 @@ template <> struct gemv_traits<B200_TYPE_Q6_K> {
     }
 };
 
+// ---- q6_K in the group-SoA repack (b200_repack.cu): same unit, fields found through the group map ----------------
+#define B200_TYPE_Q6_K_REPACKED 1014
+template <> struct gemv_traits<B200_TYPE_Q6_K_REPACKED> {
+    static constexpr int units_per_block = 16, block_elems = 256, block_bytes = 210;
+    template <int NC>
+    static __device__ __forceinline__ void unit(const uint8_t * row, int64_t u, const act_image & a, int64_t col0, float * acc) {
+        const int64_t b = u >> 4; const int r = (int) (u & 15);
+        const int h = r >> 3, l = 4 * (r & 7), j = l >> 4, ii = l & 15, bb = (int) (b & 7);
+        const uint8_t * G = row + (b >> 3) * 1680;
+        const int qa = *(const int *) (G + ((((h * 2 + j) * 2 + 0) * 8 + bb) << 4) + ii);
+        const int qb = *(const int *) (G + ((((h * 2 + j) * 2 + 1) * 8 + bb) << 4) + ii);
+        const int qh = *(const int *) (G + 1024 + (((h * 2 + j) * 8 + bb) << 4) + ii);
+        const int8_t * sc = (const int8_t *) (G + 1536 + bb * 16) + 8 * h + j;
+        const float d = __half2float(*(const __half *) (G + 1664 + bb * 2));
+        int w[4];
+        w[0] = __vsub4((qa & 0x0F0F0F0F)        | ((qh & 0x03030303) << 4),        0x20202020);
+        w[1] = __vsub4((qb & 0x0F0F0F0F)        | (((qh >> 2) & 0x03030303) << 4), 0x20202020);
+        w[2] = __vsub4(((qa >> 4) & 0x0F0F0F0F) | (((qh >> 4) & 0x03030303) << 4), 0x20202020);
+        w[3] = __vsub4(((qb >> 4) & 0x0F0F0F0F) | (((qh >> 6) & 0x03030303) << 4), 0x20202020);
+        float dsc[4];
+#pragma unroll
+        for (int g = 0; g < 4; ++g) dsc[g] = d * (float) sc[2 * g];
+        const int64_t ab = b * 8 + 4 * h;
+#pragma unroll
+        for (int n = 0; n < NC; ++n) {
+            const int8_t *  aq = a.qs + (col0 + n) * a.K;
+            const __half2 * ad = a.ds + (col0 + n) * (a.K >> 5);
+            float s = 0.0f;
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+                const int av = *(const int *) (aq + (ab + g) * 32 + l);
+                s += dsc[g] * __low2float(ad[ab + g]) * (float) __dp4a(w[g], av, 0);
+            }
+            acc[n] += s;
+        }
+    }
+};
+
 // ---- q4_0 (raw GGUF, 18-byte blocks): unit = one block --------------------------------------
 template <> struct gemv_traits<B200_TYPE_Q4_0> {
     static constexpr int units_per_block = 1, block_elems = 32, block_bytes = 18;
@@ -286,7 +324,8 @@ int b200_launch_gemv_q(b200_ctx * ctx, const b200_tensor * w, const void * image
     switch (w->type) {
         case B200_TYPE_Q4_K: return launch_gemv_type<B200_TYPE_Q4_K>(ctx, p, (int) ne11);
         case B200_TYPE_Q5_K: return launch_gemv_type<B200_TYPE_Q5_K>(ctx, p, (int) ne11);
-        case B200_TYPE_Q6_K: return launch_gemv_type<B200_TYPE_Q6_K>(ctx, p, (int) ne11);
+        case B200_TYPE_Q6_K: return (w->flags & B200_TENSOR_REPACKED) ? launch_gemv_type<B200_TYPE_Q6_K_REPACKED>(ctx, p, (int) ne11)
+                                                                        : launch_gemv_type<B200_TYPE_Q6_K>(ctx, p, (int) ne11);
         case B200_TYPE_Q4_0: return launch_gemv_type<B200_TYPE_Q4_0>(ctx, p, (int) ne11);
         case B200_TYPE_Q8_0: return launch_gemv_type<B200_TYPE_Q8_0>(ctx, p, (int) ne11);
     }
@@ -344,7 +383,10 @@ int b200_launch_gemv_id_q(b200_ctx * ctx, const b200_tensor * as, const void * i
     switch (as->type) {
         case B200_TYPE_Q4_K: B200_LAUNCH(ctx, B200_K_GEMV_ID, k_gemv_id<B200_TYPE_Q4_K, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p)); break;
         case B200_TYPE_Q5_K: B200_LAUNCH(ctx, B200_K_GEMV_ID, k_gemv_id<B200_TYPE_Q5_K, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p)); break;
-        case B200_TYPE_Q6_K: B200_LAUNCH(ctx, B200_K_GEMV_ID, k_gemv_id<B200_TYPE_Q6_K, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p)); break;
+        case B200_TYPE_Q6_K:
+            if (as->flags & B200_TENSOR_REPACKED) B200_LAUNCH(ctx, B200_K_GEMV_ID, k_gemv_id<B200_TYPE_Q6_K_REPACKED, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p));
+            else                                  B200_LAUNCH(ctx, B200_K_GEMV_ID, k_gemv_id<B200_TYPE_Q6_K, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p));
+            break;
         case B200_TYPE_Q4_0: B200_LAUNCH(ctx, B200_K_GEMV_ID, k_gemv_id<B200_TYPE_Q4_0, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p)); break;
         case B200_TYPE_Q8_0: B200_LAUNCH(ctx, B200_K_GEMV_ID, k_gemv_id<B200_TYPE_Q8_0, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p)); break;
         default: b200_set_error("gemv_id: weight type %d unsupported", as->type); return B200_ERR_UNSUPPORTED;

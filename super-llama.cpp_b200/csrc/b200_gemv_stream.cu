@@ -1,93 +1,187 @@
-// b200_gemv_stream.cu -- the decode dequant-GEMV (MUL_MAT with one activation column), streamed through the TMA engine.
+// b200_gemv_stream.cu -- the decode dequant-GEMV (MUL_MAT with one activation column), streamed through the TMA engine,
+// with the q8_1 activation quantization fused in and up to three weight tensors that share src1 (wq/wk/wv, gate/up)
+// served by ONE launch.
 //
-// Replaces the CPU inner loop ggml_vec_dot_q4_K_q8_K / q6_K_q8_K / q8_0_q8_0 / q4_0_q8_0 driven by
-// ggml_compute_forward_mul_mat (reference ggml/src/ggml-cpu/ggml-cpu.c:1136-1224, quants.c:115,305,550,708).
+// Replaces the CPU inner loop ggml_vec_dot_q4_K_q8_K / q6_K_q8_K driven by ggml_compute_forward_mul_mat
+// (reference ggml/src/ggml-cpu/ggml-cpu.c:1136-1224, quants.c:550,708) and quantize_row_q8_1
+// (ggml-cpu/arch/x86/quants.c:388-449; same arithmetic as b200_quantize.cu, shared through q8_1_block()).
 //
-// Bound: HBM.  Algorithmic bytes per launch = M * K * bytes_per_block / block_size (each weight byte read once).
+// Bound: HBM.  Algorithmic bytes per launch = sum over segments of M * K * bytes_per_block / 256 (each weight byte once).
 //
-// Why this shape (measured, profiles/r1_run1_*): a plain "one warp per row, 128-bit loads" kernel reached 20 % of HBM on
-// B200 -- with ~30 resident warps per SM and two 16-byte loads in flight per lane it cannot cover the ~1 us loaded HBM
-// latency at 44 B/ns/SM.  Here every warp is its own streaming engine: lane 0 issues cp.async.bulk copies (the TMA engine,
-// no registers, no LSU slots) of RW row-chunks into a private STAGES-deep shared-memory ring, completion is signalled on
-// an mbarrier per stage, and the 32 lanes consume a stage with conflict-free 128-bit shared loads while the next
-// STAGES-1 stages are in flight (~14 KB per warp, ~160 KB per SM).  The q8_1 activation image (L2 resident, produced by
-// b200_quantize.cu) is copied once per CTA into shared memory in the order the lanes read it.
-// Rows are split evenly over all warps of the grid (<= 1 row of imbalance), so odd row counts cost nothing.
+// Shape of the kernel (why: profiles/r1_gemv_stream_v2_*):
+//  * every warp is its own streaming engine: lane 0 issues cp.async.bulk copies (TMA engine: no registers, no LSU slots)
+//    of GS_RW row-chunks into a private GS_STAGES-deep shared-memory ring, an mbarrier per stage signals arrival, the 32
+//    lanes consume a stage with conflict-free 128-bit shared loads while the other stages are in flight;
+//  * rows of all segments are split evenly over all warps of a persistent-size grid (two CTAs per SM);
+//  * each CTA quantizes the activation column itself (bit-exact q8_1) straight into shared memory, in the order its
+//    lanes will read it, while the first ring stages are landing -- no separate quantize launch, no image in HBM;
+//  * launched with programmatic dependent launch: barrier init and the weight prefetch (which do not depend on the
+//    previous kernel) run under the previous kernel's tail; griddepcontrol.wait guards the first read of src1.
 #include "b200_common.cuh"
 #include "b200_ptx.cuh"
 
 #define GS_WARPS  8
 #define GS_STAGES 4
 #define GS_RW     2       // rows per warp per stage
-#define GS_CB     8       // q4_K blocks per row-chunk (1152 B)
+#define GS_CB     8       // 256-weight blocks per row-chunk
+#define GS_MAXSEG 3
 
-struct gs_args {
-    const uint8_t * w; size_t w_nb1;        // weight rows (raw GGUF q4_K blocks)
-    const int8_t *  aq;                     // q8_1 image: quants [K]
-    const __half2 * ads;                    //             (d, s) [K/32]
-    float * dst;                            // [M]
-    int M; int K;
+struct gs_seg { const uint8_t * w; size_t nb1; float * dst; int M; };
+struct gs_args { gs_seg seg[GS_MAXSEG]; int nseg; int Mtot; const float * x; int K; };
+
+template <int TYPE> struct gs_traits;
+
+// ================================================ q4_K (raw GGUF blocks) ================================================
+// 144-byte blocks, every field 16-byte aligned, so the raw row is streamed as is; chunk = 8 blocks = 1152 B.
+// Lane -> work inside one stage: block b = lane & 7; it in {0, 1}; c = (lane >> 3) + 4 it is the 16-byte unit of the
+// block's qs, i.e. sub-block pair p = c >> 1 = (lane >> 4) + 2 it, half = (lane >> 3) & 1.  All lanes are in the same
+// branch of get_scale_min_k4 (ggml-quants.c:703-710) for a given `it`, so the 6-bit decode is straight-line code.
+// Shared reads are conflict-free: a quarter-warp reads 8 blocks at stride 144 B = 36 words (banks 4i..4i+3).
+// Activations in shared memory: quant planes plane0[c][gb] / plane1[c][gb] (16 B: the int8 that meet the low / high
+// nibbles of unit (gb, c)) and ds4[p][gb] = (dA(2p), s(2p), dA(2p+1)/16, s(2p+1)); the /16 undoes the unshifted high
+// nibbles (dp4a on q & 0xF0F0F0F0 gives 16 x the sum).
+template <> struct gs_traits<B200_TYPE_Q4_K> {
+    static constexpr int BLOCK_BYTES = 144;
+    static __host__ __device__ size_t act_bytes(int K) { return (size_t) K + (size_t) (K >> 8) * 64; }
+    // 4 consecutive quants (bytes off..off+3 of q8_1 block blk32) packed in `word`; the group leader also stores (d, s)
+    static __device__ __forceinline__ void store_act(uint8_t * s_act, int K, int nblocks, int blk32, int off, unsigned word, bool leader, float d, float s) {
+        const int gb = blk32 >> 3, sub = blk32 & 7, hf = off >> 4;
+        *(unsigned *) (s_act + (sub & 1) * (K >> 1) + (((sub >> 1) * 2 + hf) * nblocks + gb) * 16 + (off & 15)) = word;
+        if (leader) {
+            float * ds = (float *) (s_act + K) + ((sub >> 1) * nblocks + gb) * 4 + (sub & 1) * 2;
+            ds[0] = (sub & 1) ? d * 0.0625f : d; ds[1] = s;
+        }
+    }
+    template <int NR>
+    static __device__ __forceinline__ void consume(uint32_t st, int row_stride, int bl, int gb, int lane, uint32_t act, int K, int nblocks,
+                                                   float (&acc)[GS_RW]) {
+        const int cq = lane >> 3, half = cq & 1, sh = 16 * (lane >> 4), shm = sh + 8 * half;
+        const uint32_t blk = st + bl * 144;
+#pragma unroll
+        for (int it = 0; it < 2; ++it) {
+            const int c = cq + 4 * it, pp = (lane >> 4) + 2 * it;
+            const int4 a0 = lds128(act + (c * nblocks + gb) * 16), a1 = lds128(act + (K >> 1) + (c * nblocks + gb) * 16);
+            const int4 dsr = lds128(act + K + (pp * nblocks + gb) * 16);
+            const float dA0 = __int_as_float(dsr.x), dA1 = __int_as_float(dsr.z), ssel = __int_as_float(half ? dsr.w : dsr.y);
+#pragma unroll
+            for (int r = 0; r < NR; ++r) {
+                const uint32_t base = blk + r * row_stride;
+                const int4 hdr = lds128(base);
+                const int4 q   = lds128(base + 16 + c * 16);
+                const unsigned s0 = (unsigned) hdr.y, s1 = (unsigned) hdr.z, s2 = (unsigned) hdr.w;
+                int sc0, sc1, msel;
+                if (it == 0) {
+                    sc0  = (s0 >> sh) & 63;
+                    sc1  = (s0 >> (sh + 8)) & 63;
+                    msel = (s1 >> shm) & 63;
+                } else {
+                    sc0  = ((s2 >> sh) & 0xF)        | (((s0 >> (sh + 6)) & 3) << 4);
+                    sc1  = ((s2 >> (sh + 8)) & 0xF)  | (((s0 >> (sh + 14)) & 3) << 4);
+                    msel = ((s2 >> (shm + 4)) & 0xF) | (((s1 >> (shm + 6)) & 3) << 4);
+                }
+                int i0 = __dp4a(q.x & 0x0F0F0F0F, a0.x, 0); i0 = __dp4a(q.y & 0x0F0F0F0F, a0.y, i0);
+                i0 = __dp4a(q.z & 0x0F0F0F0F, a0.z, i0);    i0 = __dp4a(q.w & 0x0F0F0F0F, a0.w, i0);
+                int i1 = dp4a_us((unsigned) q.x & 0xF0F0F0F0u, a1.x, 0); i1 = dp4a_us((unsigned) q.y & 0xF0F0F0F0u, a1.y, i1);
+                i1 = dp4a_us((unsigned) q.z & 0xF0F0F0F0u, a1.z, i1);    i1 = dp4a_us((unsigned) q.w & 0xF0F0F0F0u, a1.w, i1);
+                const float2 dm = __half22float2(*(const __half2 *) &hdr.x);
+                const float t = (float) (sc0 * i0) * dA0 + (float) (sc1 * i1) * dA1;
+                acc[r] = fmaf(dm.x, t, acc[r]);
+                acc[r] = fmaf(-dm.y, (float) msel * ssel, acc[r]);
+            }
+        }
+    }
 };
 
-// Lane -> work mapping inside one stage (a chunk of up to 8 blocks of RW rows):
-//   block b = lane & 7; iteration it in {0, 1}; c = (lane >> 3) + 4 it is the 16-byte unit of the block's qs,
-//   i.e. sub-block pair p = c >> 1 = (lane >> 4) + 2 it, half = (lane >> 3) & 1.
-// Every lane of the warp is in the same branch of get_scale_min_k4 (ggml-quants.c:703-710) for a given `it` (p < 2 for
-// it = 0, p >= 2 for it = 1), so the 6-bit scale decode is straight-line code with lane-constant shifts.
-// Shared-memory reads are conflict-free: a quarter-warp reads 8 blocks at stride 144 B = 36 words (banks 4i..4i+3).
-// The activation image is laid out in shared memory as the lanes read it:
-//   quants: plane0[c][gb] / plane1[c][gb], 16 B each -- the 16 int8 that meet the low / high nibbles of unit (gb, c);
-//   scales: ds4[p][gb] = (dA(2p), s(2p), dA(2p+1)/16, s(2p+1)) as four floats -- the /16 undoes the unshifted high
-//   nibbles (dp4a on q & 0xF0F0F0F0 yields 16 x the sum).
-template <int NR, int IT>
-static __device__ __forceinline__ void gs_q4k_unit(uint32_t blk, int cq, int sh, int shm, int half,
-                                                   const int4 & a0, const int4 & a1, const float4 & ds, float ssel,
-                                                   float (&accd)[GS_RW], float (&accm)[GS_RW]) {
-#pragma unroll
-    for (int r = 0; r < NR; ++r) {
-        const uint32_t base = blk + r * (GS_CB * 144);
-        const int4 hdr = lds128(base);
-        const int4 q   = lds128(base + 16 + (cq + 4 * IT) * 16);
-        const unsigned s0 = (unsigned) hdr.y, s1 = (unsigned) hdr.z, s2 = (unsigned) hdr.w;
-        int sc0, sc1, msel;
-        if (IT == 0) {
-            sc0  = (s0 >> sh) & 63;
-            sc1  = (s0 >> (sh + 8)) & 63;
-            msel = (s1 >> shm) & 63;
-        } else {
-            sc0  = ((s2 >> sh) & 0xF)        | (((s0 >> (sh + 6)) & 3) << 4);
-            sc1  = ((s2 >> (sh + 8)) & 0xF)  | (((s0 >> (sh + 14)) & 3) << 4);
-            msel = ((s2 >> (shm + 4)) & 0xF) | (((s1 >> (shm + 6)) & 3) << 4);
-        }
-        int i0 = __dp4a(q.x & 0x0F0F0F0F, a0.x, 0); i0 = __dp4a(q.y & 0x0F0F0F0F, a0.y, i0);
-        i0 = __dp4a(q.z & 0x0F0F0F0F, a0.z, i0);    i0 = __dp4a(q.w & 0x0F0F0F0F, a0.w, i0);
-        int i1 = dp4a_us((unsigned) q.x & 0xF0F0F0F0u, a1.x, 0); i1 = dp4a_us((unsigned) q.y & 0xF0F0F0F0u, a1.y, i1);
-        i1 = dp4a_us((unsigned) q.z & 0xF0F0F0F0u, a1.z, i1);    i1 = dp4a_us((unsigned) q.w & 0xF0F0F0F0u, a1.w, i1);
-        const float2 dm = __half22float2(*(const __half2 *) &hdr.x);
-        const float t = (float) (sc0 * i0) * ds.x + (float) (sc1 * i1) * ds.z;
-        accd[r] = fmaf(dm.x, t, accd[r]);
-        accm[r] = fmaf(dm.y, (float) msel * ssel, accm[r]);
+// ================================================ q6_K (group-SoA repack) ================================================
+// Raw q6_K blocks are 210 bytes with 2-byte aligned fields: unusable for 128-bit shared loads.  At load time
+// (b200_repack, b200_repack.cu) every aligned group of 8 blocks (1680 B) of a row is permuted in place into
+//     QL [t = (n*2+j)*2+AB][b] 16 B   ql[64 n + 32 AB + 16 j + 0..15] of block b          offset 0
+//     QH [nj = n*2+j][b]       16 B   qh[32 n + 16 j + 0..15]                              offset 1024
+//     SC [b]                   16 B   scales[0..15]                                        offset 1536
+//     D  [b]                    2 B   d                                                    offset 1664
+// so a lane (b = lane & 7, nj = lane >> 3) reads 16-byte words that are contiguous across the 8 lanes of its quarter-warp.
+// Unit (b, n, j) = 64 weights y[128 n + 32 g + 16 j + 0..15], g = 0..3 (ggml-quants.c:1762-1791), one int8 scale each:
+// sc[8 n + j + 2 g].  Activations: planes[g][nj][gb] (16 int8) and dA4[n][gb] = (dA(4n), .., dA(4n+3)).
+template <> struct gs_traits<B200_TYPE_Q6_K> {
+    static constexpr int BLOCK_BYTES = 210;
+    static __host__ __device__ size_t act_bytes(int K) { return (size_t) K + (size_t) (K >> 8) * 32; }
+    static __device__ __forceinline__ void store_act(uint8_t * s_act, int K, int nblocks, int blk32, int off, unsigned word, bool leader, float d, float s) {
+        const int gb = blk32 >> 3, sub = blk32 & 7, n = sub >> 2, g = sub & 3, hf = off >> 4;
+        *(unsigned *) (s_act + ((g * 4 + n * 2 + hf) * nblocks + gb) * 16 + (off & 15)) = word;
+        if (leader) ((float *) (s_act + K))[(n * nblocks + gb) * 4 + g] = d;
+        (void) s;
     }
-    (void) half;
+    template <int NR>
+    static __device__ __forceinline__ void consume(uint32_t st, int row_stride, int bl, int gb, int lane, uint32_t act, int K, int nblocks,
+                                                   float (&acc)[GS_RW]) {
+        const int nj = lane >> 3, n = nj >> 1, j = nj & 1;
+        int4 a[4];
+#pragma unroll
+        for (int g = 0; g < 4; ++g) a[g] = lds128(act + ((g * 4 + nj) * nblocks + gb) * 16);
+        const int4 dar = lds128(act + K + (n * nblocks + gb) * 16);
+        const float dA[4] = { __int_as_float(dar.x), __int_as_float(dar.y), __int_as_float(dar.z), __int_as_float(dar.w) };
+#pragma unroll
+        for (int r = 0; r < NR; ++r) {
+            const uint32_t G = st + r * row_stride;
+            const int4 qa = lds128(G + ((nj * 2 + 0) * 8 + bl) * 16);
+            const int4 qb = lds128(G + ((nj * 2 + 1) * 8 + bl) * 16);
+            const int4 qh = lds128(G + 1024 + (nj * 8 + bl) * 16);
+            const int2 scr = lds64(G + 1536 + bl * 16 + 8 * n);                 // scales[8 n .. 8 n + 7]
+            unsigned short dh;
+            asm volatile("ld.shared.u16 %0, [%1];" : "=h"(dh) : "r"(G + 1664 + bl * 2));
+            const float d = __half2float(__ushort_as_half(dh));
+            const int qav[4] = { qa.x, qa.y, qa.z, qa.w }, qbv[4] = { qb.x, qb.y, qb.z, qb.w }, qhv[4] = { qh.x, qh.y, qh.z, qh.w };
+            const int av[4][4] = { { a[0].x, a[0].y, a[0].z, a[0].w }, { a[1].x, a[1].y, a[1].z, a[1].w },
+                                   { a[2].x, a[2].y, a[2].z, a[2].w }, { a[3].x, a[3].y, a[3].z, a[3].w } };
+            int I[4] = { 0, 0, 0, 0 };
+#pragma unroll
+            for (int w = 0; w < 4; ++w) {
+                const int v0 = (qav[w] & 0x0F0F0F0F)        | ((qhv[w] << 4) & 0x30303030);
+                const int v1 = (qbv[w] & 0x0F0F0F0F)        | ((qhv[w] << 2) & 0x30303030);
+                const int v2 = ((qav[w] >> 4) & 0x0F0F0F0F) | (qhv[w] & 0x30303030);
+                const int v3 = ((qbv[w] >> 4) & 0x0F0F0F0F) | ((qhv[w] >> 2) & 0x30303030);
+                I[0] = __dp4a((int) __vsub4(v0, 0x20202020), av[0][w], I[0]);
+                I[1] = __dp4a((int) __vsub4(v1, 0x20202020), av[1][w], I[1]);
+                I[2] = __dp4a((int) __vsub4(v2, 0x20202020), av[2][w], I[2]);
+                I[3] = __dp4a((int) __vsub4(v3, 0x20202020), av[3][w], I[3]);
+            }
+            // sc[8 n + j + 2 g]: byte j + 2 g of the 8 loaded bytes, sign-extended
+            const unsigned lo = (unsigned) scr.x >> (8 * j), hi = (unsigned) scr.y >> (8 * j);
+            const int sc0 = (int) (signed char) (lo & 0xFF), sc1 = (int) (signed char) ((lo >> 16) & 0xFF);
+            const int sc2 = (int) (signed char) (hi & 0xFF), sc3 = (int) (signed char) ((hi >> 16) & 0xFF);
+            const float t = (float) (sc0 * I[0]) * dA[0] + (float) (sc1 * I[1]) * dA[1] + (float) (sc2 * I[2]) * dA[2] + (float) (sc3 * I[3]) * dA[3];
+            acc[r] = fmaf(d, t, acc[r]);
+        }
+    }
+};
+
+// ====================================================== the kernel ======================================================
+static __device__ __forceinline__ void gs_locate(const gs_args & p, int gr, const uint8_t * & w, float * & dst) {
+    // global row -> (segment, row): at most two compares
+    int s = 0, r = gr;
+    if (p.nseg > 1 && r >= p.seg[0].M) { r -= p.seg[0].M; s = 1; if (p.nseg > 2 && r >= p.seg[1].M) { r -= p.seg[1].M; s = 2; } }
+    w = p.seg[s].w + (size_t) r * p.seg[s].nb1;
+    dst = p.seg[s].dst + r;
 }
 
-__global__ void __launch_bounds__(GS_WARPS * 32, 2) k_gemv_stream_q4k(const gs_args p) {
-    constexpr int CHUNK_BYTES = 144 * GS_CB;
+template <int TYPE>
+__global__ void __launch_bounds__(GS_WARPS * 32, 2) k_gemv_stream(const gs_args p) {
+    using T = gs_traits<TYPE>;
+    constexpr int CHUNK_BYTES = T::BLOCK_BYTES * GS_CB;
     constexpr int STAGE_BYTES = CHUNK_BYTES * GS_RW;
     extern __shared__ __align__(128) uint8_t smem[];
-    // layout: [GS_WARPS][GS_STAGES][STAGE_BYTES] rings | quant planes [K] | ds4 [K/64] float4 | mbarriers
+    // layout: [GS_WARPS][GS_STAGES][STAGE_BYTES] rings | activation image (T::act_bytes) | mbarriers
     const int nblocks = p.K >> 8;
-    uint8_t *  s_aq  = smem + GS_WARPS * GS_STAGES * STAGE_BYTES;
-    float4 *   s_ds  = (float4 *) (s_aq + p.K);
-    uint64_t * s_bar = (uint64_t *) (s_ds + nblocks * 4);
+    uint8_t *  s_act = smem + GS_WARPS * GS_STAGES * STAGE_BYTES;
+    uint64_t * s_bar = (uint64_t *) (s_act + T::act_bytes(p.K));
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t ring = smem_u32(smem + warp * GS_STAGES * STAGE_BYTES);
     const uint32_t bar0 = smem_u32(s_bar + warp * GS_STAGES);
 
-    // this warp's rows: an even split of [0, M) over every warp of the grid
+    // this warp's rows: an even split of [0, Mtot) over every warp of the grid
     const int gw = blockIdx.x * GS_WARPS + warp, nw = gridDim.x * GS_WARPS;
-    const int r_begin = (int) ((int64_t) p.M * gw / nw), r_end = (int) ((int64_t) p.M * (gw + 1) / nw);
+    const int r_begin = (int) ((int64_t) p.Mtot * gw / nw), r_end = (int) ((int64_t) p.Mtot * (gw + 1) / nw);
     const int rows = r_end - r_begin;
     const int nchunks = (nblocks + GS_CB - 1) / GS_CB;
     const int npairs = (rows + GS_RW - 1) / GS_RW;
@@ -98,70 +192,84 @@ __global__ void __launch_bounds__(GS_WARPS * 32, 2) k_gemv_stream_q4k(const gs_a
         mbar_fence_init();
     }
     __syncwarp();
+    // let the next kernel of the stream start its own prologue (PDL); nothing it may touch is ours
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
     const uint64_t policy = l2_policy_evict_first();
-    const uint8_t * wbase = p.w + (size_t) r_begin * p.w_nb1;
-    // producer cursor (uniform across the warp; only lane 0 issues)
-    int prp = 0, pkc = 0;
+    int prp = 0, pkc = 0;                                                 // producer cursor (warp-uniform; lane 0 issues)
     auto issue = [&](int stage) {
         const int cb = min(GS_CB, nblocks - pkc * GS_CB);
         const int nr = min(GS_RW, rows - prp * GS_RW);
         if (lane == 0) {
-            const uint32_t bytes = (uint32_t) cb * 144, bar = bar0 + 8 * stage;
+            const uint32_t bytes = (uint32_t) cb * T::BLOCK_BYTES, bar = bar0 + 8 * stage;
             mbar_arrive_expect_tx(bar, bytes * nr);
-            const uint8_t * src = wbase + (size_t) (prp * GS_RW) * p.w_nb1 + (size_t) pkc * CHUNK_BYTES;
-            bulk_g2s_hint(ring + stage * STAGE_BYTES, src, bytes, bar, policy);
-            if (nr > 1) bulk_g2s_hint(ring + stage * STAGE_BYTES + CHUNK_BYTES, src + p.w_nb1, bytes, bar, policy);
+            for (int r = 0; r < nr; ++r) {
+                const uint8_t * w; float * dst;
+                gs_locate(p, r_begin + prp * GS_RW + r, w, dst);
+                bulk_g2s_hint(ring + stage * STAGE_BYTES + r * CHUNK_BYTES, w + (size_t) pkc * CHUNK_BYTES, bytes, bar, policy);
+            }
         }
         if (++pkc == nchunks) { pkc = 0; ++prp; }
     };
     const int npro = min(nitems, GS_STAGES);
-    for (int i = 0; i < npro; ++i) issue(i);
+    for (int i = 0; i < npro; ++i) issue(i);                              // weights do not depend on the previous kernel
 
-    // activation image -> shared memory in lane order (overlaps the first bulk copies)
+    // src1 is produced by the previous kernel in the stream: wait for it (and its memory) before the first read
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+
+    // quantize the activation column to q8_1 straight into shared memory, in lane order.  Same arithmetic as
+    // q8_1_block<B200_Q8_1_X86> (bit-exact with the reference), but 128-bit loads: a lane holds 4 consecutive values, the
+    // 8 lanes of a group hold one 32-value block, and up to GS_QB independent loads per lane are in flight at once.
     {
-        const int4 * src = (const int4 *) p.aq;
-        for (int j = threadIdx.x; j < (p.K >> 4); j += blockDim.x) {       // j: 16-byte word of the natural image
-            const int blk32 = j >> 1, hf = j & 1, gb = blk32 >> 3, sub = blk32 & 7;
-            const int c = (sub >> 1) * 2 + hf;
-            *(int4 *) (s_aq + (sub & 1) * (p.K >> 1) + (c * nblocks + gb) * 16) = src[j];
-        }
-        for (int j = threadIdx.x; j < (p.K >> 6); j += blockDim.x) {       // j: pair of q8_1 blocks
-            const int gb = j >> 2, pp = j & 3;
-            const float2 e = __half22float2(p.ads[2 * j]), o = __half22float2(p.ads[2 * j + 1]);
-            s_ds[pp * nblocks + gb] = make_float4(e.x, e.y, o.x * 0.0625f, o.y);
+        constexpr int GS_QB = 8;
+        const float4 * x4 = (const float4 *) p.x;
+        const int nvec = p.K >> 7;                                        // 128-float chunks = 4 q8_1 blocks
+        for (int c0 = warp; c0 < nvec; c0 += GS_WARPS * GS_QB) {
+            float4 v[GS_QB];
+#pragma unroll
+            for (int i = 0; i < GS_QB; ++i) { const int c = c0 + i * GS_WARPS; v[i] = c < nvec ? x4[c * 32 + lane] : make_float4(0.f, 0.f, 0.f, 0.f); }
+#pragma unroll
+            for (int i = 0; i < GS_QB; ++i) {
+                const int c = c0 + i * GS_WARPS;
+                if (c >= nvec) break;                                     // warp-uniform
+                float amax = fmaxf(fmaxf(fabsf(v[i].x), fabsf(v[i].y)), fmaxf(fabsf(v[i].z), fabsf(v[i].w)));
+                amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+                amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+                amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 4));
+                const float d  = __fdiv_rn(amax, 127.0f);
+                const float id = amax != 0.0f ? __fdiv_rn(127.0f, amax) : 0.0f;
+                const int q0 = cvt_x86(rintf(__fmul_rn(v[i].x, id))), q1 = cvt_x86(rintf(__fmul_rn(v[i].y, id)));
+                const int q2 = cvt_x86(rintf(__fmul_rn(v[i].z, id))), q3 = cvt_x86(rintf(__fmul_rn(v[i].w, id)));
+                unsigned usum = (unsigned) q0 + (unsigned) q1 + (unsigned) q2 + (unsigned) q3;   // int32 lanes summed before saturation
+                usum += __shfl_xor_sync(0xffffffffu, usum, 1);
+                usum += __shfl_xor_sync(0xffffffffu, usum, 2);
+                usum += __shfl_xor_sync(0xffffffffu, usum, 4);
+                const unsigned word = ((unsigned) max(-128, min(127, q0)) & 0xffu)        | (((unsigned) max(-128, min(127, q1)) & 0xffu) << 8) |
+                                      (((unsigned) max(-128, min(127, q2)) & 0xffu) << 16) | (((unsigned) max(-128, min(127, q3)) & 0xffu) << 24);
+                // d and s take the fp16 round trip they would take through block_q8_1
+                T::store_act(s_act, p.K, nblocks, c * 4 + (lane >> 3), 4 * (lane & 7), word, (lane & 7) == 0,
+                             __half2float(__float2half_rn(d)), __half2float(__float2half_rn(__fmul_rn(d, (float) (int) usum))));
+            }
         }
     }
     __syncthreads();
 
-    const int bl = lane & 7, cq = lane >> 3, half = cq & 1;
-    const int sh = 16 * (lane >> 4), shm = sh + 8 * half;
-    const uint32_t aq0 = smem_u32(s_aq), aq1 = aq0 + (p.K >> 1), ads = smem_u32(s_ds);
-    float accd[GS_RW], accm[GS_RW];
+    const int bl = lane & 7;
+    const uint32_t act = smem_u32(s_act);
+    float acc[GS_RW];
 #pragma unroll
-    for (int r = 0; r < GS_RW; ++r) accd[r] = accm[r] = 0.0f;
+    for (int r = 0; r < GS_RW; ++r) acc[r] = 0.0f;
 
     int stage = 0, phase = 0, rp = 0, kc = 0;
     for (int item = 0; item < nitems; ++item) {
         const int cb = min(GS_CB, nblocks - kc * GS_CB);
         const int nr = min(GS_RW, rows - rp * GS_RW);
         mbar_wait(bar0 + 8 * stage, (uint32_t) phase);
-
         if (bl < cb) {
+            const uint32_t st = ring + stage * STAGE_BYTES;
             const int gb = kc * GS_CB + bl;
-            const uint32_t blk = ring + stage * STAGE_BYTES + bl * 144;
-#pragma unroll
-            for (int it = 0; it < 2; ++it) {
-                const int c = cq + 4 * it, pp = (lane >> 4) + 2 * it;
-                const int4 a0 = lds128(aq0 + (c * nblocks + gb) * 16), a1 = lds128(aq1 + (c * nblocks + gb) * 16);
-                const int4 dsr = lds128(ads + (pp * nblocks + gb) * 16);
-                const float4 ds = make_float4(__int_as_float(dsr.x), __int_as_float(dsr.y), __int_as_float(dsr.z), __int_as_float(dsr.w));
-                const float ssel = half ? ds.w : ds.y;
-                if (nr == GS_RW) { if (it == 0) gs_q4k_unit<GS_RW, 0>(blk, cq, sh, shm, half, a0, a1, ds, ssel, accd, accm);
-                                   else         gs_q4k_unit<GS_RW, 1>(blk, cq, sh, shm, half, a0, a1, ds, ssel, accd, accm); }
-                else             { if (it == 0) gs_q4k_unit<1, 0>(blk, cq, sh, shm, half, a0, a1, ds, ssel, accd, accm);
-                                   else         gs_q4k_unit<1, 1>(blk, cq, sh, shm, half, a0, a1, ds, ssel, accd, accm); }
-            }
+            if (nr == GS_RW) T::template consume<GS_RW>(st, CHUNK_BYTES, bl, gb, lane, act, p.K, nblocks, acc);
+            else             T::template consume<1>(st, CHUNK_BYTES, bl, gb, lane, act, p.K, nblocks, acc);
         }
         __syncwarp();                                                     // every lane is done reading this stage
         if (item + GS_STAGES < nitems) issue(stage);
@@ -169,9 +277,13 @@ __global__ void __launch_bounds__(GS_WARPS * 32, 2) k_gemv_stream_q4k(const gs_a
         if (kc == nchunks - 1) {
 #pragma unroll
             for (int r = 0; r < GS_RW; ++r) {
-                const float v = warp_sum(accd[r] - accm[r]);
-                if (lane == 0 && r < nr) p.dst[r_begin + rp * GS_RW + r] = v;
-                accd[r] = accm[r] = 0.0f;
+                const float v = warp_sum(acc[r]);
+                if (lane == 0 && r < nr) {
+                    const uint8_t * w; float * dst;
+                    gs_locate(p, r_begin + rp * GS_RW + r, w, dst);
+                    *dst = v;
+                }
+                acc[r] = 0.0f;
             }
             kc = 0; ++rp;
         } else ++kc;
@@ -179,32 +291,55 @@ __global__ void __launch_bounds__(GS_WARPS * 32, 2) k_gemv_stream_q4k(const gs_a
     }
 }
 
-static size_t gs_smem_bytes(int K) {
-    return (size_t) GS_WARPS * GS_STAGES * 144 * GS_CB * GS_RW + K + (size_t) (K >> 8) * 4 * 16 + GS_WARPS * GS_STAGES * 8;
+template <int TYPE> static size_t gs_smem_bytes(int K) {
+    return (size_t) GS_WARPS * GS_STAGES * gs_traits<TYPE>::BLOCK_BYTES * GS_CB * GS_RW + gs_traits<TYPE>::act_bytes(K) + GS_WARPS * GS_STAGES * 8;
 }
+#define GS_SMEM_MAX (112 * 1024)
 
-// true when the streaming kernel can take this MUL_MAT (one activation column, 2-D weight, aligned rows)
-bool b200_gemv_stream_supported(const b200_tensor * w, int64_t ne11, int64_t ne12, int64_t ne13) {
-    if (ne11 != 1 || ne12 != 1 || ne13 != 1 || w->ne[2] != 1 || w->ne[3] != 1) return false;
-    if (w->type != B200_TYPE_Q4_K) return false;
-    if (((uintptr_t) w->data & 15) || (w->nb[1] & 15) || w->ne[0] % 256 != 0 || w->ne[0] > 32768 || w->ne[1] > (1 << 30)) return false;
-    return gs_smem_bytes((int) w->ne[0]) <= 110 * 1024;
-}
-
-int b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * w, const void * image, float * dst) {
-    gs_args p;
+// true when the streaming kernel can take a MUL_MAT of this weight with ONE contiguous f32 activation column
+bool b200_gemv_stream_supported(const b200_tensor * w, const b200_tensor * x) {
+    if (x->ne[1] != 1 || x->ne[2] != 1 || x->ne[3] != 1 || w->ne[2] != 1 || w->ne[3] != 1) return false;
+    if (x->type != B200_TYPE_F32 || x->nb[0] != 4 || ((uintptr_t) x->data & 15)) return false;
+    if (((uintptr_t) w->data & 15) || (w->nb[1] & 15) || w->ne[0] % 256 != 0 || w->ne[0] > 32768 || w->ne[1] > (1 << 28)) return false;
     const int K = (int) w->ne[0];
-    p.w = (const uint8_t *) w->data; p.w_nb1 = w->nb[1];
-    p.aq = (const int8_t *) image; p.ads = (const __half2 *) ((const int8_t *) image + K);
-    p.dst = dst; p.M = (int) w->ne[1]; p.K = K;
-    const size_t smem = gs_smem_bytes(K);
-    if (!ctx->attr_done[0]) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(k_gemv_stream_q4k, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024));
-        ctx->attr_done[0] = 1;
+    if (w->type == B200_TYPE_Q4_K) return !(w->flags & B200_TENSOR_REPACKED) && gs_smem_bytes<B200_TYPE_Q4_K>(K) <= GS_SMEM_MAX;
+    if (w->type == B200_TYPE_Q6_K) return (w->flags & B200_TENSOR_REPACKED) && K % 2048 == 0 && gs_smem_bytes<B200_TYPE_Q6_K>(K) <= GS_SMEM_MAX;
+    return false;
+}
+
+template <int TYPE>
+static int gs_launch(b200_ctx * ctx, const gs_args & p, int attr_slot) {
+    const size_t smem = gs_smem_bytes<TYPE>(p.K);
+    if (!ctx->attr_done[attr_slot]) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(k_gemv_stream<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, GS_SMEM_MAX));
+        ctx->attr_done[attr_slot] = 1;
     }
-    // persistent-style grid: two CTAs per SM, rows split evenly over all warps; fewer CTAs when there are few rows
-    const int64_t want = (p.M + GS_WARPS - 1) / GS_WARPS;
-    const unsigned grid = (unsigned) max((int64_t) 1, min(want, (int64_t) ctx->sm_count * 2));
-    B200_LAUNCH(ctx, B200_K_GEMV, k_gemv_stream_q4k<<<grid, GS_WARPS * 32, smem, ctx->stream>>>(p));
+    // persistent-size grid: two CTAs per SM, rows split evenly over all warps; fewer CTAs when there are few rows
+    const int64_t want = (p.Mtot + GS_WARPS - 1) / GS_WARPS;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned) max((int64_t) 1, min(want, (int64_t) ctx->sm_count * 2)));
+    cfg.blockDim = dim3(GS_WARPS * 32);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = ctx->pdl ? 1 : 0;
+    B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_gemv_stream<TYPE>, p));
     return B200_OK;
+}
+
+// n <= 3 weights of the same type sharing the activation column x; dst[i] is the f32 column of weight i
+int b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, float * const * dst) {
+    gs_args p;
+    p.nseg = n; p.Mtot = 0; p.x = (const float *) x->data; p.K = (int) w[0]->ne[0];
+    for (int i = 0; i < n; ++i) {
+        p.seg[i].w = (const uint8_t *) w[i]->data; p.seg[i].nb1 = w[i]->nb[1]; p.seg[i].dst = dst[i]; p.seg[i].M = (int) w[i]->ne[1];
+        p.Mtot += p.seg[i].M;
+    }
+    for (int i = n; i < GS_MAXSEG; ++i) { p.seg[i].w = nullptr; p.seg[i].nb1 = 0; p.seg[i].dst = nullptr; p.seg[i].M = 0; }
+    if (w[0]->type == B200_TYPE_Q4_K) return gs_launch<B200_TYPE_Q4_K>(ctx, p, 0);
+    if (w[0]->type == B200_TYPE_Q6_K) return gs_launch<B200_TYPE_Q6_K>(ctx, p, 1);
+    b200_set_error("gemv_stream: unsupported type %d", w[0]->type);
+    return B200_ERR_UNSUPPORTED;
 }

@@ -11,32 +11,6 @@
 // Bytes: reads 128 B, writes 36 B per block -> HBM/L2 bound, negligible next to the GEMV it feeds.
 #include "b200_common.cuh"
 
-// float -> int32 the way x86 cvtps2dq / cvttss2si do it: out-of-range (a denormal amax makes id = inf) and NaN
-// give the "integer indefinite" 0x80000000 instead of CUDA's saturation.
-static __device__ __forceinline__ int cvt_x86(float r) { return fabsf(r) < 2147483648.0f ? __float2int_rn(r) : (int) 0x80000000u; }
-
-// one warp, one block: returns this lane's quant, the block scale d (fp32) and the integer sum of quants
-template <int VARIANT>
-static __device__ __forceinline__ void q8_1_block(float v, int & q, float & d, int & isum) {
-    const float amax = warp_max(fabsf(v));
-    d = __fdiv_rn(amax, 127.0f);
-    unsigned usum;
-    if (VARIANT == B200_Q8_1_X86) {
-        const float id  = amax != 0.0f ? __fdiv_rn(127.0f, amax) : 0.0f;
-        const int   q32 = cvt_x86(rintf(__fmul_rn(v, id)));      // round-half-even, as _mm256_round_ps(NEAREST) + cvtps_epi32
-        q    = max(-128, min(127, q32));                         // packs_epi32/epi16 saturate
-        usum = (unsigned) q32;                                   // ... but the AVX2 body sums the int32 lanes before packing
-    } else {
-        const float id  = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
-        const int   q32 = cvt_x86(roundf(__fmul_rn(v, id)));     // half away from zero, as roundf(); then C's (int8_t) cast
-        q    = (int) (int8_t) (q32 & 0xff);
-        usum = (unsigned) q;
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) usum += __shfl_xor_sync(0xffffffffu, usum, o);
-    isum = (int) usum;
-}
-
 template <int VARIANT>
 __global__ void __launch_bounds__(256) k_quantize_q8_1(const float * __restrict__ x, size_t x_row_stride,
                                                       blk_q8_1 * __restrict__ y, int64_t nblk_row, int64_t nblk_total) {

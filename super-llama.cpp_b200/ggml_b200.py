@@ -52,7 +52,8 @@ def lib():
         "b200_malloc": (vp, [vp, sz]), "b200_free": (i, [vp, vp]), "b200_host_alloc": (vp, [sz]), "b200_host_free": (i, [vp]),
         "b200_memcpy_h2d": (i, [vp, vp, vp, sz]), "b200_memcpy_d2h": (i, [vp, vp, vp, sz]), "b200_memset": (i, [vp, vp, i, sz]),
         "b200_quantize_q8_1": (i, [vp, vp, sz, vp, i64, i64, i]),
-        "b200_mul_mat": (i, [vp, tp, tp, tp]), "b200_mul_mat_id": (i, [vp, tp, tp, tp, tp]),
+        "b200_mul_mat": (i, [vp, tp, tp, tp]), "b200_mul_mat_multi": (i, [vp, C.POINTER(tp), i, tp, C.POINTER(tp)]),
+        "b200_repack_supported": (i, [i, i64]), "b200_repack": (i, [vp, i, vp, i64, i64, sz]), "b200_unrepack": (i, [vp, i, vp, i64, i64, sz]), "b200_mul_mat_id": (i, [vp, tp, tp, tp, tp]),
         "b200_flash_attn_ext": (i, [vp, tp, tp, tp, tp, tp, tp, f, f, f]),
         "b200_ctx_launch_count_kind": (C.c_uint64, [vp, i]), "b200_ctx_profile": (i, [vp, i]),
         "b200_ctx_profile_get": (i, [vp, i, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]),
@@ -93,6 +94,7 @@ class DeviceTensor:
         self.ctx, self.type, self.ne = ctx, t, ne
         self.nb = list(nb) if nb is not None else contiguous_strides(t, ne)
         self.owner = owner
+        self.flags = 0               # B200_TENSOR_REPACKED after Context.repack()
         if ptr is None:
             self.nbytes = self.span()
             self.ptr = ctx.malloc(self.nbytes)
@@ -112,13 +114,15 @@ class DeviceTensor:
 
     def c(self):
         t = _Tensor()
-        t.data, t.type, t.flags = self.ptr, self.type, 0
+        t.data, t.type, t.flags = self.ptr, self.type, self.flags
         for d in range(4):
             t.ne[d], t.nb[d] = self.ne[d], self.nb[d]
         return t
 
     def view(self, ne, nb, offset=0):
-        return DeviceTensor(self.ctx, self.type, ne, nb, ptr=self.ptr + offset, owner=self.owner or self)
+        v = DeviceTensor(self.ctx, self.type, ne, nb, ptr=self.ptr + offset, owner=self.owner or self)
+        v.flags = self.flags         # a whole-row view of a repacked weight is still repacked
+        return v
 
     def free(self):
         if self._owned and self.ptr:
@@ -259,6 +263,27 @@ class Context:
         cw, cx, cd = w.c(), x.c(), dst.c()
         _check(lib().b200_mul_mat(self.h, C.byref(cw), C.byref(cx), C.byref(cd)), "mul_mat")
 
+    def mul_mat_multi(self, ws, x, dsts):
+        """n MUL_MATs sharing x (wq/wk/wv, gate/up): one launch when the streaming GEMV can take them"""
+        n = len(ws)
+        cw = [w.c() for w in ws]; cd = [d.c() for d in dsts]; cx = x.c()
+        tp = C.POINTER(_Tensor)
+        aw = (tp * n)(*[C.pointer(t) for t in cw]); ad = (tp * n)(*[C.pointer(t) for t in cd])
+        _check(lib().b200_mul_mat_multi(self.h, aw, n, C.byref(cx), ad), "mul_mat_multi")
+
+    def repack(self, w):
+        """load-time repack of a weight tensor in place (no-op for types consumed in GGUF layout); returns w"""
+        if w.flags == 0 and lib().b200_repack_supported(w.type, w.ne[0]):
+            _check(lib().b200_repack(self.h, w.type, w.ptr, w.ne[0], w.ne[1] * w.ne[2] * w.ne[3], w.nb[1]), "repack")
+            w.flags = 1
+        return w
+
+    def unrepack(self, w):
+        if w.flags == 1:
+            _check(lib().b200_unrepack(self.h, w.type, w.ptr, w.ne[0], w.ne[1] * w.ne[2] * w.ne[3], w.nb[1]), "unrepack")
+            w.flags = 0
+        return w
+
     def mul_mat_id(self, as_, b, ids, dst):
         ca, cb, ci, cd = as_.c(), b.c(), ids.c(), dst.c()
         _check(lib().b200_mul_mat_id(self.h, C.byref(ca), C.byref(cb), C.byref(ci), C.byref(cd)), "mul_mat_id")
@@ -281,8 +306,10 @@ class Context:
         self.quantize_q8_1(dx.ptr, dy.ptr, k, nrows, variant=variant)
         return self.download(dy, np.uint8)
 
-    def mul_mat_host(self, t, w, K, M, x, N, ne02=1, ne03=1, ne12=1, ne13=1):
+    def mul_mat_host(self, t, w, K, M, x, N, ne02=1, ne03=1, ne12=1, ne13=1, repack=False):
         dw = self.upload(t, [K, M, ne02, ne03], w)
+        if repack:
+            self.repack(dw)
         dx = self.upload(F32, [K, N, ne12, ne13], np.ascontiguousarray(x, dtype=np.float32))
         dd = self.empty(F32, [M, N, ne12, ne13])
         self.mul_mat(dw, dx, dd)

@@ -162,26 +162,71 @@ def test_mul_mat_decode_ragged_rows(ctx, orc, t, M, K):
     assert _check_mm(orc, got, t, w, K, M, x, 1) < 1e-9
 
 
+@pytest.mark.parametrize("K,M", [(2048, 67), (4096, 131), (14336, 64)])
+def test_repack_q6_K_roundtrip_and_parity(ctx, B, orc, K, M):
+    """load-time repack (b200_repack): in place, exactly invertible, and every MUL_MAT path reads the repacked layout"""
+    rng = np.random.default_rng(K + M)
+    w = O.random_blocks(rng, O.Q6_K, K, M)
+    dw = ctx.upload(B.Q6_K, [K, M], w)
+    ctx.repack(dw)
+    assert dw.flags == 1
+    packed = ctx.download(dw, np.uint8)
+    assert not np.array_equal(packed, w) and np.array_equal(np.sort(packed.reshape(M, -1), axis=1), np.sort(w.reshape(M, -1), axis=1))
+    for n in (1, 3, 12):                                         # streaming GEMV, column-blocked GEMV, prefill path
+        x = rng.standard_normal((n, K)).astype(np.float32)
+        dx = ctx.upload(B.F32, [K, n], x); dd = ctx.empty(B.F32, [M, n])
+        ctx.mul_mat(dw, dx, dd)
+        got = ctx.download(dd).reshape(1, 1, n, M)
+        assert O.nmse(orc.mul_mat(O.Q6_K, w, K, M, x, n, act=O.ACT_CPU), got) < NMSE_HARNESS
+        if n <= 8:
+            assert O.nmse(orc.mul_mat(O.Q6_K, w, K, M, x, n, act=O.ACT_Q8_1), got) < 1e-9
+    ctx.unrepack(dw)
+    assert np.array_equal(ctx.download(dw, np.uint8), w)
+    assert B.lib().b200_repack_supported(B.Q6_K, 256) == 0 and B.lib().b200_repack_supported(B.Q4_K, 4096) == 0
+
+
+@pytest.mark.parametrize("t", [O.Q4_K, O.Q6_K])
+def test_mul_mat_multi_shared_src1(ctx, B, orc, t):
+    """wq/wk/wv in one launch (b200_mul_mat_multi): identical to three separate MUL_MATs"""
+    rng = np.random.default_rng(5 + t)
+    K, Ms = 4096, (4096, 1024, 1027)
+    ws = [O.random_blocks(rng, t, K, M) for M in Ms]
+    x = rng.standard_normal((1, K)).astype(np.float32)
+    dws = [ctx.repack(ctx.upload(t, [K, M], w)) for w, M in zip(ws, Ms)]
+    dx = ctx.upload(B.F32, [K, 1], x)
+    dds = [ctx.empty(B.F32, [M, 1]) for M in Ms]
+    n0 = ctx.launches
+    ctx.mul_mat_multi(dws, dx, dds)
+    assert ctx.launches - n0 == 1                                   # one fused launch, no separate quantize
+    for w, M, dd in zip(ws, Ms, dds):
+        assert O.nmse(orc.mul_mat(t, w, K, M, x, 1, act=O.ACT_Q8_1), ctx.download(dd)) < 1e-9
+    # a mixed-type group falls back to per-tensor calls with the same results
+    wq8 = O.random_blocks(rng, O.Q8_0, K, 64)
+    dq8 = ctx.upload(B.Q8_0, [K, 64], wq8); d8 = ctx.empty(B.F32, [64, 1])
+    ctx.mul_mat_multi([dws[0], dq8], dx, [dds[0], d8])
+    assert O.nmse(orc.mul_mat(O.Q8_0, wq8, K, 64, x, 1, act=O.ACT_Q8_1), ctx.download(d8)) < 1e-9
+
+
 def test_mul_mat_shared_activation_cache(ctx, B, orc):
     """wq/wk/wv-style reuse of one activation tensor, then an overwrite of it through the API: the cached q8_1 image
     must be dropped (b200_ctx_invalidate semantics, include/ggml-b200.h)"""
     rng = np.random.default_rng(99)
     K, M = 1024, 64
-    w1, w2 = O.random_blocks(rng, O.Q4_K, K, M), O.random_blocks(rng, O.Q4_K, K, M)
+    w1, w2 = O.random_blocks(rng, O.Q8_0, K, M), O.random_blocks(rng, O.Q8_0, K, M)
     x1 = rng.standard_normal((1, K)).astype(np.float32); x2 = rng.standard_normal((1, K)).astype(np.float32)
-    dw1, dw2 = ctx.upload(B.Q4_K, [K, M], w1), ctx.upload(B.Q4_K, [K, M], w2)
+    dw1, dw2 = ctx.upload(B.Q8_0, [K, M], w1), ctx.upload(B.Q8_0, [K, M], w2)
     dx = ctx.upload(B.F32, [K, 1], x1); d1, d2 = ctx.empty(B.F32, [M, 1]), ctx.empty(B.F32, [M, 1])
     q0 = ctx.launches_by_kind()["quantize_q8_1"]
     ctx.mul_mat(dw1, dx, d1); ctx.mul_mat(dw2, dx, d2)
     assert ctx.launches_by_kind()["quantize_q8_1"] == q0 + 1          # quantized once for both
-    assert O.nmse(orc.mul_mat(O.Q4_K, w2, K, M, x1, 1, act=O.ACT_Q8_1), ctx.download(d2)) < 1e-9
+    assert O.nmse(orc.mul_mat(O.Q8_0, w2, K, M, x1, 1, act=O.ACT_Q8_1), ctx.download(d2)) < 1e-9
     ctx.h2d(dx.ptr, x2)                                               # overwrite the activations
     ctx.mul_mat(dw1, dx, d1)
-    assert O.nmse(orc.mul_mat(O.Q4_K, w1, K, M, x2, 1, act=O.ACT_Q8_1), ctx.download(d1)) < 1e-9
+    assert O.nmse(orc.mul_mat(O.Q8_0, w1, K, M, x2, 1, act=O.ACT_Q8_1), ctx.download(d1)) < 1e-9
     ctx.mul_mat(dw2, dx, dx.view([M, 1], [4, M * 4, M * 4, M * 4]))   # dst aliases the cached source: must invalidate
     ctx.mul_mat(dw1, dx, d1)
     x3 = ctx.download(dx).reshape(1, K)
-    assert O.nmse(orc.mul_mat(O.Q4_K, w1, K, M, x3, 1, act=O.ACT_Q8_1), ctx.download(d1)) < 1e-9
+    assert O.nmse(orc.mul_mat(O.Q8_0, w1, K, M, x3, 1, act=O.ACT_Q8_1), ctx.download(d1)) < 1e-9
 
 
 @pytest.mark.parametrize("t", [O.Q4_0, O.Q4_K, O.Q8_0, O.Q6_K])
