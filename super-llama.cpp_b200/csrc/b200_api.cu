@@ -228,7 +228,9 @@ extern "C" int b200_mul_mat(b200_ctx * ctx, const b200_tensor * w, const b200_te
         if (x->ne[1] > B200_GEMV_MAX_COLS && b200_gemm_supported(w, x)) rc = b200_launch_gemm_q(ctx, w, x, dst);
         else if (q8_1_variant_env() == B200_Q8_1_X86 && b200_gemv_stream_supported(w, x)) {
             float * d = (float *) dst->data;
-            rc = b200_launch_gemv_stream(ctx, &w, 1, x, &d);            // fused quantize + TMA-streamed GEMV
+            const void * image = nullptr;
+            if (w->ne[0] > B200_GEMV_FUSED_QUANT_MAX_K) { image = quantized_activations(ctx, x, B200_Q8_1_X86, &rc); if (!image) return rc; }
+            rc = b200_launch_gemv_stream(ctx, &w, 1, x, image, &d);      // TMA-streamed GEMV, q8_1 quantization fused for small K
         } else {
             const void * image = quantized_activations(ctx, x, q8_1_variant_env(), &rc);
             if (!image) return rc;
@@ -257,7 +259,10 @@ extern "C" int b200_mul_mat_multi(b200_ctx * ctx, const b200_tensor * const * w,
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
     float * d[3];
     for (int i = 0; i < n; ++i) d[i] = (float *) dst[i]->data;
-    const int rc = b200_launch_gemv_stream(ctx, w, n, x, d);
+    int rc;
+    const void * image = nullptr;
+    if (w[0]->ne[0] > B200_GEMV_FUSED_QUANT_MAX_K) { image = quantized_activations(ctx, x, B200_Q8_1_X86, &rc); if (!image) return rc; }
+    rc = b200_launch_gemv_stream(ctx, w, n, x, image, d);
     for (int i = 0; i < n; ++i) b200_note_write(ctx, dst[i]->data, b200_tensor_span(dst[i]));
     return rc;
 }
@@ -303,7 +308,10 @@ extern "C" int b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const 
         return B200_ERR_UNSUPPORTED;
     }
     if (mask && (mask->ne[0] < k->ne[1] || mask->ne[1] < q->ne[1])) { b200_set_error("flash_attn_ext: mask too small"); return B200_ERR_INVALID; }
-    const int rc = b200_launch_fattn_vec(ctx, q, k, v, mask, sinks, dst, scale, max_bias, logit_softcap);
+    static const int no_dec = getenv("GGML_B200_FATTN_VEC") != nullptr;
+    const int rc = (!no_dec && b200_fattn_dec_supported(q, k, v))
+        ? b200_launch_fattn_dec(ctx, q, k, v, mask, sinks, dst, scale, max_bias, logit_softcap)
+        : b200_launch_fattn_vec(ctx, q, k, v, mask, sinks, dst, scale, max_bias, logit_softcap);
     b200_note_write(ctx, dst->data, b200_tensor_span(dst));
     return rc;
 }

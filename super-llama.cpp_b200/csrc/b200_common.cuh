@@ -152,8 +152,13 @@ int b200_launch_gemv_id_q(b200_ctx * ctx, const b200_tensor * as, const void * i
 int b200_launch_fattn_vec(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v,
                           const b200_tensor * mask, const b200_tensor * sinks, b200_tensor * dst,
                           float scale, float max_bias, float softcap);
+bool b200_fattn_dec_supported(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v);
+int  b200_launch_fattn_dec(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v,
+                           const b200_tensor * mask, const b200_tensor * sinks, b200_tensor * dst,
+                           float scale, float max_bias, float softcap);
 bool b200_gemv_stream_supported(const b200_tensor * w, const b200_tensor * x);
-int  b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, float * const * dst);
+int  b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, const void * image, float * const * dst);
+#define B200_GEMV_FUSED_QUANT_MAX_K 8192    // above this, one quantize launch + image beats one quantization per CTA
 #define B200_GEMV_MAX_COLS 8
 bool b200_gemm_supported(const b200_tensor * w, const b200_tensor * x);
 int  b200_launch_gemm_q(b200_ctx * ctx, const b200_tensor * w, const b200_tensor * x, b200_tensor * dst);

@@ -19,15 +19,21 @@
 //    previous kernel) run under the previous kernel's tail; griddepcontrol.wait guards the first read of src1.
 #include "b200_common.cuh"
 #include "b200_ptx.cuh"
+#include <stdlib.h>
 
-#define GS_WARPS  8
-#define GS_STAGES 4
+// Two launch shapes (measured, profiles/r1_gemv_*): WIDE = 2 CTAs x 8 warps per SM with deep rings for matrices that
+// outlast the rings (best steady-state bandwidth); LEAN = 1 CTA x 12 warps per SM (<= 113 KB smem, <= 85 regs) so that this
+// kernel and the PDL-launched next one co-reside on an SM and the next matmul's weights stream in while this one computes.
 #define GS_RW     2       // rows per warp per stage
 #define GS_CB     8       // 256-weight blocks per row-chunk
 #define GS_MAXSEG 3
 
 struct gs_seg { const uint8_t * w; size_t nb1; float * dst; int M; };
-struct gs_args { gs_seg seg[GS_MAXSEG]; int nseg; int Mtot; const float * x; int K; };
+struct gs_args {
+    gs_seg seg[GS_MAXSEG]; int nseg; int Mtot; int K;
+    const float * x;                         // f32 activation column: quantized in-kernel when aq == NULL
+    const int8_t * aq; const __half2 * ads;  // or a q8_1 image made by k_quantize_q8_1_soa (natural order): [K] quants, [K/32] (d, s)
+};
 
 template <int TYPE> struct gs_traits;
 
@@ -42,6 +48,7 @@ template <int TYPE> struct gs_traits;
 // nibbles (dp4a on q & 0xF0F0F0F0 gives 16 x the sum).
 template <> struct gs_traits<B200_TYPE_Q4_K> {
     static constexpr int BLOCK_BYTES = 144;
+    static __host__ __device__ constexpr int stages(bool wide) { return wide ? 4 : 3; }
     static __host__ __device__ size_t act_bytes(int K) { return (size_t) K + (size_t) (K >> 8) * 64; }
     // 4 consecutive quants (bytes off..off+3 of q8_1 block blk32) packed in `word`; the group leader also stores (d, s)
     static __device__ __forceinline__ void store_act(uint8_t * s_act, int K, int nblocks, int blk32, int off, unsigned word, bool leader, float d, float s) {
@@ -104,6 +111,7 @@ template <> struct gs_traits<B200_TYPE_Q4_K> {
 // sc[8 n + j + 2 g].  Activations: planes[g][nj][gb] (16 int8) and dA4[n][gb] = (dA(4n), .., dA(4n+3)).
 template <> struct gs_traits<B200_TYPE_Q6_K> {
     static constexpr int BLOCK_BYTES = 210;
+    static __host__ __device__ constexpr int stages(bool wide) { return wide ? 3 : 2; }
     static __host__ __device__ size_t act_bytes(int K) { return (size_t) K + (size_t) (K >> 8) * 32; }
     static __device__ __forceinline__ void store_act(uint8_t * s_act, int K, int nblocks, int blk32, int off, unsigned word, bool leader, float d, float s) {
         const int gb = blk32 >> 3, sub = blk32 & 7, n = sub >> 2, g = sub & 3, hf = off >> 4;
@@ -164,9 +172,11 @@ static __device__ __forceinline__ void gs_locate(const gs_args & p, int gr, cons
     dst = p.seg[s].dst + r;
 }
 
-template <int TYPE>
-__global__ void __launch_bounds__(GS_WARPS * 32, 2) k_gemv_stream(const gs_args p) {
+template <int TYPE, bool WIDE>
+__global__ void __launch_bounds__(WIDE ? 256 : 384, WIDE ? 2 : 1) k_gemv_stream(const gs_args p) {
     using T = gs_traits<TYPE>;
+    constexpr int GS_WARPS = WIDE ? 8 : 12;
+    constexpr int GS_STAGES = T::stages(WIDE);
     constexpr int CHUNK_BYTES = T::BLOCK_BYTES * GS_CB;
     constexpr int STAGE_BYTES = CHUNK_BYTES * GS_RW;
     extern __shared__ __align__(128) uint8_t smem[];
@@ -220,7 +230,21 @@ __global__ void __launch_bounds__(GS_WARPS * 32, 2) k_gemv_stream(const gs_args 
     // quantize the activation column to q8_1 straight into shared memory, in lane order.  Same arithmetic as
     // q8_1_block<B200_Q8_1_X86> (bit-exact with the reference), but 128-bit loads: a lane holds 4 consecutive values, the
     // 8 lanes of a group hold one 32-value block, and up to GS_QB independent loads per lane are in flight at once.
-    {
+    if (p.aq != nullptr) {
+        // a ready q8_1 image (large K: one quantize launch instead of one quantization per CTA): permuting copy
+        const int4 * src = (const int4 *) p.aq;
+        for (int j = threadIdx.x; j < (p.K >> 4); j += blockDim.x) {
+            const int4 v = src[j];
+            const int blk32 = j >> 1;
+            const bool leader = (j & 1) == 0;
+            float2 ds = make_float2(0.f, 0.f);
+            if (leader) ds = __half22float2(p.ads[blk32]);
+            T::store_act(s_act, p.K, nblocks, blk32, 16 * (j & 1) + 0,  (unsigned) v.x, leader, ds.x, ds.y);
+            T::store_act(s_act, p.K, nblocks, blk32, 16 * (j & 1) + 4,  (unsigned) v.y, false, 0.f, 0.f);
+            T::store_act(s_act, p.K, nblocks, blk32, 16 * (j & 1) + 8,  (unsigned) v.z, false, 0.f, 0.f);
+            T::store_act(s_act, p.K, nblocks, blk32, 16 * (j & 1) + 12, (unsigned) v.w, false, 0.f, 0.f);
+        }
+    } else {
         constexpr int GS_QB = 8;
         const float4 * x4 = (const float4 *) p.x;
         const int nvec = p.K >> 7;                                        // 128-float chunks = 4 q8_1 blocks
@@ -291,10 +315,11 @@ __global__ void __launch_bounds__(GS_WARPS * 32, 2) k_gemv_stream(const gs_args 
     }
 }
 
-template <int TYPE> static size_t gs_smem_bytes(int K) {
+template <int TYPE> static size_t gs_smem_bytes(int K, bool wide) {
+    const int GS_WARPS = wide ? 8 : 12, GS_STAGES = gs_traits<TYPE>::stages(wide);
     return (size_t) GS_WARPS * GS_STAGES * gs_traits<TYPE>::BLOCK_BYTES * GS_CB * GS_RW + gs_traits<TYPE>::act_bytes(K) + GS_WARPS * GS_STAGES * 8;
 }
-#define GS_SMEM_MAX (112 * 1024)
+#define GS_SMEM_MAX (200 * 1024)   // typical shapes need <= 113 KB, which lets two kernels co-reside on an SM
 
 // true when the streaming kernel can take a MUL_MAT of this weight with ONE contiguous f32 activation column
 bool b200_gemv_stream_supported(const b200_tensor * w, const b200_tensor * x) {
@@ -302,37 +327,50 @@ bool b200_gemv_stream_supported(const b200_tensor * w, const b200_tensor * x) {
     if (x->type != B200_TYPE_F32 || x->nb[0] != 4 || ((uintptr_t) x->data & 15)) return false;
     if (((uintptr_t) w->data & 15) || (w->nb[1] & 15) || w->ne[0] % 256 != 0 || w->ne[0] > 32768 || w->ne[1] > (1 << 28)) return false;
     const int K = (int) w->ne[0];
-    if (w->type == B200_TYPE_Q4_K) return !(w->flags & B200_TENSOR_REPACKED) && gs_smem_bytes<B200_TYPE_Q4_K>(K) <= GS_SMEM_MAX;
-    if (w->type == B200_TYPE_Q6_K) return (w->flags & B200_TENSOR_REPACKED) && K % 2048 == 0 && gs_smem_bytes<B200_TYPE_Q6_K>(K) <= GS_SMEM_MAX;
+    if (w->type == B200_TYPE_Q4_K) return !(w->flags & B200_TENSOR_REPACKED) && gs_smem_bytes<B200_TYPE_Q4_K>(K, false) <= GS_SMEM_MAX;
+    if (w->type == B200_TYPE_Q6_K) return (w->flags & B200_TENSOR_REPACKED) && K % 2048 == 0 && gs_smem_bytes<B200_TYPE_Q6_K>(K, false) <= GS_SMEM_MAX;
     return false;
 }
 
-template <int TYPE>
-static int gs_launch(b200_ctx * ctx, const gs_args & p, int attr_slot) {
-    const size_t smem = gs_smem_bytes<TYPE>(p.K);
+template <int TYPE, bool WIDE>
+static int gs_launch_cfg(b200_ctx * ctx, const gs_args & p, int attr_slot) {
+    constexpr int WARPS = WIDE ? 8 : 12;
+    const size_t smem = gs_smem_bytes<TYPE>(p.K, WIDE);
     if (!ctx->attr_done[attr_slot]) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(k_gemv_stream<TYPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, GS_SMEM_MAX));
+        B200_CUDA_TRY(cudaFuncSetAttribute(k_gemv_stream<TYPE, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, WIDE ? 113 * 1024 : GS_SMEM_MAX));
         ctx->attr_done[attr_slot] = 1;
     }
-    // persistent-size grid: two CTAs per SM, rows split evenly over all warps; fewer CTAs when there are few rows
-    const int64_t want = (p.Mtot + GS_WARPS - 1) / GS_WARPS;
+    // persistent-size grid, rows split evenly over all warps; fewer CTAs when there are few rows
+    const int64_t want = (p.Mtot + WARPS - 1) / WARPS;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned) max((int64_t) 1, min(want, (int64_t) ctx->sm_count * 2)));
-    cfg.blockDim = dim3(GS_WARPS * 32);
+    cfg.gridDim = dim3((unsigned) max((int64_t) 1, min(want, (int64_t) ctx->sm_count * (WIDE ? 2 : 1))));
+    cfg.blockDim = dim3(WARPS * 32);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = ctx->stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = ctx->pdl ? 1 : 0;
-    B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_gemv_stream<TYPE>, p));
+    B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_gemv_stream<TYPE, WIDE>, p));
     return B200_OK;
+}
+template <int TYPE>
+static int gs_launch(b200_ctx * ctx, const gs_args & p, int attr_slot) {
+    // WIDE once the weights outlast what the rings of one wave can hold (~22 MB), if its smem fits two CTAs per SM
+    const size_t bytes = (size_t) p.Mtot * (p.K >> 8) * gs_traits<TYPE>::BLOCK_BYTES;
+    static int force = -1;
+    if (force < 0) { const char * e = getenv("GGML_B200_GEMV_SHAPE"); force = e ? (e[0] == 'w' ? 1 : e[0] == 'l' ? 2 : 0) : 0; }
+    bool wide = bytes > ((size_t) 24 << 20);
+    if (force == 1) wide = true; else if (force == 2) wide = false;
+    if (wide && gs_smem_bytes<TYPE>(p.K, true) <= 113 * 1024) return gs_launch_cfg<TYPE, true>(ctx, p, attr_slot);
+    return gs_launch_cfg<TYPE, false>(ctx, p, attr_slot + 2);
 }
 
 // n <= 3 weights of the same type sharing the activation column x; dst[i] is the f32 column of weight i
-int b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, float * const * dst) {
+int b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, const void * image, float * const * dst) {
     gs_args p;
     p.nseg = n; p.Mtot = 0; p.x = (const float *) x->data; p.K = (int) w[0]->ne[0];
+    p.aq = (const int8_t *) image; p.ads = image ? (const __half2 *) ((const int8_t *) image + p.K) : nullptr;
     for (int i = 0; i < n; ++i) {
         p.seg[i].w = (const uint8_t *) w[i]->data; p.seg[i].nb1 = w[i]->nb[1]; p.seg[i].dst = dst[i]; p.seg[i].M = (int) w[i]->ne[1];
         p.Mtot += p.seg[i].M;

@@ -63,6 +63,7 @@ __global__ void __launch_bounds__(256) k_quantize_q8_1_soa(const float * __restr
                                                           int64_t ne1, int64_t ne2,
                                                           int8_t * __restrict__ qs, __half2 * __restrict__ ds,
                                                           int64_t nblk_col, int64_t nblk_total) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");    // lets a PDL-launched consumer prefetch its weights meanwhile
     const int     lane = threadIdx.x & 31;
     const int64_t ib   = (int64_t) blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (ib >= nblk_total) return;
