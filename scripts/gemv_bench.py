@@ -51,6 +51,7 @@ for tn in a.types.split(","):
         ctx.record(e1); ms = ctx.elapsed_ms(e0, e1) / (reps * nbuf)
         kern = {k: v[0] / v[1] * 1e3 for k, v in prof.items()}
         gbs = wb / (ms * 1e-3) / 1e9
+        if a.n > 8: print(f"      n={a.n}: {2.0 * M * K * a.n / (ms * 1e-3) / 1e12:8.1f} TFLOP/s", flush=True)
         print(f"{tn:5s} K={K:6d} M={M:6d} n={a.n}  {wb/1e6:8.2f} MB  graph {ms*1e3:8.2f} us/op {gbs:7.1f} GB/s ({gbs/6551:.2f})  kernel us: " +
               ", ".join(f"{k} {v:.2f}" for k, v in kern.items()), flush=True)
         out.append(dict(type=tn, K=K, M=M, n=a.n, us=ms * 1e3, gbs=gbs, kernel_us=kern))

@@ -191,9 +191,10 @@ static const void * quantized_activations(b200_ctx * ctx, const b200_tensor * x,
     if (qc.valid && qc.data == x->data && qc.variant == variant && ctx->scratch[0] &&
         !memcmp(qc.ne, x->ne, sizeof(qc.ne)) && !memcmp(qc.nb, x->nb, sizeof(qc.nb))) return ctx->scratch[0];
     qc.valid = 0;
-    void * image = b200_scratch(ctx, 0, b200_q8_1_soa_size(K, ncol));
+    void * image = b200_scratch(ctx, 0, variant == B200_ACT_BF16 ? (size_t) ncol * K * 2 : b200_q8_1_soa_size(K, ncol));
     if (!image) { *rc = B200_ERR_ALLOC; return nullptr; }
-    *rc = b200_launch_quantize_q8_1_soa(ctx, (const float *) x->data, x->nb[1], x->nb[2], x->nb[3], K, x->ne[1], x->ne[2], x->ne[3], image, variant);
+    if (variant == B200_ACT_BF16) *rc = b200_launch_act_bf16(ctx, (const float *) x->data, x->nb[1], K, x->ne[1], image);   // 2-D only (b200_gemm_supported)
+    else *rc = b200_launch_quantize_q8_1_soa(ctx, (const float *) x->data, x->nb[1], x->nb[2], x->nb[3], K, x->ne[1], x->ne[2], x->ne[3], image, variant);
     if (*rc) return nullptr;
     qc.data = x->data; memcpy(qc.ne, x->ne, sizeof(qc.ne)); memcpy(qc.nb, x->nb, sizeof(qc.nb));
     qc.span = b200_tensor_span(x); qc.variant = variant; qc.valid = 1;
@@ -225,7 +226,11 @@ extern "C" int b200_mul_mat(b200_ctx * ctx, const b200_tensor * w, const b200_te
         if (K % b200_blck_size(w->type) != 0) { b200_set_error("mul_mat: K=%lld not a multiple of the block size", (long long) K); return B200_ERR_INVALID; }
         if (w->nb[0] != b200_type_size(w->type)) { b200_set_error("mul_mat: quantized weight rows must be contiguous"); return B200_ERR_UNSUPPORTED; }
         int rc;
-        if (x->ne[1] > B200_GEMV_MAX_COLS && b200_gemm_supported(w, x)) rc = b200_launch_gemm_q(ctx, w, x, dst);
+        if (x->ne[1] > B200_GEMV_MAX_COLS && b200_gemm_supported(w, x)) {
+            const void * image = quantized_activations(ctx, x, B200_ACT_BF16, &rc);   // bf16 [N][K], shared by wq/wk/wv and gate/up
+            if (!image) return rc;
+            rc = b200_launch_gemm_q(ctx, w, image, x->ne[1], dst);
+        }
         else if (q8_1_variant_env() == B200_Q8_1_X86 && b200_gemv_stream_supported(w, x)) {
             float * d = (float *) dst->data;
             const void * image = nullptr;

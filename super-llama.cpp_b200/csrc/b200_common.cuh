@@ -161,7 +161,9 @@ int  b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int 
 #define B200_GEMV_FUSED_QUANT_MAX_K 8192    // above this, one quantize launch + image beats one quantization per CTA
 #define B200_GEMV_MAX_COLS 8
 bool b200_gemm_supported(const b200_tensor * w, const b200_tensor * x);
-int  b200_launch_gemm_q(b200_ctx * ctx, const b200_tensor * w, const b200_tensor * x, b200_tensor * dst);
+int  b200_launch_gemm_q(b200_ctx * ctx, const b200_tensor * w, const void * image, int64_t N, b200_tensor * dst);   // image: bf16 [N][K]
+int  b200_launch_act_bf16(b200_ctx * ctx, const float * x, size_t nb1, int64_t K, int64_t N, void * image);
+#define B200_ACT_BF16 2                     // activation-image kind next to the two q8_1 variants
 bool b200_gemm_id_supported(const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids);
 int  b200_launch_gemm_id_q(b200_ctx * ctx, const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids, b200_tensor * dst);
 int  b200_launch_matmul_float(b200_ctx * ctx, const b200_tensor * w, const b200_tensor * x, b200_tensor * dst);

@@ -99,6 +99,47 @@ def test_mul_mat_golden(ctx, orc, gold, t):
     assert e < 1e-9, f"vs q8_1-path oracle: nmse {e:.3e}"
 
 
+GEMM_TYPES = (O.Q4_K,)          # types the tcgen05 prefill GEMM takes (bf16 operands, fp32 TMEM accumulation) when n > 8
+NMSE_BF16 = 5e-5                # bf16 rounding of weights and activations vs exact-activation arithmetic
+
+
+def _check_prefill(orc, got, t, w, K, M, x, N):
+    assert np.isfinite(got).all()
+    e_cpu = O.nmse(orc.mul_mat(t, w, K, M, x, N, act=O.ACT_CPU), got)
+    assert e_cpu < NMSE_HARNESS, f"vs ggml-cpu numerics: nmse {e_cpu:.3e}"
+    e = O.nmse(orc.mul_mat(t, w, K, M, x, N, act=O.ACT_F64), got)
+    assert e < NMSE_BF16, f"vs exact-activation oracle: nmse {e:.3e}"
+
+
+@pytest.mark.parametrize("t", GEMM_TYPES)
+@pytest.mark.parametrize("M,N,K", [(128, 16, 256), (16, 9, 256), (200, 33, 512), (129, 64, 1024), (300, 260, 1024), (1024, 512, 4096),
+                                   (4096, 100, 256), (256, 128, 14336)])
+def test_mul_mat_prefill_gemm(ctx, orc, t, M, N, K):
+    """n > 8: tcgen05 GEMM; ragged M (not a multiple of 128), ragged N (TMA zero fill), every BN tile width, long K"""
+    rng = np.random.default_rng(M + 3 * N + K)
+    w = O.random_blocks(rng, t, K, M)
+    x = rng.standard_normal((N, K)).astype(np.float32)
+    got = ctx.mul_mat_host(t, w, K, M, x, N)
+    _check_prefill(orc, got, t, w, K, M, x, N)
+
+
+@pytest.mark.parametrize("t", GEMM_TYPES)
+def test_mul_mat_prefill_gemm_strided(ctx, B, orc, t):
+    """activation rows and result columns with padding between them (views into larger buffers)"""
+    rng = np.random.default_rng(77)
+    K, M, N = 512, 192, 40
+    w = O.random_blocks(rng, t, K, M)
+    xbuf = rng.standard_normal((N, K + 64)).astype(np.float32)
+    dx = ctx.upload(B.F32, [K + 64, N], xbuf).view([K, N, 1, 1], [4, (K + 64) * 4, (K + 64) * 4 * N, (K + 64) * 4 * N])
+    dw = ctx.upload(t, [K, M], w)
+    dbuf = ctx.upload(B.F32, [M + 32, N], np.full((N, M + 32), 7.0, np.float32))
+    dd = dbuf.view([M, N, 1, 1], [4, (M + 32) * 4, (M + 32) * 4 * N, (M + 32) * 4 * N])
+    ctx.mul_mat(dw, dx, dd)
+    out = ctx.download(dbuf).reshape(N, M + 32)
+    assert (out[:, M:] == 7.0).all()
+    _check_prefill(orc, out[:, :M].reshape(1, 1, N, M), t, w, K, M, np.ascontiguousarray(xbuf[:, :K]), N)
+
+
 @pytest.mark.parametrize("t", QTYPES)
 @pytest.mark.parametrize("n", [1, 2, 3, 4, 5, 6, 7, 8, 9, 16])
 def test_mul_mat_small_n(ctx, orc, t, n):
@@ -108,6 +149,8 @@ def test_mul_mat_small_n(ctx, orc, t, n):
     w = O.random_blocks(rng, t, K, M)
     x = rng.uniform(-1, 1, (n, K)).astype(np.float32)
     got = ctx.mul_mat_host(t, w, K, M, x, n)
+    if n > 8 and t in GEMM_TYPES:
+        return _check_prefill(orc, got, t, w, K, M, x, n)
     assert _check_mm(orc, got, t, w, K, M, x, n) < 1e-9
 
 
