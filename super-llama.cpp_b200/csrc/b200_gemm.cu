@@ -8,13 +8,17 @@
 // Dequantizing to bf16 in shared memory keeps ONE fp32 accumulator in TMEM for the whole K loop; bf16 rounding of weights and
 // activations costs ~1e-5 NMSE against the 5e-4 bar (tests/test-backend-ops.cpp:6080-6082).
 //
-// CTA = 128 weight rows x BN activation columns.  Warp roles:
-//   warps 0-3  A producers: each thread owns one weight row.  Raw GGUF blocks arrive in a per-warp ring by cp.async.bulk (one
-//              copy per row and 256-K block); the thread expands 64 K-values at a time to bf16 (value = d*sc*q - dmin*m, two
-//              values per HFMA2.BF16) and stores them in the 128-byte-swizzled K-major layout UMMA reads.  After the K loop the
-//              same warps run the epilogue: tcgen05.ld their 32 TMEM lanes and store fp32 columns (coalesced along M).
+// CTA = 128 weight rows x BN activation columns.  The A operand (weights) never touches shared memory as bf16: an SS-mode
+// M=128 MMA reads A and B from shared memory at the full 128 B/clk the SM has, which measured as the limiter of the first
+// version of this kernel (profiles/r1_gemm_v1_*).  Here A is fed from TMEM.  Warp roles:
+//   warps 0-3  A producers: thread = weight row = TMEM lane.  Raw GGUF blocks of the 128-row tile arrive in a shared ring by one
+//              TMA tiled load per 256-K block (a 2-D byte tensor map over the weight rows); the thread expands 64 K-values at a
+//              time to bf16 (value = d*sc*q - dmin*m, two values per HFMA2.BF16) and writes them with one tcgen05.st (32 columns
+//              of its lane).  After the K loop the same warps run the epilogue: tcgen05.ld the accumulator lanes and store fp32
+//              columns (coalesced along M).
 //   warp 4     B producer: one thread, TMA tiled loads (SWIZZLE_128B) of the bf16 activation image [N][K].
-//   warp 5     TMEM owner + MMA issuer: one thread, four tcgen05.mma (K=16 each) per stage, tcgen05.commit frees the stage.
+//   warp 5     TMEM owner + MMA issuer: one thread, four tcgen05.mma (A in TMEM, K=16 each) per stage; tcgen05.commit frees it.
+//   warp 6     raw-weight producer: one thread, the TMA loads of the GGUF block ring.
 #include "b200_common.cuh"
 #include "b200_ptx.cuh"
 #include <cuda.h>
@@ -22,14 +26,16 @@
 
 #define GM_BM      128
 #define GM_BK      64
-#define GM_THREADS 192
-#define GM_RAW_STAGES 3
+#define GM_THREADS 224
+#define GM_STAGES  4          // A (TMEM) / B (smem) pipeline depth in 64-K steps
+#define GM_RAW_STAGES 4      // ring of raw 256-K weight blocks
 
 struct gm_args {
     const uint8_t * w; size_t w_nb1;
     float * dst; size_t d_ld;            // dst[m + n * d_ld]
     int M, N, K;
-    int BN, nstage;
+    int BN;
+    int dbg;                             // timing experiments only (GGML_B200_GEMM_DBG): 1 = no weight fetch, 2 = no expansion math
 };
 
 // ---- activations f32 [K, N] -> bf16 image [N][K] ---------------------------------------------------------------------
@@ -74,7 +80,7 @@ template <> struct gm_traits<B200_TYPE_Q4_K> {
         u.m_hi  = ((u2 >> 4) & 0x0f0f0f0fu) | (((u1 >> 6) & 0x03030303u) << 4);
     }
     // K-chunk g (0..3) of the block: sub-block 2g = low nibbles of qs[32g..32g+31], sub-block 2g+1 = high nibbles (ggml-quants.c:1352-1374)
-    template <int G> static __device__ __forceinline__ void expand(uint32_t raw, const unit & u, uint4 (&out)[8]) {
+    template <int G> static __device__ __forceinline__ void expand(uint32_t raw, const unit & u, uint32_t (&out)[32]) {
         const uint32_t scs = G < 2 ? u.sc_lo : u.sc_hi, ms = G < 2 ? u.m_lo : u.m_hi;
         const int sh = (G & 1) * 16;
         const float d0 = u.d * (float) ((scs >> sh) & 0xff), d1 = u.d * (float) ((scs >> (sh + 8)) & 0xff);
@@ -83,7 +89,7 @@ template <> struct gm_traits<B200_TYPE_Q4_K> {
         uint32_t w[8];
         { const int4 a = lds128(raw + 16 + 32 * G), b = lds128(raw + 32 + 32 * G);
           w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w; w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w; }
-        uint32_t lo[16], hi[16];
+        uint32_t * lo = out, * hi = out + 16;                                // natural K order: 32 low-nibble values, then 32 high
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             // nibble q -> bf16 bits 0x4300|q = 128+q (exact); PRMT drops the 0x43 bytes in while pairing neighbours
@@ -93,81 +99,71 @@ template <> struct gm_traits<B200_TYPE_Q4_K> {
             hi[2 * i]     = fma_magic(__byte_perm(h4, 0x43434343u, 0x4140), s_hi, o_hi);
             hi[2 * i + 1] = fma_magic(__byte_perm(h4, 0x43434343u, 0x4342), s_hi, o_hi);
         }
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            out[c]     = make_uint4(lo[4 * c], lo[4 * c + 1], lo[4 * c + 2], lo[4 * c + 3]);
-            out[4 + c] = make_uint4(hi[4 * c], hi[4 * c + 1], hi[4 * c + 2], hi[4 * c + 3]);
-        }
     }
 };
 
 template <int TYPE>
-__global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const __grid_constant__ CUtensorMap tmap_x) {
+__global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w) {
     using T = gm_traits<TYPE>;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     const uint32_t base  = (smem_u32(smem_raw) + 1023u) & ~1023u;
-    const uint32_t a_sm  = base;                                             // [nstage][128 rows][128 B]
-    const uint32_t b_sm  = a_sm + p.nstage * (GM_BM * 128);                  // [nstage][BN rows][128 B]
-    const uint32_t r_sm  = b_sm + p.nstage * (p.BN * 128);                   // [4 warps][RAW_STAGES][32 rows][RAW_BYTES]
-    const uint32_t bars  = r_sm + 4 * GM_RAW_STAGES * 32 * T::RAW_BYTES;     // 8-byte aligned (all terms are multiples of 16)
-    const uint32_t full0 = bars, empty0 = bars + 8 * p.nstage, raw0 = empty0 + 8 * p.nstage;
-    const uint32_t tfull = raw0 + 8 * 4 * GM_RAW_STAGES, tslot = tfull + 8;
+    const uint32_t b_sm  = base;                                             // [GM_STAGES][BN rows][128 B], 128B-swizzled by TMA
+    const uint32_t r_sm  = b_sm + GM_STAGES * (p.BN * 128);                  // [GM_RAW_STAGES][128 rows][RAW_BYTES]
+    const uint32_t bars  = r_sm + GM_RAW_STAGES * GM_BM * T::RAW_BYTES;
+    const uint32_t fa0 = bars, fb0 = fa0 + 8 * GM_STAGES, empty0 = fb0 + 8 * GM_STAGES;   // A written / B landed / stage consumed
+    const uint32_t rf0 = empty0 + 8 * GM_STAGES, re0 = rf0 + 8 * GM_RAW_STAGES;           // raw block landed / raw block consumed
+    const uint32_t tfull = re0 + 8 * GM_RAW_STAGES, tslot = tfull + 8;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n0 = blockIdx.x * p.BN, m0 = blockIdx.y * GM_BM;
-    const int nks = p.K / GM_BK;
+    const int nks = p.K / GM_BK, nunits = p.K / T::RAW_K;
+    const uint32_t tcols = p.BN + 32 * GM_STAGES <= 256 ? 256u : 512u;       // accumulator [0, BN) + A stages [BN, BN + 32*GM_STAGES)
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < p.nstage; ++s) { mbar_init(full0 + 8 * s, 5); mbar_init(empty0 + 8 * s, 1); }
-        for (int s = 0; s < 4 * GM_RAW_STAGES; ++s) mbar_init(raw0 + 8 * s, 1);
+        for (int s = 0; s < GM_STAGES; ++s) { mbar_init(fa0 + 8 * s, 4); mbar_init(fb0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
+        for (int s = 0; s < GM_RAW_STAGES; ++s) { mbar_init(rf0 + 8 * s, 1); mbar_init(re0 + 8 * s, 4); }
         mbar_init(tfull, 1);
         mbar_fence_init();
     }
-    if (warp == 5) tmem_alloc(tslot, (uint32_t) (p.BN < 32 ? 32 : p.BN));
+    if (warp == 5) tmem_alloc(tslot, tcols);
     if (warp == 4 && lane == 0) tma_prefetch_desc(&tmap_x);
+    if (warp == 6 && lane == 0) tma_prefetch_desc(&tmap_w);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     uint32_t tmem;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem) : "r"(tslot));
+    const uint32_t tmem_a = tmem + (uint32_t) p.BN;
 
     if (warp < 4) {
         // ===== A producers =====
         const int row = warp * 32 + lane;
-        const int64_t m = min(m0 + row, p.M - 1);                            // rows past M re-read the last row; masked in the epilogue
-        const uint8_t * wrow = p.w + (size_t) m * p.w_nb1;
-        const uint32_t ring = r_sm + warp * (GM_RAW_STAGES * 32 * T::RAW_BYTES);
-        const uint32_t rbar = raw0 + 8 * warp * GM_RAW_STAGES;
-        const int nunits = p.K / T::RAW_K;
-        auto fetch = [&](int unit, int slot) {
-            if (lane == 0) mbar_arrive_expect_tx(rbar + 8 * slot, 32u * T::RAW_BYTES);
-            __syncwarp();
-            bulk_g2s(ring + (slot * 32 + lane) * T::RAW_BYTES, wrow + (size_t) unit * T::RAW_BYTES, T::RAW_BYTES, rbar + 8 * slot);
-        };
-        for (int s = 0; s < GM_RAW_STAGES && s < nunits; ++s) fetch(s, s);
-        const uint32_t a_row = (uint32_t) ((row >> 3) * 1024 + (row & 7) * 128), sw = (uint32_t) (row & 7);
-        int ks = 0, stage = 0; uint32_t eph = 1;                             // eph: parity to wait for on empty[stage] (1 = fresh barrier passes)
+        const uint32_t lane_base = (uint32_t) (warp * 32) << 16;
+        int stage = 0; uint32_t eph = 1;                                     // parity to wait for on empty[stage] (1: a fresh barrier passes)
         int slot = 0; uint32_t rph = 0;
-        auto emit = [&](const uint4 (&o)[8]) {
+        auto emit = [&](const uint32_t (&o)[32]) {
             mbar_wait(empty0 + 8 * stage, eph);
-            const uint32_t dst = a_sm + stage * (GM_BM * 128) + a_row;
-#pragma unroll
-            for (int c = 0; c < 8; ++c) sts128(dst + (((uint32_t) c ^ sw) << 4), make_int4((int) o[c].x, (int) o[c].y, (int) o[c].z, (int) o[c].w));
-            fence_proxy_async();
+            tc_fence_after();
+            tmem_st32(tmem_a + lane_base + 32u * stage, o);
+            tmem_st_wait();
+            tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(full0 + 8 * stage);
-            ++ks; if (++stage == p.nstage) { stage = 0; eph ^= 1u; }
+            if (lane == 0) mbar_arrive(fa0 + 8 * stage);
+            if (++stage == GM_STAGES) { stage = 0; eph ^= 1u; }
         };
         for (int unit = 0; unit < nunits; ++unit) {
-            mbar_wait(rbar + 8 * slot, rph);
-            const uint32_t raw = ring + (slot * 32 + lane) * T::RAW_BYTES;
+            if (!(p.dbg & 1)) mbar_wait(rf0 + 8 * slot, rph);
+            const uint32_t raw = r_sm + (slot * GM_BM + row) * T::RAW_BYTES;
             typename T::unit u; T::load_unit(raw, u);
-            uint4 o[8];
+            uint32_t o[32];
+            if (p.dbg & 2) { for (int c = 0; c < 32; ++c) o[c] = u.sc_lo; emit(o); emit(o); emit(o); emit(o); }
+            else {
             T::template expand<0>(raw, u, o); emit(o);
             T::template expand<1>(raw, u, o); emit(o);
             T::template expand<2>(raw, u, o); emit(o);
             T::template expand<3>(raw, u, o); emit(o);
+            }
             __syncwarp();
-            if (unit + GM_RAW_STAGES < nunits) fetch(unit + GM_RAW_STAGES, slot);
+            if (lane == 0) mbar_arrive(re0 + 8 * slot);
             if (++slot == GM_RAW_STAGES) { slot = 0; rph ^= 1u; }
         }
         // ===== epilogue: TMEM -> registers -> dst (columns of dst are contiguous along M) =====
@@ -178,7 +174,7 @@ __global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const
         for (int c0 = 0; c0 < p.BN; c0 += 16) {
             if (n0 + c0 >= p.N) break;
             uint32_t r[16];
-            tmem_ld16(tmem + ((uint32_t) (warp * 32) << 16) + (uint32_t) c0, r);
+            tmem_ld16(tmem + lane_base + (uint32_t) c0, r);
             tmem_ld_wait();
             if (mm < p.M) {
 #pragma unroll
@@ -192,31 +188,43 @@ __global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const
             int stage = 0; uint32_t eph = 1;
             for (int ks = 0; ks < nks; ++ks) {
                 mbar_wait(empty0 + 8 * stage, eph);
-                mbar_arrive_expect_tx(full0 + 8 * stage, (uint32_t) p.BN * 128u);
-                tma_load_2d(b_sm + stage * (p.BN * 128), &tmap_x, ks * GM_BK, n0, full0 + 8 * stage);
-                if (++stage == p.nstage) { stage = 0; eph ^= 1u; }
+                mbar_arrive_expect_tx(fb0 + 8 * stage, (uint32_t) p.BN * 128u);
+                tma_load_2d(b_sm + stage * (p.BN * 128), &tmap_x, ks * GM_BK, n0, fb0 + 8 * stage);
+                if (++stage == GM_STAGES) { stage = 0; eph ^= 1u; }
             }
         }
-    } else {
+    } else if (warp == 5) {
         // ===== MMA issuer =====
         if (lane == 0) {
-            const uint32_t idesc = umma_idesc_bf16(GM_BM, p.BN < 16 ? 16 : p.BN);
+            const uint32_t idesc = umma_idesc_bf16(GM_BM, p.BN);
             int stage = 0; uint32_t fph = 0;
             for (int ks = 0; ks < nks; ++ks) {
-                mbar_wait(full0 + 8 * stage, fph);
+                mbar_wait(fa0 + 8 * stage, fph);
+                mbar_wait(fb0 + 8 * stage, fph);
                 tc_fence_after();
-                const uint64_t da = umma_desc_sw128(a_sm + stage * (GM_BM * 128)), db = umma_desc_sw128(b_sm + stage * (p.BN * 128));
+                const uint64_t db = umma_desc_sw128(b_sm + stage * (p.BN * 128));
 #pragma unroll
-                for (int k = 0; k < GM_BK / 16; ++k) umma_f16(tmem, da + 2 * k, db + 2 * k, idesc, (uint32_t) ((ks | k) != 0));
+                for (int k = 0; k < GM_BK / 16; ++k) umma_f16_ts(tmem, tmem_a + 32u * stage + 8u * k, db + 2 * k, idesc, (uint32_t) ((ks | k) != 0));
                 umma_commit(empty0 + 8 * stage);
-                if (++stage == p.nstage) { stage = 0; fph ^= 1u; }
+                if (++stage == GM_STAGES) { stage = 0; fph ^= 1u; }
             }
             umma_commit(tfull);
         }
         __syncwarp();
+    } else {
+        // ===== raw weight producer: one 128-row x RAW_BYTES box per 256-K block (rows past M are zero-filled) =====
+        if (lane == 0 && !(p.dbg & 1)) {
+            int slot = 0; uint32_t eph = 1;
+            for (int unit = 0; unit < nunits; ++unit) {
+                mbar_wait(re0 + 8 * slot, eph);
+                mbar_arrive_expect_tx(rf0 + 8 * slot, (uint32_t) (GM_BM * T::RAW_BYTES));
+                tma_load_2d(r_sm + slot * (GM_BM * T::RAW_BYTES), &tmap_w, unit * T::RAW_BYTES, m0, rf0 + 8 * slot);
+                if (++slot == GM_RAW_STAGES) { slot = 0; eph ^= 1u; }
+            }
+        }
     }
     __syncthreads();
-    if (warp == 5) { tc_fence_after(); tmem_dealloc(tmem, (uint32_t) (p.BN < 32 ? 32 : p.BN)); }
+    if (warp == 5) { tc_fence_after(); tmem_dealloc(tmem, tcols); }
 }
 
 // ---- host side -------------------------------------------------------------------------------------------------------------
@@ -262,7 +270,8 @@ int b200_launch_gemm_q(b200_ctx * ctx, const b200_tensor * w, const void * image
     p.M = (int) w->ne[1]; p.N = (int) N; p.K = (int) w->ne[0];
     static const int force_bn = getenv("GGML_B200_GEMM_BN") ? atoi(getenv("GGML_B200_GEMM_BN")) : 0;
     p.BN = force_bn ? force_bn : gemm_pick_bn(ctx, p.M, p.N);
-    p.nstage = p.BN == 256 ? 3 : 4;
+    static const int dbg = getenv("GGML_B200_GEMM_DBG") ? atoi(getenv("GGML_B200_GEMM_DBG")) : 0;
+    p.dbg = dbg;
     CUtensorMap tmap;
     const cuuint64_t gdim[2] = { (cuuint64_t) p.K, (cuuint64_t) p.N };
     const cuuint64_t gstr[1] = { (cuuint64_t) p.K * 2 };
@@ -272,13 +281,21 @@ int b200_launch_gemm_q(b200_ctx * ctx, const b200_tensor * w, const void * image
                                CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (cr != CUDA_SUCCESS) { b200_set_error("gemm: cuTensorMapEncodeTiled failed (%d)", (int) cr); return B200_ERR_CUDA; }
     using T = gm_traits<B200_TYPE_Q4_K>;
-    const size_t smem = 1024 + (size_t) p.nstage * (GM_BM * 128 + p.BN * 128) + 4 * GM_RAW_STAGES * 32 * T::RAW_BYTES + 8 * (2 * p.nstage + 4 * GM_RAW_STAGES + 1) + 16;
+    // the weight rows as a 2-D byte tensor: box = one 256-K block of 128 consecutive rows
+    CUtensorMap tmap_w;
+    const cuuint64_t wdim[2] = { (cuuint64_t) (p.K / T::RAW_K) * T::RAW_BYTES, (cuuint64_t) p.M };
+    const cuuint64_t wstr[1] = { (cuuint64_t) p.w_nb1 };
+    const cuuint32_t wbox[2] = { T::RAW_BYTES, GM_BM };
+    const CUresult cw = encode(&tmap_w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, (void *) p.w, wdim, wstr, wbox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (cw != CUDA_SUCCESS) { b200_set_error("gemm: cuTensorMapEncodeTiled (weights) failed (%d)", (int) cw); return B200_ERR_CUDA; }
+    const size_t smem = 1024 + (size_t) GM_STAGES * (p.BN * 128) + GM_RAW_STAGES * GM_BM * T::RAW_BYTES + 8 * (3 * GM_STAGES + 2 * GM_RAW_STAGES + 1) + 16;
     if (!ctx->attr_done[5]) {
         B200_CUDA_TRY(cudaFuncSetAttribute(k_gemm_q<B200_TYPE_Q4_K>, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
         ctx->attr_done[5] = 1;
     }
     dim3 grid((unsigned) ((p.N + p.BN - 1) / p.BN), (unsigned) ((p.M + GM_BM - 1) / GM_BM));
-    B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q4_K><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap));
+    B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q4_K><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap, tmap_w));
     return B200_OK;
 }
 
