@@ -8,17 +8,20 @@
 // Dequantizing to bf16 in shared memory keeps ONE fp32 accumulator in TMEM for the whole K loop; bf16 rounding of weights and
 // activations costs ~1e-5 NMSE against the 5e-4 bar (tests/test-backend-ops.cpp:6080-6082).
 //
-// CTA = 128 weight rows x BN activation columns.  The A operand (weights) never touches shared memory as bf16: an SS-mode
+// CTA = MT*128 weight rows x BN activation columns.  The limiter is L2->SM traffic (~6.3 KB/clk chip-wide): per 64-K step a CTA
+// pulls BN*128 B of activations but only MT*128*36 B of 4.5-bit weights, so tall tiles (MT=2, BN=128) are preferred.
+// The A operand (weights) never touches shared memory as bf16: an SS-mode
 // M=128 MMA reads A and B from shared memory at the full 128 B/clk the SM has, which measured as the limiter of the first
 // version of this kernel (profiles/r1_gemm_v1_*).  Here A is fed from TMEM.  Warp roles:
-//   warps 0-3  A producers: thread = weight row = TMEM lane.  Raw GGUF blocks of the 128-row tile arrive in a shared ring by one
+//   warps 0-7  A producers: thread = weight row = TMEM lane (MT=2: warps 4-7 own the second 128 rows; MT=1: the two groups
+//              alternate 64-K steps).  Raw GGUF blocks of the 128-row tile arrive in a shared ring by one
 //              TMA tiled load per 256-K block (a 2-D byte tensor map over the weight rows); the thread expands 64 K-values at a
 //              time to bf16 (value = d*sc*q - dmin*m, two values per HFMA2.BF16) and writes them with one tcgen05.st (32 columns
 //              of its lane).  After the K loop the same warps run the epilogue: tcgen05.ld the accumulator lanes and store fp32
 //              columns (coalesced along M).
-//   warp 4     B producer: one thread, TMA tiled loads (SWIZZLE_128B) of the bf16 activation image [N][K].
-//   warp 5     TMEM owner + MMA issuer: one thread, four tcgen05.mma (A in TMEM, K=16 each) per stage; tcgen05.commit frees it.
-//   warp 6     raw-weight producer: one thread, the TMA loads of the GGUF block ring.
+//   warp 8     B producer: one thread, TMA tiled loads (SWIZZLE_128B) of the bf16 activation image [N][K].
+//   warp 9     TMEM owner + MMA issuer: one thread, four tcgen05.mma (A in TMEM, K=16 each) per stage; tcgen05.commit frees it.
+//   warp 10    raw-weight producer: one thread, the TMA loads of the GGUF block ring.
 #include "b200_common.cuh"
 #include "b200_ptx.cuh"
 #include <cuda.h>
@@ -26,16 +29,17 @@
 
 #define GM_BM      128
 #define GM_BK      64
-#define GM_THREADS 224
-#define GM_STAGES  4          // A (TMEM) / B (smem) pipeline depth in 64-K steps
-#define GM_RAW_STAGES 4      // ring of raw 256-K weight blocks
+#define GM_PRODUCERS 8       // A-producer warps (two per TMEM lane quarter)
+#define GM_THREADS ((GM_PRODUCERS + 3) * 32)
 
 struct gm_args {
     const uint8_t * w; size_t w_nb1;
     float * dst; size_t d_ld;            // dst[m + n * d_ld]
     int M, N, K;
-    int BN;
-    int dbg;                             // timing experiments only (GGML_B200_GEMM_DBG): 1 = no weight fetch, 2 = no expansion math
+    int BN;                              // activation columns per CTA (UMMA N)
+    int MT;                              // 128-row weight tiles per CTA (1 or 2): 2 halves the activation traffic per flop
+    int SA, SB, RS;                      // ring depths: A stages in TMEM (power of two), B stages in smem (64-K steps), raw 256-K weight blocks
+    int dbg;                             // timing experiments only (GGML_B200_GEMM_DBG): 1 = no weight fetch, 2 = no expansion math, 4 = no activation fetch
 };
 
 // ---- activations f32 [K, N] -> bf16 image [N][K] ---------------------------------------------------------------------
@@ -68,9 +72,10 @@ static __device__ __forceinline__ uint32_t fma_magic(uint32_t t, uint32_t s, uin
 template <int TYPE> struct gm_traits;
 
 template <> struct gm_traits<B200_TYPE_Q4_K> {
-    static constexpr int RAW_K = 256, RAW_BYTES = 144;
+    static constexpr int RAW_K = 256, ROW_BYTES = 144, TILE_BYTES = GM_BM * 144;   // raw slot of one 128-row tile: [128][144]
     struct unit { float d, dmin; uint32_t sc_lo, sc_hi, m_lo, m_hi; };   // 8 x 6-bit scales / mins, one per byte
-    static __device__ __forceinline__ void load_unit(uint32_t raw, unit & u) {
+    static __device__ __forceinline__ void load_unit(uint32_t tile, int rt, int, unit & u) {
+        const uint32_t raw = tile + rt * ROW_BYTES;
         const int4 h = lds128(raw);                                          // d, dmin, scales[12]
         const float2 dm = __half22float2(*(const __half2 *) &h.x);
         u.d = dm.x; u.dmin = dm.y;
@@ -80,7 +85,8 @@ template <> struct gm_traits<B200_TYPE_Q4_K> {
         u.m_hi  = ((u2 >> 4) & 0x0f0f0f0fu) | (((u1 >> 6) & 0x03030303u) << 4);
     }
     // K-chunk g (0..3) of the block: sub-block 2g = low nibbles of qs[32g..32g+31], sub-block 2g+1 = high nibbles (ggml-quants.c:1352-1374)
-    template <int G> static __device__ __forceinline__ void expand(uint32_t raw, const unit & u, uint32_t (&out)[32]) {
+    template <int G> static __device__ __forceinline__ void expand(uint32_t tile, int rt, const unit & u, uint32_t (&out)[32]) {
+        const uint32_t raw = tile + rt * ROW_BYTES;
         const uint32_t scs = G < 2 ? u.sc_lo : u.sc_hi, ms = G < 2 ? u.m_lo : u.m_hi;
         const int sh = (G & 1) * 16;
         const float d0 = u.d * (float) ((scs >> sh) & 0xff), d1 = u.d * (float) ((scs >> (sh + 8)) & 0xff);
@@ -102,79 +108,144 @@ template <> struct gm_traits<B200_TYPE_Q4_K> {
     }
 };
 
+// q6_K in the load-time repacked group layout (b200_repack.cu): per row, groups of 8 blocks = 1680 B =
+//   QL[8 units][8 blocks][16 B] | QH[4 units][8 blocks][16 B] | SC[8 blocks][16 B] | D[8 blocks][2 B]
+// Block b of a group is column b of a [13 x 128 B] byte matrix: one 4-D TMA box {16 B, 13, 1 group, 128 rows} fetches it for a
+// whole tile ([128 rows][13][16 B] in the slot); the 16 B of fp16 d's come through a second 3-D map ([128 rows][16 B]).
+template <> struct gm_traits<B200_TYPE_Q6_K> {
+    static constexpr int RAW_K = 256, ROW_BYTES = 208, TILE_BYTES = GM_BM * (208 + 16);
+    struct unit { float d; int4 sc; };
+    static __device__ __forceinline__ void load_unit(uint32_t tile, int rt, int blk, unit & u) {
+        u.sc = lds128(tile + rt * ROW_BYTES + 12 * 16);
+        const uint32_t dd = (uint32_t) lds32(tile + GM_BM * ROW_BYTES + rt * 16 + ((blk & 7) >> 1) * 4);
+        u.d = __half2float(__ushort_as_half((unsigned short) ((blk & 1) ? dd >> 16 : dd & 0xffffu)));
+    }
+    // K-step G of the block: half n = G>>1, nibble hi = G&1 (ggml-quants.c:1762-1791).  Element e = ab*32 + j*16 + byte comes from QL unit
+    // (n*2+j)*2+ab (nibble hi) and QH unit n*2+j (bits 4hi+2ab, +1), scale sc[8n + 4hi + 2ab + j]; value = d * sc * (q - 32).
+    template <int G> static __device__ __forceinline__ void expand(uint32_t tile, int rt, const unit & u, uint32_t (&out)[32]) {
+        constexpr int n = G >> 1, hi = G & 1;
+        const uint32_t raw = tile + rt * ROW_BYTES;
+        const uint32_t scw[4] = { (uint32_t) u.sc.x, (uint32_t) u.sc.y, (uint32_t) u.sc.z, (uint32_t) u.sc.w };
+        const uint32_t sc4 = scw[2 * n + hi];                                // the four int8 scales of this K-step: (ab, j) = (0,0) (0,1) (1,0) (1,1)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const int4 qh = lds128(raw + (8 + n * 2 + j) * 16);
+#pragma unroll
+            for (int ab = 0; ab < 2; ++ab) {
+                const int4 ql = lds128(raw + (((n * 2 + j) * 2 + ab) * 16));
+                const float sf = u.d * (float) (int) (int8_t) ((sc4 >> (8 * (2 * ab + j))) & 0xffu);
+                const uint32_t s2 = bf2(sf, sf);
+                const uint32_t qlw[4] = { (uint32_t) ql.x, (uint32_t) ql.y, (uint32_t) ql.z, (uint32_t) ql.w };
+                const uint32_t qhw[4] = { (uint32_t) qh.x, (uint32_t) qh.y, (uint32_t) qh.z, (uint32_t) qh.w };
+#pragma unroll
+                for (int w = 0; w < 4; ++w) {
+                    constexpr int hs = 4 * hi;                               // bit offset of the two qh bits is hs + 2ab; they go to bits 4..5
+                    const int sh = hs + 2 * ab;
+                    const uint32_t lo4 = (qlw[w] >> hs) & 0x0F0F0F0Fu;
+                    const uint32_t h2 = sh >= 4 ? (qhw[w] >> (sh - 4)) : (qhw[w] << (4 - sh));
+                    const uint32_t q = (h2 & 0x30303030u) | lo4;             // four 6-bit values, one per byte
+                    const uint32_t c160 = 0x43204320u;                       // bf16 160 = 128 + 32
+                    uint32_t t0 = __byte_perm(q, 0x43434343u, 0x4140), t1 = __byte_perm(q, 0x43434343u, 0x4342);   // 128+q, exact
+                    __nv_bfloat162 r0 = __hmul2(__hsub2(*(__nv_bfloat162 *) &t0, *(const __nv_bfloat162 *) &c160), *(const __nv_bfloat162 *) &s2);
+                    __nv_bfloat162 r1 = __hmul2(__hsub2(*(__nv_bfloat162 *) &t1, *(const __nv_bfloat162 *) &c160), *(const __nv_bfloat162 *) &s2);
+                    out[ab * 16 + j * 8 + w * 2]     = *(uint32_t *) &r0;
+                    out[ab * 16 + j * 8 + w * 2 + 1] = *(uint32_t *) &r1;
+                }
+            }
+        }
+    }
+};
+
 template <int TYPE>
-__global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w) {
+__global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
+                                                                const __grid_constant__ CUtensorMap tmap_w2) {
     using T = gm_traits<TYPE>;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
+    const int MT = p.MT, BN = p.BN, SA = p.SA, SB = p.SB, RS = p.RS;
     const uint32_t base  = (smem_u32(smem_raw) + 1023u) & ~1023u;
-    const uint32_t b_sm  = base;                                             // [GM_STAGES][BN rows][128 B], 128B-swizzled by TMA
-    const uint32_t r_sm  = b_sm + GM_STAGES * (p.BN * 128);                  // [GM_RAW_STAGES][128 rows][RAW_BYTES]
-    const uint32_t bars  = r_sm + GM_RAW_STAGES * GM_BM * T::RAW_BYTES;
-    const uint32_t fa0 = bars, fb0 = fa0 + 8 * GM_STAGES, empty0 = fb0 + 8 * GM_STAGES;   // A written / B landed / stage consumed
-    const uint32_t rf0 = empty0 + 8 * GM_STAGES, re0 = rf0 + 8 * GM_RAW_STAGES;           // raw block landed / raw block consumed
-    const uint32_t tfull = re0 + 8 * GM_RAW_STAGES, tslot = tfull + 8;
+    const uint32_t b_sm  = base;                                             // [SB][BN rows][128 B], 128B-swizzled by TMA
+    const uint32_t r_sm  = b_sm + SB * (BN * 128);                    // [RS][MT tiles][TILE_BYTES]
+    const uint32_t raw_slot = (uint32_t) (MT * T::TILE_BYTES);
+    const uint32_t bars  = r_sm + RS * raw_slot;
+    const uint32_t fa0 = bars, ea0 = fa0 + 8 * SA, fb0 = ea0 + 8 * SA, eb0 = fb0 + 8 * SB;   // A written / A consumed / B landed / B consumed
+    const uint32_t rf0 = eb0 + 8 * SB, re0 = rf0 + 8 * RS;           // raw block landed / raw block consumed
+    const uint32_t tfull = re0 + 8 * RS, tslot = tfull + 8;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n0 = blockIdx.x * p.BN, m0 = blockIdx.y * GM_BM;
+    const int n0 = blockIdx.x * BN, m0 = blockIdx.y * (MT * GM_BM);
     const int nks = p.K / GM_BK, nunits = p.K / T::RAW_K;
-    const uint32_t tcols = p.BN + 32 * GM_STAGES <= 256 ? 256u : 512u;       // accumulator [0, BN) + A stages [BN, BN + 32*GM_STAGES)
+    // TMEM columns: accumulators [0, MT*BN), then A stages: stage s, tile t at MT*BN + (s*MT + t)*32
+    const uint32_t tneed = (uint32_t) (MT * BN + MT * 32 * SA);
+    const uint32_t tcols = tneed <= 128 ? 128u : tneed <= 256 ? 256u : 512u;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < GM_STAGES; ++s) { mbar_init(fa0 + 8 * s, 4); mbar_init(fb0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
-        for (int s = 0; s < GM_RAW_STAGES; ++s) { mbar_init(rf0 + 8 * s, 1); mbar_init(re0 + 8 * s, 4); }
+        for (int s = 0; s < SA; ++s) { mbar_init(fa0 + 8 * s, 4 * MT); mbar_init(ea0 + 8 * s, 1); }
+        for (int s = 0; s < SB; ++s) { mbar_init(fb0 + 8 * s, 1); mbar_init(eb0 + 8 * s, 1); }
+        for (int s = 0; s < RS; ++s) { mbar_init(rf0 + 8 * s, 1); mbar_init(re0 + 8 * s, GM_PRODUCERS); }
         mbar_init(tfull, 1);
         mbar_fence_init();
     }
-    if (warp == 5) tmem_alloc(tslot, tcols);
-    if (warp == 4 && lane == 0) tma_prefetch_desc(&tmap_x);
-    if (warp == 6 && lane == 0) tma_prefetch_desc(&tmap_w);
+    if (warp == GM_PRODUCERS + 1) tmem_alloc(tslot, tcols);
+    if (warp == GM_PRODUCERS && lane == 0) tma_prefetch_desc(&tmap_x);
+    if (warp == GM_PRODUCERS + 2 && lane == 0) tma_prefetch_desc(&tmap_w);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     uint32_t tmem;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem) : "r"(tslot));
-    const uint32_t tmem_a = tmem + (uint32_t) p.BN;
+    const uint32_t tmem_a = tmem + (uint32_t) (MT * BN);
 
-    if (warp < 4) {
+    if (warp < GM_PRODUCERS) {
         // ===== A producers =====
-        const int row = warp * 32 + lane;
-        const uint32_t lane_base = (uint32_t) (warp * 32) << 16;
-        int stage = 0; uint32_t eph = 1;                                     // parity to wait for on empty[stage] (1: a fresh barrier passes)
-        int slot = 0; uint32_t rph = 0;
-        auto emit = [&](const uint32_t (&o)[32]) {
-            mbar_wait(empty0 + 8 * stage, eph);
-            tc_fence_after();
-            tmem_st32(tmem_a + lane_base + 32u * stage, o);
-            tmem_st_wait();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(fa0 + 8 * stage);
-            if (++stage == GM_STAGES) { stage = 0; eph ^= 1u; }
+        const int grp = warp >> 2, q = warp & 3;
+        const int tile = MT == 2 ? grp : 0;                                  // which 128-row tile this thread's row is in
+        const int rt = q * 32 + lane;                                        // row inside the tile = TMEM lane
+        const uint32_t lane_base = (uint32_t) (q * 32) << 16;
+        const int sshift = SA == 8 ? 3 : SA == 4 ? 2 : 1;
+        int pending = -1;                                                    // stage whose tcgen05.st is still in flight
+        auto flush = [&]() {
+            if (pending >= 0) {
+                tmem_st_wait(); tc_fence_before(); __syncwarp();
+                if (lane == 0) mbar_arrive(fa0 + 8 * pending);
+                pending = -1;
+            }
         };
+        auto emit = [&](int ks, const uint32_t (&o)[32]) {
+            flush();                                                         // the expansion of this step overlapped the previous store
+            const int stage = ks & (SA - 1);
+            mbar_wait(ea0 + 8 * stage, (((uint32_t) ks >> sshift) & 1u) ^ 1u);
+            tc_fence_after();
+            tmem_st32(tmem_a + lane_base + (uint32_t) ((stage * MT + tile) * 32), o);
+            pending = stage;
+        };
+        int slot = 0; uint32_t rph = 0;
         for (int unit = 0; unit < nunits; ++unit) {
             if (!(p.dbg & 1)) mbar_wait(rf0 + 8 * slot, rph);
-            const uint32_t raw = r_sm + (slot * GM_BM + row) * T::RAW_BYTES;
-            typename T::unit u; T::load_unit(raw, u);
+            const uint32_t raw = r_sm + slot * raw_slot + tile * T::TILE_BYTES;
+            typename T::unit u; T::load_unit(raw, rt, unit, u);
             uint32_t o[32];
-            if (p.dbg & 2) { for (int c = 0; c < 32; ++c) o[c] = u.sc_lo; emit(o); emit(o); emit(o); emit(o); }
+            const int ks = unit * 4;
+            if (p.dbg & 2) { for (int c = 0; c < 32; ++c) o[c] = __float_as_uint(u.d); for (int g = 0; g < 4; ++g) if (MT == 2 || (g & 1) == grp) emit(ks + g, o); }
             else {
-            T::template expand<0>(raw, u, o); emit(o);
-            T::template expand<1>(raw, u, o); emit(o);
-            T::template expand<2>(raw, u, o); emit(o);
-            T::template expand<3>(raw, u, o); emit(o);
+                if (MT == 2 || grp == 0) { T::template expand<0>(raw, rt, u, o); emit(ks + 0, o); }
+                if (MT == 2 || grp == 1) { T::template expand<1>(raw, rt, u, o); emit(ks + 1, o); }
+                if (MT == 2 || grp == 0) { T::template expand<2>(raw, rt, u, o); emit(ks + 2, o); }
+                if (MT == 2 || grp == 1) { T::template expand<3>(raw, rt, u, o); emit(ks + 3, o); }
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(re0 + 8 * slot);
-            if (++slot == GM_RAW_STAGES) { slot = 0; rph ^= 1u; }
+            if (++slot == RS) { slot = 0; rph ^= 1u; }
         }
+        flush();
         // ===== epilogue: TMEM -> registers -> dst (columns of dst are contiguous along M) =====
         mbar_wait(tfull, 0);
         tc_fence_after();
-        const int mm = m0 + row;
+        const int mm = m0 + tile * GM_BM + q * 32 + lane;
+        const int c_begin = MT == 2 ? 0 : grp * (BN / 2), c_end = MT == 2 ? BN : c_begin + BN / 2;   // MT=1: the groups split the columns
         float * drow = p.dst + mm;
-        for (int c0 = 0; c0 < p.BN; c0 += 16) {
+        for (int c0 = c_begin; c0 < c_end; c0 += 16) {
             if (n0 + c0 >= p.N) break;
             uint32_t r[16];
-            tmem_ld16(tmem + lane_base + (uint32_t) c0, r);
+            tmem_ld16(tmem + lane_base + (uint32_t) (tile * BN + c0), r);
             tmem_ld_wait();
             if (mm < p.M) {
 #pragma unroll
@@ -182,49 +253,72 @@ __global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const
             }
         }
         tc_fence_before();
-    } else if (warp == 4) {
-        // ===== B producer =====
-        if (lane == 0) {
-            int stage = 0; uint32_t eph = 1;
-            for (int ks = 0; ks < nks; ++ks) {
-                mbar_wait(empty0 + 8 * stage, eph);
-                mbar_arrive_expect_tx(fb0 + 8 * stage, (uint32_t) p.BN * 128u);
-                tma_load_2d(b_sm + stage * (p.BN * 128), &tmap_x, ks * GM_BK, n0, fb0 + 8 * stage);
-                if (++stage == GM_STAGES) { stage = 0; eph ^= 1u; }
+    } else if (warp == GM_PRODUCERS) {
+        // ===== B producer (control flow is warp-uniform; one elected lane issues) =====
+        int stage = 0; uint32_t eph = 1;
+        for (int ks = 0; ks < nks; ++ks) {
+            mbar_wait(eb0 + 8 * stage, eph);
+            if (elect_one()) {
+                if (p.dbg & 4) mbar_arrive(fb0 + 8 * stage);
+                else {
+                    mbar_arrive_expect_tx(fb0 + 8 * stage, (uint32_t) BN * 128u);
+                    tma_load_2d(b_sm + stage * (BN * 128), &tmap_x, ks * GM_BK, n0, fb0 + 8 * stage);
+                }
             }
+            __syncwarp();
+            if (++stage == SB) { stage = 0; eph ^= 1u; }
         }
-    } else if (warp == 5) {
+    } else if (warp == GM_PRODUCERS + 1) {
         // ===== MMA issuer =====
-        if (lane == 0) {
-            const uint32_t idesc = umma_idesc_bf16(GM_BM, p.BN);
-            int stage = 0; uint32_t fph = 0;
-            for (int ks = 0; ks < nks; ++ks) {
-                mbar_wait(fa0 + 8 * stage, fph);
-                mbar_wait(fb0 + 8 * stage, fph);
-                tc_fence_after();
-                const uint64_t db = umma_desc_sw128(b_sm + stage * (p.BN * 128));
+        const uint32_t idesc = umma_idesc_bf16(GM_BM, BN);
+        int sa = 0, sb = 0; uint32_t pa = 0, pb = 0;
+        for (int ks = 0; ks < nks; ++ks) {
+            mbar_wait(fa0 + 8 * sa, pa);
+            mbar_wait(fb0 + 8 * sb, pb);
+            tc_fence_after();
+            const uint64_t db = umma_desc_sw128(b_sm + sb * (BN * 128));
+            const uint32_t ta = tmem_a + (uint32_t) (sa * MT * 32);
+            if (elect_one()) {
 #pragma unroll
-                for (int k = 0; k < GM_BK / 16; ++k) umma_f16_ts(tmem, tmem_a + 32u * stage + 8u * k, db + 2 * k, idesc, (uint32_t) ((ks | k) != 0));
-                umma_commit(empty0 + 8 * stage);
-                if (++stage == GM_STAGES) { stage = 0; fph ^= 1u; }
+                for (int k = 0; k < GM_BK / 16; ++k) umma_f16_ts(tmem, ta + 8u * k, db + 2 * k, idesc, (uint32_t) ((ks | k) != 0));
+                if (MT == 2) {
+#pragma unroll
+                    for (int k = 0; k < GM_BK / 16; ++k) umma_f16_ts(tmem + (uint32_t) BN, ta + 32u + 8u * k, db + 2 * k, idesc, (uint32_t) ((ks | k) != 0));
+                }
+                umma_commit(ea0 + 8 * sa);
+                umma_commit(eb0 + 8 * sb);
             }
-            umma_commit(tfull);
+            __syncwarp();
+            if (++sa == SA) { sa = 0; pa ^= 1u; }
+            if (++sb == SB) { sb = 0; pb ^= 1u; }
         }
+        if (elect_one()) umma_commit(tfull);
         __syncwarp();
     } else {
-        // ===== raw weight producer: one 128-row x RAW_BYTES box per 256-K block (rows past M are zero-filled) =====
-        if (lane == 0 && !(p.dbg & 1)) {
+        // ===== raw weight producer: one TMA box per 128-row tile and 256-K block (rows past M are zero-filled) =====
+        if (!(p.dbg & 1)) {
             int slot = 0; uint32_t eph = 1;
             for (int unit = 0; unit < nunits; ++unit) {
                 mbar_wait(re0 + 8 * slot, eph);
-                mbar_arrive_expect_tx(rf0 + 8 * slot, (uint32_t) (GM_BM * T::RAW_BYTES));
-                tma_load_2d(r_sm + slot * (GM_BM * T::RAW_BYTES), &tmap_w, unit * T::RAW_BYTES, m0, rf0 + 8 * slot);
-                if (++slot == GM_RAW_STAGES) { slot = 0; eph ^= 1u; }
+                if (elect_one()) {
+                    mbar_arrive_expect_tx(rf0 + 8 * slot, raw_slot);
+                    for (int t = 0; t < MT; ++t) {
+                        const uint32_t dstp = r_sm + slot * raw_slot + t * T::TILE_BYTES;
+                        if (TYPE == B200_TYPE_Q6_K) {
+                            tma_load_4d(dstp, &tmap_w, (unit & 7) * 16, 0, unit >> 3, m0 + t * GM_BM, rf0 + 8 * slot);
+                            tma_load_3d(dstp + GM_BM * T::ROW_BYTES, &tmap_w2, 0, unit >> 3, m0 + t * GM_BM, rf0 + 8 * slot);
+                        } else {
+                            tma_load_2d(dstp, &tmap_w, unit * T::ROW_BYTES, m0 + t * GM_BM, rf0 + 8 * slot);
+                        }
+                    }
+                }
+                __syncwarp();
+                if (++slot == RS) { slot = 0; eph ^= 1u; }
             }
         }
     }
     __syncthreads();
-    if (warp == 5) { tc_fence_after(); tmem_dealloc(tmem, tcols); }
+    if (warp == GM_PRODUCERS + 1) { tc_fence_after(); tmem_dealloc(tmem, tcols); }
 }
 
 // ---- host side -------------------------------------------------------------------------------------------------------------
@@ -245,19 +339,22 @@ static encode_tiled_fn get_encode_tiled() {
 bool b200_gemm_supported(const b200_tensor * w, const b200_tensor * x) {
     static const int off = getenv("GGML_B200_NO_GEMM") != nullptr;
     if (off) return false;
-    if (w->type != B200_TYPE_Q4_K || (w->flags & B200_TENSOR_REPACKED)) return false;
+    const bool q4k = w->type == B200_TYPE_Q4_K && !(w->flags & B200_TENSOR_REPACKED);
+    const bool q6k = w->type == B200_TYPE_Q6_K && (w->flags & B200_TENSOR_REPACKED) && w->ne[0] % 2048 == 0;   // group layout of b200_repack.cu
+    if (!q4k && !q6k) return false;
     if (w->ne[2] != 1 || w->ne[3] != 1 || x->ne[2] != 1 || x->ne[3] != 1) return false;
     if (((uintptr_t) w->data & 15) || (w->nb[1] & 15) || ((uintptr_t) x->data & 15) || (x->nb[1] & 15)) return false;
     if (w->ne[0] % 256 != 0 || w->ne[0] > (1 << 20) || w->ne[1] > (1 << 30) || x->ne[1] > (1 << 30)) return false;
     return x->ne[1] > B200_GEMV_MAX_COLS;
 }
 
-static int gemm_pick_bn(const b200_ctx * ctx, int64_t M, int64_t N) {
+// tile shape.  Measured on B200 (profiles/r1_gemm_sweep.txt): 128x256 tiles beat two stacked 128x128 tiles (MT=2) whenever they
+// give at least ~0.7 waves; below that, narrower tiles that fill more SMs win.
+static void gemm_pick_tile(const b200_ctx * ctx, int64_t M, int64_t N, int & MT, int & BN) {
+    MT = 1;
     const int64_t mt = (M + GM_BM - 1) / GM_BM;
-    if (N > 128 && mt * ((N + 255) / 256) >= (int64_t) ctx->sm_count * 3 / 4) return 256;
-    if (N > 64) return 128;
-    if (N > 32) return 64;
-    return 32;
+    if (N > 128 && mt * ((N + 255) / 256) >= (int64_t) ctx->sm_count * 7 / 10) { BN = 256; return; }
+    BN = N > 64 ? 128 : N > 32 ? 64 : 32;
 }
 
 // image = bf16 [N][K] activations (b200_launch_act_bf16)
@@ -269,7 +366,17 @@ int b200_launch_gemm_q(b200_ctx * ctx, const b200_tensor * w, const void * image
     p.dst = (float *) dst->data; p.d_ld = dst->nb[1] / 4;
     p.M = (int) w->ne[1]; p.N = (int) N; p.K = (int) w->ne[0];
     static const int force_bn = getenv("GGML_B200_GEMM_BN") ? atoi(getenv("GGML_B200_GEMM_BN")) : 0;
-    p.BN = force_bn ? force_bn : gemm_pick_bn(ctx, p.M, p.N);
+    static const int force_mt = getenv("GGML_B200_GEMM_MT") ? atoi(getenv("GGML_B200_GEMM_MT")) : 0;
+    gemm_pick_tile(ctx, p.M, p.N, p.MT, p.BN);
+    if (force_bn) p.BN = force_bn;
+    if (force_mt) p.MT = force_mt;
+    if (p.MT == 2 && p.BN > 128) p.BN = 128;                              // TMEM: 2*BN accumulator columns + 256 columns of A stages
+    static const int force_s = getenv("GGML_B200_GEMM_S") ? atoi(getenv("GGML_B200_GEMM_S")) : 0, force_rs = getenv("GGML_B200_GEMM_RS") ? atoi(getenv("GGML_B200_GEMM_RS")) : 0;
+    static const int force_sb = getenv("GGML_B200_GEMM_SB") ? atoi(getenv("GGML_B200_GEMM_SB")) : 0;
+    // depth in TIME is what hides the TMA and producer latencies (~1 us): as many 64-K steps in flight as TMEM and smem allow
+    p.SA = force_s ? force_s : (p.MT * p.BN + p.MT * 256 <= 512 ? 8 : 4);
+    p.RS = force_rs ? force_rs : (p.MT == 2 ? 2 : 3);
+    p.SB = force_sb;
     static const int dbg = getenv("GGML_B200_GEMM_DBG") ? atoi(getenv("GGML_B200_GEMM_DBG")) : 0;
     p.dbg = dbg;
     CUtensorMap tmap;
@@ -280,22 +387,46 @@ int b200_launch_gemm_q(b200_ctx * ctx, const b200_tensor * w, const void * image
     const CUresult cr = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (void *) image, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (cr != CUDA_SUCCESS) { b200_set_error("gemm: cuTensorMapEncodeTiled failed (%d)", (int) cr); return B200_ERR_CUDA; }
-    using T = gm_traits<B200_TYPE_Q4_K>;
-    // the weight rows as a 2-D byte tensor: box = one 256-K block of 128 consecutive rows
-    CUtensorMap tmap_w;
-    const cuuint64_t wdim[2] = { (cuuint64_t) (p.K / T::RAW_K) * T::RAW_BYTES, (cuuint64_t) p.M };
-    const cuuint64_t wstr[1] = { (cuuint64_t) p.w_nb1 };
-    const cuuint32_t wbox[2] = { T::RAW_BYTES, GM_BM };
-    const CUresult cw = encode(&tmap_w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, (void *) p.w, wdim, wstr, wbox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    const bool q6 = w->type == B200_TYPE_Q6_K;
+    const int tile_bytes = q6 ? gm_traits<B200_TYPE_Q6_K>::TILE_BYTES : gm_traits<B200_TYPE_Q4_K>::TILE_BYTES;
+    CUtensorMap tmap_w, tmap_w2;
+    CUresult cw;
+    if (!q6) {
+        // q4_K: the weight rows as a 2-D byte tensor; box = one 144-byte block of 128 consecutive rows
+        const cuuint64_t wdim[2] = { (cuuint64_t) (p.K / 256) * 144, (cuuint64_t) p.M };
+        const cuuint64_t wstr[1] = { (cuuint64_t) p.w_nb1 };
+        const cuuint32_t wbox[2] = { 144, GM_BM };
+        cw = encode(&tmap_w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, (void *) p.w, wdim, wstr, wbox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        tmap_w2 = tmap_w;
+    } else {
+        // repacked q6_K: {byte in unit-row (128), unit-row (13), group (K/2048), weight row}; box = column b (16 B) of the 13 unit-rows
+        const cuuint64_t wdim[4] = { 128, 13, (cuuint64_t) (p.K / 2048), (cuuint64_t) p.M };
+        const cuuint64_t wstr[3] = { 128, 1680, (cuuint64_t) p.w_nb1 };
+        const cuuint32_t wbox[4] = { 16, 13, 1, GM_BM }, e4[4] = { 1, 1, 1, 1 };
+        cw = encode(&tmap_w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 4, (void *) p.w, wdim, wstr, wbox, e4, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        // the eight fp16 d's of a group: 16 B at byte 1664 of every group
+        const cuuint64_t ddim[3] = { 16, (cuuint64_t) (p.K / 2048), (cuuint64_t) p.M };
+        const cuuint64_t dstr[2] = { 1680, (cuuint64_t) p.w_nb1 };
+        const cuuint32_t dbox[3] = { 16, 1, GM_BM };
+        if (cw == CUDA_SUCCESS)
+            cw = encode(&tmap_w2, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void *) (p.w + 1664), ddim, dstr, dbox, e4, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    }
     if (cw != CUDA_SUCCESS) { b200_set_error("gemm: cuTensorMapEncodeTiled (weights) failed (%d)", (int) cw); return B200_ERR_CUDA; }
-    const size_t smem = 1024 + (size_t) GM_STAGES * (p.BN * 128) + GM_RAW_STAGES * GM_BM * T::RAW_BYTES + 8 * (3 * GM_STAGES + 2 * GM_RAW_STAGES + 1) + 16;
+    const size_t raw_bytes = (size_t) p.RS * p.MT * tile_bytes;
+    if (!force_sb) { p.SB = (int) ((220 * 1024 - 2048 - raw_bytes) / ((size_t) p.BN * 128)); if (p.SB > 8) p.SB = 8; }
+    if (p.SB < 2) { b200_set_error("gemm: tile does not fit in shared memory"); return B200_ERR_UNSUPPORTED; }
+    const size_t smem = 1024 + (size_t) p.SB * (p.BN * 128) + raw_bytes + 8 * (2 * p.SA + 2 * p.SB + 2 * p.RS + 1) + 16;
     if (!ctx->attr_done[5]) {
         B200_CUDA_TRY(cudaFuncSetAttribute(k_gemm_q<B200_TYPE_Q4_K>, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
+        B200_CUDA_TRY(cudaFuncSetAttribute(k_gemm_q<B200_TYPE_Q6_K>, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
         ctx->attr_done[5] = 1;
     }
-    dim3 grid((unsigned) ((p.N + p.BN - 1) / p.BN), (unsigned) ((p.M + GM_BM - 1) / GM_BM));
-    B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q4_K><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap, tmap_w));
+    dim3 grid((unsigned) ((p.N + p.BN - 1) / p.BN), (unsigned) ((p.M + p.MT * GM_BM - 1) / (p.MT * GM_BM)));
+    if (q6) B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q6_K><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap, tmap_w, tmap_w2));
+    else    B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q4_K><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap, tmap_w, tmap_w2));
     return B200_OK;
 }
 

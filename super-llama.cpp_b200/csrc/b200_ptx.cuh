@@ -75,10 +75,26 @@ static __device__ __forceinline__ int dp4a_us(unsigned a, int b, int c) {
     return d;
 }
 
+// one lane of a converged warp (the others get false); keeps the surrounding control flow warp-uniform so that descriptors
+// and barrier addresses stay in uniform registers
+static __device__ __forceinline__ bool elect_one() {
+    uint32_t pred = 0;
+    asm volatile("{\n .reg .b32 rx;\n .reg .pred px;\n elect.sync rx|px, %1;\n @px mov.s32 %0, 1;\n}" : "+r"(pred) : "r"(0xffffffffu));
+    return pred != 0;
+}
+
 // ---- TMA tiled load (2-D tensor map), completion on an mbarrier -------------------------------------------------------
 static __device__ __forceinline__ void tma_load_2d(uint32_t dst, const void * tmap, int c0, int c1, uint32_t bar) {
     asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
                  :: "r"(dst), "l"(tmap), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+static __device__ __forceinline__ void tma_load_3d(uint32_t dst, const void * tmap, int c0, int c1, int c2, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                 :: "r"(dst), "l"(tmap), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+static __device__ __forceinline__ void tma_load_4d(uint32_t dst, const void * tmap, int c0, int c1, int c2, int c3, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+                 :: "r"(dst), "l"(tmap), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
 }
 static __device__ __forceinline__ void tma_prefetch_desc(const void * tmap) {
     asm volatile("prefetch.tensormap [%0];" :: "l"(tmap) : "memory");

@@ -123,6 +123,18 @@ def test_mul_mat_prefill_gemm(ctx, orc, t, M, N, K):
     _check_prefill(orc, got, t, w, K, M, x, N)
 
 
+@pytest.mark.parametrize("M,N,K", [(128, 16, 2048), (200, 33, 2048), (300, 260, 4096), (1024, 512, 4096), (256, 128, 14336)])
+def test_mul_mat_prefill_gemm_q6_K_repacked(ctx, B, orc, M, N, K):
+    """q6_K weights in the load-time group layout (b200_repack) through the tcgen05 GEMM: 4-D TMA box per 256-K block"""
+    rng = np.random.default_rng(M + 5 * N + K)
+    w = O.random_blocks(rng, O.Q6_K, K, M)
+    x = rng.standard_normal((N, K)).astype(np.float32)
+    dw = ctx.upload(B.Q6_K, [K, M], w); ctx.repack(dw)
+    dx = ctx.upload(B.F32, [K, N], x); dd = ctx.empty(B.F32, [M, N])
+    ctx.mul_mat(dw, dx, dd)
+    _check_prefill(orc, ctx.download(dd).reshape(1, 1, N, M), O.Q6_K, w, K, M, x, N)
+
+
 @pytest.mark.parametrize("t", GEMM_TYPES)
 def test_mul_mat_prefill_gemm_strided(ctx, B, orc, t):
     """activation rows and result columns with padding between them (views into larger buffers)"""
