@@ -177,11 +177,11 @@ size_t b200_tensor_span(const b200_tensor * t) {                 // ggml_nbytes
     return n;
 }
 void b200_note_write(b200_ctx * ctx, const void * ptr, size_t nbytes) {
-    if (!ctx->qcache.valid) return;
-    const char * a = (const char *) ctx->qcache.data, * b = (const char *) ptr;
-    if (b < a + ctx->qcache.span && a < b + nbytes) ctx->qcache.valid = 0;
+    const char * b = (const char *) ptr;
+    if (ctx->qcache.valid) { const char * a = (const char *) ctx->qcache.data; if (b < a + ctx->qcache.span && a < b + nbytes) ctx->qcache.valid = 0; }
+    if (ctx->mcache.valid) { const char * a = (const char *) ctx->mcache.data; if (b < a + ctx->mcache.span && a < b + nbytes) ctx->mcache.valid = 0; }
 }
-extern "C" int b200_ctx_invalidate(b200_ctx * ctx) { ctx->qcache.valid = 0; return B200_OK; }
+extern "C" int b200_ctx_invalidate(b200_ctx * ctx) { ctx->qcache.valid = 0; ctx->mcache.valid = 0; return B200_OK; }
 
 // q8_1 image of x in scratch slot 0, reused when the same activation tensor feeds consecutive matmuls
 static const void * quantized_activations(b200_ctx * ctx, const b200_tensor * x, int variant, int * rc) {
@@ -314,9 +314,12 @@ extern "C" int b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const 
     }
     if (mask && (mask->ne[0] < k->ne[1] || mask->ne[1] < q->ne[1])) { b200_set_error("flash_attn_ext: mask too small"); return B200_ERR_INVALID; }
     static const int no_dec = getenv("GGML_B200_FATTN_VEC") != nullptr;
-    const int rc = (!no_dec && b200_fattn_dec_supported(q, k, v))
-        ? b200_launch_fattn_dec(ctx, q, k, v, mask, sinks, dst, scale, max_bias, logit_softcap)
-        : b200_launch_fattn_vec(ctx, q, k, v, mask, sinks, dst, scale, max_bias, logit_softcap);
+    int rc = B200_ERR_UNSUPPORTED;
+    if (!no_dec && b200_fattn_dec_supported(q, k, v)) rc = b200_launch_fattn_dec(ctx, q, k, v, mask, sinks, dst, scale, max_bias, logit_softcap);
+    else {
+        if (!no_dec && b200_fattn_tc_supported(q, k, v, mask, dst)) rc = b200_launch_fattn_tc(ctx, q, k, v, mask, sinks, dst, scale, max_bias, logit_softcap);
+        if (rc == B200_ERR_UNSUPPORTED) rc = b200_launch_fattn_vec(ctx, q, k, v, mask, sinks, dst, scale, max_bias, logit_softcap);
+    }
     b200_note_write(ctx, dst->data, b200_tensor_span(dst));
     return rc;
 }

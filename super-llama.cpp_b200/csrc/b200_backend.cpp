@@ -237,7 +237,7 @@ static int compute_node(b200_ctx * ctx, ggml_tensor * node) {
 static enum ggml_status be_graph_compute(ggml_backend_t be, ggml_cgraph * g) {
     b200_backend_ctx * c = (b200_backend_ctx *) be->context;
     if (cudaSetDevice(c->device) != cudaSuccess) return GGML_STATUS_FAILED;
-    c->ctx->qcache.valid = 0;      // tensors may have been rewritten through buffer set_tensor since the last graph
+    c->ctx->qcache.valid = 0; c->ctx->mcache.valid = 0;      // tensors may have been rewritten through buffer set_tensor since the last graph
     for (int i = 0; i < g->n_nodes; ++i) {
         ggml_tensor * node = g->nodes[i];
         if (op_is_view((int) node->op) || tensor_nelements(node) == 0) continue;

@@ -68,6 +68,8 @@ struct b200_ctx {
     int          capturing;
     // the q8_1 image of the most recently quantized activation tensor (scratch slot 0): wq/wk/wv and gate/up share theirs
     struct { const void * data; int64_t ne[4]; size_t nb[4]; size_t span; int variant; int valid; } qcache;
+    // per-tile liveness flags of the most recently scanned attention mask (scratch slot 2)
+    struct { const void * data; int64_t ne[4]; size_t nb[4]; size_t span; int64_t n; int valid; } mcache;
     int          attr_done[8];
     int          pdl;                // launch the streaming GEMV with programmatic dependent launch (GGML_B200_NO_PDL=1 disables)       // per-kernel one-time cudaFuncSetAttribute flags (a ctx is bound to one device)
 };
@@ -156,6 +158,10 @@ bool b200_fattn_dec_supported(const b200_tensor * q, const b200_tensor * k, cons
 int  b200_launch_fattn_dec(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v,
                            const b200_tensor * mask, const b200_tensor * sinks, b200_tensor * dst,
                            float scale, float max_bias, float softcap);
+bool b200_fattn_tc_supported(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask, const b200_tensor * dst);
+int  b200_launch_fattn_tc(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v,
+                          const b200_tensor * mask, const b200_tensor * sinks, b200_tensor * dst,
+                          float scale, float max_bias, float softcap);     // B200_ERR_UNSUPPORTED = use another kernel
 bool b200_gemv_stream_supported(const b200_tensor * w, const b200_tensor * x);
 int  b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, const void * image, float * const * dst);
 #define B200_GEMV_FUSED_QUANT_MAX_K 8192    // above this, one quantize launch + image beats one quantization per CTA

@@ -325,7 +325,7 @@ __global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const
 typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
                                     const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
                                     CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-static encode_tiled_fn get_encode_tiled() {
+encode_tiled_fn b200_get_encode_tiled() {
     static encode_tiled_fn fn = nullptr; static int tried = 0;
     if (!tried) {
         tried = 1;
@@ -359,7 +359,7 @@ static void gemm_pick_tile(const b200_ctx * ctx, int64_t M, int64_t N, int & MT,
 
 // image = bf16 [N][K] activations (b200_launch_act_bf16)
 int b200_launch_gemm_q(b200_ctx * ctx, const b200_tensor * w, const void * image, int64_t N, b200_tensor * dst) {
-    encode_tiled_fn encode = get_encode_tiled();
+    encode_tiled_fn encode = b200_get_encode_tiled();
     if (!encode) { b200_set_error("gemm: cuTensorMapEncodeTiled not available from the driver"); return B200_ERR_CUDA; }
     gm_args p;
     p.w = (const uint8_t *) w->data; p.w_nb1 = w->nb[1];

@@ -148,6 +148,47 @@ def test_flash_attn_decode_8k_context(ctx, orc):
     assert O.nmse(orc.flash_attn_ext(q, k, v, mask, None, 0.0884), got) < 1e-6
 
 
+def causal_mask(n_batch, n_kv, n_past, pad=64):
+    """the KQ mask llama.cpp builds for a prefill ubatch: query i sees keys 0..n_past+i, everything else -inf; rows padded"""
+    nm = (n_batch + pad - 1) // pad * pad
+    m = np.full((1, 1, nm, n_kv), -np.inf, dtype=np.float32)
+    for i in range(n_batch):
+        m[0, 0, i, : n_past + i + 1] = 0.0
+    return m.astype(np.float16)
+
+
+@pytest.mark.parametrize("D", [64, 128])
+@pytest.mark.parametrize("n_batch,n_kv,n_past", [(512, 512, 0), (200, 768, 300), (64, 1024, 900), (16, 256, 17), (129, 130, 1)])
+def test_flash_attn_prefill_causal(ctx, orc, D, n_batch, n_kv, n_past):
+    """prefill attention (tcgen05 kernel): causal mask with whole tiles masked (skipped), partial tiles, ragged query and
+    key counts, GQA; checked against the fp32 oracle and against the reference's fp16 numerics"""
+    rng = np.random.default_rng(D + n_batch + n_kv)
+    H, Hk = 8, 2
+    q = rng.standard_normal((1, H, n_batch, D)).astype(np.float32)
+    k = rng.standard_normal((1, Hk, n_kv, D)).astype(np.float16)
+    v = rng.standard_normal((1, Hk, n_kv, D)).astype(np.float16)
+    mask = causal_mask(n_batch, n_kv, n_past)
+    sc = 1.0 / np.sqrt(D)
+    got = ctx.flash_attn_ext_host(q, k, v, mask, None, sc)
+    assert np.isfinite(got).all()
+    assert O.nmse(orc.flash_attn_ext(q, k, v, mask, None, sc), got) < 2e-6
+    assert O.nmse(orc.flash_attn_ext(q, k, v, mask, None, sc, faithful=True), got) < 5e-4
+
+
+@pytest.mark.parametrize("opts", [dict(sinks=True), dict(max_bias=8.0), dict(softcap=10.0), dict(nomask=True), dict(sinks=True, max_bias=8.0, softcap=10.0)])
+def test_flash_attn_prefill_options(ctx, orc, opts):
+    rng = np.random.default_rng(len(str(opts)) + 99)
+    S, H, Hk, N, KV, D = 2, 4, 2, 150, 333, 128
+    q = rng.uniform(-1, 1, (S, H, N, D)).astype(np.float32)
+    k = rng.uniform(-1, 1, (S, Hk, KV, D)).astype(np.float16)
+    v = rng.uniform(-1, 1, (S, Hk, KV, D)).astype(np.float16)
+    mask = None if opts.get("nomask") else make_mask(rng, 192, KV)
+    sinks = rng.uniform(-10, 10, H).astype(np.float32) if opts.get("sinks") else None
+    args = (0.0884, opts.get("max_bias", 0.0), opts.get("softcap", 0.0))
+    got = ctx.flash_attn_ext_host(q, k, v, mask, sinks, *args)
+    assert O.nmse(orc.flash_attn_ext(q, k, v, mask, sinks, *args), got) < 2e-6
+
+
 def test_flash_attn_rejects_unsupported(ctx, B):
     dq = ctx.empty(B.F32, [40, 1, 1, 1]); dk = ctx.empty(B.F16, [40, 8, 1, 1]); dd = ctx.empty(B.F32, [40, 1, 1, 1])
     with pytest.raises(B.B200Error):
