@@ -118,9 +118,11 @@ class HotPathModel:
     """The hot-path nodes of one llama decode/prefill step over device-resident random-init Q4_K_M weights.
     rank/world: split-mode=row shard (rows [lo, hi) of every weight); world == 1 is the whole model."""
 
-    def __init__(self, B, ctx, cfg, n_tokens, depth, rank=0, world=1, seed=1234, alloc=None):
+    def __init__(self, B, ctx, cfg, n_tokens, depth, rank=0, world=1, seed=1234, alloc=None, dist=None):
         self.B, self.ctx, self.cfg, self.N = B, ctx, cfg, n_tokens
         self.rank, self.world = rank, world
+        from row_split import RowSplit                      # partition rule + gather shared with tests/test_row_split_gloo.py
+        self.rs = RowSplit(dist, world, rank, 32)
         rng = np.random.default_rng(seed + rank)
         types, out_type = q4_k_m_layer_types(cfg)
         shapes = weight_shapes(cfg)
@@ -128,7 +130,7 @@ class HotPathModel:
         self.weight_bytes = 0
 
         def make_weight(t, K, M):
-            lo, hi = B.split_row_range(M, world, rank, 32) if world > 1 else (0, M)
+            lo, hi = self.rs.row_range(M)
             ml = hi - lo
             w = ctx.empty(t, [K, ml])
             nb, blk = w.nbytes, TSIZE[t]
@@ -194,7 +196,7 @@ class HotPathModel:
             M, N = dst.ne[0], dst.ne[1]
             local = dst.view([hi - lo, N, 1, 1], [4, M * 4, M * 4 * N, M * 4 * N], offset=lo * 4)   # rows [lo, hi) of every column
             self.ctx.mul_mat(wt, x, local)
-            self.gather(dst, lo, hi)
+            self.gather(dst, M, N)
 
     def _mm_group(self, ws, x, dsts):
         """MUL_MATs that share src1: one fused launch per run of equal weight types (the plugin fuses the same nodes)"""
@@ -241,6 +243,18 @@ class HotPathModel:
 
     def attn_flops(self):
         return 2 * self.cfg["n_head"] * self.N * 2 * self.cfg["head_dim"] * self.n_kv * self.cfg["n_layer"]
+
+
+def traffic_per_launch(algorithmic_bytes_per_launch):
+    """DRAM bytes per launch of the dominant kernel: dram__bytes_read.sum + dram__bytes_write.sum of the committed
+    `ncu --set full` capture (profiles/*_traffic.json) relative to the algorithmic bytes of the same launches, applied to
+    this run's per-launch algorithmic bytes.  None when no capture is committed."""
+    try:
+        cands = sorted(f for f in os.listdir(os.path.join(ROOT, "profiles")) if f.endswith("_traffic.json"))
+        d = json.load(open(os.path.join(ROOT, "profiles", cands[-1])))
+        return algorithmic_bytes_per_launch * float(d["traffic_over_algorithmic"])
+    except Exception:
+        return None
 
 
 # ------------------------------------------------------------------------------------------------------------
@@ -356,15 +370,14 @@ def run_b200(args):
         dt.torch = buf
         return dt
 
-    tg = HotPathModel(B, ctx, cfg, 1, args.depth, rank, world, alloc=alloc)
+    tg = HotPathModel(B, ctx, cfg, 1, args.depth, rank, world, alloc=alloc, dist=dist)
     if world > 1:
         ext = torch.cuda.ExternalStream(ctx.stream, device=f"cuda:{local}")
 
-        def gather(full, lo, hi):
-            # even split (rounding 32 divides every row count here): rank r's slice sits at rows [r*m, (r+1)*m)
-            t = full.torch.view(torch.float32)
+        def gather(full, M, N):
+            # the one exchange step of split-mode=row: all-gather of the row slices, issued on the context's own stream
             with torch.cuda.stream(ext):
-                dist.all_gather_into_tensor(t, t[lo:hi])        # in place: input is the rank's own slice of the output
+                tg.rs.gather(full.torch.view(torch.float32), M, N)
         tg.gather = gather
 
     def timed(model, steps, warmup, use_graph):
@@ -472,7 +485,7 @@ def run_b200(args):
                        "l2": "weights 4.6 GB >> 126 MB L2, streamed once per step"},
             "hbm_bytes_per_step": total_bytes, "hbm_frac_whole_step": total_bytes / world / (ms_tg * 1e-3) / 1e9 / hbm_gbs,
             "roofline": {"kernel": "k_gemv_stream (TMA-streamed dequant-GEMV with fused q8_1 quantization, q4_K + q6_K)", "bound": "hbm", "achieved": achieved, "peak": hbm_gbs, "unit": "GB/s",
-                         "frac": achieved / hbm_gbs, "traffic": None, "peak_source": f"{peak_src} (MEASURED_PEAKS.json hbm_gbs)",
+                         "frac": achieved / hbm_gbs, "traffic": traffic_per_launch(gemv_bytes_step / max(gemv_n, 1)), "algorithmic_bytes_per_launch": gemv_bytes_step / max(gemv_n, 1), "peak_source": f"{peak_src} (MEASURED_PEAKS.json hbm_gbs)",
                          "launches_per_step": gemv_n, "other_launches_in_timed_graph": other_n, "ms_per_step": gemv_ms_step,
                          "algorithmic_bytes_per_step": gemv_bytes_step,
                          "how": "CUDA events around 10 replays of a graph holding only the MUL_MAT nodes of one token"},
