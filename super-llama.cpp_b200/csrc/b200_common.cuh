@@ -70,7 +70,7 @@ struct b200_ctx {
     struct { const void * data; int64_t ne[4]; size_t nb[4]; size_t span; int variant; int valid; } qcache;
     // per-tile liveness flags of the most recently scanned attention mask (scratch slot 2)
     struct { const void * data; int64_t ne[4]; size_t nb[4]; size_t span; int64_t n; int valid; } mcache;
-    int          attr_done[8];
+    int          attr_done[16];
     int          pdl;                // launch the streaming GEMV with programmatic dependent launch (GGML_B200_NO_PDL=1 disables)       // per-kernel one-time cudaFuncSetAttribute flags (a ctx is bound to one device)
 };
 

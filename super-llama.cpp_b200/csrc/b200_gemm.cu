@@ -73,6 +73,7 @@ template <int TYPE> struct gm_traits;
 
 template <> struct gm_traits<B200_TYPE_Q4_K> {
     static constexpr int RAW_K = 256, ROW_BYTES = 144, TILE_BYTES = GM_BM * 144;   // raw slot of one 128-row tile: [128][144]
+    static constexpr int A_FMT = 1;                                                // A operand written as bf16
     struct unit { float d, dmin; uint32_t sc_lo, sc_hi, m_lo, m_hi; };   // 8 x 6-bit scales / mins, one per byte
     static __device__ __forceinline__ void load_unit(uint32_t tile, int rt, int, unit & u) {
         const uint32_t raw = tile + rt * ROW_BYTES;
@@ -114,6 +115,7 @@ template <> struct gm_traits<B200_TYPE_Q4_K> {
 // whole tile ([128 rows][13][16 B] in the slot); the 16 B of fp16 d's come through a second 3-D map ([128 rows][16 B]).
 template <> struct gm_traits<B200_TYPE_Q6_K> {
     static constexpr int RAW_K = 256, ROW_BYTES = 208, TILE_BYTES = GM_BM * (208 + 16);
+    static constexpr int A_FMT = 1;
     struct unit { float d; int4 sc; };
     static __device__ __forceinline__ void load_unit(uint32_t tile, int rt, int blk, unit & u) {
         u.sc = lds128(tile + rt * ROW_BYTES + 12 * 16);
@@ -150,6 +152,69 @@ template <> struct gm_traits<B200_TYPE_Q6_K> {
                     __nv_bfloat162 r1 = __hmul2(__hsub2(*(__nv_bfloat162 *) &t1, *(const __nv_bfloat162 *) &c160), *(const __nv_bfloat162 *) &s2);
                     out[ab * 16 + j * 8 + w * 2]     = *(uint32_t *) &r0;
                     out[ab * 16 + j * 8 + w * 2 + 1] = *(uint32_t *) &r1;
+                }
+            }
+        }
+    }
+};
+
+// q4_0 / q8_0 in the run-of-8 layout of b200_repack.cu: per 256 weights [8 x fp16 d][8 x qs].
+// q4_0: the same 144-byte rows as q4_K (one 2-D TMA box); value = d (q - 8).
+template <> struct gm_traits<B200_TYPE_Q4_0> {
+    static constexpr int RAW_K = 256, ROW_BYTES = 144, TILE_BYTES = GM_BM * 144;
+    static constexpr int A_FMT = 1;
+    struct unit { int4 d8; };
+    static __device__ __forceinline__ void load_unit(uint32_t tile, int rt, int, unit & u) { u.d8 = lds128(tile + rt * ROW_BYTES); }
+    template <int G> static __device__ __forceinline__ void expand(uint32_t tile, int rt, const unit & u, uint32_t (&out)[32]) {
+        const uint32_t raw = tile + rt * ROW_BYTES;
+        const uint32_t dw = G == 0 ? (uint32_t) u.d8.x : G == 1 ? (uint32_t) u.d8.y : G == 2 ? (uint32_t) u.d8.z : (uint32_t) u.d8.w;   // d of sub-blocks 2G, 2G+1
+        const float2 df = __half22float2(*(const __half2 *) &dw);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {                                        // sub-block 2G + h: low nibbles = elements 0..15, high = 16..31
+            const int4 qv = lds128(raw + 16 + 16 * (2 * G + h));
+            const uint32_t w[4] = { (uint32_t) qv.x, (uint32_t) qv.y, (uint32_t) qv.z, (uint32_t) qv.w };
+            const float d = h ? df.y : df.x;
+            const uint32_t s2 = bf2(d, d), c136 = 0x43084308u;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const uint32_t l4 = w[i] & 0x0F0F0F0Fu, h4 = (w[i] >> 4) & 0x0F0F0F0Fu;
+                uint32_t t[4] = { __byte_perm(l4, 0x43434343u, 0x4140), __byte_perm(l4, 0x43434343u, 0x4342),
+                                  __byte_perm(h4, 0x43434343u, 0x4140), __byte_perm(h4, 0x43434343u, 0x4342) };
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    __nv_bfloat162 r = __hmul2(__hsub2(*(__nv_bfloat162 *) &t[k], *(const __nv_bfloat162 *) &c136), *(const __nv_bfloat162 *) &s2);
+                    out[h * 16 + (k >> 1) * 8 + 2 * i + (k & 1)] = *(uint32_t *) &r;
+                }
+            }
+        }
+    }
+};
+// q8_0: 272-byte rows ([16 B of d][256 quants]) fetched as a 3-D box {16 B, 17, 128 rows}.  int8 -> float without a convert:
+// u = q + 128 dropped into mantissa bits 8..15 of 0x47000000 is exactly 32768 + u, so d*q = fma(f, d, -32896 d) (the rounding of
+// the constant is 2^-24 * 32896 d = 0.002 d, far below the bf16 rounding that follows); pairs are packed to bf16 by F2FP.
+template <> struct gm_traits<B200_TYPE_Q8_0> {
+    static constexpr int RAW_K = 256, ROW_BYTES = 272, TILE_BYTES = GM_BM * 272;
+    static constexpr int A_FMT = 1;
+    struct unit { int4 d8; };
+    static __device__ __forceinline__ void load_unit(uint32_t tile, int rt, int, unit & u) { u.d8 = lds128(tile + rt * ROW_BYTES); }
+    template <int G> static __device__ __forceinline__ void expand(uint32_t tile, int rt, const unit & u, uint32_t (&out)[32]) {
+        const uint32_t raw = tile + rt * ROW_BYTES;
+        const uint32_t dw = G == 0 ? (uint32_t) u.d8.x : G == 1 ? (uint32_t) u.d8.y : G == 2 ? (uint32_t) u.d8.z : (uint32_t) u.d8.w;
+        const float2 df = __half22float2(*(const __half2 *) &dw);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const float d = h ? df.y : df.x, c = -32896.0f * d;
+#pragma unroll
+            for (int v = 0; v < 2; ++v) {
+                const int4 qv = lds128(raw + 16 + 32 * (2 * G + h) + 16 * v);
+                const uint32_t w[4] = { (uint32_t) qv.x, (uint32_t) qv.y, (uint32_t) qv.z, (uint32_t) qv.w };
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const uint32_t wx = w[i] ^ 0x80808080u;
+                    const float f0 = __uint_as_float(__byte_perm(wx, 0x47000000u, 0x7604)), f1 = __uint_as_float(__byte_perm(wx, 0x47000000u, 0x7614));
+                    const float f2 = __uint_as_float(__byte_perm(wx, 0x47000000u, 0x7624)), f3 = __uint_as_float(__byte_perm(wx, 0x47000000u, 0x7634));
+                    out[h * 16 + v * 8 + 2 * i]     = bf2(fmaf(f0, d, c), fmaf(f1, d, c));
+                    out[h * 16 + v * 8 + 2 * i + 1] = bf2(fmaf(f2, d, c), fmaf(f3, d, c));
                 }
             }
         }
@@ -224,7 +289,7 @@ __global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const
             typename T::unit u; T::load_unit(raw, rt, unit, u);
             uint32_t o[32];
             const int ks = unit * 4;
-            if (p.dbg & 2) { for (int c = 0; c < 32; ++c) o[c] = __float_as_uint(u.d); for (int g = 0; g < 4; ++g) if (MT == 2 || (g & 1) == grp) emit(ks + g, o); }
+            if (p.dbg & 2) { for (int c = 0; c < 32; ++c) o[c] = 0x3c003c00u + (uint32_t) c; for (int g = 0; g < 4; ++g) if (MT == 2 || (g & 1) == grp) emit(ks + g, o); }
             else {
                 if (MT == 2 || grp == 0) { T::template expand<0>(raw, rt, u, o); emit(ks + 0, o); }
                 if (MT == 2 || grp == 1) { T::template expand<1>(raw, rt, u, o); emit(ks + 1, o); }
@@ -270,7 +335,7 @@ __global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const
         }
     } else if (warp == GM_PRODUCERS + 1) {
         // ===== MMA issuer =====
-        const uint32_t idesc = umma_idesc_bf16(GM_BM, BN);
+        const uint32_t idesc = umma_idesc_bf16(GM_BM, BN) & ~((T::A_FMT ? 0u : 1u) << 7);     // A format: bf16 or fp16; B is always bf16
         int sa = 0, sb = 0; uint32_t pa = 0, pb = 0;
         for (int ks = 0; ks < nks; ++ks) {
             mbar_wait(fa0 + 8 * sa, pa);
@@ -304,7 +369,9 @@ __global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const
                     mbar_arrive_expect_tx(rf0 + 8 * slot, raw_slot);
                     for (int t = 0; t < MT; ++t) {
                         const uint32_t dstp = r_sm + slot * raw_slot + t * T::TILE_BYTES;
-                        if (TYPE == B200_TYPE_Q6_K) {
+                        if (TYPE == B200_TYPE_Q8_0) {
+                            tma_load_3d(dstp, &tmap_w, 0, unit * 17, m0 + t * GM_BM, rf0 + 8 * slot);
+                        } else if (TYPE == B200_TYPE_Q6_K) {
                             tma_load_4d(dstp, &tmap_w, (unit & 7) * 16, 0, unit >> 3, m0 + t * GM_BM, rf0 + 8 * slot);
                             tma_load_3d(dstp + GM_BM * T::ROW_BYTES, &tmap_w2, 0, unit >> 3, m0 + t * GM_BM, rf0 + 8 * slot);
                         } else {
@@ -341,7 +408,8 @@ bool b200_gemm_supported(const b200_tensor * w, const b200_tensor * x) {
     if (off) return false;
     const bool q4k = w->type == B200_TYPE_Q4_K && !(w->flags & B200_TENSOR_REPACKED);
     const bool q6k = w->type == B200_TYPE_Q6_K && (w->flags & B200_TENSOR_REPACKED) && w->ne[0] % 2048 == 0;   // group layout of b200_repack.cu
-    if (!q4k && !q6k) return false;
+    const bool q40 = w->type == B200_TYPE_Q4_0 && (w->flags & B200_TENSOR_REPACKED), q80 = w->type == B200_TYPE_Q8_0 && (w->flags & B200_TENSOR_REPACKED);
+    if (!q4k && !q6k && !q40 && !q80) return false;
     if (w->ne[2] != 1 || w->ne[3] != 1 || x->ne[2] != 1 || x->ne[3] != 1) return false;
     if (((uintptr_t) w->data & 15) || (w->nb[1] & 15) || ((uintptr_t) x->data & 15) || (x->nb[1] & 15)) return false;
     if (w->ne[0] % 256 != 0 || w->ne[0] > (1 << 20) || w->ne[1] > (1 << 30) || x->ne[1] > (1 << 30)) return false;
@@ -387,12 +455,20 @@ int b200_launch_gemm_q(b200_ctx * ctx, const b200_tensor * w, const void * image
     const CUresult cr = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (void *) image, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (cr != CUDA_SUCCESS) { b200_set_error("gemm: cuTensorMapEncodeTiled failed (%d)", (int) cr); return B200_ERR_CUDA; }
-    const bool q6 = w->type == B200_TYPE_Q6_K;
-    const int tile_bytes = q6 ? gm_traits<B200_TYPE_Q6_K>::TILE_BYTES : gm_traits<B200_TYPE_Q4_K>::TILE_BYTES;
+    const bool q6 = w->type == B200_TYPE_Q6_K, q8 = w->type == B200_TYPE_Q8_0;
+    const int tile_bytes = q6 ? gm_traits<B200_TYPE_Q6_K>::TILE_BYTES : q8 ? gm_traits<B200_TYPE_Q8_0>::TILE_BYTES : gm_traits<B200_TYPE_Q4_K>::TILE_BYTES;
     CUtensorMap tmap_w, tmap_w2;
     CUresult cw;
-    if (!q6) {
-        // q4_K: the weight rows as a 2-D byte tensor; box = one 144-byte block of 128 consecutive rows
+    if (q8) {
+        // repacked q8_0: rows of 17 x 16 B per 256 weights
+        const cuuint64_t wdim[3] = { 16, (cuuint64_t) (p.K / 256) * 17, (cuuint64_t) p.M };
+        const cuuint64_t wstr[2] = { 16, (cuuint64_t) p.w_nb1 };
+        const cuuint32_t wbox[3] = { 16, 17, GM_BM }, e3[3] = { 1, 1, 1 };
+        cw = encode(&tmap_w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void *) p.w, wdim, wstr, wbox, e3, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        tmap_w2 = tmap_w;
+    } else if (!q6) {
+        // q4_K and repacked q4_0: the weight rows as a 2-D byte tensor; box = 144 bytes (256 weights) of 128 consecutive rows
         const cuuint64_t wdim[2] = { (cuuint64_t) (p.K / 256) * 144, (cuuint64_t) p.M };
         const cuuint64_t wstr[1] = { (cuuint64_t) p.w_nb1 };
         const cuuint32_t wbox[2] = { 144, GM_BM };
@@ -422,11 +498,17 @@ int b200_launch_gemm_q(b200_ctx * ctx, const b200_tensor * w, const void * image
     if (!ctx->attr_done[5]) {
         B200_CUDA_TRY(cudaFuncSetAttribute(k_gemm_q<B200_TYPE_Q4_K>, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
         B200_CUDA_TRY(cudaFuncSetAttribute(k_gemm_q<B200_TYPE_Q6_K>, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
+        B200_CUDA_TRY(cudaFuncSetAttribute(k_gemm_q<B200_TYPE_Q4_0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
+        B200_CUDA_TRY(cudaFuncSetAttribute(k_gemm_q<B200_TYPE_Q8_0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
         ctx->attr_done[5] = 1;
     }
     dim3 grid((unsigned) ((p.N + p.BN - 1) / p.BN), (unsigned) ((p.M + p.MT * GM_BM - 1) / (p.MT * GM_BM)));
-    if (q6) B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q6_K><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap, tmap_w, tmap_w2));
-    else    B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q4_K><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap, tmap_w, tmap_w2));
+    switch (w->type) {
+        case B200_TYPE_Q6_K: B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q6_K><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap, tmap_w, tmap_w2)); break;
+        case B200_TYPE_Q8_0: B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q8_0><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap, tmap_w, tmap_w2)); break;
+        case B200_TYPE_Q4_0: B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q4_0><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap, tmap_w, tmap_w2)); break;
+        default:             B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q4_K><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap, tmap_w, tmap_w2)); break;
+    }
     return B200_OK;
 }
 

@@ -247,6 +247,51 @@ template <> struct gemv_traits<B200_TYPE_Q8_0> {
     }
 };
 
+// ---- q4_0 / q8_0 in the load-time run-of-8 layout (b200_repack.cu): [8 x d][8 x qs] per 256 weights, 16-byte aligned quants ----
+#define B200_TYPE_Q4_0_REPACKED 1002
+#define B200_TYPE_Q8_0_REPACKED 1008
+template <> struct gemv_traits<B200_TYPE_Q4_0_REPACKED> {
+    static constexpr int units_per_block = 1, block_elems = 32, block_bytes = 18;
+    template <int NC>
+    static __device__ __forceinline__ void unit(const uint8_t * row, int64_t u, const act_image & a, int64_t col0, float * acc) {
+        const uint8_t * run = row + (u >> 3) * 144; const int c = (int) (u & 7);
+        const float d = __half2float(*(const __half *) (run + 2 * c));
+        const int4 qv = ld_stream_16(run + 16 + 16 * c);
+        const int q[4] = { qv.x, qv.y, qv.z, qv.w };
+#pragma unroll
+        for (int n = 0; n < NC; ++n) {
+            const int8_t *  aq = a.qs + (col0 + n) * a.K + u * 32;
+            const float2    ds = __half22float2(a.ds[(col0 + n) * (a.K >> 5) + u]);
+            const int4 a0 = *(const int4 *) aq, a1 = *(const int4 *) (aq + 16);
+            int s = 0;
+            s = __dp4a(q[0] & 0x0F0F0F0F, a0.x, s); s = __dp4a(q[1] & 0x0F0F0F0F, a0.y, s);
+            s = __dp4a(q[2] & 0x0F0F0F0F, a0.z, s); s = __dp4a(q[3] & 0x0F0F0F0F, a0.w, s);
+            s = __dp4a((q[0] >> 4) & 0x0F0F0F0F, a1.x, s); s = __dp4a((q[1] >> 4) & 0x0F0F0F0F, a1.y, s);
+            s = __dp4a((q[2] >> 4) & 0x0F0F0F0F, a1.z, s); s = __dp4a((q[3] >> 4) & 0x0F0F0F0F, a1.w, s);
+            acc[n] += d * (ds.x * (float) s - 8.0f * ds.y);
+        }
+    }
+};
+template <> struct gemv_traits<B200_TYPE_Q8_0_REPACKED> {
+    static constexpr int units_per_block = 1, block_elems = 32, block_bytes = 34;
+    template <int NC>
+    static __device__ __forceinline__ void unit(const uint8_t * row, int64_t u, const act_image & a, int64_t col0, float * acc) {
+        const uint8_t * run = row + (u >> 3) * 272; const int c = (int) (u & 7);
+        const float d = __half2float(*(const __half *) (run + 2 * c));
+        const int4 q0 = ld_stream_16(run + 16 + 32 * c), q1 = ld_stream_16(run + 32 + 32 * c);
+#pragma unroll
+        for (int n = 0; n < NC; ++n) {
+            const int8_t * aq = a.qs + (col0 + n) * a.K + u * 32;
+            const float    da = __low2float(a.ds[(col0 + n) * (a.K >> 5) + u]);
+            const int4 a0 = *(const int4 *) aq, a1 = *(const int4 *) (aq + 16);
+            int s = 0;
+            s = __dp4a(q0.x, a0.x, s); s = __dp4a(q0.y, a0.y, s); s = __dp4a(q0.z, a0.z, s); s = __dp4a(q0.w, a0.w, s);
+            s = __dp4a(q1.x, a1.x, s); s = __dp4a(q1.y, a1.y, s); s = __dp4a(q1.z, a1.z, s); s = __dp4a(q1.w, a1.w, s);
+            acc[n] += d * da * (float) s;
+        }
+    }
+};
+
 // ------------------------------------------------------------------------------------------
 struct gemv_args {
     const uint8_t * w; size_t w_nb1, w_nb2, w_nb3;     // weight rows
@@ -326,8 +371,10 @@ int b200_launch_gemv_q(b200_ctx * ctx, const b200_tensor * w, const void * image
         case B200_TYPE_Q5_K: return launch_gemv_type<B200_TYPE_Q5_K>(ctx, p, (int) ne11);
         case B200_TYPE_Q6_K: return (w->flags & B200_TENSOR_REPACKED) ? launch_gemv_type<B200_TYPE_Q6_K_REPACKED>(ctx, p, (int) ne11)
                                                                         : launch_gemv_type<B200_TYPE_Q6_K>(ctx, p, (int) ne11);
-        case B200_TYPE_Q4_0: return launch_gemv_type<B200_TYPE_Q4_0>(ctx, p, (int) ne11);
-        case B200_TYPE_Q8_0: return launch_gemv_type<B200_TYPE_Q8_0>(ctx, p, (int) ne11);
+        case B200_TYPE_Q4_0: return (w->flags & B200_TENSOR_REPACKED) ? launch_gemv_type<B200_TYPE_Q4_0_REPACKED>(ctx, p, (int) ne11)
+                                                                        : launch_gemv_type<B200_TYPE_Q4_0>(ctx, p, (int) ne11);
+        case B200_TYPE_Q8_0: return (w->flags & B200_TENSOR_REPACKED) ? launch_gemv_type<B200_TYPE_Q8_0_REPACKED>(ctx, p, (int) ne11)
+                                                                        : launch_gemv_type<B200_TYPE_Q8_0>(ctx, p, (int) ne11);
     }
     b200_set_error("gemv: weight type %d unsupported", w->type);
     return B200_ERR_UNSUPPORTED;
@@ -387,8 +434,14 @@ int b200_launch_gemv_id_q(b200_ctx * ctx, const b200_tensor * as, const void * i
             if (as->flags & B200_TENSOR_REPACKED) B200_LAUNCH(ctx, B200_K_GEMV_ID, k_gemv_id<B200_TYPE_Q6_K_REPACKED, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p));
             else                                  B200_LAUNCH(ctx, B200_K_GEMV_ID, k_gemv_id<B200_TYPE_Q6_K, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p));
             break;
-        case B200_TYPE_Q4_0: B200_LAUNCH(ctx, B200_K_GEMV_ID, k_gemv_id<B200_TYPE_Q4_0, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p)); break;
-        case B200_TYPE_Q8_0: B200_LAUNCH(ctx, B200_K_GEMV_ID, k_gemv_id<B200_TYPE_Q8_0, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p)); break;
+        case B200_TYPE_Q4_0:
+            if (as->flags & B200_TENSOR_REPACKED) B200_LAUNCH(ctx, B200_K_GEMV_ID, k_gemv_id<B200_TYPE_Q4_0_REPACKED, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p));
+            else                                  B200_LAUNCH(ctx, B200_K_GEMV_ID, k_gemv_id<B200_TYPE_Q4_0, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p));
+            break;
+        case B200_TYPE_Q8_0:
+            if (as->flags & B200_TENSOR_REPACKED) B200_LAUNCH(ctx, B200_K_GEMV_ID, k_gemv_id<B200_TYPE_Q8_0_REPACKED, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p));
+            else                                  B200_LAUNCH(ctx, B200_K_GEMV_ID, k_gemv_id<B200_TYPE_Q8_0, WARPS><<<grid, WARPS * 32, 0, ctx->stream>>>(p));
+            break;
         default: b200_set_error("gemv_id: weight type %d unsupported", as->type); return B200_ERR_UNSUPPORTED;
     }
     return B200_OK;

@@ -163,6 +163,77 @@ template <> struct gs_traits<B200_TYPE_Q6_K> {
     }
 };
 
+// ============================================ q4_0 / q8_0 (run-of-8 repack) ============================================
+// b200_repack turns every 8 consecutive blocks (256 weights) into [8 x fp16 d][8 x qs]: 144 B (q4_0) / 272 B (q8_0), both
+// multiples of 16 with a bank stride of 4 words, so the same lane map as q4_K applies (b = lane & 7 picks the run, lane >> 3
+// the 16-byte unit).  q4_0: unit c = sub-block c, low nibbles meet activations 32c..32c+15 (plane 0), high nibbles
+// 32c+16..32c+31 (plane 1); value = d (q - 8), the -8 goes through q8_1's s = d_a * sum(a).  q8_0: unit c16 = 16 quants.
+template <> struct gs_traits<B200_TYPE_Q4_0> {
+    static constexpr int BLOCK_BYTES = 144;
+    static __host__ __device__ constexpr int stages(bool wide) { return wide ? 4 : 3; }
+    static __host__ __device__ size_t act_bytes(int K) { return (size_t) K + (size_t) (K >> 5) * 8; }
+    static __device__ __forceinline__ void store_act(uint8_t * s_act, int K, int nblocks, int blk32, int off, unsigned word, bool leader, float d, float s) {
+        const int gb = blk32 >> 3, c = blk32 & 7;
+        *(unsigned *) (s_act + (off >> 4) * (K >> 1) + (c * nblocks + gb) * 16 + (off & 15)) = word;
+        if (leader) { float * ds = (float *) (s_act + K) + (c * nblocks + gb) * 2; ds[0] = d; ds[1] = s; }
+    }
+    template <int NR>
+    static __device__ __forceinline__ void consume(uint32_t st, int row_stride, int bl, int gb, int lane, uint32_t act, int K, int nblocks,
+                                                   float (&acc)[GS_RW]) {
+        const int cq = lane >> 3;
+#pragma unroll
+        for (int it = 0; it < 2; ++it) {
+            const int c = cq + 4 * it;
+            const int4 a0 = lds128(act + (c * nblocks + gb) * 16), a1 = lds128(act + (K >> 1) + (c * nblocks + gb) * 16);
+            const int2 dsr = lds64(act + K + (c * nblocks + gb) * 8);
+            const float dA = __int_as_float(dsr.x), sA = __int_as_float(dsr.y);
+#pragma unroll
+            for (int r = 0; r < NR; ++r) {
+                const uint32_t base = st + bl * 144 + r * row_stride;
+                const int4 q = lds128(base + 16 + c * 16);
+                unsigned short dh;
+                asm volatile("ld.shared.u16 %0, [%1];" : "=h"(dh) : "r"(base + 2 * c));
+                int i0 = __dp4a(q.x & 0x0F0F0F0F, a0.x, 0); i0 = __dp4a(q.y & 0x0F0F0F0F, a0.y, i0);
+                i0 = __dp4a(q.z & 0x0F0F0F0F, a0.z, i0);    i0 = __dp4a(q.w & 0x0F0F0F0F, a0.w, i0);
+                int i1 = dp4a_us((unsigned) q.x & 0xF0F0F0F0u, a1.x, 0); i1 = dp4a_us((unsigned) q.y & 0xF0F0F0F0u, a1.y, i1);
+                i1 = dp4a_us((unsigned) q.z & 0xF0F0F0F0u, a1.z, i1);    i1 = dp4a_us((unsigned) q.w & 0xF0F0F0F0u, a1.w, i1);
+                acc[r] = fmaf(__half2float(__ushort_as_half(dh)), dA * (float) (i0 + (i1 >> 4)) - 8.0f * sA, acc[r]);
+            }
+        }
+    }
+};
+template <> struct gs_traits<B200_TYPE_Q8_0> {
+    static constexpr int BLOCK_BYTES = 272;
+    static __host__ __device__ constexpr int stages(bool wide) { return wide ? 3 : 2; }
+    static __host__ __device__ size_t act_bytes(int K) { return (size_t) K + (size_t) (K >> 5) * 4; }
+    static __device__ __forceinline__ void store_act(uint8_t * s_act, int K, int nblocks, int blk32, int off, unsigned word, bool leader, float d, float s) {
+        const int gb = blk32 >> 3, sub = blk32 & 7;
+        *(unsigned *) (s_act + ((sub * 2 + (off >> 4)) * nblocks + gb) * 16 + (off & 15)) = word;
+        if (leader) ((float *) (s_act + K))[sub * nblocks + gb] = d;
+        (void) s;
+    }
+    template <int NR>
+    static __device__ __forceinline__ void consume(uint32_t st, int row_stride, int bl, int gb, int lane, uint32_t act, int K, int nblocks,
+                                                   float (&acc)[GS_RW]) {
+        const int cq = lane >> 3;
+#pragma unroll
+        for (int it = 0; it < 4; ++it) {
+            const int c16 = cq + 4 * it, sub = c16 >> 1;
+            const int4 a = lds128(act + (c16 * nblocks + gb) * 16);
+            const float dA = __int_as_float(lds32(act + K + (sub * nblocks + gb) * 4));
+#pragma unroll
+            for (int r = 0; r < NR; ++r) {
+                const uint32_t base = st + bl * 272 + r * row_stride;
+                const int4 q = lds128(base + 16 + c16 * 16);
+                unsigned short dh;
+                asm volatile("ld.shared.u16 %0, [%1];" : "=h"(dh) : "r"(base + 2 * sub));
+                int i = __dp4a(q.x, a.x, 0); i = __dp4a(q.y, a.y, i); i = __dp4a(q.z, a.z, i); i = __dp4a(q.w, a.w, i);
+                acc[r] = fmaf(__half2float(__ushort_as_half(dh)) * dA, (float) i, acc[r]);
+            }
+        }
+    }
+};
+
 // ====================================================== the kernel ======================================================
 static __device__ __forceinline__ void gs_locate(const gs_args & p, int gr, const uint8_t * & w, float * & dst) {
     // global row -> (segment, row): at most two compares
@@ -329,6 +400,8 @@ bool b200_gemv_stream_supported(const b200_tensor * w, const b200_tensor * x) {
     const int K = (int) w->ne[0];
     if (w->type == B200_TYPE_Q4_K) return !(w->flags & B200_TENSOR_REPACKED) && gs_smem_bytes<B200_TYPE_Q4_K>(K, false) <= GS_SMEM_MAX;
     if (w->type == B200_TYPE_Q6_K) return (w->flags & B200_TENSOR_REPACKED) && K % 2048 == 0 && gs_smem_bytes<B200_TYPE_Q6_K>(K, false) <= GS_SMEM_MAX;
+    if (w->type == B200_TYPE_Q4_0) return (w->flags & B200_TENSOR_REPACKED) && gs_smem_bytes<B200_TYPE_Q4_0>(K, false) <= GS_SMEM_MAX;
+    if (w->type == B200_TYPE_Q8_0) return (w->flags & B200_TENSOR_REPACKED) && gs_smem_bytes<B200_TYPE_Q8_0>(K, false) <= GS_SMEM_MAX;
     return false;
 }
 
@@ -363,7 +436,7 @@ static int gs_launch(b200_ctx * ctx, const gs_args & p, int attr_slot) {
     bool wide = bytes > ((size_t) 24 << 20);
     if (force == 1) wide = true; else if (force == 2) wide = false;
     if (wide && gs_smem_bytes<TYPE>(p.K, true) <= 113 * 1024) return gs_launch_cfg<TYPE, true>(ctx, p, attr_slot);
-    return gs_launch_cfg<TYPE, false>(ctx, p, attr_slot + 2);
+    return gs_launch_cfg<TYPE, false>(ctx, p, attr_slot + 4);
 }
 
 // n <= 3 weights of the same type sharing the activation column x; dst[i] is the f32 column of weight i
@@ -376,8 +449,10 @@ int b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n
         p.Mtot += p.seg[i].M;
     }
     for (int i = n; i < GS_MAXSEG; ++i) { p.seg[i].w = nullptr; p.seg[i].nb1 = 0; p.seg[i].dst = nullptr; p.seg[i].M = 0; }
-    if (w[0]->type == B200_TYPE_Q4_K) return gs_launch<B200_TYPE_Q4_K>(ctx, p, 0);
-    if (w[0]->type == B200_TYPE_Q6_K) return gs_launch<B200_TYPE_Q6_K>(ctx, p, 1);
+    if (w[0]->type == B200_TYPE_Q4_K) return gs_launch<B200_TYPE_Q4_K>(ctx, p, 8);     // attr_done slots 8..11 wide, 12..15 lean
+    if (w[0]->type == B200_TYPE_Q6_K) return gs_launch<B200_TYPE_Q6_K>(ctx, p, 9);
+    if (w[0]->type == B200_TYPE_Q4_0) return gs_launch<B200_TYPE_Q4_0>(ctx, p, 10);
+    if (w[0]->type == B200_TYPE_Q8_0) return gs_launch<B200_TYPE_Q8_0>(ctx, p, 11);
     b200_set_error("gemv_stream: unsupported type %d", w[0]->type);
     return B200_ERR_UNSUPPORTED;
 }

@@ -17,6 +17,29 @@ static __device__ __forceinline__ int q6k_fwd(int s) {
     return 1664 + b * 2 + (o - 208);
 }
 
+// q8_0 / q4_0: every aligned run of 8 blocks (256 weights: 272 / 144 B, both multiples of 16) becomes [8 x fp16 d][8 x qs],
+// so the quants sit at 16-byte aligned addresses and a run is one bulk-copy / TMA-box unit
+static __device__ __forceinline__ int q80_fwd(int s) { const int b = s / 34, o = s - b * 34; return o < 2 ? b * 2 + o : 16 + b * 32 + (o - 2); }
+static __device__ __forceinline__ int q40_fwd(int s) { const int b = s / 18, o = s - b * 18; return o < 2 ? b * 2 + o : 16 + b * 16 + (o - 2); }
+
+// one thread block per row chunk of 8 runs; TYPE selects the byte map
+template <int TYPE, bool INVERSE>
+__global__ void __launch_bounds__(256) k_repack_run8(uint8_t * data, size_t row_stride, int runs_per_row, int64_t nruns) {
+    constexpr int RUN = TYPE == B200_TYPE_Q8_0 ? 272 : 144;
+    __shared__ uint8_t buf[RUN];
+    for (int64_t g = blockIdx.x; g < nruns; g += gridDim.x) {
+        uint8_t * grp = data + (size_t) (g / runs_per_row) * row_stride + (size_t) (g % runs_per_row) * RUN;
+        for (int i = threadIdx.x; i < RUN / 4; i += blockDim.x) ((uint32_t *) buf)[i] = ((const uint32_t *) grp)[i];
+        __syncthreads();
+        for (int s = threadIdx.x; s < RUN; s += blockDim.x) {
+            const int d = TYPE == B200_TYPE_Q8_0 ? q80_fwd(s) : q40_fwd(s);
+            if (INVERSE) grp[s] = buf[d];
+            else         grp[d] = buf[s];
+        }
+        __syncthreads();
+    }
+}
+
 template <bool INVERSE>
 __global__ void __launch_bounds__(256) k_repack_q6k(uint8_t * data, size_t row_stride, int groups_per_row, int64_t ngroups) {
     __shared__ uint8_t buf[1680];
@@ -32,13 +55,31 @@ __global__ void __launch_bounds__(256) k_repack_q6k(uint8_t * data, size_t row_s
     }
 }
 
-extern "C" int b200_repack_supported(int type, int64_t k) { return type == B200_TYPE_Q6_K && k > 0 && k % 2048 == 0; }
+extern "C" int b200_repack_supported(int type, int64_t k) {
+    if (type == B200_TYPE_Q6_K) return k > 0 && k % 2048 == 0;
+    if (type == B200_TYPE_Q8_0 || type == B200_TYPE_Q4_0) return k > 0 && k % 256 == 0;
+    return 0;
+}
 
 static int repack_impl(b200_ctx * ctx, int type, void * data, int64_t k, int64_t nrows, size_t row_stride, bool inverse) {
     if (!b200_repack_supported(type, k)) { b200_set_error("repack: type %d with k=%lld has no repacked layout", type, (long long) k); return B200_ERR_UNSUPPORTED; }
     if (((uintptr_t) data & 3) || (row_stride & 3)) { b200_set_error("repack: rows must be 4-byte aligned"); return B200_ERR_INVALID; }
     if (nrows <= 0) return B200_OK;
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    if (type != B200_TYPE_Q6_K) {
+        const int rpr = (int) (k / 256);
+        const int64_t nruns = nrows * rpr;
+        const unsigned grid = (unsigned) (nruns < 148 * 32 ? nruns : 148 * 32);
+        uint8_t * d = (uint8_t *) data;
+        if (type == B200_TYPE_Q8_0) {
+            if (inverse) B200_LAUNCH(ctx, B200_K_CONVERT, k_repack_run8<B200_TYPE_Q8_0, true><<<grid, 256, 0, ctx->stream>>>(d, row_stride, rpr, nruns));
+            else         B200_LAUNCH(ctx, B200_K_CONVERT, k_repack_run8<B200_TYPE_Q8_0, false><<<grid, 256, 0, ctx->stream>>>(d, row_stride, rpr, nruns));
+        } else {
+            if (inverse) B200_LAUNCH(ctx, B200_K_CONVERT, k_repack_run8<B200_TYPE_Q4_0, true><<<grid, 256, 0, ctx->stream>>>(d, row_stride, rpr, nruns));
+            else         B200_LAUNCH(ctx, B200_K_CONVERT, k_repack_run8<B200_TYPE_Q4_0, false><<<grid, 256, 0, ctx->stream>>>(d, row_stride, rpr, nruns));
+        }
+        return B200_OK;
+    }
     const int gpr = (int) (k / 2048);
     const int64_t ngroups = nrows * gpr;
     const unsigned grid = (unsigned) (ngroups < 148 * 16 ? ngroups : 148 * 16);

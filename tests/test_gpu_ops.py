@@ -217,6 +217,44 @@ def test_mul_mat_decode_ragged_rows(ctx, orc, t, M, K):
     assert _check_mm(orc, got, t, w, K, M, x, 1) < 1e-9
 
 
+@pytest.mark.parametrize("t", [O.Q8_0, O.Q4_0])
+@pytest.mark.parametrize("K,M", [(256, 5), (2304, 67), (4096, 131), (14336, 64)])
+def test_repack_run8_roundtrip_and_parity(ctx, B, orc, t, K, M):
+    """q8_0 / q4_0 load-time repack ([8 x d][8 x qs] per 256 weights): exactly invertible, and the streaming GEMV (n=1), the
+    column-blocked GEMV (n=3), MUL_MAT_ID and the tcgen05 GEMM (n=24) all read it"""
+    rng = np.random.default_rng(K + M + t)
+    w = O.random_blocks(rng, t, K, M)
+    dw = ctx.upload(t, [K, M], w)
+    ctx.repack(dw)
+    assert dw.flags == 1
+    packed = ctx.download(dw, np.uint8)
+    assert not np.array_equal(packed, w) and np.array_equal(np.sort(packed.reshape(M, -1), axis=1), np.sort(w.reshape(M, -1), axis=1))
+    for n in (1, 3, 24):
+        x = rng.standard_normal((n, K)).astype(np.float32)
+        dx = ctx.upload(B.F32, [K, n], x); dd = ctx.empty(B.F32, [M, n])
+        ctx.mul_mat(dw, dx, dd)
+        got = ctx.download(dd).reshape(1, 1, n, M)
+        if n <= 8:
+            assert O.nmse(orc.mul_mat(t, w, K, M, x, n, act=O.ACT_CPU), got) < NMSE_HARNESS
+            assert O.nmse(orc.mul_mat(t, w, K, M, x, n, act=O.ACT_Q8_1), got) < 1e-9
+        else:
+            _check_prefill(orc, got, t, w, K, M, x, n)
+    ctx.unrepack(dw)
+    assert dw.flags == 0 and np.array_equal(ctx.download(dw, np.uint8), w)
+
+
+@pytest.mark.parametrize("t", [O.Q8_0, O.Q4_0])
+def test_mul_mat_prefill_gemm_run8(ctx, B, orc, t):
+    rng = np.random.default_rng(5 + t)
+    K, M, N = 4096, 1024, 512
+    w = O.random_blocks(rng, t, K, M)
+    x = rng.standard_normal((N, K)).astype(np.float32)
+    dw = ctx.upload(t, [K, M], w); ctx.repack(dw)
+    dx = ctx.upload(B.F32, [K, N], x); dd = ctx.empty(B.F32, [M, N])
+    ctx.mul_mat(dw, dx, dd)
+    _check_prefill(orc, ctx.download(dd).reshape(1, 1, N, M), t, w, K, M, x, N)
+
+
 @pytest.mark.parametrize("K,M", [(2048, 67), (4096, 131), (14336, 64)])
 def test_repack_q6_K_roundtrip_and_parity(ctx, B, orc, K, M):
     """load-time repack (b200_repack): in place, exactly invertible, and every MUL_MAT path reads the repacked layout"""
