@@ -13,6 +13,7 @@
 #include <string>
 #include <vector>
 #include <mutex>
+#include <unordered_set>
 #include <string.h>
 #include <stdlib.h>
 
@@ -53,8 +54,9 @@ static bool same_shape(const ggml_tensor * a, const ggml_tensor * b) {
     return a->ne[0] == b->ne[0] && a->ne[1] == b->ne[1] && a->ne[2] == b->ne[2] && a->ne[3] == b->ne[3];
 }
 
+static bool tensor_is_repacked(const ggml_tensor * t);
 static b200_tensor to_b200(const ggml_tensor * t) {
-    b200_tensor r; r.data = t->data; r.type = (int32_t) t->type; r.flags = 0;
+    b200_tensor r; r.data = t->data; r.type = (int32_t) t->type; r.flags = tensor_is_repacked(t) ? B200_TENSOR_REPACKED : 0;
     for (int i = 0; i < 4; ++i) { r.ne[i] = t->ne[i]; r.nb[i] = t->nb[i]; }
     return r;
 }
@@ -66,7 +68,8 @@ struct b200_device_ctx {
     ggml_backend_device      dev;
 };
 struct b200_reg_ctx { std::vector<b200_device_ctx *> devices; };
-struct b200_buffer_ctx { int device; void * base; };
+// `repacked`: weight tensors of this buffer that set_tensor re-laid out for the kernels (b200_repack): the load-time repack hook
+struct b200_buffer_ctx { int device; void * base; std::mutex mu; std::unordered_set<const void *> repacked; };
 struct b200_backend_ctx { int device; b200_ctx * ctx; std::string name; };
 
 static ggml_backend_reg g_reg;
@@ -75,6 +78,48 @@ static ggml_backend_buffer_type g_host_buft;
 
 static bool buft_is_b200(ggml_backend_buffer_type_t buft);
 static bool buft_is_b200_host(ggml_backend_buffer_type_t buft);
+
+// ---- load-time weight repack -------------------------------------------------------------------------------
+// Weights arrive through set_tensor in GGUF layout.  In a buffer marked USAGE_WEIGHTS (llama_model_loader does that before it
+// uploads; GGML_B200_REPACK=all extends it to every buffer, GGML_B200_REPACK=0 turns it off) a whole-tensor write of a type with
+// a device layout (b200_repack_supported) is permuted in place right after the copy; get_tensor and partial writes undo /
+// redo it, so the host only ever sees GGUF bytes.  Only MUL_MAT / MUL_MAT_ID read repacked tensors (dev_supports_op).
+static int repack_mode() {
+    static int m = -1;
+    if (m < 0) { const char * e = getenv("GGML_B200_REPACK"); m = !e ? 1 : !strcmp(e, "all") ? 2 : atoi(e) ? 1 : 0; }
+    return m;
+}
+static b200_ctx * util_ctx(int device) {                   // one helper context per device for the repack kernels
+    static std::mutex mu; static b200_ctx * ctxs[B200_MAX_DEVICES] = {};
+    std::lock_guard<std::mutex> g(mu);
+    if (!ctxs[device]) ctxs[device] = b200_ctx_create(device);
+    return ctxs[device];
+}
+static bool tensor_is_repacked(const ggml_tensor * t) {
+    const ggml_tensor * base = t->view_src ? t->view_src : t;
+    if (!base->buffer || !buft_is_b200(base->buffer->buft) || t_blck(base->type) <= 1) return false;
+    b200_buffer_ctx * c = (b200_buffer_ctx *) base->buffer->context;
+    std::lock_guard<std::mutex> g(c->mu);
+    return c->repacked.count(base->data) != 0;
+}
+static void tensor_repack(ggml_backend_buffer_t b, const ggml_tensor * t, bool inverse) {
+    b200_buffer_ctx * c = (b200_buffer_ctx *) b->context;
+    b200_ctx * u = util_ctx(c->device);
+    if (!u) return;
+    const int rc = inverse ? b200_unrepack(u, (int) t->type, t->data, t->ne[0], t->ne[1] * t->ne[2] * t->ne[3], t->nb[1])
+                           : b200_repack(u, (int) t->type, t->data, t->ne[0], t->ne[1] * t->ne[2] * t->ne[3], t->nb[1]);
+    if (rc != B200_OK || b200_ctx_synchronize(u) != B200_OK) { fprintf(stderr, "ggml-b200: repack failed: %s\n", b200_last_error()); abort(); }
+    std::lock_guard<std::mutex> g(c->mu);
+    if (inverse) c->repacked.erase(t->data); else c->repacked.insert(t->data);
+}
+static bool tensor_wants_repack(ggml_backend_buffer_t b, const ggml_tensor * t) {
+    const int mode = repack_mode();
+    if (mode == 0 || (mode == 1 && b->usage != GGML_BACKEND_BUFFER_USAGE_WEIGHTS)) return false;
+    if (t->view_src || t_blck(t->type) <= 1 || !b200_repack_supported((int) t->type, t->ne[0])) return false;
+    // rows densely packed one after the other (what the in-place group permutation assumes)
+    return t->nb[0] == t_size(t->type) && t->nb[1] == (size_t) (t->ne[0] / t_blck(t->type)) * t_size(t->type) &&
+           t->nb[2] == t->nb[1] * (size_t) t->ne[1] && t->nb[3] == t->nb[2] * (size_t) t->ne[2] && ((uintptr_t) t->data & 15) == 0;
+}
 
 // ---- buffer ---------------------------------------------------------------------------------------
 static void buf_free(ggml_backend_buffer_t b) {
@@ -96,15 +141,24 @@ static void buf_memset_tensor(ggml_backend_buffer_t b, ggml_tensor * t, uint8_t 
 }
 static void buf_set_tensor(ggml_backend_buffer_t b, ggml_tensor * t, const void * data, size_t off, size_t n) {
     b200_buffer_ctx * c = (b200_buffer_ctx *) b->context; B200_CHECK(cudaSetDevice(c->device));
+    const ggml_tensor * base = t->view_src ? t->view_src : t;
+    const bool was = tensor_is_repacked(t);
+    if (was) tensor_repack(b, base, true);                   // the host writes GGUF bytes: go back to GGUF layout first
     B200_CHECK(cudaMemcpyAsync((char *) t->data + off, data, n, cudaMemcpyHostToDevice, cudaStreamPerThread)); B200_CHECK(cudaStreamSynchronize(cudaStreamPerThread));
+    if (was || (off == 0 && n == tensor_nbytes(t) && tensor_wants_repack(b, t))) tensor_repack(b, base, false);
 }
 static void buf_get_tensor(ggml_backend_buffer_t b, const ggml_tensor * t, void * data, size_t off, size_t n) {
     b200_buffer_ctx * c = (b200_buffer_ctx *) b->context; B200_CHECK(cudaSetDevice(c->device));
+    const ggml_tensor * base = t->view_src ? t->view_src : t;
+    const bool was = tensor_is_repacked(t);
+    if (was) tensor_repack(b, base, true);
     B200_CHECK(cudaMemcpyAsync(data, (const char *) t->data + off, n, cudaMemcpyDeviceToHost, cudaStreamPerThread)); B200_CHECK(cudaStreamSynchronize(cudaStreamPerThread));
+    if (was) tensor_repack(b, base, false);
 }
 static bool buf_cpy_tensor(ggml_backend_buffer_t b, const ggml_tensor * src, ggml_tensor * dst) {
     b200_buffer_ctx * c = (b200_buffer_ctx *) b->context;
     if (!src->buffer || !buft_is_b200(src->buffer->buft)) return false;
+    if (tensor_is_repacked(src) || tensor_is_repacked(dst)) return false;     // go through get_tensor / set_tensor, which translate the layout
     b200_buffer_ctx * sc = (b200_buffer_ctx *) src->buffer->context;
     B200_CHECK(cudaSetDevice(c->device));
     if (sc->device == c->device) B200_CHECK(cudaMemcpyAsync(dst->data, src->data, tensor_nbytes(src), cudaMemcpyDeviceToDevice, cudaStreamPerThread));
@@ -174,15 +228,26 @@ static void be_free(ggml_backend_t be) {
 static void be_set_tensor_async(ggml_backend_t be, ggml_tensor * t, const void * data, size_t off, size_t n) {
     b200_backend_ctx * c = (b200_backend_ctx *) be->context; B200_CHECK(cudaSetDevice(c->device));
     b200_note_write(c->ctx, (char *) t->data + off, n);
+    if (t->buffer && buft_is_b200(t->buffer->buft) && (tensor_is_repacked(t) || (off == 0 && n == tensor_nbytes(t) && tensor_wants_repack(t->buffer, t)))) {
+        B200_CHECK(cudaStreamSynchronize(c->ctx->stream));       // layout translation is synchronous: weights are uploaded once
+        buf_set_tensor(t->buffer, t, data, off, n);
+        return;
+    }
     B200_CHECK(cudaMemcpyAsync((char *) t->data + off, data, n, cudaMemcpyHostToDevice, c->ctx->stream));
 }
 static void be_get_tensor_async(ggml_backend_t be, const ggml_tensor * t, void * data, size_t off, size_t n) {
     b200_backend_ctx * c = (b200_backend_ctx *) be->context; B200_CHECK(cudaSetDevice(c->device));
+    if (t->buffer && buft_is_b200(t->buffer->buft) && tensor_is_repacked(t)) {
+        B200_CHECK(cudaStreamSynchronize(c->ctx->stream));
+        buf_get_tensor(t->buffer, t, data, off, n);
+        return;
+    }
     B200_CHECK(cudaMemcpyAsync(data, (const char *) t->data + off, n, cudaMemcpyDeviceToHost, c->ctx->stream));
 }
 static bool be_is_b200(ggml_backend_t be) { return be && be->iface.get_name == be_name; }
 static bool be_cpy_tensor_async(ggml_backend_t be_src, ggml_backend_t be_dst, const ggml_tensor * src, ggml_tensor * dst) {
     if (!be_is_b200(be_src) || !be_is_b200(be_dst)) return false;
+    if (tensor_is_repacked(src) || tensor_is_repacked(dst)) return false;
     if (!src->buffer || !dst->buffer || !buft_is_b200(src->buffer->buft) || !buft_is_b200(dst->buffer->buft)) return false;
     b200_backend_ctx * cs = (b200_backend_ctx *) be_src->context, * cd = (b200_backend_ctx *) be_dst->context;
     b200_buffer_ctx * bs = (b200_buffer_ctx *) src->buffer->context, * bd = (b200_buffer_ctx *) dst->buffer->context;
@@ -323,6 +388,7 @@ static bool dev_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
             return true;
         }
         default:
+            for (int i = 0; i < GGML_MAX_SRC; ++i) if (op->src[i] && tensor_is_repacked(op->src[i])) return false;   // only the matmuls read device layouts
             return b200_glue_supports(op);
     }
 }

@@ -15,17 +15,17 @@ PLUGIN = os.path.join(ROOT, "super-llama.cpp_b200", "libggml-b200.so")
 OUT = os.path.join(ROOT, "gpurun_out")
 
 
-def run_harness(op, pattern=None, mode="test", timeout=1500):
+def run_harness(op, pattern=None, mode="test", timeout=1500, env_extra=None, tag=""):
     if not os.path.exists(HARNESS):
         pytest.skip("oracle/_ref/avx2/test-backend-ops not built (needs /root/reference at build time)")
-    env = dict(os.environ, GGML_BACKEND_PATH=PLUGIN)
+    env = dict(os.environ, GGML_BACKEND_PATH=PLUGIN, **(env_extra or {}))
     cmd = [HARNESS, mode, "-b", "B200_0", "-o", op]
     if pattern:
         cmd += ["-p", pattern]
     p = subprocess.run(cmd, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=timeout)
     txt = re.sub(r"\x1b\[[0-9;]*m", "", p.stdout)
     os.makedirs(OUT, exist_ok=True)
-    with open(os.path.join(OUT, f"test-backend-ops_{mode}_{op}.log"), "w") as f:
+    with open(os.path.join(OUT, f"test-backend-ops_{mode}_{op}{tag}.log"), "w") as f:
         f.write(txt)
     return p.returncode, txt
 
@@ -70,3 +70,14 @@ def test_backend_ops_flash_attn_ext():
     assert rc == 0 and passed == total and not fail, "\n".join(fail[:20])
     assert not holes, "north-star FLASH_ATTN_EXT cases declined:\n" + "\n".join(holes[:20])
     assert ok >= 300, f"only {ok} FLASH_ATTN_EXT cases ran on the device"
+
+
+@pytest.mark.parametrize("op", ["MUL_MAT", "MUL_MAT_ID"])
+def test_backend_ops_with_load_time_repack(op):
+    """the same harness with GGML_B200_REPACK=all: every whole-tensor set_tensor of q6_K / q8_0 / q4_0 weights is permuted into
+    the device layout by the plugin's buffer hook, so the repacked-layout kernels (streaming GEMV, column-blocked GEMV,
+    MUL_MAT_ID, tcgen05 GEMM) are the ones compared with ggml-cpu"""
+    rc, txt = run_harness(op, env_extra={"GGML_B200_REPACK": "all"}, tag="_repack")
+    ok, passed, total, fail, holes = summarize(txt, lambda l: False)
+    assert rc == 0 and passed == total and not fail, "\n".join(fail[:20])
+    assert ok >= 100
