@@ -285,7 +285,11 @@ extern "C" int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b20
         b200_set_error("mul_mat_id: unsupported type/layout"); return B200_ERR_UNSUPPORTED;
     }
     if (M == 0 || n_used * n_tokens == 0) return B200_OK;
-    if (n_tokens > B200_GEMV_MAX_COLS && b200_gemm_id_supported(as, b, ids)) return b200_launch_gemm_id_q(ctx, as, b, ids, dst);
+    if (n_tokens > B200_GEMV_MAX_COLS && b200_gemm_id_supported(as, b, ids)) {
+        const int rc = b200_launch_gemm_id_q(ctx, as, b, ids, dst);        // grouped tcgen05 GEMM (prefill)
+        b200_note_write(ctx, dst->data, b200_tensor_span(dst));
+        return rc;
+    }
     int rc;
     const void * image = quantized_activations(ctx, b, q8_1_variant_env(), &rc);
     if (!image) return rc;

@@ -39,6 +39,9 @@ struct gm_args {
     int BN;                              // activation columns per CTA (UMMA N)
     int MT;                              // 128-row weight tiles per CTA (1 or 2): 2 halves the activation traffic per flop
     int SA, SB, RS;                      // ring depths: A stages in TMEM (power of two), B stages in smem (64-K steps), raw 256-K weight blocks
+    // MUL_MAT_ID (grouped GEMM): activation rows sorted by expert; expert e owns rows [offsets[e], offsets[e] + counts[e]) of the
+    // image, col_off[row] is where that (token, slot) pair's result column starts in dst (in floats).  NULL for plain MUL_MAT.
+    const int * counts; const int * offsets; const long long * col_off;
     int dbg;                             // timing experiments only (GGML_B200_GEMM_DBG): 1 = no weight fetch, 2 = no expansion math, 4 = no activation fetch
 };
 
@@ -236,7 +239,13 @@ __global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const
     const uint32_t rf0 = eb0 + 8 * SB, re0 = rf0 + 8 * RS;           // raw block landed / raw block consumed
     const uint32_t tfull = re0 + 8 * RS, tslot = tfull + 8;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n0 = blockIdx.x * BN, m0 = blockIdx.y * (MT * GM_BM);
+    const int m0 = blockIdx.y * (MT * GM_BM);
+    int n0 = blockIdx.x * BN, n_end = p.N, wrow0 = m0;
+    if (p.counts) {                                                          // grouped: this CTA serves expert blockIdx.z
+        const int e = blockIdx.z, cnt = p.counts[e];
+        if (n0 >= cnt) return;                                               // uniform per CTA, before any barrier or TMEM allocation
+        n0 += p.offsets[e]; n_end = p.offsets[e] + cnt; wrow0 = e * p.M + m0; // experts are stacked rows of one tall weight matrix
+    }
     const int nks = p.K / GM_BK, nunits = p.K / T::RAW_K;
     // TMEM columns: accumulators [0, MT*BN), then A stages: stage s, tile t at MT*BN + (s*MT + t)*32
     const uint32_t tneed = (uint32_t) (MT * BN + MT * 32 * SA);
@@ -308,13 +317,14 @@ __global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const
         const int c_begin = MT == 2 ? 0 : grp * (BN / 2), c_end = MT == 2 ? BN : c_begin + BN / 2;   // MT=1: the groups split the columns
         float * drow = p.dst + mm;
         for (int c0 = c_begin; c0 < c_end; c0 += 16) {
-            if (n0 + c0 >= p.N) break;
+            if (n0 + c0 >= n_end) break;
             uint32_t r[16];
             tmem_ld16(tmem + lane_base + (uint32_t) (tile * BN + c0), r);
             tmem_ld_wait();
             if (mm < p.M) {
 #pragma unroll
-                for (int j = 0; j < 16; ++j) if (n0 + c0 + j < p.N) drow[(size_t) (n0 + c0 + j) * p.d_ld] = __uint_as_float(r[j]);
+                for (int j = 0; j < 16; ++j)
+                    if (n0 + c0 + j < n_end) drow[p.col_off ? (size_t) p.col_off[n0 + c0 + j] : (size_t) (n0 + c0 + j) * p.d_ld] = __uint_as_float(r[j]);
             }
         }
         tc_fence_before();
@@ -370,12 +380,12 @@ __global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const
                     for (int t = 0; t < MT; ++t) {
                         const uint32_t dstp = r_sm + slot * raw_slot + t * T::TILE_BYTES;
                         if (TYPE == B200_TYPE_Q8_0) {
-                            tma_load_3d(dstp, &tmap_w, 0, unit * 17, m0 + t * GM_BM, rf0 + 8 * slot);
+                            tma_load_3d(dstp, &tmap_w, 0, unit * 17, wrow0 + t * GM_BM, rf0 + 8 * slot);
                         } else if (TYPE == B200_TYPE_Q6_K) {
-                            tma_load_4d(dstp, &tmap_w, (unit & 7) * 16, 0, unit >> 3, m0 + t * GM_BM, rf0 + 8 * slot);
-                            tma_load_3d(dstp + GM_BM * T::ROW_BYTES, &tmap_w2, 0, unit >> 3, m0 + t * GM_BM, rf0 + 8 * slot);
+                            tma_load_4d(dstp, &tmap_w, (unit & 7) * 16, 0, unit >> 3, wrow0 + t * GM_BM, rf0 + 8 * slot);
+                            tma_load_3d(dstp + GM_BM * T::ROW_BYTES, &tmap_w2, 0, unit >> 3, wrow0 + t * GM_BM, rf0 + 8 * slot);
                         } else {
-                            tma_load_2d(dstp, &tmap_w, unit * T::ROW_BYTES, m0 + t * GM_BM, rf0 + 8 * slot);
+                            tma_load_2d(dstp, &tmap_w, unit * T::ROW_BYTES, wrow0 + t * GM_BM, rf0 + 8 * slot);
                         }
                     }
                 }
@@ -425,19 +435,23 @@ static void gemm_pick_tile(const b200_ctx * ctx, int64_t M, int64_t N, int & MT,
     BN = N > 64 ? 128 : N > 32 ? 64 : 32;
 }
 
-// image = bf16 [N][K] activations (b200_launch_act_bf16)
-int b200_launch_gemm_q(b200_ctx * ctx, const b200_tensor * w, const void * image, int64_t N, b200_tensor * dst) {
+// image = bf16 [N][K] activations (b200_launch_act_bf16); grouped (MUL_MAT_ID) when gi != NULL
+struct gm_group { const int * counts; const int * offsets; const long long * col_off; int n_expert; int bn; };
+static int gemm_launch(b200_ctx * ctx, const b200_tensor * w, const void * image, int64_t N, float * dst, size_t d_ld, const gm_group * gi) {
     encode_tiled_fn encode = b200_get_encode_tiled();
     if (!encode) { b200_set_error("gemm: cuTensorMapEncodeTiled not available from the driver"); return B200_ERR_CUDA; }
     gm_args p;
     p.w = (const uint8_t *) w->data; p.w_nb1 = w->nb[1];
-    p.dst = (float *) dst->data; p.d_ld = dst->nb[1] / 4;
+    p.dst = dst; p.d_ld = d_ld;
+    p.counts = gi ? gi->counts : nullptr; p.offsets = gi ? gi->offsets : nullptr; p.col_off = gi ? gi->col_off : nullptr;
+    const int64_t rows_total = w->ne[1] * (gi ? gi->n_expert : 1);     // experts stacked as rows of one tall matrix
     p.M = (int) w->ne[1]; p.N = (int) N; p.K = (int) w->ne[0];
     static const int force_bn = getenv("GGML_B200_GEMM_BN") ? atoi(getenv("GGML_B200_GEMM_BN")) : 0;
     static const int force_mt = getenv("GGML_B200_GEMM_MT") ? atoi(getenv("GGML_B200_GEMM_MT")) : 0;
     gemm_pick_tile(ctx, p.M, p.N, p.MT, p.BN);
     if (force_bn) p.BN = force_bn;
     if (force_mt) p.MT = force_mt;
+    if (gi) { p.MT = 1; p.BN = gi->bn; }
     if (p.MT == 2 && p.BN > 128) p.BN = 128;                              // TMEM: 2*BN accumulator columns + 256 columns of A stages
     static const int force_s = getenv("GGML_B200_GEMM_S") ? atoi(getenv("GGML_B200_GEMM_S")) : 0, force_rs = getenv("GGML_B200_GEMM_RS") ? atoi(getenv("GGML_B200_GEMM_RS")) : 0;
     static const int force_sb = getenv("GGML_B200_GEMM_SB") ? atoi(getenv("GGML_B200_GEMM_SB")) : 0;
@@ -461,7 +475,7 @@ int b200_launch_gemm_q(b200_ctx * ctx, const b200_tensor * w, const void * image
     CUresult cw;
     if (q8) {
         // repacked q8_0: rows of 17 x 16 B per 256 weights
-        const cuuint64_t wdim[3] = { 16, (cuuint64_t) (p.K / 256) * 17, (cuuint64_t) p.M };
+        const cuuint64_t wdim[3] = { 16, (cuuint64_t) (p.K / 256) * 17, (cuuint64_t) rows_total };
         const cuuint64_t wstr[2] = { 16, (cuuint64_t) p.w_nb1 };
         const cuuint32_t wbox[3] = { 16, 17, GM_BM }, e3[3] = { 1, 1, 1 };
         cw = encode(&tmap_w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void *) p.w, wdim, wstr, wbox, e3, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -469,7 +483,7 @@ int b200_launch_gemm_q(b200_ctx * ctx, const b200_tensor * w, const void * image
         tmap_w2 = tmap_w;
     } else if (!q6) {
         // q4_K and repacked q4_0: the weight rows as a 2-D byte tensor; box = 144 bytes (256 weights) of 128 consecutive rows
-        const cuuint64_t wdim[2] = { (cuuint64_t) (p.K / 256) * 144, (cuuint64_t) p.M };
+        const cuuint64_t wdim[2] = { (cuuint64_t) (p.K / 256) * 144, (cuuint64_t) rows_total };
         const cuuint64_t wstr[1] = { (cuuint64_t) p.w_nb1 };
         const cuuint32_t wbox[2] = { 144, GM_BM };
         cw = encode(&tmap_w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, (void *) p.w, wdim, wstr, wbox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
@@ -477,13 +491,13 @@ int b200_launch_gemm_q(b200_ctx * ctx, const b200_tensor * w, const void * image
         tmap_w2 = tmap_w;
     } else {
         // repacked q6_K: {byte in unit-row (128), unit-row (13), group (K/2048), weight row}; box = column b (16 B) of the 13 unit-rows
-        const cuuint64_t wdim[4] = { 128, 13, (cuuint64_t) (p.K / 2048), (cuuint64_t) p.M };
+        const cuuint64_t wdim[4] = { 128, 13, (cuuint64_t) (p.K / 2048), (cuuint64_t) rows_total };
         const cuuint64_t wstr[3] = { 128, 1680, (cuuint64_t) p.w_nb1 };
         const cuuint32_t wbox[4] = { 16, 13, 1, GM_BM }, e4[4] = { 1, 1, 1, 1 };
         cw = encode(&tmap_w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 4, (void *) p.w, wdim, wstr, wbox, e4, CU_TENSOR_MAP_INTERLEAVE_NONE,
                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         // the eight fp16 d's of a group: 16 B at byte 1664 of every group
-        const cuuint64_t ddim[3] = { 16, (cuuint64_t) (p.K / 2048), (cuuint64_t) p.M };
+        const cuuint64_t ddim[3] = { 16, (cuuint64_t) (p.K / 2048), (cuuint64_t) rows_total };
         const cuuint64_t dstr[2] = { 1680, (cuuint64_t) p.w_nb1 };
         const cuuint32_t dbox[3] = { 16, 1, GM_BM };
         if (cw == CUDA_SUCCESS)
@@ -502,7 +516,7 @@ int b200_launch_gemm_q(b200_ctx * ctx, const b200_tensor * w, const void * image
         B200_CUDA_TRY(cudaFuncSetAttribute(k_gemm_q<B200_TYPE_Q8_0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
         ctx->attr_done[5] = 1;
     }
-    dim3 grid((unsigned) ((p.N + p.BN - 1) / p.BN), (unsigned) ((p.M + p.MT * GM_BM - 1) / (p.MT * GM_BM)));
+    dim3 grid((unsigned) ((p.N + p.BN - 1) / p.BN), (unsigned) ((p.M + p.MT * GM_BM - 1) / (p.MT * GM_BM)), (unsigned) (gi ? gi->n_expert : 1));
     switch (w->type) {
         case B200_TYPE_Q6_K: B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q6_K><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap, tmap_w, tmap_w2)); break;
         case B200_TYPE_Q8_0: B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q8_0><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap, tmap_w, tmap_w2)); break;
@@ -512,5 +526,81 @@ int b200_launch_gemm_q(b200_ctx * ctx, const b200_tensor * w, const void * image
     return B200_OK;
 }
 
-bool b200_gemm_id_supported(const b200_tensor *, const b200_tensor *, const b200_tensor *) { return false; }
-int  b200_launch_gemm_id_q(b200_ctx *, const b200_tensor *, const b200_tensor *, const b200_tensor *, b200_tensor *) { return B200_ERR_UNSUPPORTED; }
+int b200_launch_gemm_q(b200_ctx * ctx, const b200_tensor * w, const void * image, int64_t N, b200_tensor * dst) {
+    return gemm_launch(ctx, w, image, N, (float *) dst->data, dst->nb[1] / 4, nullptr);
+}
+
+// ---- MUL_MAT_ID as a grouped GEMM -----------------------------------------------------------------------------------------------
+// Reference: ggml_compute_forward_mul_mat_id (ggml/src/ggml-cpu/ggml-cpu.c:1500-1700) buckets the (slot, token) pairs by expert
+// on thread 0 and runs one matmul per bucket.  Here: one small kernel buckets the pairs on the device, a gather kernel writes
+// the bf16 activation rows in bucket order, and ONE launch of the GEMM serves every expert (grid.z = expert; CTAs beyond an
+// expert's row count exit at once); the epilogue scatters result columns to dst[:, slot, token].
+__global__ void __launch_bounds__(1024) k_mmid_bucket(const char * ids, size_t ids_nb1, int n_used, int n_tokens, int n_expert, int ne11,
+                                                       size_t b_nb1, size_t b_nb2, long long d_ld1, long long d_ld2,
+                                                       int * counts, int * offsets, long long * col_off, long long * src_off) {
+    extern __shared__ int sm[];                                             // cnt[n_expert], cur[n_expert]
+    int * cnt = sm, * cur = sm + n_expert;
+    for (int i = threadIdx.x; i < 2 * n_expert; i += blockDim.x) sm[i] = 0;
+    __syncthreads();
+    const int npairs = n_used * n_tokens;
+    for (int i = threadIdx.x; i < npairs; i += blockDim.x) {
+        const int t = i / n_used, s = i - t * n_used;
+        const int e = ((const int *) (ids + (size_t) t * ids_nb1))[s];
+        if (e >= 0 && e < n_expert) atomicAdd(&cnt[e], 1);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) { int acc = 0; for (int e = 0; e < n_expert; ++e) { offsets[e] = acc; counts[e] = cnt[e]; cur[e] = acc; acc += cnt[e]; } }
+    __syncthreads();
+    for (int i = threadIdx.x; i < npairs; i += blockDim.x) {
+        const int t = i / n_used, s = i - t * n_used;
+        const int e = ((const int *) (ids + (size_t) t * ids_nb1))[s];
+        if (e < 0 || e >= n_expert) continue;
+        const int pos = atomicAdd(&cur[e], 1);
+        col_off[pos] = (long long) t * d_ld2 + (long long) s * d_ld1;
+        src_off[pos] = (long long) t * (long long) b_nb2 + (long long) (s % ne11) * (long long) b_nb1;
+    }
+}
+__global__ void __launch_bounds__(256) k_act_bf16_gather(const char * __restrict__ b, const long long * __restrict__ src_off, int64_t K, int64_t nrows,
+                                                          __nv_bfloat16 * __restrict__ out) {
+    const int64_t per_row = K / 4, total = per_row * nrows;
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t) gridDim.x * blockDim.x) {
+        const int64_t n = i / per_row, k = (i - n * per_row) * 4;
+        const float4 v = *(const float4 *) (b + src_off[n] + k * 4);
+        __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), c = __floats2bfloat162_rn(v.z, v.w);
+        uint2 o; o.x = *(uint32_t *) &a; o.y = *(uint32_t *) &c;
+        *(uint2 *) (out + n * K + k) = o;
+    }
+}
+
+bool b200_gemm_id_supported(const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids) {
+    b200_tensor w2 = *as; w2.ne[2] = 1;                                      // one expert's matrix, for the type / alignment rules
+    b200_tensor x2 = *b;  x2.ne[1] = 64; x2.ne[2] = 1; x2.nb[1] = (size_t) b->ne[0] * 4;
+    if (!b200_gemm_supported(&w2, &x2)) return false;
+    if (as->nb[2] != as->nb[1] * (size_t) as->ne[1] || as->ne[2] > 256 || as->ne[1] * as->ne[2] > (1ll << 30)) return false;   // experts densely stacked
+    if (((uintptr_t) b->data & 15) || (b->nb[1] & 15) || (b->nb[2] & 15) || (ids->nb[1] & 3)) return false;
+    return ids->ne[0] * ids->ne[1] > 32 && ids->ne[0] * ids->ne[1] <= (1 << 22);
+}
+
+int b200_launch_gemm_id_q(b200_ctx * ctx, const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids, b200_tensor * dst) {
+    const int n_used = (int) ids->ne[0], n_tokens = (int) ids->ne[1], n_expert = (int) as->ne[2], npairs = n_used * n_tokens;
+    const int64_t K = as->ne[0];
+    // scratch slot 3: counts | offsets | col_off | src_off ; slot 0: the bucket-ordered bf16 activation image
+    const size_t ints = ((size_t) 2 * n_expert * sizeof(int) + 15) & ~(size_t) 15;
+    char * meta = (char *) b200_scratch(ctx, 3, ints + (size_t) 2 * npairs * sizeof(long long));
+    ctx->qcache.valid = 0;
+    void * image = b200_scratch(ctx, 0, (size_t) npairs * K * 2);
+    if (!meta || !image) return B200_ERR_ALLOC;
+    int * counts = (int *) meta, * offsets = counts + n_expert;
+    long long * col_off = (long long *) (meta + ints), * src_off = col_off + npairs;
+    B200_LAUNCH(ctx, B200_K_MMID_SORT, k_mmid_bucket<<<1, 1024, 2 * n_expert * sizeof(int), ctx->stream>>>((const char *) ids->data, ids->nb[1], n_used, n_tokens,
+        n_expert, (int) b->ne[1], b->nb[1], b->nb[2], (long long) (dst->nb[1] / 4), (long long) (dst->nb[2] / 4), counts, offsets, col_off, src_off));
+    const int64_t total = K / 4 * npairs;
+    const unsigned ggrid = (unsigned) ((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
+    B200_LAUNCH(ctx, B200_K_CONVERT, k_act_bf16_gather<<<ggrid, 256, 0, ctx->stream>>>((const char *) b->data, src_off, K, npairs, (__nv_bfloat16 *) image));
+    gm_group gi;
+    gi.counts = counts; gi.offsets = offsets; gi.col_off = col_off; gi.n_expert = n_expert;
+    const int avg = npairs / (n_expert > 0 ? n_expert : 1);
+    gi.bn = avg > 96 ? 128 : avg > 48 ? 64 : 32;
+    b200_tensor w2 = *as; w2.ne[2] = 1;
+    return gemm_launch(ctx, &w2, image, npairs, (float *) dst->data, 0, &gi);
+}

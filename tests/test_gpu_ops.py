@@ -382,6 +382,29 @@ def test_mul_mat_id_shapes(ctx, orc, t, n_mats, n_used, bcast, n):
         assert O.nmse(orc.mul_mat_id(t, as_, K, M, n_mats, b, ne11, n, ids, n_used, act=O.ACT_Q8_1), got) < 1e-9
 
 
+@pytest.mark.parametrize("t,repack", [(O.Q4_K, False), (O.Q6_K, True), (O.Q8_0, True), (O.Q4_0, True)])
+@pytest.mark.parametrize("bcast", [True, False])
+def test_mul_mat_id_prefill_grouped_gemm(ctx, B, orc, t, repack, bcast):
+    """Mixtral-style prefill: 8 experts, 2 used, 200 tokens -> device-side bucketing + ONE grouped tcgen05 GEMM launch; some
+    experts get few rows, one gets none"""
+    rng = np.random.default_rng(11 + t)
+    K, M, E, U, n = (2048 if t == O.Q6_K else 1024), 300, 8, 2, 200
+    as_ = O.random_blocks(rng, t, K, M * E)
+    ids = np.stack([rng.permutation(E - 1)[:U] for _ in range(n)]).astype(np.int32)      # expert 7 is never routed to
+    ids[:3] = [[0, 6], [6, 0], [0, 6]]
+    ne11 = 1 if bcast else U
+    b = rng.standard_normal((n, ne11, K)).astype(np.float32)
+    da = ctx.upload(t, [K, M, E], as_)
+    if repack:
+        ctx.repack(da); assert da.flags == 1
+    db = ctx.upload(B.F32, [K, ne11, n], b); di = ctx.upload(B.I32, [U, n], ids); dd = ctx.empty(B.F32, [M, U, n])
+    ctx.mul_mat_id(da, db, di, dd)
+    got = ctx.download(dd).reshape(n, U, M)
+    assert np.isfinite(got).all()
+    assert O.nmse(orc.mul_mat_id(t, as_, K, M, E, b, ne11, n, ids, U, act=O.ACT_CPU), got) < NMSE_HARNESS
+    assert O.nmse(orc.mul_mat_id(t, as_, K, M, E, b, ne11, n, ids, U, act=O.ACT_F64), got) < NMSE_BF16
+
+
 def test_mul_mat_id_mixtral_decode(ctx, orc):
     rng = np.random.default_rng(77)
     K, M, E, U = 4096, 1024, 8, 2                      # a 1024-row slice of Mixtral's [4096, 14336, 8] gate tensor
