@@ -139,6 +139,31 @@ B200_API int b200_repack_supported(int type, int64_t k);
 B200_API int b200_repack(b200_ctx * ctx, int type, void * data, int64_t k, int64_t nrows, size_t row_stride);
 B200_API int b200_unrepack(b200_ctx * ctx, int type, void * data, int64_t k, int64_t nrows, size_t row_stride);
 
+// ---- split-mode=row across processes: MUL_MAT fused with its all-gather over NVLink peer memory ------------------------------
+// One process per GPU.  Every rank allocates an identical "exchange arena" (b200_malloc), publishes it with b200_peer_handle
+// (a cudaIpcMemHandle, 64 bytes, exchanged by the host program) and maps the others with b200_peer_open.  Arena layout:
+//   [0, ctrl_off)                         tensors (dst of the row-split matmuls), same offsets on every rank
+//   [ctrl_off, ctrl_off + 256)            control block (uint32 expected @32, cta counter @36, error @40), zeroed
+//   [ctrl_off + 256, ctrl_off + 256 + 2*ctrl_off)   low-latency mirror: 8 bytes (f32 value, uint32 tag) per f32 of the tensor area
+// A row-split MUL_MAT computes rows [row_lo, row_lo + w->ne[1]) of dst and its epilogue stores each of them as a (value, tag)
+// pair straight into EVERY rank's mirror (peer stores over NVLink; an 8-byte store is one transaction, so the tag validates the
+// value: no fence, no flag).  A small receive kernel on every rank polls its own mirror until all rows carry the tag and writes
+// the plain f32 column; kernels after it on the stream see the complete dst.
+// Replaces the reference's copy-compute-copy loop over split buffers (ggml/src/ggml-cuda/ggml-cuda.cu:1451-1769).
+#define B200_MAX_PEERS 8
+typedef struct b200_exchange {
+    int32_t world, rank;
+    void *  base[B200_MAX_PEERS];   // arena base address of every rank as mapped in THIS process (base[rank] = own arena)
+    size_t  ctrl_off;               // size of the tensor area = offset of the control block; arena size = 3 * ctrl_off + 256
+} b200_exchange;
+B200_API int b200_peer_handle(b200_ctx * ctx, void * dptr, void * handle64);
+B200_API int b200_peer_open(b200_ctx * ctx, const void * handle64, void ** dptr);
+B200_API int b200_peer_close(b200_ctx * ctx, void * dptr);
+// w: this rank's rows (a [K, rows] tensor), x: the full activation column, dst: the FULL result column inside the arena
+B200_API int b200_mul_mat_rowsplit(b200_ctx * ctx, const b200_tensor * w, const b200_tensor * x, b200_tensor * dst, int64_t row_lo,
+                                   const b200_exchange * ex);
+B200_API int b200_exchange_error(b200_ctx * ctx, const b200_exchange * ex);     // nonzero after a receive timed out (a peer died)
+
 // ---- row split (split-mode=row) helpers; reference ggml-cuda.cu:777-803 --------------------
 // rows [*row_low, *row_high) of an nrows-row weight that rank `rank` of `world` owns under `tensor_split`
 // (NULL = even), boundaries rounded down to `rounding` rows.

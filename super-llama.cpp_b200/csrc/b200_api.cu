@@ -272,6 +272,66 @@ extern "C" int b200_mul_mat_multi(b200_ctx * ctx, const b200_tensor * const * w,
     return rc;
 }
 
+// ---- split-mode=row over peer memory ----------------------------------------------------------------------------------------
+extern "C" int b200_peer_handle(b200_ctx * ctx, void * dptr, void * handle64) {
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "ipc handle size");
+    B200_CUDA_TRY(cudaIpcGetMemHandle((cudaIpcMemHandle_t *) handle64, dptr));
+    return B200_OK;
+}
+extern "C" int b200_peer_open(b200_ctx * ctx, const void * handle64, void ** dptr) {
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h; memcpy(&h, handle64, sizeof(h));
+    B200_CUDA_TRY(cudaIpcOpenMemHandle(dptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return B200_OK;
+}
+extern "C" int b200_peer_close(b200_ctx * ctx, void * dptr) {
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    B200_CUDA_TRY(cudaIpcCloseMemHandle(dptr));
+    return B200_OK;
+}
+static bool exchange_ok(const b200_exchange * ex) { return ex && ex->world >= 1 && ex->world <= B200_MAX_PEERS && ex->rank >= 0 && ex->rank < ex->world && ex->base[ex->rank]; }
+
+extern "C" int b200_mul_mat_rowsplit(b200_ctx * ctx, const b200_tensor * w, const b200_tensor * x, b200_tensor * dst, int64_t row_lo, const b200_exchange * ex) {
+    if (!ctx || !w || !x || !dst || !exchange_ok(ex)) { b200_set_error("mul_mat_rowsplit: bad arguments"); return B200_ERR_INVALID; }
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    const int64_t rows = w->ne[1];
+    if (x->ne[0] != w->ne[0] || row_lo < 0 || row_lo + rows > dst->ne[0] || dst->ne[1] != x->ne[1] || dst->type != B200_TYPE_F32 || dst->nb[0] != 4) {
+        b200_set_error("mul_mat_rowsplit: shape mismatch"); return B200_ERR_INVALID;
+    }
+    if (x->ne[1] != 1 || dst->ne[1] != 1) { b200_set_error("mul_mat_rowsplit: one activation column (decode) only"); return B200_ERR_UNSUPPORTED; }
+    char * own = (char *) ex->base[ex->rank];
+    const size_t doff = (size_t) ((char *) dst->data - own);
+    if (doff + (size_t) dst->ne[0] * 4 > ex->ctrl_off) { b200_set_error("mul_mat_rowsplit: dst is not inside the exchange arena"); return B200_ERR_INVALID; }
+    unsigned * ctrl = (unsigned *) (own + ex->ctrl_off);
+    const size_t ll_off = ex->ctrl_off + 256 + 2 * doff;                  // the low-latency mirror: 8 bytes per f32 of the arena
+    b200_rowsplit_peers pe; pe.nll = 0; pe.expected = ctrl + 8;
+    for (int r = 0; r < ex->world; ++r) pe.ll[pe.nll++] = (char *) ex->base[r] + ll_off + (size_t) row_lo * 8;
+    int rc = B200_OK;
+    if (rows > 0) {
+        if (!(is_quant(w->type) && q8_1_variant_env() == B200_Q8_1_X86 && b200_gemv_stream_supported(w, x))) {
+            b200_set_error("mul_mat_rowsplit: only the streaming GEMV is fused with the exchange (weight type %d, K=%lld)", w->type, (long long) w->ne[0]);
+            return B200_ERR_UNSUPPORTED;
+        }
+        float * d = (float *) dst->data + row_lo;                          // unused by the kernel in exchange mode
+        const void * image = nullptr;
+        if (w->ne[0] > B200_GEMV_FUSED_QUANT_MAX_K) { image = quantized_activations(ctx, x, B200_Q8_1_X86, &rc); if (!image) return rc; }
+        rc = b200_launch_gemv_stream(ctx, &w, 1, x, image, &d, &pe);       // compute + peer stores of (value, tag) in ONE kernel
+        if (rc) return rc;
+    }
+    // receive: all rows of dst from all ranks -> plain f32; also advances the exchange counter
+    rc = b200_launch_exchange_unpack(ctx, own + ll_off, (float *) dst->data, dst->ne[0], ctrl);
+    ctx->qcache.valid = 0; ctx->mcache.valid = 0;
+    b200_note_write(ctx, dst->data, b200_tensor_span(dst));
+    return rc;
+}
+extern "C" int b200_exchange_error(b200_ctx * ctx, const b200_exchange * ex) {
+    if (!ctx || !exchange_ok(ex)) return -1;
+    unsigned e = 0;
+    if (cudaMemcpy(&e, (unsigned *) ((char *) ex->base[ex->rank] + ex->ctrl_off) + 10, 4, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+    return (int) e;
+}
+
 extern "C" int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids, b200_tensor * dst) {
     if (!ctx || !as || !b || !ids || !dst) { b200_set_error("mul_mat_id: null argument"); return B200_ERR_INVALID; }
     B200_CUDA_TRY(cudaSetDevice(ctx->device));

@@ -163,7 +163,11 @@ int  b200_launch_fattn_tc(b200_ctx * ctx, const b200_tensor * q, const b200_tens
                           const b200_tensor * mask, const b200_tensor * sinks, b200_tensor * dst,
                           float scale, float max_bias, float softcap);     // B200_ERR_UNSUPPORTED = use another kernel
 bool b200_gemv_stream_supported(const b200_tensor * w, const b200_tensor * x);
-int  b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, const void * image, float * const * dst);
+// peers of a row-split MUL_MAT: this rank's rows inside the low-latency mirror of dst in every rank's arena (own included)
+struct b200_rowsplit_peers { int nll; void * ll[B200_MAX_PEERS]; const unsigned * expected; };
+int  b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, const void * image, float * const * dst,
+                             const b200_rowsplit_peers * peers = nullptr);
+int  b200_launch_exchange_unpack(b200_ctx * ctx, const void * ll, float * dst, int64_t M, unsigned * ctrl);
 #define B200_GEMV_FUSED_QUANT_MAX_K 8192    // above this, one quantize launch + image beats one quantization per CTA
 #define B200_GEMV_MAX_COLS 8
 bool b200_gemm_supported(const b200_tensor * w, const b200_tensor * x);

@@ -33,6 +33,10 @@ struct gs_args {
     gs_seg seg[GS_MAXSEG]; int nseg; int Mtot; int K;
     const float * x;                         // f32 activation column: quantized in-kernel when aq == NULL
     const int8_t * aq; const __half2 * ads;  // or a q8_1 image made by k_quantize_q8_1_soa (natural order): [K] quants, [K/32] (d, s)
+    // row-split exchange (nseg == 1): instead of dst, every result row is stored as an 8-byte (value, tag) pair into the
+    // low-latency mirror of dst in EVERY rank's arena (NVLink peer stores; 8-byte stores are single transactions, so the tag
+    // validates the value and no fence or flag is needed -- a system-scope fence measured ~7 us here).  tag = *expected + 1.
+    int nll; uint2 * ll[B200_MAX_PEERS]; const unsigned * expected;
 };
 
 template <int TYPE> struct gs_traits;
@@ -297,6 +301,8 @@ __global__ void __launch_bounds__(WIDE ? 256 : 384, WIDE ? 2 : 1) k_gemv_stream(
 
     // src1 is produced by the previous kernel in the stream: wait for it (and its memory) before the first read
     asm volatile("griddepcontrol.wait;" ::: "memory");
+    unsigned ll_tag = 0;
+    if (p.nll) { asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(ll_tag) : "l"(p.expected)); ll_tag += 1u; }
 
     // quantize the activation column to q8_1 straight into shared memory, in lane order.  Same arithmetic as
     // q8_1_block<B200_Q8_1_X86> (bit-exact with the reference), but 128-bit loads: a lane holds 4 consecutive values, the
@@ -376,7 +382,12 @@ __global__ void __launch_bounds__(WIDE ? 256 : 384, WIDE ? 2 : 1) k_gemv_stream(
                 if (lane == 0 && r < nr) {
                     const uint8_t * w; float * dst;
                     gs_locate(p, r_begin + rp * GS_RW + r, w, dst);
-                    *dst = v;
+                    if (p.nll == 0) *dst = v;
+                    else {
+                        const uint2 pk = make_uint2(__float_as_uint(v), ll_tag);
+                        for (int pr = 0; pr < p.nll; ++pr)
+                            asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"(p.ll[pr] + r_begin + rp * GS_RW + r), "r"(pk.x), "r"(pk.y) : "memory");
+                    }
                 }
                 acc[r] = 0.0f;
             }
@@ -384,6 +395,48 @@ __global__ void __launch_bounds__(WIDE ? 256 : 384, WIDE ? 2 : 1) k_gemv_stream(
         } else ++kc;
         if (++stage == GS_STAGES) { stage = 0; phase ^= 1; }
     }
+}
+
+// the receiving side of the row-split exchange: polls the local low-latency mirror until every row carries this exchange's tag
+// (rows arrive from all ranks, our own included), writes the plain f32 column, and the last CTA advances `expected`.  Gives up after ~5 s (a dead peer must not hang the GPU).
+__global__ void __launch_bounds__(256) k_exchange_unpack(const uint2 * ll, float * dst, int M, unsigned * expected, unsigned * counter, unsigned * error) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");      // the next matmul may prefetch its weights meanwhile
+    // the local GEMV (and through it the previous receive, which advanced `expected`) has retired: the PDL chain stays transitive
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    unsigned tag;
+    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(tag) : "l"(expected));
+    tag += 1u;
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < M; i += gridDim.x * blockDim.x) {
+        uint2 v;
+        while (true) {
+            asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(ll + i) : "memory");
+            if (v.y == tag) break;
+            unsigned long long t1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (t1 - t0 > 5000000000ull) { *error = 1u; break; }
+        }
+        dst[i] = __uint_as_float(v.x);
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned done = atomicAdd(counter, 1u);
+        if (done == gridDim.x - 1) { *counter = 0u; __threadfence(); *(volatile unsigned *) expected = tag; }
+    }
+}
+int b200_launch_exchange_unpack(b200_ctx * ctx, const void * ll, float * dst, int64_t M, unsigned * ctrl) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned) ((M + 255) / 256 < 32 ? (M + 255) / 256 : 32));
+    cfg.blockDim = dim3(256);
+    cfg.stream = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = ctx->pdl ? 1 : 0;
+    B200_LAUNCH(ctx, B200_K_GLUE, cudaLaunchKernelEx(&cfg, k_exchange_unpack, (const uint2 *) ll, dst, (int) M, ctrl + 8, ctrl + 9, ctrl + 10));
+    return B200_OK;
 }
 
 template <int TYPE> static size_t gs_smem_bytes(int K, bool wide) {
@@ -440,8 +493,15 @@ static int gs_launch(b200_ctx * ctx, const gs_args & p, int attr_slot) {
 }
 
 // n <= 3 weights of the same type sharing the activation column x; dst[i] is the f32 column of weight i
-int b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, const void * image, float * const * dst) {
+int b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, const void * image, float * const * dst,
+                            const b200_rowsplit_peers * peers) {
     gs_args p;
+    p.nll = 0; p.expected = nullptr;
+    for (int i = 0; i < B200_MAX_PEERS; ++i) p.ll[i] = nullptr;
+    if (peers && n == 1) {
+        p.nll = peers->nll; p.expected = peers->expected;
+        for (int i = 0; i < peers->nll; ++i) p.ll[i] = (uint2 *) peers->ll[i];
+    }
     p.nseg = n; p.Mtot = 0; p.x = (const float *) x->data; p.K = (int) w[0]->ne[0];
     p.aq = (const int8_t *) image; p.ads = image ? (const __half2 *) ((const int8_t *) image + p.K) : nullptr;
     for (int i = 0; i < n; ++i) {

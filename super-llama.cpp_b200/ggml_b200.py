@@ -30,6 +30,11 @@ class _Tensor(C.Structure):          # struct b200_tensor
                 ("ne", C.c_int64 * 4), ("nb", C.c_size_t * 4)]
 
 
+class Exchange(C.Structure):
+    """b200_exchange: the arenas of all ranks as mapped in this process"""
+    _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("base", C.c_void_p * 8), ("ctrl_off", C.c_size_t)]
+
+
 _lib = None
 
 
@@ -61,6 +66,9 @@ def lib():
         "b200_event_elapsed_ms": (i, [vp, vp, C.POINTER(f)]),
         "b200_graph_begin": (i, [vp]), "b200_graph_end": (vp, [vp]), "b200_graph_launch": (i, [vp, vp]), "b200_graph_destroy": (i, [vp]),
         "b200_split_row_range": (i, [i64, vp, i, i, i64, C.POINTER(i64), C.POINTER(i64)]),
+        "b200_peer_handle": (i, [vp, vp, vp]), "b200_peer_open": (i, [vp, vp, C.POINTER(vp)]), "b200_peer_close": (i, [vp, vp]),
+        "b200_mul_mat_rowsplit": (i, [vp, tp, tp, tp, i64, C.POINTER(Exchange)]), 
+        "b200_exchange_error": (i, [vp, C.POINTER(Exchange)]),
         "ggml_backend_init": (vp, []), "ggml_backend_score": (i, []), "ggml_backend_b200_reg": (vp, []),
     }
     for name, (res, args) in sig.items():
@@ -283,6 +291,24 @@ class Context:
             _check(lib().b200_unrepack(self.h, w.type, w.ptr, w.ne[0], w.ne[1] * w.ne[2] * w.ne[3], w.nb[1]), "unrepack")
             w.flags = 0
         return w
+
+    # ---- split-mode=row over NVLink peer memory (include/ggml-b200.h: b200_exchange) -----------------------------------------
+    def peer_handle(self, ptr):
+        buf = C.create_string_buffer(64)
+        _check(lib().b200_peer_handle(self.h, C.c_void_p(ptr), C.cast(buf, C.c_void_p)), "peer_handle")
+        return buf.raw
+
+    def peer_open(self, handle):
+        out = C.c_void_p()
+        _check(lib().b200_peer_open(self.h, C.cast(C.c_char_p(handle), C.c_void_p), C.byref(out)), "peer_open")
+        return out.value
+
+    def mul_mat_rowsplit(self, w, x, dst, row_lo, ex):
+        cw, cx, cd = w.c(), x.c(), dst.c()
+        _check(lib().b200_mul_mat_rowsplit(self.h, C.byref(cw), C.byref(cx), C.byref(cd), C.c_int64(row_lo), C.byref(ex)), "mul_mat_rowsplit")
+
+    def exchange_error(self, ex):
+        return lib().b200_exchange_error(self.h, C.byref(ex))
 
     def mul_mat_id(self, as_, b, ids, dst):
         ca, cb, ci, cd = as_.c(), b.c(), ids.c(), dst.c()

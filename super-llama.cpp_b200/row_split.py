@@ -51,3 +51,37 @@ class RowSplit:
         self.dist.all_gather(parts, mine)
         for (a, b), part in zip(rs, parts):
             t[:, a:b] = part[:, : b - a]
+
+
+class PeerExchange:
+    """The all-gather of split-mode=row done by the matmul kernel itself: every rank maps every other rank's exchange arena
+    (CUDA IPC over NVLink), the streaming GEMV's epilogue stores its rows as (value, tag) pairs into all arenas and a receive kernel validates them; torch.distributed is only
+    used to pass the 64-byte IPC handles around and for the start-up barrier."""
+
+    CTRL_BYTES = 256
+
+    def __init__(self, ctx, dist, world, rank, arena_bytes):
+        self.ctx, self.world, self.rank = ctx, world, rank
+        self.arena_bytes = (arena_bytes + 255) // 256 * 256
+        total = 3 * self.arena_bytes + self.CTRL_BYTES        # tensors | control block | (value, tag) mirror of the tensor area
+        self.base = ctx.malloc(total)
+        B._check(B.lib().b200_memset(ctx.h, self.base, 0, total), "memset")
+        ctx.synchronize()
+        handles = [None] * world
+        dist.all_gather_object(handles, ctx.peer_handle(self.base))
+        self.ex = B.Exchange()
+        self.ex.world, self.ex.rank, self.ex.ctrl_off = world, rank, self.arena_bytes
+        for r in range(world):
+            self.ex.base[r] = self.base if r == rank else ctx.peer_open(handles[r])
+        self.cursor = 0
+        dist.barrier()                                       # nobody signals before everybody has zeroed and mapped
+
+    def alloc(self, t, ne):
+        """carve a tensor out of the arena: same offset on every rank (every rank allocates in the same order)"""
+        dt = B.DeviceTensor(self.ctx, t, ne, ptr=self.base + self.cursor)
+        self.cursor += (dt.nbytes + 255) // 256 * 256
+        assert self.cursor <= self.arena_bytes, "exchange arena too small"
+        return dt
+
+    def mul_mat(self, w_local, x, dst_full, row_lo):
+        self.ctx.mul_mat_rowsplit(w_local, x, dst_full, row_lo, self.ex)
