@@ -52,7 +52,7 @@ template <int TYPE> struct gs_traits;
 // nibbles (dp4a on q & 0xF0F0F0F0 gives 16 x the sum).
 template <> struct gs_traits<B200_TYPE_Q4_K> {
     static constexpr int BLOCK_BYTES = 144;
-    static __host__ __device__ constexpr int stages(bool wide) { return wide ? 4 : 3; }
+    static __host__ __device__ constexpr int stages(int shape) { return shape == 1 ? 4 : 3; }
     static __host__ __device__ size_t act_bytes(int K) { return (size_t) K + (size_t) (K >> 8) * 64; }
     // 4 consecutive quants (bytes off..off+3 of q8_1 block blk32) packed in `word`; the group leader also stores (d, s)
     static __device__ __forceinline__ void store_act(uint8_t * s_act, int K, int nblocks, int blk32, int off, unsigned word, bool leader, float d, float s) {
@@ -115,7 +115,7 @@ template <> struct gs_traits<B200_TYPE_Q4_K> {
 // sc[8 n + j + 2 g].  Activations: planes[g][nj][gb] (16 int8) and dA4[n][gb] = (dA(4n), .., dA(4n+3)).
 template <> struct gs_traits<B200_TYPE_Q6_K> {
     static constexpr int BLOCK_BYTES = 210;
-    static __host__ __device__ constexpr int stages(bool wide) { return wide ? 3 : 2; }
+    static __host__ __device__ constexpr int stages(int shape) { return shape == 1 ? 3 : 2; }
     static __host__ __device__ size_t act_bytes(int K) { return (size_t) K + (size_t) (K >> 8) * 32; }
     static __device__ __forceinline__ void store_act(uint8_t * s_act, int K, int nblocks, int blk32, int off, unsigned word, bool leader, float d, float s) {
         const int gb = blk32 >> 3, sub = blk32 & 7, n = sub >> 2, g = sub & 3, hf = off >> 4;
@@ -174,7 +174,7 @@ template <> struct gs_traits<B200_TYPE_Q6_K> {
 // 32c+16..32c+31 (plane 1); value = d (q - 8), the -8 goes through q8_1's s = d_a * sum(a).  q8_0: unit c16 = 16 quants.
 template <> struct gs_traits<B200_TYPE_Q4_0> {
     static constexpr int BLOCK_BYTES = 144;
-    static __host__ __device__ constexpr int stages(bool wide) { return wide ? 4 : 3; }
+    static __host__ __device__ constexpr int stages(int shape) { return shape == 1 ? 4 : 3; }
     static __host__ __device__ size_t act_bytes(int K) { return (size_t) K + (size_t) (K >> 5) * 8; }
     static __device__ __forceinline__ void store_act(uint8_t * s_act, int K, int nblocks, int blk32, int off, unsigned word, bool leader, float d, float s) {
         const int gb = blk32 >> 3, c = blk32 & 7;
@@ -208,7 +208,7 @@ template <> struct gs_traits<B200_TYPE_Q4_0> {
 };
 template <> struct gs_traits<B200_TYPE_Q8_0> {
     static constexpr int BLOCK_BYTES = 272;
-    static __host__ __device__ constexpr int stages(bool wide) { return wide ? 3 : 2; }
+    static __host__ __device__ constexpr int stages(int shape) { return shape == 1 ? 3 : 2; }
     static __host__ __device__ size_t act_bytes(int K) { return (size_t) K + (size_t) (K >> 5) * 4; }
     static __device__ __forceinline__ void store_act(uint8_t * s_act, int K, int nblocks, int blk32, int off, unsigned word, bool leader, float d, float s) {
         const int gb = blk32 >> 3, sub = blk32 & 7;
@@ -247,11 +247,12 @@ static __device__ __forceinline__ void gs_locate(const gs_args & p, int gr, cons
     dst = p.seg[s].dst + r;
 }
 
-template <int TYPE, bool WIDE>
-__global__ void __launch_bounds__(WIDE ? 256 : 384, WIDE ? 2 : 1) k_gemv_stream(const gs_args p) {
+// SHAPE: 0 = LEAN (12 warps, 1 CTA/SM), 1 = WIDE (8 warps, deep rings, 2 CTAs/SM), 2 = DENSE (12 warps, 2 CTAs/SM: most warps per SM)
+template <int TYPE, int SHAPE>
+__global__ void __launch_bounds__(SHAPE == 1 ? 256 : 384, SHAPE == 0 ? 1 : 2) k_gemv_stream(const gs_args p) {
     using T = gs_traits<TYPE>;
-    constexpr int GS_WARPS = WIDE ? 8 : 12;
-    constexpr int GS_STAGES = T::stages(WIDE);
+    constexpr int GS_WARPS = SHAPE == 1 ? 8 : 12;
+    constexpr int GS_STAGES = T::stages(SHAPE);
     constexpr int CHUNK_BYTES = T::BLOCK_BYTES * GS_CB;
     constexpr int STAGE_BYTES = CHUNK_BYTES * GS_RW;
     extern __shared__ __align__(128) uint8_t smem[];
@@ -439,8 +440,8 @@ int b200_launch_exchange_unpack(b200_ctx * ctx, const void * ll, float * dst, in
     return B200_OK;
 }
 
-template <int TYPE> static size_t gs_smem_bytes(int K, bool wide) {
-    const int GS_WARPS = wide ? 8 : 12, GS_STAGES = gs_traits<TYPE>::stages(wide);
+template <int TYPE> static size_t gs_smem_bytes(int K, int shape) {
+    const int GS_WARPS = shape == 1 ? 8 : 12, GS_STAGES = gs_traits<TYPE>::stages(shape);
     return (size_t) GS_WARPS * GS_STAGES * gs_traits<TYPE>::BLOCK_BYTES * GS_CB * GS_RW + gs_traits<TYPE>::act_bytes(K) + GS_WARPS * GS_STAGES * 8;
 }
 #define GS_SMEM_MAX (200 * 1024)   // typical shapes need <= 113 KB, which lets two kernels co-reside on an SM
@@ -451,20 +452,23 @@ bool b200_gemv_stream_supported(const b200_tensor * w, const b200_tensor * x) {
     if (x->type != B200_TYPE_F32 || x->nb[0] != 4 || ((uintptr_t) x->data & 15)) return false;
     if (((uintptr_t) w->data & 15) || (w->nb[1] & 15) || w->ne[0] % 256 != 0 || w->ne[0] > 32768 || w->ne[1] > (1 << 28)) return false;
     const int K = (int) w->ne[0];
-    if (w->type == B200_TYPE_Q4_K) return !(w->flags & B200_TENSOR_REPACKED) && gs_smem_bytes<B200_TYPE_Q4_K>(K, false) <= GS_SMEM_MAX;
-    if (w->type == B200_TYPE_Q6_K) return (w->flags & B200_TENSOR_REPACKED) && K % 2048 == 0 && gs_smem_bytes<B200_TYPE_Q6_K>(K, false) <= GS_SMEM_MAX;
-    if (w->type == B200_TYPE_Q4_0) return (w->flags & B200_TENSOR_REPACKED) && gs_smem_bytes<B200_TYPE_Q4_0>(K, false) <= GS_SMEM_MAX;
-    if (w->type == B200_TYPE_Q8_0) return (w->flags & B200_TENSOR_REPACKED) && gs_smem_bytes<B200_TYPE_Q8_0>(K, false) <= GS_SMEM_MAX;
+    if (w->type == B200_TYPE_Q4_K) return !(w->flags & B200_TENSOR_REPACKED) && gs_smem_bytes<B200_TYPE_Q4_K>(K, 0) <= GS_SMEM_MAX;
+    if (w->type == B200_TYPE_Q6_K) return (w->flags & B200_TENSOR_REPACKED) && K % 2048 == 0 && gs_smem_bytes<B200_TYPE_Q6_K>(K, 0) <= GS_SMEM_MAX;
+    if (w->type == B200_TYPE_Q4_0) return (w->flags & B200_TENSOR_REPACKED) && gs_smem_bytes<B200_TYPE_Q4_0>(K, 0) <= GS_SMEM_MAX;
+    if (w->type == B200_TYPE_Q8_0) return (w->flags & B200_TENSOR_REPACKED) && gs_smem_bytes<B200_TYPE_Q8_0>(K, 0) <= GS_SMEM_MAX;
     return false;
 }
 
-template <int TYPE, bool WIDE>
+template <int TYPE, int SHAPE>
 static int gs_launch_cfg(b200_ctx * ctx, const gs_args & p, int attr_slot) {
-    constexpr int WARPS = WIDE ? 8 : 12;
-    const size_t smem = gs_smem_bytes<TYPE>(p.K, WIDE);
-    if (!ctx->attr_done[attr_slot]) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(k_gemv_stream<TYPE, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, WIDE ? 113 * 1024 : GS_SMEM_MAX));
-        ctx->attr_done[attr_slot] = 1;
+    constexpr int WARPS = SHAPE == 1 ? 8 : 12;
+    constexpr bool WIDE = SHAPE != 0;                                     // two CTAs per SM
+    const size_t smem = gs_smem_bytes<TYPE>(p.K, SHAPE);
+    static bool attr_done[64] = {};                                       // per kernel instantiation and device
+    (void) attr_slot;
+    if (!attr_done[ctx->device & 63]) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(k_gemv_stream<TYPE, SHAPE>, cudaFuncAttributeMaxDynamicSharedMemorySize, WIDE ? 113 * 1024 : GS_SMEM_MAX));
+        attr_done[ctx->device & 63] = true;
     }
     // persistent-size grid, rows split evenly over all warps; fewer CTAs when there are few rows
     const int64_t want = (p.Mtot + WARPS - 1) / WARPS;
@@ -477,7 +481,7 @@ static int gs_launch_cfg(b200_ctx * ctx, const gs_args & p, int attr_slot) {
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = ctx->pdl ? 1 : 0;
-    B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_gemv_stream<TYPE, WIDE>, p));
+    B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_gemv_stream<TYPE, SHAPE>, p));
     return B200_OK;
 }
 template <int TYPE>
@@ -485,11 +489,15 @@ static int gs_launch(b200_ctx * ctx, const gs_args & p, int attr_slot) {
     // WIDE once the weights outlast what the rings of one wave can hold (~22 MB), if its smem fits two CTAs per SM
     const size_t bytes = (size_t) p.Mtot * (p.K >> 8) * gs_traits<TYPE>::BLOCK_BYTES;
     static int force = -1;
-    if (force < 0) { const char * e = getenv("GGML_B200_GEMV_SHAPE"); force = e ? (e[0] == 'w' ? 1 : e[0] == 'l' ? 2 : 0) : 0; }
+    if (force < 0) { const char * e = getenv("GGML_B200_GEMV_SHAPE"); force = e ? (e[0] == 'w' ? 1 : e[0] == 'l' ? 2 : e[0] == 'd' ? 3 : 0) : 0; }
     bool wide = bytes > ((size_t) 24 << 20);
     if (force == 1) wide = true; else if (force == 2) wide = false;
-    if (wide && gs_smem_bytes<TYPE>(p.K, true) <= 113 * 1024) return gs_launch_cfg<TYPE, true>(ctx, p, attr_slot);
-    return gs_launch_cfg<TYPE, false>(ctx, p, attr_slot + 4);
+    // two-CTA shapes: DENSE (24 warps per SM) measured 8-10 % faster than WIDE in isolation for K <= 8192, but in the token's
+    // kernel chain it leaves no room for the next kernel's PDL prologue and the whole step got 3 % slower: opt-in only
+    const bool dense = force == 3;
+    if ((wide || force == 3) && dense && gs_smem_bytes<TYPE>(p.K, 2) <= 113 * 1024) return gs_launch_cfg<TYPE, 2>(ctx, p, attr_slot);
+    if (wide && gs_smem_bytes<TYPE>(p.K, 1) <= 113 * 1024) return gs_launch_cfg<TYPE, 1>(ctx, p, attr_slot);
+    return gs_launch_cfg<TYPE, 0>(ctx, p, attr_slot + 4);
 }
 
 // n <= 3 weights of the same type sharing the activation column x; dst[i] is the f32 column of weight i
