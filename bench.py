@@ -220,7 +220,7 @@ class HotPathModel:
     def step(self, attention=True):
         """issue every MUL_MAT and FLASH_ATTN_EXT node of one llama graph evaluation on the ctx stream"""
         c = self.ctx
-        fuse = self.N == 1
+        fuse = True      # wq/wk/wv and gate/up share src1: one launch per run of equal weight types (GEMV at n=1, GEMM at n=512)
         for il, L in enumerate(self.layers):
             if fuse:
                 self._mm_group([L["wq"], L["wk"], L["wv"]], self.x, [self.q, self.k, self.v])

@@ -257,6 +257,20 @@ extern "C" int b200_mul_mat_multi(b200_ctx * ctx, const b200_tensor * const * w,
         fuse = b200_gemv_stream_supported(w[i], x) && w[i]->type == w[0]->type && w[i]->ne[0] == w[0]->ne[0] && x->ne[0] == w[i]->ne[0] &&
                dst[i]->type == B200_TYPE_F32 && dst[i]->nb[0] == 4 && dst[i]->ne[0] == w[i]->ne[1] && dst[i]->ne[1] == 1 && dst[i]->ne[2] == 1 && dst[i]->ne[3] == 1;
     }
+    // prefill: the same fusion for the tcgen05 GEMM (grid.y walks the row tiles of all weights)
+    bool fuse_gemm = !fuse && n > 1 && n <= 3 && x->ne[1] > B200_GEMV_MAX_COLS;
+    for (int i = 0; i < n && fuse_gemm; ++i)
+        fuse_gemm = is_quant(w[i]->type) && b200_gemm_supported(w[i], x) && w[i]->type == w[0]->type && w[i]->ne[0] == w[0]->ne[0] && x->ne[0] == w[i]->ne[0] &&
+                    dst[i]->type == B200_TYPE_F32 && dst[i]->nb[0] == 4 && dst[i]->ne[0] == w[i]->ne[1] && dst[i]->ne[1] == x->ne[1] && dst[i]->ne[2] == 1 && dst[i]->ne[3] == 1;
+    if (fuse_gemm) {
+        B200_CUDA_TRY(cudaSetDevice(ctx->device));
+        int rc;
+        const void * image = quantized_activations(ctx, x, B200_ACT_BF16, &rc);
+        if (!image) return rc;
+        rc = b200_launch_gemm_multi(ctx, w, n, image, x->ne[1], dst);
+        for (int i = 0; i < n; ++i) b200_note_write(ctx, dst[i]->data, b200_tensor_span(dst[i]));
+        return rc;
+    }
     if (!fuse) {
         for (int i = 0; i < n; ++i) { const int rc = b200_mul_mat(ctx, w[i], x, dst[i]); if (rc) return rc; }
         return B200_OK;

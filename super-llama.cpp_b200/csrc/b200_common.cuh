@@ -172,6 +172,7 @@ int  b200_launch_exchange_unpack(b200_ctx * ctx, const void * ll, float * dst, i
 #define B200_GEMV_MAX_COLS 8
 bool b200_gemm_supported(const b200_tensor * w, const b200_tensor * x);
 int  b200_launch_gemm_q(b200_ctx * ctx, const b200_tensor * w, const void * image, int64_t N, b200_tensor * dst);   // image: bf16 [N][K]
+int  b200_launch_gemm_multi(b200_ctx * ctx, const b200_tensor * const * w, int n, const void * image, int64_t N, b200_tensor * const * dst);
 int  b200_launch_act_bf16(b200_ctx * ctx, const float * x, size_t nb1, int64_t K, int64_t N, void * image);
 #define B200_ACT_BF16 2                     // activation-image kind next to the two q8_1 variants
 bool b200_gemm_id_supported(const b200_tensor * as, const b200_tensor * b, const b200_tensor * ids);

@@ -33,9 +33,10 @@
 #define GM_THREADS ((GM_PRODUCERS + 3) * 32)
 
 struct gm_args {
-    const uint8_t * w; size_t w_nb1;
-    float * dst; size_t d_ld;            // dst[m + n * d_ld]
-    int M, N, K;
+    // up to three weight tensors of one type that share the activations (wq/wk/wv, ffn_gate/ffn_up): grid.y walks their row tiles
+    struct { float * dst; size_t d_ld; int M; int mtiles; } seg[3];   // dst[m + n * d_ld]
+    int nseg;
+    int N, K;
     int BN;                              // activation columns per CTA (UMMA N)
     int MT;                              // 128-row weight tiles per CTA (1 or 2): 2 halves the activation traffic per flop
     int SA, SB, RS;                      // ring depths: A stages in TMEM (power of two), B stages in smem (64-K steps), raw 256-K weight blocks
@@ -224,9 +225,10 @@ template <> struct gm_traits<B200_TYPE_Q8_0> {
     }
 };
 
+struct gm_maps { CUtensorMap w[3]; CUtensorMap w2[3]; };
+
 template <int TYPE>
-__global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
-                                                                const __grid_constant__ CUtensorMap tmap_w2) {
+__global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ gm_maps maps) {
     using T = gm_traits<TYPE>;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     const int MT = p.MT, BN = p.BN, SA = p.SA, SB = p.SB, RS = p.RS;
@@ -239,12 +241,16 @@ __global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const
     const uint32_t rf0 = eb0 + 8 * SB, re0 = rf0 + 8 * RS;           // raw block landed / raw block consumed
     const uint32_t tfull = re0 + 8 * RS, tslot = tfull + 8;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int m0 = blockIdx.y * (MT * GM_BM);
+    int sg = 0, mtile = blockIdx.y;
+    if (p.nseg > 1 && mtile >= p.seg[0].mtiles) { mtile -= p.seg[0].mtiles; sg = 1; if (p.nseg > 2 && mtile >= p.seg[1].mtiles) { mtile -= p.seg[1].mtiles; sg = 2; } }
+    const CUtensorMap & tmap_w = maps.w[sg], & tmap_w2 = maps.w2[sg];
+    const int pM = p.seg[sg].M;
+    const int m0 = mtile * (MT * GM_BM);
     int n0 = blockIdx.x * BN, n_end = p.N, wrow0 = m0;
     if (p.counts) {                                                          // grouped: this CTA serves expert blockIdx.z
         const int e = blockIdx.z, cnt = p.counts[e];
         if (n0 >= cnt) return;                                               // uniform per CTA, before any barrier or TMEM allocation
-        n0 += p.offsets[e]; n_end = p.offsets[e] + cnt; wrow0 = e * p.M + m0; // experts are stacked rows of one tall weight matrix
+        n0 += p.offsets[e]; n_end = p.offsets[e] + cnt; wrow0 = e * pM + m0; // experts are stacked rows of one tall weight matrix
     }
     const int nks = p.K / GM_BK, nunits = p.K / T::RAW_K;
     // TMEM columns: accumulators [0, MT*BN), then A stages: stage s, tile t at MT*BN + (s*MT + t)*32
@@ -315,16 +321,16 @@ __global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const
         tc_fence_after();
         const int mm = m0 + tile * GM_BM + q * 32 + lane;
         const int c_begin = MT == 2 ? 0 : grp * (BN / 2), c_end = MT == 2 ? BN : c_begin + BN / 2;   // MT=1: the groups split the columns
-        float * drow = p.dst + mm;
+        float * drow = p.seg[sg].dst + mm;
         for (int c0 = c_begin; c0 < c_end; c0 += 16) {
             if (n0 + c0 >= n_end) break;
             uint32_t r[16];
             tmem_ld16(tmem + lane_base + (uint32_t) (tile * BN + c0), r);
             tmem_ld_wait();
-            if (mm < p.M) {
+            if (mm < pM) {
 #pragma unroll
                 for (int j = 0; j < 16; ++j)
-                    if (n0 + c0 + j < n_end) drow[p.col_off ? (size_t) p.col_off[n0 + c0 + j] : (size_t) (n0 + c0 + j) * p.d_ld] = __uint_as_float(r[j]);
+                    if (n0 + c0 + j < n_end) drow[p.col_off ? (size_t) p.col_off[n0 + c0 + j] : (size_t) (n0 + c0 + j) * p.seg[sg].d_ld] = __uint_as_float(r[j]);
             }
         }
         tc_fence_before();
@@ -435,20 +441,59 @@ static void gemm_pick_tile(const b200_ctx * ctx, int64_t M, int64_t N, int & MT,
     BN = N > 64 ? 128 : N > 32 ? 64 : 32;
 }
 
-// image = bf16 [N][K] activations (b200_launch_act_bf16); grouped (MUL_MAT_ID) when gi != NULL
+// tensor maps over one weight tensor (rows_total rows; for MUL_MAT_ID the experts stacked)
+static bool gemm_weight_maps(encode_tiled_fn encode, const b200_tensor * w, int64_t rows_total, CUtensorMap * tmap_w, CUtensorMap * tmap_w2) {
+    const cuuint32_t e4[4] = { 1, 1, 1, 1 };
+    const int64_t K = w->ne[0];
+    CUresult cw;
+    if (w->type == B200_TYPE_Q8_0) {
+        // repacked q8_0: rows of 17 x 16 B per 256 weights
+        const cuuint64_t wdim[3] = { 16, (cuuint64_t) (K / 256) * 17, (cuuint64_t) rows_total };
+        const cuuint64_t wstr[2] = { 16, (cuuint64_t) w->nb[1] };
+        const cuuint32_t wbox[3] = { 16, 17, GM_BM };
+        cw = encode(tmap_w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, w->data, wdim, wstr, wbox, e4, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        *tmap_w2 = *tmap_w;
+    } else if (w->type != B200_TYPE_Q6_K) {
+        // q4_K and repacked q4_0: the weight rows as a 2-D byte tensor; box = 144 bytes (256 weights) of 128 consecutive rows
+        const cuuint64_t wdim[2] = { (cuuint64_t) (K / 256) * 144, (cuuint64_t) rows_total };
+        const cuuint64_t wstr[1] = { (cuuint64_t) w->nb[1] };
+        const cuuint32_t wbox[2] = { 144, GM_BM };
+        cw = encode(tmap_w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, w->data, wdim, wstr, wbox, e4, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        *tmap_w2 = *tmap_w;
+    } else {
+        // repacked q6_K: {byte in unit-row (128), unit-row (13), group (K/2048), weight row}; box = column b (16 B) of the 13 unit-rows
+        const cuuint64_t wdim[4] = { 128, 13, (cuuint64_t) (K / 2048), (cuuint64_t) rows_total };
+        const cuuint64_t wstr[3] = { 128, 1680, (cuuint64_t) w->nb[1] };
+        const cuuint32_t wbox[4] = { 16, 13, 1, GM_BM };
+        cw = encode(tmap_w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 4, w->data, wdim, wstr, wbox, e4, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        // the eight fp16 d's of a group: 16 B at byte 1664 of every group
+        const cuuint64_t ddim[3] = { 16, (cuuint64_t) (K / 2048), (cuuint64_t) rows_total };
+        const cuuint64_t dstr[2] = { 1680, (cuuint64_t) w->nb[1] };
+        const cuuint32_t dbox[3] = { 16, 1, GM_BM };
+        if (cw == CUDA_SUCCESS)
+            cw = encode(tmap_w2, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (char *) w->data + 1664, ddim, dstr, dbox, e4, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    }
+    return cw == CUDA_SUCCESS;
+}
+
+// image = bf16 [N][K] activations (b200_launch_act_bf16); nseg weights of one type sharing them; grouped (MUL_MAT_ID) when gi != NULL
 struct gm_group { const int * counts; const int * offsets; const long long * col_off; int n_expert; int bn; };
-static int gemm_launch(b200_ctx * ctx, const b200_tensor * w, const void * image, int64_t N, float * dst, size_t d_ld, const gm_group * gi) {
+static int gemm_launch(b200_ctx * ctx, const b200_tensor * const * ws, int nseg, const void * image, int64_t N, float * const * dst, const size_t * d_ld, const gm_group * gi) {
     encode_tiled_fn encode = b200_get_encode_tiled();
     if (!encode) { b200_set_error("gemm: cuTensorMapEncodeTiled not available from the driver"); return B200_ERR_CUDA; }
+    const b200_tensor * w = ws[0];
     gm_args p;
-    p.w = (const uint8_t *) w->data; p.w_nb1 = w->nb[1];
-    p.dst = dst; p.d_ld = d_ld;
     p.counts = gi ? gi->counts : nullptr; p.offsets = gi ? gi->offsets : nullptr; p.col_off = gi ? gi->col_off : nullptr;
-    const int64_t rows_total = w->ne[1] * (gi ? gi->n_expert : 1);     // experts stacked as rows of one tall matrix
-    p.M = (int) w->ne[1]; p.N = (int) N; p.K = (int) w->ne[0];
+    p.N = (int) N; p.K = (int) w->ne[0]; p.nseg = nseg;
+    int64_t Mtot = 0;
+    for (int i = 0; i < nseg; ++i) Mtot += ws[i]->ne[1];
     static const int force_bn = getenv("GGML_B200_GEMM_BN") ? atoi(getenv("GGML_B200_GEMM_BN")) : 0;
     static const int force_mt = getenv("GGML_B200_GEMM_MT") ? atoi(getenv("GGML_B200_GEMM_MT")) : 0;
-    gemm_pick_tile(ctx, p.M, p.N, p.MT, p.BN);
+    gemm_pick_tile(ctx, Mtot, p.N, p.MT, p.BN);
     if (force_bn) p.BN = force_bn;
     if (force_mt) p.MT = force_mt;
     if (gi) { p.MT = 1; p.BN = gi->bn; }
@@ -469,42 +514,20 @@ static int gemm_launch(b200_ctx * ctx, const b200_tensor * w, const void * image
     const CUresult cr = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (void *) image, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (cr != CUDA_SUCCESS) { b200_set_error("gemm: cuTensorMapEncodeTiled failed (%d)", (int) cr); return B200_ERR_CUDA; }
+    gm_maps maps;
+    unsigned mtiles_total = 0;
+    for (int i = 0; i < 3; ++i) {
+        const b200_tensor * wi = ws[i < nseg ? i : 0];
+        if (!gemm_weight_maps(encode, wi, wi->ne[1] * (gi ? gi->n_expert : 1), &maps.w[i], &maps.w2[i])) {
+            b200_set_error("gemm: cuTensorMapEncodeTiled (weights) failed"); return B200_ERR_CUDA;
+        }
+        p.seg[i].dst = i < nseg ? dst[i] : nullptr; p.seg[i].d_ld = i < nseg ? d_ld[i] : 0;
+        p.seg[i].M = i < nseg ? (int) wi->ne[1] : 0;
+        p.seg[i].mtiles = i < nseg ? (int) ((wi->ne[1] + p.MT * GM_BM - 1) / (p.MT * GM_BM)) : 0;
+        mtiles_total += (unsigned) p.seg[i].mtiles;
+    }
     const bool q6 = w->type == B200_TYPE_Q6_K, q8 = w->type == B200_TYPE_Q8_0;
     const int tile_bytes = q6 ? gm_traits<B200_TYPE_Q6_K>::TILE_BYTES : q8 ? gm_traits<B200_TYPE_Q8_0>::TILE_BYTES : gm_traits<B200_TYPE_Q4_K>::TILE_BYTES;
-    CUtensorMap tmap_w, tmap_w2;
-    CUresult cw;
-    if (q8) {
-        // repacked q8_0: rows of 17 x 16 B per 256 weights
-        const cuuint64_t wdim[3] = { 16, (cuuint64_t) (p.K / 256) * 17, (cuuint64_t) rows_total };
-        const cuuint64_t wstr[2] = { 16, (cuuint64_t) p.w_nb1 };
-        const cuuint32_t wbox[3] = { 16, 17, GM_BM }, e3[3] = { 1, 1, 1 };
-        cw = encode(&tmap_w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void *) p.w, wdim, wstr, wbox, e3, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                    CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        tmap_w2 = tmap_w;
-    } else if (!q6) {
-        // q4_K and repacked q4_0: the weight rows as a 2-D byte tensor; box = 144 bytes (256 weights) of 128 consecutive rows
-        const cuuint64_t wdim[2] = { (cuuint64_t) (p.K / 256) * 144, (cuuint64_t) rows_total };
-        const cuuint64_t wstr[1] = { (cuuint64_t) p.w_nb1 };
-        const cuuint32_t wbox[2] = { 144, GM_BM };
-        cw = encode(&tmap_w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, (void *) p.w, wdim, wstr, wbox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                    CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        tmap_w2 = tmap_w;
-    } else {
-        // repacked q6_K: {byte in unit-row (128), unit-row (13), group (K/2048), weight row}; box = column b (16 B) of the 13 unit-rows
-        const cuuint64_t wdim[4] = { 128, 13, (cuuint64_t) (p.K / 2048), (cuuint64_t) rows_total };
-        const cuuint64_t wstr[3] = { 128, 1680, (cuuint64_t) p.w_nb1 };
-        const cuuint32_t wbox[4] = { 16, 13, 1, GM_BM }, e4[4] = { 1, 1, 1, 1 };
-        cw = encode(&tmap_w, CU_TENSOR_MAP_DATA_TYPE_UINT8, 4, (void *) p.w, wdim, wstr, wbox, e4, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                    CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-        // the eight fp16 d's of a group: 16 B at byte 1664 of every group
-        const cuuint64_t ddim[3] = { 16, (cuuint64_t) (p.K / 2048), (cuuint64_t) rows_total };
-        const cuuint64_t dstr[2] = { 1680, (cuuint64_t) p.w_nb1 };
-        const cuuint32_t dbox[3] = { 16, 1, GM_BM };
-        if (cw == CUDA_SUCCESS)
-            cw = encode(&tmap_w2, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void *) (p.w + 1664), ddim, dstr, dbox, e4, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                        CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    }
-    if (cw != CUDA_SUCCESS) { b200_set_error("gemm: cuTensorMapEncodeTiled (weights) failed (%d)", (int) cw); return B200_ERR_CUDA; }
     const size_t raw_bytes = (size_t) p.RS * p.MT * tile_bytes;
     if (!force_sb) { p.SB = (int) ((220 * 1024 - 2048 - raw_bytes) / ((size_t) p.BN * 128)); if (p.SB > 8) p.SB = 8; }
     if (p.SB < 2) { b200_set_error("gemm: tile does not fit in shared memory"); return B200_ERR_UNSUPPORTED; }
@@ -516,18 +539,25 @@ static int gemm_launch(b200_ctx * ctx, const b200_tensor * w, const void * image
         B200_CUDA_TRY(cudaFuncSetAttribute(k_gemm_q<B200_TYPE_Q8_0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 225 * 1024));
         ctx->attr_done[5] = 1;
     }
-    dim3 grid((unsigned) ((p.N + p.BN - 1) / p.BN), (unsigned) ((p.M + p.MT * GM_BM - 1) / (p.MT * GM_BM)), (unsigned) (gi ? gi->n_expert : 1));
+    dim3 grid((unsigned) ((p.N + p.BN - 1) / p.BN), mtiles_total, (unsigned) (gi ? gi->n_expert : 1));
     switch (w->type) {
-        case B200_TYPE_Q6_K: B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q6_K><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap, tmap_w, tmap_w2)); break;
-        case B200_TYPE_Q8_0: B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q8_0><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap, tmap_w, tmap_w2)); break;
-        case B200_TYPE_Q4_0: B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q4_0><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap, tmap_w, tmap_w2)); break;
-        default:             B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q4_K><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap, tmap_w, tmap_w2)); break;
+        case B200_TYPE_Q6_K: B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q6_K><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap, maps)); break;
+        case B200_TYPE_Q8_0: B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q8_0><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap, maps)); break;
+        case B200_TYPE_Q4_0: B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q4_0><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap, maps)); break;
+        default:             B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q4_K><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap, maps)); break;
     }
     return B200_OK;
 }
 
 int b200_launch_gemm_q(b200_ctx * ctx, const b200_tensor * w, const void * image, int64_t N, b200_tensor * dst) {
-    return gemm_launch(ctx, w, image, N, (float *) dst->data, dst->nb[1] / 4, nullptr);
+    float * d = (float *) dst->data; const size_t ld = dst->nb[1] / 4;
+    return gemm_launch(ctx, &w, 1, image, N, &d, &ld, nullptr);
+}
+// n <= 3 weights of one type and K sharing the activation image: one launch
+int b200_launch_gemm_multi(b200_ctx * ctx, const b200_tensor * const * w, int n, const void * image, int64_t N, b200_tensor * const * dst) {
+    float * d[3]; size_t ld[3];
+    for (int i = 0; i < n; ++i) { d[i] = (float *) dst[i]->data; ld[i] = dst[i]->nb[1] / 4; }
+    return gemm_launch(ctx, w, n, image, N, d, ld, nullptr);
 }
 
 // ---- MUL_MAT_ID as a grouped GEMM -----------------------------------------------------------------------------------------------
@@ -602,5 +632,6 @@ int b200_launch_gemm_id_q(b200_ctx * ctx, const b200_tensor * as, const b200_ten
     const int avg = npairs / (n_expert > 0 ? n_expert : 1);
     gi.bn = avg > 96 ? 128 : avg > 48 ? 64 : 32;
     b200_tensor w2 = *as; w2.ne[2] = 1;
-    return gemm_launch(ctx, &w2, image, npairs, (float *) dst->data, 0, &gi);
+    const b200_tensor * wp = &w2; float * dd = (float *) dst->data; const size_t ld0 = 0;
+    return gemm_launch(ctx, &wp, 1, image, npairs, &dd, &ld0, &gi);
 }

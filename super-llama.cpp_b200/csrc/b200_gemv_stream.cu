@@ -249,7 +249,7 @@ static __device__ __forceinline__ void gs_locate(const gs_args & p, int gr, cons
 
 // SHAPE: 0 = LEAN (12 warps, 1 CTA/SM), 1 = WIDE (8 warps, deep rings, 2 CTAs/SM), 2 = DENSE (12 warps, 2 CTAs/SM: most warps per SM)
 template <int TYPE, int SHAPE>
-__global__ void __launch_bounds__(SHAPE == 1 ? 256 : 384, SHAPE == 0 ? 1 : 2) k_gemv_stream(const gs_args p) {
+__global__ void __launch_bounds__(SHAPE == 1 ? 256 : 384, 2) k_gemv_stream(const gs_args p) {
     using T = gs_traits<TYPE>;
     constexpr int GS_WARPS = SHAPE == 1 ? 8 : 12;
     constexpr int GS_STAGES = T::stages(SHAPE);

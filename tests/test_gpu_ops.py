@@ -300,6 +300,23 @@ def test_mul_mat_multi_shared_src1(ctx, B, orc, t):
     assert O.nmse(orc.mul_mat(O.Q8_0, wq8, K, 64, x, 1, act=O.ACT_Q8_1), ctx.download(d8)) < 1e-9
 
 
+@pytest.mark.parametrize("t", [O.Q4_K, O.Q6_K])
+def test_mul_mat_multi_prefill_gemm(ctx, B, orc, t):
+    """wq/wk/wv (and gate/up) of a prefill ubatch in ONE tcgen05 GEMM launch: grid.y walks the row tiles of all weights"""
+    rng = np.random.default_rng(15 + t)
+    K, N, Ms = 2048, 96, (512, 128, 200)
+    ws = [O.random_blocks(rng, t, K, M) for M in Ms]
+    x = rng.standard_normal((N, K)).astype(np.float32)
+    dws = [ctx.repack(ctx.upload(t, [K, M], w)) for w, M in zip(ws, Ms)]
+    dx = ctx.upload(B.F32, [K, N], x)
+    dds = [ctx.empty(B.F32, [M, N]) for M in Ms]
+    k0 = ctx.launches_by_kind()["gemm"]
+    ctx.mul_mat_multi(dws, dx, dds)
+    assert ctx.launches_by_kind()["gemm"] - k0 == 1
+    for w, M, dd in zip(ws, Ms, dds):
+        _check_prefill(orc, ctx.download(dd).reshape(1, 1, N, M), t, w, K, M, x, N)
+
+
 def test_mul_mat_shared_activation_cache(ctx, B, orc):
     """wq/wk/wv-style reuse of one activation tensor, then an overwrite of it through the API: the cached q8_1 image
     must be dropped (b200_ctx_invalidate semantics, include/ggml-b200.h)"""
