@@ -35,6 +35,9 @@ TSIZE = {Q4_K: 144, Q6_K: 210}
 
 # Llama-3-8B: n_embd, n_ff, n_head, n_head_kv, head_dim, n_layer, n_vocab
 LLAMA3_8B = dict(name="llama3-8b", n_embd=4096, n_ff=14336, n_head=32, n_head_kv=8, head_dim=128, n_layer=32, n_vocab=128256)
+# BASELINE.json configs[3]: the 8-GPU row-split scale point (not the default bench line)
+LLAMA3_70B = dict(name="llama3-70b", n_embd=8192, n_ff=28672, n_head=64, n_head_kv=8, head_dim=128, n_layer=80, n_vocab=128256)
+MODELS = {"8b": LLAMA3_8B, "70b": LLAMA3_70B}
 
 
 def use_more_bits(i, n):       # src/llama-quant.cpp:186-188
@@ -203,6 +206,9 @@ class HotPathModel:
     def _mm_group(self, ws, x, dsts):
         """MUL_MATs that share src1: one fused launch per run of equal weight types (the plugin fuses the same nodes)"""
         if self.world > 1:
+            if getattr(self, "peer", None) is not None and dsts[0].ne[1] == 1:
+                self.peer.mul_mat_multi([w[0] for w in ws], x, dsts, [w[1] for w in ws])   # one launch per run of equal types, exchange included
+                return
             for w, d in zip(ws, dsts):
                 self._mm(w, x, d)
             return
@@ -330,16 +336,16 @@ def cpu_baseline(cfg, depth, budget_s=20.0, full_token_steps=0, warmup=1):
 
 
 def run_reference(args):
-    cfg = LLAMA3_8B
+    cfg = MODELS[args.model]
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     t0 = time.time()
     tps, kind, cores, sample = cpu_baseline(cfg, args.depth, budget_s=60.0)
-    line = {"impl": "reference", "metric": "tg128 tok/s (llama-bench, Llama-3-8B Q4_K_M)", "value": tps, "unit": "tok/s", "n_gpus": args.gpus,
+    line = {"impl": "reference", "metric": f"tg128 tok/s (llama-bench, {cfg['name'].replace('llama3', 'Llama-3').upper().replace('LLAMA', 'Llama')} Q4_K_M)", "value": tps, "unit": "tok/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / tps, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "int8 dot / f32 accumulate (q8_0, q8_K activations)", "data": "synthetic",
-            "config": {"workload": "llama3-8b-q4_k_m tg128 decode hot path (MUL_MAT + FLASH_ATTN_EXT nodes)", "depth": args.depth},
+            "config": {"workload": f"{cfg['name']}-q4_k_m tg128 decode hot path (MUL_MAT + FLASH_ATTN_EXT nodes)", "depth": args.depth},
             "cpu_baseline": {"value": tps, "unit": "tok/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": tps, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "wall_s": time.time() - t0}
@@ -362,7 +368,7 @@ def run_b200(args):
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     ctx = B.Context(local)
-    cfg = LLAMA3_8B
+    cfg = MODELS[args.model]
     hbm_gbs, tf_burst, tf_sust, peak_src = measured_peaks()
 
     keep = []
@@ -490,13 +496,13 @@ def run_b200(args):
         tps = 1e3 / ms_tg
         total_bytes = tg.weight_bytes * world + tg.kv_bytes_per_layer * cfg["n_layer"]
         result = {
-            "metric": "tg128 tok/s (llama-bench, Llama-3-8B Q4_K_M)", "value": tps, "unit": "tok/s", "n_gpus": world, "steps": args.steps,
+            "metric": f"tg128 tok/s (llama-bench, {cfg['name'].replace('llama3', 'Llama-3').upper().replace('LLAMA', 'Llama')} Q4_K_M)", "value": tps, "unit": "tok/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_tg, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "int8 dp4a dot / f32 accumulate (q8_1 activations); f16 KV, f32 softmax", "data": "synthetic",
-            "config": {"workload": "llama3-8b-q4_k_m tg128: all MUL_MAT + FLASH_ATTN_EXT nodes of one decode token (32 layers + output head); glue ops not included",
+            "config": {"workload": f"{cfg['name']}-q4_k_m tg128: all MUL_MAT + FLASH_ATTN_EXT nodes of one decode token ({cfg['n_layer']} layers + output head); glue ops not included",
                        "tensor_types": "Q4_K_M mix: q4_K, q6_K on attn_v/ffn_down of 16 layers, q6_K output", "depth": args.depth, "n_kv": tg.n_kv,
                        "parallelism": (f"row-split tp{world}, all-gather " + ("fused into the GEMV epilogue (NVLink peer stores)" if peer is not None else "by NCCL")) if world > 1 else "single GPU", "cuda_graph": bool(graph),
-                       "l2": "weights 4.6 GB >> 126 MB L2, streamed once per step"},
+                       "l2": f"weights {tg.weight_bytes * world / 1e9:.1f} GB >> 126 MB L2, streamed once per step"},
             "hbm_bytes_per_step": total_bytes, "hbm_frac_whole_step": total_bytes / world / (ms_tg * 1e-3) / 1e9 / hbm_gbs,
             "roofline": {"kernel": "k_gemv_stream (TMA-streamed dequant-GEMV with fused q8_1 quantization, q4_K + q6_K)", "bound": "hbm", "achieved": achieved, "peak": hbm_gbs, "unit": "GB/s",
                          "frac": achieved / hbm_gbs, "traffic": traffic_per_launch(gemv_bytes_step / max(gemv_n, 1)), "algorithmic_bytes_per_launch": gemv_bytes_step / max(gemv_n, 1), "peak_source": f"{peak_src} (MEASURED_PEAKS.json hbm_gbs)",
@@ -539,6 +545,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--depth", type=int, default=0, help="tokens already in the KV cache (llama-bench -d)")
+    ap.add_argument("--model", default="8b", choices=sorted(MODELS), help="8b = the headline config; 70b = configs[3] scale point")
     ap.add_argument("--no-pp", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-graph", action="store_true")

@@ -147,8 +147,9 @@ B200_API int b200_unrepack(b200_ctx * ctx, int type, void * data, int64_t k, int
 //   [ctrl_off + 256, ctrl_off + 256 + 2*ctrl_off)   low-latency mirror: 8 bytes (f32 value, uint32 tag) per f32 of the tensor area
 // A row-split MUL_MAT computes rows [row_lo, row_lo + w->ne[1]) of dst and its epilogue stores each of them as a (value, tag)
 // pair straight into EVERY rank's mirror (peer stores over NVLink; an 8-byte store is one transaction, so the tag validates the
-// value: no fence, no flag).  A small receive kernel on every rank polls its own mirror until all rows carry the tag and writes
-// the plain f32 column; kernels after it on the stream see the complete dst.
+// value: no fence, no flag).  The SAME kernel then receives: its threads poll the rank's own mirror until every row of dst carries
+// the tag and write the plain f32 column, so kernels after it on the stream see the complete dst (a rank that owns no rows of a
+// tensor runs a small receive-only kernel instead).  One launch per exchange; no NCCL call and no host involvement on the path.
 // Replaces the reference's copy-compute-copy loop over split buffers (ggml/src/ggml-cuda/ggml-cuda.cu:1451-1769).
 #define B200_MAX_PEERS 8
 typedef struct b200_exchange {
@@ -162,6 +163,9 @@ B200_API int b200_peer_close(b200_ctx * ctx, void * dptr);
 // w: this rank's rows (a [K, rows] tensor), x: the full activation column, dst: the FULL result column inside the arena
 B200_API int b200_mul_mat_rowsplit(b200_ctx * ctx, const b200_tensor * w, const b200_tensor * x, b200_tensor * dst, int64_t row_lo,
                                    const b200_exchange * ex);
+// n <= 3 row-split MUL_MATs of the same activation column (wq/wk/wv, gate/up): runs of equal weight type share one launch
+B200_API int b200_mul_mat_rowsplit_multi(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, b200_tensor * const * dst,
+                                         const int64_t * row_lo, const b200_exchange * ex);
 B200_API int b200_exchange_error(b200_ctx * ctx, const b200_exchange * ex);     // nonzero after a receive timed out (a peer died)
 
 // ---- row split (split-mode=row) helpers; reference ggml-cuda.cu:777-803 --------------------

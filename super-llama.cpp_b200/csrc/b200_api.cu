@@ -306,38 +306,54 @@ extern "C" int b200_peer_close(b200_ctx * ctx, void * dptr) {
 }
 static bool exchange_ok(const b200_exchange * ex) { return ex && ex->world >= 1 && ex->world <= B200_MAX_PEERS && ex->rank >= 0 && ex->rank < ex->world && ex->base[ex->rank]; }
 
-extern "C" int b200_mul_mat_rowsplit(b200_ctx * ctx, const b200_tensor * w, const b200_tensor * x, b200_tensor * dst, int64_t row_lo, const b200_exchange * ex) {
-    if (!ctx || !w || !x || !dst || !exchange_ok(ex)) { b200_set_error("mul_mat_rowsplit: bad arguments"); return B200_ERR_INVALID; }
+// n <= 3 row-split MUL_MATs of one activation column: weight i holds rows [row_lo[i], row_lo[i] + w[i]->ne[1]) of dst[i].
+// Runs of equal weight type share one launch (compute + peer stores + receive in ONE kernel); a rank with no rows only receives.
+extern "C" int b200_mul_mat_rowsplit_multi(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, b200_tensor * const * dst,
+                                           const int64_t * row_lo, const b200_exchange * ex) {
+    if (!ctx || !w || !x || !dst || !row_lo || n < 1 || n > 3 || !exchange_ok(ex)) { b200_set_error("mul_mat_rowsplit: bad arguments"); return B200_ERR_INVALID; }
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
-    const int64_t rows = w->ne[1];
-    if (x->ne[0] != w->ne[0] || row_lo < 0 || row_lo + rows > dst->ne[0] || dst->ne[1] != x->ne[1] || dst->type != B200_TYPE_F32 || dst->nb[0] != 4) {
-        b200_set_error("mul_mat_rowsplit: shape mismatch"); return B200_ERR_INVALID;
-    }
-    if (x->ne[1] != 1 || dst->ne[1] != 1) { b200_set_error("mul_mat_rowsplit: one activation column (decode) only"); return B200_ERR_UNSUPPORTED; }
     char * own = (char *) ex->base[ex->rank];
-    const size_t doff = (size_t) ((char *) dst->data - own);
-    if (doff + (size_t) dst->ne[0] * 4 > ex->ctrl_off) { b200_set_error("mul_mat_rowsplit: dst is not inside the exchange arena"); return B200_ERR_INVALID; }
     unsigned * ctrl = (unsigned *) (own + ex->ctrl_off);
-    const size_t ll_off = ex->ctrl_off + 256 + 2 * doff;                  // the low-latency mirror: 8 bytes per f32 of the arena
-    b200_rowsplit_peers pe; pe.nll = 0; pe.expected = ctrl + 8;
-    for (int r = 0; r < ex->world; ++r) pe.ll[pe.nll++] = (char *) ex->base[r] + ll_off + (size_t) row_lo * 8;
-    int rc = B200_OK;
-    if (rows > 0) {
-        if (!(is_quant(w->type) && q8_1_variant_env() == B200_Q8_1_X86 && b200_gemv_stream_supported(w, x))) {
-            b200_set_error("mul_mat_rowsplit: only the streaming GEMV is fused with the exchange (weight type %d, K=%lld)", w->type, (long long) w->ne[0]);
+    for (int i = 0; i < n; ++i) {
+        if (!w[i] || !dst[i]) { b200_set_error("mul_mat_rowsplit: null tensor"); return B200_ERR_INVALID; }
+        if (x->ne[0] != w[i]->ne[0] || row_lo[i] < 0 || row_lo[i] + w[i]->ne[1] > dst[i]->ne[0] || dst[i]->ne[1] != x->ne[1] || dst[i]->type != B200_TYPE_F32 || dst[i]->nb[0] != 4) {
+            b200_set_error("mul_mat_rowsplit: shape mismatch"); return B200_ERR_INVALID;
+        }
+        if (x->ne[1] != 1 || dst[i]->ne[1] != 1) { b200_set_error("mul_mat_rowsplit: one activation column (decode) only"); return B200_ERR_UNSUPPORTED; }
+        const size_t doff = (size_t) ((char *) dst[i]->data - own);
+        if ((char *) dst[i]->data < own || doff + (size_t) dst[i]->ne[0] * 4 > ex->ctrl_off) { b200_set_error("mul_mat_rowsplit: dst is not inside the exchange arena"); return B200_ERR_INVALID; }
+        if (w[i]->ne[1] > 0 && !(is_quant(w[i]->type) && q8_1_variant_env() == B200_Q8_1_X86 && b200_gemv_stream_supported(w[i], x))) {
+            b200_set_error("mul_mat_rowsplit: only the streaming GEMV is fused with the exchange (weight type %d, K=%lld)", w[i]->type, (long long) w[i]->ne[0]);
             return B200_ERR_UNSUPPORTED;
         }
-        float * d = (float *) dst->data + row_lo;                          // unused by the kernel in exchange mode
-        const void * image = nullptr;
-        if (w->ne[0] > B200_GEMV_FUSED_QUANT_MAX_K) { image = quantized_activations(ctx, x, B200_Q8_1_X86, &rc); if (!image) return rc; }
-        rc = b200_launch_gemv_stream(ctx, &w, 1, x, image, &d, &pe);       // compute + peer stores of (value, tag) in ONE kernel
-        if (rc) return rc;
     }
-    // receive: all rows of dst from all ranks -> plain f32; also advances the exchange counter
-    rc = b200_launch_exchange_unpack(ctx, own + ll_off, (float *) dst->data, dst->ne[0], ctrl);
+    b200_rowsplit_peers pe; pe.nll = 0; pe.arena = own; pe.ctrl = ctrl;
+    for (int r = 0; r < ex->world; ++r) pe.ll_base[pe.nll++] = (char *) ex->base[r] + ex->ctrl_off + 256;   // mirror: 8 bytes per f32 of the arena
+    pe.ll_self = pe.ll_base[ex->rank];
+    int rc = B200_OK;
+    const void * image = nullptr;
+    if (w[0]->ne[0] > B200_GEMV_FUSED_QUANT_MAX_K) { image = quantized_activations(ctx, x, B200_Q8_1_X86, &rc); if (!image) return rc; }
+    for (int i = 0; i < n && rc == B200_OK; ) {
+        int j = i + 1;
+        while (j < n && w[j]->type == w[i]->type && (w[j]->flags & B200_TENSOR_REPACKED) == (w[i]->flags & B200_TENSOR_REPACKED)) ++j;
+        int64_t rows = 0;
+        float * d[3];
+        for (int t = i; t < j; ++t) {
+            rows += w[t]->ne[1];
+            d[t - i] = (float *) dst[t]->data + row_lo[t];
+            pe.full[t - i] = (float *) dst[t]->data; pe.full_m[t - i] = (int) dst[t]->ne[0];
+        }
+        if (rows > 0) rc = b200_launch_gemv_stream(ctx, w + i, j - i, x, image, d, &pe);
+        else for (int t = i; t < j && rc == B200_OK; ++t)                  // no local rows: receive only
+            rc = b200_launch_exchange_unpack(ctx, (const char *) pe.ll_self + 2 * (size_t) ((char *) dst[t]->data - own), (float *) dst[t]->data, dst[t]->ne[0], ctrl);
+        i = j;
+    }
     ctx->qcache.valid = 0; ctx->mcache.valid = 0;
-    b200_note_write(ctx, dst->data, b200_tensor_span(dst));
+    for (int i = 0; i < n; ++i) b200_note_write(ctx, dst[i]->data, b200_tensor_span(dst[i]));
     return rc;
+}
+extern "C" int b200_mul_mat_rowsplit(b200_ctx * ctx, const b200_tensor * w, const b200_tensor * x, b200_tensor * dst, int64_t row_lo, const b200_exchange * ex) {
+    return b200_mul_mat_rowsplit_multi(ctx, &w, 1, x, &dst, &row_lo, ex);
 }
 extern "C" int b200_exchange_error(b200_ctx * ctx, const b200_exchange * ex) {
     if (!ctx || !exchange_ok(ex)) return -1;

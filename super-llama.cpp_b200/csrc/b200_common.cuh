@@ -163,8 +163,9 @@ int  b200_launch_fattn_tc(b200_ctx * ctx, const b200_tensor * q, const b200_tens
                           const b200_tensor * mask, const b200_tensor * sinks, b200_tensor * dst,
                           float scale, float max_bias, float softcap);     // B200_ERR_UNSUPPORTED = use another kernel
 bool b200_gemv_stream_supported(const b200_tensor * w, const b200_tensor * x);
-// peers of a row-split MUL_MAT: this rank's rows inside the low-latency mirror of dst in every rank's arena (own included)
-struct b200_rowsplit_peers { int nll; void * ll[B200_MAX_PEERS]; const unsigned * expected; };
+// peers of a row-split MUL_MAT: the low-latency mirror (8 bytes per arena float) of every rank's arena, our own arena and its
+// control words, and the full f32 columns (inside our arena) that the kernel receives after it has sent its own rows
+struct b200_rowsplit_peers { int nll; void * ll_base[B200_MAX_PEERS]; const void * ll_self; const void * arena; unsigned * ctrl; float * full[3]; int full_m[3]; };
 int  b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, const void * image, float * const * dst,
                              const b200_rowsplit_peers * peers = nullptr);
 int  b200_launch_exchange_unpack(b200_ctx * ctx, const void * ll, float * dst, int64_t M, unsigned * ctrl);

@@ -33,10 +33,15 @@ struct gs_args {
     gs_seg seg[GS_MAXSEG]; int nseg; int Mtot; int K;
     const float * x;                         // f32 activation column: quantized in-kernel when aq == NULL
     const int8_t * aq; const __half2 * ads;  // or a q8_1 image made by k_quantize_q8_1_soa (natural order): [K] quants, [K/32] (d, s)
-    // row-split exchange (nseg == 1): instead of dst, every result row is stored as an 8-byte (value, tag) pair into the
-    // low-latency mirror of dst in EVERY rank's arena (NVLink peer stores; 8-byte stores are single transactions, so the tag
-    // validates the value and no fence or flag is needed -- a system-scope fence measured ~7 us here).  tag = *expected + 1.
-    int nll; uint2 * ll[B200_MAX_PEERS]; const unsigned * expected;
+    // row-split exchange: seg[i].dst points at this rank's rows inside the FULL f32 column full[i], which lives in the exchange
+    // arena.  Instead of a plain store, every result row goes as an 8-byte (value, tag) pair into the low-latency mirror of that
+    // float in EVERY rank's arena (NVLink peer stores; an 8-byte store is a single transaction, so the tag validates the value
+    // and no fence or flag is needed -- a system-scope fence measured ~7 us here).  tag = *expected + 1.  The same kernel then
+    // receives: its threads poll the local mirror of all rows of full[i] (from every rank, ours included), write the plain f32
+    // column, and the last CTA advances `expected`.  All CTAs of the grid are co-resident (grid <= SMs x CTAs/SM), so the spin
+    // cannot starve a producer; peers never wait on us inside the same exchange.
+    int nll; char * ll_base[B200_MAX_PEERS]; const char * ll_self; const char * arena; unsigned * ctrl;
+    struct { float * dst; int M; } full[GS_MAXSEG];
 };
 
 template <int TYPE> struct gs_traits;
@@ -303,7 +308,7 @@ __global__ void __launch_bounds__(SHAPE == 1 ? 256 : 384, 2) k_gemv_stream(const
     // src1 is produced by the previous kernel in the stream: wait for it (and its memory) before the first read
     asm volatile("griddepcontrol.wait;" ::: "memory");
     unsigned ll_tag = 0;
-    if (p.nll) { asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(ll_tag) : "l"(p.expected)); ll_tag += 1u; }
+    if (p.nll) { asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(ll_tag) : "l"(p.ctrl + 8)); ll_tag += 1u; }
 
     // quantize the activation column to q8_1 straight into shared memory, in lane order.  Same arithmetic as
     // q8_1_block<B200_Q8_1_X86> (bit-exact with the reference), but 128-bit loads: a lane holds 4 consecutive values, the
@@ -386,8 +391,9 @@ __global__ void __launch_bounds__(SHAPE == 1 ? 256 : 384, 2) k_gemv_stream(const
                     if (p.nll == 0) *dst = v;
                     else {
                         const uint2 pk = make_uint2(__float_as_uint(v), ll_tag);
+                        const size_t off = 2 * (size_t) ((const char *) dst - p.arena);
                         for (int pr = 0; pr < p.nll; ++pr)
-                            asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"(p.ll[pr] + r_begin + rp * GS_RW + r), "r"(pk.x), "r"(pk.y) : "memory");
+                            asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"(p.ll_base[pr] + off), "r"(pk.x), "r"(pk.y) : "memory");
                     }
                 }
                 acc[r] = 0.0f;
@@ -395,6 +401,34 @@ __global__ void __launch_bounds__(SHAPE == 1 ? 256 : 384, 2) k_gemv_stream(const
             kc = 0; ++rp;
         } else ++kc;
         if (++stage == GS_STAGES) { stage = 0; phase ^= 1; }
+    }
+
+    if (p.nll) {
+        // receive side of the exchange (see gs_args)
+        const int total = p.full[0].M + p.full[1].M + p.full[2].M;
+        unsigned long long t0;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+            int sgm = 0, r = i;
+            if (r >= p.full[0].M) { r -= p.full[0].M; sgm = 1; if (r >= p.full[1].M) { r -= p.full[1].M; sgm = 2; } }
+            float * d = p.full[sgm].dst + r;
+            const char * src = p.ll_self + 2 * (size_t) ((const char *) d - p.arena);
+            uint2 v;
+            while (true) {
+                asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(src) : "memory");
+                if (v.y == ll_tag) break;
+                unsigned long long t1;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                if (t1 - t0 > 5000000000ull) { p.ctrl[10] = 1u; break; }      // a dead peer must not hang the GPU
+            }
+            *d = __uint_as_float(v.x);
+        }
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const unsigned done = atomicAdd(p.ctrl + 9, 1u);
+            if (done == gridDim.x - 1) { p.ctrl[9] = 0u; __threadfence(); *(volatile unsigned *) (p.ctrl + 8) = ll_tag; }
+        }
     }
 }
 
@@ -504,11 +538,13 @@ static int gs_launch(b200_ctx * ctx, const gs_args & p, int attr_slot) {
 int b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, const void * image, float * const * dst,
                             const b200_rowsplit_peers * peers) {
     gs_args p;
-    p.nll = 0; p.expected = nullptr;
-    for (int i = 0; i < B200_MAX_PEERS; ++i) p.ll[i] = nullptr;
-    if (peers && n == 1) {
-        p.nll = peers->nll; p.expected = peers->expected;
-        for (int i = 0; i < peers->nll; ++i) p.ll[i] = (uint2 *) peers->ll[i];
+    p.nll = 0; p.ll_self = nullptr; p.arena = nullptr; p.ctrl = nullptr;
+    for (int i = 0; i < B200_MAX_PEERS; ++i) p.ll_base[i] = nullptr;
+    for (int i = 0; i < GS_MAXSEG; ++i) { p.full[i].dst = nullptr; p.full[i].M = 0; }
+    if (peers) {
+        p.nll = peers->nll; p.ll_self = (const char *) peers->ll_self; p.arena = (const char *) peers->arena; p.ctrl = peers->ctrl;
+        for (int i = 0; i < peers->nll; ++i) p.ll_base[i] = (char *) peers->ll_base[i];
+        for (int i = 0; i < n; ++i) { p.full[i].dst = peers->full[i]; p.full[i].M = peers->full_m[i]; }
     }
     p.nseg = n; p.Mtot = 0; p.x = (const float *) x->data; p.K = (int) w[0]->ne[0];
     p.aq = (const int8_t *) image; p.ads = image ? (const __half2 *) ((const int8_t *) image + p.K) : nullptr;

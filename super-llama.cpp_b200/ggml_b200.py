@@ -67,7 +67,8 @@ def lib():
         "b200_graph_begin": (i, [vp]), "b200_graph_end": (vp, [vp]), "b200_graph_launch": (i, [vp, vp]), "b200_graph_destroy": (i, [vp]),
         "b200_split_row_range": (i, [i64, vp, i, i, i64, C.POINTER(i64), C.POINTER(i64)]),
         "b200_peer_handle": (i, [vp, vp, vp]), "b200_peer_open": (i, [vp, vp, C.POINTER(vp)]), "b200_peer_close": (i, [vp, vp]),
-        "b200_mul_mat_rowsplit": (i, [vp, tp, tp, tp, i64, C.POINTER(Exchange)]), 
+        "b200_mul_mat_rowsplit": (i, [vp, tp, tp, tp, i64, C.POINTER(Exchange)]),
+        "b200_mul_mat_rowsplit_multi": (i, [vp, C.POINTER(tp), i, tp, C.POINTER(tp), C.POINTER(i64), C.POINTER(Exchange)]),
         "b200_exchange_error": (i, [vp, C.POINTER(Exchange)]),
         "ggml_backend_init": (vp, []), "ggml_backend_score": (i, []), "ggml_backend_b200_reg": (vp, []),
     }
@@ -306,6 +307,14 @@ class Context:
     def mul_mat_rowsplit(self, w, x, dst, row_lo, ex):
         cw, cx, cd = w.c(), x.c(), dst.c()
         _check(lib().b200_mul_mat_rowsplit(self.h, C.byref(cw), C.byref(cx), C.byref(cd), C.c_int64(row_lo), C.byref(ex)), "mul_mat_rowsplit")
+
+    def mul_mat_rowsplit_multi(self, ws, x, dsts, row_los, ex):
+        cws, cds, cx = [w.c() for w in ws], [d.c() for d in dsts], x.c()
+        n = len(ws)
+        TP = C.POINTER(_Tensor)
+        wa = (TP * n)(*[C.pointer(c) for c in cws]); da = (TP * n)(*[C.pointer(c) for c in cds])
+        lo = (C.c_int64 * n)(*row_los)
+        _check(lib().b200_mul_mat_rowsplit_multi(self.h, wa, n, C.byref(cx), da, lo, C.byref(ex)), "mul_mat_rowsplit_multi")
 
     def exchange_error(self, ex):
         return lib().b200_exchange_error(self.h, C.byref(ex))

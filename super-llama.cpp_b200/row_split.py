@@ -85,3 +85,7 @@ class PeerExchange:
 
     def mul_mat(self, w_local, x, dst_full, row_lo):
         self.ctx.mul_mat_rowsplit(w_local, x, dst_full, row_lo, self.ex)
+
+    def mul_mat_multi(self, ws_local, x, dsts_full, row_los):
+        """up to 3 row-split MUL_MATs of one activation column in one launch per run of equal weight type"""
+        self.ctx.mul_mat_rowsplit_multi(ws_local, x, dsts_full, row_los, self.ex)

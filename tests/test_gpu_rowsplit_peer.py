@@ -49,6 +49,33 @@ for rep in range(3):                                   # several rounds through 
         sums = [None] * world; dist.all_gather_object(sums, got.tobytes())      # every rank holds the identical gathered tensor
         ok = ok and all(b == sums[0] for b in sums)
         dist.barrier()                                  # the next case reuses dx on the host side
+# wq/wk/wv of one column in one call: q4_K, q4_K share a launch, the q6_K one (repacked) gets its own; M = 32 leaves rank 1 without rows
+multi = [(O.Q4_K, 1024, False), (O.Q4_K, 32, False), (O.Q6_K, 256, True)]
+K = 2048
+mx = peer.alloc(B.F32, [K, 1])
+md = [peer.alloc(B.F32, [M, 1]) for _, M, _ in multi]
+for rep in range(3):
+    rng = np.random.default_rng(77 + rep)
+    x = rng.standard_normal((1, K)).astype(np.float32)
+    ctx.h2d(mx.ptr, x)
+    ws, los, full = [], [], []
+    for t, M, repack in multi:
+        w = O.random_blocks(rng, t, K, M)
+        mine, lo, hi = rs.shard_weight(w, w.size // M, M)
+        dw = ctx.upload(t, [K, hi - lo], mine)
+        if repack and hi > lo: ctx.repack(dw)
+        elif repack: dw.flags = 1
+        ws.append(dw); los.append(lo); full.append(w)
+    peer.mul_mat_multi(ws, mx, md, los)
+    for (t, M, _), w, dd in zip(multi, full, md):
+        got = ctx.download(dd).reshape(1, 1, 1, M)
+        want = orc.mul_mat(t, w, K, M, x, 1, act=O.ACT_Q8_1)
+        same = O.nmse(want, got) < 1e-9
+        if not same: print(f"rank {rank} multi rep {rep} type {t} M {M}: nmse {O.nmse(want, got)}", flush=True)
+        ok = ok and same
+        sums = [None] * world; dist.all_gather_object(sums, got.tobytes())
+        ok = ok and all(b == sums[0] for b in sums)
+    dist.barrier()
 err = ctx.exchange_error(peer.ex)
 if err: print(f'rank {rank}: exchange error flag {err}', flush=True)
 ok = ok and err == 0
