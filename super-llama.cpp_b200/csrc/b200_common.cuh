@@ -168,6 +168,9 @@ bool b200_gemv_stream_supported(const b200_tensor * w, const b200_tensor * x);
 struct b200_rowsplit_peers { int nll; void * ll_base[B200_MAX_PEERS]; const void * ll_self; const void * arena; unsigned * ctrl; float * full[3]; int full_m[3]; };
 int  b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, const void * image, float * const * dst,
                              const b200_rowsplit_peers * peers = nullptr);
+bool b200_gemv_mma_supported(const b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x);
+int  b200_launch_gemv_mma(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, const void * image, float * const * dst,
+                          const b200_rowsplit_peers * peers);
 int  b200_launch_exchange_unpack(b200_ctx * ctx, const void * ll, float * dst, int64_t M, unsigned * ctrl);
 #define B200_GEMV_FUSED_QUANT_MAX_K 8192    // above this, one quantize launch + image beats one quantization per CTA
 #define B200_GEMV_MAX_COLS 8

@@ -1,0 +1,350 @@
+// Decode MUL_MAT (one activation column) for raw GGUF block_q4_K weights: TMA-tiled weight stream + int8 tensor-core dot products.
+// Replaces the per-row loop ggml_vec_dot_q4_K_q8_K (ggml/src/ggml-cpu/quants.c:550, x86 arch/x86/quants.c:1741) driven by
+// ggml_compute_forward_mul_mat (ggml/src/ggml-cpu/ggml-cpu.c:1226-1418), with q8_1 activations (quantize_row_q8_1,
+// arch/x86/quants.c:388-490, bit-exact) as ggml-cuda's mul_mat_vec_q does.
+//
+// Why tensor cores for a GEMV: the kernel is HBM-bound, but the dp4a version (b200_gemv_stream.cu) spends ~94 issue slots per 512
+// weight bytes on nibble masks, dp4a and the 6-bit scale decode, and ncu shows the issue slots, not HBM, as the limiter.  One
+// mma.sync.m16n8k32 (u8 x s8 -> s32) does a whole 8-row x 64-weight group, which cuts the instruction count ~2.8x:
+//   A (16 x 32): rows 0-7  = low  nibbles of qs[32p .. 32p+31] of 8 weight rows  -> sub-block 2p
+//                rows 8-15 = high nibbles of the same bytes                      -> sub-block 2p+1
+//   B (32 x 8):  column c = the 32 int8 activations of sub-block c of this 256-block (the SAME registers for p = 0..3)
+//   C[g][2p] and C[g+8][2p+1] are the two wanted sums; both land in lane (g, t = p), so after the four MMAs of a block lane (g, t)
+//   owns sub-blocks 2t, 2t+1 of weight row g and applies their scales: all 32 lanes do scale work, none is idle.
+//   Fragment k index 4t+i <-> byte 8t+i and 16+4t+i <-> byte 8t+4+i of the 32-byte group, for A and B alike, so both are LDS.64.
+// Data movement: one 2-D TMA box {288 B = 2 blocks, 8 rows} per stage straight from the row-major GGUF tensor (sector-aligned:
+// 288 = 9 x 32 B), per-warp rings of 3 stages with one mbarrier each; rows beyond M and blocks beyond K arrive as zeros.
+// Work split: a CTA owns a contiguous range of 8-row groups; its (group, 2-block chunk) items go round-robin over the 12 warps, each
+// item leaves 8 partial sums in shared memory and the CTA adds them in chunk order at the end (deterministic, no atomics).
+#include "b200_common.cuh"
+#include "b200_ptx.cuh"
+#include <cuda.h>
+#include <stdlib.h>
+#include <mutex>
+
+#define GQ_WARPS   12
+#define GQ_STAGES  3
+#define GQ_ROWS    8
+#define GQ_CHUNK   288                         // bytes of one row in a stage: two 144-byte blocks
+#define GQ_STAGE_BYTES (GQ_ROWS * GQ_CHUNK)    // 2304
+#define GQ_MAXSEG  3
+
+struct gq_args {
+    float * dst[GQ_MAXSEG]; int M[GQ_MAXSEG]; int nseg; int K;
+    const float * x; const int8_t * aq; const __half2 * ads;            // as gs_args (b200_gemv_stream.cu)
+    int gmax;                                                           // most 8-row groups any CTA owns
+    // row-split exchange, see b200_gemv_stream.cu
+    int nll; char * ll_base[B200_MAX_PEERS]; const char * ll_self; const char * arena; unsigned * ctrl;
+    struct { float * dst; int M; } full[GQ_MAXSEG];
+    int dbg;
+    int npf;                                                            // items per warp to prefetch into L2 behind the ring fill
+};
+struct gq_maps { CUtensorMap m[GQ_MAXSEG]; };
+
+static __device__ __forceinline__ void tma_load_2d_hint(uint32_t dst, const void * tmap, int c0, int c1, uint32_t bar, uint64_t policy) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;"
+                 :: "r"(dst), "l"(tmap), "r"(bar), "r"(c0), "r"(c1), "l"(policy) : "memory");
+}
+static __device__ __forceinline__ void tma_prefetch_l2_2d(const void * tmap, int c0, int c1) {
+    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" :: "l"(tmap), "r"(c0), "r"(c1) : "memory");
+}
+static __device__ __forceinline__ void mma_u8s8(int (&c)[4], unsigned a0, unsigned a1, unsigned a2, unsigned a3, unsigned b0, unsigned b1) {
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+                 : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+__global__ void __launch_bounds__(GQ_WARPS * 32, 2) k_gemv_q4k_mma(const gq_args p, const __grid_constant__ gq_maps maps) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    // layout: [GQ_WARPS][GQ_STAGES][2304] rings | q8 quants [K] | (d, s) float2 [K/32] | partial sums [gmax][nchunks][8] | mbarriers
+    const int nblocks = p.K >> 8, nchunks = (nblocks + 1) >> 1;
+    uint8_t *  s_q   = smem + GQ_WARPS * GQ_STAGES * GQ_STAGE_BYTES;
+    float2 *   s_ds  = (float2 *) (s_q + p.K);
+    float *    s_par = (float *) (s_ds + (p.K >> 5));
+    uint64_t * s_bar = (uint64_t *) (s_par + (size_t) p.gmax * nchunks * GQ_ROWS);
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t ring = smem_u32(smem + warp * GQ_STAGES * GQ_STAGE_BYTES);
+    const uint32_t bar0 = smem_u32(s_bar + warp * GQ_STAGES);
+
+    // this CTA's 8-row groups, numbered through the segments
+    const int G0 = (p.M[0] + GQ_ROWS - 1) / GQ_ROWS, G1 = p.nseg > 1 ? (p.M[1] + GQ_ROWS - 1) / GQ_ROWS : 0, G2 = p.nseg > 2 ? (p.M[2] + GQ_ROWS - 1) / GQ_ROWS : 0;
+    const int G = G0 + G1 + G2;
+    const int g_lo = (int) ((int64_t) G * blockIdx.x / gridDim.x), g_hi = (int) ((int64_t) G * (blockIdx.x + 1) / gridDim.x);
+    const int nitems_cta = (p.dbg & 4) ? 0 : (g_hi - g_lo) * nchunks;
+
+    if (lane == 0) {
+        for (int s = 0; s < GQ_STAGES; ++s) mbar_init(bar0 + 8 * s, 1);
+        mbar_fence_init();
+    }
+    __syncwarp();
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");      // the next kernel may start its prologue (PDL)
+
+    const uint64_t policy = l2_policy_evict_first();
+    int pit = warp;                                                       // producer cursor: next item of this warp to fetch
+    auto issue = [&](int stage) {
+        if (lane == 0) {
+            const int gl = pit / nchunks, ch = pit - gl * nchunks;
+            int gg = g_lo + gl, s = 0;
+            if (gg >= G0) { gg -= G0; s = 1; if (gg >= G1) { gg -= G1; s = 2; } }
+            const uint32_t bar = bar0 + 8 * stage;
+            mbar_arrive_expect_tx(bar, GQ_STAGE_BYTES);
+            tma_load_2d_hint(ring + stage * GQ_STAGE_BYTES, &maps.m[s], ch * (GQ_CHUNK / 4), gg * GQ_ROWS, bar, policy);
+        }
+        pit += GQ_WARPS;
+    };
+    for (int i = 0; i < GQ_STAGES && pit < nitems_cta; ++i) issue(i);    // weights do not depend on the previous kernel
+    // The rings hold ~83 KB per CTA; the activations only exist once the previous kernel has retired and are then quantized
+    // (~3 us in all) with nothing consuming, so HBM would idle.  Keep it busy: pull this warp's next items into L2 meanwhile
+    // (126 MB); the ring refills then hit L2.
+    if (lane == 0) {
+        int it = pit;
+        for (int i = 0; i < p.npf && it < nitems_cta; ++i, it += GQ_WARPS) {
+            const int gl = it / nchunks, ch = it - gl * nchunks;
+            int gg = g_lo + gl, s = 0;
+            if (gg >= G0) { gg -= G0; s = 1; if (gg >= G1) { gg -= G1; s = 2; } }
+            tma_prefetch_l2_2d(&maps.m[s], ch * (GQ_CHUNK / 4), gg * GQ_ROWS);
+        }
+    }
+
+    asm volatile("griddepcontrol.wait;" ::: "memory");                    // src1 comes from the previous kernel of the stream
+    unsigned ll_tag = 0;
+    if (p.nll) { asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(ll_tag) : "l"(p.ctrl + 8)); ll_tag += 1u; }
+
+    // activation column -> q8_1 in shared memory, natural order (same arithmetic as q8_1_block<B200_Q8_1_X86>, bit-exact)
+    if (p.dbg & 1) {
+    } else if (p.aq != nullptr) {
+        const int4 * src = (const int4 *) p.aq;
+        for (int j = threadIdx.x; j < (p.K >> 4); j += blockDim.x) ((int4 *) s_q)[j] = src[j];
+        for (int j = threadIdx.x; j < (p.K >> 5); j += blockDim.x) s_ds[j] = __half22float2(p.ads[j]);
+    } else {
+        constexpr int QB = 8;
+        const float4 * x4 = (const float4 *) p.x;
+        const int nvec = p.K >> 7;                                        // 128-float chunks = 4 q8_1 blocks per warp pass
+        for (int c0 = warp; c0 < nvec; c0 += GQ_WARPS * QB) {
+            float4 v[QB];
+#pragma unroll
+            for (int i = 0; i < QB; ++i) { const int c = c0 + i * GQ_WARPS; v[i] = c < nvec ? x4[c * 32 + lane] : make_float4(0.f, 0.f, 0.f, 0.f); }
+#pragma unroll
+            for (int i = 0; i < QB; ++i) {
+                const int c = c0 + i * GQ_WARPS;
+                if (c >= nvec) break;                                     // warp-uniform
+                float amax = fmaxf(fmaxf(fabsf(v[i].x), fabsf(v[i].y)), fmaxf(fabsf(v[i].z), fabsf(v[i].w)));
+                amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+                amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
+                amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 4));
+                const float d  = __fdiv_rn(amax, 127.0f);
+                const float id = amax != 0.0f ? __fdiv_rn(127.0f, amax) : 0.0f;
+                const int q0 = cvt_x86(rintf(__fmul_rn(v[i].x, id))), q1 = cvt_x86(rintf(__fmul_rn(v[i].y, id)));
+                const int q2 = cvt_x86(rintf(__fmul_rn(v[i].z, id))), q3 = cvt_x86(rintf(__fmul_rn(v[i].w, id)));
+                unsigned usum = (unsigned) q0 + (unsigned) q1 + (unsigned) q2 + (unsigned) q3;   // int32 lanes summed before saturation
+                usum += __shfl_xor_sync(0xffffffffu, usum, 1);
+                usum += __shfl_xor_sync(0xffffffffu, usum, 2);
+                usum += __shfl_xor_sync(0xffffffffu, usum, 4);
+                const unsigned word = ((unsigned) max(-128, min(127, q0)) & 0xffu)        | (((unsigned) max(-128, min(127, q1)) & 0xffu) << 8) |
+                                      (((unsigned) max(-128, min(127, q2)) & 0xffu) << 16) | (((unsigned) max(-128, min(127, q3)) & 0xffu) << 24);
+                ((unsigned *) s_q)[c * 32 + lane] = word;
+                // d and s take the fp16 round trip they would take through block_q8_1
+                if ((lane & 7) == 0) s_ds[c * 4 + (lane >> 3)] = make_float2(__half2float(__float2half_rn(d)), __half2float(__float2half_rn(__fmul_rn(d, (float) (int) usum))));
+            }
+        }
+    }
+    __syncthreads();
+
+    const int g = lane >> 2, t = lane & 3;
+    const uint32_t q_sm = smem_u32(s_q) + lane * 8, ds_sm = smem_u32(s_ds) + t * 16;
+    const int sh = 16 * (t & 1);
+    int stage = 0, phase = 0;
+    for (int it = warp; it < nitems_cta; it += GQ_WARPS) {
+        const int gl = it / nchunks, ch = it - gl * nchunks;
+        mbar_wait(bar0 + 8 * stage, (uint32_t) phase);
+        float acc = 0.0f;
+        if (!(p.dbg & 2)) {
+            const uint32_t row = ring + stage * GQ_STAGE_BYTES + g * GQ_CHUNK;
+#pragma unroll
+            for (int b = 0; b < 2; ++b) {
+                const int blk = ch * 2 + b;
+                if (blk >= nblocks) break;                                // warp-uniform (odd block count: the box tail is zero fill)
+                const uint32_t rb = row + b * 144;
+                const int4 hdr = lds128(rb);                              // d | dmin, scales[12]
+                const int2 bq  = lds64(q_sm + blk * 256);
+                int c[4][4];
+#pragma unroll
+                for (int pp = 0; pp < 4; ++pp) {
+                    c[pp][0] = c[pp][1] = c[pp][2] = c[pp][3] = 0;
+                    const int2 w = lds64(rb + 16 + 32 * pp + 8 * t);
+                    mma_u8s8(c[pp], (unsigned) w.x & 0x0F0F0F0Fu, ((unsigned) w.x >> 4) & 0x0F0F0F0Fu,
+                                    (unsigned) w.y & 0x0F0F0F0Fu, ((unsigned) w.y >> 4) & 0x0F0F0F0Fu, (unsigned) bq.x, (unsigned) bq.y);
+                }
+                const int ilo = t == 0 ? c[0][0] : t == 1 ? c[1][0] : t == 2 ? c[2][0] : c[3][0];
+                const int ihi = t == 0 ? c[0][3] : t == 1 ? c[1][3] : t == 2 ? c[2][3] : c[3][3];
+                // get_scale_min_k4 (ggml-quants.c:703-710) for sub-blocks j = 2t, 2t+1: two bytes at a time
+                const unsigned a1 = ((unsigned) hdr.y >> sh) & 0xFFFFu, a2 = ((unsigned) hdr.z >> sh) & 0xFFFFu, a3 = ((unsigned) hdr.w >> sh) & 0xFFFFu;
+                const unsigned sc2 = t < 2 ? (a1 & 0x3F3Fu) : ((a3 & 0x0F0Fu) | ((a1 >> 2) & 0x3030u));
+                const unsigned m2  = t < 2 ? (a2 & 0x3F3Fu) : (((a3 >> 4) & 0x0F0Fu) | ((a2 >> 2) & 0x3030u));
+                const int4 dsi = lds128(ds_sm + blk * 64);                // dA(2t), s(2t), dA(2t+1), s(2t+1)
+                const float4 ds = make_float4(__int_as_float(dsi.x), __int_as_float(dsi.y), __int_as_float(dsi.z), __int_as_float(dsi.w));
+                const float2 dm = make_float2(__half2float(__ushort_as_half((unsigned short) ((unsigned) hdr.x & 0xFFFFu))),
+                                              __half2float(__ushort_as_half((unsigned short) ((unsigned) hdr.x >> 16))));
+                const float dot = ds.x * (float) (ilo * (int) (sc2 & 0xFFu)) + ds.z * (float) (ihi * (int) (sc2 >> 8));
+                const float mn  = ds.y * (float) (m2 & 0xFFu) + ds.w * (float) (m2 >> 8);
+                acc += dm.x * dot - dm.y * mn;
+            }
+        }
+        __syncwarp();                                                     // every lane is done reading this stage
+        if (pit < nitems_cta) issue(stage);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+        if (t == 0) s_par[(gl * nchunks + ch) * GQ_ROWS + g] = acc;
+        if (++stage == GQ_STAGES) { stage = 0; phase ^= 1; }
+    }
+    __syncthreads();
+
+    // add the chunk partials of every row in chunk order and store (or send) the row
+    for (int i = threadIdx.x; i < (g_hi - g_lo) * GQ_ROWS; i += blockDim.x) {
+        const int gl = i >> 3, r = i & 7;
+        float v = 0.0f;
+        if (!(p.dbg & 4)) for (int ch = 0; ch < nchunks; ++ch) v += s_par[(gl * nchunks + ch) * GQ_ROWS + r];
+        int gg = g_lo + gl, s = 0;
+        if (gg >= G0) { gg -= G0; s = 1; if (gg >= G1) { gg -= G1; s = 2; } }
+        const int rowi = gg * GQ_ROWS + r;
+        if (rowi < p.M[s]) {
+            float * d = p.dst[s] + rowi;
+            if (p.nll == 0) *d = v;
+            else {
+                const size_t off = 2 * (size_t) ((const char *) d - p.arena);
+                for (int pr = 0; pr < p.nll; ++pr)
+                    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"(p.ll_base[pr] + off), "r"(__float_as_uint(v)), "r"(ll_tag) : "memory");
+            }
+        }
+    }
+
+    if (p.nll) {
+        // receive side of the exchange (see gs_args in b200_gemv_stream.cu)
+        const int total = p.full[0].M + p.full[1].M + p.full[2].M;
+        unsigned long long t0;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+            int sgm = 0, r = i;
+            if (r >= p.full[0].M) { r -= p.full[0].M; sgm = 1; if (r >= p.full[1].M) { r -= p.full[1].M; sgm = 2; } }
+            float * d = p.full[sgm].dst + r;
+            const char * src = p.ll_self + 2 * (size_t) ((const char *) d - p.arena);
+            uint2 v;
+            while (true) {
+                asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(src) : "memory");
+                if (v.y == ll_tag) break;
+                unsigned long long t1;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                if (t1 - t0 > 5000000000ull) { p.ctrl[10] = 1u; break; }      // a dead peer must not hang the GPU
+            }
+            *d = __uint_as_float(v.x);
+        }
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const unsigned done = atomicAdd(p.ctrl + 9, 1u);
+            if (done == gridDim.x - 1) { p.ctrl[9] = 0u; __threadfence(); *(volatile unsigned *) (p.ctrl + 8) = ll_tag; }
+        }
+    }
+}
+
+// ---- host side -------------------------------------------------------------------------------------------------------------
+typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                    const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+encode_tiled_fn b200_get_encode_tiled();
+
+static size_t gq_smem_bytes(int K, int gmax) {
+    const int nchunks = ((K >> 8) + 1) >> 1;
+    return (size_t) GQ_WARPS * GQ_STAGES * GQ_STAGE_BYTES + (size_t) K + (size_t) (K >> 5) * 8 + (size_t) gmax * nchunks * GQ_ROWS * 4 + GQ_WARPS * GQ_STAGES * 8;
+}
+#define GQ_SMEM_MAX (113 * 1024)               // two CTAs (this kernel's, or this and the PDL-launched next one) per SM
+
+static int gq_grid(const b200_ctx * ctx, int64_t G, size_t bytes) {
+    static const int per_sm = getenv("GGML_B200_GQ_CTAS") ? atoi(getenv("GGML_B200_GQ_CTAS")) : 0;
+    const int64_t cap = (int64_t) ctx->sm_count * (per_sm ? per_sm : bytes > ((size_t) 24 << 20) ? 2 : 1);
+    return (int) (G < cap ? G : cap);
+}
+
+bool b200_gemv_mma_supported(const b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x) {
+    // measured (profiles/r1_gemv_mma_microbench.txt): 5.2 vs 4.5 TB/s on a 295 MB matrix, where the instruction count is what limits
+    // the dp4a kernel; no gain at <= 33 MB, where launch, quantization and ramp-up latencies dominate.  GGML_B200_GEMV_MMA=1 / 0
+    // forces it on for every supported shape / off.
+    static const int mode = getenv("GGML_B200_GEMV_MMA") ? atoi(getenv("GGML_B200_GEMV_MMA")) : -1;
+    if (mode == 0 || n < 1 || n > GQ_MAXSEG) return false;
+    int64_t G = 0; size_t bytes = 0;
+    for (int i = 0; i < n; ++i) {
+        if (w[i]->type != B200_TYPE_Q4_K || (w[i]->flags & B200_TENSOR_REPACKED) || w[i]->ne[0] != w[0]->ne[0]) return false;
+        if (w[i]->ne[1] > (1 << 28) || (w[i]->ne[1] > 0 && (w[i]->nb[1] & 15)) || ((uintptr_t) w[i]->data & 15) || w[i]->ne[2] != 1 || w[i]->ne[3] != 1) return false;
+        G += (w[i]->ne[1] + GQ_ROWS - 1) / GQ_ROWS; bytes += (size_t) w[i]->ne[1] * (w[i]->ne[0] >> 8) * 144;
+    }
+    const int64_t K = w[0]->ne[0];
+    if (K % 256 != 0 || K < 512 || K > 32768 || G < 1) return false;
+    if (mode < 0 && bytes < ((size_t) 48 << 20)) return false;
+    if (x->type != B200_TYPE_F32 || x->nb[0] != 4 || ((uintptr_t) x->data & 15) || x->ne[1] != 1 || x->ne[2] != 1 || x->ne[3] != 1) return false;
+    const int grid = gq_grid(ctx, G, bytes);
+    return gq_smem_bytes((int) K, (int) ((G + grid - 1) / grid)) <= GQ_SMEM_MAX && b200_get_encode_tiled() != nullptr;
+}
+
+// tensor maps of the weights are static: a small direct-mapped cache keyed by (data, row stride, K, M)
+struct gq_map_entry { const void * data; size_t nb1; int64_t K, M; CUtensorMap map; };
+static gq_map_entry g_map_cache[512];
+static std::mutex g_map_mutex;
+
+static int gq_weight_map(const b200_tensor * w, CUtensorMap * out) {
+    const size_t h = (((uintptr_t) w->data >> 8) ^ ((uintptr_t) w->data >> 20) ^ (size_t) w->ne[1]) & 511;
+    std::lock_guard<std::mutex> lock(g_map_mutex);
+    gq_map_entry & e = g_map_cache[h];
+    if (e.data == w->data && e.nb1 == w->nb[1] && e.K == w->ne[0] && e.M == w->ne[1]) { *out = e.map; return B200_OK; }
+    const cuuint64_t dims[2] = { (cuuint64_t) (w->ne[0] >> 8) * 36, (cuuint64_t) (w->ne[1] > 0 ? w->ne[1] : 1) };   // u32 words per row, rows
+    const cuuint64_t strides[1] = { (cuuint64_t) (w->ne[1] > 1 ? w->nb[1] : (size_t) (w->ne[0] >> 8) * 144) };
+    const cuuint32_t box[2] = { GQ_CHUNK / 4, GQ_ROWS }, es[2] = { 1, 1 };
+    const CUresult r = b200_get_encode_tiled()(out, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, (void *) w->data, dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { b200_set_error("gemv_mma: cuTensorMapEncodeTiled failed (%d)", (int) r); return B200_ERR_CUDA; }
+    e.data = w->data; e.nb1 = w->nb[1]; e.K = w->ne[0]; e.M = w->ne[1]; e.map = *out;
+    return B200_OK;
+}
+
+// n <= 3 raw q4_K weights sharing the activation column x; dst[i] is where weight i's rows go (see b200_launch_gemv_stream)
+int b200_launch_gemv_mma(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, const void * image, float * const * dst,
+                         const b200_rowsplit_peers * peers) {
+    gq_args p; gq_maps maps;
+    memset(&maps, 0, sizeof(maps));
+    p.nseg = n; p.K = (int) w[0]->ne[0]; p.x = (const float *) x->data;
+    p.aq = (const int8_t *) image; p.ads = image ? (const __half2 *) ((const int8_t *) image + p.K) : nullptr;
+    int64_t G = 0; size_t bytes = 0;
+    for (int i = 0; i < GQ_MAXSEG; ++i) { p.dst[i] = nullptr; p.M[i] = 0; p.full[i].dst = nullptr; p.full[i].M = 0; }
+    for (int i = 0; i < n; ++i) {
+        p.dst[i] = dst[i]; p.M[i] = (int) w[i]->ne[1];
+        G += (w[i]->ne[1] + GQ_ROWS - 1) / GQ_ROWS; bytes += (size_t) w[i]->ne[1] * (w[i]->ne[0] >> 8) * 144;
+        if (w[i]->ne[1] > 0) { const int rc = gq_weight_map(w[i], &maps.m[i]); if (rc) return rc; }
+    }
+    p.nll = 0; p.ll_self = nullptr; p.arena = nullptr; p.ctrl = nullptr;
+    for (int i = 0; i < B200_MAX_PEERS; ++i) p.ll_base[i] = nullptr;
+    if (peers) {
+        p.nll = peers->nll; p.ll_self = (const char *) peers->ll_self; p.arena = (const char *) peers->arena; p.ctrl = peers->ctrl;
+        for (int i = 0; i < peers->nll; ++i) p.ll_base[i] = (char *) peers->ll_base[i];
+        for (int i = 0; i < n; ++i) { p.full[i].dst = peers->full[i]; p.full[i].M = peers->full_m[i]; }
+    }
+    { static int dbg = -1; if (dbg < 0) { const char * e = getenv("GGML_B200_GS_DBG"); dbg = e ? atoi(e) : 0; } p.dbg = dbg; }
+    { static int npf = -1; if (npf < 0) { const char * e = getenv("GGML_B200_GQ_NPF"); npf = e ? atoi(e) : 0; } p.npf = npf; }
+    const int grid = gq_grid(ctx, G, bytes);
+    p.gmax = (int) ((G + grid - 1) / grid);
+    const size_t smem = gq_smem_bytes(p.K, p.gmax);
+    static bool attr_done[64] = {};
+    if (!attr_done[ctx->device & 63]) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(k_gemv_q4k_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, GQ_SMEM_MAX));
+        attr_done[ctx->device & 63] = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned) grid);
+    cfg.blockDim = dim3(GQ_WARPS * 32);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = ctx->pdl ? 1 : 0;
+    B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_gemv_q4k_mma, p, maps));
+    return B200_OK;
+}

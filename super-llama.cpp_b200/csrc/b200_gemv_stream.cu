@@ -42,6 +42,7 @@ struct gs_args {
     // cannot starve a producer; peers never wait on us inside the same exchange.
     int nll; char * ll_base[B200_MAX_PEERS]; const char * ll_self; const char * arena; unsigned * ctrl;
     struct { float * dst; int M; } full[GS_MAXSEG];
+    int dbg;                                 // GGML_B200_GS_DBG (measurement only): 1 skip quantization, 2 skip the dot products, 4 no weight traffic
 };
 
 template <int TYPE> struct gs_traits;
@@ -276,7 +277,7 @@ __global__ void __launch_bounds__(SHAPE == 1 ? 256 : 384, 2) k_gemv_stream(const
     const int rows = r_end - r_begin;
     const int nchunks = (nblocks + GS_CB - 1) / GS_CB;
     const int npairs = (rows + GS_RW - 1) / GS_RW;
-    const int nitems = npairs * nchunks;
+    const int nitems = (p.dbg & 4) ? 0 : npairs * nchunks;
 
     if (lane == 0) {
         for (int s = 0; s < GS_STAGES; ++s) mbar_init(bar0 + 8 * s, 1);
@@ -313,7 +314,8 @@ __global__ void __launch_bounds__(SHAPE == 1 ? 256 : 384, 2) k_gemv_stream(const
     // quantize the activation column to q8_1 straight into shared memory, in lane order.  Same arithmetic as
     // q8_1_block<B200_Q8_1_X86> (bit-exact with the reference), but 128-bit loads: a lane holds 4 consecutive values, the
     // 8 lanes of a group hold one 32-value block, and up to GS_QB independent loads per lane are in flight at once.
-    if (p.aq != nullptr) {
+    if (p.dbg & 1) {
+    } else if (p.aq != nullptr) {
         // a ready q8_1 image (large K: one quantize launch instead of one quantization per CTA): permuting copy
         const int4 * src = (const int4 *) p.aq;
         for (int j = threadIdx.x; j < (p.K >> 4); j += blockDim.x) {
@@ -372,7 +374,7 @@ __global__ void __launch_bounds__(SHAPE == 1 ? 256 : 384, 2) k_gemv_stream(const
         const int cb = min(GS_CB, nblocks - kc * GS_CB);
         const int nr = min(GS_RW, rows - rp * GS_RW);
         mbar_wait(bar0 + 8 * stage, (uint32_t) phase);
-        if (bl < cb) {
+        if (bl < cb && !(p.dbg & 2)) {
             const uint32_t st = ring + stage * STAGE_BYTES;
             const int gb = kc * GS_CB + bl;
             if (nr == GS_RW) T::template consume<GS_RW>(st, CHUNK_BYTES, bl, gb, lane, act, p.K, nblocks, acc);
@@ -537,6 +539,7 @@ static int gs_launch(b200_ctx * ctx, const gs_args & p, int attr_slot) {
 // n <= 3 weights of the same type sharing the activation column x; dst[i] is the f32 column of weight i
 int b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, const void * image, float * const * dst,
                             const b200_rowsplit_peers * peers) {
+    if (b200_gemv_mma_supported(ctx, w, n, x)) return b200_launch_gemv_mma(ctx, w, n, x, image, dst, peers);   // raw q4_K: tensor-core dots
     gs_args p;
     p.nll = 0; p.ll_self = nullptr; p.arena = nullptr; p.ctrl = nullptr;
     for (int i = 0; i < B200_MAX_PEERS; ++i) p.ll_base[i] = nullptr;
@@ -546,6 +549,7 @@ int b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n
         for (int i = 0; i < peers->nll; ++i) p.ll_base[i] = (char *) peers->ll_base[i];
         for (int i = 0; i < n; ++i) { p.full[i].dst = peers->full[i]; p.full[i].M = peers->full_m[i]; }
     }
+    { static int dbg = -1; if (dbg < 0) { const char * e = getenv("GGML_B200_GS_DBG"); dbg = e ? atoi(e) : 0; } p.dbg = dbg; }
     p.nseg = n; p.Mtot = 0; p.x = (const float *) x->data; p.K = (int) w[0]->ne[0];
     p.aq = (const int8_t *) image; p.ads = image ? (const __half2 *) ((const int8_t *) image + p.K) : nullptr;
     for (int i = 0; i < n; ++i) {

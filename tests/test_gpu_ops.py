@@ -217,6 +217,37 @@ def test_mul_mat_decode_ragged_rows(ctx, orc, t, M, K):
     assert _check_mm(orc, got, t, w, K, M, x, 1) < 1e-9
 
 
+def test_mul_mat_decode_q4_K_tensor_core_gemv(ctx, B, orc):
+    """raw q4_K weights of >= 48 MB take the mma.sync GEMV (b200_gemv_mma.cu) by default: a 4096 x 24580 matrix (ragged last
+    8-row group) alone, and as one of two segments sharing the column"""
+    rng = np.random.default_rng(4242)
+    K, M = 4096, 24580
+    w = O.random_blocks(rng, O.Q4_K, K, M)
+    x = rng.standard_normal((1, K)).astype(np.float32)
+    dw = ctx.upload(O.Q4_K, [K, M], w); dx = ctx.upload(B.F32, [K, 1], x); dd = ctx.empty(B.F32, [M, 1])
+    ctx.mul_mat(dw, dx, dd)
+    want = orc.mul_mat(O.Q4_K, w, K, M, x, 1, act=O.ACT_Q8_1)
+    assert O.nmse(want, ctx.download(dd)) < 1e-9
+    assert O.nmse(orc.mul_mat(O.Q4_K, w, K, M, x, 1, act=O.ACT_CPU), ctx.download(dd)) < NMSE_HARNESS
+    w2 = O.random_blocks(rng, O.Q4_K, K, 1027)
+    dw2 = ctx.upload(O.Q4_K, [K, 1027], w2); dd2 = ctx.empty(B.F32, [1027, 1])
+    ctx.h2d(dd.ptr, np.zeros(M, np.float32))
+    ctx.mul_mat_multi([dw2, dw], dx, [dd2, dd])
+    assert O.nmse(want, ctx.download(dd)) < 1e-9
+    assert O.nmse(orc.mul_mat(O.Q4_K, w2, K, 1027, x, 1, act=O.ACT_Q8_1), ctx.download(dd2)) < 1e-9
+
+
+def test_mul_mat_decode_tensor_core_gemv_all_shapes():
+    """the decode tests again with GGML_B200_GEMV_MMA=1, which sends every supported raw q4_K shape (ragged rows, odd block counts,
+    fused segments, K = 14336 through the q8_1 image) to the mma.sync GEMV instead of only the large ones"""
+    import subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, GGML_B200_GEMV_MMA="1")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(root, "tests", "test_gpu_ops.py"), "-m", "gpu", "-q", "-x", "-p", "no:cacheprovider",
+                        "-k", "(decode or multi_shared or golden or small_n or shared_activation) and not all_shapes"], env=env, cwd=root, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+
+
 @pytest.mark.parametrize("t", [O.Q8_0, O.Q4_0])
 @pytest.mark.parametrize("K,M", [(256, 5), (2304, 67), (4096, 131), (14336, 64)])
 def test_repack_run8_roundtrip_and_parity(ctx, B, orc, t, K, M):

@@ -89,7 +89,8 @@ def _free_port():
     s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close(); return p
 
 
-def test_rowsplit_peer_exchange_two_gpus(tmp_path):
+@pytest.mark.parametrize("mma", ["", "1"])           # "1": the raw q4_K cases go through the mma.sync GEMV's exchange epilogue
+def test_rowsplit_peer_exchange_two_gpus(tmp_path, mma):
     sys.path.insert(0, os.path.join(ROOT, "super-llama.cpp_b200"))
     import ggml_b200 as B
     if B.lib().b200_device_count() < 2:
@@ -99,6 +100,8 @@ def test_rowsplit_peer_exchange_two_gpus(tmp_path):
     procs = []
     for r in range(2):
         env = dict(os.environ, RANK=str(r), WORLD_SIZE="2", LOCAL_RANK=str(r), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+        if mma:
+            env["GGML_B200_GEMV_MMA"] = mma
         procs.append(subprocess.Popen([sys.executable, str(script), ROOT], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT))
     outs = [p.communicate(timeout=600)[0].decode() for p in procs]
     assert all(p.returncode == 0 for p in procs), "\n".join(outs)
