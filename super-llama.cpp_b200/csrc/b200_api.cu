@@ -409,7 +409,9 @@ extern "C" int b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const 
     if (mask && (mask->ne[0] < k->ne[1] || mask->ne[1] < q->ne[1])) { b200_set_error("flash_attn_ext: mask too small"); return B200_ERR_INVALID; }
     static const int no_dec = getenv("GGML_B200_FATTN_VEC") != nullptr;
     int rc = B200_ERR_UNSUPPORTED;
-    if (!no_dec && b200_fattn_dec_supported(q, k, v)) rc = b200_launch_fattn_dec(ctx, q, k, v, mask, sinks, dst, scale, max_bias, logit_softcap);
+    if (!no_dec && b200_fattn_gqa_supported(q, k, v, mask, dst)) rc = b200_launch_fattn_gqa(ctx, q, k, v, mask, sinks, dst, scale, max_bias, logit_softcap);
+    if (rc != B200_ERR_UNSUPPORTED) {}
+    else if (!no_dec && b200_fattn_dec_supported(q, k, v)) rc = b200_launch_fattn_dec(ctx, q, k, v, mask, sinks, dst, scale, max_bias, logit_softcap);
     else {
         if (!no_dec && b200_fattn_tc_supported(q, k, v, mask, dst)) rc = b200_launch_fattn_tc(ctx, q, k, v, mask, sinks, dst, scale, max_bias, logit_softcap);
         if (rc == B200_ERR_UNSUPPORTED) rc = b200_launch_fattn_vec(ctx, q, k, v, mask, sinks, dst, scale, max_bias, logit_softcap);

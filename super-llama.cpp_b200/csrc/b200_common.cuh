@@ -158,6 +158,9 @@ bool b200_fattn_dec_supported(const b200_tensor * q, const b200_tensor * k, cons
 int  b200_launch_fattn_dec(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v,
                            const b200_tensor * mask, const b200_tensor * sinks, b200_tensor * dst,
                            float scale, float max_bias, float softcap);
+bool b200_fattn_gqa_supported(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask, const b200_tensor * dst);
+int  b200_launch_fattn_gqa(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v,
+                           const b200_tensor * mask, const b200_tensor * sinks, b200_tensor * dst, float scale, float max_bias, float softcap);
 bool b200_fattn_tc_supported(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask, const b200_tensor * dst);
 int  b200_launch_fattn_tc(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v,
                           const b200_tensor * mask, const b200_tensor * sinks, b200_tensor * dst,

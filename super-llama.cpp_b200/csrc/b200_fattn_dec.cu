@@ -201,6 +201,14 @@ __global__ void __launch_bounds__(128) k_fattn_combine(const fattn_args p, const
     }
 }
 
+// shared with b200_fattn_gqa.cu: partial layout [S][H][N][nsplit][DV + 2]
+int b200_launch_fattn_combine(b200_ctx * ctx, const fattn_args & p, int64_t S, int nsplit, float * partial) {
+    fd_extra x; x.nsplit = nsplit; x.ntiles = 0; x.tiles_per_split = 0; x.nstage = 0; x.partial = partial;
+    dim3 cgrid((unsigned) p.N, (unsigned) p.H, (unsigned) S);
+    B200_LAUNCH(ctx, B200_K_FATTN_COMBINE, k_fattn_combine<<<cgrid, 128, 0, ctx->stream>>>(p, x));
+    return B200_OK;
+}
+
 bool b200_fattn_dec_supported(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v) {
     if (q->ne[1] > 8) return false;                              // larger batches: the prefill kernels
     if ((v->nb[1] & 15) || (v->nb[2] & 15) || (v->nb[3] & 15) || ((uintptr_t) v->data & 15)) return false;

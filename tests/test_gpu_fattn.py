@@ -193,3 +193,15 @@ def test_flash_attn_rejects_unsupported(ctx, B):
     dq = ctx.empty(B.F32, [40, 1, 1, 1]); dk = ctx.empty(B.F16, [40, 8, 1, 1]); dd = ctx.empty(B.F32, [40, 1, 1, 1])
     with pytest.raises(B.B200Error):
         ctx.flash_attn_ext(dq, dk, dk, None, None, dd, 1.0)
+
+
+def test_flash_attn_gqa_decode_kernel_all_shapes():
+    """every decode-sized case again with GGML_B200_FATTN_GQA=1, which also sends one-token / short-context calls (by default the
+    gather kernel's) through the GQA-grouped mma.sync kernel: ragged kv, head sizes 64 / 128, sinks, softcap, ALiBi, KV-cache views"""
+    import subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, GGML_B200_FATTN_GQA="1")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.join(root, "tests", "test_gpu_fattn.py"), "-m", "gpu", "-q", "-x", "-p", "no:cacheprovider",
+                        "-k", "not prefill and not all_shapes"], env=env, cwd=root, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+
