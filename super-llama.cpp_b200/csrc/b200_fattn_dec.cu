@@ -227,11 +227,12 @@ int b200_launch_fattn_dec(b200_ctx * ctx, const b200_tensor * q, const b200_tens
     fd_extra x;
     x.ntiles = (int) ((p.KV + FD_TILE - 1) / FD_TILE);
     x.nstage = (p.DK + p.DV <= 256) ? 2 : 1;
-    // split the KV range over CTAs until the grid covers the SMs, keeping >= 8 tiles (256 keys) per split
+    // split the KV range over CTAs until the grid covers the SMs, keeping >= 16 tiles (512 keys) per split: a split costs a second
+    // launch (k_fattn_combine), ~9 us inside a token's kernel chain, which 4 tiles per warp do not
     const int64_t rows = p.N * p.H * S;
     int nsplit = (int) (ctx->sm_count / (rows > 0 ? rows : 1));
     nsplit = nsplit < 1 ? 1 : nsplit;
-    if (nsplit > x.ntiles / 8) nsplit = x.ntiles / 8 > 0 ? x.ntiles / 8 : 1;
+    if (nsplit > x.ntiles / 16) nsplit = x.ntiles / 16 > 0 ? x.ntiles / 16 : 1;
     x.tiles_per_split = (x.ntiles + nsplit - 1) / nsplit;
     x.nsplit = (x.ntiles + x.tiles_per_split - 1) / x.tiles_per_split;
     x.partial = nullptr;

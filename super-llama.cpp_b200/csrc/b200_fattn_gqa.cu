@@ -65,8 +65,13 @@ __global__ void __launch_bounds__(GA_WARPS * 32, 1) k_fattn_gqa(const fattn_args
     if (lane == 0) {
         for (int s = 0; s < GA_STAGES; ++s) mbar_init(bar0 + 8 * s, 1);
         mbar_fence_init();
+        if (warp == 0) { tma_prefetch_desc(&tmap_k); tma_prefetch_desc(&tmap_v); }
     }
     __syncwarp();
+    // programmatic dependent launch: the next kernel may begin its prologue now; ours ends here, because Q, the mask and the newest
+    // K/V rows all come from kernels before us
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
 
     // rows of this lane: g and g + 8
     const int ra = g, rb = g + 8;
@@ -104,7 +109,7 @@ __global__ void __launch_bounds__(GA_WARPS * 32, 1) k_fattn_gqa(const fattn_args
     {
         const char * mbase = p.mask ? p.mask + ((hkv * x.G) % p.m_ne2) * p.m_nb2 + (iq3 % p.m_ne3) * p.m_nb3 : nullptr;
         int idx = 0;
-        for (int tile0 = t_begin + warp; tile0 < t_end; tile0 += 8 * GA_WARPS, idx += 8) {
+        for (int tile0 = t_begin + warp; tile0 < t_end; tile0 += 8 * GA_WARPS, idx += 8) {   // 8 = the unroll below
             unsigned cls[8];                                 // bit 0: something visible, bit 1: something not plain zero
 #pragma unroll
             for (int u = 0; u < 8; ++u) {
@@ -189,9 +194,9 @@ __global__ void __launch_bounds__(GA_WARPS * 32, 1) k_fattn_gqa(const fattn_args
             const uint32_t st = ring + stage * STAGE;
 
             // S = Q K^T for 16 keys
-            float s[2][4];
+            float s[2][4], s2[2][4];                                             // two accumulators per n-tile: half the mma dependency chain
 #pragma unroll
-            for (int nt = 0; nt < 2; ++nt) s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.0f;
+            for (int nt = 0; nt < 2; ++nt) { s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.0f; s2[nt][0] = s2[nt][1] = s2[nt][2] = s2[nt][3] = 0.0f; }
 #pragma unroll
             for (int j = 0; j < KS / 2; ++j) {
                 const int chunk = 4 * j + mi;                                   // 16-byte chunk of the D*2-byte row
@@ -202,9 +207,11 @@ __global__ void __launch_bounds__(GA_WARPS * 32, 1) k_fattn_gqa(const fattn_args
                     unsigned b0, b1, b2, b3;
                     ldsm_x4(box + row * 128 + (((chunk & 7) ^ (row & 7)) << 4), b0, b1, b2, b3);
                     mma_f16(s[nt], qa[2 * j][0], qa[2 * j][1], qa[2 * j][2], qa[2 * j][3], b0, b1);
-                    mma_f16(s[nt], qa[2 * j + 1][0], qa[2 * j + 1][1], qa[2 * j + 1][2], qa[2 * j + 1][3], b2, b3);
+                    mma_f16(s2[nt], qa[2 * j + 1][0], qa[2 * j + 1][1], qa[2 * j + 1][2], qa[2 * j + 1][3], b2, b3);
                 }
             }
+#pragma unroll
+            for (int nt = 0; nt < 2; ++nt) { s[nt][0] += s2[nt][0]; s[nt][1] += s2[nt][1]; s[nt][2] += s2[nt][2]; s[nt][3] += s2[nt][3]; }
             // scale, softcap, mask (ops.cpp:8176-8184); rows g (values 0, 1) and g + 8 (values 2, 3)
             float mxa = -INFINITY, mxb = -INFINITY;
 #pragma unroll
@@ -400,12 +407,17 @@ int b200_launch_fattn_gqa(b200_ctx * ctx, const b200_tensor * q, const b200_tens
     CUtensorMap tk, tv;
     if (!ga_make_map(encode, &tk, k, &x.k_swap) || !ga_make_map(encode, &tv, v, &x.v_swap)) return B200_ERR_UNSUPPORTED;
     x.ntiles = (int) ((p.KV + GA_TILE - 1) / GA_TILE);
-    // split the KV range over CTAs until the grid covers the SMs, keeping >= 4 tiles per warp (512 keys) per split
+    // A 16-key tile is ~0.9 us of dependent ldmatrix / mma / softmax work for its warp and the split merge costs ~4 us once, so contexts
+    // are cut finely: as many splits as one wave of CTAs allows (one CTA per SM, >= 1 tile per warp), then the FEWEST splits that
+    // still give the same number of tile rounds per warp (8k keys: 16 even splits, not 18 ragged ones).
+    // Measured alternatives, all slower: 4 warps x 2 CTAs per SM; >= 2 / 4 / 8 / 16 tiles per warp; a second wave of CTAs.
     const int64_t groups = Hkv * S;
-    int nsplit = (int) (ctx->sm_count / groups);                          // one CTA per SM: never a second, mostly empty wave
-    const int max_split = x.ntiles / (4 * GA_WARPS) > 0 ? x.ntiles / (4 * GA_WARPS) : 1;
-    if (nsplit > max_split) nsplit = max_split;
-    if (nsplit < 1) nsplit = 1;
+    int cap = (int) (ctx->sm_count / groups);
+    if (cap > x.ntiles / GA_WARPS) cap = x.ntiles / GA_WARPS;
+    if (cap < 1) cap = 1;
+    auto rounds = [&](int n) { return ((x.ntiles + n - 1) / n + GA_WARPS - 1) / GA_WARPS; };
+    int nsplit = cap;
+    while (nsplit > 1 && rounds(nsplit - 1) == rounds(cap)) --nsplit;
     x.tiles_per_split = (x.ntiles + nsplit - 1) / nsplit;
     x.nsplit = (x.ntiles + x.tiles_per_split - 1) / x.tiles_per_split;
     x.partial = nullptr; x.counters = nullptr;
@@ -432,9 +444,19 @@ int b200_launch_fattn_gqa(b200_ctx * ctx, const b200_tensor * q, const b200_tens
         B200_CUDA_TRY(cudaFuncSetAttribute(k_fattn_gqa<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
         ctx->attr_done[7] = 1;
     }
-    dim3 grid((unsigned) x.nsplit, (unsigned) Hkv, (unsigned) S);
-    if (D == 64) B200_LAUNCH(ctx, B200_K_FATTN, k_fattn_gqa<64><<<grid, GA_WARPS * 32, smem, ctx->stream>>>(p, x, tk, tv));
-    else         B200_LAUNCH(ctx, B200_K_FATTN, k_fattn_gqa<128><<<grid, GA_WARPS * 32, smem, ctx->stream>>>(p, x, tk, tv));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned) x.nsplit, (unsigned) Hkv, (unsigned) S);
+    cfg.blockDim = dim3(GA_WARPS * 32);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    // opt-in: with 192 KB of rings per CTA nothing can co-reside, and in the token chain PDL measured 2 % slower
+    static const int use_pdl = getenv("GGML_B200_FATTN_PDL") != nullptr;
+    cfg.attrs = attr; cfg.numAttrs = (ctx->pdl && use_pdl) ? 1 : 0;
+    if (D == 64) B200_LAUNCH(ctx, B200_K_FATTN, cudaLaunchKernelEx(&cfg, k_fattn_gqa<64>, p, x, tk, tv));
+    else         B200_LAUNCH(ctx, B200_K_FATTN, cudaLaunchKernelEx(&cfg, k_fattn_gqa<128>, p, x, tk, tv));
     if (x.nsplit > 1 && !x.counters) return b200_launch_fattn_combine(ctx, p, S, x.nsplit, x.partial);
     return B200_OK;
 }
