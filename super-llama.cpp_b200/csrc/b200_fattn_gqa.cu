@@ -68,8 +68,9 @@ __global__ void __launch_bounds__(GA_WARPS * 32, 1) k_fattn_gqa(const fattn_args
         if (warp == 0) { tma_prefetch_desc(&tmap_k); tma_prefetch_desc(&tmap_v); }
     }
     __syncwarp();
-    // programmatic dependent launch: the next kernel may begin its prologue now; ours ends here, because Q, the mask and the newest
-    // K/V rows all come from kernels before us
+    // the matmul behind us is a programmatic dependent: let it start its prologue and weight prefetch now (it reads our output only
+    // after its own griddepcontrol.wait).  Our own wait matters only with GGML_B200_FATTN_PDL: Q, the mask and the newest K/V rows
+    // all come from kernels before us.
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
 

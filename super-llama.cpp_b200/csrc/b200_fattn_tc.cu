@@ -97,6 +97,9 @@ __global__ void __launch_bounds__(FT_THREADS, 1) k_fattn_tc(const fattn_args p, 
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    // the kernels behind us (activation conversion, then the wo GEMM) are programmatic dependents: the GEMM's weight side may start on SMs
+    // our last wave leaves idle; everything that reads our output waits for this whole grid first
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     uint32_t tmem;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem) : "r"(tslot));
     const uint32_t t_s = tmem, t_o = tmem + 256, t_p = tmem + 384;          // S[2][128] | O[<=128] | P[64]

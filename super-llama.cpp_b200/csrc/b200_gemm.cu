@@ -44,11 +44,20 @@ struct gm_args {
     // image, col_off[row] is where that (token, slot) pair's result column starts in dst (in floats).  NULL for plain MUL_MAT.
     const int * counts; const int * offsets; const long long * col_off;
     int dbg;                             // timing experiments only (GGML_B200_GEMM_DBG): 1 = no weight fetch, 2 = no expansion math, 4 = no activation fetch
+    // plain MUL_MAT runs on a 1-D grid: CTA id < n_unsplit is the whole tile `id` (N tile fastest); the tiles after those -- the
+    // partial last wave -- are cut in two along K, CTA n_unsplit + 2 j + h doing half h of tile n_unsplit + j, so that the tail
+    // of the grid takes half a tile time.  Half 0 stores and raises flags[j]; half 1 waits for it and adds (fixed order: results
+    // do not depend on timing); half 0 always has the smaller CTA id, so it is resident whenever half 1 is.
+    int lin, ntn, n_unsplit; unsigned * flags;
 };
 
 // ---- activations f32 [K, N] -> bf16 image [N][K] ---------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_act_bf16(const float * __restrict__ x, size_t nb1, int64_t K, int64_t N, __nv_bfloat16 * __restrict__ out) {
     const int64_t per_row = K / 4, total = per_row * N;
+    // PDL: the GEMM behind us may start fetching and expanding its weights now; x comes from the kernel before us, and the image we
+    // overwrite may still be read by the GEMM before us, so everything we touch waits for the whole previous grid
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t) gridDim.x * blockDim.x) {
         const int64_t n = i / per_row, k = (i - n * per_row) * 4;
         const float4 v = *(const float4 *) ((const char *) x + n * nb1 + k * 4);
@@ -60,7 +69,13 @@ __global__ void __launch_bounds__(256) k_act_bf16(const float * __restrict__ x, 
 int b200_launch_act_bf16(b200_ctx * ctx, const float * x, size_t nb1, int64_t K, int64_t N, void * image) {
     const int64_t total = K / 4 * N;
     const unsigned grid = (unsigned) ((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
-    B200_LAUNCH(ctx, B200_K_CONVERT, k_act_bf16<<<grid, 256, 0, ctx->stream>>>(x, nb1, K, N, (__nv_bfloat16 *) image));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(256); cfg.dynamicSmemBytes = 0; cfg.stream = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = ctx->pdl ? 1 : 0;
+    B200_LAUNCH(ctx, B200_K_CONVERT, cudaLaunchKernelEx(&cfg, k_act_bf16, x, nb1, K, N, (__nv_bfloat16 *) image));
     return B200_OK;
 }
 
@@ -228,7 +243,7 @@ template <> struct gm_traits<B200_TYPE_Q8_0> {
 struct gm_maps { CUtensorMap w[3]; CUtensorMap w2[3]; };
 
 template <int TYPE>
-__global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ gm_maps maps) {
+__global__ void __launch_bounds__(GM_THREADS, 2) k_gemm_q(const gm_args p, const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ gm_maps maps) {
     using T = gm_traits<TYPE>;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     const int MT = p.MT, BN = p.BN, SA = p.SA, SB = p.SB, RS = p.RS;
@@ -241,18 +256,25 @@ __global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const
     const uint32_t rf0 = eb0 + 8 * SB, re0 = rf0 + 8 * RS;           // raw block landed / raw block consumed
     const uint32_t tfull = re0 + 8 * RS, tslot = tfull + 8;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    int sg = 0, mtile = blockIdx.y;
+    int sg = 0, mtile = blockIdx.y, ntile = blockIdx.x, kpart = 0, ksplit = 1, split_j = 0;
+    if (p.lin) {
+        int id = blockIdx.x;
+        if (id >= p.n_unsplit) { split_j = (id - p.n_unsplit) >> 1; kpart = (id - p.n_unsplit) & 1; ksplit = 2; id = p.n_unsplit + split_j; }
+        mtile = id / p.ntn; ntile = id - mtile * p.ntn;
+    }
     if (p.nseg > 1 && mtile >= p.seg[0].mtiles) { mtile -= p.seg[0].mtiles; sg = 1; if (p.nseg > 2 && mtile >= p.seg[1].mtiles) { mtile -= p.seg[1].mtiles; sg = 2; } }
     const CUtensorMap & tmap_w = maps.w[sg], & tmap_w2 = maps.w2[sg];
     const int pM = p.seg[sg].M;
     const int m0 = mtile * (MT * GM_BM);
-    int n0 = blockIdx.x * BN, n_end = p.N, wrow0 = m0;
+    int n0 = ntile * BN, n_end = p.N, wrow0 = m0;
     if (p.counts) {                                                          // grouped: this CTA serves expert blockIdx.z
         const int e = blockIdx.z, cnt = p.counts[e];
         if (n0 >= cnt) return;                                               // uniform per CTA, before any barrier or TMEM allocation
         n0 += p.offsets[e]; n_end = p.offsets[e] + cnt; wrow0 = e * pM + m0; // experts are stacked rows of one tall weight matrix
     }
-    const int nks = p.K / GM_BK, nunits = p.K / T::RAW_K;
+    const int units_all = p.K / T::RAW_K;
+    const int u0 = ksplit == 2 ? kpart * (units_all / 2) : 0, u1 = ksplit == 2 && kpart == 0 ? units_all / 2 : units_all;   // this CTA's 256-K blocks
+    const int nunits = u1 - u0, nks = nunits * (T::RAW_K / GM_BK);
     // TMEM columns: accumulators [0, MT*BN), then A stages: stage s, tile t at MT*BN + (s*MT + t)*32
     const uint32_t tneed = (uint32_t) (MT * BN + MT * 32 * SA);
     const uint32_t tcols = tneed <= 128 ? 128u : tneed <= 256 ? 256u : 512u;
@@ -273,6 +295,9 @@ __global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const
     uint32_t tmem;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem) : "r"(tslot));
     const uint32_t tmem_a = tmem + (uint32_t) (MT * BN);
+    // PDL: weights are static, so the raw-weight producer and the expanding warps run ahead under the previous kernel's tail (on the
+    // SMs its last wave leaves idle); only the activation image (B producer) and dst (epilogue) wait for the previous grid
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
     if (warp < GM_PRODUCERS) {
         // ===== A producers =====
@@ -301,7 +326,7 @@ __global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const
         for (int unit = 0; unit < nunits; ++unit) {
             if (!(p.dbg & 1)) mbar_wait(rf0 + 8 * slot, rph);
             const uint32_t raw = r_sm + slot * raw_slot + tile * T::TILE_BYTES;
-            typename T::unit u; T::load_unit(raw, rt, unit, u);
+            typename T::unit u; T::load_unit(raw, rt, u0 + unit, u);
             uint32_t o[32];
             const int ks = unit * 4;
             if (p.dbg & 2) { for (int c = 0; c < 32; ++c) o[c] = 0x3c003c00u + (uint32_t) c; for (int g = 0; g < 4; ++g) if (MT == 2 || (g & 1) == grp) emit(ks + g, o); }
@@ -319,23 +344,41 @@ __global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const
         // ===== epilogue: TMEM -> registers -> dst (columns of dst are contiguous along M) =====
         mbar_wait(tfull, 0);
         tc_fence_after();
+        asm volatile("griddepcontrol.wait;" ::: "memory");                    // long satisfied; orders our stores after the previous grid
         const int mm = m0 + tile * GM_BM + q * 32 + lane;
         const int c_begin = MT == 2 ? 0 : grp * (BN / 2), c_end = MT == 2 ? BN : c_begin + BN / 2;   // MT=1: the groups split the columns
         float * drow = p.seg[sg].dst + mm;
+        if (ksplit == 2 && kpart == 1) {                                     // the other half's stores must be visible before we add
+            while (*(volatile unsigned *) (p.flags + split_j) == 0u) { }
+            __threadfence();
+        }
         for (int c0 = c_begin; c0 < c_end; c0 += 16) {
             if (n0 + c0 >= n_end) break;
             uint32_t r[16];
             tmem_ld16(tmem + lane_base + (uint32_t) (tile * BN + c0), r);
             tmem_ld_wait();
             if (mm < pM) {
+                if (ksplit == 2 && kpart == 1) {                             // all 16 loads in flight before the first store (they may not be reordered past it)
+                    float prev[16];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) prev[j] = n0 + c0 + j < n_end ? __ldcg(drow + (size_t) (n0 + c0 + j) * p.seg[sg].d_ld) : 0.0f;
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) r[j] = __float_as_uint(prev[j] + __uint_as_float(r[j]));
+                }
 #pragma unroll
                 for (int j = 0; j < 16; ++j)
                     if (n0 + c0 + j < n_end) drow[p.col_off ? (size_t) p.col_off[n0 + c0 + j] : (size_t) (n0 + c0 + j) * p.seg[sg].d_ld] = __uint_as_float(r[j]);
             }
         }
+        if (ksplit == 2) {
+            __threadfence();
+            asm volatile("bar.sync 1, %0;" :: "n"(GM_PRODUCERS * 32));       // the eight epilogue warps
+            if (threadIdx.x == 0) *(volatile unsigned *) (p.flags + split_j) = kpart == 0 ? 1u : 0u;   // half 1 re-arms the flag for the next launch
+        }
         tc_fence_before();
     } else if (warp == GM_PRODUCERS) {
         // ===== B producer (control flow is warp-uniform; one elected lane issues) =====
+        asm volatile("griddepcontrol.wait;" ::: "memory");                    // the image is written by the kernel before us
         int stage = 0; uint32_t eph = 1;
         for (int ks = 0; ks < nks; ++ks) {
             mbar_wait(eb0 + 8 * stage, eph);
@@ -343,7 +386,7 @@ __global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const
                 if (p.dbg & 4) mbar_arrive(fb0 + 8 * stage);
                 else {
                     mbar_arrive_expect_tx(fb0 + 8 * stage, (uint32_t) BN * 128u);
-                    tma_load_2d(b_sm + stage * (BN * 128), &tmap_x, ks * GM_BK, n0, fb0 + 8 * stage);
+                    tma_load_2d(b_sm + stage * (BN * 128), &tmap_x, (u0 * (T::RAW_K / GM_BK) + ks) * GM_BK, n0, fb0 + 8 * stage);
                 }
             }
             __syncwarp();
@@ -386,12 +429,12 @@ __global__ void __launch_bounds__(GM_THREADS, 1) k_gemm_q(const gm_args p, const
                     for (int t = 0; t < MT; ++t) {
                         const uint32_t dstp = r_sm + slot * raw_slot + t * T::TILE_BYTES;
                         if (TYPE == B200_TYPE_Q8_0) {
-                            tma_load_3d(dstp, &tmap_w, 0, unit * 17, wrow0 + t * GM_BM, rf0 + 8 * slot);
+                            tma_load_3d(dstp, &tmap_w, 0, (u0 + unit) * 17, wrow0 + t * GM_BM, rf0 + 8 * slot);
                         } else if (TYPE == B200_TYPE_Q6_K) {
-                            tma_load_4d(dstp, &tmap_w, (unit & 7) * 16, 0, unit >> 3, wrow0 + t * GM_BM, rf0 + 8 * slot);
-                            tma_load_3d(dstp + GM_BM * T::ROW_BYTES, &tmap_w2, 0, unit >> 3, wrow0 + t * GM_BM, rf0 + 8 * slot);
+                            tma_load_4d(dstp, &tmap_w, ((u0 + unit) & 7) * 16, 0, (u0 + unit) >> 3, wrow0 + t * GM_BM, rf0 + 8 * slot);
+                            tma_load_3d(dstp + GM_BM * T::ROW_BYTES, &tmap_w2, 0, (u0 + unit) >> 3, wrow0 + t * GM_BM, rf0 + 8 * slot);
                         } else {
-                            tma_load_2d(dstp, &tmap_w, unit * T::ROW_BYTES, wrow0 + t * GM_BM, rf0 + 8 * slot);
+                            tma_load_2d(dstp, &tmap_w, (u0 + unit) * T::ROW_BYTES, wrow0 + t * GM_BM, rf0 + 8 * slot);
                         }
                     }
                 }
@@ -434,11 +477,21 @@ bool b200_gemm_supported(const b200_tensor * w, const b200_tensor * x) {
 
 // tile shape.  Measured on B200 (profiles/r1_gemm_sweep.txt): 128x256 tiles beat two stacked 128x128 tiles (MT=2) whenever they
 // give at least ~0.7 waves; below that, narrower tiles that fill more SMs win.
-static void gemm_pick_tile(const b200_ctx * ctx, int64_t M, int64_t N, int & MT, int & BN) {
+// Cost model of one launch in microseconds, fitted to scripts/gemv_bench.py --n 512 (profiles/r1_gemm_split.txt): a 128 x 256 tile
+// takes 24.4 us per 4096 of K at the MMA rate one SM sustains, a 128 x 128 tile half of that / 0.85; every CTA adds ~10 us of fill,
+// drain and epilogue; a tile of the partial last wave is cut in two along K (gm_args::lin) when both halves fit into that wave,
+// which halves its MMA time and adds ~10 us for the second half's read-add-store epilogue behind the first's.
+static double gemm_cost(int sms, int64_t tiles, int BN, int64_t K, bool can_split) {
+    const double work = 24.4 * (double) K / 4096.0 * (BN == 256 ? 1.0 : BN / 256.0 / 0.85), c = 10.0, e = 10.0;
+    const int64_t full = tiles / sms, left = tiles - full * sms;
+    double t = (double) full * (work + c);
+    if (left) t += (can_split && 2 * left <= sms && work / 2 + e < work) ? work / 2 + c + e : work + c;
+    return t;
+}
+static void gemm_pick_tile(const b200_ctx * ctx, int64_t mt, int64_t N, int64_t K, bool can_split, int & MT, int & BN) {
     MT = 1;
-    const int64_t mt = (M + GM_BM - 1) / GM_BM;
-    if (N > 128 && mt * ((N + 255) / 256) >= (int64_t) ctx->sm_count * 7 / 10) { BN = 256; return; }
     BN = N > 64 ? 128 : N > 32 ? 64 : 32;
+    if (N > 128 && gemm_cost(ctx->sm_count, mt * ((N + 255) / 256), 256, K, can_split) <= gemm_cost(ctx->sm_count, mt * ((N + 127) / 128), 128, K, can_split)) BN = 256;
 }
 
 // tensor maps over one weight tensor (rows_total rows; for MUL_MAT_ID the experts stacked)
@@ -493,7 +546,12 @@ static int gemm_launch(b200_ctx * ctx, const b200_tensor * const * ws, int nseg,
     for (int i = 0; i < nseg; ++i) Mtot += ws[i]->ne[1];
     static const int force_bn = getenv("GGML_B200_GEMM_BN") ? atoi(getenv("GGML_B200_GEMM_BN")) : 0;
     static const int force_mt = getenv("GGML_B200_GEMM_MT") ? atoi(getenv("GGML_B200_GEMM_MT")) : 0;
-    gemm_pick_tile(ctx, Mtot, p.N, p.MT, p.BN);
+    // measured in the pp512 chain: 46.2 k tok/s with the split, 46.8 k without (the second half's epilogue eats the gain): opt-in
+    static const int want_split = getenv("GGML_B200_GEMM_KSPLIT") && atoi(getenv("GGML_B200_GEMM_KSPLIT")) != 0;
+    const bool can_split = !gi && want_split && (p.K / 256) >= 2;
+    int64_t mt128 = 0;
+    for (int i = 0; i < nseg; ++i) mt128 += (ws[i]->ne[1] + GM_BM - 1) / GM_BM;
+    gemm_pick_tile(ctx, mt128, p.N, p.K, can_split, p.MT, p.BN);
     if (force_bn) p.BN = force_bn;
     if (force_mt) p.MT = force_mt;
     if (gi) { p.MT = 1; p.BN = gi->bn; }
@@ -540,11 +598,33 @@ static int gemm_launch(b200_ctx * ctx, const b200_tensor * const * ws, int nseg,
         ctx->attr_done[5] = 1;
     }
     dim3 grid((unsigned) ((p.N + p.BN - 1) / p.BN), mtiles_total, (unsigned) (gi ? gi->n_expert : 1));
+    p.lin = 0; p.ntn = (int) grid.x; p.n_unsplit = 0; p.flags = nullptr;
+    if (!gi) {
+        const int64_t tiles = (int64_t) grid.x * mtiles_total;
+        const int64_t left = tiles % ctx->sm_count;
+        const double work = 24.4 * (double) p.K / 4096.0 * (p.BN == 256 ? 1.0 : p.BN / 256.0 / 0.85);
+        const int64_t nsplit = (can_split && left && 2 * left <= ctx->sm_count && left <= 1024 && work / 2 + 10.0 < work) ? left : 0;
+        if (nsplit) {
+            const bool fresh = ctx->scratch[6] == nullptr;
+            p.flags = (unsigned *) b200_scratch(ctx, 6, 1024 * sizeof(unsigned));          // fixed size, zeroed once, re-armed by the kernel
+            if (!p.flags) return B200_ERR_ALLOC;
+            if (fresh) B200_CUDA_TRY(cudaMemsetAsync(p.flags, 0, 1024 * sizeof(unsigned), ctx->stream));
+        }
+        p.lin = 1; p.n_unsplit = (int) (tiles - nsplit);
+        grid = dim3((unsigned) (tiles + nsplit), 1, 1);
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = dim3(GM_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    static const int no_pdl = getenv("GGML_B200_GEMM_NO_PDL") != nullptr;
+    cfg.attrs = attr; cfg.numAttrs = (ctx->pdl && !gi && !no_pdl) ? 1 : 0;    // grouped: the bucket tables are read before anything else
     switch (w->type) {
-        case B200_TYPE_Q6_K: B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q6_K><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap, maps)); break;
-        case B200_TYPE_Q8_0: B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q8_0><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap, maps)); break;
-        case B200_TYPE_Q4_0: B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q4_0><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap, maps)); break;
-        default:             B200_LAUNCH(ctx, B200_K_GEMM, k_gemm_q<B200_TYPE_Q4_K><<<grid, GM_THREADS, smem, ctx->stream>>>(p, tmap, maps)); break;
+        case B200_TYPE_Q6_K: B200_LAUNCH(ctx, B200_K_GEMM, cudaLaunchKernelEx(&cfg, k_gemm_q<B200_TYPE_Q6_K>, p, tmap, maps)); break;
+        case B200_TYPE_Q8_0: B200_LAUNCH(ctx, B200_K_GEMM, cudaLaunchKernelEx(&cfg, k_gemm_q<B200_TYPE_Q8_0>, p, tmap, maps)); break;
+        case B200_TYPE_Q4_0: B200_LAUNCH(ctx, B200_K_GEMM, cudaLaunchKernelEx(&cfg, k_gemm_q<B200_TYPE_Q4_0>, p, tmap, maps)); break;
+        default:             B200_LAUNCH(ctx, B200_K_GEMM, cudaLaunchKernelEx(&cfg, k_gemm_q<B200_TYPE_Q4_K>, p, tmap, maps)); break;
     }
     return B200_OK;
 }
