@@ -29,24 +29,31 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.join(ROOT, "super-llama.cpp_b200"))
 
-F32, F16, Q4_K, Q6_K, I32 = 0, 1, 12, 14, 26
-BLCK = {Q4_K: 256, Q6_K: 256}
-TSIZE = {Q4_K: 144, Q6_K: 210}
+F32, F16, Q4_0, Q8_0, Q4_K, Q6_K, I32 = 0, 1, 2, 8, 12, 14, 26
+BLCK = {Q4_K: 256, Q6_K: 256, Q4_0: 32, Q8_0: 32}
+TSIZE = {Q4_K: 144, Q6_K: 210, Q4_0: 18, Q8_0: 34}
 
 # Llama-3-8B: n_embd, n_ff, n_head, n_head_kv, head_dim, n_layer, n_vocab
 LLAMA3_8B = dict(name="llama3-8b", n_embd=4096, n_ff=14336, n_head=32, n_head_kv=8, head_dim=128, n_layer=32, n_vocab=128256)
 # BASELINE.json configs[3]: the 8-GPU row-split scale point (not the default bench line)
 LLAMA3_70B = dict(name="llama3-70b", n_embd=8192, n_ff=28672, n_head=64, n_head_kv=8, head_dim=128, n_layer=80, n_vocab=128256)
-MODELS = {"8b": LLAMA3_8B, "70b": LLAMA3_70B}
+# BASELINE.json configs[0] (the reference's CPU-runnable case) and configs[4] (MUL_MAT_ID: 8 experts, 2 used per token)
+TINYLLAMA = dict(name="tinyllama-1.1b", n_embd=2048, n_ff=5632, n_head=32, n_head_kv=4, head_dim=64, n_layer=22, n_vocab=32000)
+MIXTRAL = dict(name="mixtral-8x7b", n_embd=4096, n_ff=14336, n_head=32, n_head_kv=8, head_dim=128, n_layer=32, n_vocab=32000, n_expert=8, n_expert_used=2)
+MODELS = {"8b": LLAMA3_8B, "70b": LLAMA3_70B, "tinyllama": TINYLLAMA, "mixtral": MIXTRAL}
 
 
 def use_more_bits(i, n):       # src/llama-quant.cpp:186-188
     return i < n // 8 or i >= 7 * n // 8 or (i - n // 8) % 3 == 2
 
 
-def q4_k_m_layer_types(cfg):
-    """tensor types llama-quantize picks for Q4_K_M (src/llama-quant.cpp:207-227,302-303,358-364)"""
+def q4_k_m_layer_types(cfg, quant="q4_k_m"):
+    """tensor types llama-quantize picks for Q4_K_M (src/llama-quant.cpp:207-227,302-303,358-364); Q8_0 / Q4_0 files are uniform
+    (Q4_0 keeps a q6_K output head, llama-quant.cpp:207-227)"""
     n = cfg["n_layer"]
+    if quant in ("q8_0", "q4_0"):
+        t = Q8_0 if quant == "q8_0" else Q4_0
+        return [dict(wq=t, wk=t, wv=t, wo=t, gate=t, up=t, down=t) for _ in range(n)], (Q8_0 if quant == "q8_0" else Q6_K)
     out = []
     for i in range(n):
         more = use_more_bits(i, n)
@@ -59,6 +66,10 @@ def weight_shapes(cfg):
     return dict(wq=(e, e), wk=(e, kv), wv=(e, kv), wo=(e, e), gate=(e, f), up=(e, f), down=(f, e))   # (K, M)
 
 
+def pretty(cfg):
+    return {"llama3-8b": "Llama-3-8B", "llama3-70b": "Llama-3-70B", "tinyllama-1.1b": "TinyLlama-1.1B", "mixtral-8x7b": "Mixtral-8x7B"}[cfg["name"]]
+
+
 def wbytes(t, K, M):
     return K // BLCK[t] * TSIZE[t] * M
 
@@ -68,6 +79,8 @@ def random_blocks(rng, t, nblocks):
     if t == Q4_K:
         raw[:, 0:2] = (rng.uniform(0.1, 1, nblocks) * 2e-3).astype(np.float16).view(np.uint8).reshape(nblocks, 2)
         raw[:, 2:4] = (rng.uniform(0.1, 1, nblocks) * 2e-3).astype(np.float16).view(np.uint8).reshape(nblocks, 2)
+    elif t in (Q4_0, Q8_0):
+        raw[:, 0:2] = (rng.uniform(-1, 1, nblocks) * (2e-3 if t == Q4_0 else 2e-4)).astype(np.float16).view(np.uint8).reshape(nblocks, 2)
     else:
         raw[:, 208:210] = (rng.uniform(-1, 1, nblocks) * 1e-3).astype(np.float16).view(np.uint8).reshape(nblocks, 2)
     return raw.reshape(-1)
@@ -121,21 +134,26 @@ class HotPathModel:
     """The hot-path nodes of one llama decode/prefill step over device-resident random-init Q4_K_M weights.
     rank/world: split-mode=row shard (rows [lo, hi) of every weight); world == 1 is the whole model."""
 
-    def __init__(self, B, ctx, cfg, n_tokens, depth, rank=0, world=1, seed=1234, alloc=None, dist=None):
+    def __init__(self, B, ctx, cfg, n_tokens, depth, rank=0, world=1, seed=1234, alloc=None, dist=None, quant="q4_k_m"):
         self.B, self.ctx, self.cfg, self.N = B, ctx, cfg, n_tokens
+        self.quant = quant
+        self.moe = cfg.get("n_expert", 0)
+        if self.moe and world > 1:
+            raise SystemExit("MUL_MAT_ID does not shard (the reference asserts against split buffers, ggml-cuda.cu:2274): replicas only")
         self.rank, self.world = rank, world
         from row_split import RowSplit                      # partition rule + gather shared with tests/test_row_split_gloo.py
         self.rs = RowSplit(dist, world, rank, 32)
         rng = np.random.default_rng(seed + rank)
-        types, out_type = q4_k_m_layer_types(cfg)
+        types, out_type = q4_k_m_layer_types(cfg, quant)
         shapes = weight_shapes(cfg)
-        pool = {t: random_blocks(rng, t, (48 << 20) // TSIZE[t]) for t in (Q4_K, Q6_K)}
-        self.weight_bytes = 0
+        used = {t for lt in types for t in lt.values()} | {out_type}
+        pool = {t: random_blocks(rng, t, (48 << 20) // TSIZE[t]) for t in used}
+        self.weight_bytes = 0          # bytes of weights one token reads (MoE: the experts it routes to)
 
-        def make_weight(t, K, M):
+        def make_weight(t, K, M, ne=1):
             lo, hi = self.rs.row_range(M)
             ml = hi - lo
-            w = ctx.empty(t, [K, ml])
+            w = ctx.empty(t, [K, ml] if ne == 1 else [K, ml, ne])
             nb, blk = w.nbytes, TSIZE[t]
             off = 0
             while off < nb:                       # tile the random pool at random block-aligned offsets
@@ -143,13 +161,13 @@ class HotPathModel:
                 n = min(nb - off, pool[t].size - start)
                 ctx.h2d(w.ptr + off, pool[t][start:start + n])
                 off += n
-            self.weight_bytes += nb
+            self.weight_bytes += nb if ne == 1 else nb * cfg["n_expert_used"] // ne
             ctx.repack(w)                         # load-time repack (q6_K -> 16-byte aligned group layout), as set_tensor does
             return w, lo, hi
 
         self.layers = []
         for lt in types:
-            self.layers.append({name: make_weight(lt[name], *shapes[name]) for name in shapes})
+            self.layers.append({name: make_weight(lt[name], *shapes[name], ne=(self.moe if self.moe and name in ("gate", "up", "down") else 1)) for name in shapes})
         self.output = make_weight(out_type, cfg["n_embd"], cfg["n_vocab"])
         ctx.synchronize()
 
@@ -164,6 +182,13 @@ class HotPathModel:
         self.q = alloc(F32, [e, N]); self.k = alloc(F32, [kvd, N]); self.v = alloc(F32, [kvd, N])
         self.attn = alloc(F32, [e, N]); self.o = alloc(F32, [e, N]); self.g = alloc(F32, [f, N]); self.u = alloc(F32, [f, N])
         self.d = alloc(F32, [e, N])
+        if self.moe:
+            nu = cfg["n_expert_used"]
+            self.g3 = ctx.empty(F32, [f, nu, N]); self.u3 = ctx.empty(F32, [f, nu, N]); self.ff3 = ctx.empty(F32, [f, nu, N]); self.d3 = ctx.empty(F32, [e, nu, N])
+            ctx.h2d(self.ff3.ptr, (rng.standard_normal(f * nu * N) * 0.3).astype(np.float32))
+            self.h3 = self.h.view([e, 1, N, 1], [4, e * 4, e * 4, e * 4 * N])
+            ids = np.stack([rng.permutation(self.moe)[:nu] for _ in range(N)]).astype(np.int32)      # top-k routing: distinct experts per token
+            self.ids = ctx.upload(I32, [nu, N], ids)
         self.logits = alloc(F32, [cfg["n_vocab"], 1])
         for t, scale in ((self.x, 1.0), (self.h, 1.0), (self.ff, 0.3), (self.attn, 0.5)):
             ctx.h2d(t.ptr, (rng.standard_normal(t.ne[0] * t.ne[1]) * scale).astype(np.float32))
@@ -235,18 +260,22 @@ class HotPathModel:
             if attention:
                 c.flash_attn_ext(self.qview, self.kviews[il], self.vviews[il], self.mask, None, self.attn4, self.scale)
             self._mm(L["wo"], self.attn, self.o)
-            if fuse:
+            if self.moe:                                  # build_moe_ffn: MUL_MAT_ID x 3 (src/llama-graph.cpp), router and glue not on the hot path
+                c.mul_mat_id(L["gate"][0], self.h3, self.ids, self.g3); c.mul_mat_id(L["up"][0], self.h3, self.ids, self.u3)
+                c.mul_mat_id(L["down"][0], self.ff3, self.ids, self.d3)
+            elif fuse:
                 self._mm_group([L["gate"], L["up"]], self.h, [self.g, self.u])
+                self._mm(L["down"], self.ff, self.d)
             else:
                 self._mm(L["gate"], self.h, self.g); self._mm(L["up"], self.h, self.u)
-            self._mm(L["down"], self.ff, self.d)
+                self._mm(L["down"], self.ff, self.d)
         last = self.x if self.N == 1 else self.x.view([self.cfg["n_embd"], 1, 1, 1], self.x.nb, offset=(self.N - 1) * self.cfg["n_embd"] * 4)
         self._mm(self.output, last, self.logits)          # output head runs for the last row only (src/models/llama.cpp:97-98)
 
     # ---- algorithmic work --------------------------------------------------------------
     def matmul_flops(self):
         shapes = weight_shapes(self.cfg)
-        per_layer = sum(2 * K * M for K, M in shapes.values())
+        per_layer = sum(2 * K * M * (self.cfg["n_expert_used"] if self.moe and name in ("gate", "up", "down") else 1) for name, (K, M) in shapes.items())
         return self.N * per_layer * self.cfg["n_layer"] + 2 * self.cfg["n_embd"] * self.cfg["n_vocab"]
 
     def attn_flops(self):
@@ -266,7 +295,7 @@ def traffic_per_launch(algorithmic_bytes_per_launch):
 
 
 # ------------------------------------------------------------------------------------------------------------
-def cpu_baseline(cfg, depth, budget_s=20.0, full_token_steps=0, warmup=1):
+def cpu_baseline(cfg, depth, budget_s=20.0, steps=5, warmup=3, quant="q4_k_m"):
     """The reference's ggml-cpu implementation of the same ops, timed on this box's host cores (oracle/_ref compiled
     in place from /root/reference; the plain-C oracle port if that is absent).  Bounded sample: ONE transformer layer
     of each tensor-type variant (7 MUL_MAT + FLASH_ATTN_EXT at n=1) + the output head, extrapolated to n_layer layers.
@@ -276,7 +305,9 @@ def cpu_baseline(cfg, depth, budget_s=20.0, full_token_steps=0, warmup=1):
     cores = os.cpu_count() or 1
     rng = np.random.default_rng(7)
     shapes = weight_shapes(cfg)
-    types, out_type = q4_k_m_layer_types(cfg)
+    if cfg.get("n_expert"):
+        raise RuntimeError("no CPU baseline for the MUL_MAT_ID workload in this harness")
+    types, out_type = q4_k_m_layer_types(cfg, quant)
     n_kv = ((depth + 1 + 255) // 256) * 256
     if O.have_reference():
         ref = O.Reference()
@@ -304,26 +335,24 @@ def cpu_baseline(cfg, depth, budget_s=20.0, full_token_steps=0, warmup=1):
             variants[tuple(sorted(lt.items()))] += 1
         total_us = 0.0
         t_start = time.time()
-        for var, count in variants.items():
-            layer_ops = [mm(t, *shapes[name]) for name, t in var] + [fa]
-            for _ in range(3):                                      # warm-up: thread pool + page faults
+        head = mm(out_type, cfg["n_embd"], cfg["n_vocab"])
+        groups = [([mm(t, *shapes[name]) for name, t in var] + [fa], count) for var, count in variants.items()] + [([head], 1)]
+        done = steps
+        for layer_ops, count in groups:
+            for _ in range(max(warmup, 1)):                         # warm-up: thread pool + page faults
                 for op in layer_ops:
                     op.run()
-            best = None
-            for _ in range(5):
-                us = sum(op.run() for op in layer_ops)
-                best = us if best is None else min(best, us)
+            acc, n = 0.0, 0
+            for _ in range(steps):                                  # a step = this sample run once; the mean over the steps is reported
+                acc += sum(op.run() for op in layer_ops); n += 1
                 if time.time() - t_start > budget_s:
                     break
-            total_us += best * count
-        head = mm(out_type, cfg["n_embd"], cfg["n_vocab"])
-        for _ in range(2):
-            head.run()
-        total_us += min(head.run() for _ in range(3))
+            done = min(done, n)
+            total_us += acc / n * count
         for op in list(ops.values()) + [fa]:
             op.free()
-        return 1e6 / total_us, "reference", cores, (f"one layer of each of the {len(variants)} Q4_K_M tensor-type variants (7 MUL_MAT + FLASH_ATTN_EXT, n=1, "
-                                                    f"n_kv={n_kv}) + output head on ggml-cpu (oracle/_ref, OpenMP, {cores} threads), best of 5, x{cfg['n_layer']} layers")
+        return 1e6 / total_us, "reference", cores, (f"one layer of each of the {len(variants)} {quant.upper()} tensor-type variants (7 MUL_MAT + FLASH_ATTN_EXT, n=1, "
+                                                    f"n_kv={n_kv}) + output head on ggml-cpu (oracle/_ref, OpenMP, {cores} threads), mean of {done} timed steps after {max(warmup, 1)} warm-up, x{cfg['n_layer']} layers")
     # port: the scalar oracle on one core, one q4_K ffn_down GEMV, scaled by bytes
     orc = O.Oracle()
     K, M = shapes["down"]
@@ -341,11 +370,11 @@ def run_reference(args):
     if rank != 0:
         return
     t0 = time.time()
-    tps, kind, cores, sample = cpu_baseline(cfg, args.depth, budget_s=60.0)
-    line = {"impl": "reference", "metric": f"tg128 tok/s (llama-bench, {cfg['name'].replace('llama3', 'Llama-3').upper().replace('LLAMA', 'Llama')} Q4_K_M)", "value": tps, "unit": "tok/s", "n_gpus": args.gpus,
+    tps, kind, cores, sample = cpu_baseline(cfg, args.depth, budget_s=150.0, steps=args.steps, warmup=args.warmup, quant=args.quant)
+    line = {"impl": "reference", "metric": f"tg128 tok/s (llama-bench, {pretty(cfg)} {args.quant.upper()})", "value": tps, "unit": "tok/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / tps, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "int8 dot / f32 accumulate (q8_0, q8_K activations)", "data": "synthetic",
-            "config": {"workload": f"{cfg['name']}-q4_k_m tg128 decode hot path (MUL_MAT + FLASH_ATTN_EXT nodes)", "depth": args.depth},
+            "config": {"workload": f"{cfg['name']}-{args.quant} tg128 decode hot path (MUL_MAT + FLASH_ATTN_EXT nodes)", "depth": args.depth},
             "cpu_baseline": {"value": tps, "unit": "tok/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": tps, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "wall_s": time.time() - t0}
@@ -389,7 +418,7 @@ def run_b200(args):
         dt.torch = buf
         return dt
 
-    tg = HotPathModel(B, ctx, cfg, 1, args.depth, rank, world, alloc=alloc, dist=dist)
+    tg = HotPathModel(B, ctx, cfg, 1, args.depth, rank, world, alloc=alloc, dist=dist, quant=args.quant)
     tg.peer = peer
     if world > 1 and peer is None:
         ext = torch.cuda.ExternalStream(ctx.stream, device=f"cuda:{local}")
@@ -470,7 +499,7 @@ def run_b200(args):
         l0 = ctx.launches_by_kind()
         ctx.graph_begin(); mm_only(); g2 = ctx.graph_end()
         l1 = ctx.launches_by_kind()
-        gemv_n = l1["gemv"] - l0["gemv"]
+        gemv_n = l1["gemv"] - l0["gemv"] + l1["gemv_id"] - l0["gemv_id"]
         other_n = sum(l1.values()) - sum(l0.values()) - gemv_n
         ctx.graph_launch(g2); ctx.synchronize()
         e0, e1 = ctx.event(), ctx.event()
@@ -485,9 +514,10 @@ def run_b200(args):
     prof = ctx.profile_get()
     ctx.profile(False)
     if gemv_ms_step is None:
-        gemv_ms_step, gemv_n, other_n = prof.get("gemv", (0.0, 0))[0] / 3, prof.get("gemv", (0.0, 0))[1] // 3, 0
+        gemv_ms_step = (prof.get("gemv", (0.0, 0))[0] + prof.get("gemv_id", (0.0, 0))[0]) / 3
+        gemv_n, other_n = (prof.get("gemv", (0.0, 0))[1] + prof.get("gemv_id", (0.0, 0))[1]) // 3, 0
     shapes = weight_shapes(cfg)
-    act_bytes = sum(K * 4 + M * 4 for lt in tg.layers for (K, M) in [shapes[n] for n in shapes]) // max(world, 1)
+    act_bytes = sum(K * 4 + M * 4 for lt in tg.layers for (K, M) in [shapes[n] for n in shapes]) // max(world, 1)   # (MoE: x2 on the expert tensors, < 0.1 % of the bytes)
     gemv_bytes_step = tg.weight_bytes + act_bytes
     achieved = gemv_bytes_step / (gemv_ms_step * 1e-3) / 1e9 if gemv_ms_step > 0 else 0.0
 
@@ -496,11 +526,11 @@ def run_b200(args):
         tps = 1e3 / ms_tg
         total_bytes = tg.weight_bytes * world + tg.kv_bytes_per_layer * cfg["n_layer"]
         result = {
-            "metric": f"tg128 tok/s (llama-bench, {cfg['name'].replace('llama3', 'Llama-3').upper().replace('LLAMA', 'Llama')} Q4_K_M)", "value": tps, "unit": "tok/s", "n_gpus": world, "steps": args.steps,
+            "metric": f"tg128 tok/s (llama-bench, {pretty(cfg)} {args.quant.upper()})", "value": tps, "unit": "tok/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_tg, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "int8 dp4a dot / f32 accumulate (q8_1 activations); f16 KV, f32 softmax", "data": "synthetic",
-            "config": {"workload": f"{cfg['name']}-q4_k_m tg128: all MUL_MAT + FLASH_ATTN_EXT nodes of one decode token ({cfg['n_layer']} layers + output head); glue ops not included",
-                       "tensor_types": "Q4_K_M mix: q4_K, q6_K on attn_v/ffn_down of 16 layers, q6_K output", "depth": args.depth, "n_kv": tg.n_kv,
+            "config": {"workload": f"{cfg['name']}-{args.quant} tg128: all MUL_MAT{'_ID' if cfg.get('n_expert') else ''} + FLASH_ATTN_EXT nodes of one decode token ({cfg['n_layer']} layers + output head); glue ops not included",
+                       "tensor_types": "Q4_K_M mix: q4_K, q6_K on attn_v/ffn_down of half the layers, q6_K output" if args.quant == "q4_k_m" else args.quant + " weights", "depth": args.depth, "n_kv": tg.n_kv,
                        "parallelism": (f"row-split tp{world}, all-gather " + ("fused into the GEMV epilogue (NVLink peer stores)" if peer is not None else "by NCCL")) if world > 1 else "single GPU", "cuda_graph": bool(graph),
                        "l2": f"weights {tg.weight_bytes * world / 1e9:.1f} GB >> 126 MB L2, streamed once per step"},
             "hbm_bytes_per_step": total_bytes, "hbm_frac_whole_step": total_bytes / world / (ms_tg * 1e-3) / 1e9 / hbm_gbs,
@@ -516,11 +546,11 @@ def run_b200(args):
     # ---- secondary: pp512 (prefill) on one GPU
     if world == 1 and not args.no_pp:
         del tg
-        pp = HotPathModel(B, ctx, cfg, 512, args.depth)
+        pp = HotPathModel(B, ctx, cfg, 512, args.depth, quant=args.quant)
         ms_pp, _, _ = timed(pp, max(2, min(args.steps, 5)), 1, False)
         ctx.profile(True); pp.step(); prof_pp = ctx.profile_get(); ctx.profile(False)
         flops = pp.matmul_flops()
-        mm_ms = prof_pp.get("gemm", (0.0, 0))[0] + prof_pp.get("gemv", (0.0, 0))[0]
+        mm_ms = prof_pp.get("gemm", (0.0, 0))[0] + prof_pp.get("gemv", (0.0, 0))[0] + prof_pp.get("gemv_id", (0.0, 0))[0]
         result["pp512"] = {"value": 512e3 / ms_pp, "unit": "tok/s", "ms_per_step": ms_pp, "matmul_tflop_per_step": flops / 1e12,
                            "roofline": {"kernel": "MUL_MAT prefill kernels", "bound": "tensor", "achieved": flops / (mm_ms * 1e-3) / 1e12 if mm_ms else 0.0,
                                         "peak": tf_sust, "unit": "TFLOP/s", "frac": (flops / (mm_ms * 1e-3) / 1e12 / tf_sust) if mm_ms else 0.0,
@@ -529,7 +559,7 @@ def run_b200(args):
     if rank == 0:
         if not args.no_cpu and world == 1:
             try:
-                v, kind, cores, sample = cpu_baseline(cfg, args.depth)
+                v, kind, cores, sample = cpu_baseline(cfg, args.depth, quant=args.quant)
                 result["cpu_baseline"] = {"value": v, "unit": "tok/s", "cores": cores, "kind": kind, "sample": sample}
             except Exception as ex:                      # the baseline is a reported number, never a reason to lose the GPU line
                 result["cpu_baseline"] = {"value": None, "unit": "tok/s", "cores": os.cpu_count(), "kind": "unavailable", "sample": repr(ex)}
@@ -546,6 +576,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--depth", type=int, default=0, help="tokens already in the KV cache (llama-bench -d)")
     ap.add_argument("--model", default="8b", choices=sorted(MODELS), help="8b = the headline config; 70b = configs[3] scale point")
+    ap.add_argument("--quant", default="q4_k_m", choices=["q4_k_m", "q8_0", "q4_0"], help="GGUF file type of the synthetic weights")
     ap.add_argument("--no-pp", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
