@@ -381,6 +381,38 @@ extern "C" int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b20
         return rc;
     }
     int rc;
+    // decode (one token, <= 3 experts used): the experts are segments of the streaming GEMV (TMA ring, fused q8_1 quantization), which
+    // picks each segment's expert from the device-side ids; shared activations (gate/up) = one launch, per-slot activations (down) = one
+    // launch per slot
+    static const int no_stream_id = getenv("GGML_B200_NO_GEMV_STREAM_ID") != nullptr;
+    if (!no_stream_id && n_tokens == 1 && n_used <= 3 && q8_1_variant_env() == B200_Q8_1_X86 && ids->nb[0] == 4 && dst->nb[1] % 4 == 0 && b->nb[1] % 16 == 0) {
+        b200_tensor w2 = *as; w2.ne[2] = 1; w2.ne[3] = 1;                   // expert 0 as a plain [K, M] matrix
+        b200_tensor x2 = *b;  x2.ne[1] = 1; x2.ne[2] = 1; x2.ne[3] = 1;
+        if (b200_gemv_stream_supported(&w2, &x2)) {
+            const b200_tensor * ws[3] = { &w2, &w2, &w2 };
+            float * d[3];
+            for (int64_t sl = 0; sl < n_used; ++sl) d[sl] = (float *) ((char *) dst->data + sl * dst->nb[1]);
+            b200_gemv_ids idm; idm.ids = (const int *) ids->data; idm.stride = as->nb[2]; idm.ads = nullptr;
+            rc = B200_OK;
+            if (b->ne[1] == 1) {
+                const void * image = nullptr;
+                if (K > B200_GEMV_FUSED_QUANT_MAX_K) { image = quantized_activations(ctx, &x2, B200_Q8_1_X86, &rc); if (!image) return rc; }
+                idm.base = 0;
+                rc = b200_launch_gemv_stream(ctx, ws, (int) n_used, &x2, image, d, nullptr, &idm);
+            } else {
+                const char * image = nullptr;                               // all slots' columns quantized by one launch
+                if (K > B200_GEMV_FUSED_QUANT_MAX_K) { image = (const char *) quantized_activations(ctx, b, B200_Q8_1_X86, &rc); if (!image) return rc; }
+                for (int64_t sl = 0; sl < n_used && rc == B200_OK; ++sl) {
+                    x2.data = (char *) b->data + sl * b->nb[1];
+                    idm.base = (int) sl;
+                    idm.ads = image ? image + (size_t) n_used * K + (size_t) sl * (K / 32) * 4 : nullptr;
+                    rc = b200_launch_gemv_stream(ctx, ws, 1, &x2, image ? image + (size_t) sl * K : nullptr, d + sl, nullptr, &idm);
+                }
+            }
+            b200_note_write(ctx, dst->data, b200_tensor_span(dst));
+            return rc;
+        }
+    }
     const void * image = quantized_activations(ctx, b, q8_1_variant_env(), &rc);
     if (!image) return rc;
     rc = b200_launch_gemv_id_q(ctx, as, image, b->ne[1], n_tokens, ids, dst);

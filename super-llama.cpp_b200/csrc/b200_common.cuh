@@ -169,8 +169,10 @@ bool b200_gemv_stream_supported(const b200_tensor * w, const b200_tensor * x);
 // peers of a row-split MUL_MAT: the low-latency mirror (8 bytes per arena float) of every rank's arena, our own arena and its
 // control words, and the full f32 columns (inside our arena) that the kernel receives after it has sent its own rows
 struct b200_rowsplit_peers { int nll; void * ll_base[B200_MAX_PEERS]; const void * ll_self; const void * arena; unsigned * ctrl; float * full[3]; int full_m[3]; };
+// decode MUL_MAT_ID through the streaming GEMV: segment s reads expert ids[base + s] (device memory) at byte stride `stride`
+struct b200_gemv_ids { const int * ids; int base; size_t stride; const void * ads; };   // ads: (d, s) pairs of this column when `image` is one column of a wider q8_1 image
 int  b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, const void * image, float * const * dst,
-                             const b200_rowsplit_peers * peers = nullptr);
+                             const b200_rowsplit_peers * peers = nullptr, const b200_gemv_ids * idm = nullptr);
 bool b200_gemv_mma_supported(const b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x);
 int  b200_launch_gemv_mma(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, const void * image, float * const * dst,
                           const b200_rowsplit_peers * peers);

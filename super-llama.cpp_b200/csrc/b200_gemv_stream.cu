@@ -42,6 +42,9 @@ struct gs_args {
     // cannot starve a producer; peers never wait on us inside the same exchange.
     int nll; char * ll_base[B200_MAX_PEERS]; const char * ll_self; const char * arena; unsigned * ctrl;
     struct { float * dst; int M; } full[GS_MAXSEG];
+    // decode MUL_MAT_ID: segment s reads expert ids[id_base + s] of a stacked weight tensor (seg[s].w = expert 0); the ids live on the
+    // device and come from an earlier kernel, so in this mode the first weight fetch is issued after griddepcontrol.wait
+    const int * ids; int id_base; size_t estride;
     int dbg;                                 // GGML_B200_GS_DBG (measurement only): 1 skip quantization, 2 skip the dot products, 4 no weight traffic
 };
 
@@ -245,12 +248,13 @@ template <> struct gs_traits<B200_TYPE_Q8_0> {
 };
 
 // ====================================================== the kernel ======================================================
-static __device__ __forceinline__ void gs_locate(const gs_args & p, int gr, const uint8_t * & w, float * & dst) {
+static __device__ __forceinline__ void gs_locate(const gs_args & p, int gr, const uint8_t * & w, float * & dst, int * seg = nullptr) {
     // global row -> (segment, row): at most two compares
     int s = 0, r = gr;
     if (p.nseg > 1 && r >= p.seg[0].M) { r -= p.seg[0].M; s = 1; if (p.nseg > 2 && r >= p.seg[1].M) { r -= p.seg[1].M; s = 2; } }
     w = p.seg[s].w + (size_t) r * p.seg[s].nb1;
     dst = p.seg[s].dst + r;
+    if (seg) *seg = s;
 }
 
 // SHAPE: 0 = LEAN (12 warps, 1 CTA/SM), 1 = WIDE (8 warps, deep rings, 2 CTAs/SM), 2 = DENSE (12 warps, 2 CTAs/SM: most warps per SM)
@@ -296,20 +300,22 @@ __global__ void __launch_bounds__(SHAPE == 1 ? 256 : 384, 2) k_gemv_stream(const
             const uint32_t bytes = (uint32_t) cb * T::BLOCK_BYTES, bar = bar0 + 8 * stage;
             mbar_arrive_expect_tx(bar, bytes * nr);
             for (int r = 0; r < nr; ++r) {
-                const uint8_t * w; float * dst;
-                gs_locate(p, r_begin + prp * GS_RW + r, w, dst);
+                const uint8_t * w; float * dst; int sg;
+                gs_locate(p, r_begin + prp * GS_RW + r, w, dst, &sg);
+                if (p.ids) w += (size_t) __ldg(p.ids + p.id_base + sg) * p.estride;
                 bulk_g2s_hint(ring + stage * STAGE_BYTES + r * CHUNK_BYTES, w + (size_t) pkc * CHUNK_BYTES, bytes, bar, policy);
             }
         }
         if (++pkc == nchunks) { pkc = 0; ++prp; }
     };
     const int npro = min(nitems, GS_STAGES);
-    for (int i = 0; i < npro; ++i) issue(i);                              // weights do not depend on the previous kernel
+    if (!p.ids) for (int i = 0; i < npro; ++i) issue(i);                  // weights do not depend on the previous kernel
 
     // src1 is produced by the previous kernel in the stream: wait for it (and its memory) before the first read
     asm volatile("griddepcontrol.wait;" ::: "memory");
     unsigned ll_tag = 0;
     if (p.nll) { asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(ll_tag) : "l"(p.ctrl + 8)); ll_tag += 1u; }
+    if (p.ids) for (int i = 0; i < npro; ++i) issue(i);                   // which experts: only known now
 
     // quantize the activation column to q8_1 straight into shared memory, in lane order.  Same arithmetic as
     // q8_1_block<B200_Q8_1_X86> (bit-exact with the reference), but 128-bit loads: a lane holds 4 consecutive values, the
@@ -538,9 +544,10 @@ static int gs_launch(b200_ctx * ctx, const gs_args & p, int attr_slot) {
 
 // n <= 3 weights of the same type sharing the activation column x; dst[i] is the f32 column of weight i
 int b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, const void * image, float * const * dst,
-                            const b200_rowsplit_peers * peers) {
-    if (b200_gemv_mma_supported(ctx, w, n, x)) return b200_launch_gemv_mma(ctx, w, n, x, image, dst, peers);   // raw q4_K: tensor-core dots
+                            const b200_rowsplit_peers * peers, const b200_gemv_ids * idm) {
+    if (!idm && b200_gemv_mma_supported(ctx, w, n, x)) return b200_launch_gemv_mma(ctx, w, n, x, image, dst, peers);   // raw q4_K: tensor-core dots
     gs_args p;
+    p.ids = idm ? idm->ids : nullptr; p.id_base = idm ? idm->base : 0; p.estride = idm ? idm->stride : 0;
     p.nll = 0; p.ll_self = nullptr; p.arena = nullptr; p.ctrl = nullptr;
     for (int i = 0; i < B200_MAX_PEERS; ++i) p.ll_base[i] = nullptr;
     for (int i = 0; i < GS_MAXSEG; ++i) { p.full[i].dst = nullptr; p.full[i].M = 0; }
@@ -552,6 +559,7 @@ int b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n
     { static int dbg = -1; if (dbg < 0) { const char * e = getenv("GGML_B200_GS_DBG"); dbg = e ? atoi(e) : 0; } p.dbg = dbg; }
     p.nseg = n; p.Mtot = 0; p.x = (const float *) x->data; p.K = (int) w[0]->ne[0];
     p.aq = (const int8_t *) image; p.ads = image ? (const __half2 *) ((const int8_t *) image + p.K) : nullptr;
+    if (image && idm && idm->ads) p.ads = (const __half2 *) idm->ads;
     for (int i = 0; i < n; ++i) {
         p.seg[i].w = (const uint8_t *) w[i]->data; p.seg[i].nb1 = w[i]->nb[1]; p.seg[i].dst = dst[i]; p.seg[i].M = (int) w[i]->ne[1];
         p.Mtot += p.seg[i].M;
