@@ -93,6 +93,9 @@ B200_API int      b200_event_destroy(void * ev);
 B200_API int      b200_event_record(b200_ctx * ctx, void * ev);
 B200_API int      b200_event_elapsed_ms(void * ev0, void * ev1, float * ms);     // waits for ev1
 // capture everything issued on the ctx stream between begin/end into a graph; launch replays it on the ctx stream
+/* measurement only: every CTA of the decode GEMV kernels appends a 32 x u64 timeline record to `buf` (device memory,
+ * (1 + cap) * 256 bytes, word 0 = record counter, zeroed by the caller); buf = NULL switches it off */
+B200_API int      b200_debug_trace(b200_ctx * ctx, void * buf, int cap);
 B200_API int      b200_graph_begin(b200_ctx * ctx);
 B200_API void *   b200_graph_end(b200_ctx * ctx);                    // cudaGraphExec_t, NULL on failure
 B200_API int      b200_graph_launch(b200_ctx * ctx, void * graph_exec);

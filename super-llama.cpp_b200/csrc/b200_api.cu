@@ -98,6 +98,7 @@ extern "C" int b200_event_elapsed_ms(void * ev0, void * ev1, float * ms) {
     B200_CUDA_TRY(cudaEventElapsedTime(ms, (cudaEvent_t) ev0, (cudaEvent_t) ev1));
     return B200_OK;
 }
+extern "C" int b200_debug_trace(b200_ctx * ctx, void * buf, int cap) { ctx->trace = (unsigned long long *) buf; ctx->trace_cap = buf ? cap : 0; return B200_OK; }
 extern "C" int b200_graph_begin(b200_ctx * ctx) {
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
     B200_CUDA_TRY(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
@@ -183,6 +184,12 @@ void b200_note_write(b200_ctx * ctx, const void * ptr, size_t nbytes) {
 }
 extern "C" int b200_ctx_invalidate(b200_ctx * ctx) { ctx->qcache.valid = 0; ctx->mcache.valid = 0; return B200_OK; }
 
+// largest K whose activation column every GEMV CTA quantizes itself; above it one quantize launch writes an image (GGML_B200_FUSED_QUANT_MAX_K)
+static int64_t fused_quant_max_k() {
+    static int64_t v = -1;
+    if (v < 0) { const char * e = getenv("GGML_B200_FUSED_QUANT_MAX_K"); v = e ? atoll(e) : B200_GEMV_FUSED_QUANT_MAX_K; }
+    return v;
+}
 // q8_1 image of x in scratch slot 0, reused when the same activation tensor feeds consecutive matmuls
 static const void * quantized_activations(b200_ctx * ctx, const b200_tensor * x, int variant, int * rc) {
     const int64_t K = x->ne[0], ncol = x->ne[1] * x->ne[2] * x->ne[3];
@@ -234,7 +241,7 @@ extern "C" int b200_mul_mat(b200_ctx * ctx, const b200_tensor * w, const b200_te
         else if (q8_1_variant_env() == B200_Q8_1_X86 && b200_gemv_stream_supported(w, x)) {
             float * d = (float *) dst->data;
             const void * image = nullptr;
-            if (w->ne[0] > B200_GEMV_FUSED_QUANT_MAX_K) { image = quantized_activations(ctx, x, B200_Q8_1_X86, &rc); if (!image) return rc; }
+            if (w->ne[0] > fused_quant_max_k()) { image = quantized_activations(ctx, x, B200_Q8_1_X86, &rc); if (!image) return rc; }
             rc = b200_launch_gemv_stream(ctx, &w, 1, x, image, &d);      // TMA-streamed GEMV, q8_1 quantization fused for small K
         } else {
             const void * image = quantized_activations(ctx, x, q8_1_variant_env(), &rc);
@@ -280,7 +287,7 @@ extern "C" int b200_mul_mat_multi(b200_ctx * ctx, const b200_tensor * const * w,
     for (int i = 0; i < n; ++i) d[i] = (float *) dst[i]->data;
     int rc;
     const void * image = nullptr;
-    if (w[0]->ne[0] > B200_GEMV_FUSED_QUANT_MAX_K) { image = quantized_activations(ctx, x, B200_Q8_1_X86, &rc); if (!image) return rc; }
+    if (w[0]->ne[0] > fused_quant_max_k()) { image = quantized_activations(ctx, x, B200_Q8_1_X86, &rc); if (!image) return rc; }
     rc = b200_launch_gemv_stream(ctx, w, n, x, image, d);
     for (int i = 0; i < n; ++i) b200_note_write(ctx, dst[i]->data, b200_tensor_span(dst[i]));
     return rc;
@@ -332,7 +339,7 @@ extern "C" int b200_mul_mat_rowsplit_multi(b200_ctx * ctx, const b200_tensor * c
     pe.ll_self = pe.ll_base[ex->rank];
     int rc = B200_OK;
     const void * image = nullptr;
-    if (w[0]->ne[0] > B200_GEMV_FUSED_QUANT_MAX_K) { image = quantized_activations(ctx, x, B200_Q8_1_X86, &rc); if (!image) return rc; }
+    if (w[0]->ne[0] > fused_quant_max_k()) { image = quantized_activations(ctx, x, B200_Q8_1_X86, &rc); if (!image) return rc; }
     for (int i = 0; i < n && rc == B200_OK; ) {
         int j = i + 1;
         while (j < n && w[j]->type == w[i]->type && (w[j]->flags & B200_TENSOR_REPACKED) == (w[i]->flags & B200_TENSOR_REPACKED)) ++j;
@@ -396,12 +403,12 @@ extern "C" int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b20
             rc = B200_OK;
             if (b->ne[1] == 1) {
                 const void * image = nullptr;
-                if (K > B200_GEMV_FUSED_QUANT_MAX_K) { image = quantized_activations(ctx, &x2, B200_Q8_1_X86, &rc); if (!image) return rc; }
+                if (K > fused_quant_max_k()) { image = quantized_activations(ctx, &x2, B200_Q8_1_X86, &rc); if (!image) return rc; }
                 idm.base = 0;
                 rc = b200_launch_gemv_stream(ctx, ws, (int) n_used, &x2, image, d, nullptr, &idm);
             } else {
                 const char * image = nullptr;                               // all slots' columns quantized by one launch
-                if (K > B200_GEMV_FUSED_QUANT_MAX_K) { image = (const char *) quantized_activations(ctx, b, B200_Q8_1_X86, &rc); if (!image) return rc; }
+                if (K > fused_quant_max_k()) { image = (const char *) quantized_activations(ctx, b, B200_Q8_1_X86, &rc); if (!image) return rc; }
                 for (int64_t sl = 0; sl < n_used && rc == B200_OK; ++sl) {
                     x2.data = (char *) b->data + sl * b->nb[1];
                     idm.base = (int) sl;

@@ -71,8 +71,25 @@ struct b200_ctx {
     // per-tile liveness flags of the most recently scanned attention mask (scratch slot 2)
     struct { const void * data; int64_t ne[4]; size_t nb[4]; size_t span; int64_t n; int valid; } mcache;
     int          attr_done[16];
-    int          pdl;                // launch the streaming GEMV with programmatic dependent launch (GGML_B200_NO_PDL=1 disables)       // per-kernel one-time cudaFuncSetAttribute flags (a ctx is bound to one device)
+    int          pdl;                // launch the streaming GEMV with programmatic dependent launch (GGML_B200_NO_PDL=1 disables)
+    // device-side timeline of the decode GEMV kernels (b200_debug_trace; measurement only, NULL in production)
+    unsigned long long * trace; int trace_cap;
 };
+// one record per CTA, 32 x u64 (stamps 6.. are kernel-specific fine-grain points): [0] Mtot << 32 | K, [1] smid << 32 | blockIdx, then (globaltimer ns, clock64) pairs at:
+// CTA start, prologue prefetch issued, griddepcontrol.wait returned, activations quantized, first stage landed (warp 0), CTA end
+#define B200_TRACE_WORDS 32
+static __device__ __forceinline__ void b200_trace_stamp(unsigned long long * rec, int i) {
+    if (rec) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); rec[2 + 2 * i] = t; rec[3 + 2 * i] = (unsigned long long) clock64(); }
+}
+static __device__ __forceinline__ unsigned long long * b200_trace_open(unsigned long long * trace, int cap, int Mtot, int K) {
+    if (!trace) return nullptr;
+    const unsigned long long slot = atomicAdd(trace, 1ull);
+    if (slot >= (unsigned long long) cap) return nullptr;
+    unsigned smid; asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    unsigned long long * rec = trace + B200_TRACE_WORDS * (1 + slot);
+    rec[0] = ((unsigned long long) Mtot << 32) | (unsigned) K; rec[1] = ((unsigned long long) smid << 32) | blockIdx.x;
+    return rec;
+}
 
 void   b200_set_error(const char * fmt, ...);
 void * b200_scratch(b200_ctx * ctx, int slot, size_t nbytes);   // returns device ptr, NULL on failure
@@ -141,6 +158,87 @@ static __device__ __forceinline__ void q8_1_block(float v, int & q, float & d, i
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) usum += __shfl_xor_sync(0xffffffffu, usum, o);
     isum = (int) usum;
+}
+
+// CTA-wide q8_1 quantization (x86 variant, bit-exact with q8_1_block<B200_Q8_1_X86>) of one f32 column x[0, K) for the decode GEMV
+// kernels: TWO lanes per 32-value block, 16 values (one 16-byte unit of quants) per lane, so a block costs one shuffle for amax and
+// one for the sum and the 16 conversions of a lane are independent instructions (the 8-lanes-per-block form spent ~2000 cycles per
+// CTA in shuffle / division latency chains, measured with b200_debug_trace).  Rounds are double-buffered: the next round's loads are
+// in flight while this one converts.  store(blk32, hf, quants, d, s): hf = which half of block blk32, d and s after their fp16 round trip.
+template <class F>
+static __device__ __forceinline__ void b200_quantize_column_x86(const float * x, int K, F store) {
+    const int nunits = K >> 4, lane = threadIdx.x & 31;
+    const float4 * x4 = (const float4 *) x;
+    int base = (int) (threadIdx.x & ~31u);                               // warp-uniform; K % 32 == 0 keeps lane pairs together
+    float4 v[4];
+    if (base < nunits) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[j] = base + lane < nunits ? x4[(base + lane) * 4 + j] : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    while (base < nunits) {
+        const int u = base + lane, nb = base + (int) blockDim.x;
+        float4 nx[4];
+        if (nb < nunits) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) nx[j] = nb + lane < nunits ? x4[(nb + lane) * 4 + j] : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        const float f[16] = { v[0].x, v[0].y, v[0].z, v[0].w, v[1].x, v[1].y, v[1].z, v[1].w, v[2].x, v[2].y, v[2].z, v[2].w, v[3].x, v[3].y, v[3].z, v[3].w };
+        // amax over the |bit patterns| as integers: same order as the floats, and a NaN input shows up as amax > inf
+        unsigned ab[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) ab[i] = max(__float_as_uint(f[2 * i]) & 0x7fffffffu, __float_as_uint(f[2 * i + 1]) & 0x7fffffffu);
+        unsigned abits = max(max(max(ab[0], ab[1]), max(ab[2], ab[3])), max(max(ab[4], ab[5]), max(ab[6], ab[7])));
+        abits = max(abits, __shfl_xor_sync(0xffffffffu, abits, 1));
+        const bool  nan_in = abits > 0x7f800000u;
+        // NaN inputs never win the reference's amax search (`a > amax` from 0, oracle/ggml_oracle.c): largest non-NaN magnitude, rare path
+        float amax = __uint_as_float(abits);
+        if (__any_sync(0xffffffffu, nan_in)) {
+            amax = 0.0f;
+#pragma unroll
+            for (int i = 0; i < 16; ++i) amax = fmaxf(amax, fabsf(f[i]));
+            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+        }
+        const float d  = __fdiv_rn(amax, 127.0f);
+        const float id = amax != 0.0f ? __fdiv_rn(127.0f, amax) : 0.0f;
+        int4 w;
+        int * wp = (int *) &w;
+        unsigned usum;
+        // finite inputs and a finite 127/amax: |x * id| <= 127 (1 + 2^-23), so every quant is in [-127, 127]: nothing saturates, the
+        // x86 "integer indefinite" cannot occur and the int32 sum equals the sum of the packed bytes
+        const bool fast = !nan_in && abits < 0x7f800000u && (__float_as_uint(id) & 0x7fffffffu) < 0x7f800000u;
+        if (__all_sync(0xffffffffu, fast)) {
+            int acc = 0;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int q0 = __float2int_rn(__fmul_rn(f[4 * i], id)),     q1 = __float2int_rn(__fmul_rn(f[4 * i + 1], id));
+                const int q2 = __float2int_rn(__fmul_rn(f[4 * i + 2], id)), q3 = __float2int_rn(__fmul_rn(f[4 * i + 3], id));
+                int hi, wd;
+                asm("cvt.pack.sat.s8.s32.b32 %0, %1, %2, %3;" : "=r"(hi) : "r"(q3), "r"(q2), "r"(0));
+                asm("cvt.pack.sat.s8.s32.b32 %0, %1, %2, %3;" : "=r"(wd) : "r"(q1), "r"(q0), "r"(hi));
+                wp[i] = wd;
+                acc = __dp4a(wd, 0x01010101, acc);
+            }
+            usum = (unsigned) acc;
+        } else {
+            int q[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) q[i] = cvt_x86(__fmul_rn(f[i], id));   // cvt.rni rounds half to even itself: same as rintf() first
+            usum = 0u;                                                    // int32 lanes summed before saturation (AVX2 body)
+#pragma unroll
+            for (int i = 0; i < 16; ++i) usum += (unsigned) q[i];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                wp[i] = (int) (((unsigned) max(-128, min(127, q[4 * i])) & 0xffu)            | (((unsigned) max(-128, min(127, q[4 * i + 1])) & 0xffu) << 8) |
+                               (((unsigned) max(-128, min(127, q[4 * i + 2])) & 0xffu) << 16) | (((unsigned) max(-128, min(127, q[4 * i + 3])) & 0xffu) << 24));
+        }
+        usum += __shfl_xor_sync(0xffffffffu, usum, 1);
+        if (u < nunits) store(u >> 1, u & 1, w, __half2float(__float2half_rn(d)), __half2float(__float2half_rn(__fmul_rn(d, (float) (int) usum))));
+        if (nb < nunits) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[j] = nx[j];
+        }
+        base = nb;
+    }
 }
 
 // ---- internal launchers (defined in the .cu files) ----------------------------------------

@@ -38,6 +38,7 @@ struct gq_args {
     struct { float * dst; int M; } full[GQ_MAXSEG];
     int dbg;
     int npf;                                                            // items per warp to prefetch into L2 behind the ring fill
+    unsigned long long * trace; int trace_cap;                          // b200_debug_trace (measurement only)
 };
 struct gq_maps { CUtensorMap m[GQ_MAXSEG]; };
 
@@ -72,6 +73,9 @@ __global__ void __launch_bounds__(GQ_WARPS * 32, 2) k_gemv_q4k_mma(const gq_args
     const int g_lo = (int) ((int64_t) G * blockIdx.x / gridDim.x), g_hi = (int) ((int64_t) G * (blockIdx.x + 1) / gridDim.x);
     const int nitems_cta = (p.dbg & 4) ? 0 : (g_hi - g_lo) * nchunks;
 
+    unsigned long long * rec = nullptr;
+    if (p.trace && threadIdx.x == 0) rec = b200_trace_open(p.trace, p.trace_cap, p.M[0] + p.M[1] + p.M[2], p.K | (1 << 30));
+    b200_trace_stamp(rec, 0);
     if (lane == 0) {
         for (int s = 0; s < GQ_STAGES; ++s) mbar_init(bar0 + 8 * s, 1);
         mbar_fence_init();
@@ -106,7 +110,9 @@ __global__ void __launch_bounds__(GQ_WARPS * 32, 2) k_gemv_q4k_mma(const gq_args
         }
     }
 
+    b200_trace_stamp(rec, 1);
     asm volatile("griddepcontrol.wait;" ::: "memory");                    // src1 comes from the previous kernel of the stream
+    b200_trace_stamp(rec, 2);
     unsigned ll_tag = 0;
     if (p.nll) { asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(ll_tag) : "l"(p.ctrl + 8)); ll_tag += 1u; }
 
@@ -117,38 +123,13 @@ __global__ void __launch_bounds__(GQ_WARPS * 32, 2) k_gemv_q4k_mma(const gq_args
         for (int j = threadIdx.x; j < (p.K >> 4); j += blockDim.x) ((int4 *) s_q)[j] = src[j];
         for (int j = threadIdx.x; j < (p.K >> 5); j += blockDim.x) s_ds[j] = __half22float2(p.ads[j]);
     } else {
-        constexpr int QB = 8;
-        const float4 * x4 = (const float4 *) p.x;
-        const int nvec = p.K >> 7;                                        // 128-float chunks = 4 q8_1 blocks per warp pass
-        for (int c0 = warp; c0 < nvec; c0 += GQ_WARPS * QB) {
-            float4 v[QB];
-#pragma unroll
-            for (int i = 0; i < QB; ++i) { const int c = c0 + i * GQ_WARPS; v[i] = c < nvec ? x4[c * 32 + lane] : make_float4(0.f, 0.f, 0.f, 0.f); }
-#pragma unroll
-            for (int i = 0; i < QB; ++i) {
-                const int c = c0 + i * GQ_WARPS;
-                if (c >= nvec) break;                                     // warp-uniform
-                float amax = fmaxf(fmaxf(fabsf(v[i].x), fabsf(v[i].y)), fmaxf(fabsf(v[i].z), fabsf(v[i].w)));
-                amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
-                amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
-                amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 4));
-                const float d  = __fdiv_rn(amax, 127.0f);
-                const float id = amax != 0.0f ? __fdiv_rn(127.0f, amax) : 0.0f;
-                const int q0 = cvt_x86(rintf(__fmul_rn(v[i].x, id))), q1 = cvt_x86(rintf(__fmul_rn(v[i].y, id)));
-                const int q2 = cvt_x86(rintf(__fmul_rn(v[i].z, id))), q3 = cvt_x86(rintf(__fmul_rn(v[i].w, id)));
-                unsigned usum = (unsigned) q0 + (unsigned) q1 + (unsigned) q2 + (unsigned) q3;   // int32 lanes summed before saturation
-                usum += __shfl_xor_sync(0xffffffffu, usum, 1);
-                usum += __shfl_xor_sync(0xffffffffu, usum, 2);
-                usum += __shfl_xor_sync(0xffffffffu, usum, 4);
-                const unsigned word = ((unsigned) max(-128, min(127, q0)) & 0xffu)        | (((unsigned) max(-128, min(127, q1)) & 0xffu) << 8) |
-                                      (((unsigned) max(-128, min(127, q2)) & 0xffu) << 16) | (((unsigned) max(-128, min(127, q3)) & 0xffu) << 24);
-                ((unsigned *) s_q)[c * 32 + lane] = word;
-                // d and s take the fp16 round trip they would take through block_q8_1
-                if ((lane & 7) == 0) s_ds[c * 4 + (lane >> 3)] = make_float2(__half2float(__float2half_rn(d)), __half2float(__float2half_rn(__fmul_rn(d, (float) (int) usum))));
-            }
-        }
+        b200_quantize_column_x86(p.x, p.K, [&](int blk32, int hf, int4 w, float d, float sm) {
+            ((int4 *) s_q)[blk32 * 2 + hf] = w;
+            if (hf == 0) s_ds[blk32] = make_float2(d, sm);
+        });
     }
     __syncthreads();
+    b200_trace_stamp(rec, 3);
 
     const int g = lane >> 2, t = lane & 3;
     const uint32_t q_sm = smem_u32(s_q) + lane * 8, ds_sm = smem_u32(s_ds) + t * 16;
@@ -157,6 +138,7 @@ __global__ void __launch_bounds__(GQ_WARPS * 32, 2) k_gemv_q4k_mma(const gq_args
     for (int it = warp; it < nitems_cta; it += GQ_WARPS) {
         const int gl = it / nchunks, ch = it - gl * nchunks;
         mbar_wait(bar0 + 8 * stage, (uint32_t) phase);
+        if (it == 0) b200_trace_stamp(rec, 4);
         float acc = 0.0f;
         if (!(p.dbg & 2)) {
             const uint32_t row = ring + stage * GQ_STAGE_BYTES + g * GQ_CHUNK;
@@ -196,8 +178,11 @@ __global__ void __launch_bounds__(GQ_WARPS * 32, 2) k_gemv_q4k_mma(const gq_args
         acc += __shfl_xor_sync(0xffffffffu, acc, 2);
         if (t == 0) s_par[(gl * nchunks + ch) * GQ_ROWS + g] = acc;
         if (++stage == GQ_STAGES) { stage = 0; phase ^= 1; }
+        if (it == warp) b200_trace_stamp(rec, 9);                           // warp 0: first item done
     }
+    b200_trace_stamp(rec, 6);                                             // warp 0: all its items done
     __syncthreads();
+    b200_trace_stamp(rec, 7);                                             // every warp done
 
     // add the chunk partials of every row in chunk order and store (or send) the row
     for (int i = threadIdx.x; i < (g_hi - g_lo) * GQ_ROWS; i += blockDim.x) {
@@ -218,6 +203,7 @@ __global__ void __launch_bounds__(GQ_WARPS * 32, 2) k_gemv_q4k_mma(const gq_args
         }
     }
 
+    if (p.trace) { __syncthreads(); b200_trace_stamp(rec, 5); }
     if (p.nll) {
         // receive side of the exchange (see gs_args in b200_gemv_stream.cu)
         const int total = p.full[0].M + p.full[1].M + p.full[2].M;
@@ -328,6 +314,7 @@ int b200_launch_gemv_mma(b200_ctx * ctx, const b200_tensor * const * w, int n, c
     }
     { static int dbg = -1; if (dbg < 0) { const char * e = getenv("GGML_B200_GS_DBG"); dbg = e ? atoi(e) : 0; } p.dbg = dbg; }
     { static int npf = -1; if (npf < 0) { const char * e = getenv("GGML_B200_GQ_NPF"); npf = e ? atoi(e) : 0; } p.npf = npf; }
+    p.trace = ctx->trace; p.trace_cap = ctx->trace_cap;
     const int grid = gq_grid(ctx, G, bytes);
     p.gmax = (int) ((G + grid - 1) / grid);
     const size_t smem = gq_smem_bytes(p.K, p.gmax);

@@ -46,6 +46,8 @@ struct gs_args {
     // device and come from an earlier kernel, so in this mode the first weight fetch is issued after griddepcontrol.wait
     const int * ids; int id_base; size_t estride;
     int dbg;                                 // GGML_B200_GS_DBG (measurement only): 1 skip quantization, 2 skip the dot products, 4 no weight traffic
+    int npf;                                 // GGML_B200_GS_NPF: bytes of this warp's rows (behind the ring fill) to pull into L2 from the prologue
+    unsigned long long * trace; int trace_cap;   // b200_debug_trace (measurement only)
 };
 
 template <int TYPE> struct gs_traits;
@@ -63,13 +65,13 @@ template <> struct gs_traits<B200_TYPE_Q4_K> {
     static constexpr int BLOCK_BYTES = 144;
     static __host__ __device__ constexpr int stages(int shape) { return shape == 1 ? 4 : 3; }
     static __host__ __device__ size_t act_bytes(int K) { return (size_t) K + (size_t) (K >> 8) * 64; }
-    // 4 consecutive quants (bytes off..off+3 of q8_1 block blk32) packed in `word`; the group leader also stores (d, s)
-    static __device__ __forceinline__ void store_act(uint8_t * s_act, int K, int nblocks, int blk32, int off, unsigned word, bool leader, float d, float s) {
-        const int gb = blk32 >> 3, sub = blk32 & 7, hf = off >> 4;
-        *(unsigned *) (s_act + (sub & 1) * (K >> 1) + (((sub >> 1) * 2 + hf) * nblocks + gb) * 16 + (off & 15)) = word;
-        if (leader) {
+    // the 16 quants of half hf of q8_1 block blk32 (one 16-byte unit); the first half also stores the block's (d, s)
+    static __device__ __forceinline__ void store_unit(uint8_t * s_act, int K, int nblocks, int blk32, int hf, int4 w, float d, float s) {
+        const int gb = blk32 >> 3, sub = blk32 & 7;
+        *(int4 *) (s_act + (sub & 1) * (K >> 1) + (((sub >> 1) * 2 + hf) * nblocks + gb) * 16) = w;
+        if (hf == 0) {
             float * ds = (float *) (s_act + K) + ((sub >> 1) * nblocks + gb) * 4 + (sub & 1) * 2;
-            ds[0] = (sub & 1) ? d * 0.0625f : d; ds[1] = s;
+            *(float2 *) ds = make_float2((sub & 1) ? d * 0.0625f : d, s);
         }
     }
     template <int NR>
@@ -126,10 +128,10 @@ template <> struct gs_traits<B200_TYPE_Q6_K> {
     static constexpr int BLOCK_BYTES = 210;
     static __host__ __device__ constexpr int stages(int shape) { return shape == 1 ? 3 : 2; }
     static __host__ __device__ size_t act_bytes(int K) { return (size_t) K + (size_t) (K >> 8) * 32; }
-    static __device__ __forceinline__ void store_act(uint8_t * s_act, int K, int nblocks, int blk32, int off, unsigned word, bool leader, float d, float s) {
-        const int gb = blk32 >> 3, sub = blk32 & 7, n = sub >> 2, g = sub & 3, hf = off >> 4;
-        *(unsigned *) (s_act + ((g * 4 + n * 2 + hf) * nblocks + gb) * 16 + (off & 15)) = word;
-        if (leader) ((float *) (s_act + K))[(n * nblocks + gb) * 4 + g] = d;
+    static __device__ __forceinline__ void store_unit(uint8_t * s_act, int K, int nblocks, int blk32, int hf, int4 w, float d, float s) {
+        const int gb = blk32 >> 3, sub = blk32 & 7, n = sub >> 2, g = sub & 3;
+        *(int4 *) (s_act + ((g * 4 + n * 2 + hf) * nblocks + gb) * 16) = w;
+        if (hf == 0) ((float *) (s_act + K))[(n * nblocks + gb) * 4 + g] = d;
         (void) s;
     }
     template <int NR>
@@ -185,10 +187,10 @@ template <> struct gs_traits<B200_TYPE_Q4_0> {
     static constexpr int BLOCK_BYTES = 144;
     static __host__ __device__ constexpr int stages(int shape) { return shape == 1 ? 4 : 3; }
     static __host__ __device__ size_t act_bytes(int K) { return (size_t) K + (size_t) (K >> 5) * 8; }
-    static __device__ __forceinline__ void store_act(uint8_t * s_act, int K, int nblocks, int blk32, int off, unsigned word, bool leader, float d, float s) {
+    static __device__ __forceinline__ void store_unit(uint8_t * s_act, int K, int nblocks, int blk32, int hf, int4 w, float d, float s) {
         const int gb = blk32 >> 3, c = blk32 & 7;
-        *(unsigned *) (s_act + (off >> 4) * (K >> 1) + (c * nblocks + gb) * 16 + (off & 15)) = word;
-        if (leader) { float * ds = (float *) (s_act + K) + (c * nblocks + gb) * 2; ds[0] = d; ds[1] = s; }
+        *(int4 *) (s_act + hf * (K >> 1) + (c * nblocks + gb) * 16) = w;
+        if (hf == 0) *(float2 *) ((float *) (s_act + K) + (c * nblocks + gb) * 2) = make_float2(d, s);
     }
     template <int NR>
     static __device__ __forceinline__ void consume(uint32_t st, int row_stride, int bl, int gb, int lane, uint32_t act, int K, int nblocks,
@@ -219,10 +221,10 @@ template <> struct gs_traits<B200_TYPE_Q8_0> {
     static constexpr int BLOCK_BYTES = 272;
     static __host__ __device__ constexpr int stages(int shape) { return shape == 1 ? 3 : 2; }
     static __host__ __device__ size_t act_bytes(int K) { return (size_t) K + (size_t) (K >> 5) * 4; }
-    static __device__ __forceinline__ void store_act(uint8_t * s_act, int K, int nblocks, int blk32, int off, unsigned word, bool leader, float d, float s) {
+    static __device__ __forceinline__ void store_unit(uint8_t * s_act, int K, int nblocks, int blk32, int hf, int4 w, float d, float s) {
         const int gb = blk32 >> 3, sub = blk32 & 7;
-        *(unsigned *) (s_act + ((sub * 2 + (off >> 4)) * nblocks + gb) * 16 + (off & 15)) = word;
-        if (leader) ((float *) (s_act + K))[sub * nblocks + gb] = d;
+        *(int4 *) (s_act + ((sub * 2 + hf) * nblocks + gb) * 16) = w;
+        if (hf == 0) ((float *) (s_act + K))[sub * nblocks + gb] = d;
         (void) s;
     }
     template <int NR>
@@ -283,6 +285,9 @@ __global__ void __launch_bounds__(SHAPE == 1 ? 256 : 384, 2) k_gemv_stream(const
     const int npairs = (rows + GS_RW - 1) / GS_RW;
     const int nitems = (p.dbg & 4) ? 0 : npairs * nchunks;
 
+    unsigned long long * rec = nullptr;
+    if (p.trace && threadIdx.x == 0) rec = b200_trace_open(p.trace, p.trace_cap, p.Mtot, p.K);
+    b200_trace_stamp(rec, 0);
     if (lane == 0) {
         for (int s = 0; s < GS_STAGES; ++s) mbar_init(bar0 + 8 * s, 1);
         mbar_fence_init();
@@ -310,64 +315,43 @@ __global__ void __launch_bounds__(SHAPE == 1 ? 256 : 384, 2) k_gemv_stream(const
     };
     const int npro = min(nitems, GS_STAGES);
     if (!p.ids) for (int i = 0; i < npro; ++i) issue(i);                  // weights do not depend on the previous kernel
+    // The rings hold ~83 KB per CTA.  Until the previous kernel has retired and the activations are quantized nothing is consumed,
+    // so nothing more is fetched and HBM idles: pull the rows behind the ring fill into L2 meanwhile (the ring refills then hit L2).
+    if (p.npf > 0 && !p.ids && lane == 0 && nitems > npro) {
+        const uint32_t rowb = (uint32_t) nblocks * T::BLOCK_BYTES;
+        int left = p.npf;
+        for (int r = prp * GS_RW; r < rows && left > 0; ++r, left -= (int) rowb) {
+            const uint8_t * w; float * dst;
+            gs_locate(p, r_begin + r, w, dst);
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(w), "r"(rowb) : "memory");
+        }
+    }
+    b200_trace_stamp(rec, 1);
 
     // src1 is produced by the previous kernel in the stream: wait for it (and its memory) before the first read
     asm volatile("griddepcontrol.wait;" ::: "memory");
+    b200_trace_stamp(rec, 2);
     unsigned ll_tag = 0;
     if (p.nll) { asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(ll_tag) : "l"(p.ctrl + 8)); ll_tag += 1u; }
     if (p.ids) for (int i = 0; i < npro; ++i) issue(i);                   // which experts: only known now
 
-    // quantize the activation column to q8_1 straight into shared memory, in lane order.  Same arithmetic as
-    // q8_1_block<B200_Q8_1_X86> (bit-exact with the reference), but 128-bit loads: a lane holds 4 consecutive values, the
-    // 8 lanes of a group hold one 32-value block, and up to GS_QB independent loads per lane are in flight at once.
+    // quantize the activation column to q8_1 straight into shared memory, in lane order (b200_quantize_column_x86: same arithmetic
+    // as q8_1_block<B200_Q8_1_X86>, bit-exact with the reference)
     if (p.dbg & 1) {
     } else if (p.aq != nullptr) {
-        // a ready q8_1 image (large K: one quantize launch instead of one quantization per CTA): permuting copy
+        // a ready q8_1 image (one quantize launch instead of one quantization per CTA): permuting copy
         const int4 * src = (const int4 *) p.aq;
         for (int j = threadIdx.x; j < (p.K >> 4); j += blockDim.x) {
             const int4 v = src[j];
-            const int blk32 = j >> 1;
-            const bool leader = (j & 1) == 0;
             float2 ds = make_float2(0.f, 0.f);
-            if (leader) ds = __half22float2(p.ads[blk32]);
-            T::store_act(s_act, p.K, nblocks, blk32, 16 * (j & 1) + 0,  (unsigned) v.x, leader, ds.x, ds.y);
-            T::store_act(s_act, p.K, nblocks, blk32, 16 * (j & 1) + 4,  (unsigned) v.y, false, 0.f, 0.f);
-            T::store_act(s_act, p.K, nblocks, blk32, 16 * (j & 1) + 8,  (unsigned) v.z, false, 0.f, 0.f);
-            T::store_act(s_act, p.K, nblocks, blk32, 16 * (j & 1) + 12, (unsigned) v.w, false, 0.f, 0.f);
+            if ((j & 1) == 0) ds = __half22float2(p.ads[j >> 1]);
+            T::store_unit(s_act, p.K, nblocks, j >> 1, j & 1, v, ds.x, ds.y);
         }
     } else {
-        constexpr int GS_QB = 8;
-        const float4 * x4 = (const float4 *) p.x;
-        const int nvec = p.K >> 7;                                        // 128-float chunks = 4 q8_1 blocks
-        for (int c0 = warp; c0 < nvec; c0 += GS_WARPS * GS_QB) {
-            float4 v[GS_QB];
-#pragma unroll
-            for (int i = 0; i < GS_QB; ++i) { const int c = c0 + i * GS_WARPS; v[i] = c < nvec ? x4[c * 32 + lane] : make_float4(0.f, 0.f, 0.f, 0.f); }
-#pragma unroll
-            for (int i = 0; i < GS_QB; ++i) {
-                const int c = c0 + i * GS_WARPS;
-                if (c >= nvec) break;                                     // warp-uniform
-                float amax = fmaxf(fmaxf(fabsf(v[i].x), fabsf(v[i].y)), fmaxf(fabsf(v[i].z), fabsf(v[i].w)));
-                amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
-                amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 2));
-                amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 4));
-                const float d  = __fdiv_rn(amax, 127.0f);
-                const float id = amax != 0.0f ? __fdiv_rn(127.0f, amax) : 0.0f;
-                const int q0 = cvt_x86(rintf(__fmul_rn(v[i].x, id))), q1 = cvt_x86(rintf(__fmul_rn(v[i].y, id)));
-                const int q2 = cvt_x86(rintf(__fmul_rn(v[i].z, id))), q3 = cvt_x86(rintf(__fmul_rn(v[i].w, id)));
-                unsigned usum = (unsigned) q0 + (unsigned) q1 + (unsigned) q2 + (unsigned) q3;   // int32 lanes summed before saturation
-                usum += __shfl_xor_sync(0xffffffffu, usum, 1);
-                usum += __shfl_xor_sync(0xffffffffu, usum, 2);
-                usum += __shfl_xor_sync(0xffffffffu, usum, 4);
-                const unsigned word = ((unsigned) max(-128, min(127, q0)) & 0xffu)        | (((unsigned) max(-128, min(127, q1)) & 0xffu) << 8) |
-                                      (((unsigned) max(-128, min(127, q2)) & 0xffu) << 16) | (((unsigned) max(-128, min(127, q3)) & 0xffu) << 24);
-                // d and s take the fp16 round trip they would take through block_q8_1
-                T::store_act(s_act, p.K, nblocks, c * 4 + (lane >> 3), 4 * (lane & 7), word, (lane & 7) == 0,
-                             __half2float(__float2half_rn(d)), __half2float(__float2half_rn(__fmul_rn(d, (float) (int) usum))));
-            }
-        }
+        b200_quantize_column_x86(p.x, p.K, [&](int blk32, int hf, int4 w, float d, float sm) { T::store_unit(s_act, p.K, nblocks, blk32, hf, w, d, sm); });
     }
     __syncthreads();
+    b200_trace_stamp(rec, 3);
 
     const int bl = lane & 7;
     const uint32_t act = smem_u32(s_act);
@@ -380,6 +364,7 @@ __global__ void __launch_bounds__(SHAPE == 1 ? 256 : 384, 2) k_gemv_stream(const
         const int cb = min(GS_CB, nblocks - kc * GS_CB);
         const int nr = min(GS_RW, rows - rp * GS_RW);
         mbar_wait(bar0 + 8 * stage, (uint32_t) phase);
+        if (item == 0) b200_trace_stamp(rec, 4);
         if (bl < cb && !(p.dbg & 2)) {
             const uint32_t st = ring + stage * STAGE_BYTES;
             const int gb = kc * GS_CB + bl;
@@ -409,8 +394,11 @@ __global__ void __launch_bounds__(SHAPE == 1 ? 256 : 384, 2) k_gemv_stream(const
             kc = 0; ++rp;
         } else ++kc;
         if (++stage == GS_STAGES) { stage = 0; phase ^= 1; }
+        if (item == 0) b200_trace_stamp(rec, 9);                            // warp 0: first item done
     }
+    b200_trace_stamp(rec, 6);                                             // warp 0: all its items done
 
+    if (p.trace) { __syncthreads(); b200_trace_stamp(rec, 5); }
     if (p.nll) {
         // receive side of the exchange (see gs_args)
         const int total = p.full[0].M + p.full[1].M + p.full[2].M;
@@ -557,6 +545,8 @@ int b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n
         for (int i = 0; i < n; ++i) { p.full[i].dst = peers->full[i]; p.full[i].M = peers->full_m[i]; }
     }
     { static int dbg = -1; if (dbg < 0) { const char * e = getenv("GGML_B200_GS_DBG"); dbg = e ? atoi(e) : 0; } p.dbg = dbg; }
+    { static int npf = -1; if (npf < 0) { const char * e = getenv("GGML_B200_GS_NPF"); npf = e ? atoi(e) : 0; } p.npf = npf; }
+    p.trace = ctx->trace; p.trace_cap = ctx->trace_cap;
     p.nseg = n; p.Mtot = 0; p.x = (const float *) x->data; p.K = (int) w[0]->ne[0];
     p.aq = (const int8_t *) image; p.ads = image ? (const __half2 *) ((const int8_t *) image + p.K) : nullptr;
     if (image && idm && idm->ads) p.ads = (const __half2 *) idm->ads;

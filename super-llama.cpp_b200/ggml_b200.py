@@ -64,6 +64,7 @@ def lib():
         "b200_ctx_profile_get": (i, [vp, i, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]),
         "b200_event_create": (vp, []), "b200_event_destroy": (i, [vp]), "b200_event_record": (i, [vp, vp]),
         "b200_event_elapsed_ms": (i, [vp, vp, C.POINTER(f)]),
+        "b200_debug_trace": (i, [vp, vp, i]),
         "b200_graph_begin": (i, [vp]), "b200_graph_end": (vp, [vp]), "b200_graph_launch": (i, [vp, vp]), "b200_graph_destroy": (i, [vp]),
         "b200_split_row_range": (i, [i64, vp, i, i, i64, C.POINTER(i64), C.POINTER(i64)]),
         "b200_peer_handle": (i, [vp, vp, vp]), "b200_peer_open": (i, [vp, vp, C.POINTER(vp)]), "b200_peer_close": (i, [vp, vp]),

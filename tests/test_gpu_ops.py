@@ -79,6 +79,56 @@ def test_q8_1_strided_rows_and_empty(ctx, B, orc):
         ctx.quantize_q8_1(dx.ptr, dy.ptr, 100, 1)                                      # k % 32 != 0
 
 
+@pytest.mark.parametrize("K", [1024, 4096, 14336])
+@pytest.mark.parametrize("mma", [False, True])
+def test_q8_1_fused_in_gemv_bit_exact_probe(ctx, B, orc, K, mma, monkeypatch):
+    """The decode GEMV quantizes its activation column itself (b200_quantize_column_x86).  Probe weights read the quantized
+    column back through MUL_MAT exactly: a q8_0 row holding a single 1 (d = 1) returns d_a * q_a of one element, a q4_0 row of
+    zero nibbles with d = 1 on one block returns -8 * s of that block; both must equal the reference's quantize_row_q8_1
+    bit for bit, special blocks (zeros, denormal amax, ties) included."""
+    rng = np.random.default_rng(K)
+    x = (rng.standard_normal(K) * 10.0 ** rng.integers(-4, 4, K // 32).repeat(32)).astype(np.float32)
+    x[:32] = 0.0
+    x[32:64] = 1e-40                                               # denormal amax: id = inf, quants become the x86 "integer indefinite"
+    x[64:96] = 1000.0
+    x[96:128] = np.round(x[96:128] * 2) / 2 + 0.5                  # exact .5 ties
+    x[128:160] = -1.0
+    x[192:224] = -x[160:192]
+    q = orc.quantize_q8_1(x[None, :], 0).reshape(-1, 36)
+    d = q[:, 0:2].copy().view(np.float16).astype(np.float32).reshape(-1)
+    sm = q[:, 2:4].copy().view(np.float16).astype(np.float32).reshape(-1)
+    qa = q[:, 4:].view(np.int8).astype(np.float32)
+    one = np.float16(1.0).view(np.uint16)
+    dx = ctx.upload(B.F32, [K, 1], x)
+    with np.errstate(invalid="ignore", over="ignore"):
+        want_dq = (d[:, None] * qa).reshape(-1)                        # element probe
+        want_s = np.float32(-8.0) * sm                                  # block probe
+    # q8_0 element probe: row r = weight 1 at position r
+    w8 = np.zeros((K, K // 32, 34), dtype=np.uint8)
+    r = np.arange(K)
+    w8[r, r // 32, 0:2] = np.array([one], dtype=np.uint16).view(np.uint8)
+    w8[r, r // 32, 2 + r % 32] = 1
+    w4 = np.zeros((K // 32, K // 32, 18), dtype=np.uint8)              # q4_0 block probe: row b = d = 1 on block b, nibbles 0 (value -8)
+    b = np.arange(K // 32)
+    w4[b, b, 0:2] = np.array([one], dtype=np.uint16).view(np.uint8)
+    for t, w, M, want in ((O.Q8_0, w8, K, want_dq), (O.Q4_0, w4, K // 32, want_s)):
+        dw = ctx.upload(t, [K, M], w.reshape(-1)); ctx.repack(dw)
+        dd = ctx.empty(B.F32, [M, 1])
+        ctx.mul_mat(dw, dx, dd)
+        got = ctx.download(dd).reshape(-1)
+        assert np.isfinite(want).all()                                 # (an inf scale would poison every row through 0 * inf)
+        assert np.array_equal(got, want), (t, np.nonzero(got != want)[0][:8], got[got != want][:4], want[got != want][:4])
+    if mma:                                                            # the tensor-core GEMV has its own copy of the fused quantizer: q4_K probe
+        M = 64
+        w = O.random_blocks(rng, O.Q4_K, K, M)
+        xs = np.where(np.isfinite(x), x, 0.0).astype(np.float32); xs[32:96] = 0.25
+        dxs = ctx.upload(B.F32, [K, 1], xs)
+        dw = ctx.upload(O.Q4_K, [K, M], w); dd = ctx.empty(B.F32, [M, 1])
+        ctx.mul_mat(dw, dxs, dd)
+        got = ctx.download(dd).reshape(1, 1, 1, M)
+        assert O.nmse(orc.mul_mat(O.Q4_K, w, K, M, xs[None, :], 1, act=O.ACT_Q8_1), got) < 1e-9
+
+
 # ---- MUL_MAT ------------------------------------------------------------------------------------------
 def _check_mm(orc, got, t, w, K, M, x, N, want_cpu=None, **bc):
     exact = orc.mul_mat(t, w, K, M, x, N, act=O.ACT_Q8_1, **bc)
