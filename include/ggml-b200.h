@@ -82,6 +82,9 @@ B200_API uint64_t     b200_ctx_launch_count(const b200_ctx * ctx);   // kernels 
 // The ctx keeps the q8_1 image of the last quantized activation tensor so that matmuls sharing src1 (wq/wk/wv, gate/up)
 // quantize it once.  Writes made through this API invalidate it; call this after writing activations by other means.
 B200_API int          b200_ctx_invalidate(b200_ctx * ctx);
+/* tell the context that [ptr, ptr + nbytes) was written by something other than this API (a glue kernel of the caller):
+ * cached activation images / mask tile flags derived from that memory are dropped */
+B200_API int          b200_ctx_note_write(b200_ctx * ctx, const void * ptr, size_t nbytes);
 
 // ---- measurement helpers (bench.py): CUDA events on the ctx stream, per-kernel-kind event profile, CUDA graphs ----
 // kernel kinds: 0 quantize_q8_1, 1 gemv, 2 gemv_id, 3 gemm, 4 fattn, 5 fattn_combine, 6 matmul_float, 7 glue, 8 mmid_sort, 9 convert

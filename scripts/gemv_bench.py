@@ -20,7 +20,7 @@ def blocks(rng, t, n):
     return raw.reshape(-1)
 
 ap = argparse.ArgumentParser(); ap.add_argument("--types", default="q4_K,q6_K"); ap.add_argument("--n", type=int, default=1)
-ap.add_argument("--iters", type=int, default=200); ap.add_argument("--ncu", action="store_true"); ap.add_argument("--shapes", default="")
+ap.add_argument("--iters", type=int, default=200); ap.add_argument("--same", action="store_true", help="one weight buffer: L2-resident weights (126 MB L2)"); ap.add_argument("--ncu", action="store_true"); ap.add_argument("--shapes", default="")
 a = ap.parse_args()
 ctx = B.Context(0); rng = np.random.default_rng(0); out = []
 shapes = [tuple(int(v) for v in s.split("x")) for s in a.shapes.split(",")] if a.shapes else SH
@@ -28,7 +28,7 @@ for tn in a.types.split(","):
     t = T[tn]
     for K, M in shapes:
         wb = K // B.BLCK[t] * B.TSIZE[t] * M
-        nbuf = 2 if a.ncu else max(2, min(64, int(400e6 // wb) + 1))
+        nbuf = 1 if a.same else 2 if a.ncu else max(2, min(64, int(400e6 // wb) + 1))
         pool = blocks(rng, t, min(wb // B.TSIZE[t], 1 << 18))
         ws = []
         for _ in range(nbuf):
@@ -43,12 +43,12 @@ for tn in a.types.split(","):
         for i in range(iters): ctx.mul_mat(ws[i % nbuf], x, d)
         prof = ctx.profile_get(); ctx.profile(False)
         ctx.graph_begin()
-        for i in range(nbuf): ctx.mul_mat(ws[i], x, d)
-        g = ctx.graph_end(); ctx.graph_launch(g); ctx.synchronize()
-        e0, e1 = ctx.event(), ctx.event(); reps = max(1, iters // nbuf)
+        for i in range(max(nbuf, 8)): ctx.note_write(x); ctx.mul_mat(ws[i % nbuf], x, d)
+        g = ctx.graph_end(); nrep = max(nbuf, 8); ctx.graph_launch(g); ctx.synchronize()
+        e0, e1 = ctx.event(), ctx.event(); reps = max(1, iters // max(nbuf, 8))
         ctx.record(e0)
         for _ in range(reps): ctx.graph_launch(g)
-        ctx.record(e1); ms = ctx.elapsed_ms(e0, e1) / (reps * nbuf)
+        ctx.record(e1); ms = ctx.elapsed_ms(e0, e1) / (reps * nrep)
         kern = {k: v[0] / v[1] * 1e3 for k, v in prof.items()}
         gbs = wb / (ms * 1e-3) / 1e9
         if a.n > 8: print(f"      n={a.n}: {2.0 * M * K * a.n / (ms * 1e-3) / 1e12:8.1f} TFLOP/s", flush=True)

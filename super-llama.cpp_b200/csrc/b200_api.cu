@@ -182,6 +182,7 @@ void b200_note_write(b200_ctx * ctx, const void * ptr, size_t nbytes) {
     if (ctx->qcache.valid) { const char * a = (const char *) ctx->qcache.data; if (b < a + ctx->qcache.span && a < b + nbytes) ctx->qcache.valid = 0; }
     if (ctx->mcache.valid) { const char * a = (const char *) ctx->mcache.data; if (b < a + ctx->mcache.span && a < b + nbytes) ctx->mcache.valid = 0; }
 }
+extern "C" int b200_ctx_note_write(b200_ctx * ctx, const void * ptr, size_t nbytes) { b200_note_write(ctx, ptr, nbytes); return B200_OK; }
 extern "C" int b200_ctx_invalidate(b200_ctx * ctx) { ctx->qcache.valid = 0; ctx->mcache.valid = 0; return B200_OK; }
 
 // largest K whose activation column every GEMV CTA quantizes itself; above it one quantize launch writes an image (GGML_B200_FUSED_QUANT_MAX_K)

@@ -165,22 +165,33 @@ static __device__ __forceinline__ void q8_1_block(float v, int & q, float & d, i
 // one for the sum and the 16 conversions of a lane are independent instructions (the 8-lanes-per-block form spent ~2000 cycles per
 // CTA in shuffle / division latency chains, measured with b200_debug_trace).  Rounds are double-buffered: the next round's loads are
 // in flight while this one converts.  store(blk32, hf, quants, d, s): hf = which half of block blk32, d and s after their fp16 round trip.
-template <class F>
-static __device__ __forceinline__ void b200_quantize_column_x86(const float * x, int K, F store) {
+struct b200_no_hook { __device__ __forceinline__ void operator()() const {} };
+// after_loads() runs once, right after the first round of loads has been issued (a place to start bulk traffic BEHIND them)
+template <class F, class H = b200_no_hook>
+static __device__ __forceinline__ void b200_quantize_column_x86(const float * x, int K, F store, unsigned long long * rec = nullptr, H after_loads = H()) {
     const int nunits = K >> 4, lane = threadIdx.x & 31;
     const float4 * x4 = (const float4 *) x;
+    // every CTA of the grid reads the same small column while gigabytes of weights stream through L2 (evict_first): ask L2 to keep it
+    uint64_t keep;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(keep));
+    auto ldx = [&](int i) {
+        float4 r;
+        asm volatile("ld.global.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(x4 + i), "l"(keep));
+        return r;
+    };
     int base = (int) (threadIdx.x & ~31u);                               // warp-uniform; K % 32 == 0 keeps lane pairs together
     float4 v[4];
     if (base < nunits) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) v[j] = base + lane < nunits ? x4[(base + lane) * 4 + j] : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int j = 0; j < 4; ++j) v[j] = base + lane < nunits ? ldx((base + lane) * 4 + j) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
+    after_loads();
     while (base < nunits) {
         const int u = base + lane, nb = base + (int) blockDim.x;
         float4 nx[4];
         if (nb < nunits) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) nx[j] = nb + lane < nunits ? x4[(nb + lane) * 4 + j] : make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int j = 0; j < 4; ++j) nx[j] = nb + lane < nunits ? ldx((nb + lane) * 4 + j) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
         const float f[16] = { v[0].x, v[0].y, v[0].z, v[0].w, v[1].x, v[1].y, v[1].z, v[1].w, v[2].x, v[2].y, v[2].z, v[2].w, v[3].x, v[3].y, v[3].z, v[3].w };
         // amax over the |bit patterns| as integers: same order as the floats, and a NaN input shows up as amax > inf
@@ -189,6 +200,7 @@ static __device__ __forceinline__ void b200_quantize_column_x86(const float * x,
         for (int i = 0; i < 8; ++i) ab[i] = max(__float_as_uint(f[2 * i]) & 0x7fffffffu, __float_as_uint(f[2 * i + 1]) & 0x7fffffffu);
         unsigned abits = max(max(max(ab[0], ab[1]), max(ab[2], ab[3])), max(max(ab[4], ab[5]), max(ab[6], ab[7])));
         abits = max(abits, __shfl_xor_sync(0xffffffffu, abits, 1));
+        if (rec && abits != 0xffffffffu) b200_trace_stamp(rec, 8);         // (measurement only) the column's first loads have landed
         const bool  nan_in = abits > 0x7f800000u;
         // NaN inputs never win the reference's amax search (`a > amax` from 0, oracle/ggml_oracle.c): largest non-NaN magnitude, rare path
         float amax = __uint_as_float(abits);
@@ -275,7 +287,7 @@ bool b200_gemv_mma_supported(const b200_ctx * ctx, const b200_tensor * const * w
 int  b200_launch_gemv_mma(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, const void * image, float * const * dst,
                           const b200_rowsplit_peers * peers);
 int  b200_launch_exchange_unpack(b200_ctx * ctx, const void * ll, float * dst, int64_t M, unsigned * ctrl);
-#define B200_GEMV_FUSED_QUANT_MAX_K 8192    // above this, one quantize launch + image beats one quantization per CTA
+#define B200_GEMV_FUSED_QUANT_MAX_K 16384   // above this, one quantize launch + image beats one quantization per CTA
 #define B200_GEMV_MAX_COLS 8
 bool b200_gemm_supported(const b200_tensor * w, const b200_tensor * x);
 int  b200_launch_gemm_q(b200_ctx * ctx, const b200_tensor * w, const void * image, int64_t N, b200_tensor * dst);   // image: bf16 [N][K]

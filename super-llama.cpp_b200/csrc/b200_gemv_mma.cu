@@ -38,6 +38,7 @@ struct gq_args {
     struct { float * dst; int M; } full[GQ_MAXSEG];
     int dbg;
     int npf;                                                            // items per warp to prefetch into L2 behind the ring fill
+    int npre;                                                           // ring stages to fill before the dependency wait
     unsigned long long * trace; int trace_cap;                          // b200_debug_trace (measurement only)
 };
 struct gq_maps { CUtensorMap m[GQ_MAXSEG]; };
@@ -54,11 +55,14 @@ static __device__ __forceinline__ void mma_u8s8(int (&c)[4], unsigned a0, unsign
                  : "+r"(c[0]), "+r"(c[1]), "+r"(c[2]), "+r"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 
-__global__ void __launch_bounds__(GQ_WARPS * 32, 2) k_gemv_q4k_mma(const gq_args p, const __grid_constant__ gq_maps maps) {
+// NW = 12: two CTAs per SM (this kernel's, or this and the PDL-launched next one); NW = 24: ONE CTA per SM for long streams -- the same
+// warps per SM, but the activation column is fetched and quantized once per SM (L2 broadcast bandwidth, see b200_gemv_stream.cu BIG)
+template <int NW>
+__global__ void __launch_bounds__(NW * 32, NW == 24 ? 1 : 2) k_gemv_q4k_mma(const gq_args p, const __grid_constant__ gq_maps maps) {
     extern __shared__ __align__(128) uint8_t smem[];
-    // layout: [GQ_WARPS][GQ_STAGES][2304] rings | q8 quants [K] | (d, s) float2 [K/32] | partial sums [gmax][nchunks][8] | mbarriers
+    // layout: [NW][GQ_STAGES][2304] rings | q8 quants [K] | (d, s) float2 [K/32] | partial sums [gmax][nchunks][8] | mbarriers
     const int nblocks = p.K >> 8, nchunks = (nblocks + 1) >> 1;
-    uint8_t *  s_q   = smem + GQ_WARPS * GQ_STAGES * GQ_STAGE_BYTES;
+    uint8_t *  s_q   = smem + NW * GQ_STAGES * GQ_STAGE_BYTES;
     float2 *   s_ds  = (float2 *) (s_q + p.K);
     float *    s_par = (float *) (s_ds + (p.K >> 5));
     uint64_t * s_bar = (uint64_t *) (s_par + (size_t) p.gmax * nchunks * GQ_ROWS);
@@ -81,28 +85,34 @@ __global__ void __launch_bounds__(GQ_WARPS * 32, 2) k_gemv_q4k_mma(const gq_args
         mbar_fence_init();
     }
     __syncwarp();
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");      // the next kernel may start its prologue (PDL)
+    if (p.dbg & 8) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");      // (old placement of the PDL trigger)
 
     const uint64_t policy = l2_policy_evict_first();
-    int pit = warp;                                                       // producer cursor: next item of this warp to fetch
+    int pit = warp, pgl = warp / nchunks, pch = warp - pgl * nchunks;     // producer cursor: next item of this warp to fetch = (group, chunk)
     auto issue = [&](int stage) {
         if (lane == 0) {
-            const int gl = pit / nchunks, ch = pit - gl * nchunks;
-            int gg = g_lo + gl, s = 0;
+            int gg = g_lo + pgl, s = 0;
             if (gg >= G0) { gg -= G0; s = 1; if (gg >= G1) { gg -= G1; s = 2; } }
             const uint32_t bar = bar0 + 8 * stage;
             mbar_arrive_expect_tx(bar, GQ_STAGE_BYTES);
-            tma_load_2d_hint(ring + stage * GQ_STAGE_BYTES, &maps.m[s], ch * (GQ_CHUNK / 4), gg * GQ_ROWS, bar, policy);
+            tma_load_2d_hint(ring + stage * GQ_STAGE_BYTES, &maps.m[s], pch * (GQ_CHUNK / 4), gg * GQ_ROWS, bar, policy);
         }
-        pit += GQ_WARPS;
+        pit += NW; pch += NW;
+        while (pch >= nchunks) { pch -= nchunks; ++pgl; }
     };
-    for (int i = 0; i < GQ_STAGES && pit < nitems_cta; ++i) issue(i);    // weights do not depend on the previous kernel
+    // weights do not depend on the previous kernel: fill the ring before the dependency wait.  Small matrices (the whole matrix fits the
+    // rings: p.npre = 1) fetch only one stage now and the rest BEHIND the activation loads, which otherwise queue up behind ~80 KB of
+    // ring fill per CTA (measured: wait -> quantized 3800 -> 2900 cycles, qkv 6.9 -> 5.3 us); long streams need the early start more
+    const int npre = p.npre;
+    int nfilled = 0;
+    for (; nfilled < npre && pit < nitems_cta; ++nfilled) issue(nfilled);
+    auto fill_rest = [&]() { for (; nfilled < GQ_STAGES && pit < nitems_cta; ++nfilled) issue(nfilled); };
     // The rings hold ~83 KB per CTA; the activations only exist once the previous kernel has retired and are then quantized
     // (~3 us in all) with nothing consuming, so HBM would idle.  Keep it busy: pull this warp's next items into L2 meanwhile
     // (126 MB); the ring refills then hit L2.
     if (lane == 0) {
         int it = pit;
-        for (int i = 0; i < p.npf && it < nitems_cta; ++i, it += GQ_WARPS) {
+        for (int i = 0; i < p.npf && it < nitems_cta; ++i, it += NW) {
             const int gl = it / nchunks, ch = it - gl * nchunks;
             int gg = g_lo + gl, s = 0;
             if (gg >= G0) { gg -= G0; s = 1; if (gg >= G1) { gg -= G1; s = 2; } }
@@ -121,13 +131,16 @@ __global__ void __launch_bounds__(GQ_WARPS * 32, 2) k_gemv_q4k_mma(const gq_args
     } else if (p.aq != nullptr) {
         const int4 * src = (const int4 *) p.aq;
         for (int j = threadIdx.x; j < (p.K >> 4); j += blockDim.x) ((int4 *) s_q)[j] = src[j];
-        for (int j = threadIdx.x; j < (p.K >> 5); j += blockDim.x) s_ds[j] = __half22float2(p.ads[j]);
+        for (int j = threadIdx.x; j < (p.K >> 5); j += blockDim.x) { float2 v = __half22float2(p.ads[j]); if (j & 1) v.x *= 0.0625f; s_ds[j] = v; }
     } else {
         b200_quantize_column_x86(p.x, p.K, [&](int blk32, int hf, int4 w, float d, float sm) {
             ((int4 *) s_q)[blk32 * 2 + hf] = w;
-            if (hf == 0) s_ds[blk32] = make_float2(d, sm);
-        });
+            if (hf == 0) s_ds[blk32] = make_float2((blk32 & 1) ? d * 0.0625f : d, sm);   // odd sub-blocks meet unshifted high nibbles (16 x)
+        }, rec, fill_rest);
     }
+    fill_rest();
+    // the next kernel may start its prologue (PDL) only now that our activation loads have landed (see b200_gemv_stream.cu)
+    if (!(p.dbg & 8)) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     __syncthreads();
     b200_trace_stamp(rec, 3);
 
@@ -135,35 +148,46 @@ __global__ void __launch_bounds__(GQ_WARPS * 32, 2) k_gemv_q4k_mma(const gq_args
     const uint32_t q_sm = smem_u32(s_q) + lane * 8, ds_sm = smem_u32(s_ds) + t * 16;
     const int sh = 16 * (t & 1);
     int stage = 0, phase = 0;
-    for (int it = warp; it < nitems_cta; it += GQ_WARPS) {
-        const int gl = it / nchunks, ch = it - gl * nchunks;
+    int gl = warp / nchunks, ch = warp - gl * nchunks;
+    // B operand masks: MMA pp only keeps activation columns 2pp, 2pp+1 (this lane feeds column g), so the four MMAs of a block can
+    // accumulate into ONE C fragment and lane (g, t) finds its two sums in c[0] (row g, column 2t) and c[3] (row g+8, column 2t+1)
+    const unsigned bm0 = (g >> 1) == 0 ? 0xFFFFFFFFu : 0u, bm1 = (g >> 1) == 1 ? 0xFFFFFFFFu : 0u,
+                   bm2 = (g >> 1) == 2 ? 0xFFFFFFFFu : 0u, bm3 = (g >> 1) == 3 ? 0xFFFFFFFFu : 0u;
+    // get_scale_min_k4 (ggml-quants.c:703-710) for sub-blocks j = 2t, 2t+1, two bytes at a time, with lane-constant selectors so that the
+    // decode is branch-free: j < 4 (t < 2): bytes j of scales[0..3] / [4..7]; j >= 4: low / high nibbles of scales[8..11] plus the top
+    // two bits of the bytes above
+    const bool     hi4 = t >= 2;
+    const unsigned mA = hi4 ? 0x0F0Fu : 0x3F3Fu, mB = hi4 ? 0x3030u : 0u;
+    const int      shm = hi4 ? sh + 4 : sh;
+    for (int it = warp; it < nitems_cta; it += NW) {
         mbar_wait(bar0 + 8 * stage, (uint32_t) phase);
-        if (it == 0) b200_trace_stamp(rec, 4);
         float acc = 0.0f;
-        if (!(p.dbg & 2)) {
+        {
             const uint32_t row = ring + stage * GQ_STAGE_BYTES + g * GQ_CHUNK;
 #pragma unroll
             for (int b = 0; b < 2; ++b) {
                 const int blk = ch * 2 + b;
-                if (blk >= nblocks) break;                                // warp-uniform (odd block count: the box tail is zero fill)
+                if (b && blk >= nblocks) break;                           // warp-uniform (odd block count: the box tail is zero fill)
                 const uint32_t rb = row + b * 144;
                 const int4 hdr = lds128(rb);                              // d | dmin, scales[12]
                 const int2 bq  = lds64(q_sm + blk * 256);
-                int c[4][4];
-#pragma unroll
-                for (int pp = 0; pp < 4; ++pp) {
-                    c[pp][0] = c[pp][1] = c[pp][2] = c[pp][3] = 0;
-                    const int2 w = lds64(rb + 16 + 32 * pp + 8 * t);
-                    mma_u8s8(c[pp], (unsigned) w.x & 0x0F0F0F0Fu, ((unsigned) w.x >> 4) & 0x0F0F0F0Fu,
-                                    (unsigned) w.y & 0x0F0F0F0Fu, ((unsigned) w.y >> 4) & 0x0F0F0F0Fu, (unsigned) bq.x, (unsigned) bq.y);
-                }
-                const int ilo = t == 0 ? c[0][0] : t == 1 ? c[1][0] : t == 2 ? c[2][0] : c[3][0];
-                const int ihi = t == 0 ? c[0][3] : t == 1 ? c[1][3] : t == 2 ? c[2][3] : c[3][3];
-                // get_scale_min_k4 (ggml-quants.c:703-710) for sub-blocks j = 2t, 2t+1: two bytes at a time
-                const unsigned a1 = ((unsigned) hdr.y >> sh) & 0xFFFFu, a2 = ((unsigned) hdr.z >> sh) & 0xFFFFu, a3 = ((unsigned) hdr.w >> sh) & 0xFFFFu;
-                const unsigned sc2 = t < 2 ? (a1 & 0x3F3Fu) : ((a3 & 0x0F0Fu) | ((a1 >> 2) & 0x3030u));
-                const unsigned m2  = t < 2 ? (a2 & 0x3F3Fu) : (((a3 >> 4) & 0x0F0Fu) | ((a2 >> 2) & 0x3030u));
-                const int4 dsi = lds128(ds_sm + blk * 64);                // dA(2t), s(2t), dA(2t+1), s(2t+1)
+                int c[4] = { 0, 0, 0, 0 };
+                // A rows 0-7 take the bytes as they are (lo + 16 hi), rows 8-15 the high nibbles in place (16 hi): with the masked B
+                // operand c[0] = sum (lo + 16 hi) a(2t), c[2] = sum 16 hi a(2t), c[3] = sum 16 hi a(2t+1); the 16 x is undone by the
+                // activation scale of odd sub-blocks
+                { const int2 w = lds64(rb + 16 + 8 * t);
+                  mma_u8s8(c, (unsigned) w.x, (unsigned) w.x & 0xF0F0F0F0u, (unsigned) w.y, (unsigned) w.y & 0xF0F0F0F0u, (unsigned) bq.x & bm0, (unsigned) bq.y & bm0); }
+                { const int2 w = lds64(rb + 48 + 8 * t);
+                  mma_u8s8(c, (unsigned) w.x, (unsigned) w.x & 0xF0F0F0F0u, (unsigned) w.y, (unsigned) w.y & 0xF0F0F0F0u, (unsigned) bq.x & bm1, (unsigned) bq.y & bm1); }
+                { const int2 w = lds64(rb + 80 + 8 * t);
+                  mma_u8s8(c, (unsigned) w.x, (unsigned) w.x & 0xF0F0F0F0u, (unsigned) w.y, (unsigned) w.y & 0xF0F0F0F0u, (unsigned) bq.x & bm2, (unsigned) bq.y & bm2); }
+                { const int2 w = lds64(rb + 112 + 8 * t);
+                  mma_u8s8(c, (unsigned) w.x, (unsigned) w.x & 0xF0F0F0F0u, (unsigned) w.y, (unsigned) w.y & 0xF0F0F0F0u, (unsigned) bq.x & bm3, (unsigned) bq.y & bm3); }
+                const int ilo = c[0] - c[2], ihi = c[3];
+                const unsigned xs = hi4 ? (unsigned) hdr.w : (unsigned) hdr.y, xm = hi4 ? (unsigned) hdr.w : (unsigned) hdr.z;
+                const unsigned sc2 = ((xs >> sh) & mA)  | (((unsigned) hdr.y >> (sh + 2)) & mB);
+                const unsigned m2  = ((xm >> shm) & mA) | (((unsigned) hdr.z >> (sh + 2)) & mB);
+                const int4 dsi = lds128(ds_sm + blk * 64);                // dA(2t), s(2t), dA(2t+1) / 16, s(2t+1)
                 const float4 ds = make_float4(__int_as_float(dsi.x), __int_as_float(dsi.y), __int_as_float(dsi.z), __int_as_float(dsi.w));
                 const float2 dm = make_float2(__half2float(__ushort_as_half((unsigned short) ((unsigned) hdr.x & 0xFFFFu))),
                                               __half2float(__ushort_as_half((unsigned short) ((unsigned) hdr.x >> 16))));
@@ -178,7 +202,8 @@ __global__ void __launch_bounds__(GQ_WARPS * 32, 2) k_gemv_q4k_mma(const gq_args
         acc += __shfl_xor_sync(0xffffffffu, acc, 2);
         if (t == 0) s_par[(gl * nchunks + ch) * GQ_ROWS + g] = acc;
         if (++stage == GQ_STAGES) { stage = 0; phase ^= 1; }
-        if (it == warp) b200_trace_stamp(rec, 9);                           // warp 0: first item done
+        ch += NW;
+        while (ch >= nchunks) { ch -= nchunks; ++gl; }
     }
     b200_trace_stamp(rec, 6);                                             // warp 0: all its items done
     __syncthreads();
@@ -239,15 +264,25 @@ typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32
                                     CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 encode_tiled_fn b200_get_encode_tiled();
 
-static size_t gq_smem_bytes(int K, int gmax) {
+static size_t gq_smem_bytes(int K, int gmax, int nw = GQ_WARPS) {
     const int nchunks = ((K >> 8) + 1) >> 1;
-    return (size_t) GQ_WARPS * GQ_STAGES * GQ_STAGE_BYTES + (size_t) K + (size_t) (K >> 5) * 8 + (size_t) gmax * nchunks * GQ_ROWS * 4 + GQ_WARPS * GQ_STAGES * 8;
+    return (size_t) nw * GQ_STAGES * GQ_STAGE_BYTES + (size_t) K + (size_t) (K >> 5) * 8 + (size_t) gmax * nchunks * GQ_ROWS * 4 + nw * GQ_STAGES * 8;
 }
+#define GQ_SMEM_MAX_BIG (200 * 1024)           // the 24-warp shape owns the SM
 #define GQ_SMEM_MAX (113 * 1024)               // two CTAs (this kernel's, or this and the PDL-launched next one) per SM
 
-static int gq_grid(const b200_ctx * ctx, int64_t G, size_t bytes) {
-    static const int per_sm = getenv("GGML_B200_GQ_CTAS") ? atoi(getenv("GGML_B200_GQ_CTAS")) : 0;
-    const int64_t cap = (int64_t) ctx->sm_count * (per_sm ? per_sm : bytes > ((size_t) 24 << 20) ? 2 : 1);
+// long streams (> 24 MB) take every warp slot we can register-wise fill: two 12-warp CTAs per SM, or (default) one 24-warp CTA
+static bool gq_big(size_t bytes, int K, int64_t G, const b200_ctx * ctx) {
+    static const int want = getenv("GGML_B200_GQ_BIG") ? atoi(getenv("GGML_B200_GQ_BIG")) : 0;         // measured slower than two 12-warp CTAs: opt-in
+    if (!want || bytes <= ((size_t) 24 << 20)) return false;
+    const int64_t grid = G < ctx->sm_count ? G : ctx->sm_count;
+    return gq_smem_bytes(K, (int) ((G + grid - 1) / grid), 24) <= GQ_SMEM_MAX_BIG;
+}
+static int gq_grid(const b200_ctx * ctx, int64_t G, size_t bytes, bool big) {
+    // two CTAs per SM for every size (measured: 24 warps per SM beat one CTA + the next kernel's co-resident prologue, wo 5.0 -> 4.1 us)
+    static const int per_sm = getenv("GGML_B200_GQ_CTAS") ? atoi(getenv("GGML_B200_GQ_CTAS")) : 2;
+    (void) bytes;
+    const int64_t cap = (int64_t) ctx->sm_count * (big ? 1 : per_sm);
     return (int) (G < cap ? G : cap);
 }
 
@@ -265,10 +300,12 @@ bool b200_gemv_mma_supported(const b200_ctx * ctx, const b200_tensor * const * w
     }
     const int64_t K = w[0]->ne[0];
     if (K % 256 != 0 || K < 512 || K > 32768 || G < 1) return false;
-    if (mode < 0 && bytes < ((size_t) 48 << 20)) return false;
+    if (mode < 0 && bytes < ((size_t) 48 << 20) && K > 8192) return false;   // (measured: the dp4a kernel is as quick on mid-size matrices with long rows)
     if (x->type != B200_TYPE_F32 || x->nb[0] != 4 || ((uintptr_t) x->data & 15) || x->ne[1] != 1 || x->ne[2] != 1 || x->ne[3] != 1) return false;
-    const int grid = gq_grid(ctx, G, bytes);
-    return gq_smem_bytes((int) K, (int) ((G + grid - 1) / grid)) <= GQ_SMEM_MAX && b200_get_encode_tiled() != nullptr;
+    if (b200_get_encode_tiled() == nullptr) return false;
+    if (gq_big(bytes, (int) K, G, ctx)) return true;
+    const int grid = gq_grid(ctx, G, bytes, false);
+    return gq_smem_bytes((int) K, (int) ((G + grid - 1) / grid)) <= GQ_SMEM_MAX;
 }
 
 // tensor maps of the weights are static: a small direct-mapped cache keyed by (data, row stride, K, M)
@@ -315,23 +352,28 @@ int b200_launch_gemv_mma(b200_ctx * ctx, const b200_tensor * const * w, int n, c
     { static int dbg = -1; if (dbg < 0) { const char * e = getenv("GGML_B200_GS_DBG"); dbg = e ? atoi(e) : 0; } p.dbg = dbg; }
     { static int npf = -1; if (npf < 0) { const char * e = getenv("GGML_B200_GQ_NPF"); npf = e ? atoi(e) : 0; } p.npf = npf; }
     p.trace = ctx->trace; p.trace_cap = ctx->trace_cap;
-    const int grid = gq_grid(ctx, G, bytes);
+    { static int f = -1; if (f < 0) { const char * e = getenv("GGML_B200_GQ_NPRE"); f = e ? atoi(e) : 0; }
+      p.npre = f > 0 ? (f > GQ_STAGES ? GQ_STAGES : f) : (bytes > ((size_t) 24 << 20) ? GQ_STAGES : 1); }
+    const bool big = gq_big(bytes, p.K, G, ctx);
+    const int grid = gq_grid(ctx, G, bytes, big);
     p.gmax = (int) ((G + grid - 1) / grid);
-    const size_t smem = gq_smem_bytes(p.K, p.gmax);
+    const size_t smem = gq_smem_bytes(p.K, p.gmax, big ? 24 : GQ_WARPS);
     static bool attr_done[64] = {};
     if (!attr_done[ctx->device & 63]) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(k_gemv_q4k_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, GQ_SMEM_MAX));
+        B200_CUDA_TRY(cudaFuncSetAttribute(k_gemv_q4k_mma<GQ_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, GQ_SMEM_MAX));
+        B200_CUDA_TRY(cudaFuncSetAttribute(k_gemv_q4k_mma<24>, cudaFuncAttributeMaxDynamicSharedMemorySize, GQ_SMEM_MAX_BIG));
         attr_done[ctx->device & 63] = true;
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned) grid);
-    cfg.blockDim = dim3(GQ_WARPS * 32);
+    cfg.blockDim = dim3((big ? 24 : GQ_WARPS) * 32);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = ctx->stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = ctx->pdl ? 1 : 0;
-    B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_gemv_q4k_mma, p, maps));
+    if (big) B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_gemv_q4k_mma<24>, p, maps));
+    else     B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_gemv_q4k_mma<GQ_WARPS>, p, maps));
     return B200_OK;
 }

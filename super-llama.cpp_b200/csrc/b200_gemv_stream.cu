@@ -46,6 +46,7 @@ struct gs_args {
     // device and come from an earlier kernel, so in this mode the first weight fetch is issued after griddepcontrol.wait
     const int * ids; int id_base; size_t estride;
     int dbg;                                 // GGML_B200_GS_DBG (measurement only): 1 skip quantization, 2 skip the dot products, 4 no weight traffic
+    int npre;                                // ring stages to fill before the dependency wait
     int npf;                                 // GGML_B200_GS_NPF: bytes of this warp's rows (behind the ring fill) to pull into L2 from the prologue
     unsigned long long * trace; int trace_cap;   // b200_debug_trace (measurement only)
 };
@@ -259,12 +260,14 @@ static __device__ __forceinline__ void gs_locate(const gs_args & p, int gr, cons
     if (seg) *seg = s;
 }
 
-// SHAPE: 0 = LEAN (12 warps, 1 CTA/SM), 1 = WIDE (8 warps, deep rings, 2 CTAs/SM), 2 = DENSE (12 warps, 2 CTAs/SM: most warps per SM)
+// SHAPE: 0 = LEAN (12 warps, 1 CTA/SM), 1 = WIDE (8 warps, deep rings, 2 CTAs/SM), 2 = DENSE (12 warps, 2 CTAs/SM: most warps per SM),
+// 3 = BIG (16 warps, deep rings, ONE CTA per SM: the warps of WIDE, but the activation column is fetched and quantized once per SM --
+// with two CTAs per SM the 57 KB column of a K = 14336 matmul took ~6100 cycles to arrive, L2 broadcast bandwidth, measured)
 template <int TYPE, int SHAPE>
-__global__ void __launch_bounds__(SHAPE == 1 ? 256 : 384, 2) k_gemv_stream(const gs_args p) {
+__global__ void __launch_bounds__(SHAPE == 3 ? 512 : SHAPE == 1 ? 256 : 384, SHAPE == 3 ? 1 : 2) k_gemv_stream(const gs_args p) {
     using T = gs_traits<TYPE>;
-    constexpr int GS_WARPS = SHAPE == 1 ? 8 : 12;
-    constexpr int GS_STAGES = T::stages(SHAPE);
+    constexpr int GS_WARPS = SHAPE == 3 ? 16 : SHAPE == 1 ? 8 : 12;
+    constexpr int GS_STAGES = T::stages(SHAPE == 3 ? 1 : SHAPE);
     constexpr int CHUNK_BYTES = T::BLOCK_BYTES * GS_CB;
     constexpr int STAGE_BYTES = CHUNK_BYTES * GS_RW;
     extern __shared__ __align__(128) uint8_t smem[];
@@ -293,8 +296,8 @@ __global__ void __launch_bounds__(SHAPE == 1 ? 256 : 384, 2) k_gemv_stream(const
         mbar_fence_init();
     }
     __syncwarp();
-    // let the next kernel of the stream start its own prologue (PDL); nothing it may touch is ours
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    // (dbg & 8: the old placement of the PDL trigger, right at the start)
+    if (p.dbg & 8) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
     const uint64_t policy = l2_policy_evict_first();
     int prp = 0, pkc = 0;                                                 // producer cursor (warp-uniform; lane 0 issues)
@@ -314,7 +317,11 @@ __global__ void __launch_bounds__(SHAPE == 1 ? 256 : 384, 2) k_gemv_stream(const
         if (++pkc == nchunks) { pkc = 0; ++prp; }
     };
     const int npro = min(nitems, GS_STAGES);
-    if (!p.ids) for (int i = 0; i < npro; ++i) issue(i);                  // weights do not depend on the previous kernel
+    // weights do not depend on the previous kernel: fill the ring before the dependency wait -- for small matrices (p.npre = 1) only one
+    // stage, the rest behind the activation loads (see b200_gemv_mma.cu)
+    int nfilled = 0;
+    if (!p.ids) for (; nfilled < min(npro, p.npre); ++nfilled) issue(nfilled);
+    auto fill_rest = [&]() { for (; nfilled < npro; ++nfilled) issue(nfilled); };
     // The rings hold ~83 KB per CTA.  Until the previous kernel has retired and the activations are quantized nothing is consumed,
     // so nothing more is fetched and HBM idles: pull the rows behind the ring fill into L2 meanwhile (the ring refills then hit L2).
     if (p.npf > 0 && !p.ids && lane == 0 && nitems > npro) {
@@ -333,7 +340,7 @@ __global__ void __launch_bounds__(SHAPE == 1 ? 256 : 384, 2) k_gemv_stream(const
     b200_trace_stamp(rec, 2);
     unsigned ll_tag = 0;
     if (p.nll) { asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(ll_tag) : "l"(p.ctrl + 8)); ll_tag += 1u; }
-    if (p.ids) for (int i = 0; i < npro; ++i) issue(i);                   // which experts: only known now
+    if (p.ids || p.aq != nullptr || (p.dbg & 1)) fill_rest();             // (which experts: only known now)
 
     // quantize the activation column to q8_1 straight into shared memory, in lane order (b200_quantize_column_x86: same arithmetic
     // as q8_1_block<B200_Q8_1_X86>, bit-exact with the reference)
@@ -341,15 +348,28 @@ __global__ void __launch_bounds__(SHAPE == 1 ? 256 : 384, 2) k_gemv_stream(const
     } else if (p.aq != nullptr) {
         // a ready q8_1 image (one quantize launch instead of one quantization per CTA): permuting copy
         const int4 * src = (const int4 *) p.aq;
-        for (int j = threadIdx.x; j < (p.K >> 4); j += blockDim.x) {
-            const int4 v = src[j];
-            float2 ds = make_float2(0.f, 0.f);
-            if ((j & 1) == 0) ds = __half22float2(p.ads[j >> 1]);
-            T::store_unit(s_act, p.K, nblocks, j >> 1, j & 1, v, ds.x, ds.y);
+        const int nunits = p.K >> 4;
+        for (int j0 = threadIdx.x; j0 < nunits; j0 += 4 * blockDim.x) {    // four loads in flight per thread: one L2 round trip for K <= 16384
+            int4 v[4]; float2 ds[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int j = j0 + i * blockDim.x;
+                if (j < nunits) { v[i] = src[j]; if ((j & 1) == 0) ds[i] = __half22float2(p.ads[j >> 1]); }
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int j = j0 + i * blockDim.x;
+                if (j < nunits) T::store_unit(s_act, p.K, nblocks, j >> 1, j & 1, v[i], ds[i].x, ds[i].y);
+            }
         }
     } else {
-        b200_quantize_column_x86(p.x, p.K, [&](int blk32, int hf, int4 w, float d, float sm) { T::store_unit(s_act, p.K, nblocks, blk32, hf, w, d, sm); });
+        b200_quantize_column_x86(p.x, p.K, [&](int blk32, int hf, int4 w, float d, float sm) { T::store_unit(s_act, p.K, nblocks, blk32, hf, w, d, sm); }, rec, fill_rest);
     }
+    // Let the next kernel of the stream start its prologue (PDL) only now: its CTA lands on this SM and pulls ~80 KB of weights,
+    // and loads issued behind that burst wait for it (the activation column took ~1300 cycles to arrive with the trigger at the top
+    // of the kernel, measured with b200_debug_trace).  Our own activation loads are done; the next kernel's ring fill overlaps our dot
+    // products instead.
+    if (!(p.dbg & 8)) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     __syncthreads();
     b200_trace_stamp(rec, 3);
 
@@ -471,7 +491,7 @@ int b200_launch_exchange_unpack(b200_ctx * ctx, const void * ll, float * dst, in
 }
 
 template <int TYPE> static size_t gs_smem_bytes(int K, int shape) {
-    const int GS_WARPS = shape == 1 ? 8 : 12, GS_STAGES = gs_traits<TYPE>::stages(shape);
+    const int GS_WARPS = shape == 3 ? 16 : shape == 1 ? 8 : 12, GS_STAGES = gs_traits<TYPE>::stages(shape == 3 ? 1 : shape);
     return (size_t) GS_WARPS * GS_STAGES * gs_traits<TYPE>::BLOCK_BYTES * GS_CB * GS_RW + gs_traits<TYPE>::act_bytes(K) + GS_WARPS * GS_STAGES * 8;
 }
 #define GS_SMEM_MAX (200 * 1024)   // typical shapes need <= 113 KB, which lets two kernels co-reside on an SM
@@ -491,8 +511,8 @@ bool b200_gemv_stream_supported(const b200_tensor * w, const b200_tensor * x) {
 
 template <int TYPE, int SHAPE>
 static int gs_launch_cfg(b200_ctx * ctx, const gs_args & p, int attr_slot) {
-    constexpr int WARPS = SHAPE == 1 ? 8 : 12;
-    constexpr bool WIDE = SHAPE != 0;                                     // two CTAs per SM
+    constexpr int WARPS = SHAPE == 3 ? 16 : SHAPE == 1 ? 8 : 12;
+    constexpr bool WIDE = SHAPE == 1 || SHAPE == 2;                       // two CTAs per SM
     const size_t smem = gs_smem_bytes<TYPE>(p.K, SHAPE);
     static bool attr_done[64] = {};                                       // per kernel instantiation and device
     (void) attr_slot;
@@ -519,13 +539,15 @@ static int gs_launch(b200_ctx * ctx, const gs_args & p, int attr_slot) {
     // WIDE once the weights outlast what the rings of one wave can hold (~22 MB), if its smem fits two CTAs per SM
     const size_t bytes = (size_t) p.Mtot * (p.K >> 8) * gs_traits<TYPE>::BLOCK_BYTES;
     static int force = -1;
-    if (force < 0) { const char * e = getenv("GGML_B200_GEMV_SHAPE"); force = e ? (e[0] == 'w' ? 1 : e[0] == 'l' ? 2 : e[0] == 'd' ? 3 : 0) : 0; }
+    if (force < 0) { const char * e = getenv("GGML_B200_GEMV_SHAPE"); force = e ? (e[0] == 'w' ? 1 : e[0] == 'l' ? 2 : e[0] == 'd' ? 3 : e[0] == '2' ? 4 : 0) : 0; }
     bool wide = bytes > ((size_t) 24 << 20);
     if (force == 1) wide = true; else if (force == 2) wide = false;
     // two-CTA shapes: DENSE (24 warps per SM) measured 8-10 % faster than WIDE in isolation for K <= 8192, but in the token's
     // kernel chain it leaves no room for the next kernel's PDL prologue and the whole step got 3 % slower: opt-in only
     const bool dense = force == 3;
     if ((wide || force == 3) && dense && gs_smem_bytes<TYPE>(p.K, 2) <= 113 * 1024) return gs_launch_cfg<TYPE, 2>(ctx, p, attr_slot);
+    // long streams: BIG (one 16-warp CTA per SM); GGML_B200_GEMV_SHAPE=2 keeps the two 8-warp CTAs of WIDE
+    if (wide && force != 4 && gs_smem_bytes<TYPE>(p.K, 3) <= GS_SMEM_MAX) return gs_launch_cfg<TYPE, 3>(ctx, p, attr_slot);
     if (wide && gs_smem_bytes<TYPE>(p.K, 1) <= 113 * 1024) return gs_launch_cfg<TYPE, 1>(ctx, p, attr_slot);
     return gs_launch_cfg<TYPE, 0>(ctx, p, attr_slot + 4);
 }
@@ -555,6 +577,8 @@ int b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n
         p.Mtot += p.seg[i].M;
     }
     for (int i = n; i < GS_MAXSEG; ++i) { p.seg[i].w = nullptr; p.seg[i].nb1 = 0; p.seg[i].dst = nullptr; p.seg[i].M = 0; }
+    { static int f = -1; if (f < 0) { const char * e = getenv("GGML_B200_GS_NPRE"); f = e ? atoi(e) : 0; }
+      p.npre = f > 0 ? f : ((size_t) p.Mtot * b200_row_size(w[0]->type, p.K) > ((size_t) 24 << 20) ? 8 : 1); }
     if (w[0]->type == B200_TYPE_Q4_K) return gs_launch<B200_TYPE_Q4_K>(ctx, p, 8);     // attr_done slots 8..11 wide, 12..15 lean
     if (w[0]->type == B200_TYPE_Q6_K) return gs_launch<B200_TYPE_Q6_K>(ctx, p, 9);
     if (w[0]->type == B200_TYPE_Q4_0) return gs_launch<B200_TYPE_Q4_0>(ctx, p, 10);

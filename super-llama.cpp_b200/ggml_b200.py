@@ -53,7 +53,7 @@ def lib():
         "b200_device_count": (i, []), "b200_last_error": (C.c_char_p, []),
         "b200_ctx_create": (vp, [i]), "b200_ctx_destroy": (None, [vp]), "b200_ctx_device": (i, [vp]),
         "b200_ctx_stream": (vp, [vp]), "b200_ctx_synchronize": (i, [vp]), "b200_ctx_launch_count": (C.c_uint64, [vp]),
-        "b200_ctx_invalidate": (i, [vp]),
+        "b200_ctx_invalidate": (i, [vp]), "b200_ctx_note_write": (i, [vp, vp, C.c_size_t]),
         "b200_malloc": (vp, [vp, sz]), "b200_free": (i, [vp, vp]), "b200_host_alloc": (vp, [sz]), "b200_host_free": (i, [vp]),
         "b200_memcpy_h2d": (i, [vp, vp, vp, sz]), "b200_memcpy_d2h": (i, [vp, vp, vp, sz]), "b200_memset": (i, [vp, vp, i, sz]),
         "b200_quantize_q8_1": (i, [vp, vp, sz, vp, i64, i64, i]),
@@ -178,6 +178,10 @@ class Context:
     def invalidate(self):
         """drop the cached q8_1 activation image (after activations were written by something other than this API)"""
         lib().b200_ctx_invalidate(self.h)
+
+    def note_write(self, t):
+        """the device tensor t was (re)written outside this API: drop activation images cached from it"""
+        lib().b200_ctx_note_write(self.h, t.ptr, t.nbytes)
 
     def synchronize(self):
         _check(lib().b200_ctx_synchronize(self.h), "synchronize")
