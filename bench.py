@@ -539,13 +539,13 @@ def run_b200(args):
         result = {
             "metric": f"tg128 tok/s (llama-bench, {pretty(cfg)} {args.quant.upper()})", "value": tps, "unit": "tok/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_tg, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "int8 dp4a dot / f32 accumulate (q8_1 activations); f16 KV, f32 softmax", "data": "synthetic",
+            "dtype": "int8 dot (mma.sync / dp4a) with f32 accumulate over q8_1 activations; f16 KV, f32 softmax", "data": "synthetic",
             "config": {"workload": f"{cfg['name']}-{args.quant} tg128: all MUL_MAT{'_ID' if cfg.get('n_expert') else ''} + FLASH_ATTN_EXT nodes of one decode token ({cfg['n_layer']} layers + output head); glue ops not included",
                        "tensor_types": "Q4_K_M mix: q4_K, q6_K on attn_v/ffn_down of half the layers, q6_K output" if args.quant == "q4_k_m" else args.quant + " weights", "depth": args.depth, "n_kv": tg.n_kv,
                        "parallelism": (f"row-split tp{world}, all-gather " + ("fused into the GEMV epilogue (NVLink peer stores)" if peer is not None else "by NCCL")) if world > 1 else "single GPU", "cuda_graph": bool(graph),
                        "l2": f"weights {tg.weight_bytes * world / 1e9:.1f} GB >> 126 MB L2, streamed once per step"},
             "hbm_bytes_per_step": total_bytes, "hbm_frac_whole_step": total_bytes / world / (ms_tg * 1e-3) / 1e9 / hbm_gbs,
-            "roofline": {"kernel": "k_gemv_stream (TMA-streamed dequant-GEMV with fused q8_1 quantization, q4_K + q6_K)", "bound": "hbm", "achieved": achieved, "peak": hbm_gbs, "unit": "GB/s",
+            "roofline": {"kernel": "decode dequant-GEMV with fused q8_1 quantization: k_gemv_q4k_mma (raw q4_K, TMA boxes + int8 mma.sync) and k_gemv_stream (q6_K / long-row q4_K, TMA-streamed dp4a)", "bound": "hbm", "achieved": achieved, "peak": hbm_gbs, "unit": "GB/s",
                          "frac": achieved / hbm_gbs, "traffic": traffic_per_launch(gemv_bytes_step / max(gemv_n, 1)), "algorithmic_bytes_per_launch": gemv_bytes_step / max(gemv_n, 1), "peak_source": f"{peak_src} (MEASURED_PEAKS.json hbm_gbs)",
                          "launches_per_step": gemv_n, "other_launches_in_timed_graph": other_n, "ms_per_step": gemv_ms_step,
                          "algorithmic_bytes_per_step": gemv_bytes_step,

@@ -5,8 +5,5 @@ mkdir -p gpurun_out
 if [ "${1:-}" != "skip" ]; then timeout 900 python -m pytest tests/test_gpu_ops.py -m gpu -x -q --timeout 600 ${1:+-k "$1"} > gpurun_out/iter_pytest.log 2>&1; echo "pytest rc=$?"; tail -4 gpurun_out/iter_pytest.log; fi
 run() { tag=$1; shift; env "$@" timeout 300 python scripts/gemv_trace.py --layers 32 --tag $tag > gpurun_out/$tag.txt 2> gpurun_out/$tag.err || echo "$tag failed rc=$?"; grep "^##" gpurun_out/$tag.txt; }
 run i_default X=1
-run i_pre3    GGML_B200_GQ_NPRE=3 GGML_B200_GS_NPRE=8
-run i_pre1    GGML_B200_GQ_NPRE=1 GGML_B200_GS_NPRE=1
-run i_w2      GGML_B200_GEMV_SHAPE=2
 
-python scripts/trace_agg.py i_default i_pre1 i_w2
+python scripts/trace_agg.py i_default

@@ -1,11 +1,19 @@
 #!/bin/bash
-# One gpurun call: GPU parity tests, smoke, the bench line, the reference's own perf harness.  Logs -> gpurun_out/.
+# One gpurun call: GPU parity tests, smoke, the bench line (both arms), ncu launch list + one full capture, the reference's own harness.
 set -u
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,driver_version,memory.total,clocks.max.sm --format=csv > gpurun_out/gpu.txt 2>&1
 lscpu | head -20 > gpurun_out/cpu.txt; nproc >> gpurun_out/cpu.txt; free -g >> gpurun_out/cpu.txt
 timeout 2400 python -m pytest tests -m gpu -x -q --timeout 1800 ${PYTEST_ARGS:-} > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
-tail -25 gpurun_out/pytest_gpu.log
-timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -3 gpurun_out/smoke.log
-timeout 900 python bench.py ${BENCH_ARGS:-} > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"; cat gpurun_out/bench.json; tail -5 gpurun_out/bench.err
-GGML_BACKEND_PATH=$PWD/super-llama.cpp_b200/libggml-b200.so timeout 600 oracle/_ref/avx2/test-backend-ops perf -b B200_0 -o MUL_MAT -p "type_a=(q4_0|q8_0|q4_K|q6_K),type_b=f32,m=4096" > gpurun_out/perf_mul_mat.log 2>&1; echo "perf rc=$?"; grep -E "q4_K|q8_0" gpurun_out/perf_mul_mat.log | head -20
+tail -6 gpurun_out/pytest_gpu.log
+timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -2 gpurun_out/smoke.log
+timeout 900 python bench.py ${BENCH_ARGS:-} > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"; cat gpurun_out/bench.json; tail -3 gpurun_out/bench.err
+timeout 600 python bench.py --impl reference --steps 3 --warmup 3 > gpurun_out/bench_reference.json 2> gpurun_out/bench_reference.err; echo "bench reference rc=$?"; cat gpurun_out/bench_reference.json
+# ncu: launch list of the bench command (shares, not absolutes), then ONE full capture of the dominant kernels
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 700 --csv --log-file gpurun_out/ncu_launches.csv python bench.py --steps 2 --warmup 3 --no-pp --no-cpu --no-graph > gpurun_out/ncu_launches.log 2>&1; echo "ncu list rc=$?"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_gemv_q4k_mma|k_gemv_stream' -s 20 -c 6 -o gpurun_out/ncu_full_gemv -f python bench.py --steps 2 --warmup 3 --no-pp --no-cpu --no-graph > gpurun_out/ncu_full.log 2>&1; echo "ncu full rc=$?"
+if [ -z "${SKIP_TBO:-}" ]; then
+for op in MUL_MAT MUL_MAT_ID FLASH_ATTN_EXT; do
+  GGML_BACKEND_PATH=$PWD/super-llama.cpp_b200/libggml-b200.so timeout 900 oracle/_ref/avx2/test-backend-ops test -b B200_0 -o $op > gpurun_out/tbo_$op.log 2>&1; echo "test-backend-ops $op rc=$?"; tail -3 gpurun_out/tbo_$op.log
+done
+fi
