@@ -83,11 +83,24 @@ static inline int cvt_x86(float r) { return (r >= -2147483648.0f && r < 21474836
 // X86: ggml-cpu/arch/x86/quants.c:388-449 -- id = 127/amax, _mm256_round_ps(NEAREST) = ties-to-even,
 //      packs saturate to int8, s = fp16(d * (float) sum_q).
 // REF: ggml-quants.c:225-258 -- id = 1/d, roundf (ties away), (int8_t) cast, s = fp16(sum * d).
+// MAXPS / MAXSS and the scalar MAX() macro alike: a > b ? a : b, i.e. the SECOND operand whenever one of them is NaN
+static inline float mx(float a, float b) { return a > b ? a : b; }
+// amax exactly as the AVX2 body computes it (arch/x86/quants.c:402-412): four 8-lane vectors folded with _mm256_max_ps, then
+// _mm_max_ps(high half, low half), _mm_max_ps(max4, movehl), _mm_max_ss(max4, movehdup).  For NaN-free input this is the plain
+// maximum; with NaNs the result depends on where they sit, and this order reproduces it.
+static float amax_x86(const float * x) {
+    float m[8];
+    for (int j = 0; j < 8; ++j) m[j] = mx(mx(mx(fabsf(x[j]), fabsf(x[8 + j])), fabsf(x[16 + j])), fabsf(x[24 + j]));
+    float q[4];
+    for (int k = 0; k < 4; ++k) q[k] = mx(m[4 + k], m[k]);
+    return mx(mx(q[0], q[2]), mx(q[1], q[3]));
+}
 void orc_quantize_row_q8_1(const float * x, void * vy, int64_t k, int variant) {
     q8_1_t * y = (q8_1_t *) vy;
     for (int64_t i = 0; i < k / QK; ++i) {
         float amax = 0.0f;
-        for (int j = 0; j < QK; ++j) { const float a = fabsf(x[i * QK + j]); if (a > amax) amax = a; }
+        if (variant == ORC_Q8_1_X86) amax = amax_x86(x + i * QK);
+        else for (int j = 0; j < QK; ++j) amax = mx(amax, fabsf(x[i * QK + j]));        // ggml-quants.c:233-236, MAX(amax, fabsf(v))
         const float d = amax / 127.0f;
         y[i].d = orc_fp32_to_fp16(d);
         int sum = 0;
@@ -114,8 +127,7 @@ void orc_quantize_row_q8_1(const float * x, void * vy, int64_t k, int variant) {
 void orc_quantize_row_q8_0(const float * x, void * vy, int64_t k) {
     q8_0_t * y = (q8_0_t *) vy;
     for (int64_t i = 0; i < k / QK; ++i) {
-        float amax = 0.0f;
-        for (int j = 0; j < QK; ++j) { const float a = fabsf(x[i * QK + j]); if (a > amax) amax = a; }
+        const float amax = amax_x86(x + i * QK);
         const float d = amax / 127.0f;
         const float id = amax != 0.0f ? 127.0f / amax : 0.0f;
         y[i].d = orc_fp32_to_fp16(d);

@@ -138,10 +138,44 @@ static __device__ __forceinline__ int ld_u16x2(const void * p) {   // 4 bytes fr
 // give the "integer indefinite" 0x80000000 instead of CUDA's saturation.
 static __device__ __forceinline__ int cvt_x86(float r) { return fabsf(r) < 2147483648.0f ? __float2int_rn(r) : (int) 0x80000000u; }
 
+// MAXPS / MAXSS and the scalar MAX() macro alike: a > b ? a : b, i.e. the SECOND operand whenever one of them is NaN
+static __device__ __forceinline__ float mx_x86(float a, float b) { return a > b ? a : b; }
+// amax of one 32-value block held one value per lane.  NaN-free blocks: the plain maximum.  With NaNs the reference's result depends on
+// where they sit: the AVX2 body folds four 8-lane vectors with _mm256_max_ps, then high half against low half, movehl, movehdup
+// (arch/x86/quants.c:402-412); the scalar code runs MAX(amax, fabsf(v)) left to right (ggml-quants.c:233-236).  Same order here.
+template <int VARIANT>
+static __device__ __forceinline__ float q8_1_amax(float v) {
+    const float a = fabsf(v);
+    if (!__any_sync(0xffffffffu, v != v)) return warp_max(a);
+    if (VARIANT == B200_Q8_1_X86) {
+        float t = mx_x86(a, __shfl_down_sync(0xffffffffu, a, 8));          // lanes 0-7: lane j folds x[j], x[8+j], x[16+j], x[24+j]
+        t = mx_x86(t, __shfl_down_sync(0xffffffffu, a, 16));
+        t = mx_x86(t, __shfl_down_sync(0xffffffffu, a, 24));
+        t = mx_x86(__shfl_down_sync(0xffffffffu, t, 4), t);                // lanes 0-3: max(high half, low half)
+        t = mx_x86(t, __shfl_down_sync(0xffffffffu, t, 2));                // lanes 0-1: max(max4, movehl)
+        t = mx_x86(t, __shfl_down_sync(0xffffffffu, t, 1));                // lane 0:    max_ss(max4, movehdup)
+        return __shfl_sync(0xffffffffu, t, 0);
+    }
+    float amax = 0.0f;
+    for (int j = 0; j < 32; ++j) amax = mx_x86(amax, __shfl_sync(0xffffffffu, a, j));
+    return amax;
+}
+
+// fp32 -> fp16 as vcvtps2ph gives it for the NaNs a q8_1 block can hold: a NaN PROPAGATED from a (default, positive) NaN input -> 0x7e00,
+// a NaN GENERATED by an invalid operation (inf * 0) is x86's negative "real indefinite" -> 0xfe00.  CUDA arithmetic returns the canonical
+// 0x7fffffff for both, so the caller says which one it is.  (Payloads of non-default input NaNs are not reproduced.)
+static __device__ __forceinline__ __half f2h_q8_1(float v, bool generated) {
+    return v != v ? __ushort_as_half((unsigned short) (generated ? 0xfe00 : 0x7e00)) : __float2half_rn(v);
+}
+// the (d, s) pair of a block: s = d * sum is a propagated NaN when d is one, a generated one for inf * 0
+static __device__ __forceinline__ __half2 q8_1_ds(float d, int isum) {
+    return __halves2half2(f2h_q8_1(d, false), f2h_q8_1(__fmul_rn(d, (float) isum), !(d != d)));
+}
+
 // one warp, one block: returns this lane's quant, the block scale d (fp32) and the integer sum of quants
 template <int VARIANT>
 static __device__ __forceinline__ void q8_1_block(float v, int & q, float & d, int & isum) {
-    const float amax = warp_max(fabsf(v));
+    const float amax = q8_1_amax<VARIANT>(v);
     d = __fdiv_rn(amax, 127.0f);
     unsigned usum;
     if (VARIANT == B200_Q8_1_X86) {
@@ -202,13 +236,19 @@ static __device__ __forceinline__ void b200_quantize_column_x86(const float * x,
         abits = max(abits, __shfl_xor_sync(0xffffffffu, abits, 1));
         if (rec && abits != 0xffffffffu) b200_trace_stamp(rec, 8);         // (measurement only) the column's first loads have landed
         const bool  nan_in = abits > 0x7f800000u;
-        // NaN inputs never win the reference's amax search (`a > amax` from 0, oracle/ggml_oracle.c): largest non-NaN magnitude, rare path
+        // with a NaN in the block the reference's amax depends on where it sits (q8_1_amax): same fold order, rare path
         float amax = __uint_as_float(abits);
         if (__any_sync(0xffffffffu, nan_in)) {
-            amax = 0.0f;
+            float lo[16], hi[16];                                         // x[0..15] (even lane of the pair), x[16..31] (odd lane)
 #pragma unroll
-            for (int i = 0; i < 16; ++i) amax = fmaxf(amax, fabsf(f[i]));
-            amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, 1));
+            for (int i = 0; i < 16; ++i) {
+                const float o = __shfl_xor_sync(0xffffffffu, f[i], 1);
+                lo[i] = fabsf((lane & 1) ? o : f[i]); hi[i] = fabsf((lane & 1) ? f[i] : o);
+            }
+            float m[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) m[j] = mx_x86(mx_x86(mx_x86(lo[j], lo[8 + j]), hi[j]), hi[8 + j]);
+            amax = mx_x86(mx_x86(mx_x86(m[4], m[0]), mx_x86(m[6], m[2])), mx_x86(mx_x86(m[5], m[1]), mx_x86(m[7], m[3])));
         }
         const float d  = __fdiv_rn(amax, 127.0f);
         const float id = amax != 0.0f ? __fdiv_rn(127.0f, amax) : 0.0f;

@@ -13,6 +13,7 @@
 // Long contexts are split over CTAs (split-KV); partial (max, sum, acc) triples are merged by k_fattn_combine.
 #include "b200_fattn.cuh"
 #include "b200_ptx.cuh"
+#include <stdlib.h>
 
 #define FD_WARPS 4
 #define FD_TILE  32
@@ -41,6 +42,9 @@ __global__ void __launch_bounds__(FD_WARPS * 32, 1) k_fattn_dec(const fattn_args
     if (lane == 0) { mbar_init(bar0, 1); mbar_init(bar0 + 8, 1); mbar_fence_init(); }
     // no griddepcontrol.launch_dependents here: letting the PDL-launched GEMV behind us start on the SMs this small grid leaves free
     // measured 2 % SLOWER for the whole token (662 -> 649 tok/s): its CTAs on our SMs start late and become the stragglers
+    // launched with the PDL attribute (GGML_B200_FATTN_DEC_PDL != 0): our launch latency hides under the previous kernel's tail; Q, the
+    // mask and the newest K/V rows come from that kernel, so everything below waits for it.  (A no-op without the attribute.)
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const float * qrow = (const float *) (p.q + iq1 * p.q_nb1 + iq2 * p.q_nb2 + iq3 * p.q_nb3);
     for (int i = threadIdx.x; i < p.DK; i += blockDim.x) sq[i] = qrow[i];
     __syncthreads();
@@ -249,11 +253,20 @@ int b200_launch_fattn_dec(b200_ctx * ctx, const b200_tensor * q, const b200_tens
         B200_CUDA_TRY(cudaFuncSetAttribute(k_fattn_dec<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         ctx->attr_done[4] = 1;
     }
-    dim3 grid((unsigned) (p.N * x.nsplit), (unsigned) p.H, (unsigned) S);
+    static const int use_pdl = getenv("GGML_B200_FATTN_DEC_PDL") ? atoi(getenv("GGML_B200_FATTN_DEC_PDL")) : 1;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned) (p.N * x.nsplit), (unsigned) p.H, (unsigned) S);
+    cfg.blockDim = dim3(FD_WARPS * 32);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = (ctx->pdl && use_pdl) ? 1 : 0;
     switch (p.DV / 64) {
-        case 1: B200_LAUNCH(ctx, B200_K_FATTN, k_fattn_dec<1><<<grid, FD_WARPS * 32, smem, ctx->stream>>>(p, x)); break;
-        case 2: B200_LAUNCH(ctx, B200_K_FATTN, k_fattn_dec<2><<<grid, FD_WARPS * 32, smem, ctx->stream>>>(p, x)); break;
-        case 4: B200_LAUNCH(ctx, B200_K_FATTN, k_fattn_dec<4><<<grid, FD_WARPS * 32, smem, ctx->stream>>>(p, x)); break;
+        case 1: B200_LAUNCH(ctx, B200_K_FATTN, cudaLaunchKernelEx(&cfg, k_fattn_dec<1>, p, x)); break;
+        case 2: B200_LAUNCH(ctx, B200_K_FATTN, cudaLaunchKernelEx(&cfg, k_fattn_dec<2>, p, x)); break;
+        case 4: B200_LAUNCH(ctx, B200_K_FATTN, cudaLaunchKernelEx(&cfg, k_fattn_dec<4>, p, x)); break;
         default: b200_set_error("fattn: DV=%d unsupported", p.DV); return B200_ERR_UNSUPPORTED;
     }
     if (x.nsplit > 1) {

@@ -34,8 +34,7 @@ __global__ void __launch_bounds__(256) k_quantize_q8_1(const float * __restrict_
     blk_q8_1 * yb = y + ib;
     if ((lane & 3) == 0) *(unsigned *) (yb->qs + lane) = t;
     if (lane == 1) {
-        __half2 ds = __halves2half2(__float2half_rn(d), __float2half_rn(__fmul_rn(d, (float) isum)));
-        *(__half2 *) &yb->d = ds;
+        *(__half2 *) &yb->d = q8_1_ds(d, isum);
     }
 }
 
@@ -78,7 +77,7 @@ __global__ void __launch_bounds__(256) k_quantize_q8_1_soa(const float * __restr
     t |= __shfl_down_sync(0xffffffffu, t, 1) << 8;
     t |= __shfl_down_sync(0xffffffffu, t, 2) << 16;
     if ((lane & 3) == 0) *(unsigned *) (qs + ib * 32 + lane) = t;
-    if (lane == 1) ds[ib] = __halves2half2(__float2half_rn(d), __float2half_rn(__fmul_rn(d, (float) isum)));
+    if (lane == 1) ds[ib] = q8_1_ds(d, isum);
 }
 
 int b200_launch_quantize_q8_1_soa(b200_ctx * ctx, const float * x, size_t nb1, size_t nb2, size_t nb3,

@@ -31,6 +31,21 @@ def main():
     out["q8_1_x"] = x
     out["q8_1_x86"] = ref.quantize_q8_1(x, O.Q8_1_X86)
     out["q8_1_ref"] = ref.quantize_q8_1(x, O.Q8_1_REF)
+    # rows with NaN / inf inputs: the AVX2 amax depends on WHERE a NaN sits (maxps returns its second operand), the scalar code on
+    # whether it comes last; own generator so that the vectors above stay as they were
+    rn = np.random.default_rng(20261105)
+    xn = rn.standard_normal((72, 32)).astype(np.float32)
+    xn[0, :] = np.nan
+    for i in range(1, 33):
+        xn[i, i - 1] = np.nan
+    xn[33, :8] = np.nan; xn[34, 24:] = np.nan; xn[35, 8:16] = np.nan
+    for i in range(36, 72):
+        xn[i, rn.random(32) < rn.uniform(0.03, 0.6)] = np.nan
+        if i % 5 == 0:
+            xn[i, rn.integers(0, 32)] = np.inf
+    out["q8_1_nan_x"] = xn
+    out["q8_1_nan_x86"] = ref.quantize_q8_1(xn, O.Q8_1_X86)
+    out["q8_1_nan_ref"] = ref.quantize_q8_1(xn, O.Q8_1_REF)
     out["q8_0_cpu"] = ref.from_float(O.Q8_0, x)
     out["q8_K_cpu"] = ref.from_float(O.Q8_K, x)
 

@@ -48,6 +48,9 @@ def test_q8_1_bit_exact_golden(ctx, gold):
     x = gold["q8_1_x"]
     assert np.array_equal(ctx.quantize_q8_1_host(x, 0), gold["q8_1_x86"])
     assert np.array_equal(ctx.quantize_q8_1_host(x, 1), gold["q8_1_ref"])
+    xn = gold["q8_1_nan_x"]                                         # NaN / inf at every lane position: same amax fold order as the reference
+    assert np.array_equal(ctx.quantize_q8_1_host(xn, 0), gold["q8_1_nan_x86"])
+    assert np.array_equal(ctx.quantize_q8_1_host(xn, 1), gold["q8_1_nan_ref"])
 
 
 @pytest.mark.parametrize("variant", [0, 1])
@@ -85,7 +88,7 @@ def test_q8_1_fused_in_gemv_bit_exact_probe(ctx, B, orc, K, mma, monkeypatch):
     """The decode GEMV quantizes its activation column itself (b200_quantize_column_x86).  Probe weights read the quantized
     column back through MUL_MAT exactly: a q8_0 row holding a single 1 (d = 1) returns d_a * q_a of one element, a q4_0 row of
     zero nibbles with d = 1 on one block returns -8 * s of that block; both must equal the reference's quantize_row_q8_1
-    bit for bit, special blocks (zeros, denormal amax, ties) included."""
+    bit for bit, special blocks (zeros, denormal amax, ties, NaN elements) included."""
     rng = np.random.default_rng(K)
     x = (rng.standard_normal(K) * 10.0 ** rng.integers(-4, 4, K // 32).repeat(32)).astype(np.float32)
     x[:32] = 0.0
@@ -93,7 +96,9 @@ def test_q8_1_fused_in_gemv_bit_exact_probe(ctx, B, orc, K, mma, monkeypatch):
     x[64:96] = 1000.0
     x[96:128] = np.round(x[96:128] * 2) / 2 + 0.5                  # exact .5 ties
     x[128:160] = -1.0
-    x[192:224] = -x[160:192]
+    x[192:224] = rng.uniform(-1e-3, 1e-3, 32)                      # (keeps d * 2^31 inside fp16: a finite s)
+    x[200] = np.nan                                                # its quant is the saturated x86 "integer indefinite", the int32 sum wraps
+    x[224:256] = rng.uniform(-1e-3, 1e-3, 32); x[231] = np.nan; x[250] = np.nan
     q = orc.quantize_q8_1(x[None, :], 0).reshape(-1, 36)
     d = q[:, 0:2].copy().view(np.float16).astype(np.float32).reshape(-1)
     sm = q[:, 2:4].copy().view(np.float16).astype(np.float32).reshape(-1)
