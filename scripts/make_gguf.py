@@ -1,0 +1,76 @@
+#!/usr/bin/env python
+"""Random-init GGUF of a llama-architecture model with the tensor types llama-quantize would pick, written directly as GGUF blocks
+(random nibbles / bytes, small fp16 scales) with the `gguf` package -- no f16 stage and no quantize tool, so a 4.6 GB Q4_K_M file takes
+well under a minute on the GPU box.  Tokenizer: "no_vocab" (src/llama-vocab.cpp:1706-1725 then adds llama.vocab_size dummy tokens;
+llama-bench feeds random token ids).  Used by scripts/gpu_llama_bench.sh to run the reference's own llama-bench through the plugin.
+
+  python scripts/make_gguf.py --model tinyllama --quant q4_0 -o /tmp/tiny-q4_0.gguf
+"""
+import argparse, os, sys
+import numpy as np
+import gguf
+from gguf import GGMLQuantizationType as QT
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench                       # model tables + the Q4_K_M tensor-type rule (src/llama-quant.cpp restated there)
+
+QTYPE = {bench.Q4_0: QT.Q4_0, bench.Q8_0: QT.Q8_0, bench.Q4_K: QT.Q4_K, bench.Q6_K: QT.Q6_K}
+
+
+def blocks(rng, t, K, M):
+    """[M rows][K / blck * tsize bytes] of random blocks of ggml type t (same generator as bench.random_blocks, but one pool reused)"""
+    nb = K // bench.BLCK[t] * M
+    pool = bench.random_blocks(rng, t, min(nb, 1 << 18)).reshape(-1, bench.TSIZE[t])
+    reps = (nb + pool.shape[0] - 1) // pool.shape[0]
+    raw = np.tile(pool, (reps, 1))[:nb]
+    return raw.reshape(M, K // bench.BLCK[t] * bench.TSIZE[t])
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--model", default="tinyllama", choices=["tinyllama", "8b"])
+    ap.add_argument("--quant", default="q4_0", choices=["q4_0", "q8_0", "q4_k_m"])
+    ap.add_argument("--layers", type=int, default=0, help="override the layer count (smoke runs)")
+    ap.add_argument("-o", "--out", required=True)
+    a = ap.parse_args()
+    cfg = dict(bench.MODELS[a.model])
+    if a.layers:
+        cfg["n_layer"] = a.layers
+    e, f, nh, nkv, hd, nl, nv = cfg["n_embd"], cfg["n_ff"], cfg["n_head"], cfg["n_head_kv"], cfg["head_dim"], cfg["n_layer"], cfg["n_vocab"]
+    types, out_type = bench.q4_k_m_layer_types(cfg, a.quant)
+    emb_type = {"q4_0": bench.Q4_0, "q8_0": bench.Q8_0, "q4_k_m": bench.Q4_K}[a.quant]           # token_embd: the file's base type
+    rng = np.random.default_rng(1234)
+    w = gguf.GGUFWriter(a.out, "llama")
+    w.add_name(f"{cfg['name']}-random-{a.quant}")
+    w.add_context_length(8192 if a.model == "8b" else 2048)
+    w.add_embedding_length(e); w.add_block_count(nl); w.add_feed_forward_length(f)
+    w.add_head_count(nh); w.add_head_count_kv(nkv); w.add_rope_dimension_count(hd)
+    w.add_layer_norm_rms_eps(1e-5); w.add_rope_freq_base(500000.0 if a.model == "8b" else 10000.0)
+    w.add_vocab_size(nv)
+    w.add_file_type({"q4_0": 2, "q8_0": 7, "q4_k_m": 15}[a.quant])                                 # LLAMA_FTYPE_MOSTLY_*
+    w.add_tokenizer_model("no_vocab")
+    kvd = nkv * hd
+
+    def q(name, t, K, M):
+        w.add_tensor(name, blocks(rng, t, K, M), raw_dtype=QTYPE[t])
+
+    def norm(name, n):
+        w.add_tensor(name, np.ones(n, dtype=np.float32))
+
+    q("token_embd.weight", emb_type, e, nv)
+    for i, lt in enumerate(types):
+        p = f"blk.{i}."
+        norm(p + "attn_norm.weight", e)
+        q(p + "attn_q.weight", lt["wq"], e, e); q(p + "attn_k.weight", lt["wk"], e, kvd); q(p + "attn_v.weight", lt["wv"], e, kvd)
+        q(p + "attn_output.weight", lt["wo"], e, e)
+        norm(p + "ffn_norm.weight", e)
+        q(p + "ffn_gate.weight", lt["gate"], e, f); q(p + "ffn_up.weight", lt["up"], e, f); q(p + "ffn_down.weight", lt["down"], f, e)
+    norm("output_norm.weight", e)
+    q("output.weight", out_type, e, nv)
+    w.write_header_to_file(); w.write_kv_data_to_file(); w.write_tensors_to_file(); w.close()
+    print(f"wrote {a.out}: {os.path.getsize(a.out) / 1e9:.2f} GB, {nl} layers, {a.quant}")
+
+
+if __name__ == "__main__":
+    main()

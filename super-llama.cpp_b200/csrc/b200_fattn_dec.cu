@@ -20,6 +20,7 @@
 
 struct fd_extra {
     int nsplit, ntiles, tiles_per_split, nstage;
+    int trigger;                // GGML_B200_FATTN_DEC_TRIGGER: 1 = PDL trigger once Q is in shared memory, 2 = at the top of the kernel
     float * partial;            // [S][H][N][nsplit][DV + 2] when nsplit > 1
 };
 
@@ -44,10 +45,12 @@ __global__ void __launch_bounds__(FD_WARPS * 32, 1) k_fattn_dec(const fattn_args
     // measured 2 % SLOWER for the whole token (662 -> 649 tok/s): its CTAs on our SMs start late and become the stragglers
     // launched with the PDL attribute (GGML_B200_FATTN_DEC_PDL != 0): our launch latency hides under the previous kernel's tail; Q, the
     // mask and the newest K/V rows come from that kernel, so everything below waits for it.  (A no-op without the attribute.)
+    if (x.trigger == 2) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
     const float * qrow = (const float *) (p.q + iq1 * p.q_nb1 + iq2 * p.q_nb2 + iq3 * p.q_nb3);
     for (int i = threadIdx.x; i < p.DK; i += blockDim.x) sq[i] = qrow[i];
     __syncthreads();
+    if (x.trigger == 1) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
     const uint32_t h = (uint32_t) iq2;
     const float slope = fattn_slope(p, h);
@@ -241,6 +244,7 @@ int b200_launch_fattn_dec(b200_ctx * ctx, const b200_tensor * q, const b200_tens
     if (nsplit > x.ntiles / 16) nsplit = x.ntiles / 16 > 0 ? x.ntiles / 16 : 1;
     x.tiles_per_split = (x.ntiles + nsplit - 1) / nsplit;
     x.nsplit = (x.ntiles + x.tiles_per_split - 1) / x.tiles_per_split;
+    { static int tr = -1; if (tr < 0) { const char * e = getenv("GGML_B200_FATTN_DEC_TRIGGER"); tr = e ? atoi(e) : 2; } x.trigger = tr; }   // measured: 677 (none) -> 687 tok/s (top of the kernel)
     x.partial = nullptr;
     if (x.nsplit > 1) {
         x.partial = (float *) b200_scratch(ctx, 1, (size_t) rows * x.nsplit * (p.DV + 2) * sizeof(float));
