@@ -79,6 +79,7 @@ B200_API int          b200_ctx_device(const b200_ctx * ctx);
 B200_API void *       b200_ctx_stream(const b200_ctx * ctx);   // cudaStream_t
 B200_API int          b200_ctx_synchronize(b200_ctx * ctx);
 B200_API uint64_t     b200_ctx_launch_count(const b200_ctx * ctx);   // kernels launched so far through this ctx
+B200_API uint64_t     b200_ctx_scratch_generation(const b200_ctx * ctx);   // bumped when a scratch block moves: CUDA graphs recorded before are stale
 // The ctx keeps the q8_1 image of the last quantized activation tensor so that matmuls sharing src1 (wq/wk/wv, gate/up)
 // quantize it once.  Writes made through this API invalidate it; call this after writing activations by other means.
 B200_API int          b200_ctx_invalidate(b200_ctx * ctx);

@@ -116,6 +116,7 @@ extern "C" void * b200_graph_end(b200_ctx * ctx) {
 extern "C" int b200_graph_launch(b200_ctx * ctx, void * ge) { B200_CUDA_TRY(cudaGraphLaunch((cudaGraphExec_t) ge, ctx->stream)); return B200_OK; }
 extern "C" int b200_graph_destroy(void * ge) { B200_CUDA_TRY(cudaGraphExecDestroy((cudaGraphExec_t) ge)); return B200_OK; }
 
+extern "C" uint64_t b200_ctx_scratch_generation(const b200_ctx * ctx) { return ctx->scratch_gen; }
 extern "C" int      b200_ctx_device(const b200_ctx * ctx) { return ctx->device; }
 extern "C" void *   b200_ctx_stream(const b200_ctx * ctx) { return (void *) ctx->stream; }
 extern "C" uint64_t b200_ctx_launch_count(const b200_ctx * ctx) { return ctx->launches; }
@@ -132,7 +133,7 @@ void * b200_scratch(b200_ctx * ctx, int slot, size_t nbytes) {
     cudaStreamSynchronize(ctx->stream);
     if (ctx->scratch[slot]) cudaFree(ctx->scratch[slot]);
     size_t want = nbytes + nbytes / 2; if (want < (1u << 20)) want = 1u << 20;
-    ctx->scratch[slot] = nullptr; ctx->scratch_size[slot] = 0;
+    ctx->scratch[slot] = nullptr; ctx->scratch_size[slot] = 0; ++ctx->scratch_gen;
     if (cudaMalloc(&ctx->scratch[slot], want) != cudaSuccess) { cudaGetLastError(); b200_set_error("scratch alloc of %zu bytes failed", want); return nullptr; }
     ctx->scratch_size[slot] = want;
     return ctx->scratch[slot];

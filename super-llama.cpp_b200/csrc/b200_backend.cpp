@@ -13,6 +13,7 @@
 #include <string>
 #include <vector>
 #include <mutex>
+#include <atomic>
 #include <unordered_set>
 #include <string.h>
 #include <stdlib.h>
@@ -70,7 +71,16 @@ struct b200_device_ctx {
 struct b200_reg_ctx { std::vector<b200_device_ctx *> devices; };
 // `repacked`: weight tensors of this buffer that set_tensor re-laid out for the kernels (b200_repack): the load-time repack hook
 struct b200_buffer_ctx { int device; void * base; std::mutex mu; std::unordered_set<const void *> repacked; };
-struct b200_backend_ctx { int device; b200_ctx * ctx; std::string name; };
+// one instantiated CUDA graph per ggml graph this backend has computed before (be_graph_compute)
+struct b200_graph_entry { uint64_t h1, h2; int n_nodes; void * exec; int seen; int failed; uint64_t used; };
+struct b200_backend_ctx {
+    int device; b200_ctx * ctx; std::string name;
+    std::vector<b200_graph_entry> graphs; uint64_t graphs_epoch = 0, tick = 0, n_replayed = 0, n_captured = 0, n_eager = 0;
+    // GGML_B200_GRAPH_STATS: device time of every replay (event pairs, read in be_free) and host time spent inside graph_compute
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> replay_events; double host_us = 0;
+};
+// bumped whenever something a captured graph baked in may have changed under it: a weight tensor changed layout, a buffer was freed
+static std::atomic<uint64_t> g_layout_epoch{1};
 
 static ggml_backend_reg g_reg;
 static b200_reg_ctx     g_reg_ctx;
@@ -111,6 +121,7 @@ static void tensor_repack(ggml_backend_buffer_t b, const ggml_tensor * t, bool i
     if (rc != B200_OK || b200_ctx_synchronize(u) != B200_OK) { fprintf(stderr, "ggml-b200: repack failed: %s\n", b200_last_error()); abort(); }
     std::lock_guard<std::mutex> g(c->mu);
     if (inverse) c->repacked.erase(t->data); else c->repacked.insert(t->data);
+    ++g_layout_epoch;
 }
 static bool tensor_wants_repack(ggml_backend_buffer_t b, const ggml_tensor * t) {
     const int mode = repack_mode();
@@ -125,6 +136,7 @@ static bool tensor_wants_repack(ggml_backend_buffer_t b, const ggml_tensor * t) 
 static void buf_free(ggml_backend_buffer_t b) {
     b200_buffer_ctx * c = (b200_buffer_ctx *) b->context;
     cudaSetDevice(c->device); cudaFree(c->base); delete c;
+    ++g_layout_epoch;
 }
 static void * buf_get_base(ggml_backend_buffer_t b) { return ((b200_buffer_ctx *) b->context)->base; }
 static enum ggml_status buf_init_tensor(ggml_backend_buffer_t b, ggml_tensor * t) {
@@ -145,7 +157,9 @@ static void buf_set_tensor(ggml_backend_buffer_t b, ggml_tensor * t, const void 
     const bool was = tensor_is_repacked(t);
     if (was) tensor_repack(b, base, true);                   // the host writes GGUF bytes: go back to GGUF layout first
     B200_CHECK(cudaMemcpyAsync((char *) t->data + off, data, n, cudaMemcpyHostToDevice, cudaStreamPerThread)); B200_CHECK(cudaStreamSynchronize(cudaStreamPerThread));
-    if (was || (off == 0 && n == tensor_nbytes(t) && tensor_wants_repack(b, t))) tensor_repack(b, base, false);
+    // llama_model_loader without mmap uploads a tensor in ascending chunks (src/llama-model-loader.cpp:1136-1186): the write that
+    // reaches the last byte completes the tensor
+    if (was || (off + n == tensor_nbytes(t) && tensor_wants_repack(b, t))) tensor_repack(b, base, false);
 }
 static void buf_get_tensor(ggml_backend_buffer_t b, const ggml_tensor * t, void * data, size_t off, size_t n) {
     b200_buffer_ctx * c = (b200_buffer_ctx *) b->context; B200_CHECK(cudaSetDevice(c->device));
@@ -223,12 +237,27 @@ static ggml_guid g_guid = { 0xb2, 0x00, 0x5a, 0x10, 0x0a, 0x67, 0x67, 0x6d, 0x6c
 static const char * be_name(ggml_backend_t be) { return ((b200_backend_ctx *) be->context)->name.c_str(); }
 static void be_free(ggml_backend_t be) {
     b200_backend_ctx * c = (b200_backend_ctx *) be->context;
+    for (auto & e : c->graphs) if (e.exec) b200_graph_destroy(e.exec);
+    if (!c->replay_events.empty()) {
+        cudaStreamSynchronize(c->ctx->stream);
+        double ms = 0, mn = 1e30; for (auto & p : c->replay_events) { float t = 0; cudaEventElapsedTime(&t, p.first, p.second); ms += t; if (t < mn) mn = t; cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
+        fprintf(stderr, "ggml-b200 graphs: %zu replays timed: %.1f us each on the device (fastest %.1f us)\n", c->replay_events.size(), ms * 1e3 / c->replay_events.size(), mn * 1e3);
+    }
+    if (getenv("GGML_B200_PROFILE") || getenv("GGML_B200_GRAPH_STATS"))
+        fprintf(stderr, "ggml-b200 graphs: %llu computed launch by launch, %llu recorded, %llu replayed\n", (unsigned long long) c->n_eager, (unsigned long long) c->n_captured, (unsigned long long) c->n_replayed);
+    if (getenv("GGML_B200_PROFILE")) {                           // per-kernel-kind device time of everything this backend launched
+        static const char * kinds[] = { "quantize_q8_1", "gemv", "gemv_id", "gemm", "fattn", "fattn_combine", "matmul_float", "glue", "mmid_sort", "convert" };
+        for (int k = 0; k < 10; ++k) {
+            double ms = 0; uint64_t n = 0;
+            if (b200_ctx_profile_get(c->ctx, k, &ms, &n) == B200_OK && n) fprintf(stderr, "ggml-b200 profile: %-14s %8llu launches %10.3f ms  %8.2f us each\n", kinds[k], (unsigned long long) n, ms, ms * 1e3 / n);
+        }
+    }
     b200_ctx_destroy(c->ctx); delete c; delete be;
 }
 static void be_set_tensor_async(ggml_backend_t be, ggml_tensor * t, const void * data, size_t off, size_t n) {
     b200_backend_ctx * c = (b200_backend_ctx *) be->context; B200_CHECK(cudaSetDevice(c->device));
     b200_note_write(c->ctx, (char *) t->data + off, n);
-    if (t->buffer && buft_is_b200(t->buffer->buft) && (tensor_is_repacked(t) || (off == 0 && n == tensor_nbytes(t) && tensor_wants_repack(t->buffer, t)))) {
+    if (t->buffer && buft_is_b200(t->buffer->buft) && (tensor_is_repacked(t) || (off + n == tensor_nbytes(t) && tensor_wants_repack(t->buffer, t)))) {
         B200_CHECK(cudaStreamSynchronize(c->ctx->stream));       // layout translation is synchronous: weights are uploaded once
         buf_set_tensor(t->buffer, t, data, off, n);
         return;
@@ -299,20 +328,148 @@ static int compute_node(b200_ctx * ctx, ggml_tensor * node) {
     }
 }
 
-static enum ggml_status be_graph_compute(ggml_backend_t be, ggml_cgraph * g) {
-    b200_backend_ctx * c = (b200_backend_ctx *) be->context;
-    if (cudaSetDevice(c->device) != cudaSuccess) return GGML_STATUS_FAILED;
+static bool fuse_off() { static int v = -1; if (v < 0) { const char * e = getenv("GGML_B200_NO_FUSE"); v = (e && atoi(e)) ? 1 : 0; } return v != 0; }
+static bool ranges_overlap(const ggml_tensor * a, const ggml_tensor * b) {
+    if (!a || !b || !a->data || !b->data) return false;
+    const char * pa = (const char *) a->data, * pb = (const char *) b->data;
+    return pa < pb + tensor_nbytes(b) && pb < pa + tensor_nbytes(a);
+}
+static enum ggml_status run_nodes(b200_backend_ctx * c, ggml_cgraph * g) {
     c->ctx->qcache.valid = 0; c->ctx->mcache.valid = 0;      // tensors may have been rewritten through buffer set_tensor since the last graph
     for (int i = 0; i < g->n_nodes; ++i) {
         ggml_tensor * node = g->nodes[i];
         if (op_is_view((int) node->op) || tensor_nelements(node) == 0) continue;
-        const int rc = compute_node(c->ctx, node);
+        int rc;
+        // MUL_MAT nodes that follow each other (views in between do no work) and read the same src1 -- ffn_gate / ffn_up, attn_v / attn_k
+        // of a llama layer -- go out as ONE launch (b200_mul_mat_multi; it falls back to one launch each when the kernels cannot take them
+        // together).  Only adjacent nodes: running a later node early could write into memory the graph allocator still lends to a
+        // tensor in between, so a candidate's dst must also not overlap anything the nodes before it in the group read or write.
+        int group[3] = { i, -1, -1 }, ng = 1;
+        if (node->op == GGML_OP_MUL_MAT && !fuse_off()) {
+            for (int j = i + 1; j < g->n_nodes && ng < 3; ++j) {
+                ggml_tensor * nj = g->nodes[j];
+                if (op_is_view((int) nj->op) || tensor_nelements(nj) == 0) continue;
+                if (nj->op != GGML_OP_MUL_MAT || nj->src[1] != node->src[1] || nj->src[0]->type != node->src[0]->type) break;
+                bool clash = false;
+                for (int k = 0; k < ng && !clash; ++k) {
+                    const ggml_tensor * nk = g->nodes[group[k]];
+                    clash = ranges_overlap(nj, nk) || ranges_overlap(nj, nk->src[0]) || ranges_overlap(nj, nk->src[1]);
+                }
+                if (clash) break;
+                group[ng++] = j;
+            }
+        }
+        if (ng > 1) {
+            b200_tensor w[3], d[3], x = to_b200(node->src[1]);
+            const b200_tensor * wp[3]; b200_tensor * dp[3];
+            for (int k = 0; k < ng; ++k) { w[k] = to_b200(g->nodes[group[k]]->src[0]); d[k] = to_b200(g->nodes[group[k]]); wp[k] = &w[k]; dp[k] = &d[k]; }
+            rc = b200_mul_mat_multi(c->ctx, wp, ng, &x, dp);
+            if (rc == B200_OK) i = group[ng - 1];                       // (views between the members need no work)
+        } else if (node->op == GGML_OP_RMS_NORM && !fuse_off() && i + 1 < g->n_nodes && g->nodes[i + 1]->op == GGML_OP_MUL &&
+                   (rc = b200_glue_rms_norm_mul(c->ctx, node, g->nodes[i + 1])) == B200_OK) {
+            b200_note_write(c->ctx, node->data, tensor_nbytes(node));
+            b200_note_write(c->ctx, g->nodes[i + 1]->data, tensor_nbytes(g->nodes[i + 1]));
+            ++i;
+        } else {
+            rc = compute_node(c->ctx, node);
+        }
         if (rc != B200_OK) {
             B200_LOG("graph_compute: node %d (%s, op %d) failed: %s", i, node->name, (int) node->op, b200_last_error());
             return GGML_STATUS_FAILED;
         }
     }
     return GGML_STATUS_SUCCESS;
+}
+
+// ---- CUDA graphs for repeated ggml graphs ----------------------------------------------------------------------------------------
+// A decode step is ~500 launches of 2-15 us kernels: issued one by one the host cannot keep the device fed (llama-bench tg128 on
+// Llama-3-8B Q4_K_M: 4.2 ms per token against ~2 ms of kernel time).  So the second time a graph with the same identity arrives -- same
+// ops, op_params, shapes, strides and data pointers on every node and source, what ggml-cuda.cu's graph-properties check compares -- the node
+// loop is recorded into a CUDA graph (PDL edges included) and from then on one cudaGraphLaunch replays it.  Tensor CONTENTS may differ
+// freely between replays (token ids, positions, KV indices and the mask are tensors); everything the host decided while recording
+// depends on identity only.  Recorded graphs are dropped when a scratch block moved (b200_ctx_scratch_generation) or a weight
+// changed layout / a buffer was freed (g_layout_epoch).  Only small-batch graphs on plain device buffers (no row-split peers) are
+// recorded; GGML_B200_GRAPHS=0 turns it off.
+static bool graphs_on() { static int v = -1; if (v < 0) { const char * e = getenv("GGML_B200_GRAPHS"); v = (e && !atoi(e)) ? 0 : 1; } return v != 0; }
+static inline void hash_mix(uint64_t & h1, uint64_t & h2, uint64_t v) {
+    h1 = (h1 ^ v) * 0x100000001b3ull; h1 ^= h1 >> 29;
+    h2 = (h2 + v) * 0x9e3779b97f4a7c15ull; h2 ^= h2 >> 32;
+}
+static inline void hash_tensor(uint64_t & h1, uint64_t & h2, const ggml_tensor * t) {
+    hash_mix(h1, h2, (uint64_t) (uintptr_t) t->data); hash_mix(h1, h2, ((uint64_t) t->type << 32) | (uint32_t) t->op);
+    for (int i = 0; i < 4; ++i) { hash_mix(h1, h2, (uint64_t) t->ne[i]); hash_mix(h1, h2, (uint64_t) t->nb[i]); }
+}
+static bool graph_identity(const ggml_cgraph * g, uint64_t & h1, uint64_t & h2) {
+    h1 = 0xcbf29ce484222325ull; h2 = 0x84222325cbf29ce4ull;
+    int work = 0;
+    for (int i = 0; i < g->n_nodes; ++i) {
+        const ggml_tensor * n = g->nodes[i];
+        hash_tensor(h1, h2, n);
+        if (op_is_view((int) n->op)) continue;
+        ++work;
+        if (n->buffer && !buft_is_b200(n->buffer->buft)) return false;
+        for (int k = 0; k < (int) (GGML_MAX_OP_PARAMS / sizeof(int32_t)); k += 2) hash_mix(h1, h2, ((uint64_t) (uint32_t) n->op_params[k] << 32) | (uint32_t) n->op_params[k + 1]);
+        for (int k = 0; k < GGML_MAX_SRC; ++k) {
+            const ggml_tensor * s = n->src[k];
+            if (!s) { hash_mix(h1, h2, 0x5eedull + k); continue; }
+            if (s->buffer && !buft_is_b200(s->buffer->buft)) return false;             // row-split weights: peers, events, staging
+            hash_tensor(h1, h2, s);
+        }
+        // prefill-sized work is not launch-bound and its paths may size scratch by content
+        if ((n->op == GGML_OP_MUL_MAT || n->op == GGML_OP_MUL_MAT_ID || n->op == GGML_OP_FLASH_ATTN_EXT) && n->ne[1] * n->ne[2] * n->ne[3] > 64) return false;
+    }
+    return work >= 2;
+}
+static enum ggml_status be_graph_compute(ggml_backend_t be, ggml_cgraph * g) {
+    b200_backend_ctx * c = (b200_backend_ctx *) be->context;
+    if (cudaSetDevice(c->device) != cudaSuccess) return GGML_STATUS_FAILED;
+    uint64_t h1, h2;
+    if (!graphs_on() || c->ctx->profile || c->ctx->trace || c->ctx->capturing || !graph_identity(g, h1, h2)) { ++c->n_eager; return run_nodes(c, g); }
+    const uint64_t epoch = g_layout_epoch.load() * 0x10001ull + b200_ctx_scratch_generation(c->ctx);
+    if (epoch != c->graphs_epoch) {                            // recordings are stale; what was seen before is recorded again right away
+        B200_CHECK(cudaStreamSynchronize(c->ctx->stream));
+        for (auto & x : c->graphs) { if (x.exec) b200_graph_destroy(x.exec); x.exec = nullptr; x.failed = 0; }
+        c->graphs_epoch = epoch;
+    }
+    b200_graph_entry * e = nullptr;
+    for (auto & x : c->graphs) if (x.h1 == h1 && x.h2 == h2 && x.n_nodes == g->n_nodes) { e = &x; break; }
+    if (!e) {                                                   // first sight: run eagerly (sizes the scratch blocks), remember
+        if (c->graphs.size() >= 16) {
+            size_t lru = 0; for (size_t i = 1; i < c->graphs.size(); ++i) if (c->graphs[i].used < c->graphs[lru].used) lru = i;
+            if (c->graphs[lru].exec) { B200_CHECK(cudaStreamSynchronize(c->ctx->stream)); b200_graph_destroy(c->graphs[lru].exec); }
+            c->graphs.erase(c->graphs.begin() + lru);
+        }
+        c->graphs.push_back({ h1, h2, g->n_nodes, nullptr, 1, 0, ++c->tick });
+        ++c->n_eager;
+        return run_nodes(c, g);
+    }
+    e->used = ++c->tick;
+    if (!e->exec && !e->failed) {
+        if (b200_graph_begin(c->ctx) != B200_OK) { e->failed = 1; cudaGetLastError(); }
+        else {
+            const enum ggml_status st = run_nodes(c, g);
+            void * exec = b200_graph_end(c->ctx);
+            c->ctx->qcache.valid = 0; c->ctx->mcache.valid = 0;
+            if (st == GGML_STATUS_SUCCESS && exec) { e->exec = exec; ++c->n_captured; }
+            else {
+                if (exec) b200_graph_destroy(exec);
+                cudaGetLastError(); e->failed = 1;
+                B200_LOG("graph_compute: recording a %d-node graph failed (%s): it keeps running launch by launch", g->n_nodes, b200_last_error());
+            }
+        }
+    }
+    if (e->exec) {
+        static const bool stats = getenv("GGML_B200_GRAPH_STATS") != nullptr;
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        if (stats && c->replay_events.size() < 8192) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, c->ctx->stream); }
+        const int rc = b200_graph_launch(c->ctx, e->exec);
+        if (e0) { cudaEventRecord(e1, c->ctx->stream); c->replay_events.push_back({ e0, e1 }); }
+        if (rc == B200_OK) { ++c->n_replayed; return GGML_STATUS_SUCCESS; }
+        B200_LOG("graph_compute: graph launch failed: %s", b200_last_error());
+        return GGML_STATUS_FAILED;
+    }
+    ++c->n_eager;
+    return run_nodes(c, g);
 }
 
 static void be_event_record(ggml_backend_t be, ggml_backend_event_t ev) {
@@ -345,6 +502,7 @@ static void dev_props(ggml_backend_dev_t d, ggml_backend_dev_props * p) {
 static ggml_backend_t dev_init_backend(ggml_backend_dev_t d, const char *) {
     b200_device_ctx * c = (b200_device_ctx *) d->context;
     b200_ctx * ctx = b200_ctx_create(c->device);
+    if (ctx && getenv("GGML_B200_PROFILE")) b200_ctx_profile(ctx, 1);
     if (!ctx) { B200_LOG("init_backend: %s", b200_last_error()); return nullptr; }
     return new ggml_backend{ &g_guid, k_backend_iface, d, new b200_backend_ctx{ c->device, ctx, c->name } };
 }
@@ -426,6 +584,7 @@ ggml_backend_buffer_type_t b200_split_buffer_type(int main_device, const float *
 static void * reg_proc_address(ggml_backend_reg_t, const char * name) {
     if (!strcmp(name, "ggml_backend_get_features"))      return (void *) reg_get_features;
     if (!strcmp(name, "ggml_backend_split_buffer_type")) return (void *) b200_split_buffer_type;
+    if (!strcmp(name, "ggml_backend_b200_tensor_is_repacked")) return (void *) +[](const ggml_tensor * t) -> int { return tensor_is_repacked(t) ? 1 : 0; };   // tests/upload_probe.cpp
     return nullptr;    // "ggml_backend_set_n_threads", "ggml_backend_dev_get_extra_bufts": not applicable
 }
 static const ggml_backend_reg_i k_reg_iface = { reg_name, reg_dev_count, reg_get_dev, reg_proc_address };

@@ -58,6 +58,7 @@ struct b200_ctx {
     // scratch arena for activation quantization / split-KV partials / sorted ids (grows on demand)
     void *       scratch[8];
     size_t       scratch_size[8];
+    uint64_t     scratch_gen;       // bumped whenever a scratch block moves (recorded CUDA graphs hold the old address)
     uint64_t     launches;
     uint64_t     launches_kind[B200_K_COUNT];
     // optional per-kernel timing with CUDA events on the launching stream (bench.py's roofline leg)

@@ -1,6 +1,396 @@
-// b200_glue.cu -- non-hot-path ggml ops (see b200_glue.cuh).  Filled in after the hot path is green.
+// b200_glue.cu -- the cheap ops between the hot-path nodes of a llama graph: RMS_NORM, ADD / MUL / SUB / DIV with
+// broadcast, ROPE (normal and neox), SET_ROWS (the KV-cache write), CPY / CONT / DUP, GLU (SwiGLU), GET_ROWS (f32 rows) and SCALE.
+// They exist so that ggml_backend_sched keeps a whole decode graph on the device instead of bouncing every second node through the
+// CPU backend.  Plain bandwidth-trivial kernels over ggml's strided views; semantics follow the reference's CPU operators
+// (ggml/src/ggml-cpu/ops.cpp: rms_norm 3560-3640, rope 5524-5790, set_rows, glu; binary-ops.cpp; ggml.c:4255-4269 for the YaRN
+// correction range).  What is not listed in b200_glue_supports() stays on the CPU backend.
 #include "b200_glue.cuh"
 #include "../../include/ggml-b200-abi.h"
+#include <math.h>
+#include <string.h>
 
-bool b200_glue_supports(const struct ggml_tensor *) { return false; }
-int  b200_glue_compute(b200_ctx *, struct ggml_tensor * op) { b200_set_error("op %d not implemented", (int) op->op); return B200_ERR_UNSUPPORTED; }
+// every glue kernel is launched with programmatic dependent launch: the next kernel (usually a GEMV that prefetches its weights) may
+// start at once, and we wait for the kernel in front of us before touching memory
+#define GL_PDL() do { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); asm volatile("griddepcontrol.wait;" ::: "memory"); } while (0)
+
+struct gl_view { char * p; int64_t ne[4]; size_t nb[4]; };
+static gl_view gl_of(const ggml_tensor * t) {
+    gl_view v; v.p = (char *) t->data;
+    for (int i = 0; i < 4; ++i) { v.ne[i] = t->ne[i]; v.nb[i] = t->nb[i]; }
+    return v;
+}
+static bool gl_contig_rows(const ggml_tensor * t, size_t es) { return t->nb[0] == es; }
+static bool gl_contiguous(const ggml_tensor * t, size_t es) {
+    return t->nb[0] == es && t->nb[1] == es * t->ne[0] && t->nb[2] == t->nb[1] * t->ne[1] && t->nb[3] == t->nb[2] * t->ne[2];
+}
+static int64_t gl_nrows(const ggml_tensor * t) { return t->ne[1] * t->ne[2] * t->ne[3]; }
+static int64_t gl_nelem(const ggml_tensor * t) { return t->ne[0] * gl_nrows(t); }
+static size_t gl_esize(int type) { return type == GGML_TYPE_F32 || type == GGML_TYPE_I32 ? 4 : type == GGML_TYPE_F16 || type == GGML_TYPE_BF16 ? 2 : type == GGML_TYPE_I64 ? 8 : 0; }
+
+// row index -> (i1, i2, i3) of a view
+static __device__ __forceinline__ void gl_unrow(int64_t r, const gl_view & v, int64_t & i1, int64_t & i2, int64_t & i3) {
+    i1 = r % v.ne[1]; r /= v.ne[1]; i2 = r % v.ne[2]; i3 = r / v.ne[2];
+}
+
+// Launch shape of the row-wise kernels.  A decode graph runs every one of them on a single row of 4096 .. 14336 floats: a loop of
+// dependent load -> store rounds in one CTA costs a memory latency per round (k_swiglu measured 60 us that way), so a row is cut into
+// chunks of GL_CHUNK elements, one CTA each, and every thread issues all its loads (one float4 when the row is 16-byte aligned)
+// before its first store.  blockIdx.x = row * chunks + chunk.
+#define GL_CHUNK 1024
+static bool gl_vec_ok(const ggml_tensor * t) {                   // rows of float4: 16-byte aligned base and strides, ne0 % 4 == 0
+    return t->ne[0] % 4 == 0 && ((uintptr_t) t->data & 15) == 0 && t->nb[1] % 16 == 0 && t->nb[2] % 16 == 0 && t->nb[3] % 16 == 0;
+}
+static __device__ __forceinline__ float block_sum(float s, float * red) {          // red: 32 floats of shared memory
+    s = warp_sum(s);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    const int nw = (blockDim.x + 31) >> 5;
+    s = (int) threadIdx.x < nw ? red[threadIdx.x] : 0.0f;
+    if (threadIdx.x < 32) { s = warp_sum(s); if (threadIdx.x == 0) red[0] = s; }
+    __syncthreads();
+    return red[0];
+}
+
+// ---- RMS_NORM: y = x / sqrt(mean(x^2) + eps), one CTA per row; optionally followed by MUL with the norm weight (every llama norm):
+// one pass, both nodes' outputs written.  CACHED: the row (<= 8 * blockDim elements, float4-aligned) stays in registers between the
+// sum and the scaling ----------------------------------------------------------------------------------------------------------------
+template <bool MUL, bool CACHED>
+__global__ void __launch_bounds__(1024) k_rms_norm(const gl_view x, const gl_view y, const gl_view w, const gl_view z, float eps, int write_y) {
+    GL_PDL();
+    int64_t i1, i2, i3; gl_unrow(blockIdx.x, x, i1, i2, i3);
+    const float * xr = (const float *) (x.p + i1 * x.nb[1] + i2 * x.nb[2] + i3 * x.nb[3]);
+    float *       yr = (float *) (y.p + i1 * y.nb[1] + i2 * y.nb[2] + i3 * y.nb[3]);
+    const float * wr = MUL ? (const float *) (w.p + (i1 % w.ne[1]) * w.nb[1] + (i2 % w.ne[2]) * w.nb[2] + (i3 % w.ne[3]) * w.nb[3]) : nullptr;
+    float *       zr = MUL ? (float *) (z.p + i1 * z.nb[1] + i2 * z.nb[2] + i3 * z.nb[3]) : nullptr;
+    __shared__ float red[32];
+    const int64_t n0 = x.ne[0];
+    if (CACHED) {
+        float4 v[2], g[2];
+        float s = 0.0f;
+        #pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int64_t i = ((int64_t) k * blockDim.x + threadIdx.x) * 4;
+            v[k] = i < n0 ? *(const float4 *) (xr + i) : make_float4(0, 0, 0, 0);
+            if (MUL) g[k] = i < n0 ? *(const float4 *) (wr + i) : make_float4(0, 0, 0, 0);
+        }
+        #pragma unroll
+        for (int k = 0; k < 2; ++k) { s = fmaf(v[k].x, v[k].x, s); s = fmaf(v[k].y, v[k].y, s); s = fmaf(v[k].z, v[k].z, s); s = fmaf(v[k].w, v[k].w, s); }
+        const float scale = rsqrtf(block_sum(s, red) / (float) n0 + eps);
+        #pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int64_t i = ((int64_t) k * blockDim.x + threadIdx.x) * 4;
+            if (i >= n0) continue;
+            const float4 o = make_float4(v[k].x * scale, v[k].y * scale, v[k].z * scale, v[k].w * scale);   // the RMS_NORM node's value, rounded as the unfused kernel rounds it
+            if (!MUL || write_y) *(float4 *) (yr + i) = o;
+            if (MUL) *(float4 *) (zr + i) = make_float4(o.x * g[k].x, o.y * g[k].y, o.z * g[k].z, o.w * g[k].w);
+        }
+    } else {
+        float s = 0.0f;
+        for (int64_t i = threadIdx.x; i < n0; i += blockDim.x) { const float v = xr[i]; s = fmaf(v, v, s); }
+        const float scale = rsqrtf(block_sum(s, red) / (float) n0 + eps);
+        for (int64_t i = threadIdx.x; i < n0; i += blockDim.x) {
+            const float v = xr[i] * scale;
+            if (!MUL || write_y) yr[i] = v;
+            if (MUL) zr[i] = v * wr[i];
+        }
+    }
+}
+
+// ---- ADD / SUB / MUL / DIV with src1 broadcast over src0 (ggml_can_repeat) ------------------------------------------------------------
+template <int OP> static __device__ __forceinline__ float gl_bin(float x, float y) { return OP == 0 ? x + y : OP == 1 ? x - y : OP == 2 ? x * y : x / y; }
+template <int OP, bool VEC>
+__global__ void __launch_bounds__(256) k_binary(const gl_view a, const gl_view b, const gl_view d, int chunks) {
+    GL_PDL();
+    const int64_t row = blockIdx.x / chunks; const int64_t c0 = (int64_t) (blockIdx.x - row * chunks) * GL_CHUNK;
+    int64_t i1, i2, i3; gl_unrow(row, d, i1, i2, i3);
+    const float * ar = (const float *) (a.p + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3]);
+    const float * br = (const float *) (b.p + (i1 % b.ne[1]) * b.nb[1] + (i2 % b.ne[2]) * b.nb[2] + (i3 % b.ne[3]) * b.nb[3]);
+    float *       dr = (float *) (d.p + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]);
+    const int64_t n0 = d.ne[0], nb0 = b.ne[0];
+    if (VEC) {                                                                    // (nb0 == n0)
+        const int64_t i = c0 + threadIdx.x * 4;
+        if (i >= n0) return;
+        const float4 x = *(const float4 *) (ar + i), y = *(const float4 *) (br + i);
+        *(float4 *) (dr + i) = make_float4(gl_bin<OP>(x.x, y.x), gl_bin<OP>(x.y, y.y), gl_bin<OP>(x.z, y.z), gl_bin<OP>(x.w, y.w));
+    } else {
+        float x[4], y[4];
+        #pragma unroll
+        for (int k = 0; k < 4; ++k) { const int64_t i = c0 + k * 256 + threadIdx.x; if (i < n0) { x[k] = ar[i]; y[k] = br[nb0 == n0 ? i : i % nb0]; } }
+        #pragma unroll
+        for (int k = 0; k < 4; ++k) { const int64_t i = c0 + k * 256 + threadIdx.x; if (i < n0) dr[i] = gl_bin<OP>(x[k], y[k]); }
+    }
+}
+
+// ---- SCALE: y = x * s + b (contiguous) ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_scale(const float * x, float * y, int64_t n, float s, float b) {
+    GL_PDL();
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) y[i] = fmaf(x[i], s, b);
+}
+
+// ---- ROPE (GGML_ROPE_TYPE_NORMAL = 0: pairs (2i, 2i+1); NEOX = 2: pairs (i, i + n_dims/2)), YaRN as ops.cpp:5524-5547 -----------------
+struct gl_rope { int n_dims, neox; float freq_scale, ext_factor, attn_factor, theta_scale, corr0, corr1; const int32_t * pos; const float * ff; };
+__global__ void __launch_bounds__(128) k_rope(const gl_view x, const gl_view y, const gl_rope r) {
+    GL_PDL();
+    const int64_t i1 = blockIdx.x, i2 = blockIdx.y, i3 = blockIdx.z;          // head, token, batch
+    const float * xr = (const float *) (x.p + i1 * x.nb[1] + i2 * x.nb[2] + i3 * x.nb[3]);
+    float *       yr = (float *) (y.p + i1 * y.nb[1] + i2 * y.nb[2] + i3 * y.nb[3]);
+    const float p = (float) r.pos[i2];
+    for (int64_t ip = threadIdx.x; ip < x.ne[0] / 2; ip += blockDim.x) {       // pair index
+        const int64_t i0 = 2 * ip;
+        if (i0 >= r.n_dims) { yr[i0] = xr[i0]; yr[i0 + 1] = xr[i0 + 1]; continue; }     // channels beyond n_dims pass through
+        const float theta_extrap = p * powf(r.theta_scale, (float) ip) / (r.ff ? r.ff[ip] : 1.0f);
+        const float theta_interp = r.freq_scale * theta_extrap;
+        float theta = theta_interp, mscale = r.attn_factor;
+        if (r.ext_factor != 0.0f) {
+            const float yy = ((float) ip - r.corr0) / fmaxf(0.001f, r.corr1 - r.corr0);
+            const float ramp_mix = (1.0f - fminf(1.0f, fmaxf(0.0f, yy))) * r.ext_factor;
+            theta = theta_interp * (1.0f - ramp_mix) + theta_extrap * ramp_mix;
+            mscale *= 1.0f + 0.1f * logf(1.0f / r.freq_scale);
+        }
+        float sn, cs; sincosf(theta, &sn, &cs); sn *= mscale; cs *= mscale;
+        const int64_t ia = r.neox ? ip : i0, ib = r.neox ? ip + r.n_dims / 2 : i0 + 1;
+        const float x0 = xr[ia], x1 = xr[ib];
+        yr[ia] = x0 * cs - x1 * sn; yr[ib] = x0 * sn + x1 * cs;
+    }
+}
+
+// ---- SET_ROWS: dst row idx[i1, i2 % ne11, i3 % ne12] <- src row (i1, i2, i3), f32 -> f32 / f16 ---------------------------------------------
+template <typename T> static __device__ __forceinline__ T gl_cvt(float v);
+template <> __device__ __forceinline__ float  gl_cvt<float>(float v)  { return v; }
+template <> __device__ __forceinline__ __half gl_cvt<__half>(float v) { return __float2half_rn(v); }
+template <typename T, bool VEC>
+__global__ void __launch_bounds__(256) k_set_rows(const gl_view s, const gl_view idx, const gl_view d, int chunks) {
+    GL_PDL();
+    const int64_t r = blockIdx.x / chunks; const int64_t c0 = (int64_t) (blockIdx.x - r * chunks) * GL_CHUNK;
+    int64_t i1, i2, i3; gl_unrow(r, s, i1, i2, i3);
+    const int64_t row = *(const int64_t *) (idx.p + i1 * idx.nb[0] + (i2 % idx.ne[1]) * idx.nb[1] + (i3 % idx.ne[2]) * idx.nb[2]);
+    const float * sr = (const float *) (s.p + i1 * s.nb[1] + i2 * s.nb[2] + i3 * s.nb[3]);
+    T * dr = (T *) (d.p + row * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]);
+    const int64_t n0 = s.ne[0];
+    if (VEC) {                                                                    // src rows float4-aligned, dst rows 16-byte aligned
+        const int64_t i = c0 + threadIdx.x * 4;
+        if (i >= n0) return;
+        const float4 v = *(const float4 *) (sr + i);
+        if (sizeof(T) == 4) *(float4 *) (dr + i) = v;
+        else { __half2 lo = __floats2half2_rn(v.x, v.y), hi = __floats2half2_rn(v.z, v.w); uint2 o; o.x = *(unsigned *) &lo; o.y = *(unsigned *) &hi; *(uint2 *) (dr + i) = o; }
+    } else {
+        float v[4];
+        #pragma unroll
+        for (int k = 0; k < 4; ++k) { const int64_t i = c0 + k * 256 + threadIdx.x; if (i < n0) v[k] = sr[i]; }
+        #pragma unroll
+        for (int k = 0; k < 4; ++k) { const int64_t i = c0 + k * 256 + threadIdx.x; if (i < n0) dr[i] = gl_cvt<T>(v[k]); }
+    }
+}
+
+// ---- GET_ROWS (f32 rows): dst[:, i10, i11, i12] = src0[:, ids[i10, i11, i12], i11, i12] -------------------------------------------------
+__global__ void __launch_bounds__(256) k_get_rows_f32(const gl_view s, const gl_view idx, const gl_view d) {
+    GL_PDL();
+    int64_t i10, i11, i12; gl_unrow(blockIdx.x, d, i10, i11, i12);
+    const int32_t row = *(const int32_t *) (idx.p + i10 * idx.nb[0] + i11 * idx.nb[1] + i12 * idx.nb[2]);
+    const float * sr = (const float *) (s.p + (int64_t) row * s.nb[1] + i11 * s.nb[2] + i12 * s.nb[3]);
+    float * dr = (float *) (d.p + i10 * d.nb[1] + i11 * d.nb[2] + i12 * d.nb[3]);
+    for (int64_t i = threadIdx.x; i < d.ne[0]; i += blockDim.x) dr[i] = sr[i];
+}
+
+// ---- CPY / CONT / DUP: same logical element order, either side strided; f32 / f16 in, f32 / f16 out -----------------------------------------
+template <typename TS, typename TD>
+__global__ void __launch_bounds__(256) k_cpy(const gl_view s, const gl_view d, int64_t n) {
+    GL_PDL();
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    // element i in ggml order (dim 0 fastest) of EACH tensor: the shapes may differ as long as the counts agree (ggml_cpy)
+    int64_t r = i; const int64_t s0 = r % s.ne[0]; r /= s.ne[0]; const int64_t s1 = r % s.ne[1]; r /= s.ne[1]; const int64_t s2 = r % s.ne[2]; const int64_t s3 = r / s.ne[2];
+    r = i;         const int64_t d0 = r % d.ne[0]; r /= d.ne[0]; const int64_t d1 = r % d.ne[1]; r /= d.ne[1]; const int64_t d2 = r % d.ne[2]; const int64_t d3 = r / d.ne[2];
+    const TS v = *(const TS *) (s.p + s0 * s.nb[0] + s1 * s.nb[1] + s2 * s.nb[2] + s3 * s.nb[3]);
+    *(TD *) (d.p + d0 * d.nb[0] + d1 * d.nb[1] + d2 * d.nb[2] + d3 * d.nb[3]) = (TD) v;
+}
+
+// ---- GLU, SwiGLU: dst = silu(a) * b, a / b either two tensors (split) or the halves of one row; silu(x) = x / (1 + exp(-x)) ------------------
+static __device__ __forceinline__ float gl_swiglu1(float x, float y) { return x / (1.0f + expf(-x)) * y; }
+template <bool VEC>
+__global__ void __launch_bounds__(256) k_swiglu(const gl_view a, const gl_view b, const gl_view d, int64_t aoff, int64_t boff, int chunks) {
+    GL_PDL();
+    const int64_t row = blockIdx.x / chunks; const int64_t c0 = (int64_t) (blockIdx.x - row * chunks) * GL_CHUNK;
+    int64_t i1, i2, i3; gl_unrow(row, d, i1, i2, i3);
+    const float * ar = (const float *) (a.p + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3]) + aoff;
+    const float * br = (const float *) (b.p + i1 * b.nb[1] + i2 * b.nb[2] + i3 * b.nb[3]) + boff;
+    float *       dr = (float *) (d.p + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]);
+    const int64_t n0 = d.ne[0];
+    if (VEC) {
+        const int64_t i = c0 + threadIdx.x * 4;
+        if (i >= n0) return;
+        const float4 x = *(const float4 *) (ar + i), y = *(const float4 *) (br + i);
+        *(float4 *) (dr + i) = make_float4(gl_swiglu1(x.x, y.x), gl_swiglu1(x.y, y.y), gl_swiglu1(x.z, y.z), gl_swiglu1(x.w, y.w));
+    } else {
+        float x[4], y[4];
+        #pragma unroll
+        for (int k = 0; k < 4; ++k) { const int64_t i = c0 + k * 256 + threadIdx.x; if (i < n0) { x[k] = ar[i]; y[k] = br[i]; } }
+        #pragma unroll
+        for (int k = 0; k < 4; ++k) { const int64_t i = c0 + k * 256 + threadIdx.x; if (i < n0) dr[i] = gl_swiglu1(x[k], y[k]); }
+    }
+}
+
+template <typename... KArgs, typename... Args>
+static cudaError_t gl_launch(b200_ctx * ctx, void (*kernel)(KArgs...), dim3 grid, unsigned block, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = dim3(block); cfg.dynamicSmemBytes = 0; cfg.stream = ctx->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = ctx->pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
+// ---- which nodes we take ---------------------------------------------------------------------------------------------------------------
+static bool gl_same_shape(const ggml_tensor * a, const ggml_tensor * b) { return a->ne[0] == b->ne[0] && a->ne[1] == b->ne[1] && a->ne[2] == b->ne[2] && a->ne[3] == b->ne[3]; }
+static bool gl_can_repeat(const ggml_tensor * b, const ggml_tensor * a) {           // b broadcasts over a (ggml_can_repeat)
+    for (int i = 0; i < 4; ++i) if (b->ne[i] <= 0 || a->ne[i] % b->ne[i] != 0) return false;
+    return true;
+}
+static bool gl_grid_ok(const ggml_tensor * t) { return gl_nrows(t) * ((t->ne[0] + GL_CHUNK - 1) / GL_CHUNK) <= 0x7fffffff && t->ne[2] <= 65535 && t->ne[3] <= 65535; }
+
+bool b200_glue_supports(const struct ggml_tensor * op) {
+    const ggml_tensor * a = op->src[0], * b = op->src[1];
+    switch ((int) op->op) {
+        case GGML_OP_RMS_NORM:
+            return a->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && gl_contig_rows(a, 4) && gl_contig_rows(op, 4) && gl_grid_ok(op);
+        case GGML_OP_ADD: case GGML_OP_SUB: case GGML_OP_MUL: case GGML_OP_DIV:
+            return a->type == GGML_TYPE_F32 && b->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && gl_contig_rows(a, 4) && gl_contig_rows(b, 4) &&
+                   gl_contig_rows(op, 4) && gl_same_shape(a, op) && gl_can_repeat(b, a) && gl_grid_ok(op);
+        case GGML_OP_SCALE:
+            return a->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && gl_contiguous(a, 4) && gl_contiguous(op, 4);
+        case GGML_OP_ROPE: {
+            const int mode = op->op_params[2];
+            if (mode != 0 && mode != 2) return false;                       // normal and neox; mrope / vision stay on the CPU backend
+            if (a->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32 || b->type != GGML_TYPE_I32 || !gl_contig_rows(a, 4) || !gl_contig_rows(op, 4)) return false;
+            if (op->src[2] && (op->src[2]->type != GGML_TYPE_F32 || op->src[2]->ne[0] < op->op_params[1] / 2)) return false;
+            return a->ne[0] % 2 == 0 && op->op_params[1] % 2 == 0 && op->op_params[1] <= a->ne[0] && a->ne[1] <= 0x7fffffff && gl_grid_ok(op);
+        }
+        case GGML_OP_SET_ROWS:
+            return a->type == GGML_TYPE_F32 && b->type == GGML_TYPE_I64 && (op->type == GGML_TYPE_F16 || op->type == GGML_TYPE_F32) &&
+                   gl_contig_rows(a, 4) && op->nb[0] == gl_esize(op->type) && gl_grid_ok(a);
+        case GGML_OP_GET_ROWS:
+            return a->type == GGML_TYPE_F32 && b->type == GGML_TYPE_I32 && op->type == GGML_TYPE_F32 && gl_contig_rows(a, 4) && gl_contig_rows(op, 4) && gl_grid_ok(op);
+        case GGML_OP_CPY: case GGML_OP_CONT: case GGML_OP_DUP: {
+            const ggml_tensor * d = op;                                          // (ggml_cpy(a, b): the node is a view of b)
+            const bool ts = a->type == GGML_TYPE_F32 || a->type == GGML_TYPE_F16, td = d->type == GGML_TYPE_F32 || d->type == GGML_TYPE_F16;
+            return ts && td && gl_nelem(a) == gl_nelem(d) && gl_nelem(a) < ((int64_t) 1 << 40);
+        }
+        case GGML_OP_GLU:
+            if (op->op_params[0] != GGML_GLU_OP_SWIGLU || a->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32 || !gl_contig_rows(a, 4) || !gl_contig_rows(op, 4)) return false;
+            if (b && (b->type != GGML_TYPE_F32 || !gl_contig_rows(b, 4) || !gl_same_shape(a, b))) return false;
+            return gl_grid_ok(op);
+        default: return false;
+    }
+}
+
+// RMS_NORM node + the MUL node right behind it that scales it by a weight row: both outputs from one kernel.  Returns
+// B200_ERR_UNSUPPORTED when the pair does not have that shape (the caller then runs the nodes one by one).
+int b200_glue_rms_norm_mul(b200_ctx * ctx, struct ggml_tensor * norm, struct ggml_tensor * mul) {
+    if (norm->op != GGML_OP_RMS_NORM || mul->op != GGML_OP_MUL || !b200_glue_supports(norm) || !b200_glue_supports(mul)) return B200_ERR_UNSUPPORTED;
+    if (mul->src[0] != norm) return B200_ERR_UNSUPPORTED;
+    const ggml_tensor * w = mul->src[1];
+    if (w->ne[0] != norm->ne[0] || w == norm) return B200_ERR_UNSUPPORTED;
+    // the graph allocator may give the MUL the norm's own memory (in place): then only the product is stored; any other overlap: no fusion
+    const char * pa = (const char *) norm->data, * pb = (const char *) mul->data;
+    const size_t na = (size_t) gl_nrows(norm) * norm->nb[1], nb = (size_t) gl_nrows(mul) * mul->nb[1];
+    const bool same = pa == pb && norm->nb[1] == mul->nb[1] && norm->nb[2] == mul->nb[2] && norm->nb[3] == mul->nb[3];
+    if (!same && pa < pb + nb && pb < pa + na) return B200_ERR_UNSUPPORTED;
+    if (!gl_contiguous(norm, 4) && !same) return B200_ERR_UNSUPPORTED;
+    float eps; memcpy(&eps, norm->op_params, 4);
+    const ggml_tensor * x = norm->src[0];
+    if (x->ne[0] <= 8192 && gl_vec_ok(x) && gl_vec_ok(norm) && gl_vec_ok(w) && gl_vec_ok(mul)) {
+        const unsigned block = x->ne[0] <= 1024 ? 128 : x->ne[0] <= 2048 ? 256 : x->ne[0] <= 4096 ? 512 : 1024;
+        B200_LAUNCH(ctx, B200_K_GLUE, gl_launch(ctx, k_rms_norm<true, true>, dim3((unsigned) gl_nrows(norm)), block, gl_of(x), gl_of(norm), gl_of(w), gl_of(mul), eps, same ? 0 : 1));
+    } else B200_LAUNCH(ctx, B200_K_GLUE, gl_launch(ctx, k_rms_norm<true, false>, dim3((unsigned) gl_nrows(norm)), 256, gl_of(x), gl_of(norm), gl_of(w), gl_of(mul), eps, same ? 0 : 1));
+    return B200_OK;
+}
+
+// ---- dispatch -------------------------------------------------------------------------------------------------------------------------
+#define GL_LAUNCH(...) B200_LAUNCH(ctx, B200_K_GLUE, __VA_ARGS__)
+int b200_glue_compute(b200_ctx * ctx, struct ggml_tensor * op) {
+    const ggml_tensor * a = op->src[0], * b = op->src[1];
+    cudaStream_t st = ctx->stream;
+    const unsigned rows = (unsigned) gl_nrows(op);
+    const int chunks = (int) ((op->ne[0] + GL_CHUNK - 1) / GL_CHUNK);       // CTAs per row of the row-wise kernels
+    switch ((int) op->op) {
+        case GGML_OP_RMS_NORM: {
+            float eps; memcpy(&eps, op->op_params, 4);
+            if (a->ne[0] <= 8192 && gl_vec_ok(a) && gl_vec_ok(op)) {
+                const unsigned block = a->ne[0] <= 1024 ? 128 : a->ne[0] <= 2048 ? 256 : a->ne[0] <= 4096 ? 512 : 1024;
+                GL_LAUNCH(gl_launch(ctx, k_rms_norm<false, true>, dim3(rows), block, gl_of(a), gl_of(op), gl_of(op), gl_of(op), eps, 1));
+            } else GL_LAUNCH(gl_launch(ctx, k_rms_norm<false, false>, dim3(rows), 256, gl_of(a), gl_of(op), gl_of(op), gl_of(op), eps, 1));
+            return B200_OK;
+        }
+        case GGML_OP_ADD: case GGML_OP_SUB: case GGML_OP_MUL: case GGML_OP_DIV: {
+            const bool vec = b->ne[0] == op->ne[0] && gl_vec_ok(a) && gl_vec_ok(b) && gl_vec_ok(op);
+            const dim3 grid(rows * chunks);
+            #define GL_BIN(OP) do { if (vec) GL_LAUNCH(gl_launch(ctx, k_binary<OP, true>, grid, 256, gl_of(a), gl_of(b), gl_of(op), chunks)); \
+                                    else     GL_LAUNCH(gl_launch(ctx, k_binary<OP, false>, grid, 256, gl_of(a), gl_of(b), gl_of(op), chunks)); } while (0)
+            if (op->op == GGML_OP_ADD) GL_BIN(0); else if (op->op == GGML_OP_SUB) GL_BIN(1); else if (op->op == GGML_OP_MUL) GL_BIN(2); else GL_BIN(3);
+            #undef GL_BIN
+            return B200_OK;
+        }
+        case GGML_OP_SCALE: {
+            float s, bias; memcpy(&s, op->op_params, 4); memcpy(&bias, op->op_params + 1, 4);
+            const int64_t n = gl_nelem(op);
+            GL_LAUNCH(gl_launch(ctx, k_scale, dim3((unsigned) ((n + 255) / 256)), 256, (const float *) a->data, (float *) op->data, n, s, bias));
+            return B200_OK;
+        }
+        case GGML_OP_ROPE: {
+            gl_rope r;
+            float freq_base, beta_fast, beta_slow;
+            r.n_dims = op->op_params[1]; r.neox = op->op_params[2] == 2;
+            const int n_ctx_orig = op->op_params[4];
+            memcpy(&freq_base, op->op_params + 5, 4);     memcpy(&r.freq_scale, op->op_params + 6, 4);
+            memcpy(&r.ext_factor, op->op_params + 7, 4);  memcpy(&r.attn_factor, op->op_params + 8, 4);
+            memcpy(&beta_fast, op->op_params + 9, 4);     memcpy(&beta_slow, op->op_params + 10, 4);
+            r.theta_scale = powf(freq_base, -2.0f / r.n_dims);
+            // ggml_rope_yarn_corr_dims (ggml.c:4255-4269)
+            auto corr = [&](float n_rot) { return r.n_dims * logf(n_ctx_orig / (n_rot * 2.0f * (float) M_PI)) / (2.0f * logf(freq_base)); };
+            r.corr0 = fmaxf(0.0f, floorf(corr(beta_fast))); r.corr1 = fminf((float) r.n_dims - 1.0f, ceilf(corr(beta_slow)));
+            r.pos = (const int32_t *) b->data; r.ff = op->src[2] ? (const float *) op->src[2]->data : nullptr;
+            GL_LAUNCH(gl_launch(ctx, k_rope, dim3(dim3((unsigned) op->ne[1], (unsigned) op->ne[2], (unsigned) op->ne[3])), 128, gl_of(a), gl_of(op), r));
+            return B200_OK;
+        }
+        case GGML_OP_SET_ROWS: {
+            const unsigned srows = (unsigned) gl_nrows(a);
+            const int sch = (int) ((a->ne[0] + GL_CHUNK - 1) / GL_CHUNK);
+            const bool vec = gl_vec_ok(a) && ((uintptr_t) op->data & 15) == 0 && op->nb[1] % 16 == 0 && op->nb[2] % 16 == 0 && op->nb[3] % 16 == 0;
+            const dim3 grid(srows * sch);
+            if (op->type == GGML_TYPE_F16) { if (vec) GL_LAUNCH(gl_launch(ctx, k_set_rows<__half, true>, grid, 256, gl_of(a), gl_of(b), gl_of(op), sch));
+                                             else     GL_LAUNCH(gl_launch(ctx, k_set_rows<__half, false>, grid, 256, gl_of(a), gl_of(b), gl_of(op), sch)); }
+            else                           { if (vec) GL_LAUNCH(gl_launch(ctx, k_set_rows<float, true>, grid, 256, gl_of(a), gl_of(b), gl_of(op), sch));
+                                             else     GL_LAUNCH(gl_launch(ctx, k_set_rows<float, false>, grid, 256, gl_of(a), gl_of(b), gl_of(op), sch)); }
+            return B200_OK;
+        }
+        case GGML_OP_GET_ROWS:
+            GL_LAUNCH(gl_launch(ctx, k_get_rows_f32, dim3(rows), 256, gl_of(a), gl_of(b), gl_of(op)));
+            return B200_OK;
+        case GGML_OP_CPY: case GGML_OP_CONT: case GGML_OP_DUP: {
+            const int64_t n = gl_nelem(a);
+            const unsigned grid = (unsigned) ((n + 255) / 256);
+            const bool sf = a->type == GGML_TYPE_F32, df = op->type == GGML_TYPE_F32;
+            if (sf && df)       GL_LAUNCH(gl_launch(ctx, k_cpy<float, float>, dim3(grid), 256, gl_of(a), gl_of(op), n));
+            else if (sf && !df) GL_LAUNCH(gl_launch(ctx, k_cpy<float, __half>, dim3(grid), 256, gl_of(a), gl_of(op), n));
+            else if (!sf && df) GL_LAUNCH(gl_launch(ctx, k_cpy<__half, float>, dim3(grid), 256, gl_of(a), gl_of(op), n));
+            else                GL_LAUNCH(gl_launch(ctx, k_cpy<__half, __half>, dim3(grid), 256, gl_of(a), gl_of(op), n));
+            return B200_OK;
+        }
+        case GGML_OP_GLU: {
+            const bool swapped = op->op_params[1] != 0;
+            const int64_t nc = op->ne[0];
+            const ggml_tensor * bb = b ? b : a;
+            const int64_t aoff = b ? 0 : swapped ? nc : 0, boff = b ? 0 : swapped ? 0 : nc;
+            const bool vec = nc % 4 == 0 && gl_vec_ok(a) && gl_vec_ok(bb) && gl_vec_ok(op);
+            const dim3 grid(rows * chunks);
+            if (vec) GL_LAUNCH(gl_launch(ctx, k_swiglu<true>, grid, 256, gl_of(a), gl_of(bb), gl_of(op), aoff, boff, chunks));
+            else     GL_LAUNCH(gl_launch(ctx, k_swiglu<false>, grid, 256, gl_of(a), gl_of(bb), gl_of(op), aoff, boff, chunks));
+            return B200_OK;
+        }
+        default:
+            b200_set_error("glue: op %d not implemented", (int) op->op);
+            return B200_ERR_UNSUPPORTED;
+    }
+}

@@ -7,3 +7,5 @@
 struct ggml_tensor;
 bool b200_glue_supports(const struct ggml_tensor * op);
 int  b200_glue_compute(b200_ctx * ctx, struct ggml_tensor * op);
+// RMS_NORM + the MUL by the norm weight right behind it as one kernel; B200_ERR_UNSUPPORTED when the pair does not fit
+int  b200_glue_rms_norm_mul(b200_ctx * ctx, struct ggml_tensor * norm, struct ggml_tensor * mul);

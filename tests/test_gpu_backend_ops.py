@@ -81,3 +81,34 @@ def test_backend_ops_with_load_time_repack(op):
     ok, passed, total, fail, holes = summarize(txt, lambda l: False)
     assert rc == 0 and passed == total and not fail, "\n".join(fail[:20])
     assert ok >= 100
+
+
+GLUE_OPS = ["RMS_NORM", "RMS_NORM_MUL_ADD", "ADD", "MUL", "SCALE", "ROPE", "SET_ROWS", "GET_ROWS", "CPY", "CONT", "SWIGLU"]
+
+
+@pytest.mark.parametrize("op", GLUE_OPS)
+def test_backend_ops_glue(op):
+    """the ops between the hot ops of a llama-architecture graph (b200_glue.cu), so that the whole decode graph
+    stays on the device.  Cases the plugin declines (other types, non-contiguous rows) run nowhere and are not counted; every case
+    it claims must pass against ggml-cpu"""
+    rc, txt = run_harness(op, tag="_glue")
+    ok, passed, total, fail, holes = summarize(txt, lambda l: False)
+    assert rc == 0 and passed == total and not fail, "\n".join(fail[:20])
+    assert ok >= 4, f"only {ok} {op} cases ran on the device"
+
+
+@pytest.mark.parametrize("wtype,K,M,chunk", [(14, 4096, 1024, 1 << 20), (14, 4096, 64, 100000), (8, 4096, 512, 65536 + 34),
+                                             (2, 2048, 256, 18 * 1000), (12, 4096, 256, 1 << 18), (14, 14336, 128, 1 << 22)])
+def test_chunked_async_upload_repacks(wtype, K, M, chunk):
+    """llama_model_loader without mmap uploads every weight in ascending chunks through set_tensor_async
+    (src/llama-model-loader.cpp:1136-1186): the chunked upload must end in the device layout, read back as GGUF bytes and give
+    the same MUL_MAT bits as a whole-tensor write (tests/upload_probe.cpp, built from include/ggml-b200-abi.h only)"""
+    exe = os.path.join(OUT, "upload_probe")
+    os.makedirs(OUT, exist_ok=True)
+    if not os.path.exists(exe):
+        subprocess.check_call(["g++", "-std=c++17", "-O1", "-I" + os.path.join(ROOT, "include"), os.path.join(ROOT, "tests", "upload_probe.cpp"),
+                               "-o", exe, "-ldl"])
+    p = subprocess.run([exe, PLUGIN, str(wtype), str(K), str(M), str(chunk)], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+    assert p.returncode == 0 and "upload_probe: OK" in p.stdout, p.stdout[-2000:]
+    if wtype in (14, 8, 2):                                   # types with a device layout (b200_repack_supported)
+        assert "repacked chunked=1 whole=1" in p.stdout, p.stdout
