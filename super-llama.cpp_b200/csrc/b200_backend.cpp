@@ -334,6 +334,27 @@ static bool ranges_overlap(const ggml_tensor * a, const ggml_tensor * b) {
     const char * pa = (const char *) a->data, * pb = (const char *) b->data;
     return pa < pb + tensor_nbytes(b) && pb < pa + tensor_nbytes(a);
 }
+static int next_work(const ggml_cgraph * g, int i) {            // next node after i that launches something, or -1
+    for (int j = i + 1; j < g->n_nodes; ++j) if (!op_is_view((int) g->nodes[j]->op) && tensor_nelements(g->nodes[j]) != 0) return j;
+    return -1;
+}
+// node i is a ROPE: if it opens the KV-cache update of a llama layer -- [ROPE(Q)] ROPE(K) SET_ROWS(K) SET_ROWS(V), only views in between --
+// run the whole run as one launch and return the index of its last node; -1 when it is not that pattern (b200_glue_rope_kv checks the rest)
+static int try_rope_kv(b200_backend_ctx * c, ggml_cgraph * g, int i) {
+    int j1 = next_work(g, i), j2 = j1 < 0 ? -1 : next_work(g, j1), j3 = -1;
+    if (j2 < 0) return -1;
+    ggml_tensor * rq = nullptr, * rk, * sk, * sv;
+    if (g->nodes[j1]->op == GGML_OP_ROPE) {
+        j3 = next_work(g, j2);
+        if (j3 < 0) return -1;
+        rq = g->nodes[i]; rk = g->nodes[j1]; sk = g->nodes[j2]; sv = g->nodes[j3];
+    } else { rk = g->nodes[i]; sk = g->nodes[j1]; sv = g->nodes[j2]; j3 = j2; }
+    if (sk->op != GGML_OP_SET_ROWS || sv->op != GGML_OP_SET_ROWS) return -1;
+    if (b200_glue_rope_kv(c->ctx, rq, rk, sk, sv) != B200_OK) return -1;
+    ggml_tensor * outs[4] = { rq, rk, sk, sv };
+    for (ggml_tensor * t : outs) if (t) b200_note_write(c->ctx, t->data, tensor_nbytes(t));
+    return j3;
+}
 static enum ggml_status run_nodes(b200_backend_ctx * c, ggml_cgraph * g) {
     c->ctx->qcache.valid = 0; c->ctx->mcache.valid = 0;      // tensors may have been rewritten through buffer set_tensor since the last graph
     for (int i = 0; i < g->n_nodes; ++i) {
@@ -365,6 +386,13 @@ static enum ggml_status run_nodes(b200_backend_ctx * c, ggml_cgraph * g) {
             for (int k = 0; k < ng; ++k) { w[k] = to_b200(g->nodes[group[k]]->src[0]); d[k] = to_b200(g->nodes[group[k]]); wp[k] = &w[k]; dp[k] = &d[k]; }
             rc = b200_mul_mat_multi(c->ctx, wp, ng, &x, dp);
             if (rc == B200_OK) i = group[ng - 1];                       // (views between the members need no work)
+        } else if (node->op == GGML_OP_ADD && !fuse_off() && i + 2 < g->n_nodes && g->nodes[i + 1]->op == GGML_OP_RMS_NORM && g->nodes[i + 2]->op == GGML_OP_MUL &&
+                   (rc = b200_glue_add_rms_norm_mul(c->ctx, node, g->nodes[i + 1], g->nodes[i + 2])) == B200_OK) {
+            // residual add + the norm behind it + the norm weight: one launch
+            for (int k = 0; k < 3; ++k) b200_note_write(c->ctx, g->nodes[i + k]->data, tensor_nbytes(g->nodes[i + k]));
+            i += 2;
+        } else if (node->op == GGML_OP_ROPE && !fuse_off() && (rc = try_rope_kv(c, g, i)) >= 0) {
+            i = rc; rc = B200_OK;                                      // [ROPE(Q)] ROPE(K) SET_ROWS(K) SET_ROWS(V): one launch
         } else if (node->op == GGML_OP_RMS_NORM && !fuse_off() && i + 1 < g->n_nodes && g->nodes[i + 1]->op == GGML_OP_MUL &&
                    (rc = b200_glue_rms_norm_mul(c->ctx, node, g->nodes[i + 1])) == B200_OK) {
             b200_note_write(c->ctx, node->data, tensor_nbytes(node));
@@ -480,9 +508,38 @@ static void be_event_wait(ggml_backend_t be, ggml_backend_event_t ev) {
     b200_backend_ctx * c = (b200_backend_ctx *) be->context; B200_CHECK(cudaSetDevice(c->device));
     B200_CHECK(cudaStreamWaitEvent(c->ctx->stream, (cudaEvent_t) ev->context, 0));
 }
+// graph_optimize (ggml_backend_sched calls it on every split BEFORE the graph allocator runs, ggml-backend.cpp:1321-1324, so moving a node
+// cannot break buffer reuse): MUL_MATs of plain weight tensors that read the same activation are pulled up next to the first of them,
+// same weight types side by side.  llama's attention block arrives as  Q = wq x, ROPE(Q), V = wv x, K = wk x, ROPE(K), SET_ROWS x 2:
+// afterwards the three matmuls are adjacent (one launch for equal types, be_graph_compute) and so are the four glue nodes
+// (b200_glue_rope_kv).  A weight matmul depends on its activation and a leaf only, so it may run anywhere after the activation exists.
+static bool is_weight_leaf(const ggml_tensor * w) {
+    return w && w->op == GGML_OP_NONE && w->view_src == nullptr && w->buffer && w->buffer->usage == GGML_BACKEND_BUFFER_USAGE_WEIGHTS;
+}
+static void be_graph_optimize(ggml_backend_t, ggml_cgraph * g) {
+    static const bool off = [] { const char * e = getenv("GGML_B200_NO_REORDER"); return e && atoi(e); }();
+    if (off || fuse_off()) return;
+    for (int i = 0; i < g->n_nodes; ++i) {
+        ggml_tensor * a = g->nodes[i];
+        if (a->op != GGML_OP_MUL_MAT || !is_weight_leaf(a->src[0])) continue;
+        int at = i + 1;                                             // where the next member of the group goes
+        int members[3] = { i, -1, -1 }, nm = 1;
+        for (int j = i + 1; j < g->n_nodes && j <= i + 16 && nm < 3; ++j) {
+            ggml_tensor * b = g->nodes[j];
+            if (b->op != GGML_OP_MUL_MAT || b->src[1] != a->src[1] || !is_weight_leaf(b->src[0])) continue;
+            if (j != at) { for (int k = j; k > at; --k) g->nodes[k] = g->nodes[k - 1]; g->nodes[at] = b; }
+            members[nm++] = at; ++at;
+        }
+        if (nm == 3) {                                              // equal weight types next to each other, first-come order otherwise
+            ggml_tensor * m[3] = { g->nodes[members[0]], g->nodes[members[1]], g->nodes[members[2]] };
+            if (m[0]->src[0]->type != m[1]->src[0]->type && m[0]->src[0]->type == m[2]->src[0]->type) { g->nodes[members[1]] = m[2]; g->nodes[members[2]] = m[1]; }
+        }
+        i = at - 1;
+    }
+}
 static const ggml_backend_i k_backend_iface = {
     be_name, be_free, be_set_tensor_async, be_get_tensor_async, be_cpy_tensor_async, be_synchronize,
-    nullptr, nullptr, nullptr, nullptr, be_graph_compute, be_event_record, be_event_wait, nullptr,
+    nullptr, nullptr, nullptr, nullptr, be_graph_compute, be_event_record, be_event_wait, be_graph_optimize,
 };
 
 // ---- device -------------------------------------------------------------------------------------------

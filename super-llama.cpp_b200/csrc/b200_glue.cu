@@ -54,6 +54,42 @@ static __device__ __forceinline__ float block_sum(float s, float * red) {       
 // ---- RMS_NORM: y = x / sqrt(mean(x^2) + eps), one CTA per row; optionally followed by MUL with the norm weight (every llama norm):
 // one pass, both nodes' outputs written.  CACHED: the row (<= 8 * blockDim elements, float4-aligned) stays in registers between the
 // sum and the scaling ----------------------------------------------------------------------------------------------------------------
+// k_add_rms_norm_mul: the residual ADD in front of the norm taken along (x = a + b stored to the ADD node's dst u, then as below): the
+// three nodes between two matmuls of a llama layer in one launch
+__global__ void __launch_bounds__(1024) k_add_rms_norm_mul(const gl_view a, const gl_view b, const gl_view u, const gl_view y, const gl_view w, const gl_view z, float eps, int write_y) {
+    GL_PDL();
+    int64_t i1, i2, i3; gl_unrow(blockIdx.x, a, i1, i2, i3);
+    const float * ar = (const float *) (a.p + i1 * a.nb[1] + i2 * a.nb[2] + i3 * a.nb[3]);
+    const float * br = (const float *) (b.p + i1 * b.nb[1] + i2 * b.nb[2] + i3 * b.nb[3]);
+    float *       ur = (float *) (u.p + i1 * u.nb[1] + i2 * u.nb[2] + i3 * u.nb[3]);
+    float *       yr = (float *) (y.p + i1 * y.nb[1] + i2 * y.nb[2] + i3 * y.nb[3]);
+    const float * wr = (const float *) (w.p + (i1 % w.ne[1]) * w.nb[1] + (i2 % w.ne[2]) * w.nb[2] + (i3 % w.ne[3]) * w.nb[3]);
+    float *       zr = (float *) (z.p + i1 * z.nb[1] + i2 * z.nb[2] + i3 * z.nb[3]);
+    __shared__ float red[32];
+    const int64_t n0 = a.ne[0];
+    float4 v[2], g[2];
+    float s = 0.0f;
+    #pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const int64_t i = ((int64_t) k * blockDim.x + threadIdx.x) * 4;
+        const float4 p = i < n0 ? *(const float4 *) (ar + i) : make_float4(0, 0, 0, 0), q = i < n0 ? *(const float4 *) (br + i) : make_float4(0, 0, 0, 0);
+        g[k] = i < n0 ? *(const float4 *) (wr + i) : make_float4(0, 0, 0, 0);
+        v[k] = make_float4(p.x + q.x, p.y + q.y, p.z + q.z, p.w + q.w);
+    }
+    #pragma unroll
+    for (int k = 0; k < 2; ++k) { s = fmaf(v[k].x, v[k].x, s); s = fmaf(v[k].y, v[k].y, s); s = fmaf(v[k].z, v[k].z, s); s = fmaf(v[k].w, v[k].w, s); }
+    const float scale = rsqrtf(block_sum(s, red) / (float) n0 + eps);
+    #pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const int64_t i = ((int64_t) k * blockDim.x + threadIdx.x) * 4;
+        if (i >= n0) continue;
+        *(float4 *) (ur + i) = v[k];
+        const float4 o = make_float4(v[k].x * scale, v[k].y * scale, v[k].z * scale, v[k].w * scale);
+        if (write_y) *(float4 *) (yr + i) = o;
+        *(float4 *) (zr + i) = make_float4(o.x * g[k].x, o.y * g[k].y, o.z * g[k].z, o.w * g[k].w);
+    }
+}
+
 template <bool MUL, bool CACHED>
 __global__ void __launch_bounds__(1024) k_rms_norm(const gl_view x, const gl_view y, const gl_view w, const gl_view z, float eps, int write_y) {
     GL_PDL();
@@ -130,15 +166,19 @@ __global__ void __launch_bounds__(256) k_scale(const float * x, float * y, int64
 
 // ---- ROPE (GGML_ROPE_TYPE_NORMAL = 0: pairs (2i, 2i+1); NEOX = 2: pairs (i, i + n_dims/2)), YaRN as ops.cpp:5524-5547 -----------------
 struct gl_rope { int n_dims, neox; float freq_scale, ext_factor, attn_factor, theta_scale, corr0, corr1; const int32_t * pos; const float * ff; };
-__global__ void __launch_bounds__(128) k_rope(const gl_view x, const gl_view y, const gl_rope r) {
-    GL_PDL();
-    const int64_t i1 = blockIdx.x, i2 = blockIdx.y, i3 = blockIdx.z;          // head, token, batch
+// one head row (i1 = head, i2 = token, i3 = batch); `cache` (optional): the f16 KV-cache row segment that takes a copy of the result
+static __device__ __forceinline__ void gl_rope_row(const gl_view & x, const gl_view & y, const gl_rope & r, int64_t i1, int64_t i2, int64_t i3, __half * cache) {
     const float * xr = (const float *) (x.p + i1 * x.nb[1] + i2 * x.nb[2] + i3 * x.nb[3]);
     float *       yr = (float *) (y.p + i1 * y.nb[1] + i2 * y.nb[2] + i3 * y.nb[3]);
     const float p = (float) r.pos[i2];
     for (int64_t ip = threadIdx.x; ip < x.ne[0] / 2; ip += blockDim.x) {       // pair index
         const int64_t i0 = 2 * ip;
-        if (i0 >= r.n_dims) { yr[i0] = xr[i0]; yr[i0 + 1] = xr[i0 + 1]; continue; }     // channels beyond n_dims pass through
+        if (i0 >= r.n_dims) {                                                   // channels beyond n_dims pass through
+            const float x0 = xr[i0], x1 = xr[i0 + 1];
+            yr[i0] = x0; yr[i0 + 1] = x1;
+            if (cache) { cache[i0] = __float2half_rn(x0); cache[i0 + 1] = __float2half_rn(x1); }
+            continue;
+        }
         const float theta_extrap = p * powf(r.theta_scale, (float) ip) / (r.ff ? r.ff[ip] : 1.0f);
         const float theta_interp = r.freq_scale * theta_extrap;
         float theta = theta_interp, mscale = r.attn_factor;
@@ -151,8 +191,14 @@ __global__ void __launch_bounds__(128) k_rope(const gl_view x, const gl_view y, 
         float sn, cs; sincosf(theta, &sn, &cs); sn *= mscale; cs *= mscale;
         const int64_t ia = r.neox ? ip : i0, ib = r.neox ? ip + r.n_dims / 2 : i0 + 1;
         const float x0 = xr[ia], x1 = xr[ib];
-        yr[ia] = x0 * cs - x1 * sn; yr[ib] = x0 * sn + x1 * cs;
+        const float y0 = x0 * cs - x1 * sn, y1 = x0 * sn + x1 * cs;
+        yr[ia] = y0; yr[ib] = y1;
+        if (cache) { cache[ia] = __float2half_rn(y0); cache[ib] = __float2half_rn(y1); }
     }
+}
+__global__ void __launch_bounds__(128) k_rope(const gl_view x, const gl_view y, const gl_rope r) {
+    GL_PDL();
+    gl_rope_row(x, y, r, blockIdx.x, blockIdx.y, blockIdx.z, nullptr);          // head, token, batch
 }
 
 // ---- SET_ROWS: dst row idx[i1, i2 % ne11, i3 % ne12] <- src row (i1, i2, i3), f32 -> f32 / f16 ---------------------------------------------
@@ -228,6 +274,52 @@ __global__ void __launch_bounds__(256) k_swiglu(const gl_view a, const gl_view b
         for (int k = 0; k < 4; ++k) { const int64_t i = c0 + k * 256 + threadIdx.x; if (i < n0) { x[k] = ar[i]; y[k] = br[i]; } }
         #pragma unroll
         for (int k = 0; k < 4; ++k) { const int64_t i = c0 + k * 256 + threadIdx.x; if (i < n0) dr[i] = gl_swiglu1(x[k], y[k]); }
+    }
+}
+
+// ---- ROPE(Q) + ROPE(K) + SET_ROWS(K -> cache) + SET_ROWS(V -> cache): the four nodes between the QKV matmuls and the attention of a
+// llama layer as one launch.  CTAs [0, nq): one Q head row each; [nq, nq + nk): one K head row each, whose result also goes (f16) to
+// the cache row idx[token] that the SET_ROWS node behind it names; the rest: chunks of the V rows (as k_set_rows) -----------------------------
+struct gl_rope_kv {
+    gl_view qx, qy; gl_rope qr; int nq;
+    gl_view kx, ky; gl_rope kr; int nk;
+    gl_view kidx, kd; int64_t k_ne0;              // SET_ROWS(K): its src is ky seen as rows of k_ne0 floats (k_ne0 % ky.ne[0] == 0)
+    gl_view vs, vidx, vd; int vchunks;
+};
+__global__ void __launch_bounds__(128) k_rope_kv(const gl_rope_kv a) {
+    GL_PDL();
+    int b = blockIdx.x;
+    if (b < a.nq) {
+        const int64_t i1 = b % a.qx.ne[1], t = b / a.qx.ne[1];
+        gl_rope_row(a.qx, a.qy, a.qr, i1, t % a.qx.ne[2], t / a.qx.ne[2], nullptr);
+        return;
+    }
+    b -= a.nq;
+    if (b < a.nk) {
+        const int64_t i1 = b % a.kx.ne[1], t = b / a.kx.ne[1];
+        const int64_t e = (int64_t) b * a.ky.ne[0];                              // first element of this head row in the contiguous result
+        const int64_t r = e / a.k_ne0, c = e - r * a.k_ne0;
+        const int64_t row = *(const int64_t *) (a.kidx.p + r * a.kidx.nb[0]);
+        gl_rope_row(a.kx, a.ky, a.kr, i1, t % a.kx.ne[2], t / a.kx.ne[2], (__half *) (a.kd.p + row * a.kd.nb[1]) + c);
+        return;
+    }
+    b -= a.nk;
+    {                                                                            // V: source row r, chunk of GL_CHUNK floats, two float4 per thread
+        const int64_t r = b / a.vchunks; const int64_t c0 = (int64_t) (b - r * a.vchunks) * GL_CHUNK;
+        const int64_t row = *(const int64_t *) (a.vidx.p + r * a.vidx.nb[0]);
+        const float * sr = (const float *) (a.vs.p + r * a.vs.nb[1]);
+        __half * dr = (__half *) (a.vd.p + row * a.vd.nb[1]);
+        const int64_t n0 = a.vs.ne[0];
+        float4 v[2];
+        #pragma unroll
+        for (int k = 0; k < 2; ++k) { const int64_t i = c0 + (k * 128 + threadIdx.x) * 4; if (i < n0) v[k] = *(const float4 *) (sr + i); }
+        #pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int64_t i = c0 + (k * 128 + threadIdx.x) * 4;
+            if (i >= n0) continue;
+            __half2 lo = __floats2half2_rn(v[k].x, v[k].y), hi = __floats2half2_rn(v[k].z, v[k].w); uint2 o; o.x = *(unsigned *) &lo; o.y = *(unsigned *) &hi;
+            *(uint2 *) (dr + i) = o;
+        }
     }
 }
 
@@ -307,6 +399,85 @@ int b200_glue_rms_norm_mul(b200_ctx * ctx, struct ggml_tensor * norm, struct ggm
     return B200_OK;
 }
 
+static gl_rope gl_rope_params(const ggml_tensor * op) {
+    gl_rope r;
+    float freq_base, beta_fast, beta_slow;
+    r.n_dims = op->op_params[1]; r.neox = op->op_params[2] == 2;
+    const int n_ctx_orig = op->op_params[4];
+    memcpy(&freq_base, op->op_params + 5, 4);     memcpy(&r.freq_scale, op->op_params + 6, 4);
+    memcpy(&r.ext_factor, op->op_params + 7, 4);  memcpy(&r.attn_factor, op->op_params + 8, 4);
+    memcpy(&beta_fast, op->op_params + 9, 4);     memcpy(&beta_slow, op->op_params + 10, 4);
+    r.theta_scale = powf(freq_base, -2.0f / r.n_dims);
+    // ggml_rope_yarn_corr_dims (ggml.c:4255-4269)
+    auto corr = [&](float n_rot) { return r.n_dims * logf(n_ctx_orig / (n_rot * 2.0f * (float) M_PI)) / (2.0f * logf(freq_base)); };
+    r.corr0 = fmaxf(0.0f, floorf(corr(beta_fast))); r.corr1 = fminf((float) r.n_dims - 1.0f, ceilf(corr(beta_slow)));
+    r.pos = (const int32_t *) op->src[1]->data; r.ff = op->src[2] ? (const float *) op->src[2]->data : nullptr;
+    return r;
+}
+
+// byte spans of two strided tensors do not meet
+static bool gl_span_disjoint(const ggml_tensor * a, const ggml_tensor * b) {
+    const char * pa = (const char *) a->data, * pb = (const char *) b->data;
+    size_t na = gl_esize(a->type), nb = gl_esize(b->type);
+    for (int i = 0; i < 4; ++i) { na += (size_t) (a->ne[i] - 1) * a->nb[i]; nb += (size_t) (b->ne[i] - 1) * b->nb[i]; }
+    return pa + na <= pb || pb + nb <= pa;
+}
+static bool gl_same_view(const ggml_tensor * a, const ggml_tensor * b) { return a->data == b->data && a->nb[1] == b->nb[1] && a->nb[2] == b->nb[2] && a->nb[3] == b->nb[3]; }
+
+// [ROPE(Q)] + ROPE(K) + SET_ROWS(K) + SET_ROWS(V) as one launch (rq may be NULL); B200_ERR_UNSUPPORTED when the nodes do not have the
+// shape of a llama layer's KV-cache update
+int b200_glue_rope_kv(b200_ctx * ctx, struct ggml_tensor * rq, struct ggml_tensor * rk, struct ggml_tensor * sk, struct ggml_tensor * sv) {
+    if (!rk || !sk || !sv || rk->op != GGML_OP_ROPE || sk->op != GGML_OP_SET_ROWS || sv->op != GGML_OP_SET_ROWS || (rq && rq->op != GGML_OP_ROPE)) return B200_ERR_UNSUPPORTED;
+    if (!b200_glue_supports(rk) || !b200_glue_supports(sk) || !b200_glue_supports(sv) || (rq && !b200_glue_supports(rq))) return B200_ERR_UNSUPPORTED;
+    const ggml_tensor * ks = sk->src[0], * vs = sv->src[0], * kidx = sk->src[1], * vidx = sv->src[1];
+    // SET_ROWS(K) stores exactly the ROPE(K) result, seen as 2-D rows; both caches f16, one index per source row
+    if (ks->data != rk->data || !gl_contiguous(rk, 4) || !gl_contiguous(ks, 4) || gl_nelem(ks) != gl_nelem(rk) || ks->ne[2] != 1 || ks->ne[3] != 1) return B200_ERR_UNSUPPORTED;
+    if (ks->ne[0] % rk->ne[0] != 0 || sk->type != GGML_TYPE_F16 || sv->type != GGML_TYPE_F16 || vs->ne[2] != 1 || vs->ne[3] != 1) return B200_ERR_UNSUPPORTED;
+    if (kidx->ne[0] != ks->ne[1] || kidx->ne[1] != 1 || kidx->ne[2] != 1 || vidx->ne[0] != vs->ne[1] || vidx->ne[1] != 1 || vidx->ne[2] != 1) return B200_ERR_UNSUPPORTED;
+    if (((uintptr_t) sk->data & 1) || sk->nb[1] % 2 || !gl_vec_ok(vs) || ((uintptr_t) sv->data & 15) || sv->nb[1] % 16) return B200_ERR_UNSUPPORTED;
+    // independent sections: nothing one of them writes may be something another reads or writes (rope in place is fine)
+    const ggml_tensor * outs[4] = { rq, rk, sk, sv };
+    const ggml_tensor * ins[4]  = { rq ? rq->src[0] : nullptr, rk->src[0], nullptr, vs };
+    for (int o = 0; o < 4; ++o) for (int i = 0; i < 4; ++i) {
+        if (!outs[o] || o == i) continue;
+        if (outs[i] && o < i && !gl_span_disjoint(outs[o], outs[i])) return B200_ERR_UNSUPPORTED;
+        if (ins[i] && !gl_span_disjoint(outs[o], ins[i])) return B200_ERR_UNSUPPORTED;
+    }
+    for (int o = 0; o < 4; ++o) if (outs[o] && (!gl_span_disjoint(outs[o], kidx) || !gl_span_disjoint(outs[o], vidx) || !gl_span_disjoint(outs[o], rk->src[1]))) return B200_ERR_UNSUPPORTED;
+    gl_rope_kv a;
+    memset(&a, 0, sizeof a);
+    if (rq) { a.qx = gl_of(rq->src[0]); a.qy = gl_of(rq); a.qr = gl_rope_params(rq); a.nq = (int) gl_nrows(rq); }
+    a.kx = gl_of(rk->src[0]); a.ky = gl_of(rk); a.kr = gl_rope_params(rk); a.nk = (int) gl_nrows(rk);
+    a.kidx = gl_of(kidx); a.kd = gl_of(sk); a.k_ne0 = ks->ne[0];
+    a.vs = gl_of(vs); a.vidx = gl_of(vidx); a.vd = gl_of(sv); a.vchunks = (int) ((vs->ne[0] + GL_CHUNK - 1) / GL_CHUNK);
+    if (gl_nrows(rk) > 0x3fffffff || (rq && gl_nrows(rq) > 0x3fffffff)) return B200_ERR_UNSUPPORTED;
+    const int64_t grid = (int64_t) a.nq + a.nk + vs->ne[1] * a.vchunks;
+    if (grid > 0x7fffffff) return B200_ERR_UNSUPPORTED;
+    B200_LAUNCH(ctx, B200_K_GLUE, gl_launch(ctx, k_rope_kv, dim3((unsigned) grid), 128, a));
+    return B200_OK;
+}
+
+// ADD + RMS_NORM + MUL (residual add, norm, norm weight) in one launch; B200_ERR_UNSUPPORTED when the triple does not fit
+int b200_glue_add_rms_norm_mul(b200_ctx * ctx, struct ggml_tensor * add, struct ggml_tensor * norm, struct ggml_tensor * mul) {
+    if (add->op != GGML_OP_ADD || norm->op != GGML_OP_RMS_NORM || mul->op != GGML_OP_MUL || norm->src[0] != add || mul->src[0] != norm) return B200_ERR_UNSUPPORTED;
+    if (!b200_glue_supports(add) || !b200_glue_supports(norm) || !b200_glue_supports(mul)) return B200_ERR_UNSUPPORTED;
+    const ggml_tensor * a = add->src[0], * b = add->src[1], * w = mul->src[1];
+    if (!gl_same_shape(a, b) || w->ne[0] != norm->ne[0] || w == norm || w == add || add->ne[0] > 8192) return B200_ERR_UNSUPPORTED;
+    const ggml_tensor * all[6] = { a, b, add, norm, mul, w };
+    for (int i = 0; i < 6; ++i) if (!gl_vec_ok(all[i])) return B200_ERR_UNSUPPORTED;
+    // every thread reads its elements of a, b, w before it writes the same elements of add / norm / mul: an output may coincide exactly
+    // with a or b (in-place nodes) or be disjoint from the inputs, nothing in between; of the outputs only norm and mul may coincide
+    const ggml_tensor * ins[3] = { a, b, w }, * outs[3] = { add, norm, mul };
+    for (int o = 0; o < 3; ++o) for (int i = 0; i < 3; ++i) if (!gl_span_disjoint(outs[o], ins[i]) && !(i < 2 && gl_same_view(outs[o], ins[i]))) return B200_ERR_UNSUPPORTED;
+    if (!gl_span_disjoint(add, norm) || !gl_span_disjoint(add, mul)) return B200_ERR_UNSUPPORTED;
+    const bool same = gl_same_view(norm, mul);
+    if (!same && !gl_span_disjoint(norm, mul)) return B200_ERR_UNSUPPORTED;
+    float eps; memcpy(&eps, norm->op_params, 4);
+    const unsigned block = add->ne[0] <= 1024 ? 128 : add->ne[0] <= 2048 ? 256 : add->ne[0] <= 4096 ? 512 : 1024;
+    B200_LAUNCH(ctx, B200_K_GLUE, gl_launch(ctx, k_add_rms_norm_mul, dim3((unsigned) gl_nrows(add)), block, gl_of(a), gl_of(b), gl_of(add), gl_of(norm), gl_of(w), gl_of(mul), eps, same ? 0 : 1));
+    return B200_OK;
+}
+
 // ---- dispatch -------------------------------------------------------------------------------------------------------------------------
 #define GL_LAUNCH(...) B200_LAUNCH(ctx, B200_K_GLUE, __VA_ARGS__)
 int b200_glue_compute(b200_ctx * ctx, struct ggml_tensor * op) {
@@ -339,18 +510,7 @@ int b200_glue_compute(b200_ctx * ctx, struct ggml_tensor * op) {
             return B200_OK;
         }
         case GGML_OP_ROPE: {
-            gl_rope r;
-            float freq_base, beta_fast, beta_slow;
-            r.n_dims = op->op_params[1]; r.neox = op->op_params[2] == 2;
-            const int n_ctx_orig = op->op_params[4];
-            memcpy(&freq_base, op->op_params + 5, 4);     memcpy(&r.freq_scale, op->op_params + 6, 4);
-            memcpy(&r.ext_factor, op->op_params + 7, 4);  memcpy(&r.attn_factor, op->op_params + 8, 4);
-            memcpy(&beta_fast, op->op_params + 9, 4);     memcpy(&beta_slow, op->op_params + 10, 4);
-            r.theta_scale = powf(freq_base, -2.0f / r.n_dims);
-            // ggml_rope_yarn_corr_dims (ggml.c:4255-4269)
-            auto corr = [&](float n_rot) { return r.n_dims * logf(n_ctx_orig / (n_rot * 2.0f * (float) M_PI)) / (2.0f * logf(freq_base)); };
-            r.corr0 = fmaxf(0.0f, floorf(corr(beta_fast))); r.corr1 = fminf((float) r.n_dims - 1.0f, ceilf(corr(beta_slow)));
-            r.pos = (const int32_t *) b->data; r.ff = op->src[2] ? (const float *) op->src[2]->data : nullptr;
+            const gl_rope r = gl_rope_params(op);
             GL_LAUNCH(gl_launch(ctx, k_rope, dim3(dim3((unsigned) op->ne[1], (unsigned) op->ne[2], (unsigned) op->ne[3])), 128, gl_of(a), gl_of(op), r));
             return B200_OK;
         }

@@ -9,3 +9,7 @@ bool b200_glue_supports(const struct ggml_tensor * op);
 int  b200_glue_compute(b200_ctx * ctx, struct ggml_tensor * op);
 // RMS_NORM + the MUL by the norm weight right behind it as one kernel; B200_ERR_UNSUPPORTED when the pair does not fit
 int  b200_glue_rms_norm_mul(b200_ctx * ctx, struct ggml_tensor * norm, struct ggml_tensor * mul);
+// ADD + RMS_NORM + MUL (the residual add in front of a llama norm) as one launch, same contract
+int  b200_glue_add_rms_norm_mul(b200_ctx * ctx, struct ggml_tensor * add, struct ggml_tensor * norm, struct ggml_tensor * mul);
+// [ROPE(Q)] + ROPE(K) + SET_ROWS(K result -> f16 cache) + SET_ROWS(V -> f16 cache) as one launch (rq may be NULL), same contract
+int  b200_glue_rope_kv(b200_ctx * ctx, struct ggml_tensor * rq, struct ggml_tensor * rk, struct ggml_tensor * sk, struct ggml_tensor * sv);

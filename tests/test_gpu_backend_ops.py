@@ -83,7 +83,7 @@ def test_backend_ops_with_load_time_repack(op):
     assert ok >= 100
 
 
-GLUE_OPS = ["RMS_NORM", "RMS_NORM_MUL_ADD", "ADD", "MUL", "SCALE", "ROPE", "SET_ROWS", "GET_ROWS", "CPY", "CONT", "SWIGLU"]
+GLUE_OPS = ["RMS_NORM", "RMS_NORM_MUL_ADD", "ADD_RMS_NORM", "ADD", "MUL", "SCALE", "ROPE", "SET_ROWS", "GET_ROWS", "CPY", "CONT", "SWIGLU"]
 
 
 @pytest.mark.parametrize("op", GLUE_OPS)
@@ -112,3 +112,29 @@ def test_chunked_async_upload_repacks(wtype, K, M, chunk):
     assert p.returncode == 0 and "upload_probe: OK" in p.stdout, p.stdout[-2000:]
     if wtype in (14, 8, 2):                                   # types with a device layout (b200_repack_supported)
         assert "repacked chunked=1 whole=1" in p.stdout, p.stdout
+
+
+@pytest.mark.parametrize("vtype", [12, 14])
+def test_layer_fusions_bit_identical(vtype):
+    """what be_graph_optimize / be_graph_compute do to the head of a llama layer -- weight matmuls of one activation pulled together and
+    launched as one, ADD + RMS_NORM + MUL as one kernel, ROPE(Q) + ROPE(K) + SET_ROWS(K) + SET_ROWS(V) as one kernel, the graph recorded
+    into a CUDA graph and replayed -- changes no bit of any node's output against the same nodes run one by one
+    (tests/fusion_probe.cpp, built from include/ggml-b200-abi.h only)"""
+    exe = os.path.join(OUT, "fusion_probe")
+    os.makedirs(OUT, exist_ok=True)
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-I" + os.path.join(ROOT, "include"), os.path.join(ROOT, "tests", "fusion_probe.cpp"), "-o", exe, "-ldl"])
+    outs = []
+    for tag, extra in (("fused", {"GGML_B200_GRAPH_STATS": "1"}), ("plain", {"GGML_B200_NO_FUSE": "1", "GGML_B200_GRAPHS": "0"})):
+        f = os.path.join(OUT, f"fusion_probe_{vtype}_{tag}.bin")
+        p = subprocess.run([exe, PLUGIN, f, str(vtype)], env=dict(os.environ, **extra), stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+        assert p.returncode == 0 and "fusion_probe: OK" in p.stdout, p.stdout[-2000:]
+        if tag == "fused":
+            order = [l for l in p.stdout.splitlines() if "node order" in l][0].split(":")[-1].split()
+            iq, ik, iv = order.index("Qcur"), order.index("Kcur"), order.index("Vcur")
+            assert max(iq, ik, iv) - min(iq, ik, iv) == 2, order            # the three matmuls adjacent
+            assert abs(iq - ik) == 1 or vtype == 12, order                  # equal weight types side by side
+            assert "1 recorded, 4 replayed" in p.stdout, p.stdout           # first run launch by launch, second recorded, four graph launches
+        outs.append(open(f, "rb").read())
+        os.remove(f)
+    assert len(outs[0]) == len(outs[1]) and len(outs[0]) > 0
+    assert outs[0] == outs[1]
