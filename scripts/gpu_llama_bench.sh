@@ -11,4 +11,4 @@ LB=oracle/_ref/avx2/llama-bench
 if [ -z "${SKIP_CPU:-}" ]; then
   timeout 900 $LB -m $G -p 512 -n 128 -r ${REPS:-2} -t $(nproc) -fa 1 -ngl 0 "$@" > gpurun_out/llama_bench_cpu_$MODEL-$QUANT.txt 2>&1; echo "cpu rc=$?"; tail -6 gpurun_out/llama_bench_cpu_$MODEL-$QUANT.txt
 fi
-GGML_BACKEND_PATH=$PWD/super-llama.cpp_b200/libggml-b200.so timeout 900 $LB -m $G -p 512 -n 128 -r ${REPS:-2} -t $(nproc) -fa 1 -ngl 99 "$@" > gpurun_out/llama_bench_b200_$MODEL-$QUANT.txt 2>&1; echo "b200 rc=$?"; tail -12 gpurun_out/llama_bench_b200_$MODEL-$QUANT.txt
+GGML_B200_GRAPH_STATS=1 GGML_BACKEND_PATH=$PWD/super-llama.cpp_b200/libggml-b200.so timeout 900 $LB -m $G -p 512 -n 128 -r ${REPS:-2} -t $(nproc) -fa 1 -ngl 99 "$@" > gpurun_out/llama_bench_b200_$MODEL-$QUANT.txt 2>&1; echo "b200 rc=$?"; tail -12 gpurun_out/llama_bench_b200_$MODEL-$QUANT.txt

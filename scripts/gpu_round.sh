@@ -17,3 +17,8 @@ for op in MUL_MAT MUL_MAT_ID FLASH_ATTN_EXT; do
   GGML_BACKEND_PATH=$PWD/super-llama.cpp_b200/libggml-b200.so timeout 900 oracle/_ref/avx2/test-backend-ops test -b B200_0 -o $op > gpurun_out/tbo_$op.log 2>&1; echo "test-backend-ops $op rc=$?"; tail -3 gpurun_out/tbo_$op.log
 done
 fi
+# the reference's own llama-bench (compiled in place by `make -C oracle llama`), ggml-cpu vs the plugin, on random-init GGUFs
+if [ -x oracle/_ref/avx2/llama-bench ] && [ -z "${SKIP_LB:-}" ]; then
+  REPS=3 bash scripts/gpu_llama_bench.sh 8b q4_k_m
+  REPS=3 bash scripts/gpu_llama_bench.sh tinyllama q4_0
+fi

@@ -253,7 +253,7 @@ __global__ void __launch_bounds__(256) k_cpy(const gl_view s, const gl_view d, i
 }
 
 // ---- GLU, SwiGLU: dst = silu(a) * b, a / b either two tensors (split) or the halves of one row; silu(x) = x / (1 + exp(-x)) ------------------
-static __device__ __forceinline__ float gl_swiglu1(float x, float y) { return x / (1.0f + expf(-x)) * y; }
+static __device__ __forceinline__ float gl_swiglu1(float x, float y) { return b200_swiglu1(x, y); }      // (b200_common.cuh: the GEMV's fused quantizer computes the same)
 template <bool VEC>
 __global__ void __launch_bounds__(256) k_swiglu(const gl_view a, const gl_view b, const gl_view d, int64_t aoff, int64_t boff, int chunks) {
     GL_PDL();

@@ -1,5 +1,6 @@
 // fusion_probe.cpp -- the start of a llama layer as llama.cpp hands it to a backend (src/models/llama.cpp, build_attn with a KV cache):
 //   ADD(residual) RMS_NORM MUL(norm weight)  Q = wq x  RESHAPE ROPE(Q)  V = wv x  RESHAPE  K = wk x  RESHAPE ROPE(K)  SET_ROWS(K) SET_ROWS(V)
+//   gate = wg x  up = wu x  GLU(SWIGLU)  down = wd glu  ADD(residual)           (the FFN, fed from the same norm to keep the probe small)
 // driven through the plugin ABI only (include/ggml-b200-abi.h, dlopen): graph_optimize, then graph_compute five times with new inputs,
 // positions and cache rows each time (first run launch by launch, second recorded into a CUDA graph, then replays).  Every output of
 // every round is appended to <out file>; tests/test_gpu_backend_ops.py runs the probe with the plugin's fusions on and with
@@ -59,18 +60,19 @@ int main(int argc, char ** argv) {
     ggml_backend_t be = dev->iface.init_backend(dev, nullptr);
     REQUIRE(be);
     ggml_backend_buffer_type_t buft = dev->iface.get_buffer_type(dev);
-    const int64_t E = 4096, HD = 128, NH = 32, NKV = 8, KV = NKV * HD, NCTX = 512;
+    const int64_t E = 4096, HD = 128, NH = 32, NKV = 8, KV = NKV * HD, NCTX = 512, F = 14336;
     arena wa, ca;
-    wa.size = 64u << 20; wa.buf = buft->iface.alloc_buffer(buft, wa.size); ca.size = 16u << 20; ca.buf = buft->iface.alloc_buffer(buft, ca.size);
+    wa.size = 192u << 20; wa.buf = buft->iface.alloc_buffer(buft, wa.size); ca.size = 16u << 20; ca.buf = buft->iface.alloc_buffer(buft, ca.size);
     REQUIRE(wa.buf && ca.buf);
     wa.base = (char *) wa.buf->iface.get_base(wa.buf); wa.used = 0; ca.base = (char *) ca.buf->iface.get_base(ca.buf); ca.used = 0;
     wa.buf->usage = GGML_BACKEND_BUFFER_USAGE_WEIGHTS;
     std::vector<ggml_tensor *> all;
     // weights
     ggml_tensor * wq = mk(all, wa, GGML_TYPE_Q4_K, E, E, 1, "wq"), * wk = mk(all, wa, GGML_TYPE_Q4_K, E, KV, 1, "wk"), * wv = mk(all, wa, vtype, E, KV, 1, "wv");
+    ggml_tensor * wg = mk(all, wa, GGML_TYPE_Q4_K, E, F, 1, "wg"), * wu = mk(all, wa, GGML_TYPE_Q4_K, E, F, 1, "wu"), * wd = mk(all, wa, vtype, F, E, 1, "wd");
     ggml_tensor * nw = mk(all, wa, GGML_TYPE_F32, E, 1, 1, "norm_w");
     uint32_t s = 4242;
-    for (ggml_tensor * w : { wq, wk, wv }) {
+    for (ggml_tensor * w : { wq, wk, wv, wg, wu, wd }) {
         const size_t ts = tsize(w->type), n = w->nb[2];
         std::vector<uint8_t> host(n);
         for (auto & b : host) { s = s * 1664525u + 1013904223u; b = (uint8_t) (s >> 24); }
@@ -105,7 +107,12 @@ int main(int argc, char ** argv) {
     ggml_tensor * sk  = view(all, kc, KV, NCTX, 1, "set_k"); sk->op = GGML_OP_SET_ROWS; sk->src[0] = k2; sk->src[1] = kidx; sk->src[2] = nullptr;
     ggml_tensor * sv  = view(all, vc, KV, NCTX, 1, "set_v"); sv->op = GGML_OP_SET_ROWS; sv->src[0] = v2; sv->src[1] = vidx;
     sk->view_src = kc; sv->view_src = vc;
-    ggml_tensor * nodes[] = { add, nrm, x, q, q3, qr, v, v3, k, k3, kr, k2, v2, sk, sv };
+    ggml_tensor * ga  = mk(all, ca, GGML_TYPE_F32, F, 1, 1, "ffn_gate"); ga->op = GGML_OP_MUL_MAT; ga->src[0] = wg; ga->src[1] = x;
+    ggml_tensor * up  = mk(all, ca, GGML_TYPE_F32, F, 1, 1, "ffn_up");   up->op = GGML_OP_MUL_MAT; up->src[0] = wu; up->src[1] = x;
+    ggml_tensor * glu = mk(all, ca, GGML_TYPE_F32, F, 1, 1, "ffn_swiglu"); glu->op = GGML_OP_GLU; glu->src[0] = ga; glu->src[1] = up; glu->op_params[0] = GGML_GLU_OP_SWIGLU;
+    ggml_tensor * dn  = mk(all, ca, GGML_TYPE_F32, E, 1, 1, "ffn_out");  dn->op = GGML_OP_MUL_MAT; dn->src[0] = wd; dn->src[1] = glu;
+    ggml_tensor * res = mk(all, ca, GGML_TYPE_F32, E, 1, 1, "l_out");    res->op = GGML_OP_ADD; res->src[0] = dn; res->src[1] = add;
+    ggml_tensor * nodes[] = { add, nrm, x, q, q3, qr, v, v3, k, k3, kr, k2, v2, sk, sv, ga, up, glu, dn, res };
     const int nn = (int) (sizeof nodes / sizeof nodes[0]);
     for (int i = 0; i < nn; ++i) if (nodes[i]->op != GGML_OP_RESHAPE) REQUIRE(dev->iface.supports_op(dev, nodes[i]));
     ggml_cgraph g; memset(&g, 0, sizeof g); g.size = nn; g.n_nodes = nn; g.nodes = nodes;
@@ -132,7 +139,7 @@ int main(int argc, char ** argv) {
         be->iface.set_tensor_async(be, pos, &p, 0, 4); be->iface.set_tensor_async(be, kidx, &row_k, 0, 8); be->iface.set_tensor_async(be, vidx, &row_v, 0, 8);
         REQUIRE(be->iface.graph_compute(be, &g) == GGML_STATUS_SUCCESS);
         be->iface.synchronize(be);
-        for (ggml_tensor * t : { add, x, q, k, v, qr, kr, kc, vc }) {
+        for (ggml_tensor * t : { add, x, q, k, v, qr, kr, kc, vc, ga, up, glu, dn, res }) {
             std::vector<uint8_t> hb(t->nb[3]);
             ca.buf->iface.get_tensor(ca.buf, t, hb.data(), 0, hb.size());
             fwrite(hb.data(), 1, hb.size(), out);
