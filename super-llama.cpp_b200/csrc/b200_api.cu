@@ -286,6 +286,31 @@ extern "C" int b200_mul_mat_swiglu(b200_ctx * ctx, const b200_tensor * w, const 
     return rc;
 }
 
+// gate = wg x, up = wu x, glu = swiglu(gate, up) for one activation column in ONE launch: the tensor-core q4_K GEMV hands every CTA the
+// same rows of both weights, so its epilogue can finish the GLU node as well (no launch, no re-read of the two n_ff columns).
+// B200_ERR_UNSUPPORTED when that kernel does not serve the shape: the caller runs b200_mul_mat_multi and the GLU op then.
+extern "C" int b200_mul_mat_gate_up_swiglu(b200_ctx * ctx, const b200_tensor * wg, const b200_tensor * wu, const b200_tensor * x,
+                                           b200_tensor * gate, b200_tensor * up, b200_tensor * glu) {
+    if (!ctx || !wg || !wu || !x || !gate || !up || !glu) { b200_set_error("mul_mat_gate_up_swiglu: null argument"); return B200_ERR_INVALID; }
+    const b200_tensor * w[2] = { wg, wu };
+    const int64_t K = wg->ne[0], M = wg->ne[1];
+    b200_tensor * cols[3] = { gate, up, glu };
+    for (b200_tensor * t : cols)
+        if (t->type != B200_TYPE_F32 || t->nb[0] != 4 || t->ne[0] != M || t->ne[1] != 1 || t->ne[2] != 1 || t->ne[3] != 1) { b200_set_error("mul_mat_gate_up_swiglu: outputs are f32 columns of M values"); return B200_ERR_UNSUPPORTED; }
+    if (wu->ne[0] != K || wu->ne[1] != M || x->ne[0] != K || x->ne[1] != 1 || x->ne[2] != 1 || x->ne[3] != 1 || x->type != B200_TYPE_F32 || x->nb[0] != 4) { b200_set_error("mul_mat_gate_up_swiglu: shape mismatch"); return B200_ERR_UNSUPPORTED; }
+    if (q8_1_variant_env() != B200_Q8_1_X86 || !b200_gemv_stream_supported(wg, x) || !b200_gemv_stream_supported(wu, x) || !b200_gemv_mma_supported(ctx, w, 2, x)) {
+        b200_set_error("mul_mat_gate_up_swiglu: not a tensor-core GEMV shape"); return B200_ERR_UNSUPPORTED;
+    }
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    int rc;
+    const void * image = nullptr;
+    if (K > fused_quant_max_k()) { image = quantized_activations(ctx, x, B200_Q8_1_X86, &rc); if (!image) return rc; }
+    float * d[2] = { (float *) gate->data, (float *) up->data };
+    rc = b200_launch_gemv_mma(ctx, w, 2, x, image, d, nullptr, (float *) glu->data);
+    for (b200_tensor * t : cols) b200_note_write(ctx, t->data, b200_tensor_span(t));
+    return rc;
+}
+
 // n MUL_MATs that share src1 (wq/wk/wv, ffn_gate/ffn_up): one launch when the streaming GEMV can take them all
 extern "C" int b200_mul_mat_multi(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, b200_tensor * const * dst) {
     if (!ctx || !w || !x || !dst || n <= 0) { b200_set_error("mul_mat_multi: bad arguments"); return B200_ERR_INVALID; }

@@ -382,6 +382,22 @@ static int try_glu_mul_mat(b200_backend_ctx * c, ggml_cgraph * g, int i) {
     if (b200_mul_mat_swiglu(c->ctx, &w, &ga, &up, &go, &d) != B200_OK) return -1;
     return j;
 }
+// nodes a, b: two adjacent MUL_MATs of one activation.  If the next node is GLU(SWIGLU) of exactly their results (ffn_gate, ffn_up, in
+// either order) the tensor-core GEMV finishes it in its epilogue (b200_mul_mat_gate_up_swiglu).  Returns the GLU's index or -1.
+static int try_gate_up_glu(b200_backend_ctx * c, ggml_cgraph * g, int a, int b) {
+    const int j = next_work(g, b);
+    if (j < 0) return -1;
+    ggml_tensor * glu = g->nodes[j], * na = g->nodes[a], * nb = g->nodes[b];
+    if (glu->op != GGML_OP_GLU || glu->op_params[0] != GGML_GLU_OP_SWIGLU || glu->op_params[1] != 0 || !glu->src[1]) return -1;
+    ggml_tensor * gate = glu->src[0] == na ? na : glu->src[0] == nb ? nb : nullptr, * up = glu->src[1] == na ? na : glu->src[1] == nb ? nb : nullptr;
+    if (!gate || !up || gate == up || glu->type != GGML_TYPE_F32 || !tensor_rows_contiguous(glu)) return -1;
+    // the GLU column is written while other CTAs may still be reading the activation / weights, and beside gate and up
+    const ggml_tensor * others[5] = { gate, up, gate->src[0], up->src[0], gate->src[1] };
+    for (const ggml_tensor * o : others) if (ranges_overlap(glu, o)) return -1;
+    b200_tensor wg = to_b200(gate->src[0]), wu = to_b200(up->src[0]), x = to_b200(gate->src[1]), dg = to_b200(gate), du = to_b200(up), dl = to_b200(glu);
+    if (b200_mul_mat_gate_up_swiglu(c->ctx, &wg, &wu, &x, &dg, &du, &dl) != B200_OK) return -1;
+    return j;
+}
 static enum ggml_status run_nodes(b200_backend_ctx * c, ggml_cgraph * g) {
     c->ctx->qcache.valid = 0; c->ctx->mcache.valid = 0;      // tensors may have been rewritten through buffer set_tensor since the last graph
     for (int i = 0; i < g->n_nodes; ++i) {
@@ -407,7 +423,9 @@ static enum ggml_status run_nodes(b200_backend_ctx * c, ggml_cgraph * g) {
                 group[ng++] = j;
             }
         }
-        if (ng > 1) {
+        if (ng == 2 && (rc = try_gate_up_glu(c, g, group[0], group[1])) >= 0) {
+            i = rc; rc = B200_OK; c->n_fuse[0] += 1; c->n_fuse[4] += 1;       // ffn_gate + ffn_up + SwiGLU: one launch
+        } else if (ng > 1) {
             b200_tensor w[3], d[3], x = to_b200(node->src[1]);
             const b200_tensor * wp[3]; b200_tensor * dp[3];
             for (int k = 0; k < ng; ++k) { w[k] = to_b200(g->nodes[group[k]]->src[0]); d[k] = to_b200(g->nodes[group[k]]); wp[k] = &w[k]; dp[k] = &d[k]; }

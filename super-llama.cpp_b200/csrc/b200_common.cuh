@@ -339,7 +339,7 @@ int  b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int 
                              const b200_rowsplit_peers * peers = nullptr, const b200_gemv_ids * idm = nullptr, const b200_gemv_glu * glu = nullptr);
 bool b200_gemv_mma_supported(const b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x);
 int  b200_launch_gemv_mma(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, const void * image, float * const * dst,
-                          const b200_rowsplit_peers * peers);
+                          const b200_rowsplit_peers * peers, float * glu = nullptr);   // glu: n == 2 (gate, up), also stores swiglu(gate, up)
 int  b200_launch_exchange_unpack(b200_ctx * ctx, const void * ll, float * dst, int64_t M, unsigned * ctrl);
 #define B200_GEMV_FUSED_QUANT_MAX_K 16384   // above this, one quantize launch + image beats one quantization per CTA
 #define B200_GEMV_MAX_COLS 8

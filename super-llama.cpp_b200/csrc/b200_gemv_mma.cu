@@ -39,6 +39,8 @@ struct gq_args {
     int dbg;
     int npf;                                                            // items per warp to prefetch into L2 behind the ring fill
     int npre;                                                           // ring stages to fill before the dependency wait
+    int pair; float * glu;                                              // pair: two equal-sized segments (ffn_gate, ffn_up) interleaved group by group so that one CTA owns
+                                                                        // the same rows of both, and the epilogue also stores glu[row] = swiglu(gate[row], up[row]) (the GLU node behind them)
     int n_first, skew;                                                  // CTAs 0 .. n_first-1 get (1024 + skew) / 1024 of an even share, the others (1024 - skew) / 1024
     unsigned long long * trace; int trace_cap;                          // b200_debug_trace (measurement only)
 };
@@ -80,7 +82,7 @@ __global__ void __launch_bounds__(NW * 32, NW == 24 ? 1 : 2) k_gemv_q4k_mma(cons
     const int64_t wa = 1024 + p.skew, wb = 1024 - p.skew, n1 = p.n_first;
     const int64_t W = n1 * wa + ((int64_t) gridDim.x - n1) * wb;
     auto cut = [&](int64_t b) { const int64_t pre = b <= n1 ? b * wa : n1 * wa + (b - n1) * wb; return (int) ((int64_t) G * pre / W); };
-    const int g_lo = cut(blockIdx.x), g_hi = cut((int64_t) blockIdx.x + 1);
+    const int g_lo = p.pair ? cut(blockIdx.x) & ~1 : cut(blockIdx.x), g_hi = p.pair ? cut((int64_t) blockIdx.x + 1) & ~1 : cut((int64_t) blockIdx.x + 1);   // (G is even in pair mode)
     const int nitems_cta = (p.dbg & 4) ? 0 : (g_hi - g_lo) * nchunks;
 
     unsigned long long * rec = nullptr;
@@ -98,7 +100,7 @@ __global__ void __launch_bounds__(NW * 32, NW == 24 ? 1 : 2) k_gemv_q4k_mma(cons
     auto issue = [&](int stage) {
         if (lane == 0) {
             int gg = g_lo + pgl, s = 0;
-            if (gg >= G0) { gg -= G0; s = 1; if (gg >= G1) { gg -= G1; s = 2; } }
+            if (p.pair) { s = gg & 1; gg >>= 1; } else if (gg >= G0) { gg -= G0; s = 1; if (gg >= G1) { gg -= G1; s = 2; } }
             const uint32_t bar = bar0 + 8 * stage;
             mbar_arrive_expect_tx(bar, GQ_STAGE_BYTES);
             tma_load_2d_hint(ring + stage * GQ_STAGE_BYTES, &maps.m[s], pch * (GQ_CHUNK / 4), gg * GQ_ROWS, bar, policy);
@@ -121,7 +123,7 @@ __global__ void __launch_bounds__(NW * 32, NW == 24 ? 1 : 2) k_gemv_q4k_mma(cons
         for (int i = 0; i < p.npf && it < nitems_cta; ++i, it += NW) {
             const int gl = it / nchunks, ch = it - gl * nchunks;
             int gg = g_lo + gl, s = 0;
-            if (gg >= G0) { gg -= G0; s = 1; if (gg >= G1) { gg -= G1; s = 2; } }
+            if (p.pair) { s = gg & 1; gg >>= 1; } else if (gg >= G0) { gg -= G0; s = 1; if (gg >= G1) { gg -= G1; s = 2; } }
             tma_prefetch_l2_2d(&maps.m[s], ch * (GQ_CHUNK / 4), gg * GQ_ROWS);
         }
     }
@@ -217,6 +219,15 @@ __global__ void __launch_bounds__(NW * 32, NW == 24 ? 1 : 2) k_gemv_q4k_mma(cons
     b200_trace_stamp(rec, 7);                                             // every warp done
 
     // add the chunk partials of every row in chunk order and store (or send) the row
+    if (p.pair) {                                                         // local groups alternate gate, up: one thread finishes both values of a row
+        for (int i = threadIdx.x; i < ((g_hi - g_lo) >> 1) * GQ_ROWS; i += blockDim.x) {
+            const int pl = i >> 3, r = i & 7;
+            float vg = 0.0f, vu = 0.0f;
+            if (!(p.dbg & 4)) for (int ch = 0; ch < nchunks; ++ch) { vg += s_par[((2 * pl) * nchunks + ch) * GQ_ROWS + r]; vu += s_par[((2 * pl + 1) * nchunks + ch) * GQ_ROWS + r]; }
+            const int rowi = ((g_lo >> 1) + pl) * GQ_ROWS + r;
+            if (rowi < p.M[0]) { p.dst[0][rowi] = vg; p.dst[1][rowi] = vu; p.glu[rowi] = b200_swiglu1(vg, vu); }
+        }
+    } else
     for (int i = threadIdx.x; i < (g_hi - g_lo) * GQ_ROWS; i += blockDim.x) {
         const int gl = i >> 3, r = i & 7;
         float v = 0.0f;
@@ -337,8 +348,10 @@ static int gq_weight_map(const b200_tensor * w, CUtensorMap * out) {
 
 // n <= 3 raw q4_K weights sharing the activation column x; dst[i] is where weight i's rows go (see b200_launch_gemv_stream)
 int b200_launch_gemv_mma(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, const void * image, float * const * dst,
-                         const b200_rowsplit_peers * peers) {
+                         const b200_rowsplit_peers * peers, float * glu) {
     gq_args p; gq_maps maps;
+    if (glu && (n != 2 || peers || w[0]->ne[1] != w[1]->ne[1])) { b200_set_error("gemv_mma: the SwiGLU epilogue takes two weights of equal shape"); return B200_ERR_UNSUPPORTED; }
+    p.pair = glu ? 1 : 0; p.glu = glu;
     memset(&maps, 0, sizeof(maps));
     p.nseg = n; p.K = (int) w[0]->ne[0]; p.x = (const float *) x->data;
     p.aq = (const int8_t *) image; p.ads = image ? (const __half2 *) ((const int8_t *) image + p.K) : nullptr;
@@ -365,7 +378,7 @@ int b200_launch_gemv_mma(b200_ctx * ctx, const b200_tensor * const * w, int n, c
     const int grid = gq_grid(ctx, G, bytes, big);
     { static int sk = -1; if (sk < 0) { const char * e = getenv("GGML_B200_GQ_SKEW"); sk = e ? atoi(e) : 128; }   // measured: 1282 -> 1257 us per token between 0 and 150
       p.n_first = grid > ctx->sm_count ? ctx->sm_count : 0; p.skew = p.n_first ? sk : 0; }
-    p.gmax = (int) (((G + grid - 1) / grid) * (1024 + p.skew) / 1024 + 1);
+    p.gmax = (int) (((G + grid - 1) / grid) * (1024 + p.skew) / 1024 + 1) + (p.pair ? 2 : 0);      // (pair mode rounds both ends of a share to even)
     const size_t smem = gq_smem_bytes(p.K, p.gmax, big ? 24 : GQ_WARPS);
     static bool attr_done[64] = {};
     if (!attr_done[ctx->device & 63]) {
