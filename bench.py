@@ -574,9 +574,45 @@ def run_b200(args):
                 result["cpu_baseline"] = {"value": v, "unit": "tok/s", "cores": cores, "kind": kind, "sample": sample}
             except Exception as ex:                      # the baseline is a reported number, never a reason to lose the GPU line
                 result["cpu_baseline"] = {"value": None, "unit": "tok/s", "cores": os.cpu_count(), "kind": "unavailable", "sample": repr(ex)}
+        if world == 1 and not args.no_llama_bench:
+            result["llama_bench"] = llama_bench_through_plugin(args)
         print(json.dumps(result), flush=True)
     if dist:
         dist.barrier(); dist.destroy_process_group()
+
+
+def llama_bench_through_plugin(args, budget_s=420):
+    """Supporting evidence beside the hot-path numbers: the reference's OWN llama-bench binary (oracle/_ref/avx2/llama-bench, compiled
+    in place from the unmodified reference by `make -C oracle llama`; nothing of /root/reference is read at run time) on a random-block
+    GGUF of the same model (scripts/make_gguf.py), with libggml-b200.so loaded through GGML_BACKEND_PATH -- every node of the llama graph
+    (hot ops + glue ops) runs on the device.  Absent binary or any failure -> {"unavailable": why}; never fatal."""
+    import subprocess, tempfile, time
+    lb = os.path.join(ROOT, "oracle", "_ref", "avx2", "llama-bench")
+    plugin = os.path.join(ROOT, "super-llama.cpp_b200", "libggml-b200.so")
+    if not os.path.exists(lb):
+        return {"unavailable": "oracle/_ref/avx2/llama-bench not built (make -C oracle llama, needs the reference sources at build time)"}
+    if args.model not in ("8b", "tinyllama"):
+        return {"unavailable": f"scripts/make_gguf.py writes 8b and tinyllama only, not {args.model}"}
+    t0 = time.time()
+    gguf = os.path.join(tempfile.gettempdir(), f"b200-bench-{args.model}-{args.quant}-{os.getpid()}.gguf")
+    try:
+        subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "make_gguf.py"), "--model", args.model, "--quant", args.quant, "-o", gguf],
+                       check=True, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, timeout=budget_s / 2)
+        cmd = [lb, "-m", gguf, "-p", "512", "-n", "128", "-r", "3", "-fa", "1", "-ngl", "99", "-t", str(os.cpu_count() or 1), "-o", "json"] + (["-d", str(args.depth)] if args.depth else [])
+        p = subprocess.run(cmd, env=dict(os.environ, GGML_BACKEND_PATH=plugin), stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=max(30, budget_s - (time.time() - t0)))
+        rows = json.loads(p.stdout[p.stdout.index("["):])
+        if "B200" not in str(rows[0].get("backends")):
+            return {"unavailable": f"llama-bench did not pick the plugin up (backends: {rows[0].get('backends')})"}
+        out = {"command": " ".join(cmd[:1] + ["-m", "<random-block GGUF>"] + cmd[3:]), "backend": rows[0].get("backends"), "model": rows[0].get("model_type"), "data": "random GGUF blocks, no_vocab tokenizer, random token ids"}
+        for r in rows:
+            name = f"pp{r['n_prompt']}" if r.get("n_prompt") else f"tg{r['n_gen']}"
+            out[name] = {"value": r["avg_ts"], "stddev": r["stddev_ts"], "unit": "tok/s"}
+        return out
+    except Exception as ex:
+        return {"unavailable": repr(ex)[:300]}
+    finally:
+        try: os.remove(gguf)
+        except OSError: pass
 
 
 def main():
@@ -591,6 +627,7 @@ def main():
     ap.add_argument("--no-pp", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-llama-bench", action="store_true", help="skip the supporting run of the reference's llama-bench through the plugin")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":

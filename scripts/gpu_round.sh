@@ -10,8 +10,8 @@ timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "s
 timeout 900 python bench.py ${BENCH_ARGS:-} > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"; cat gpurun_out/bench.json; tail -3 gpurun_out/bench.err
 timeout 600 python bench.py --impl reference --steps 3 --warmup 3 > gpurun_out/bench_reference.json 2> gpurun_out/bench_reference.err; echo "bench reference rc=$?"; cat gpurun_out/bench_reference.json
 # ncu: launch list of the bench command (shares, not absolutes), then ONE full capture of the dominant kernels
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 700 --csv --log-file gpurun_out/ncu_launches.csv python bench.py --steps 2 --warmup 3 --no-pp --no-cpu --no-graph > gpurun_out/ncu_launches.log 2>&1; echo "ncu list rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_gemv_q4k_mma|k_gemv_stream' -s 20 -c 6 -o gpurun_out/ncu_full_gemv -f python bench.py --steps 2 --warmup 3 --no-pp --no-cpu --no-graph > gpurun_out/ncu_full.log 2>&1; echo "ncu full rc=$?"
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 700 --csv --log-file gpurun_out/ncu_launches.csv python bench.py --steps 2 --warmup 3 --no-pp --no-cpu --no-graph --no-llama-bench > gpurun_out/ncu_launches.log 2>&1; echo "ncu list rc=$?"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:'k_gemv_q4k_mma|k_gemv_stream' -s 20 -c 6 -o gpurun_out/ncu_full_gemv -f python bench.py --steps 2 --warmup 3 --no-pp --no-cpu --no-graph --no-llama-bench > gpurun_out/ncu_full.log 2>&1; echo "ncu full rc=$?"
 if [ -z "${SKIP_TBO:-}" ]; then
 for op in MUL_MAT MUL_MAT_ID FLASH_ATTN_EXT; do
   GGML_BACKEND_PATH=$PWD/super-llama.cpp_b200/libggml-b200.so timeout 900 oracle/_ref/avx2/test-backend-ops test -b B200_0 -o $op > gpurun_out/tbo_$op.log 2>&1; echo "test-backend-ops $op rc=$?"; tail -3 gpurun_out/tbo_$op.log

@@ -354,7 +354,11 @@ static int try_rope_kv(b200_backend_ctx * c, ggml_cgraph * g, int i) {
         rq = g->nodes[i]; rk = g->nodes[j1]; sk = g->nodes[j2]; sv = g->nodes[j3];
     } else { rk = g->nodes[i]; sk = g->nodes[j1]; sv = g->nodes[j2]; j3 = j2; }
     if (sk->op != GGML_OP_SET_ROWS || sv->op != GGML_OP_SET_ROWS) return -1;
-    if (b200_glue_rope_kv(c->ctx, rq, rk, sk, sv) != B200_OK) return -1;
+    if (b200_glue_rope_kv(c->ctx, rq, rk, sk, sv) != B200_OK) {
+        static int said = 0;
+        if (!said++ && getenv("GGML_B200_DEBUG")) B200_LOG("rope/KV-store fusion declined at node %d (%s): %s", i, g->nodes[i]->name, b200_last_error());
+        return -1;
+    }
     ggml_tensor * outs[4] = { rq, rk, sk, sv };
     for (ggml_tensor * t : outs) if (t) b200_note_write(c->ctx, t->data, tensor_nbytes(t));
     return j3;

@@ -427,23 +427,23 @@ static bool gl_same_view(const ggml_tensor * a, const ggml_tensor * b) { return 
 // [ROPE(Q)] + ROPE(K) + SET_ROWS(K) + SET_ROWS(V) as one launch (rq may be NULL); B200_ERR_UNSUPPORTED when the nodes do not have the
 // shape of a llama layer's KV-cache update
 int b200_glue_rope_kv(b200_ctx * ctx, struct ggml_tensor * rq, struct ggml_tensor * rk, struct ggml_tensor * sk, struct ggml_tensor * sv) {
-    if (!rk || !sk || !sv || rk->op != GGML_OP_ROPE || sk->op != GGML_OP_SET_ROWS || sv->op != GGML_OP_SET_ROWS || (rq && rq->op != GGML_OP_ROPE)) return B200_ERR_UNSUPPORTED;
-    if (!b200_glue_supports(rk) || !b200_glue_supports(sk) || !b200_glue_supports(sv) || (rq && !b200_glue_supports(rq))) return B200_ERR_UNSUPPORTED;
+    if (!rk || !sk || !sv || rk->op != GGML_OP_ROPE || sk->op != GGML_OP_SET_ROWS || sv->op != GGML_OP_SET_ROWS || (rq && rq->op != GGML_OP_ROPE)) { b200_set_error("rope_kv: check 1"); return B200_ERR_UNSUPPORTED; }
+    if (!b200_glue_supports(rk) || !b200_glue_supports(sk) || !b200_glue_supports(sv) || (rq && !b200_glue_supports(rq))) { b200_set_error("rope_kv: check 2"); return B200_ERR_UNSUPPORTED; }
     const ggml_tensor * ks = sk->src[0], * vs = sv->src[0], * kidx = sk->src[1], * vidx = sv->src[1];
     // SET_ROWS(K) stores exactly the ROPE(K) result, seen as 2-D rows; both caches f16, one index per source row
-    if (ks->data != rk->data || !gl_contiguous(rk, 4) || !gl_contiguous(ks, 4) || gl_nelem(ks) != gl_nelem(rk) || ks->ne[2] != 1 || ks->ne[3] != 1) return B200_ERR_UNSUPPORTED;
-    if (ks->ne[0] % rk->ne[0] != 0 || sk->type != GGML_TYPE_F16 || sv->type != GGML_TYPE_F16 || vs->ne[2] != 1 || vs->ne[3] != 1) return B200_ERR_UNSUPPORTED;
-    if (kidx->ne[0] != ks->ne[1] || kidx->ne[1] != 1 || kidx->ne[2] != 1 || vidx->ne[0] != vs->ne[1] || vidx->ne[1] != 1 || vidx->ne[2] != 1) return B200_ERR_UNSUPPORTED;
-    if (((uintptr_t) sk->data & 1) || sk->nb[1] % 2 || !gl_vec_ok(vs) || ((uintptr_t) sv->data & 15) || sv->nb[1] % 16) return B200_ERR_UNSUPPORTED;
+    if (ks->data != rk->data || !gl_contiguous(rk, 4) || !gl_contiguous(ks, 4) || gl_nelem(ks) != gl_nelem(rk) || ks->ne[2] != 1 || ks->ne[3] != 1) { b200_set_error("rope_kv: check 3"); return B200_ERR_UNSUPPORTED; }
+    if (ks->ne[0] % rk->ne[0] != 0 || sk->type != GGML_TYPE_F16 || sv->type != GGML_TYPE_F16 || vs->ne[2] != 1 || vs->ne[3] != 1) { b200_set_error("rope_kv: check 4"); return B200_ERR_UNSUPPORTED; }
+    if (kidx->ne[0] != ks->ne[1] || kidx->ne[1] != 1 || kidx->ne[2] != 1 || vidx->ne[0] != vs->ne[1] || vidx->ne[1] != 1 || vidx->ne[2] != 1) { b200_set_error("rope_kv: check 5"); return B200_ERR_UNSUPPORTED; }
+    if (((uintptr_t) sk->data & 1) || sk->nb[1] % 2 || !gl_vec_ok(vs) || ((uintptr_t) sv->data & 15) || sv->nb[1] % 16) { b200_set_error("rope_kv: check 6"); return B200_ERR_UNSUPPORTED; }
     // independent sections: nothing one of them writes may be something another reads or writes (rope in place is fine)
     const ggml_tensor * outs[4] = { rq, rk, sk, sv };
     const ggml_tensor * ins[4]  = { rq ? rq->src[0] : nullptr, rk->src[0], nullptr, vs };
     for (int o = 0; o < 4; ++o) for (int i = 0; i < 4; ++i) {
         if (!outs[o] || o == i) continue;
-        if (outs[i] && o < i && !gl_span_disjoint(outs[o], outs[i])) return B200_ERR_UNSUPPORTED;
-        if (ins[i] && !gl_span_disjoint(outs[o], ins[i])) return B200_ERR_UNSUPPORTED;
+        if (outs[i] && o < i && !gl_span_disjoint(outs[o], outs[i])) { b200_set_error("rope_kv: output %d (%s) overlaps output %d (%s)", o, outs[o]->name, i, outs[i]->name); return B200_ERR_UNSUPPORTED; }
+        if (ins[i] && !gl_span_disjoint(outs[o], ins[i])) { b200_set_error("rope_kv: output %d (%s) overlaps input %d (%s)", o, outs[o]->name, i, ins[i]->name); return B200_ERR_UNSUPPORTED; }
     }
-    for (int o = 0; o < 4; ++o) if (outs[o] && (!gl_span_disjoint(outs[o], kidx) || !gl_span_disjoint(outs[o], vidx) || !gl_span_disjoint(outs[o], rk->src[1]))) return B200_ERR_UNSUPPORTED;
+    for (int o = 0; o < 4; ++o) if (outs[o] && (!gl_span_disjoint(outs[o], kidx) || !gl_span_disjoint(outs[o], vidx) || !gl_span_disjoint(outs[o], rk->src[1]))) { b200_set_error("rope_kv: check 9"); return B200_ERR_UNSUPPORTED; }
     gl_rope_kv a;
     memset(&a, 0, sizeof a);
     if (rq) { a.qx = gl_of(rq->src[0]); a.qy = gl_of(rq); a.qr = gl_rope_params(rq); a.nq = (int) gl_nrows(rq); }
