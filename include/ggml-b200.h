@@ -126,16 +126,11 @@ B200_API int b200_mul_mat(b200_ctx * ctx, const b200_tensor * w, const b200_tens
 // n MUL_MATs sharing the activation tensor x (wq/wk/wv, ffn_gate/ffn_up in src/models/llama.cpp:40-75): same result as n
 // b200_mul_mat calls; served by one launch of the streaming GEMV when x is a single column and the weights allow it.
 B200_API int b200_mul_mat_multi(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, b200_tensor * const * dst);
-/* dst = w * swiglu(gate, up), one activation column: GGML_OP_GLU (SWIGLU, split; ggml-cpu/ops.cpp ggml_compute_forward_glu) folded into
- * the GGML_OP_MUL_MAT behind it (ffn_down).  glu_out (may be NULL) receives the GLU node's own output.  Returns B200_ERR_UNSUPPORTED when
- * the shape does not fit the streaming GEMV: run the two ops separately then. */
-/* gate = wg x, up = wu x, glu = swiglu(gate, up), one activation column, one launch: ffn_gate + ffn_up + GGML_OP_GLU of a llama layer
- * (src/llama-graph.cpp build_ffn, LLM_FFN_SILU / LLM_FFN_PAR).  B200_ERR_UNSUPPORTED unless both weights are raw q4_K served by the
- * tensor-core GEMV: use b200_mul_mat_multi + the GLU op then. */
+/* gate = wg x, up = wu x, glu = swiglu(gate, up), one activation column, one launch: ffn_gate + ffn_up + GGML_OP_GLU (SWIGLU, split;
+ * ggml-cpu/ops.cpp ggml_compute_forward_glu) of a llama layer (src/llama-graph.cpp build_ffn, LLM_FFN_SILU / LLM_FFN_PAR).
+ * B200_ERR_UNSUPPORTED unless both weights are raw q4_K served by the tensor-core GEMV: use b200_mul_mat_multi + the GLU op then. */
 B200_API int b200_mul_mat_gate_up_swiglu(b200_ctx * ctx, const b200_tensor * wg, const b200_tensor * wu, const b200_tensor * x,
                                          b200_tensor * gate, b200_tensor * up, b200_tensor * glu);
-B200_API int b200_mul_mat_swiglu(b200_ctx * ctx, const b200_tensor * w, const b200_tensor * gate, const b200_tensor * up, b200_tensor * glu_out, b200_tensor * dst);
-
 // as[K, M, n_expert], b[K, n_used|1, n_tokens] f32, ids[n_used, n_tokens] i32 -> dst[M, n_used, n_tokens]
 // (ggml/src/ggml.c:3205-3241).
 B200_API int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b200_tensor * b,

@@ -258,34 +258,6 @@ extern "C" int b200_mul_mat(b200_ctx * ctx, const b200_tensor * w, const b200_te
     return B200_ERR_UNSUPPORTED;
 }
 
-// dst = w * swiglu(gate, up) for one activation column: the GLU node in front of ffn_down folded into the GEMV's quantizer (no launch, no
-// round trip of the n_ff column).  glu_out (optional) still receives the GLU node's output.  B200_ERR_UNSUPPORTED when the streaming GEMV
-// with in-kernel quantization cannot take the shape: the caller then runs GLU and MUL_MAT separately.
-extern "C" int b200_mul_mat_swiglu(b200_ctx * ctx, const b200_tensor * w, const b200_tensor * gate, const b200_tensor * up, b200_tensor * glu_out, b200_tensor * dst) {
-    if (!ctx || !w || !gate || !up || !dst) { b200_set_error("mul_mat_swiglu: null argument"); return B200_ERR_INVALID; }
-    const int64_t K = w->ne[0], M = w->ne[1];
-    const b200_tensor * cols[3] = { gate, up, glu_out };
-    for (const b200_tensor * t : cols) {
-        if (!t) continue;
-        if (t->type != B200_TYPE_F32 || t->nb[0] != 4 || t->ne[0] != K || t->ne[1] != 1 || t->ne[2] != 1 || t->ne[3] != 1 || ((uintptr_t) t->data & 15)) {
-            b200_set_error("mul_mat_swiglu: one contiguous 16-byte aligned f32 column of K values each"); return B200_ERR_UNSUPPORTED;
-        }
-    }
-    if (dst->type != B200_TYPE_F32 || dst->nb[0] != 4 || dst->ne[0] != M || dst->ne[1] != 1 || dst->ne[2] != 1 || dst->ne[3] != 1 || w->ne[2] != 1 || w->ne[3] != 1) {
-        b200_set_error("mul_mat_swiglu: shape mismatch"); return B200_ERR_UNSUPPORTED;
-    }
-    if (!is_quant(w->type) || q8_1_variant_env() != B200_Q8_1_X86 || K > fused_quant_max_k() || !b200_gemv_stream_supported(w, gate)) {
-        b200_set_error("mul_mat_swiglu: not a streaming-GEMV shape"); return B200_ERR_UNSUPPORTED;
-    }
-    B200_CUDA_TRY(cudaSetDevice(ctx->device));
-    float * d = (float *) dst->data;
-    const b200_gemv_glu glu = { (const float *) up->data, glu_out ? (float *) glu_out->data : nullptr };
-    const int rc = b200_launch_gemv_stream(ctx, &w, 1, gate, nullptr, &d, nullptr, nullptr, &glu);
-    if (glu_out) b200_note_write(ctx, glu_out->data, b200_tensor_span(glu_out));
-    b200_note_write(ctx, dst->data, b200_tensor_span(dst));
-    return rc;
-}
-
 // gate = wg x, up = wu x, glu = swiglu(gate, up) for one activation column in ONE launch: the tensor-core q4_K GEMV hands every CTA the
 // same rows of both weights, so its epilogue can finish the GLU node as well (no launch, no re-read of the two n_ff columns).
 // B200_ERR_UNSUPPORTED when that kernel does not serve the shape: the caller runs b200_mul_mat_multi and the GLU op then.

@@ -78,7 +78,7 @@ struct b200_backend_ctx {
     std::vector<b200_graph_entry> graphs; uint64_t graphs_epoch = 0, tick = 0, n_replayed = 0, n_captured = 0, n_eager = 0;
     // GGML_B200_GRAPH_STATS: device time of every replay (event pairs, read in be_free) and host time spent inside graph_compute
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> replay_events; double host_us = 0;
-    uint64_t n_fuse[5] = { 0, 0, 0, 0, 0 };          // launches saved by: matmul groups, RMS_NORM+MUL, ADD+RMS_NORM+MUL, ROPE/SET_ROWS, GLU+MUL_MAT (counted while walking nodes)
+    uint64_t n_fuse[5] = { 0, 0, 0, 0, 0 };          // launches saved by: matmul groups, RMS_NORM+MUL, ADD+RMS_NORM+MUL, ROPE/SET_ROWS, gate+up+GLU (counted while walking nodes)
 };
 // bumped whenever something a captured graph baked in may have changed under it: a weight tensor changed layout, a buffer was freed
 static std::atomic<uint64_t> g_layout_epoch{1};
@@ -245,7 +245,7 @@ static void be_free(ggml_backend_t be) {
         fprintf(stderr, "ggml-b200 graphs: %zu replays timed: %.1f us each on the device (fastest %.1f us)\n", c->replay_events.size(), ms * 1e3 / c->replay_events.size(), mn * 1e3);
     }
     if (getenv("GGML_B200_GRAPH_STATS"))
-        fprintf(stderr, "ggml-b200 fusions (launches saved while walking nodes): matmul groups %llu, add+norm+mul %llu, rope/set_rows %llu, glu+mul_mat %llu\n",
+        fprintf(stderr, "ggml-b200 fusions (launches saved while walking nodes): matmul groups %llu, add+norm+mul %llu, rope/set_rows %llu, gate+up+glu %llu\n",
                 (unsigned long long) c->n_fuse[0], (unsigned long long) c->n_fuse[2], (unsigned long long) c->n_fuse[3], (unsigned long long) c->n_fuse[4]);
     if (getenv("GGML_B200_PROFILE") || getenv("GGML_B200_GRAPH_STATS"))
         fprintf(stderr, "ggml-b200 graphs: %llu computed launch by launch, %llu recorded, %llu replayed\n", (unsigned long long) c->n_eager, (unsigned long long) c->n_captured, (unsigned long long) c->n_replayed);
@@ -363,29 +363,6 @@ static int try_rope_kv(b200_backend_ctx * c, ggml_cgraph * g, int i) {
     for (ggml_tensor * t : outs) if (t) b200_note_write(c->ctx, t->data, tensor_nbytes(t));
     return j3;
 }
-// node i is a GLU: SWIGLU of two tensors (gate, up) feeding the MUL_MAT right behind it (ffn_down of a llama layer, one column):
-// b200_mul_mat_swiglu computes the column inside the GEMV and still stores the GLU node's output.  Returns the MUL_MAT's index or -1.
-static bool mm_weight_ok(const ggml_tensor * w);
-static int try_glu_mul_mat(b200_backend_ctx * c, ggml_cgraph * g, int i) {
-    // measured on Llama-3-8B Q4_K_M decode: every one of the 148 CTAs then evaluates the whole 14336-wide SwiGLU column itself (two L2 reads and
-    // an expf per element), which costs more (+4.5 us per layer) than the launch it saves (-2 us): opt-in, GGML_B200_FUSE_GLU=1
-    static const bool on = [] { const char * e = getenv("GGML_B200_FUSE_GLU"); return e && atoi(e); }();
-    if (!on) return -1;
-    ggml_tensor * glu = g->nodes[i];
-    const int j = next_work(g, i);
-    if (j < 0 || glu->op_params[0] != GGML_GLU_OP_SWIGLU || !glu->src[1] || glu->op_params[1] != 0) return -1;
-    ggml_tensor * mm = g->nodes[j];
-    if (mm->op != GGML_OP_MUL_MAT || mm->src[1] != glu || !buft_is_b200(mm->src[0]->buffer->buft) || !mm_weight_ok(mm->src[0])) return -1;
-    // the matmul's result must not land on the columns the kernel is still reading
-    if (ranges_overlap(mm, glu->src[0]) || ranges_overlap(mm, glu->src[1]) || ranges_overlap(mm, glu)) return -1;
-    if (ranges_overlap(glu, glu->src[0]) || ranges_overlap(glu, glu->src[1])) {
-        // GLU computed in place over gate or up: every CTA reads the whole column, one CTA would be rewriting it meanwhile
-        return -1;
-    }
-    b200_tensor w = to_b200(mm->src[0]), ga = to_b200(glu->src[0]), up = to_b200(glu->src[1]), go = to_b200(glu), d = to_b200(mm);
-    if (b200_mul_mat_swiglu(c->ctx, &w, &ga, &up, &go, &d) != B200_OK) return -1;
-    return j;
-}
 // nodes a, b: two adjacent MUL_MATs of one activation.  If the next node is GLU(SWIGLU) of exactly their results (ffn_gate, ffn_up, in
 // either order) the tensor-core GEMV finishes it in its epilogue (b200_mul_mat_gate_up_swiglu).  Returns the GLU's index or -1.
 static int try_gate_up_glu(b200_backend_ctx * c, ggml_cgraph * g, int a, int b) {
@@ -440,8 +417,6 @@ static enum ggml_status run_nodes(b200_backend_ctx * c, ggml_cgraph * g) {
             // residual add + the norm behind it + the norm weight: one launch
             for (int k = 0; k < 3; ++k) b200_note_write(c->ctx, g->nodes[i + k]->data, tensor_nbytes(g->nodes[i + k]));
             i += 2; c->n_fuse[2] += 2;
-        } else if (node->op == GGML_OP_GLU && !fuse_off() && (rc = try_glu_mul_mat(c, g, i)) >= 0) {
-            i = rc; rc = B200_OK; c->n_fuse[4] += 1;                   // SwiGLU folded into the quantizer of the ffn_down GEMV
         } else if (node->op == GGML_OP_ROPE && !fuse_off() && (rc = try_rope_kv(c, g, i)) >= 0) {
             i = rc; rc = B200_OK; c->n_fuse[3] += 2;                   // [ROPE(Q)] ROPE(K) SET_ROWS(K) SET_ROWS(V): one launch
         } else if (node->op == GGML_OP_RMS_NORM && !fuse_off() && i + 1 < g->n_nodes && g->nodes[i + 1]->op == GGML_OP_MUL &&

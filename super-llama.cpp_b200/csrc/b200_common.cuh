@@ -202,27 +202,18 @@ static __device__ __forceinline__ void q8_1_block(float v, int & q, float & d, i
 // in flight while this one converts.  store(blk32, hf, quants, d, s): hf = which half of block blk32, d and s after their fp16 round trip.
 struct b200_no_hook { __device__ __forceinline__ void operator()() const {} };
 // after_loads() runs once, right after the first round of loads has been issued (a place to start bulk traffic BEHIND them)
-// SwiGLU as the GLU node computes it (ggml-cpu/ops.cpp glu, vec.h silu: x / (1 + exp(-x))), shared by k_swiglu and the fused quantizer
+// SwiGLU as the GLU node computes it (ggml-cpu/ops.cpp glu, vec.h silu: x / (1 + exp(-x))), shared by k_swiglu and the GEMV epilogue that finishes gate/up
 static __device__ __forceinline__ float b200_swiglu1(float x, float y) { return x / (1.0f + expf(-x)) * y; }
-// x2 (optional): the column to quantize is swiglu(x, x2) -- the GLU node in front of ffn_down folded into the matmul; xout (optional, one
-// CTA of the grid passes it) receives that column, i.e. the GLU node's own output
 template <class F, class H = b200_no_hook>
-static __device__ __forceinline__ void b200_quantize_column_x86(const float * x, int K, F store, unsigned long long * rec = nullptr, H after_loads = H(),
-                                                                const float * x2 = nullptr, float * xout = nullptr) {
+static __device__ __forceinline__ void b200_quantize_column_x86(const float * x, int K, F store, unsigned long long * rec = nullptr, H after_loads = H()) {
     const int nunits = K >> 4, lane = threadIdx.x & 31;
-    const float4 * x4 = (const float4 *) x, * y4 = (const float4 *) x2;
+    const float4 * x4 = (const float4 *) x;
     // every CTA of the grid reads the same small column while gigabytes of weights stream through L2 (evict_first): ask L2 to keep it
     uint64_t keep;
     asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(keep));
     auto ldx = [&](int i) {
         float4 r;
         asm volatile("ld.global.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(x4 + i), "l"(keep));
-        if (y4) {
-            float4 y;
-            asm volatile("ld.global.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;" : "=f"(y.x), "=f"(y.y), "=f"(y.z), "=f"(y.w) : "l"(y4 + i), "l"(keep));
-            r = make_float4(b200_swiglu1(r.x, y.x), b200_swiglu1(r.y, y.y), b200_swiglu1(r.z, y.z), b200_swiglu1(r.w, y.w));
-            if (xout) ((float4 *) xout)[i] = r;
-        }
         return r;
     };
     int base = (int) (threadIdx.x & ~31u);                               // warp-uniform; K % 32 == 0 keeps lane pairs together
@@ -333,10 +324,8 @@ bool b200_gemv_stream_supported(const b200_tensor * w, const b200_tensor * x);
 struct b200_rowsplit_peers { int nll; void * ll_base[B200_MAX_PEERS]; const void * ll_self; const void * arena; unsigned * ctrl; float * full[3]; int full_m[3]; };
 // decode MUL_MAT_ID through the streaming GEMV: segment s reads expert ids[base + s] (device memory) at byte stride `stride`
 struct b200_gemv_ids { const int * ids; int base; size_t stride; const void * ads; };   // ads: (d, s) pairs of this column when `image` is one column of a wider q8_1 image
-// the activation column is swiglu(x, up) (the GLU node in front of ffn_down); `out` (optional) receives that column
-struct b200_gemv_glu { const float * up; float * out; };
 int  b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, const void * image, float * const * dst,
-                             const b200_rowsplit_peers * peers = nullptr, const b200_gemv_ids * idm = nullptr, const b200_gemv_glu * glu = nullptr);
+                             const b200_rowsplit_peers * peers = nullptr, const b200_gemv_ids * idm = nullptr);
 bool b200_gemv_mma_supported(const b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x);
 int  b200_launch_gemv_mma(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, const void * image, float * const * dst,
                           const b200_rowsplit_peers * peers, float * glu = nullptr);   // glu: n == 2 (gate, up), also stores swiglu(gate, up)

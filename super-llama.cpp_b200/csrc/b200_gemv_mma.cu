@@ -60,7 +60,8 @@ static __device__ __forceinline__ void mma_u8s8(int (&c)[4], unsigned a0, unsign
 
 // NW = 12: two CTAs per SM (this kernel's, or this and the PDL-launched next one); NW = 24: ONE CTA per SM for long streams -- the same
 // warps per SM, but the activation column is fetched and quantized once per SM (L2 broadcast bandwidth, see b200_gemv_stream.cu BIG)
-template <int NW>
+// PAIR (compile time: the mere presence of the branches in the plain kernel cost 2.4 % of the decode graph): see gq_args::pair
+template <int NW, bool PAIR = false>
 __global__ void __launch_bounds__(NW * 32, NW == 24 ? 1 : 2) k_gemv_q4k_mma(const gq_args p, const __grid_constant__ gq_maps maps) {
     extern __shared__ __align__(128) uint8_t smem[];
     // layout: [NW][GQ_STAGES][2304] rings | q8 quants [K] | (d, s) float2 [K/32] | partial sums [gmax][nchunks][8] | mbarriers
@@ -82,7 +83,8 @@ __global__ void __launch_bounds__(NW * 32, NW == 24 ? 1 : 2) k_gemv_q4k_mma(cons
     const int64_t wa = 1024 + p.skew, wb = 1024 - p.skew, n1 = p.n_first;
     const int64_t W = n1 * wa + ((int64_t) gridDim.x - n1) * wb;
     auto cut = [&](int64_t b) { const int64_t pre = b <= n1 ? b * wa : n1 * wa + (b - n1) * wb; return (int) ((int64_t) G * pre / W); };
-    const int g_lo = p.pair ? cut(blockIdx.x) & ~1 : cut(blockIdx.x), g_hi = p.pair ? cut((int64_t) blockIdx.x + 1) & ~1 : cut((int64_t) blockIdx.x + 1);   // (G is even in pair mode)
+    constexpr bool pair = PAIR;
+    const int g_lo = pair ? cut(blockIdx.x) & ~1 : cut(blockIdx.x), g_hi = pair ? cut((int64_t) blockIdx.x + 1) & ~1 : cut((int64_t) blockIdx.x + 1);   // (G is even in pair mode)
     const int nitems_cta = (p.dbg & 4) ? 0 : (g_hi - g_lo) * nchunks;
 
     unsigned long long * rec = nullptr;
@@ -100,7 +102,7 @@ __global__ void __launch_bounds__(NW * 32, NW == 24 ? 1 : 2) k_gemv_q4k_mma(cons
     auto issue = [&](int stage) {
         if (lane == 0) {
             int gg = g_lo + pgl, s = 0;
-            if (p.pair) { s = gg & 1; gg >>= 1; } else if (gg >= G0) { gg -= G0; s = 1; if (gg >= G1) { gg -= G1; s = 2; } }
+            if (pair) { s = gg & 1; gg >>= 1; } else if (gg >= G0) { gg -= G0; s = 1; if (gg >= G1) { gg -= G1; s = 2; } }
             const uint32_t bar = bar0 + 8 * stage;
             mbar_arrive_expect_tx(bar, GQ_STAGE_BYTES);
             tma_load_2d_hint(ring + stage * GQ_STAGE_BYTES, &maps.m[s], pch * (GQ_CHUNK / 4), gg * GQ_ROWS, bar, policy);
@@ -123,7 +125,7 @@ __global__ void __launch_bounds__(NW * 32, NW == 24 ? 1 : 2) k_gemv_q4k_mma(cons
         for (int i = 0; i < p.npf && it < nitems_cta; ++i, it += NW) {
             const int gl = it / nchunks, ch = it - gl * nchunks;
             int gg = g_lo + gl, s = 0;
-            if (p.pair) { s = gg & 1; gg >>= 1; } else if (gg >= G0) { gg -= G0; s = 1; if (gg >= G1) { gg -= G1; s = 2; } }
+            if (pair) { s = gg & 1; gg >>= 1; } else if (gg >= G0) { gg -= G0; s = 1; if (gg >= G1) { gg -= G1; s = 2; } }
             tma_prefetch_l2_2d(&maps.m[s], ch * (GQ_CHUNK / 4), gg * GQ_ROWS);
         }
     }
@@ -219,7 +221,7 @@ __global__ void __launch_bounds__(NW * 32, NW == 24 ? 1 : 2) k_gemv_q4k_mma(cons
     b200_trace_stamp(rec, 7);                                             // every warp done
 
     // add the chunk partials of every row in chunk order and store (or send) the row
-    if (p.pair) {                                                         // local groups alternate gate, up: one thread finishes both values of a row
+    if (pair) {                                                           // local groups alternate gate, up: one thread finishes both values of a row
         for (int i = threadIdx.x; i < ((g_hi - g_lo) >> 1) * GQ_ROWS; i += blockDim.x) {
             const int pl = i >> 3, r = i & 7;
             float vg = 0.0f, vu = 0.0f;
@@ -374,7 +376,7 @@ int b200_launch_gemv_mma(b200_ctx * ctx, const b200_tensor * const * w, int n, c
     p.trace = ctx->trace; p.trace_cap = ctx->trace_cap;
     { static int f = -1; if (f < 0) { const char * e = getenv("GGML_B200_GQ_NPRE"); f = e ? atoi(e) : 0; }
       p.npre = f > 0 ? (f > GQ_STAGES ? GQ_STAGES : f) : (bytes > ((size_t) 24 << 20) ? GQ_STAGES : 1); }
-    const bool big = gq_big(bytes, p.K, G, ctx);
+    const bool big = !p.pair && gq_big(bytes, p.K, G, ctx);                // (the 24-warp shape is opt-in and has no PAIR variant)
     const int grid = gq_grid(ctx, G, bytes, big);
     { static int sk = -1; if (sk < 0) { const char * e = getenv("GGML_B200_GQ_SKEW"); sk = e ? atoi(e) : 128; }   // measured: 1282 -> 1257 us per token between 0 and 150
       p.n_first = grid > ctx->sm_count ? ctx->sm_count : 0; p.skew = p.n_first ? sk : 0; }
@@ -384,6 +386,7 @@ int b200_launch_gemv_mma(b200_ctx * ctx, const b200_tensor * const * w, int n, c
     if (!attr_done[ctx->device & 63]) {
         B200_CUDA_TRY(cudaFuncSetAttribute(k_gemv_q4k_mma<GQ_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, GQ_SMEM_MAX));
         B200_CUDA_TRY(cudaFuncSetAttribute(k_gemv_q4k_mma<24>, cudaFuncAttributeMaxDynamicSharedMemorySize, GQ_SMEM_MAX_BIG));
+        B200_CUDA_TRY(cudaFuncSetAttribute(k_gemv_q4k_mma<GQ_WARPS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, GQ_SMEM_MAX));
         attr_done[ctx->device & 63] = true;
     }
     cudaLaunchConfig_t cfg = {};
@@ -395,7 +398,8 @@ int b200_launch_gemv_mma(b200_ctx * ctx, const b200_tensor * const * w, int n, c
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = ctx->pdl ? 1 : 0;
-    if (big) B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_gemv_q4k_mma<24>, p, maps));
+    if (p.pair) B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_gemv_q4k_mma<GQ_WARPS, true>, p, maps));
+    else if (big) B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_gemv_q4k_mma<24>, p, maps));
     else     B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_gemv_q4k_mma<GQ_WARPS>, p, maps));
     return B200_OK;
 }

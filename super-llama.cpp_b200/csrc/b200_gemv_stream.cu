@@ -32,7 +32,6 @@ struct gs_seg { const uint8_t * w; size_t nb1; float * dst; int M; };
 struct gs_args {
     gs_seg seg[GS_MAXSEG]; int nseg; int Mtot; int K;
     const float * x;                         // f32 activation column: quantized in-kernel when aq == NULL
-    const float * x2; float * xout;          // x2 != NULL: the column is swiglu(x, x2); CTA 0 also stores it to xout (the GLU node's output)
     const int8_t * aq; const __half2 * ads;  // or a q8_1 image made by k_quantize_q8_1_soa (natural order): [K] quants, [K/32] (d, s)
     // row-split exchange: seg[i].dst points at this rank's rows inside the FULL f32 column full[i], which lives in the exchange
     // arena.  Instead of a plain store, every result row goes as an 8-byte (value, tag) pair into the low-latency mirror of that
@@ -364,8 +363,7 @@ __global__ void __launch_bounds__(SHAPE == 3 ? 512 : SHAPE == 1 ? 256 : 384, SHA
             }
         }
     } else {
-        b200_quantize_column_x86(p.x, p.K, [&](int blk32, int hf, int4 w, float d, float sm) { T::store_unit(s_act, p.K, nblocks, blk32, hf, w, d, sm); }, rec, fill_rest,
-                                 p.x2, blockIdx.x == 0 ? p.xout : nullptr);
+        b200_quantize_column_x86(p.x, p.K, [&](int blk32, int hf, int4 w, float d, float sm) { T::store_unit(s_act, p.K, nblocks, blk32, hf, w, d, sm); }, rec, fill_rest);
     }
     // Let the next kernel of the stream start its prologue (PDL) only now: its CTA lands on this SM and pulls ~80 KB of weights,
     // and loads issued behind that burst wait for it (the activation column took ~1300 cycles to arrive with the trigger at the top
@@ -556,9 +554,8 @@ static int gs_launch(b200_ctx * ctx, const gs_args & p, int attr_slot) {
 
 // n <= 3 weights of the same type sharing the activation column x; dst[i] is the f32 column of weight i
 int b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n, const b200_tensor * x, const void * image, float * const * dst,
-                            const b200_rowsplit_peers * peers, const b200_gemv_ids * idm, const b200_gemv_glu * glu) {
-    if (glu && (image || idm || peers)) { b200_set_error("gemv_stream: the GLU fold needs the in-kernel quantizer, one plain weight"); return B200_ERR_UNSUPPORTED; }
-    if (!idm && !glu && b200_gemv_mma_supported(ctx, w, n, x)) return b200_launch_gemv_mma(ctx, w, n, x, image, dst, peers);   // raw q4_K: tensor-core dots
+                            const b200_rowsplit_peers * peers, const b200_gemv_ids * idm) {
+    if (!idm && b200_gemv_mma_supported(ctx, w, n, x)) return b200_launch_gemv_mma(ctx, w, n, x, image, dst, peers);   // raw q4_K: tensor-core dots
     gs_args p;
     p.ids = idm ? idm->ids : nullptr; p.id_base = idm ? idm->base : 0; p.estride = idm ? idm->stride : 0;
     p.nll = 0; p.ll_self = nullptr; p.arena = nullptr; p.ctrl = nullptr;
@@ -573,7 +570,6 @@ int b200_launch_gemv_stream(b200_ctx * ctx, const b200_tensor * const * w, int n
     { static int npf = -1; if (npf < 0) { const char * e = getenv("GGML_B200_GS_NPF"); npf = e ? atoi(e) : 0; } p.npf = npf; }
     p.trace = ctx->trace; p.trace_cap = ctx->trace_cap;
     p.nseg = n; p.Mtot = 0; p.x = (const float *) x->data; p.K = (int) w[0]->ne[0];
-    p.x2 = glu ? glu->up : nullptr; p.xout = glu ? glu->out : nullptr;
     p.aq = (const int8_t *) image; p.ads = image ? (const __half2 *) ((const int8_t *) image + p.K) : nullptr;
     if (image && idm && idm->ads) p.ads = (const __half2 *) idm->ads;
     for (int i = 0; i < n; ++i) {

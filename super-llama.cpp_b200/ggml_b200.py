@@ -58,7 +58,6 @@ def lib():
         "b200_memcpy_h2d": (i, [vp, vp, vp, sz]), "b200_memcpy_d2h": (i, [vp, vp, vp, sz]), "b200_memset": (i, [vp, vp, i, sz]),
         "b200_quantize_q8_1": (i, [vp, vp, sz, vp, i64, i64, i]),
         "b200_mul_mat": (i, [vp, tp, tp, tp]), "b200_mul_mat_multi": (i, [vp, C.POINTER(tp), i, tp, C.POINTER(tp)]),
-        "b200_mul_mat_swiglu": (i, [vp, tp, tp, tp, tp, tp]),
         "b200_mul_mat_gate_up_swiglu": (i, [vp, tp, tp, tp, tp, tp, tp]),
         "b200_repack_supported": (i, [i, i64]), "b200_repack": (i, [vp, i, vp, i64, i64, sz]), "b200_unrepack": (i, [vp, i, vp, i64, i64, sz]), "b200_mul_mat_id": (i, [vp, tp, tp, tp, tp]),
         "b200_flash_attn_ext": (i, [vp, tp, tp, tp, tp, tp, tp, f, f, f]),
@@ -291,13 +290,6 @@ class Context:
         """gate = wg x, up = wu x, glu = swiglu(gate, up) in one launch of the tensor-core q4_K GEMV (raises when it does not serve the shape)"""
         cs = [t.c() for t in (wg, wu, x, gate, up, glu)]
         _check(lib().b200_mul_mat_gate_up_swiglu(self.h, *[C.byref(t) for t in cs]), "mul_mat_gate_up_swiglu")
-
-    def mul_mat_swiglu(self, w, gate, up, glu_out, dst):
-        """dst = w * swiglu(gate, up): GGML_OP_GLU (SWIGLU, split) folded into the MUL_MAT behind it; glu_out (or None) gets the GLU output.
-        Raises when the shape does not fit the streaming GEMV (the caller then runs the ops separately)"""
-        cw, cg, cu, cd = w.c(), gate.c(), up.c(), dst.c()
-        co = glu_out.c() if glu_out is not None else None
-        _check(lib().b200_mul_mat_swiglu(self.h, C.byref(cw), C.byref(cg), C.byref(cu), C.byref(co) if co is not None else None, C.byref(cd)), "mul_mat_swiglu")
 
     def repack(self, w):
         """load-time repack of a weight tensor in place (no-op for types consumed in GGUF layout); returns w"""

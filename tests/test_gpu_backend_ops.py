@@ -117,14 +117,14 @@ def test_chunked_async_upload_repacks(wtype, K, M, chunk):
 @pytest.mark.parametrize("vtype", [12, 14])
 def test_layer_fusions_bit_identical(vtype):
     """what be_graph_optimize / be_graph_compute do to the head of a llama layer -- weight matmuls of one activation pulled together and
-    launched as one, ADD + RMS_NORM + MUL as one kernel, ROPE(Q) + ROPE(K) + SET_ROWS(K) + SET_ROWS(V) as one kernel, SwiGLU folded into the ffn_down GEMV, the graph recorded
+    launched as one, ADD + RMS_NORM + MUL as one kernel, ROPE(Q) + ROPE(K) + SET_ROWS(K) + SET_ROWS(V) as one kernel, ffn_gate + ffn_up + SwiGLU as one GEMV launch, the graph recorded
     into a CUDA graph and replayed -- changes no bit of any node's output against the same nodes run one by one
     (tests/fusion_probe.cpp, built from include/ggml-b200-abi.h only)"""
     exe = os.path.join(OUT, "fusion_probe")
     os.makedirs(OUT, exist_ok=True)
     subprocess.check_call(["g++", "-std=c++17", "-O1", "-I" + os.path.join(ROOT, "include"), os.path.join(ROOT, "tests", "fusion_probe.cpp"), "-o", exe, "-ldl"])
     outs = []
-    for tag, extra in (("fused", {"GGML_B200_GRAPH_STATS": "1", "GGML_B200_FUSE_GLU": "1"}), ("plain", {"GGML_B200_NO_FUSE": "1", "GGML_B200_GRAPHS": "0"})):
+    for tag, extra in (("fused", {"GGML_B200_GRAPH_STATS": "1"}), ("plain", {"GGML_B200_NO_FUSE": "1", "GGML_B200_GRAPHS": "0"})):
         f = os.path.join(OUT, f"fusion_probe_{vtype}_{tag}.bin")
         p = subprocess.run([exe, PLUGIN, f, str(vtype)], env=dict(os.environ, **extra), stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
         assert p.returncode == 0 and "fusion_probe: OK" in p.stdout, p.stdout[-2000:]
@@ -133,7 +133,7 @@ def test_layer_fusions_bit_identical(vtype):
             iq, ik, iv = order.index("Qcur"), order.index("Kcur"), order.index("Vcur")
             assert max(iq, ik, iv) - min(iq, ik, iv) == 2, order            # the three matmuls adjacent
             assert abs(iq - ik) == 1 or vtype == 12, order                  # equal weight types side by side
-            assert "glu+mul_mat 2" in p.stdout and "rope/set_rows 4" in p.stdout and "add+norm+mul 4" in p.stdout, p.stdout   # every fusion fired (2 node walks)
+            assert "gate+up+glu 2" in p.stdout and "rope/set_rows 4" in p.stdout and "add+norm+mul 4" in p.stdout, p.stdout   # every fusion fired (2 node walks)
             assert "1 recorded, 4 replayed" in p.stdout, p.stdout           # first run launch by launch, second recorded, four graph launches
         outs.append(open(f, "rb").read())
         os.remove(f)

@@ -408,31 +408,6 @@ def test_mul_mat_gate_up_swiglu_one_launch(ctx, B, orc, K, M):
     assert np.allclose(l, want, rtol=2e-6, atol=1e-6 * np.abs(want).max())
 
 
-@pytest.mark.parametrize("t,K,M", [(O.Q4_K, 14336, 4096), (O.Q6_K, 14336, 4096), (O.Q8_0, 5632, 2048), (O.Q4_0, 1024, 300)])
-def test_mul_mat_swiglu_folded(ctx, B, orc, t, K, M):
-    """b200_mul_mat_swiglu: ffn_down over swiglu(gate, up) computed inside the GEMV's quantizer == GLU (ggml-cpu/ops.cpp: x / (1 + exp(-x)) * y
-    in f32) followed by MUL_MAT; the GLU output is still written"""
-    rng = np.random.default_rng(77 + t)
-    w = O.random_blocks(rng, t, K, M)
-    gate = (rng.standard_normal((1, K)) * 2).astype(np.float32); up = rng.standard_normal((1, K)).astype(np.float32)
-    glu = (gate / (np.float32(1) + np.exp(-gate, dtype=np.float32)) * up).astype(np.float32)
-    dw = ctx.repack(ctx.upload(t, [K, M], w))
-    dg, du = ctx.upload(B.F32, [K, 1], gate), ctx.upload(B.F32, [K, 1], up)
-    do, dd = ctx.empty(B.F32, [K, 1]), ctx.empty(B.F32, [M, 1])
-    n0 = ctx.launches
-    ctx.mul_mat_swiglu(dw, dg, du, do, dd)
-    assert ctx.launches - n0 == 1
-    got_glu = ctx.download(do).reshape(1, K)
-    assert np.allclose(got_glu, glu, rtol=2e-6, atol=1e-7)
-    # the matmul consumed exactly the column it wrote out: compare against the oracle fed with that column
-    assert O.nmse(orc.mul_mat(t, w, K, M, got_glu, 1, act=O.ACT_Q8_1), ctx.download(dd)) < 1e-9
-    assert O.nmse(orc.mul_mat(t, w, K, M, glu, 1, act=O.ACT_CPU), ctx.download(dd)) < NMSE_HARNESS
-    # without a GLU output tensor
-    dd2 = ctx.empty(B.F32, [M, 1])
-    ctx.mul_mat_swiglu(dw, dg, du, None, dd2)
-    assert np.array_equal(ctx.download(dd), ctx.download(dd2))
-
-
 @pytest.mark.parametrize("t", [O.Q4_K, O.Q6_K])
 def test_mul_mat_multi_prefill_gemm(ctx, B, orc, t):
     """wq/wk/wv (and gate/up) of a prefill ubatch in ONE tcgen05 GEMM launch: grid.y walks the row tiles of all weights"""
