@@ -1,0 +1,48 @@
+// logits_probe.cpp -- TEST INFRASTRUCTURE (oracle/): a few lines against the reference's public llama.h API, linked with the reference's own
+// libllama / libggml compiled in place (oracle/_ref/avx2, `make -C oracle llama`).  It evaluates one fixed token sequence with the
+// reference runtime -- a prompt batch, then single-token decode steps that cross a KV-cache view boundary -- and writes the logits of
+// every step to a file.  tests/test_gpu_llama_logits.py runs it twice on the same random-block GGUF: on ggml-cpu (-ngl 0) and through
+// the B200 plugin (GGML_BACKEND_PATH, -ngl 99), and compares: the end-to-end parity check of the drop-in, through the reference's
+// graph builder, scheduler, allocator and KV cache (include/llama.h:437-996 for the calls used).
+// usage: logits_probe <model.gguf> <out.bin> <ngl> <n_prompt> <n_decode>
+#include "llama.h"
+#include "ggml-backend.h"
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+
+int main(int argc, char ** argv) {
+    if (argc < 6) { fprintf(stderr, "usage: %s model out ngl n_prompt n_decode\n", argv[0]); return 2; }
+    const int ngl = atoi(argv[3]), n_prompt = atoi(argv[4]), n_decode = atoi(argv[5]);
+    ggml_backend_load_all();
+    llama_backend_init();
+    llama_model_params mp = llama_model_default_params();
+    mp.n_gpu_layers = ngl;
+    mp.use_mmap = false;                                   // the loader's chunked async upload path: exercises the plugin's load-time repack hook
+    llama_model * model = llama_model_load_from_file(argv[1], mp);
+    if (!model) { fprintf(stderr, "logits_probe: cannot load %s\n", argv[1]); return 1; }
+    llama_context_params cp = llama_context_default_params();
+    cp.n_ctx = 1024; cp.n_batch = 512; cp.n_ubatch = 512; cp.n_threads = 8; cp.n_threads_batch = 8;
+    cp.flash_attn_type = LLAMA_FLASH_ATTN_TYPE_ENABLED;
+    cp.no_perf = true;
+    llama_context * ctx = llama_init_from_model(model, cp);
+    if (!ctx) { fprintf(stderr, "logits_probe: cannot create a context\n"); return 1; }
+    const int n_vocab = llama_vocab_n_tokens(llama_model_get_vocab(model));
+    FILE * out = fopen(argv[2], "wb");
+    if (!out) return 1;
+    unsigned s = 777;
+    auto next_tok = [&]() { s = s * 1664525u + 1013904223u; return (llama_token) ((s >> 8) % (unsigned) n_vocab); };
+    std::vector<llama_token> prompt(n_prompt);
+    for (auto & t : prompt) t = next_tok();
+    if (llama_decode(ctx, llama_batch_get_one(prompt.data(), n_prompt)) != 0) { fprintf(stderr, "logits_probe: prompt decode failed\n"); return 1; }
+    fwrite(llama_get_logits_ith(ctx, -1), sizeof(float), n_vocab, out);
+    for (int i = 0; i < n_decode; ++i) {
+        llama_token t = next_tok();
+        if (llama_decode(ctx, llama_batch_get_one(&t, 1)) != 0) { fprintf(stderr, "logits_probe: decode step %d failed\n", i); return 1; }
+        fwrite(llama_get_logits_ith(ctx, -1), sizeof(float), n_vocab, out);
+    }
+    fclose(out);
+    printf("logits_probe: wrote %d x %d logits (ngl %d)\n", 1 + n_decode, n_vocab, ngl);
+    llama_free(ctx); llama_model_free(model); llama_backend_free();
+    return 0;
+}

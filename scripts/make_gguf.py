@@ -22,6 +22,20 @@ def blocks(rng, t, K, M):
     """[M rows][K / blck * tsize bytes] of random blocks of ggml type t (same generator as bench.random_blocks, but one pool reused)"""
     nb = K // bench.BLCK[t] * M
     pool = bench.random_blocks(rng, t, min(nb, 1 << 18)).reshape(-1, bench.TSIZE[t])
+    # block scales such that the weights are zero-mean with std ~ 1 / sqrt(K): activations then stay O(1..100) through the layers, as in a
+    # trained model.  (With bench.random_blocks' scales -- fine for timing -- a q6_K matmul multiplies magnitudes by ~50 and two layers
+    # push activations past 65504 * 127, where the fp16 block scale of q8_1 overflows: tests/test_gpu_llama_logits.py found that.)
+    n = pool.shape[0]; target = 1.0 / np.sqrt(K)
+    f16 = lambda v: v.astype(np.float16).view(np.uint8).reshape(n, 2)
+    if t == bench.Q4_K:                                    # w = d * sc * q - dmin * m, sc, m in [0, 63], q in [0, 15]: dmin = 7.5 d centres it, std ~ 215 d
+        d = rng.uniform(0.5, 1.0, n) * (target / 160.0)
+        pool[:, 0:2] = f16(d); pool[:, 2:4] = f16(7.5 * d)
+    elif t == bench.Q6_K:                                  # w = d * sc * (q - 32), sc int8, q in [0, 63]: std ~ 1370 |d|
+        pool[:, 208:210] = f16(rng.uniform(-1, 1, n) * (target * np.sqrt(3) / 1370.0))
+    elif t == bench.Q4_0:                                  # w = d * (q - 8): std ~ 4.6 |d|
+        pool[:, 0:2] = f16(rng.uniform(-1, 1, n) * (target * np.sqrt(3) / 4.6))
+    elif t == bench.Q8_0:                                  # w = d * q, q int8: std ~ 74 |d|
+        pool[:, 0:2] = f16(rng.uniform(-1, 1, n) * (target * np.sqrt(3) / 74.0))
     reps = (nb + pool.shape[0] - 1) // pool.shape[0]
     raw = np.tile(pool, (reps, 1))[:nb]
     return raw.reshape(M, K // bench.BLCK[t] * bench.TSIZE[t])

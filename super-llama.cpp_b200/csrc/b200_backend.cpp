@@ -603,7 +603,30 @@ static bool mm_weight_ok(const ggml_tensor * w) {
     return false;
 }
 
+// GGML_B200_DECLINE_OPS=ROPE,GLU,... (debugging): leave these ops to the CPU backend, to bisect a wrong result in a whole graph
+static bool op_declined(const ggml_tensor * op) {
+    static const char * env = getenv("GGML_B200_DECLINE_OPS");
+    if (!env) return false;
+    static const struct { int op; const char * name; } names[] = {
+        { GGML_OP_MUL_MAT, "MUL_MAT" }, { GGML_OP_MUL_MAT_ID, "MUL_MAT_ID" }, { GGML_OP_FLASH_ATTN_EXT, "FLASH_ATTN_EXT" }, { GGML_OP_RMS_NORM, "RMS_NORM" },
+        { GGML_OP_ADD, "ADD" }, { GGML_OP_MUL, "MUL" }, { GGML_OP_ROPE, "ROPE" }, { GGML_OP_SET_ROWS, "SET_ROWS" }, { GGML_OP_GET_ROWS, "GET_ROWS" },
+        { GGML_OP_CPY, "CPY" }, { GGML_OP_CONT, "CONT" }, { GGML_OP_GLU, "GLU" }, { GGML_OP_SCALE, "SCALE" } };
+    for (const auto & n : names) {
+        if (n.op != (int) op->op) continue;
+        const char * f = strstr(env, n.name);
+        while (f) {                                                  // whole-word match (MUL vs MUL_MAT)
+            const char after = f[strlen(n.name)]; const bool start_ok = f == env || f[-1] == ',';
+            if (start_ok && (after == 0 || after == ',')) {
+                if (!strcmp(n.name, "MUL_MAT") && getenv("GGML_B200_DECLINE_DECODE_ONLY") && op->ne[1] > 1) return false;
+                return true;
+            }
+            f = strstr(f + 1, n.name);
+        }
+    }
+    return false;
+}
 static bool dev_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
+    if (op_declined(op)) return false;
     switch ((int) op->op) {
         case GGML_OP_NONE: case GGML_OP_RESHAPE: case GGML_OP_VIEW: case GGML_OP_PERMUTE: case GGML_OP_TRANSPOSE:
             return true;
