@@ -166,17 +166,24 @@ __global__ void __launch_bounds__(256) k_scale(const float * x, float * y, int64
 
 // ---- ROPE (GGML_ROPE_TYPE_NORMAL = 0: pairs (2i, 2i+1); NEOX = 2: pairs (i, i + n_dims/2)), YaRN as ops.cpp:5524-5547 -----------------
 struct gl_rope { int n_dims, neox; float freq_scale, ext_factor, attn_factor, theta_scale, corr0, corr1; const int32_t * pos; const float * ff; };
-// one head row (i1 = head, i2 = token, i3 = batch); `cache` (optional): the f16 KV-cache row segment that takes a copy of the result
-static __device__ __forceinline__ void gl_rope_row(const gl_view & x, const gl_view & y, const gl_rope & r, int64_t i1, int64_t i2, int64_t i3, __half * cache) {
-    const float * xr = (const float *) (x.p + i1 * x.nb[1] + i2 * x.nb[2] + i3 * x.nb[3]);
-    float *       yr = (float *) (y.p + i1 * y.nb[1] + i2 * y.nb[2] + i3 * y.nb[3]);
+// head rows [h0, h1) of token i2, batch i3: the angle of a pair depends on the position and the pair only, so it is evaluated once and
+// applied to every head of the group (prefill: 8 heads per CTA; decode: one, for the parallelism).  cache(h): NULL or the f16 KV-cache row
+// segment that takes a copy of head h's result
+template <class C>
+static __device__ __forceinline__ void gl_rope_rows(const gl_view & x, const gl_view & y, const gl_rope & r, int64_t h0, int64_t h1, int64_t i2, int64_t i3, C cache) {
+    const char * xb = x.p + i2 * x.nb[2] + i3 * x.nb[3];
+    char *       yb = y.p + i2 * y.nb[2] + i3 * y.nb[3];
     const float p = (float) r.pos[i2];
     for (int64_t ip = threadIdx.x; ip < x.ne[0] / 2; ip += blockDim.x) {       // pair index
         const int64_t i0 = 2 * ip;
         if (i0 >= r.n_dims) {                                                   // channels beyond n_dims pass through
-            const float x0 = xr[i0], x1 = xr[i0 + 1];
-            yr[i0] = x0; yr[i0 + 1] = x1;
-            if (cache) { cache[i0] = __float2half_rn(x0); cache[i0 + 1] = __float2half_rn(x1); }
+            for (int64_t h = h0; h < h1; ++h) {
+                const float * xr = (const float *) (xb + h * x.nb[1]); float * yr = (float *) (yb + h * y.nb[1]);
+                const float x0 = xr[i0], x1 = xr[i0 + 1];
+                yr[i0] = x0; yr[i0 + 1] = x1;
+                __half * ch = cache(h);
+                if (ch) { ch[i0] = __float2half_rn(x0); ch[i0 + 1] = __float2half_rn(x1); }
+            }
             continue;
         }
         const float theta_extrap = p * powf(r.theta_scale, (float) ip) / (r.ff ? r.ff[ip] : 1.0f);
@@ -190,15 +197,22 @@ static __device__ __forceinline__ void gl_rope_row(const gl_view & x, const gl_v
         }
         float sn, cs; sincosf(theta, &sn, &cs); sn *= mscale; cs *= mscale;
         const int64_t ia = r.neox ? ip : i0, ib = r.neox ? ip + r.n_dims / 2 : i0 + 1;
-        const float x0 = xr[ia], x1 = xr[ib];
-        const float y0 = x0 * cs - x1 * sn, y1 = x0 * sn + x1 * cs;
-        yr[ia] = y0; yr[ib] = y1;
-        if (cache) { cache[ia] = __float2half_rn(y0); cache[ib] = __float2half_rn(y1); }
+        for (int64_t h = h0; h < h1; ++h) {
+            const float * xr = (const float *) (xb + h * x.nb[1]); float * yr = (float *) (yb + h * y.nb[1]);
+            const float x0 = xr[ia], x1 = xr[ib];
+            const float y0 = x0 * cs - x1 * sn, y1 = x0 * sn + x1 * cs;
+            yr[ia] = y0; yr[ib] = y1;
+            __half * ch = cache(h);
+            if (ch) { ch[ia] = __float2half_rn(y0); ch[ib] = __float2half_rn(y1); }
+        }
     }
 }
-__global__ void __launch_bounds__(128) k_rope(const gl_view x, const gl_view y, const gl_rope r) {
+struct gl_no_cache { __device__ __forceinline__ __half * operator()(int64_t) const { return nullptr; } };
+static int gl_rope_heads_per_cta(const ggml_tensor * t) { return t->ne[2] * t->ne[3] >= 64 ? (int) (t->ne[1] < 8 ? t->ne[1] : 8) : 1; }
+__global__ void __launch_bounds__(128) k_rope(const gl_view x, const gl_view y, const gl_rope r, int hb) {
     GL_PDL();
-    gl_rope_row(x, y, r, blockIdx.x, blockIdx.y, blockIdx.z, nullptr);          // head, token, batch
+    const int64_t h0 = (int64_t) blockIdx.x * hb, h1 = h0 + hb < x.ne[1] ? h0 + hb : x.ne[1];
+    gl_rope_rows(x, y, r, h0, h1, blockIdx.y, blockIdx.z, gl_no_cache());       // head group, token, batch
 }
 
 // ---- SET_ROWS: dst row idx[i1, i2 % ne11, i3 % ne12] <- src row (i1, i2, i3), f32 -> f32 / f16 ---------------------------------------------
@@ -281,8 +295,8 @@ __global__ void __launch_bounds__(256) k_swiglu(const gl_view a, const gl_view b
 // llama layer as one launch.  CTAs [0, nq): one Q head row each; [nq, nq + nk): one K head row each, whose result also goes (f16) to
 // the cache row idx[token] that the SET_ROWS node behind it names; the rest: chunks of the V rows (as k_set_rows) -----------------------------
 struct gl_rope_kv {
-    gl_view qx, qy; gl_rope qr; int nq;
-    gl_view kx, ky; gl_rope kr; int nk;
+    gl_view qx, qy; gl_rope qr; int nq, qhb, qng;   // nq CTAs = tokens * qng head groups of qhb heads
+    gl_view kx, ky; gl_rope kr; int nk, khb, kng;
     gl_view kidx, kd; int64_t k_ne0;              // SET_ROWS(K): its src is ky seen as rows of k_ne0 floats (k_ne0 % ky.ne[0] == 0)
     gl_view vs, vidx, vd; int vchunks;
 };
@@ -290,17 +304,20 @@ __global__ void __launch_bounds__(128) k_rope_kv(const gl_rope_kv a) {
     GL_PDL();
     int b = blockIdx.x;
     if (b < a.nq) {
-        const int64_t i1 = b % a.qx.ne[1], t = b / a.qx.ne[1];
-        gl_rope_row(a.qx, a.qy, a.qr, i1, t % a.qx.ne[2], t / a.qx.ne[2], nullptr);
+        const int64_t g = b % a.qng, t = b / a.qng, h0 = g * a.qhb, h1 = h0 + a.qhb < a.qx.ne[1] ? h0 + a.qhb : a.qx.ne[1];
+        gl_rope_rows(a.qx, a.qy, a.qr, h0, h1, t % a.qx.ne[2], t / a.qx.ne[2], gl_no_cache());
         return;
     }
     b -= a.nq;
     if (b < a.nk) {
-        const int64_t i1 = b % a.kx.ne[1], t = b / a.kx.ne[1];
-        const int64_t e = (int64_t) b * a.ky.ne[0];                              // first element of this head row in the contiguous result
-        const int64_t r = e / a.k_ne0, c = e - r * a.k_ne0;
-        const int64_t row = *(const int64_t *) (a.kidx.p + r * a.kidx.nb[0]);
-        gl_rope_row(a.kx, a.ky, a.kr, i1, t % a.kx.ne[2], t / a.kx.ne[2], (__half *) (a.kd.p + row * a.kd.nb[1]) + c);
+        const int64_t g = b % a.kng, t = b / a.kng, h0 = g * a.khb, h1 = h0 + a.khb < a.kx.ne[1] ? h0 + a.khb : a.kx.ne[1];
+        auto cache = [&](int64_t h) {
+            const int64_t e = (t * a.kx.ne[1] + h) * a.ky.ne[0];                 // first element of this head row in the contiguous result
+            const int64_t r = e / a.k_ne0, c = e - r * a.k_ne0;
+            const int64_t row = *(const int64_t *) (a.kidx.p + r * a.kidx.nb[0]);
+            return (__half *) (a.kd.p + row * a.kd.nb[1]) + c;
+        };
+        gl_rope_rows(a.kx, a.ky, a.kr, h0, h1, t % a.kx.ne[2], t / a.kx.ne[2], cache);
         return;
     }
     b -= a.nk;
@@ -446,8 +463,12 @@ int b200_glue_rope_kv(b200_ctx * ctx, struct ggml_tensor * rq, struct ggml_tenso
     for (int o = 0; o < 4; ++o) if (outs[o] && (!gl_span_disjoint(outs[o], kidx) || !gl_span_disjoint(outs[o], vidx) || !gl_span_disjoint(outs[o], rk->src[1]))) { b200_set_error("rope_kv: check 9"); return B200_ERR_UNSUPPORTED; }
     gl_rope_kv a;
     memset(&a, 0, sizeof a);
-    if (rq) { a.qx = gl_of(rq->src[0]); a.qy = gl_of(rq); a.qr = gl_rope_params(rq); a.nq = (int) gl_nrows(rq); }
-    a.kx = gl_of(rk->src[0]); a.ky = gl_of(rk); a.kr = gl_rope_params(rk); a.nk = (int) gl_nrows(rk);
+    if (rq) {
+        a.qx = gl_of(rq->src[0]); a.qy = gl_of(rq); a.qr = gl_rope_params(rq);
+        a.qhb = gl_rope_heads_per_cta(rq); a.qng = (int) ((rq->ne[1] + a.qhb - 1) / a.qhb); a.nq = (int) (rq->ne[2] * rq->ne[3]) * a.qng;
+    }
+    a.kx = gl_of(rk->src[0]); a.ky = gl_of(rk); a.kr = gl_rope_params(rk);
+    a.khb = gl_rope_heads_per_cta(rk); a.kng = (int) ((rk->ne[1] + a.khb - 1) / a.khb); a.nk = (int) (rk->ne[2] * rk->ne[3]) * a.kng;
     a.kidx = gl_of(kidx); a.kd = gl_of(sk); a.k_ne0 = ks->ne[0];
     a.vs = gl_of(vs); a.vidx = gl_of(vidx); a.vd = gl_of(sv); a.vchunks = (int) ((vs->ne[0] + GL_CHUNK - 1) / GL_CHUNK);
     if (gl_nrows(rk) > 0x3fffffff || (rq && gl_nrows(rq) > 0x3fffffff)) return B200_ERR_UNSUPPORTED;
@@ -511,7 +532,8 @@ int b200_glue_compute(b200_ctx * ctx, struct ggml_tensor * op) {
         }
         case GGML_OP_ROPE: {
             const gl_rope r = gl_rope_params(op);
-            GL_LAUNCH(gl_launch(ctx, k_rope, dim3(dim3((unsigned) op->ne[1], (unsigned) op->ne[2], (unsigned) op->ne[3])), 128, gl_of(a), gl_of(op), r));
+            const int hb = gl_rope_heads_per_cta(op);
+            GL_LAUNCH(gl_launch(ctx, k_rope, dim3((unsigned) ((op->ne[1] + hb - 1) / hb), (unsigned) op->ne[2], (unsigned) op->ne[3]), 128, gl_of(a), gl_of(op), r, hb));
             return B200_OK;
         }
         case GGML_OP_SET_ROWS: {
