@@ -22,7 +22,8 @@ int main(int argc, char ** argv) {
     llama_model * model = llama_model_load_from_file(argv[1], mp);
     if (!model) { fprintf(stderr, "logits_probe: cannot load %s\n", argv[1]); return 1; }
     llama_context_params cp = llama_context_default_params();
-    cp.n_ctx = 1024; cp.n_batch = 512; cp.n_ubatch = 512; cp.n_threads = 8; cp.n_threads_batch = 8;
+    cp.n_ctx = 2048; cp.n_batch = 1024; cp.n_ubatch = 512;   // prompts up to 1024 tokens, evaluated as ubatches of 512
+    cp.n_threads = 8; cp.n_threads_batch = 8;
     cp.flash_attn_type = LLAMA_FLASH_ATTN_TYPE_ENABLED;
     cp.no_perf = true;
     llama_context * ctx = llama_init_from_model(model, cp);

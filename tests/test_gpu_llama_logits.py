@@ -1,6 +1,6 @@
 """GPU test (-m gpu): end-to-end parity of the drop-in.  oracle/_ref/avx2/logits_probe (oracle/logits_probe.cpp: a few lines against the
-reference's llama.h, linked with the reference's own libllama / libggml compiled in place) evaluates one token sequence -- a 250-token
-prompt batch, then 12 single-token decode steps that cross the 256-row KV view boundary -- on a random-block GGUF, once on ggml-cpu and
+reference's llama.h, linked with the reference's own libllama / libggml compiled in place) evaluates one token sequence -- a prompt (one or two
+ubatches), then 12 single-token decode steps that cross a 256-row KV view boundary -- on a random-block GGUF, once on ggml-cpu and
 once with every layer offloaded to the B200 plugin (GGML_BACKEND_PATH).  Through the plugin this exercises what no operator test does:
 the loader's chunked uploads with load-time repack, the scheduler's single device split, graph_optimize, the fused node groups, CUDA-graph
 recording / replay / re-recording when the KV view grows.  The logits of every step must agree with ggml-cpu's.
@@ -19,17 +19,17 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PROBE = os.path.join(ROOT, "oracle", "_ref", "avx2", "logits_probe")
 PLUGIN = os.path.join(ROOT, "super-llama.cpp_b200", "libggml-b200.so")
 OUT = os.path.join(ROOT, "gpurun_out")
-N_PROMPT, N_DECODE = 250, 12
+N_DECODE = 12
 
 
-def run_probe(gguf, tag, ngl, env_extra=None):
+def run_probe(gguf, tag, ngl, env_extra=None, n_prompt=250):
     out = os.path.join(OUT, f"logits_{tag}.bin")
     env = dict(os.environ, **(env_extra or {}))
     if ngl:
         env["GGML_BACKEND_PATH"] = PLUGIN
     else:
         env.pop("GGML_BACKEND_PATH", None)
-    p = subprocess.run([PROBE, gguf, out, str(ngl), str(N_PROMPT), str(N_DECODE)], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
+    p = subprocess.run([PROBE, gguf, out, str(ngl), str(n_prompt), str(N_DECODE)], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
     assert p.returncode == 0 and "logits_probe: wrote" in p.stdout, p.stdout[-3000:]
     a = np.fromfile(out, np.float32).reshape(1 + N_DECODE, -1)
     os.remove(out)
@@ -40,8 +40,10 @@ def nmse(ref, got):
     return float(((ref.astype(np.float64) - got) ** 2).sum() / (ref.astype(np.float64) ** 2).sum())
 
 
-@pytest.mark.parametrize("model,quant,layers", [("8b", "q4_k_m", 4), ("tinyllama", "q4_0", 6), ("tinyllama", "q8_0", 4)])
-def test_llama_logits_plugin_vs_ggml_cpu(model, quant, layers):
+# n_prompt 250: one ubatch, decode crosses the 256-row KV view; 760: two ubatches (512 + 248), decode attends over > 512 keys (the
+# GQA-grouped tensor-core decode attention) and crosses 768
+@pytest.mark.parametrize("model,quant,layers,n_prompt", [("8b", "q4_k_m", 4, 250), ("tinyllama", "q4_0", 6, 250), ("tinyllama", "q8_0", 4, 250), ("8b", "q4_k_m", 2, 760)])
+def test_llama_logits_plugin_vs_ggml_cpu(model, quant, layers, n_prompt):
     if not os.path.exists(PROBE):
         pytest.skip("oracle/_ref/avx2/logits_probe not built (make -C oracle llama; needs /root/reference at build time)")
     os.makedirs(OUT, exist_ok=True)
@@ -49,9 +51,9 @@ def test_llama_logits_plugin_vs_ggml_cpu(model, quant, layers):
     subprocess.check_call([os.sys.executable, os.path.join(ROOT, "scripts", "make_gguf.py"), "--model", model, "--quant", quant, "--layers", str(layers), "-o", gguf],
                           stdout=subprocess.DEVNULL)
     try:
-        cpu, _ = run_probe(gguf, "cpu", 0)
-        dev, log = run_probe(gguf, "b200", 99, {"GGML_B200_GRAPH_STATS": "1"})
-        plain, _ = run_probe(gguf, "b200_plain", 99, {"GGML_B200_NO_FUSE": "1", "GGML_B200_GRAPHS": "0"})
+        cpu, _ = run_probe(gguf, "cpu", 0, n_prompt=n_prompt)
+        dev, log = run_probe(gguf, "b200", 99, {"GGML_B200_GRAPH_STATS": "1"}, n_prompt=n_prompt)
+        plain, _ = run_probe(gguf, "b200_plain", 99, {"GGML_B200_NO_FUSE": "1", "GGML_B200_GRAPHS": "0"}, n_prompt=n_prompt)
     finally:
         os.remove(gguf)
     assert np.isfinite(cpu).all() and np.isfinite(dev).all()
