@@ -106,3 +106,30 @@ def test_product_never_references_oracle():
                 if re.search(r"liboracle|ggml_oracle|ref_driver|libggml-ref|import oracle|from oracle", txt):
                     bad.append(f)
     assert not bad, bad
+
+
+def test_graph_optimize_reorders_weight_matmuls_only(tmp_path):
+    """host logic of the plugin's graph_optimize (no GPU): the weight matmuls of one activation become adjacent, equal weight types side by
+    side; a matmul over a KV-cache view stays put; every node still follows its sources (tests/reorder_probe.cpp through get_proc_address)"""
+    import subprocess
+    plugin = os.path.join(ROOT, "super-llama.cpp_b200", "libggml-b200.so")
+    if not os.path.exists(plugin):
+        pytest.skip("libggml-b200.so not built")
+    exe = str(tmp_path / "reorder_probe")
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-I" + os.path.join(ROOT, "include"), os.path.join(ROOT, "tests", "reorder_probe.cpp"), "-o", exe, "-ldl"])
+    for vtype in (12, 14):
+        out = subprocess.run([exe, plugin, str(vtype)], stdout=subprocess.PIPE, text=True, timeout=60)
+        assert out.returncode == 0 and "dependencies: OK" in out.stdout, out.stdout
+        order = out.stdout.splitlines()[0].split()[1:]
+        pos = {n: i for i, n in enumerate(order)}
+        for il in (0, 1):
+            q, k, v = pos[f"Q{il}"], pos[f"K{il}"], pos[f"V{il}"]
+            assert max(q, k, v) - min(q, k, v) == 2, order                         # adjacent
+            assert pos[f"Qrope{il}"] > max(q, k, v) and pos[f"Krope{il}"] > pos[f"Qrope{il}"]
+            assert pos[f"setK{il}"] == pos[f"Krope{il}"] + 1 and pos[f"setV{il}"] == pos[f"setK{il}"] + 1
+            assert pos[f"KQ{il}"] > pos[f"setV{il}"]                               # not a weight: not hoisted over the cache write
+            assert abs(pos[f"up{il}"] - pos[f"gate{il}"]) == 1
+        if vtype == 14:
+            assert abs(pos["Q1"] - pos["K1"]) == 1                                 # q4_K, q4_K, then the q6_K one
+        with_env = subprocess.run([exe, plugin, str(vtype)], stdout=subprocess.PIPE, text=True, timeout=60, env=dict(os.environ, GGML_B200_NO_REORDER="1"))
+        assert with_env.stdout.splitlines()[0].split()[1:6] == ["norm0", "Q0", "Q3_0", "Qrope0", "V0"]
