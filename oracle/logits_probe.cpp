@@ -4,7 +4,7 @@
 // every step to a file.  tests/test_gpu_llama_logits.py runs it twice on the same random-block GGUF: on ggml-cpu (-ngl 0) and through
 // the B200 plugin (GGML_BACKEND_PATH, -ngl 99), and compares: the end-to-end parity check of the drop-in, through the reference's
 // graph builder, scheduler, allocator and KV cache (include/llama.h:437-996 for the calls used).
-// usage: logits_probe <model.gguf> <out.bin> <ngl> <n_prompt> <n_decode>
+// usage: logits_probe <model.gguf> <out.bin> <ngl> <n_prompt> <n_decode> [tokens per decode step = 1]
 #include "llama.h"
 #include "ggml-backend.h"
 #include <cstdio>
@@ -13,7 +13,7 @@
 
 int main(int argc, char ** argv) {
     if (argc < 6) { fprintf(stderr, "usage: %s model out ngl n_prompt n_decode\n", argv[0]); return 2; }
-    const int ngl = atoi(argv[3]), n_prompt = atoi(argv[4]), n_decode = atoi(argv[5]);
+    const int ngl = atoi(argv[3]), n_prompt = atoi(argv[4]), n_decode = atoi(argv[5]), n_step = argc > 6 ? atoi(argv[6]) : 1;
     ggml_backend_load_all();
     llama_backend_init();
     llama_model_params mp = llama_model_default_params();
@@ -38,8 +38,9 @@ int main(int argc, char ** argv) {
     if (llama_decode(ctx, llama_batch_get_one(prompt.data(), n_prompt)) != 0) { fprintf(stderr, "logits_probe: prompt decode failed\n"); return 1; }
     fwrite(llama_get_logits_ith(ctx, -1), sizeof(float), n_vocab, out);
     for (int i = 0; i < n_decode; ++i) {
-        llama_token t = next_tok();
-        if (llama_decode(ctx, llama_batch_get_one(&t, 1)) != 0) { fprintf(stderr, "logits_probe: decode step %d failed\n", i); return 1; }
+        std::vector<llama_token> t(n_step);                 // n_step > 1: a few positions of the same sequence per step (speculative-style small batch)
+        for (auto & x : t) x = next_tok();
+        if (llama_decode(ctx, llama_batch_get_one(t.data(), n_step)) != 0) { fprintf(stderr, "logits_probe: decode step %d failed\n", i); return 1; }
         fwrite(llama_get_logits_ith(ctx, -1), sizeof(float), n_vocab, out);
     }
     fclose(out);

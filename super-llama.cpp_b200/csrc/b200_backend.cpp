@@ -470,7 +470,9 @@ static bool graph_identity(const ggml_cgraph * g, uint64_t & h1, uint64_t & h2) 
             hash_tensor(h1, h2, s);
         }
         // prefill-sized work is not launch-bound and its paths may size scratch by content
-        if ((n->op == GGML_OP_MUL_MAT || n->op == GGML_OP_MUL_MAT_ID || n->op == GGML_OP_FLASH_ATTN_EXT) && n->ne[1] * n->ne[2] * n->ne[3] > 64) return false;
+        const int64_t tokens = n->op == GGML_OP_MUL_MAT ? n->ne[1] * n->ne[2] * n->ne[3] : n->op == GGML_OP_MUL_MAT_ID ? n->ne[2] * n->ne[3] :
+                               n->op == GGML_OP_FLASH_ATTN_EXT ? n->ne[2] * n->ne[3] : 0;         // (attention result: [head size, heads, tokens])
+        if (tokens > 64) return false;
     }
     return work >= 2;
 }

@@ -22,14 +22,14 @@ OUT = os.path.join(ROOT, "gpurun_out")
 N_DECODE = 12
 
 
-def run_probe(gguf, tag, ngl, env_extra=None, n_prompt=250):
+def run_probe(gguf, tag, ngl, env_extra=None, n_prompt=250, n_step=1):
     out = os.path.join(OUT, f"logits_{tag}.bin")
     env = dict(os.environ, **(env_extra or {}))
     if ngl:
         env["GGML_BACKEND_PATH"] = PLUGIN
     else:
         env.pop("GGML_BACKEND_PATH", None)
-    p = subprocess.run([PROBE, gguf, out, str(ngl), str(n_prompt), str(N_DECODE)], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
+    p = subprocess.run([PROBE, gguf, out, str(ngl), str(n_prompt), str(N_DECODE), str(n_step)], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=900)
     assert p.returncode == 0 and "logits_probe: wrote" in p.stdout, p.stdout[-3000:]
     a = np.fromfile(out, np.float32).reshape(1 + N_DECODE, -1)
     os.remove(out)
@@ -42,8 +42,10 @@ def nmse(ref, got):
 
 # n_prompt 250: one ubatch, decode crosses the 256-row KV view; 760: two ubatches (512 + 248), decode attends over > 512 keys (the
 # GQA-grouped tensor-core decode attention) and crosses 768
-@pytest.mark.parametrize("model,quant,layers,n_prompt", [("8b", "q4_k_m", 4, 250), ("tinyllama", "q4_0", 6, 250), ("tinyllama", "q8_0", 4, 250), ("8b", "q4_k_m", 2, 760)])
-def test_llama_logits_plugin_vs_ggml_cpu(model, quant, layers, n_prompt):
+# n_step 4: every decode step carries four positions of the sequence (MUL_MAT with 4 columns, attention with 4 queries, 4 cache rows written)
+@pytest.mark.parametrize("model,quant,layers,n_prompt,n_step", [("8b", "q4_k_m", 4, 250, 1), ("tinyllama", "q4_0", 6, 250, 1), ("tinyllama", "q8_0", 4, 250, 1),
+                                                              ("8b", "q4_k_m", 2, 760, 1), ("8b", "q4_k_m", 2, 230, 4)])
+def test_llama_logits_plugin_vs_ggml_cpu(model, quant, layers, n_prompt, n_step):
     if not os.path.exists(PROBE):
         pytest.skip("oracle/_ref/avx2/logits_probe not built (make -C oracle llama; needs /root/reference at build time)")
     os.makedirs(OUT, exist_ok=True)
@@ -51,9 +53,9 @@ def test_llama_logits_plugin_vs_ggml_cpu(model, quant, layers, n_prompt):
     subprocess.check_call([os.sys.executable, os.path.join(ROOT, "scripts", "make_gguf.py"), "--model", model, "--quant", quant, "--layers", str(layers), "-o", gguf],
                           stdout=subprocess.DEVNULL)
     try:
-        cpu, _ = run_probe(gguf, "cpu", 0, n_prompt=n_prompt)
-        dev, log = run_probe(gguf, "b200", 99, {"GGML_B200_GRAPH_STATS": "1"}, n_prompt=n_prompt)
-        plain, _ = run_probe(gguf, "b200_plain", 99, {"GGML_B200_NO_FUSE": "1", "GGML_B200_GRAPHS": "0"}, n_prompt=n_prompt)
+        cpu, _ = run_probe(gguf, "cpu", 0, n_prompt=n_prompt, n_step=n_step)
+        dev, log = run_probe(gguf, "b200", 99, {"GGML_B200_GRAPH_STATS": "1"}, n_prompt=n_prompt, n_step=n_step)
+        plain, _ = run_probe(gguf, "b200_plain", 99, {"GGML_B200_NO_FUSE": "1", "GGML_B200_GRAPHS": "0"}, n_prompt=n_prompt, n_step=n_step)
     finally:
         os.remove(gguf)
     assert np.isfinite(cpu).all() and np.isfinite(dev).all()
