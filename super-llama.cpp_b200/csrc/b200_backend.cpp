@@ -344,6 +344,7 @@ static int next_work(const ggml_cgraph * g, int i) {            // next node aft
 }
 // node i is a ROPE: if it opens the KV-cache update of a llama layer -- [ROPE(Q)] ROPE(K) SET_ROWS(K) SET_ROWS(V), only views in between --
 // run the whole run as one launch and return the index of its last node; -1 when it is not that pattern (b200_glue_rope_kv checks the rest)
+static bool ranges_overlap(const ggml_tensor * a, const ggml_tensor * b);
 static int try_rope_kv(b200_backend_ctx * c, ggml_cgraph * g, int i) {
     int j1 = next_work(g, i), j2 = j1 < 0 ? -1 : next_work(g, j1), j3 = -1;
     if (j2 < 0) return -1;
@@ -351,13 +352,21 @@ static int try_rope_kv(b200_backend_ctx * c, ggml_cgraph * g, int i) {
     if (g->nodes[j1]->op == GGML_OP_ROPE) {
         j3 = next_work(g, j2);
         if (j3 < 0) return -1;
-        rq = g->nodes[i]; rk = g->nodes[j1]; sk = g->nodes[j2]; sv = g->nodes[j3];
+        sk = g->nodes[j2]; sv = g->nodes[j3];
+        // either order: the rope that SET_ROWS(K) stores is the K one (graph_optimize puts it first, see there)
+        const bool first_is_k = sk->op == GGML_OP_SET_ROWS && sk->src[0] && sk->src[0]->data == g->nodes[i]->data;
+        rk = first_is_k ? g->nodes[i] : g->nodes[j1]; rq = first_is_k ? g->nodes[j1] : g->nodes[i];
     } else { rk = g->nodes[i]; sk = g->nodes[j1]; sv = g->nodes[j2]; j3 = j2; }
     if (sk->op != GGML_OP_SET_ROWS || sv->op != GGML_OP_SET_ROWS) return -1;
     if (b200_glue_rope_kv(c->ctx, rq, rk, sk, sv) != B200_OK) {
         static int said = 0;
         if (!said++ && getenv("GGML_B200_DEBUG")) B200_LOG("rope/KV-store fusion declined at node %d (%s): %s", i, g->nodes[i]->name, b200_last_error());
-        return -1;
+        // ROPE(K) ROPE(Q) SET_ROWS SET_ROWS where the allocator put Q's result over K's input (free blocks coalesce): K + the two cache
+        // writes still share a launch, ROPE(Q) follows.  It moves behind the SET_ROWS nodes, which it must not disturb.
+        if (!rq || rk != g->nodes[i]) return -1;
+        const ggml_tensor * keep[5] = { rk, sk->src[0], sv->src[0], sk, sv };
+        for (const ggml_tensor * t : keep) if (ranges_overlap(rq, t)) return -1;
+        if (b200_glue_rope_kv(c->ctx, nullptr, rk, sk, sv) != B200_OK || compute_node(c->ctx, rq) != B200_OK) return -1;
     }
     ggml_tensor * outs[4] = { rq, rk, sk, sv };
     for (ggml_tensor * t : outs) if (t) b200_note_write(c->ctx, t->data, tensor_nbytes(t));
@@ -563,6 +572,26 @@ static void be_graph_optimize(ggml_backend_t, ggml_cgraph * g) {
             if (m[0]->src[0]->type != m[1]->src[0]->type && m[0]->src[0]->type == m[2]->src[0]->type) { g->nodes[members[1]] = m[2]; g->nodes[members[2]] = m[1]; }
         }
         i = at - 1;
+    }
+    // ROPE(Q) [views] ROPE(K) [views] SET_ROWS(K result): run ROPE(K) first.  The allocator gives neither rope its input's memory (their
+    // parents are reshapes), so in the original order ROPE(K)'s result lands in the block Q's matmul result has just vacated, and the two
+    // ropes could not share a launch (b200_glue_rope_kv declines when one section writes what another reads).  With K first its result is
+    // allocated while Q's input is still live, and Q's (larger) result cannot fit the block K's input vacates.
+    for (int i = 0; i + 2 < g->n_nodes; ++i) {
+        if (g->nodes[i]->op != GGML_OP_ROPE) continue;
+        int j = i + 1; while (j < g->n_nodes && op_is_view((int) g->nodes[j]->op)) ++j;
+        if (j >= g->n_nodes || g->nodes[j]->op != GGML_OP_ROPE) continue;
+        int k = j + 1; while (k < g->n_nodes && op_is_view((int) g->nodes[k]->op)) ++k;
+        if (k >= g->n_nodes || g->nodes[k]->op != GGML_OP_SET_ROWS) continue;
+        const ggml_tensor * stored = g->nodes[k]->src[0];
+        if (!stored || (stored != g->nodes[j] && stored->view_src != g->nodes[j])) continue;
+        bool used = false;                                          // nothing in between may read ROPE(Q)'s result (only views are in between)
+        for (int m = i + 1; m <= j && !used; ++m) for (int sidx = 0; sidx < GGML_MAX_SRC; ++sidx) used |= g->nodes[m]->src[sidx] == g->nodes[i];
+        if (used) continue;
+        ggml_tensor * rq = g->nodes[i];
+        for (int m = i; m < j; ++m) g->nodes[m] = g->nodes[m + 1];
+        g->nodes[j] = rq;
+        i = k;
     }
 }
 static const ggml_backend_i k_backend_iface = {

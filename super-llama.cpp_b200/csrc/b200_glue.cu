@@ -244,13 +244,18 @@ __global__ void __launch_bounds__(256) k_set_rows(const gl_view s, const gl_view
 }
 
 // ---- GET_ROWS (f32 rows): dst[:, i10, i11, i12] = src0[:, ids[i10, i11, i12], i11, i12] -------------------------------------------------
-__global__ void __launch_bounds__(256) k_get_rows_f32(const gl_view s, const gl_view idx, const gl_view d) {
+__global__ void __launch_bounds__(256) k_get_rows_f32(const gl_view s, const gl_view idx, const gl_view d, int chunks) {
     GL_PDL();
-    int64_t i10, i11, i12; gl_unrow(blockIdx.x, d, i10, i11, i12);
+    const int64_t r = blockIdx.x / chunks; const int64_t c0 = (int64_t) (blockIdx.x - r * chunks) * GL_CHUNK;
+    int64_t i10, i11, i12; gl_unrow(r, d, i10, i11, i12);
     const int32_t row = *(const int32_t *) (idx.p + i10 * idx.nb[0] + i11 * idx.nb[1] + i12 * idx.nb[2]);
     const float * sr = (const float *) (s.p + (int64_t) row * s.nb[1] + i11 * s.nb[2] + i12 * s.nb[3]);
     float * dr = (float *) (d.p + i10 * d.nb[1] + i11 * d.nb[2] + i12 * d.nb[3]);
-    for (int64_t i = threadIdx.x; i < d.ne[0]; i += blockDim.x) dr[i] = sr[i];
+    float v[4];
+    #pragma unroll
+    for (int k = 0; k < 4; ++k) { const int64_t i = c0 + k * 256 + threadIdx.x; if (i < d.ne[0]) v[k] = sr[i]; }
+    #pragma unroll
+    for (int k = 0; k < 4; ++k) { const int64_t i = c0 + k * 256 + threadIdx.x; if (i < d.ne[0]) dr[i] = v[k]; }
 }
 
 // ---- CPY / CONT / DUP: same logical element order, either side strided; f32 / f16 in, f32 / f16 out -----------------------------------------
@@ -548,7 +553,7 @@ int b200_glue_compute(b200_ctx * ctx, struct ggml_tensor * op) {
             return B200_OK;
         }
         case GGML_OP_GET_ROWS:
-            GL_LAUNCH(gl_launch(ctx, k_get_rows_f32, dim3(rows), 256, gl_of(a), gl_of(b), gl_of(op)));
+            GL_LAUNCH(gl_launch(ctx, k_get_rows_f32, dim3(rows * chunks), 256, gl_of(a), gl_of(b), gl_of(op), chunks));
             return B200_OK;
         case GGML_OP_CPY: case GGML_OP_CONT: case GGML_OP_DUP: {
             const int64_t n = gl_nelem(a);
