@@ -185,6 +185,22 @@ B200_API int b200_exchange_error(b200_ctx * ctx, const b200_exchange * ex);     
 B200_API int b200_split_row_range(int64_t nrows, const float * tensor_split, int world, int rank,
                                   int64_t rounding, int64_t * row_low, int64_t * row_high);
 
+// ---- layer distribution over GPUs (host only); reference src/llama-multi-gpu.{h,cpp} -------------------------------------------
+// llama_multi_gpu_strategy (llama-multi-gpu.h:84-91); values other than the three below plan like MEMORY_BALANCED (llama-multi-gpu.cpp:170-185)
+enum b200_layer_strategy { B200_LAYERS_ROUND_ROBIN = 0, B200_LAYERS_MEMORY_BALANCED = 1, B200_LAYERS_TENSOR_PARALLEL = 4 };
+// llama_layer_assignment (llama-multi-gpu.h:75-81); split_gpu_ids[0 .. n_split) are the GPUs a split layer spans, the rest -1
+typedef struct b200_layer_assignment {
+    int32_t  layer_id, gpu_id;
+    uint64_t memory_required;
+    int32_t  is_split, n_split;
+    int32_t  split_gpu_ids[B200_MAX_PEERS];
+} b200_layer_assignment;
+// llama_multi_gpu_manager::distribute_layers (llama-multi-gpu.cpp:156-332): plans n_layers layers of layer_sizes[i] bytes (0 beyond n_sizes)
+// over n_gpus GPUs with gpu_free_memory[g] bytes free.  Writes out[0 .. n_layers) and, if not NULL, the bytes charged to each GPU into
+// gpu_allocated[n_gpus].  Returns the number of assignments (0 without GPUs) or a negative b200_status.
+B200_API int b200_distribute_layers(int strategy, int tensor_parallel_size, int n_layers, const uint64_t * layer_sizes, int n_sizes,
+                                    int n_gpus, const uint64_t * gpu_free_memory, b200_layer_assignment * out, uint64_t * gpu_allocated);
+
 // ---- ggml plugin entry points ----------------------------------------------------------------
 struct ggml_backend_reg;
 B200_API struct ggml_backend_reg * ggml_backend_init(void);       // ggml-backend-reg.cpp:255-272

@@ -68,6 +68,7 @@ def lib():
         "b200_debug_trace": (i, [vp, vp, i]),
         "b200_graph_begin": (i, [vp]), "b200_graph_end": (vp, [vp]), "b200_graph_launch": (i, [vp, vp]), "b200_graph_destroy": (i, [vp]),
         "b200_split_row_range": (i, [i64, vp, i, i, i64, C.POINTER(i64), C.POINTER(i64)]),
+        "b200_distribute_layers": (i, [i, i, i, vp, i, i, vp, vp, vp]),
         "b200_peer_handle": (i, [vp, vp, vp]), "b200_peer_open": (i, [vp, vp, C.POINTER(vp)]), "b200_peer_close": (i, [vp, vp]),
         "b200_mul_mat_rowsplit": (i, [vp, tp, tp, tp, i64, C.POINTER(Exchange)]),
         "b200_mul_mat_rowsplit_multi": (i, [vp, C.POINTER(tp), i, tp, C.POINTER(tp), C.POINTER(i64), C.POINTER(Exchange)]),
@@ -395,3 +396,19 @@ def split_row_range(nrows, world, rank, rounding, tensor_split=None):
     _check(lib().b200_split_row_range(nrows, ts.ctypes.data if ts is not None else None, world, rank, rounding,
                                       C.byref(lo), C.byref(hi)), "split_row_range")
     return lo.value, hi.value
+
+
+class _LayerAssignment(C.Structure):
+    _fields_ = [("layer_id", C.c_int32), ("gpu_id", C.c_int32), ("memory_required", C.c_uint64), ("is_split", C.c_int32), ("n_split", C.c_int32),
+                ("split_gpu_ids", C.c_int32 * 8)]
+
+
+def distribute_layers(strategy, tp_size, n_layers, layer_sizes, gpu_free):
+    """host-only layer plan (b200_distribute_layers; the fork's llama_multi_gpu_manager::distribute_layers): returns
+    ([(layer_id, gpu_id, memory_required, is_split, [split gpu ids])], bytes charged per GPU)"""
+    ls = (C.c_uint64 * max(1, len(layer_sizes)))(*layer_sizes); gf = (C.c_uint64 * max(1, len(gpu_free)))(*gpu_free)
+    out = (_LayerAssignment * max(1, n_layers))(); alloc = (C.c_uint64 * max(1, len(gpu_free)))()
+    n = lib().b200_distribute_layers(strategy, tp_size, n_layers, ls, len(layer_sizes), len(gpu_free), gf, out, alloc)
+    if n < 0:
+        _check(n, "distribute_layers")
+    return [(a.layer_id, a.gpu_id, a.memory_required, a.is_split, list(a.split_gpu_ids[:a.n_split])) for a in out[:n]], list(alloc[:len(gpu_free)])
