@@ -200,6 +200,9 @@ typedef struct b200_layer_assignment {
 // gpu_allocated[n_gpus].  Returns the number of assignments (0 without GPUs) or a negative b200_status.
 B200_API int b200_distribute_layers(int strategy, int tensor_parallel_size, int n_layers, const uint64_t * layer_sizes, int n_sizes,
                                     int n_gpus, const uint64_t * gpu_free_memory, b200_layer_assignment * out, uint64_t * gpu_allocated);
+// the plan in the form llama.cpp consumes: llama_model_params::tensor_split[n_gpus] (include/llama.h; `-ts`), the share of layers
+// (-sm layer) or of every split matrix's rows (-sm row; what b200_split_row_range takes) per GPU
+B200_API int b200_plan_tensor_split(const b200_layer_assignment * plan, int n, int n_gpus, float * tensor_split);
 
 // ---- ggml plugin entry points ----------------------------------------------------------------
 struct ggml_backend_reg;

@@ -17,7 +17,7 @@ def copy(src, name):
 
 
 for src, name in (("bench.json", "bench.json"), ("bench_reference.json", "bench_reference.json"), ("pytest_gpu.log", "pytest_gpu.log"), ("smoke.log", "smoke.log"),
-                  ("gpu.txt", "gpu.txt"), ("ncu_launches.csv", "ncu_launches.csv")):
+                  ("gpu.txt", "gpu.txt"), ("cpu.txt", "cpu.txt"), ("ncu_launches.csv", "ncu_launches.csv")):
     copy(src, name)
 for f in sorted(os.listdir(OUT)):
     if f.startswith("llama_bench_") and f.endswith(".txt"):

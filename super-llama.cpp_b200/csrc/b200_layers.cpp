@@ -51,3 +51,25 @@ extern "C" B200_API int b200_distribute_layers(int strategy, int tensor_parallel
     plan_memory_balanced(n_layers, layer_sizes, n_sizes, n_gpus, gpu_free_memory, out, allocated);
     return n_layers;
 }
+
+// The plan as llama.cpp takes it: llama_model_params::tensor_split, "proportion of the model (layers or rows) to offload to each GPU"
+// (include/llama.h) -- for -sm layer the share of layers per GPU, for a tensor-parallel plan the share of every split matrix's rows
+// (what b200_split_row_range / ggml_backend_split_buffer_type consume).  tensor_split[n_gpus], sums to 1 (all 0 for an empty plan).
+extern "C" B200_API int b200_plan_tensor_split(const b200_layer_assignment * plan, int n, int n_gpus, float * tensor_split) {
+    if (n < 0 || n_gpus <= 0 || !tensor_split || (n > 0 && !plan)) { b200_set_error("plan_tensor_split: bad arguments"); return B200_ERR_INVALID; }
+    std::vector<double> share(n_gpus, 0.0);
+    for (int i = 0; i < n; ++i) {
+        if (plan[i].is_split && plan[i].n_split > 0) {
+            for (int k = 0; k < plan[i].n_split && k < B200_MAX_PEERS; ++k) {
+                const int g = plan[i].split_gpu_ids[k];
+                if (g < 0 || g >= n_gpus) { b200_set_error("plan_tensor_split: GPU %d outside 0..%d", g, n_gpus - 1); return B200_ERR_INVALID; }
+                share[g] += 1.0 / plan[i].n_split;
+            }
+        } else {
+            if (plan[i].gpu_id < 0 || plan[i].gpu_id >= n_gpus) { b200_set_error("plan_tensor_split: GPU %d outside 0..%d", plan[i].gpu_id, n_gpus - 1); return B200_ERR_INVALID; }
+            share[plan[i].gpu_id] += 1.0;
+        }
+    }
+    for (int g = 0; g < n_gpus; ++g) tensor_split[g] = n > 0 ? (float) (share[g] / n) : 0.0f;
+    return B200_OK;
+}

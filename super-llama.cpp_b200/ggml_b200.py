@@ -69,6 +69,7 @@ def lib():
         "b200_graph_begin": (i, [vp]), "b200_graph_end": (vp, [vp]), "b200_graph_launch": (i, [vp, vp]), "b200_graph_destroy": (i, [vp]),
         "b200_split_row_range": (i, [i64, vp, i, i, i64, C.POINTER(i64), C.POINTER(i64)]),
         "b200_distribute_layers": (i, [i, i, i, vp, i, i, vp, vp, vp]),
+        "b200_plan_tensor_split": (i, [vp, i, i, vp]),
         "b200_peer_handle": (i, [vp, vp, vp]), "b200_peer_open": (i, [vp, vp, C.POINTER(vp)]), "b200_peer_close": (i, [vp, vp]),
         "b200_mul_mat_rowsplit": (i, [vp, tp, tp, tp, i64, C.POINTER(Exchange)]),
         "b200_mul_mat_rowsplit_multi": (i, [vp, C.POINTER(tp), i, tp, C.POINTER(tp), C.POINTER(i64), C.POINTER(Exchange)]),
@@ -412,3 +413,15 @@ def distribute_layers(strategy, tp_size, n_layers, layer_sizes, gpu_free):
     if n < 0:
         _check(n, "distribute_layers")
     return [(a.layer_id, a.gpu_id, a.memory_required, a.is_split, list(a.split_gpu_ids[:a.n_split])) for a in out[:n]], list(alloc[:len(gpu_free)])
+
+
+def plan_tensor_split(plan, n_gpus):
+    """llama_model_params::tensor_split for a plan returned by distribute_layers (b200_plan_tensor_split)"""
+    arr = (_LayerAssignment * max(1, len(plan)))()
+    for a, (lid, gpu, mem, split, ids) in zip(arr, plan):
+        a.layer_id, a.gpu_id, a.memory_required, a.is_split, a.n_split = lid, gpu, mem, split, len(ids)
+        for k in range(8):
+            a.split_gpu_ids[k] = ids[k] if k < len(ids) else -1
+    ts = (C.c_float * n_gpus)()
+    _check(lib().b200_plan_tensor_split(arr, len(plan), n_gpus, ts), "plan_tensor_split")
+    return list(ts)

@@ -58,3 +58,26 @@ def test_c_abi_rejects_bad_arguments():
     import ggml_b200 as B
     assert B.lib().b200_distribute_layers(1, 1, 4, None, 4, 2, None, None, None) < 0
     assert B.lib().b200_distribute_layers(1, 1, -1, None, 0, 0, None, None, None) < 0
+
+
+def test_plan_to_tensor_split_feeds_the_row_split():
+    """a plan becomes llama.cpp's tensor_split; for a tensor-parallel plan that is the even row split b200_split_row_range applies"""
+    import ggml_b200 as B
+    import ctypes as C
+    plan, _ = B.distribute_layers(4, 4, 80, [480 << 20] * 80, [80 << 30] * 8)           # TENSOR_PARALLEL over the first 4 of 8 GPUs
+    ts = B.plan_tensor_split(plan, 8)
+    assert ts == [0.25, 0.25, 0.25, 0.25, 0.0, 0.0, 0.0, 0.0]
+    starts = [sum(ts[:g]) for g in range(8)]                    # the cumulative form ggml_backend_split_buffer_type normalises proportions to (ggml-cuda.cu:850-870)
+    arr = (C.c_float * 8)(*starts)
+    lo, hi = C.c_int64(), C.c_int64()
+    covered = []
+    for r in range(8):
+        assert B.lib().b200_split_row_range(8192, arr, 8, r, 64, C.byref(lo), C.byref(hi)) == 0
+        covered.append((lo.value, hi.value))
+    assert covered[:4] == [(0, 2048), (2048, 4096), (4096, 6144), (6144, 8192)] and all(a == b for a, b in covered[4:])
+    plan, _ = B.distribute_layers(1, 1, 32, [140 << 20] * 32, [60 << 30, 20 << 30])       # memory-balanced, unequal GPUs
+    ts = B.plan_tensor_split(plan, 2)
+    assert abs(sum(ts) - 1.0) < 1e-6 and ts[0] > ts[1] > 0
+    plan, _ = B.distribute_layers(0, 1, 10, [], [1, 1, 1])                                # round-robin: 4 / 3 / 3 layers
+    assert [round(t * 10) for t in B.plan_tensor_split(plan, 3)] == [4, 3, 3]
+    assert B.plan_tensor_split([], 2) == [0.0, 0.0]
