@@ -75,7 +75,7 @@ def test_plan_to_tensor_split_feeds_the_row_split():
         assert B.lib().b200_split_row_range(8192, arr, 8, r, 64, C.byref(lo), C.byref(hi)) == 0
         covered.append((lo.value, hi.value))
     assert covered[:4] == [(0, 2048), (2048, 4096), (4096, 6144), (6144, 8192)] and all(a == b for a, b in covered[4:])
-    plan, _ = B.distribute_layers(1, 1, 32, [140 << 20] * 32, [60 << 30, 20 << 30])       # memory-balanced, unequal GPUs
+    plan, _ = B.distribute_layers(1, 1, 32, [140 << 20] * 32, [3 << 30, 2 << 30])         # memory-balanced, unequal GPUs: the larger one fills first, then they alternate
     ts = B.plan_tensor_split(plan, 2)
     assert abs(sum(ts) - 1.0) < 1e-6 and ts[0] > ts[1] > 0
     plan, _ = B.distribute_layers(0, 1, 10, [], [1, 1, 1])                                # round-robin: 4 / 3 / 3 layers
