@@ -1,5 +1,5 @@
 // b200_glue.cu -- the cheap ops between the hot-path nodes of a llama graph: RMS_NORM, ADD / MUL / SUB / DIV with
-// broadcast, ROPE (normal and neox), SET_ROWS (the KV-cache write), CPY / CONT / DUP, GLU (SwiGLU), GET_ROWS (f32 rows) and SCALE.
+// broadcast, ROPE (normal and neox), SET_ROWS (the KV-cache write), CPY / CONT / DUP, GLU (SwiGLU), GET_ROWS (f32 rows), SCALE, SOFT_MAX, SILU.
 // They exist so that ggml_backend_sched keeps a whole decode graph on the device instead of bouncing every second node through the
 // CPU backend.  Plain bandwidth-trivial kernels over ggml's strided views; semantics follow the reference's CPU operators
 // (ggml/src/ggml-cpu/ops.cpp: rms_norm 3560-3640, rope 5524-5790, set_rows, glu; binary-ops.cpp; ggml.c:4255-4269 for the YaRN
@@ -345,6 +345,55 @@ __global__ void __launch_bounds__(128) k_rope_kv(const gl_rope_kv a) {
     }
 }
 
+// ---- SOFT_MAX (ggml_soft_max_ext; ggml-cpu/ops.cpp:5160-5270): dst = softmax(x * scale + slope(head) * mask) over ne0, mask f32 / f16
+// broadcast over heads and batch, ALiBi slopes when max_bias > 0, optional per-head sinks.  One CTA per row (what -fa 0 graphs need) -----
+static __device__ __forceinline__ float block_max(float v, float * red) {
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    const int nw = (blockDim.x + 31) >> 5;
+    v = (int) threadIdx.x < nw ? red[threadIdx.x] : -INFINITY;
+    if (threadIdx.x < 32) { for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o)); if (threadIdx.x == 0) red[0] = v; }
+    __syncthreads();
+    const float r = red[0];
+    __syncthreads();
+    return r;
+}
+template <bool MASK_F16>
+__global__ void __launch_bounds__(256) k_soft_max(const gl_view x, const gl_view m, const gl_view d, const float * sinks, float scale, float max_bias, float m0, float m1, unsigned n_head_log2, int has_mask) {
+    GL_PDL();
+    int64_t i1, i2, i3; gl_unrow(blockIdx.x, x, i1, i2, i3);
+    const float * xr = (const float *) (x.p + i1 * x.nb[1] + i2 * x.nb[2] + i3 * x.nb[3]);
+    float *       dr = (float *) (d.p + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]);
+    const char *  mr = has_mask ? m.p + i1 * m.nb[1] + (i2 % m.ne[2]) * m.nb[2] + (i3 % m.ne[3]) * m.nb[3] : nullptr;
+    const unsigned h = (unsigned) i2;
+    const float slope = max_bias > 0.0f ? (h < n_head_log2 ? powf(m0, (float) (h + 1)) : powf(m1, (float) (2 * (h - n_head_log2) + 1))) : 1.0f;
+    auto val = [&](int64_t i) {
+        float v = xr[i] * scale;
+        if (mr) v += slope * (MASK_F16 ? __half2float(((const __half *) mr)[i]) : ((const float *) mr)[i]);
+        return v;
+    };
+    __shared__ float red[32];
+    const int64_t n0 = x.ne[0];
+    float mx = -INFINITY;
+    for (int64_t i = threadIdx.x; i < n0; i += blockDim.x) mx = fmaxf(mx, val(i));
+    mx = block_max(mx, red);
+    if (sinks) mx = fmaxf(mx, sinks[i2]);
+    float sum = 0.0f;
+    for (int64_t i = threadIdx.x; i < n0; i += blockDim.x) { const float v = val(i); sum += v == -INFINITY ? 0.0f : expf(v - mx); }
+    sum = block_sum(sum, red);
+    if (sinks) sum += expf(sinks[i2] - mx);
+    const float inv = 1.0f / sum;
+    for (int64_t i = threadIdx.x; i < n0; i += blockDim.x) { const float v = val(i); dr[i] = v == -INFINITY ? 0.0f : expf(v - mx) * inv; }
+}
+
+// ---- UNARY: SILU (x / (1 + exp(-x)), ggml-cpu/vec.h), contiguous f32 ----------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_silu(const float * x, float * y, int64_t n) {
+    GL_PDL();
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { const float v = x[i]; y[i] = v / (1.0f + expf(-v)); }
+}
+
 template <typename... KArgs, typename... Args>
 static cudaError_t gl_launch(b200_ctx * ctx, void (*kernel)(KArgs...), dim3 grid, unsigned block, Args... args) {
     cudaLaunchConfig_t cfg = {};
@@ -374,6 +423,16 @@ bool b200_glue_supports(const struct ggml_tensor * op) {
                    gl_contig_rows(op, 4) && gl_same_shape(a, op) && gl_can_repeat(b, a) && gl_grid_ok(op);
         case GGML_OP_SCALE:
             return a->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && gl_contiguous(a, 4) && gl_contiguous(op, 4);
+        case GGML_OP_UNARY:
+            return op->op_params[0] == GGML_UNARY_OP_SILU && a->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && gl_contiguous(a, 4) && gl_contiguous(op, 4);
+        case GGML_OP_SOFT_MAX: {
+            const ggml_tensor * sk = op->src[2];
+            if (a->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32 || !gl_contig_rows(a, 4) || !gl_contiguous(op, 4) || !gl_same_shape(a, op)) return false;
+            if (b && ((b->type != GGML_TYPE_F32 && b->type != GGML_TYPE_F16) || b->nb[0] != gl_esize(b->type) || b->ne[0] != a->ne[0] || b->ne[1] < a->ne[1] ||
+                      b->ne[2] <= 0 || b->ne[3] <= 0 || a->ne[2] % b->ne[2] != 0 || a->ne[3] % b->ne[3] != 0)) return false;
+            if (sk && (sk->type != GGML_TYPE_F32 || sk->ne[0] != a->ne[2] || sk->nb[0] != 4)) return false;
+            return gl_nrows(op) <= 0x7fffffff;
+        }
         case GGML_OP_ROPE: {
             const int mode = op->op_params[2];
             if (mode != 0 && mode != 2) return false;                       // normal and neox; mrope / vision stay on the CPU backend
@@ -533,6 +592,21 @@ int b200_glue_compute(b200_ctx * ctx, struct ggml_tensor * op) {
             float s, bias; memcpy(&s, op->op_params, 4); memcpy(&bias, op->op_params + 1, 4);
             const int64_t n = gl_nelem(op);
             GL_LAUNCH(gl_launch(ctx, k_scale, dim3((unsigned) ((n + 255) / 256)), 256, (const float *) a->data, (float *) op->data, n, s, bias));
+            return B200_OK;
+        }
+        case GGML_OP_UNARY: {
+            const int64_t n = gl_nelem(op);
+            GL_LAUNCH(gl_launch(ctx, k_silu, dim3((unsigned) ((n + 255) / 256)), 256, (const float *) a->data, (float *) op->data, n));
+            return B200_OK;
+        }
+        case GGML_OP_SOFT_MAX: {
+            float scale, max_bias; memcpy(&scale, op->op_params, 4); memcpy(&max_bias, op->op_params + 1, 4);
+            const unsigned n_head = (unsigned) a->ne[2], n_head_log2 = 1u << (unsigned) floorf(log2f((float) n_head));
+            const float m0 = powf(2.0f, -max_bias / n_head_log2), m1 = powf(2.0f, -(max_bias / 2.0f) / n_head_log2);
+            const float * sinks = op->src[2] ? (const float *) op->src[2]->data : nullptr;
+            const gl_view mv = b ? gl_of(b) : gl_of(a);
+            if (b && b->type == GGML_TYPE_F16) GL_LAUNCH(gl_launch(ctx, k_soft_max<true>, dim3(rows), 256, gl_of(a), mv, gl_of(op), sinks, scale, max_bias, m0, m1, n_head_log2, 1));
+            else                               GL_LAUNCH(gl_launch(ctx, k_soft_max<false>, dim3(rows), 256, gl_of(a), mv, gl_of(op), sinks, scale, max_bias, m0, m1, n_head_log2, b ? 1 : 0));
             return B200_OK;
         }
         case GGML_OP_ROPE: {
