@@ -24,7 +24,7 @@ int main(int argc, char ** argv) {
     llama_context_params cp = llama_context_default_params();
     cp.n_ctx = 2048; cp.n_batch = 1024; cp.n_ubatch = 512;   // prompts up to 1024 tokens, evaluated as ubatches of 512
     cp.n_threads = 8; cp.n_threads_batch = 8;
-    cp.flash_attn_type = LLAMA_FLASH_ATTN_TYPE_ENABLED;
+    cp.flash_attn_type = getenv("LOGITS_PROBE_NO_FA") ? LLAMA_FLASH_ATTN_TYPE_DISABLED : LLAMA_FLASH_ATTN_TYPE_ENABLED;   // -fa 0: attention as MUL_MAT + SOFT_MAX + MUL_MAT, V cache transposed
     cp.no_perf = true;
     llama_context * ctx = llama_init_from_model(model, cp);
     if (!ctx) { fprintf(stderr, "logits_probe: cannot create a context\n"); return 1; }

@@ -46,6 +46,16 @@ def nmse(ref, got):
 @pytest.mark.parametrize("model,quant,layers,n_prompt,n_step", [("8b", "q4_k_m", 4, 250, 1), ("tinyllama", "q4_0", 6, 250, 1), ("tinyllama", "q8_0", 4, 250, 1),
                                                               ("8b", "q4_k_m", 2, 760, 1), ("8b", "q4_k_m", 2, 230, 4)])
 def test_llama_logits_plugin_vs_ggml_cpu(model, quant, layers, n_prompt, n_step):
+    _run_case(model, quant, layers, n_prompt, n_step, {})
+
+
+def test_llama_logits_without_flash_attention():
+    """-fa 0: attention built as MUL_MAT(K) + SOFT_MAX + MUL_MAT(V) over a transposed V cache (src/llama-graph.cpp:1602-1640); with SOFT_MAX
+    among the glue ops the whole graph stays on the device here too"""
+    _run_case("tinyllama", "q4_0", 4, 250, 1, {"LOGITS_PROBE_NO_FA": "1"})
+
+
+def _run_case(model, quant, layers, n_prompt, n_step, probe_env):
     if not os.path.exists(PROBE):
         pytest.skip("oracle/_ref/avx2/logits_probe not built (make -C oracle llama; needs /root/reference at build time)")
     os.makedirs(OUT, exist_ok=True)
@@ -53,9 +63,9 @@ def test_llama_logits_plugin_vs_ggml_cpu(model, quant, layers, n_prompt, n_step)
     subprocess.check_call([os.sys.executable, os.path.join(ROOT, "scripts", "make_gguf.py"), "--model", model, "--quant", quant, "--layers", str(layers), "-o", gguf],
                           stdout=subprocess.DEVNULL)
     try:
-        cpu, _ = run_probe(gguf, "cpu", 0, n_prompt=n_prompt, n_step=n_step)
-        dev, log = run_probe(gguf, "b200", 99, {"GGML_B200_GRAPH_STATS": "1"}, n_prompt=n_prompt, n_step=n_step)
-        plain, _ = run_probe(gguf, "b200_plain", 99, {"GGML_B200_NO_FUSE": "1", "GGML_B200_GRAPHS": "0"}, n_prompt=n_prompt, n_step=n_step)
+        cpu, _ = run_probe(gguf, "cpu", 0, dict(probe_env), n_prompt=n_prompt, n_step=n_step)
+        dev, log = run_probe(gguf, "b200", 99, dict(probe_env, GGML_B200_GRAPH_STATS="1"), n_prompt=n_prompt, n_step=n_step)
+        plain, _ = run_probe(gguf, "b200_plain", 99, dict(probe_env, GGML_B200_NO_FUSE="1", GGML_B200_GRAPHS="0"), n_prompt=n_prompt, n_step=n_step)
     finally:
         os.remove(gguf)
     assert np.isfinite(cpu).all() and np.isfinite(dev).all()
