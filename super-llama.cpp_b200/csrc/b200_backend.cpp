@@ -721,6 +721,8 @@ ggml_backend_buffer_type_t b200_split_buffer_type(int main_device, const float *
 static void * reg_proc_address(ggml_backend_reg_t, const char * name) {
     if (!strcmp(name, "ggml_backend_get_features"))      return (void *) reg_get_features;
     if (!strcmp(name, "ggml_backend_split_buffer_type")) return (void *) b200_split_buffer_type;
+    if (!strcmp(name, "ggml_backend_b200_graph_identity"))      // host-only: the key of the CUDA-graph cache (tests/reorder_probe.cpp)
+        return (void *) +[](const ggml_cgraph * g, uint64_t * h1, uint64_t * h2) -> int { return graph_identity(g, *h1, *h2) ? 1 : 0; };
     if (!strcmp(name, "ggml_backend_b200_graph_optimize")) return (void *) +[](ggml_cgraph * g) { be_graph_optimize(nullptr, g); };   // host-only: tests/reorder_probe.cpp
     if (!strcmp(name, "ggml_backend_b200_tensor_is_repacked")) return (void *) +[](const ggml_tensor * t) -> int { return tensor_is_repacked(t) ? 1 : 0; };   // tests/upload_probe.cpp
     return nullptr;    // "ggml_backend_set_n_threads", "ggml_backend_dev_get_extra_bufts": not applicable

@@ -10,6 +10,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <vector>
+#include <utility>
 
 static std::vector<ggml_tensor *> all;
 static ggml_tensor * T(const char * name, int type, int op, ggml_tensor * s0 = nullptr, ggml_tensor * s1 = nullptr, ggml_backend_buffer * buf = nullptr) {
@@ -71,5 +72,34 @@ int main(int argc, char ** argv) {
         if (!before) { printf("BROKEN: %s runs before its source %s\n", g.nodes[i]->name, sr->name); return 1; }
     }
     printf("dependencies: OK\n");
+
+    // ---- the key of the plugin's CUDA-graph cache: same graph -> same key; any change of a pointer, shape, stride, op or op_param -> new key;
+    // prefill-sized graphs are not eligible for recording
+    auto identity = (int (*)(const ggml_cgraph *, uint64_t *, uint64_t *)) reg->iface.get_proc_address(reg, "ggml_backend_b200_graph_identity");
+    if (!identity) { fprintf(stderr, "no ggml_backend_b200_graph_identity\n"); return 1; }
+    for (ggml_tensor * t : all) t->buffer = nullptr;                 // (fabricated buffers have no buffer type to inspect)
+    static char mem[1 << 16]; size_t off = 0;
+    for (ggml_tensor * t : all) if (!t->view_src) { t->data = mem + off; off += 256; }
+    for (ggml_tensor * t : all) if (t->view_src) t->data = t->view_src->data;
+    uint64_t a1, a2, b1, b2;
+    const int e0 = identity(&g, &a1, &a2), e1 = identity(&g, &b1, &b2);
+    printf("identity: eligible=%d stable=%d\n", e0, e1 == e0 && a1 == b1 && a2 == b2);
+    int changed = 0, tried = 0;
+    auto differs = [&]() { uint64_t c1, c2; identity(&g, &c1, &c2); ++tried; if (c1 != a1 || c2 != a2) ++changed; };
+    ggml_tensor * n5 = nullptr;                                        // a node that launches work (views are keyed by pointer and shape only)
+    for (int i = 0; i < g.n_nodes && !n5; ++i) if (g.nodes[i]->op == GGML_OP_ROPE) n5 = g.nodes[i];
+    { void * d = n5->data; n5->data = (char *) d + 64; differs(); n5->data = d; }                        // a node moved
+    { int64_t v = n5->ne[1]; n5->ne[1] = 2; differs(); n5->ne[1] = v; }                                    // shape
+    { size_t v = n5->nb[1]; n5->nb[1] = 512; differs(); n5->nb[1] = v; }                                   // stride
+    { int32_t v = n5->op_params[3]; n5->op_params[3] = 77; differs(); n5->op_params[3] = v; }              // op parameter
+    { ggml_op v = g.nodes[1]->op; g.nodes[1]->op = GGML_OP_ADD; differs(); g.nodes[1]->op = v; }           // operator
+    { ggml_tensor * src = g.nodes[1]->src[0]; void * d = src->data; src->data = (char *) d + 128; differs(); src->data = d; }   // a source (weight) moved
+    { ggml_tensor * t = g.nodes[1]->src[1]; g.nodes[1]->src[1] = nullptr; differs(); g.nodes[1]->src[1] = t; }               // a source dropped
+    { std::swap(g.nodes[1], g.nodes[2]); differs(); std::swap(g.nodes[1], g.nodes[2]); }                   // node order
+    { --g.n_nodes; differs(); ++g.n_nodes; }                                                               // node count
+    uint64_t z1, z2; identity(&g, &z1, &z2);
+    printf("identity: %d of %d mutations changed the key, restored=%d\n", changed, tried, z1 == a1 && z2 == a2);
+    for (int i = 0; i < g.n_nodes; ++i) if (g.nodes[i]->op == GGML_OP_MUL_MAT) { g.nodes[i]->ne[1] = 512; break; }          // a prefill-sized matmul
+    printf("identity: prefill eligible=%d\n", identity(&g, &z1, &z2));
     return 0;
 }

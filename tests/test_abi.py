@@ -120,6 +120,9 @@ def test_graph_optimize_reorders_weight_matmuls_only(tmp_path):
     for vtype in (12, 14):
         out = subprocess.run([exe, plugin, str(vtype)], stdout=subprocess.PIPE, text=True, timeout=60)
         assert out.returncode == 0 and "dependencies: OK" in out.stdout, out.stdout
+        # the CUDA-graph cache key (graph_identity): deterministic, sensitive to everything a recording bakes in, prefill graphs ineligible
+        assert "identity: eligible=1 stable=1" in out.stdout and "identity: 9 of 9 mutations changed the key, restored=1" in out.stdout, out.stdout
+        assert "identity: prefill eligible=0" in out.stdout
         order = out.stdout.splitlines()[0].split()[1:]
         pos = {n: i for i, n in enumerate(order)}
         for il in (0, 1):
