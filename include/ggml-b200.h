@@ -131,6 +131,16 @@ B200_API int b200_mul_mat_multi(b200_ctx * ctx, const b200_tensor * const * w, i
  * B200_ERR_UNSUPPORTED unless both weights are raw q4_K served by the tensor-core GEMV: use b200_mul_mat_multi + the GLU op then. */
 B200_API int b200_mul_mat_gate_up_swiglu(b200_ctx * ctx, const b200_tensor * wg, const b200_tensor * wu, const b200_tensor * x,
                                          b200_tensor * gate, b200_tensor * up, b200_tensor * glu);
+/* b200_mul_mat for callers that may not allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  NO
+ * counterpart in the reference.  Same result as b200_mul_mat's general small-batch path
+ * (q8_1 image + one-warp-per-row GEMV), but the q8_1 image of the activations lives in a static device array of
+ * B200_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until exit; the call performs no cudaMalloc / cudaFree / event
+ * creation.  Limits: quantized w (q4_0 / q8_0 / q4_K / q5_K / q6_K), x->ne[1] <= 8 columns, and K * ncol * 9 / 8 bytes
+ * (ncol = ne[1] * ne[2] * ne[3] of x) must fit the array, else B200_ERR_INVALID with a message naming both sizes.  All calls on a device
+ * share the array: calls that overlap on the GPU (two contexts on one device) race; calls on one context are stream-ordered. */
+#define B200_NOALLOC_SCRATCH_BYTES (1u << 20)
+B200_API int    b200_mul_mat_noalloc(b200_ctx * ctx, const b200_tensor * w, const b200_tensor * x, b200_tensor * dst);
+B200_API size_t b200_noalloc_scratch_bytes(void);
 // as[K, M, n_expert], b[K, n_used|1, n_tokens] f32, ids[n_used, n_tokens] i32 -> dst[M, n_used, n_tokens]
 // (ggml/src/ggml.c:3205-3241).
 B200_API int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b200_tensor * b,

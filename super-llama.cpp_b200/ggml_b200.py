@@ -53,11 +53,12 @@ def lib():
         "b200_device_count": (i, []), "b200_last_error": (C.c_char_p, []),
         "b200_ctx_create": (vp, [i]), "b200_ctx_destroy": (None, [vp]), "b200_ctx_device": (i, [vp]),
         "b200_ctx_stream": (vp, [vp]), "b200_ctx_synchronize": (i, [vp]), "b200_ctx_launch_count": (C.c_uint64, [vp]),
-        "b200_ctx_invalidate": (i, [vp]), "b200_ctx_note_write": (i, [vp, vp, C.c_size_t]),
+        "b200_ctx_invalidate": (i, [vp]), "b200_ctx_scratch_generation": (C.c_uint64, [vp]), "b200_ctx_note_write": (i, [vp, vp, C.c_size_t]),
         "b200_malloc": (vp, [vp, sz]), "b200_free": (i, [vp, vp]), "b200_host_alloc": (vp, [sz]), "b200_host_free": (i, [vp]),
         "b200_memcpy_h2d": (i, [vp, vp, vp, sz]), "b200_memcpy_d2h": (i, [vp, vp, vp, sz]), "b200_memset": (i, [vp, vp, i, sz]),
         "b200_quantize_q8_1": (i, [vp, vp, sz, vp, i64, i64, i]),
-        "b200_mul_mat": (i, [vp, tp, tp, tp]), "b200_mul_mat_multi": (i, [vp, C.POINTER(tp), i, tp, C.POINTER(tp)]),
+        "b200_mul_mat": (i, [vp, tp, tp, tp]), "b200_mul_mat_noalloc": (i, [vp, tp, tp, tp]), "b200_noalloc_scratch_bytes": (sz, []),
+        "b200_mul_mat_multi": (i, [vp, C.POINTER(tp), i, tp, C.POINTER(tp)]),
         "b200_mul_mat_gate_up_swiglu": (i, [vp, tp, tp, tp, tp, tp, tp]),
         "b200_repack_supported": (i, [i, i64]), "b200_repack": (i, [vp, i, vp, i64, i64, sz]), "b200_unrepack": (i, [vp, i, vp, i64, i64, sz]), "b200_mul_mat_id": (i, [vp, tp, tp, tp, tp]),
         "b200_flash_attn_ext": (i, [vp, tp, tp, tp, tp, tp, tp, f, f, f]),
@@ -279,6 +280,11 @@ class Context:
     def mul_mat(self, w, x, dst):
         cw, cx, cd = w.c(), x.c(), dst.c()
         _check(lib().b200_mul_mat(self.h, C.byref(cw), C.byref(cx), C.byref(cd)), "mul_mat")
+
+    def mul_mat_noalloc(self, w, x, dst):
+        """b200_mul_mat_noalloc: small-batch quantized MUL_MAT whose q8_1 scratch is a static device array (no allocation of any kind)"""
+        cw, cx, cd = w.c(), x.c(), dst.c()
+        _check(lib().b200_mul_mat_noalloc(self.h, C.byref(cw), C.byref(cx), C.byref(cd)), "mul_mat_noalloc")
 
     def mul_mat_multi(self, ws, x, dsts):
         """n MUL_MATs sharing x (wq/wk/wv, gate/up): one launch when the streaming GEMV can take them"""
