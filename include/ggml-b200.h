@@ -141,6 +141,30 @@ B200_API int b200_mul_mat_gate_up_swiglu(b200_ctx * ctx, const b200_tensor * wg,
 #define B200_NOALLOC_SCRATCH_BYTES (1u << 20)
 B200_API int    b200_mul_mat_noalloc(b200_ctx * ctx, const b200_tensor * w, const b200_tensor * x, b200_tensor * dst);
 B200_API size_t b200_noalloc_scratch_bytes(void);
+/* The persistent decode chain: up to B200_CHAIN_MAX_PHASES dependent MUL_MAT groups of ONE token and the glue between them as ONE kernel
+ * launch (b200_chain.cu).  Replaces the node sequence of a llama layer between two attention operators -- wo, ADD, RMS_NORM,
+ * MUL, ffn_gate / ffn_up, GLU(SWIGLU), ffn_down, ADD, RMS_NORM, MUL, wq / wk / wv (src/models/llama.cpp:40-130) -- which the reference
+ * computes node by node (ggml_compute_forward_mul_mat ggml/src/ggml-cpu/ggml-cpu.c:1226-1418, rms_norm / glu ggml/src/ggml-cpu/ops.cpp:3560-3640).
+ * Phase p:   x = in0                                    (B200_CHAIN_X_PLAIN)
+ *            x = rms_norm(in0 + in1, eps) * normw       (B200_CHAIN_X_ADD_NORM_MUL; the three nodes' values also go to out_add / out_norm / out_mul if not NULL)
+ *            x = rms_norm(in0, eps) * normw             (B200_CHAIN_X_NORM_MUL)
+ *            dst[i] = w[i] x, i < n_w <= 3              (B200_CHAIN_Y_PLAIN)
+ *            + glu = swiglu(dst[0], dst[1]), n_w == 2   (B200_CHAIN_Y_SWIGLU)
+ * A phase may read what earlier phases of the same call wrote.  All activations are contiguous 16-byte aligned f32 columns; weights are
+ * raw q4_K or repacked q6_K with K % 2048 == 0 and M % 4 == 0.  B200_ERR_UNSUPPORTED otherwise: run the nodes one by one then. */
+#define B200_CHAIN_MAX_PHASES 6
+enum b200_chain_prologue { B200_CHAIN_X_PLAIN = 0, B200_CHAIN_X_ADD_NORM_MUL = 1, B200_CHAIN_X_NORM_MUL = 2 };
+enum b200_chain_epilogue { B200_CHAIN_Y_PLAIN = 0, B200_CHAIN_Y_SWIGLU = 1 };
+typedef struct b200_chain_phase {
+    int32_t prologue, epilogue, n_w;
+    float   eps;
+    const b200_tensor * w[3];
+    b200_tensor *       dst[3];
+    const b200_tensor * in0, * in1, * normw;
+    b200_tensor *       out_add, * out_norm, * out_mul, * glu;
+} b200_chain_phase;
+B200_API int b200_decode_chain(b200_ctx * ctx, const b200_chain_phase * phases, int n_phases);
+B200_API int b200_decode_chain_supported(b200_ctx * ctx, const b200_chain_phase * phases, int n_phases);   // 1 / 0
 // as[K, M, n_expert], b[K, n_used|1, n_tokens] f32, ids[n_used, n_tokens] i32 -> dst[M, n_used, n_tokens]
 // (ggml/src/ggml.c:3205-3241).
 B200_API int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b200_tensor * b,

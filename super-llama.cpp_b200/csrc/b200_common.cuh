@@ -195,15 +195,72 @@ static __device__ __forceinline__ void q8_1_block(float v, int & q, float & d, i
     isum = (int) usum;
 }
 
+// The arithmetic core of the CTA-wide quantizers below: this lane holds 16 consecutive values f (one half of a 32-value block), lane ^ 1 the other half.  Returns the
+// 16 quants (w), the block scale d = amax / 127 (fp32, before its fp16 round trip) and the block's int32 quant sum as the x86 code forms it.
+static __device__ __forceinline__ void b200_q8_1_half16(const float (&f)[16], int lane, int4 & w, float & d, unsigned & usum) {
+    // amax over the |bit patterns| as integers: same order as the floats, and a NaN input shows up as amax > inf
+    unsigned ab[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) ab[i] = max(__float_as_uint(f[2 * i]) & 0x7fffffffu, __float_as_uint(f[2 * i + 1]) & 0x7fffffffu);
+    unsigned abits = max(max(max(ab[0], ab[1]), max(ab[2], ab[3])), max(max(ab[4], ab[5]), max(ab[6], ab[7])));
+    abits = max(abits, __shfl_xor_sync(0xffffffffu, abits, 1));
+    const bool  nan_in = abits > 0x7f800000u;
+    // with a NaN in the block the reference's amax depends on where it sits (q8_1_amax): same fold order, rare path
+    float amax = __uint_as_float(abits);
+    if (__any_sync(0xffffffffu, nan_in)) {
+        float lo[16], hi[16];                                         // x[0..15] (even lane of the pair), x[16..31] (odd lane)
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const float o = __shfl_xor_sync(0xffffffffu, f[i], 1);
+            lo[i] = fabsf((lane & 1) ? o : f[i]); hi[i] = fabsf((lane & 1) ? f[i] : o);
+        }
+        float m[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) m[j] = mx_x86(mx_x86(mx_x86(lo[j], lo[8 + j]), hi[j]), hi[8 + j]);
+        amax = mx_x86(mx_x86(mx_x86(m[4], m[0]), mx_x86(m[6], m[2])), mx_x86(mx_x86(m[5], m[1]), mx_x86(m[7], m[3])));
+    }
+    d = __fdiv_rn(amax, 127.0f);
+    const float id = amax != 0.0f ? __fdiv_rn(127.0f, amax) : 0.0f;
+    int * wp = (int *) &w;
+    // finite inputs and a finite 127/amax: |x * id| <= 127 (1 + 2^-23), so every quant is in [-127, 127]: nothing saturates, the
+    // x86 "integer indefinite" cannot occur and the int32 sum equals the sum of the packed bytes
+    const bool fast = !nan_in && abits < 0x7f800000u && (__float_as_uint(id) & 0x7fffffffu) < 0x7f800000u;
+    if (__all_sync(0xffffffffu, fast)) {
+        int acc = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int q0 = __float2int_rn(__fmul_rn(f[4 * i], id)),     q1 = __float2int_rn(__fmul_rn(f[4 * i + 1], id));
+            const int q2 = __float2int_rn(__fmul_rn(f[4 * i + 2], id)), q3 = __float2int_rn(__fmul_rn(f[4 * i + 3], id));
+            int hi, wd;
+            asm("cvt.pack.sat.s8.s32.b32 %0, %1, %2, %3;" : "=r"(hi) : "r"(q3), "r"(q2), "r"(0));
+            asm("cvt.pack.sat.s8.s32.b32 %0, %1, %2, %3;" : "=r"(wd) : "r"(q1), "r"(q0), "r"(hi));
+            wp[i] = wd;
+            acc = __dp4a(wd, 0x01010101, acc);
+        }
+        usum = (unsigned) acc;
+    } else {
+        int q[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) q[i] = cvt_x86(__fmul_rn(f[i], id));   // cvt.rni rounds half to even itself: same as rintf() first
+        usum = 0u;                                                    // int32 lanes summed before saturation (AVX2 body)
+#pragma unroll
+        for (int i = 0; i < 16; ++i) usum += (unsigned) q[i];
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            wp[i] = (int) (((unsigned) max(-128, min(127, q[4 * i])) & 0xffu)            | (((unsigned) max(-128, min(127, q[4 * i + 1])) & 0xffu) << 8) |
+                           (((unsigned) max(-128, min(127, q[4 * i + 2])) & 0xffu) << 16) | (((unsigned) max(-128, min(127, q[4 * i + 3])) & 0xffu) << 24));
+    }
+    usum += __shfl_xor_sync(0xffffffffu, usum, 1);
+}
+struct b200_no_hook { __device__ __forceinline__ void operator()() const {} };
+// after_loads() runs once, right after the first round of loads has been issued (a place to start bulk traffic BEHIND them)
+// SwiGLU as the GLU node computes it (ggml-cpu/ops.cpp glu, vec.h silu: x / (1 + exp(-x))), shared by k_swiglu and the GEMV epilogue that finishes gate/up
+static __device__ __forceinline__ float b200_swiglu1(float x, float y) { return x / (1.0f + expf(-x)) * y; }
 // CTA-wide q8_1 quantization (x86 variant, bit-exact with q8_1_block<B200_Q8_1_X86>) of one f32 column x[0, K) for the decode GEMV
 // kernels: TWO lanes per 32-value block, 16 values (one 16-byte unit of quants) per lane, so a block costs one shuffle for amax and
 // one for the sum and the 16 conversions of a lane are independent instructions (the 8-lanes-per-block form spent ~2000 cycles per
 // CTA in shuffle / division latency chains, measured with b200_debug_trace).  Rounds are double-buffered: the next round's loads are
 // in flight while this one converts.  store(blk32, hf, quants, d, s): hf = which half of block blk32, d and s after their fp16 round trip.
-struct b200_no_hook { __device__ __forceinline__ void operator()() const {} };
-// after_loads() runs once, right after the first round of loads has been issued (a place to start bulk traffic BEHIND them)
-// SwiGLU as the GLU node computes it (ggml-cpu/ops.cpp glu, vec.h silu: x / (1 + exp(-x))), shared by k_swiglu and the GEMV epilogue that finishes gate/up
-static __device__ __forceinline__ float b200_swiglu1(float x, float y) { return x / (1.0f + expf(-x)) * y; }
 template <class F, class H = b200_no_hook>
 static __device__ __forceinline__ void b200_quantize_column_x86(const float * x, int K, F store, unsigned long long * rec = nullptr, H after_loads = H()) {
     const int nunits = K >> 4, lane = threadIdx.x & 31;
@@ -231,62 +288,9 @@ static __device__ __forceinline__ void b200_quantize_column_x86(const float * x,
             for (int j = 0; j < 4; ++j) nx[j] = nb + lane < nunits ? ldx((nb + lane) * 4 + j) : make_float4(0.f, 0.f, 0.f, 0.f);
         }
         const float f[16] = { v[0].x, v[0].y, v[0].z, v[0].w, v[1].x, v[1].y, v[1].z, v[1].w, v[2].x, v[2].y, v[2].z, v[2].w, v[3].x, v[3].y, v[3].z, v[3].w };
-        // amax over the |bit patterns| as integers: same order as the floats, and a NaN input shows up as amax > inf
-        unsigned ab[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) ab[i] = max(__float_as_uint(f[2 * i]) & 0x7fffffffu, __float_as_uint(f[2 * i + 1]) & 0x7fffffffu);
-        unsigned abits = max(max(max(ab[0], ab[1]), max(ab[2], ab[3])), max(max(ab[4], ab[5]), max(ab[6], ab[7])));
-        abits = max(abits, __shfl_xor_sync(0xffffffffu, abits, 1));
-        if (rec && abits != 0xffffffffu) b200_trace_stamp(rec, 8);         // (measurement only) the column's first loads have landed
-        const bool  nan_in = abits > 0x7f800000u;
-        // with a NaN in the block the reference's amax depends on where it sits (q8_1_amax): same fold order, rare path
-        float amax = __uint_as_float(abits);
-        if (__any_sync(0xffffffffu, nan_in)) {
-            float lo[16], hi[16];                                         // x[0..15] (even lane of the pair), x[16..31] (odd lane)
-#pragma unroll
-            for (int i = 0; i < 16; ++i) {
-                const float o = __shfl_xor_sync(0xffffffffu, f[i], 1);
-                lo[i] = fabsf((lane & 1) ? o : f[i]); hi[i] = fabsf((lane & 1) ? f[i] : o);
-            }
-            float m[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) m[j] = mx_x86(mx_x86(mx_x86(lo[j], lo[8 + j]), hi[j]), hi[8 + j]);
-            amax = mx_x86(mx_x86(mx_x86(m[4], m[0]), mx_x86(m[6], m[2])), mx_x86(mx_x86(m[5], m[1]), mx_x86(m[7], m[3])));
-        }
-        const float d  = __fdiv_rn(amax, 127.0f);
-        const float id = amax != 0.0f ? __fdiv_rn(127.0f, amax) : 0.0f;
-        int4 w;
-        int * wp = (int *) &w;
-        unsigned usum;
-        // finite inputs and a finite 127/amax: |x * id| <= 127 (1 + 2^-23), so every quant is in [-127, 127]: nothing saturates, the
-        // x86 "integer indefinite" cannot occur and the int32 sum equals the sum of the packed bytes
-        const bool fast = !nan_in && abits < 0x7f800000u && (__float_as_uint(id) & 0x7fffffffu) < 0x7f800000u;
-        if (__all_sync(0xffffffffu, fast)) {
-            int acc = 0;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int q0 = __float2int_rn(__fmul_rn(f[4 * i], id)),     q1 = __float2int_rn(__fmul_rn(f[4 * i + 1], id));
-                const int q2 = __float2int_rn(__fmul_rn(f[4 * i + 2], id)), q3 = __float2int_rn(__fmul_rn(f[4 * i + 3], id));
-                int hi, wd;
-                asm("cvt.pack.sat.s8.s32.b32 %0, %1, %2, %3;" : "=r"(hi) : "r"(q3), "r"(q2), "r"(0));
-                asm("cvt.pack.sat.s8.s32.b32 %0, %1, %2, %3;" : "=r"(wd) : "r"(q1), "r"(q0), "r"(hi));
-                wp[i] = wd;
-                acc = __dp4a(wd, 0x01010101, acc);
-            }
-            usum = (unsigned) acc;
-        } else {
-            int q[16];
-#pragma unroll
-            for (int i = 0; i < 16; ++i) q[i] = cvt_x86(__fmul_rn(f[i], id));   // cvt.rni rounds half to even itself: same as rintf() first
-            usum = 0u;                                                    // int32 lanes summed before saturation (AVX2 body)
-#pragma unroll
-            for (int i = 0; i < 16; ++i) usum += (unsigned) q[i];
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-                wp[i] = (int) (((unsigned) max(-128, min(127, q[4 * i])) & 0xffu)            | (((unsigned) max(-128, min(127, q[4 * i + 1])) & 0xffu) << 8) |
-                               (((unsigned) max(-128, min(127, q[4 * i + 2])) & 0xffu) << 16) | (((unsigned) max(-128, min(127, q[4 * i + 3])) & 0xffu) << 24));
-        }
-        usum += __shfl_xor_sync(0xffffffffu, usum, 1);
+        int4 w; float d; unsigned usum;
+        b200_q8_1_half16(f, lane, w, d, usum);
+        if (rec) b200_trace_stamp(rec, 8);                               // (measurement only) the column's first loads have landed
         if (u < nunits) store(u >> 1, u & 1, w, __half2float(__float2half_rn(d)), __half2float(__float2half_rn(__fmul_rn(d, (float) (int) usum))));
         if (nb < nunits) {
 #pragma unroll

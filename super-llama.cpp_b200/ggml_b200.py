@@ -35,6 +35,17 @@ class Exchange(C.Structure):
     _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("base", C.c_void_p * 8), ("ctrl_off", C.c_size_t)]
 
 
+class ChainPhase(C.Structure):
+    """b200_chain_phase: one MUL_MAT group of the persistent decode chain with its prologue / epilogue"""
+    _fields_ = [("prologue", C.c_int32), ("epilogue", C.c_int32), ("n_w", C.c_int32), ("eps", C.c_float),
+                ("w", C.POINTER(_Tensor) * 3), ("dst", C.POINTER(_Tensor) * 3),
+                ("in0", C.POINTER(_Tensor)), ("in1", C.POINTER(_Tensor)), ("normw", C.POINTER(_Tensor)),
+                ("out_add", C.POINTER(_Tensor)), ("out_norm", C.POINTER(_Tensor)), ("out_mul", C.POINTER(_Tensor)), ("glu", C.POINTER(_Tensor))]
+
+
+X_PLAIN, X_ADD_NORM_MUL, X_NORM_MUL = 0, 1, 2
+Y_PLAIN, Y_SWIGLU = 0, 1
+
 _lib = None
 
 
@@ -59,6 +70,7 @@ def lib():
         "b200_quantize_q8_1": (i, [vp, vp, sz, vp, i64, i64, i]),
         "b200_mul_mat": (i, [vp, tp, tp, tp]), "b200_mul_mat_noalloc": (i, [vp, tp, tp, tp]), "b200_noalloc_scratch_bytes": (sz, []),
         "b200_mul_mat_multi": (i, [vp, C.POINTER(tp), i, tp, C.POINTER(tp)]),
+        "b200_decode_chain": (i, [vp, C.POINTER(ChainPhase), i]), "b200_decode_chain_supported": (i, [vp, C.POINTER(ChainPhase), i]),
         "b200_mul_mat_gate_up_swiglu": (i, [vp, tp, tp, tp, tp, tp, tp]),
         "b200_repack_supported": (i, [i, i64]), "b200_repack": (i, [vp, i, vp, i64, i64, sz]), "b200_unrepack": (i, [vp, i, vp, i64, i64, sz]), "b200_mul_mat_id": (i, [vp, tp, tp, tp, tp]),
         "b200_flash_attn_ext": (i, [vp, tp, tp, tp, tp, tp, tp, f, f, f]),
@@ -293,6 +305,35 @@ class Context:
         tp = C.POINTER(_Tensor)
         aw = (tp * n)(*[C.pointer(t) for t in cw]); ad = (tp * n)(*[C.pointer(t) for t in cd])
         _check(lib().b200_mul_mat_multi(self.h, aw, n, C.byref(cx), ad), "mul_mat_multi")
+
+    def chain_program(self, phases):
+        """phases: dicts {w: [...], dst: [...], in0, in1, normw, out_add, out_norm, out_mul, glu, prologue, epilogue, eps} of device tensors
+        -> (b200_chain_phase array, keep-alive list) for decode_chain()"""
+        arr = (ChainPhase * len(phases))()
+        keep = []
+        def ptr(t):
+            if t is None:
+                return None
+            c = t.c(); keep.append(c)
+            return C.pointer(c)
+        for a, ph in zip(arr, phases):
+            a.prologue, a.epilogue, a.n_w, a.eps = ph.get("prologue", X_PLAIN), ph.get("epilogue", Y_PLAIN), len(ph["w"]), ph.get("eps", 0.0)
+            for k, (w, d) in enumerate(zip(ph["w"], ph["dst"])):
+                a.w[k], a.dst[k] = ptr(w), ptr(d)
+            for name in ("in0", "in1", "normw", "out_add", "out_norm", "out_mul", "glu"):
+                pt = ptr(ph.get(name))
+                if pt is not None:
+                    setattr(a, name, pt)
+        return arr, keep
+
+    def decode_chain(self, program):
+        """b200_decode_chain: the dependent MUL_MAT groups of one token between two attention operators as ONE persistent kernel"""
+        arr, _keep = program
+        _check(lib().b200_decode_chain(self.h, arr, len(arr)), "decode_chain")
+
+    def decode_chain_supported(self, program):
+        arr, _keep = program
+        return bool(lib().b200_decode_chain_supported(self.h, arr, len(arr)))
 
     def mul_mat_gate_up_swiglu(self, wg, wu, x, gate, up, glu):
         """gate = wg x, up = wu x, glu = swiglu(gate, up) in one launch of the tensor-core q4_K GEMV (raises when it does not serve the shape)"""
