@@ -86,11 +86,12 @@ print(f"chain    {a.model} {a.mix}: {res['chain_us_per_layer']:7.2f} us/layer  {
 if a.trace:
     # device-side timeline (b200_debug_trace): per phase, medians over the CTAs of the last layer's launch, ns
     CAP = 148 * len(layers) + 8
-    buf = ctx.malloc((1 + CAP) * 256); ctx.memset(buf, 0, (1 + CAP) * 256)
+    buf = ctx.malloc((1 + CAP) * 256 + 16384); ctx.memset(buf, 0, (1 + CAP) * 256 + 16384)
     B.lib().b200_debug_trace(ctx.h, buf, CAP)
     run_chain(); ctx.synchronize()
     B.lib().b200_debug_trace(ctx.h, None, 0)
-    raw = np.empty((1 + CAP) * 32, np.uint64); ctx.d2h(raw, buf); ctx.synchronize()
+    raw = np.empty((1 + CAP) * 32 + 2048, np.uint64); ctx.d2h(raw, buf); ctx.synchronize()
+    stage_t = raw[(1 + CAP) * 32:].astype(np.int64).reshape(2, 1024)
     n = int(raw[0]); recs = raw[32:32 * (1 + n)].reshape(n, 32)
     per_launch = recs.reshape(len(layers), -1, 32) if n == 148 * len(layers) else recs[None]
     names = ["wait input", "build image", "stages", "publish"]
@@ -102,7 +103,14 @@ if a.trace:
             d = [np.median(st[:, p, j + 1] - st[:, p, j]) for j in range(4)]
             print(f"  phase {p}: enters at {int(np.median(st[:, p, 0]) - t0):6d} ns (spread {int(st[:, p, 0].max() - st[:, p, 0].min())})  " +
                   "  ".join(f"{nm} {int(v):5d}" for nm, v in zip(names, d)) + f"   max stages {int((st[:, p, 3] - st[:, p, 2]).max())}", flush=True)
-        print(f"  last CTA ends at {int(st[:, len(layers[0].phases) - 1, 4].max() - t0)} ns")
+        nph = len(layers[0].phases)
+        print(f"  last CTA ends at {int(st[:, nph - 1, 4].max() - t0)} ns")
+        if li == len(per_launch) - 1:
+            ns = int((stage_t[0] > 0).sum())
+            c0 = L[L[:, 1] % (1 << 32) == 0][0, 2:32].astype(np.int64).reshape(6, 5)
+            print(f"  CTA 0 of this launch: {ns} stages; per stage: issued / seen by its consumer (ns after CTA 0 start {int(c0[0,0]-t0)}); phases enter at", [int(c0[q, 0] - c0[0, 0]) for q in range(nph)], "stage loops start at", [int(c0[q, 2] - c0[0, 0]) for q in range(nph)])
+            for i0 in range(0, ns, 12):
+                print("   ", "  ".join(f"{i}:{int(stage_t[1, i] - c0[0, 0])}/{int(stage_t[0, i] - c0[0, 0])}" for i in range(i0, min(ns, i0 + 12))))
 if not a.no_separate and not a.ncu:
     ms = timed(run_separate, reps)
     res["separate_us_per_layer"] = ms * 1e3 / len(layers); res["separate_gbs"] = nbytes / (ms * 1e-3) / 1e9

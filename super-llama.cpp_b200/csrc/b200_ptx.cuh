@@ -28,6 +28,14 @@ static __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t pari
                  : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
     return ok != 0;
 }
+// the same with a suspend-time hint: the thread sleeps in hardware until the phase completes (or the hint, in ns, runs out) instead of
+// re-issuing polls that load the shared-memory barrier unit
+static __device__ __forceinline__ bool mbar_try_wait_hint(uint32_t bar, uint32_t parity, uint32_t ns) {
+    uint32_t ok;
+    asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n selp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(ok) : "r"(bar), "r"(parity), "r"(ns) : "memory");
+    return ok != 0;
+}
 static __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     while (!mbar_try_wait(bar, parity)) { }
 }
