@@ -165,6 +165,8 @@ typedef struct b200_chain_phase {
 } b200_chain_phase;
 B200_API int b200_decode_chain(b200_ctx * ctx, const b200_chain_phase * phases, int n_phases);
 B200_API int b200_decode_chain_supported(b200_ctx * ctx, const b200_chain_phase * phases, int n_phases);   // 1 / 0
+/* every wait inside the chain kernel is bounded (2 s): 0, or the code of the first wait that ran out since the last call (synchronizes) */
+B200_API int b200_decode_chain_error(b200_ctx * ctx);
 // as[K, M, n_expert], b[K, n_used|1, n_tokens] f32, ids[n_used, n_tokens] i32 -> dst[M, n_used, n_tokens]
 // (ggml/src/ggml.c:3205-3241).
 B200_API int b200_mul_mat_id(b200_ctx * ctx, const b200_tensor * as, const b200_tensor * b,

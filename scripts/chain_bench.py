@@ -104,6 +104,10 @@ if a.trace:
             print(f"  phase {p}: enters at {int(np.median(st[:, p, 0]) - t0):6d} ns (spread {int(st[:, p, 0].max() - st[:, p, 0].min())})  " +
                   "  ".join(f"{nm} {int(v):5d}" for nm, v in zip(names, d)) + f"   max stages {int((st[:, p, 3] - st[:, p, 2]).max())}", flush=True)
         nph = len(layers[0].phases)
+        ex = L[:, 26:29].astype(np.int64)
+        if (ex > 0).all():
+            print("  phase 1 image, medians after 'input complete': loads landed %d, norm sum known %d, quantized %d, (barrier) %d ns" %
+                  tuple(int(np.median(v - st[:, 1, 1])) for v in (ex[:, 0], ex[:, 1], ex[:, 2], st[:, 1, 2])))
         print(f"  last CTA ends at {int(st[:, nph - 1, 4].max() - t0)} ns")
         if li == len(per_launch) - 1:
             ns = int((stage_t[0] > 0).sum())

@@ -78,7 +78,7 @@ struct b200_backend_ctx {
     std::vector<b200_graph_entry> graphs; uint64_t graphs_epoch = 0, tick = 0, n_replayed = 0, n_captured = 0, n_eager = 0;
     // GGML_B200_GRAPH_STATS: device time of every replay (event pairs, read in be_free) and host time spent inside graph_compute
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> replay_events; double host_us = 0;
-    uint64_t n_fuse[5] = { 0, 0, 0, 0, 0 };          // launches saved by: matmul groups, RMS_NORM+MUL, ADD+RMS_NORM+MUL, ROPE/SET_ROWS, gate+up+GLU (counted while walking nodes)
+    uint64_t n_fuse[5] = { 0, 0, 0, 0, 0 };          // launches saved by: matmul groups, [1] = decode chains launched, ADD+RMS_NORM+MUL, ROPE/SET_ROWS, gate+up+GLU (counted while walking nodes)
 };
 // bumped whenever something a captured graph baked in may have changed under it: a weight tensor changed layout, a buffer was freed
 static std::atomic<uint64_t> g_layout_epoch{1};
@@ -245,8 +245,8 @@ static void be_free(ggml_backend_t be) {
         fprintf(stderr, "ggml-b200 graphs: %zu replays timed: %.1f us each on the device (fastest %.1f us)\n", c->replay_events.size(), ms * 1e3 / c->replay_events.size(), mn * 1e3);
     }
     if (getenv("GGML_B200_GRAPH_STATS"))
-        fprintf(stderr, "ggml-b200 fusions (launches saved while walking nodes): matmul groups %llu, add+norm+mul %llu, rope/set_rows %llu, gate+up+glu %llu\n",
-                (unsigned long long) c->n_fuse[0], (unsigned long long) c->n_fuse[2], (unsigned long long) c->n_fuse[3], (unsigned long long) c->n_fuse[4]);
+        fprintf(stderr, "ggml-b200 fusions (launches saved while walking nodes): matmul groups %llu, add+norm+mul %llu, rope/set_rows %llu, gate+up+glu %llu, decode chains %llu\n",
+                (unsigned long long) c->n_fuse[0], (unsigned long long) c->n_fuse[2], (unsigned long long) c->n_fuse[3], (unsigned long long) c->n_fuse[4], (unsigned long long) c->n_fuse[1]);
     if (getenv("GGML_B200_PROFILE") || getenv("GGML_B200_GRAPH_STATS"))
         fprintf(stderr, "ggml-b200 graphs: %llu computed launch by launch, %llu recorded, %llu replayed\n", (unsigned long long) c->n_eager, (unsigned long long) c->n_captured, (unsigned long long) c->n_replayed);
     if (getenv("GGML_B200_PROFILE")) {                           // per-kernel-kind device time of everything this backend launched
@@ -388,12 +388,175 @@ static int try_gate_up_glu(b200_backend_ctx * c, ggml_cgraph * g, int a, int b) 
     if (b200_mul_mat_gate_up_swiglu(c->ctx, &wg, &wu, &x, &dg, &du, &dl) != B200_OK) return -1;
     return j;
 }
+
+// ---- the persistent decode chain (b200_decode_chain, b200_chain.cu) -----------------------------------------------------------------
+// Node i opens a run of a llama layer's decode nodes between two attention operators:
+//     MUL_MAT(s) of one column  [GLU(SWIGLU)]  { ADD, RMS_NORM, MUL, MUL_MAT(s) [GLU(SWIGLU)]  |  MUL_MAT of the GLU column } ...
+// (src/models/llama.cpp:40-130: wo, +inpSA, ffn_norm, ffn_gate / ffn_up, swiglu, ffn_down, +ffn_inp, attn_norm of the next layer, wq / wk / wv;
+// in the last layer the run ends with output_norm and the output head).  A run may also open at the ADD.  Two or more MUL_MAT groups go out
+// as ONE kernel.  Returns the index of the last node taken, or -1 (then the nodes run one by one as before).
+// The graph allocator computes ADD and MUL in place where it can (ffn_inp over wo's result, the scaled norm over the norm): inside the chain
+// every CTA still reads the addend while one of them would overwrite it.  So a result that the next ADD overwrites is kept in a private column
+// instead (nothing else reads it -- that is why the allocator could reuse it), and a norm value that the MUL overwrites is not stored.
+static bool chain_on() { static int v = -1; if (v < 0) { const char * e = getenv("GGML_B200_NO_CHAIN"); v = (e && atoi(e)) ? 0 : 1; } return v != 0; }
+static bool chain_col(const ggml_tensor * t) {
+    return t && t->type == GGML_TYPE_F32 && t->ne[1] == 1 && t->ne[2] == 1 && t->ne[3] == 1 && t->nb[0] == 4 && t->data && ((uintptr_t) t->data & 15) == 0;
+}
+static bool chain_weight(const ggml_tensor * w) {
+    return w && (w->type == GGML_TYPE_Q4_K || w->type == GGML_TYPE_Q6_K) && w->ne[2] == 1 && w->ne[3] == 1 && w->ne[0] % 2048 == 0 && w->ne[1] % 4 == 0 && w->data;
+}
+struct chain_build {
+    b200_chain_phase ph[B200_CHAIN_MAX_PHASES];
+    b200_tensor t[B200_CHAIN_MAX_PHASES][16];         // storage behind the pointers: w[3], dst[3], in0, in1, normw, out_add, out_norm, out_mul, glu
+    int n = 0;
+};
+// every reader of t in the graph is one of `ok[0 .. nok)` (views of t count as readers of t), and t is not a graph output
+static bool chain_only_read_by(const ggml_cgraph * g, const ggml_tensor * t, ggml_tensor * const * ok, int nok) {
+    if (t->flags & 2) return false;                   // GGML_TENSOR_FLAG_OUTPUT (ggml/include/ggml.h)
+    for (int k = 0; k < g->n_nodes; ++k) {
+        const ggml_tensor * n = g->nodes[k];
+        bool reads = n->view_src == t;
+        for (int sidx = 0; sidx < GGML_MAX_SRC && !reads; ++sidx) reads = n->src[sidx] == t;
+        if (!reads) continue;
+        bool allowed = false;
+        for (int q = 0; q < nok; ++q) allowed |= ok[q] == n;
+        if (!allowed) return false;
+    }
+    return true;
+}
+// MUL_MAT group at node j (adjacent matmuls of one column, views in between) [+ GLU]: fills phase `ph`, returns the last node index or -1
+static int chain_group(ggml_cgraph * g, int j, const ggml_tensor * x, chain_build & cb, int ph) {
+    ggml_tensor * mm[3]; int nm = 0, last = -1;
+    for (int k = j; k < g->n_nodes && nm < 3; ++k) {
+        ggml_tensor * n = g->nodes[k];
+        if (op_is_view((int) n->op) || tensor_nelements(n) == 0) continue;
+        if (n->op != GGML_OP_MUL_MAT || n->src[1] != x || !chain_weight(n->src[0]) || !chain_col(n) || n->src[0]->ne[0] != x->ne[0]) break;
+        mm[nm++] = n; last = k;
+    }
+    if (nm == 0) return -1;
+    b200_chain_phase & P = cb.ph[ph];
+    P.epilogue = B200_CHAIN_Y_PLAIN; P.n_w = nm; P.glu = nullptr;
+    if (nm == 2) {
+        const int k = next_work(g, last);
+        if (k >= 0) {
+            ggml_tensor * glu = g->nodes[k];
+            if (glu->op == GGML_OP_GLU && glu->op_params[0] == GGML_GLU_OP_SWIGLU && glu->op_params[1] == 0 && glu->src[1] && chain_col(glu) &&
+                ((glu->src[0] == mm[0] && glu->src[1] == mm[1]) || (glu->src[0] == mm[1] && glu->src[1] == mm[0]))) {
+                if (glu->src[0] == mm[1]) { ggml_tensor * t = mm[0]; mm[0] = mm[1]; mm[1] = t; }       // gate first
+                P.epilogue = B200_CHAIN_Y_SWIGLU;
+                cb.t[ph][12] = to_b200(glu); P.glu = &cb.t[ph][12];
+                last = k;
+            }
+        }
+    }
+    for (int i = 0; i < nm; ++i) {
+        cb.t[ph][i] = to_b200(mm[i]->src[0]); cb.t[ph][3 + i] = to_b200(mm[i]);
+        P.w[i] = &cb.t[ph][i]; P.dst[i] = &cb.t[ph][3 + i];
+    }
+    return last;
+}
+static int try_chain(b200_backend_ctx * c, ggml_cgraph * g, int i) {
+    if (!chain_on() || fuse_off()) return -1;
+    static chain_build cb_store[B200_MAX_DEVICES];
+    chain_build & cb = cb_store[c->device % B200_MAX_DEVICES];
+    cb.n = 0;
+    memset(cb.ph, 0, sizeof(cb.ph));
+    ggml_tensor * res[B200_CHAIN_MAX_PHASES] = {};       // the single result column of a phase (what an ADD may take), or its glu
+    int last = -1, at = i, why = 0, n_add = 0;
+    const void * last_sum = nullptr;                     // the out_add column of the chain's last ADD so far
+    while (cb.n < B200_CHAIN_MAX_PHASES) {
+        ggml_tensor * n0 = at >= 0 && at < g->n_nodes ? g->nodes[at] : nullptr;
+        if (!n0) { why = 1; break; }
+        const int ph = cb.n;
+        b200_chain_phase & P = cb.ph[ph];
+        int end = -1;
+        bool b_is_last_sum = false;
+        void * saved = ph > 0 ? cb.t[ph - 1][3].data : nullptr;      // (the phase before may get a private result column: undone if this phase is dropped)
+        if (n0->op == GGML_OP_MUL_MAT) {
+            ggml_tensor * x = n0->src[1];
+            if (!chain_col(x)) { why = 2; break; }
+            if (ph > 0 && x != res[ph - 1]) { why = 3; break; }        // inside a run a bare matmul continues from the GLU column (or the single result) before it
+            P.prologue = B200_CHAIN_X_PLAIN;
+            cb.t[ph][6] = to_b200(x); P.in0 = &cb.t[ph][6];
+            end = chain_group(g, at, x, cb, ph);
+        } else if (n0->op == GGML_OP_ADD) {
+            const int j1 = next_work(g, at), j2 = j1 < 0 ? -1 : next_work(g, j1), j3 = j2 < 0 ? -1 : next_work(g, j2);
+            if (j3 < 0) { why = 4; break; }
+            ggml_tensor * add = n0, * norm = g->nodes[j1], * mul = g->nodes[j2];
+            if (norm->op != GGML_OP_RMS_NORM || norm->src[0] != add || mul->op != GGML_OP_MUL) { why = 5; break; }
+            ggml_tensor * nw = mul->src[0] == norm ? mul->src[1] : mul->src[1] == norm ? mul->src[0] : nullptr;
+            if (!nw || nw->type != GGML_TYPE_F32 || nw->ne[0] != add->ne[0] || nw->nb[0] != 4 || tensor_nelements(nw) != add->ne[0] || ((uintptr_t) nw->data & 15)) { why = 6; break; }
+            if (!chain_col(add) || !chain_col(norm) || !chain_col(mul) || !chain_col(add->src[0]) || !chain_col(add->src[1])) { why = 7; break; }
+            ggml_tensor * a = add->src[0], * b = add->src[1];
+            if (ph > 0) { if (b == res[ph - 1]) { b = a; a = res[ph - 1]; } else if (a != res[ph - 1]) { why = 8; break; } }    // in0 = the result of the phase before
+            P.prologue = B200_CHAIN_X_ADD_NORM_MUL;
+            b_is_last_sum = last_sum && b->data == last_sum;
+            memcpy(&P.eps, norm->op_params, 4);
+            cb.t[ph][6] = to_b200(a); cb.t[ph][7] = to_b200(b); cb.t[ph][8] = to_b200(nw);
+            cb.t[ph][9] = to_b200(add); cb.t[ph][10] = to_b200(norm); cb.t[ph][11] = to_b200(mul);
+            P.in0 = &cb.t[ph][6]; P.in1 = &cb.t[ph][7]; P.normw = &cb.t[ph][8];
+            P.out_add = &cb.t[ph][9]; P.out_norm = &cb.t[ph][10]; P.out_mul = &cb.t[ph][11];
+            // the norm and its scaled form are read by the MUL / by this phase's matmuls only: then they need no store (the allocator usually
+            // gives them the memory of a column that has just died -- the addend, or each other)
+            end = chain_group(g, j3, mul, cb, ph);
+            if (end < 0) { why = 9; break; }
+            {
+                ggml_tensor * mm[3] = {}; int nm = 0;
+                for (int k = j3; k <= end; ++k) if (g->nodes[k]->op == GGML_OP_MUL_MAT && g->nodes[k]->src[1] == mul) mm[nm++] = g->nodes[k];
+                ggml_tensor * only_mul[1] = { mul };
+                if (chain_only_read_by(g, norm, only_mul, 1)) P.out_norm = nullptr;
+                if (chain_only_read_by(g, mul, mm, nm)) P.out_mul = nullptr;
+            }
+            // what IS stored must not land on anything the phase still reads; an ADD in place over the result of the phase before is the one
+            // case with a remedy: that result goes to a private column instead (see above)
+            const ggml_tensor * live_out[2] = { P.out_norm ? norm : nullptr, P.out_mul ? mul : nullptr };
+            bool bad = ranges_overlap(add, b) || (P.out_norm && P.out_mul && ranges_overlap(norm, mul));
+            for (const ggml_tensor * o : live_out) if (o) bad = bad || ranges_overlap(o, a) || ranges_overlap(o, b) || ranges_overlap(o, add) || ranges_overlap(o, nw);
+            if (bad) { end = -1; }
+            if (ranges_overlap(add, a)) {
+                if (ph == 0 || add->data != a->data) { why = 10; break; }
+                float * priv = (float *) b200_scratch(c->ctx, 4, (size_t) B200_CHAIN_MAX_PHASES * 32768 * 4);
+                if (!priv) { why = 11; break; }
+                priv += (size_t) ph * 32768;
+                cb.t[ph - 1][3].data = priv; cb.t[ph][6].data = priv;                  // phase before: dst[0]; this phase: in0
+            }
+        } else { why = 12; break; }
+        if (end < 0) { if (ph > 0) cb.t[ph - 1][3].data = saved; { why = 13; break; } }
+        res[ph] = P.epilogue == B200_CHAIN_Y_SWIGLU ? g->nodes[end] : (P.n_w == 1 ? g->nodes[end] : nullptr);
+        // a phase's results must not land on what the same phase still reads.  (Not the addend of a later phase when it is the chain's first
+        // from outside or the sum of the ADD before: the kernel holds those in registers from the start / from that ADD on, so a result may
+        // take the addend's memory -- the allocator often gives wq's result the block ffn_inp just left.)
+        bool clash = false;
+        for (int k = 0; k <= P.n_w && !clash; ++k) for (int q = 6; q <= 8 && !clash; ++q) {
+            if (q == 7 && ph > 0 && (n_add == 0 || b_is_last_sum)) continue;
+            const b200_tensor * in = q == 6 ? P.in0 : q == 7 ? P.in1 : P.normw, * o = k < P.n_w ? P.dst[k] : P.glu;
+            if (in && in->data && o && o->data && (const char *) in->data < (const char *) o->data + o->ne[0] * 4 && (const char *) o->data < (const char *) in->data + in->ne[0] * 4) clash = true;
+        }
+        if (clash) { if (ph > 0) cb.t[ph - 1][3].data = saved; { why = 14; break; } }
+        if (P.prologue == B200_CHAIN_X_ADD_NORM_MUL) { ++n_add; last_sum = P.out_add->data; }
+        ++cb.n; last = end;
+        at = next_work(g, end);
+        if (!res[ph]) { why = 15; break; }                              // several result columns (wq / wk / wv): nothing in a chain continues from them
+    }
+    { static int said = 0; if (said < 12 && getenv("GGML_B200_DEBUG")) { ++said; B200_LOG("decode chain at node %d (%s): %d phases, stopped at node %d (%s) for reason %d", i, g->nodes[i]->name, cb.n, at, at >= 0 && at < g->n_nodes ? g->nodes[at]->name : "-", why); } }
+    if (cb.n < 2) return -1;
+    if (!b200_decode_chain_supported(c->ctx, cb.ph, cb.n)) {
+        static int said = 0;
+        if (!said++ && getenv("GGML_B200_DEBUG")) B200_LOG("decode chain declined at node %d (%s): %s", i, g->nodes[i]->name, b200_last_error());
+        return -1;
+    }
+    if (b200_decode_chain(c->ctx, cb.ph, cb.n) != B200_OK) return -1;
+    for (int k = i; k <= last; ++k) if (!op_is_view((int) g->nodes[k]->op)) b200_note_write(c->ctx, g->nodes[k]->data, tensor_nbytes(g->nodes[k]));
+    return last;
+}
 static enum ggml_status run_nodes(b200_backend_ctx * c, ggml_cgraph * g) {
     c->ctx->qcache.valid = 0; c->ctx->mcache.valid = 0;      // tensors may have been rewritten through buffer set_tensor since the last graph
     for (int i = 0; i < g->n_nodes; ++i) {
         ggml_tensor * node = g->nodes[i];
         if (op_is_view((int) node->op) || tensor_nelements(node) == 0) continue;
         int rc;
+        // decode: the whole run of a layer's nodes between two attention operators as one persistent kernel
+        if ((node->op == GGML_OP_MUL_MAT || node->op == GGML_OP_ADD) && node->ne[1] == 1 && (rc = try_chain(c, g, i)) >= 0) { c->n_fuse[1] += 1; i = rc; continue; }
         // MUL_MAT nodes that follow each other (views in between do no work) and read the same src1 -- ffn_gate / ffn_up, attn_v / attn_k
         // of a llama layer -- go out as ONE launch (b200_mul_mat_multi; it falls back to one launch each when the kernels cannot take them
         // together).  Only adjacent nodes: running a later node early could write into memory the graph allocator still lends to a

@@ -9,15 +9,20 @@
 // ~0.7 us until its activation column has arrived and 0.5-1.5 us of q8_1 quantization before the first weight byte is used, and its
 // shared-memory ring only holds what ONE launch prefetched -- the matrices under ~35 MB (4 of 5 per layer) ran at 35-45 % of HBM.
 // Here the weight stream never stops at an operator boundary:
-//   * one CTA per SM, persistent for the whole chain.  A PRODUCER warp walks the chain's weight matrices in their fixed order and
-//     pulls this CTA's row tiles (CH_R rows x 2048 weights per stage) with cp.async.bulk into ONE shared-memory ring (~190 KB per SM,
-//     ~28 MB over the GPU = ~4 us of HBM time of lookahead); it depends on nothing but ring space, so it runs ahead through the
-//     boundaries (and, launched with PDL, under the tail of the attention kernel in front);
-//   * CH_NW CONSUMER warps take the stages round-robin: conflict-free 128-bit shared loads, dp4a on nibbles masked in place
+//   * one CTA per SM, persistent for the whole chain.  This CTA's row tiles of ALL the chain's matrices (CH_R rows x 2048 weights per
+//     stage) form one sequence that is pulled through ONE shared-memory ring (up to ~200 KB per SM) by the TMA engine, one 2-D tensor
+//     request per stage: a slot is re-armed with the stage nslot ahead the moment it has been consumed, whatever phase that stage
+//     belongs to, so the stream runs ahead through the boundaries (and, launched with PDL, under the tail of the kernel in front).
+//     Measured ceilings (profiles/r2_membw_ceilings.txt): 7.2 TB/s read-only with <= 64 requests of >= 4.6 KB in flight per SM; with 128
+//     requests of 1152 B in flight the same engine delivers 2.8 TB/s -- few, large requests;
+//   * every warp owns the ring slots q % CH_NW == warp: conflict-free 128-bit shared loads, dp4a on nibbles masked in place
 //     (b200_gemv_traits.cuh), a 6-shuffle reduction, partial sums into a per-CTA table that is summed in a fixed order (deterministic);
 //   * between two phases the activation goes through L2: results are stored, a grid-wide arrival counter (red.release / ld.acquire)
 //     tells every CTA when the column is complete, and each CTA then builds its own q8_1 image in shared memory -- residual ADD,
 //     RMS_NORM and the norm weight folded into that prologue (one pass, 16 values per thread), SwiGLU into the epilogue of gate / up.
+//     A second hand-over form is kept behind GGML_B200_CHAIN_HANDOVER=ll: the validity flag INSIDE the data (8-byte (value, tag)
+//     stores are single transactions, the reader polls the data itself, the residual stays in registers, gate / up's epilogue publishes
+//     q8_1 blocks so that ffn_down fetches 1.25 bytes per activation).  It measured no faster (see ch_force_barrier) and is not the default.
 // Bound: HBM.  Algorithmic bytes = sum over the chain's weights of M * K * bytes_per_block / 256.
 #include "b200_common.cuh"
 #include "b200_ptx.cuh"
@@ -27,13 +32,20 @@
 #include <string.h>
 
 #define CH_R       4       // weight rows per tile
-// consumer warps: template parameter NW of the kernel (CH_NW / CH_NT inside it); the dots are latency-bound per warp (~20 clk per instruction
-// at 4 warps per scheduler, measured), so the warp count is what buys consumer throughput
 #define CH_MAXPH   B200_CHAIN_MAX_PHASES
 #define CH_MAXSEG  3
+#define CH_MAXMAPS 8
+#define CH_MAXST   1024    // stages per CTA and launch (the stage table)
 #define CH_PSUM    2560    // floats in the partial-sum table: stages per CTA and phase <= CH_PSUM / CH_R
 #define CH_Q4K_CHUNK 1152  // 8 blocks of 144 B
 #define CH_Q6K_CHUNK 1680  // one repacked group of 8 blocks
+#define CH_LL_BYTES  (256 * 1024)   // hand-over area per phase: 8 bytes per f32 (K <= 32768), or 80 bytes per q8_1 block
+
+// how a phase gets its activation column (in0)
+enum { CH_IN_EXTERNAL = 0,   // written before this launch: plain loads
+       CH_IN_BARRIER  = 1,   // written by the phase before, plain f32: grid-wide arrival counter, then plain loads (general fallback)
+       CH_IN_LL_F32   = 2,   // (value, tag) pairs of the phase before
+       CH_IN_LL_Q8    = 3 }; // q8_1 blocks of the SWIGLU phase before (10 (word, tag) pairs per block) + (value, tag) pairs of its tail rows
 
 struct ch_seg { const uint8_t * w; size_t nb1; float * dst; int M; int q6; int map; };      // map: index of the weight's 2-D tensor map
 struct ch_phase {
@@ -42,70 +54,153 @@ struct ch_phase {
     const float * in0, * in1, * normw;
     float * out_add, * out_norm, * out_mul, * glu;
     float eps;
-    int nunits;            // units of CH_R rows (SWIGLU: a unit is CH_R rows of gate AND of up)
-    int off;               // unit u belongs to CTA (u + off) % gridDim.x
+    // units of CH_R rows (SWIGLU: CH_R rows of gate AND of up).  Units [0, ng8) go to the CTAs in groups of 8 consecutive units (32 rows
+    // = whole q8_1 blocks: only there a CTA can quantize its own results), gpc groups each; units [ng8, nunits) one by one, round-robin
+    int nunits, ng8, gpc;
+    int off;               // group g belongs to CTA (g + off) % G, tail unit u to CTA (u - ng8 + off) % G
     int nch;               // K / 2048
     unsigned nch_inv;      // ceil(65536 / nch): x / nch == (x * nch_inv) >> 16 for x < 4096
     int types;             // bit 0: a q4_K activation image is needed, bit 1: a q6_K one
-    int in1_early;         // in1 is not written by the phase right before: it may be fetched before the hand-over
+    int in_mode, out_mode; // CH_IN_* of this phase's in0 / of the next phase's (what the epilogue has to publish)
+    int in1_kept;          // in1 is the out_add column of an earlier phase of this launch: still in registers
+    int nq8;               // CH_IN_LL_Q8: the first nq8 activations arrive as q8_1 blocks, the rest as f32 pairs
 };
-#define CH_MAXMAPS 8
 struct ch_args {
     CUtensorMap map[CH_MAXMAPS];   // per weight matrix: rows of nb1 bytes as 8-byte elements, box = one K chunk x CH_R rows: ONE request per stage
     ch_phase ph[CH_MAXPH];
     int nph, slot_bytes, nslot, act_bytes;
-    unsigned * sync;       // [0] phase arrivals, [1] CTAs done, [2] error code
+    int pre_in1;           // the phase whose addend (in1) comes from outside the launch and is fetched at the very start, or -1
+    unsigned * sync;       // [0] phase arrivals (CH_IN_BARRIER), [1] CTAs done, [2] error code, [3] hand-over epoch, [4] abort
+    uint8_t * ll;          // hand-over areas, CH_LL_BYTES per phase
     int dbg;               // GGML_B200_CHAIN_DBG (measurement only): 1 skip the dot products, 2 no weight traffic
     unsigned long long * trace; int trace_cap;   // b200_debug_trace (measurement only): per CTA and phase, globaltimer at 5 points
 };
 
 static __device__ __forceinline__ unsigned long long ch_now() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 // every wait in this kernel is bounded: a stuck chain must fail the launch, not hang the GPU
-#define CH_TIMEOUT_NS 4000000000ull
-static __device__ __noinline__ void ch_die(unsigned * sync, unsigned code) { sync[2] = code; __threadfence(); __trap(); }
-static __device__ __forceinline__ void ch_mbar_wait(uint32_t bar, uint32_t parity, unsigned * sync, unsigned code) {
-    unsigned n = 0;
-    unsigned long long t0 = 0;                       // (%globaltimer is a slow read: only touched after ~1000 failed polls)
-    while (!mbar_try_wait_hint(bar, parity, 1000000u)) {
-        if ((++n & 0x3ffu) == 0) { const unsigned long long t = ch_now(); if (!t0) t0 = t; else if (t - t0 > CH_TIMEOUT_NS) ch_die(sync, code); }
+#define CH_TIMEOUT_NS 2000000000ull
+// A wait that runs out records where (sync[2] = code, first one wins) and raises the launch-wide abort word sync[4]; every other wait sees
+// it within its next 1024 polls and gives up too, so the kernel ENDS (with garbage results) and b200_decode_chain_error() reports it.
+struct ch_watch {                                     // (%globaltimer is a slow read: only touched every 1024 failed polls)
+    unsigned n = 0; unsigned long long t0 = 0;
+    __device__ __forceinline__ bool spin(unsigned * sync, unsigned code) {         // true: give up
+        if ((++n & 0x3ffu) != 0) return false;
+        unsigned ab;
+        asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(ab) : "l"(sync + 4));
+        if (ab) return true;
+        const unsigned long long t = ch_now();
+        if (!t0) { t0 = t; return false; }
+        if (t - t0 <= CH_TIMEOUT_NS) return false;
+        atomicCAS(sync + 2, 0u, code); atomicExch(sync + 4, 1u);
+        return true;
     }
+};
+static __device__ __forceinline__ void ch_mbar_wait(uint32_t bar, uint32_t parity, unsigned * sync, unsigned code) {
+    ch_watch w;
+    while (!mbar_try_wait_hint(bar, parity, 1000000u)) if (w.spin(sync, code)) break;
 }
 static __device__ __forceinline__ float4 ch_ldcg4(const float * p) {      // produced by other SMs during this launch: never from L1
     float4 r;
     asm volatile("ld.global.cg.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
     return r;
 }
+// hand-over pairs: an aligned 8-byte store is one transaction, so the tag validates the value next to it
+static __device__ __forceinline__ void ch_ll_store(void * p, unsigned v, unsigned tag) {
+    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" :: "l"(p), "r"(v), "r"(tag) : "memory");
+}
+static __device__ __forceinline__ uint4 ch_ll_load2(const void * p) {      // two pairs: (x = value, y = tag), (z = value, w = tag)
+    uint4 r;
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+    return r;
+}
 template <int NT> static __device__ __forceinline__ void ch_bar_n() { asm volatile("bar.sync 1, %0;" :: "n"(NT) : "memory"); }
 #define ch_bar_consumers() ch_bar_n<CH_NT>()
 
-// unit -> (first tile's segment, first row inside it); PLAIN phases concatenate the segments' rows, SWIGLU phases pair them
-static __device__ __forceinline__ void ch_locate(const ch_phase & ph, int u, int tl, int & sg, int & row) {
-    row = u * CH_R;
-    if (ph.epilogue == B200_CHAIN_Y_SWIGLU) { sg = tl; return; }
-    sg = 0;
+// local unit k of a CTA -> global unit (see ch_phase); fg / ft = the CTA's first group / first tail unit
+static __device__ __forceinline__ int ch_unit(const ch_phase & ph, int k, int fg, int ft, int G) {
+    const int kg = ph.gpc * 8;
+    return k < kg ? ((k >> 3) * G + fg) * 8 + (k & 7) : ph.ng8 + ft + (k - kg) * G;
+}
+// unit -> (segment, first row inside it); PLAIN phases concatenate the segments' rows, SWIGLU phases pair them (sg = tile parity)
+static __device__ __forceinline__ void ch_locate(const ch_phase & ph, int u, int & sg, int & row) {
+    row = u * CH_R; sg = 0;
     if (ph.nseg > 1 && row >= ph.seg[0].M) { row -= ph.seg[0].M; sg = 1; if (ph.nseg > 2 && row >= ph.seg[1].M) { row -= ph.seg[1].M; sg = 2; } }
 }
 
+// 16 quants + (d, s) of one half block into this CTA's activation image(s)
+static __device__ __forceinline__ void ch_store_unit(int u16, int4 w, float d16, float s16, int K, int nblocks, int types, uint8_t * s_act) {
+    uint8_t * a = s_act;
+    if (types & 1) { gs_traits<B200_TYPE_Q4_K>::store_unit(a, K, nblocks, u16 >> 1, u16 & 1, w, d16, s16); a += gs_traits<B200_TYPE_Q4_K>::act_bytes(K); }
+    if (types & 2)   gs_traits<B200_TYPE_Q6_K>::store_unit(a, K, nblocks, u16 >> 1, u16 & 1, w, d16, s16);
+}
 // the q8_1 image(s) of 16 values held by this thread (unit u16 = 16 consecutive activations; lanes 2i, 2i+1 form one 32-value block)
 static __device__ __forceinline__ void ch_quant_store(const float (&f)[16], int lane, int u16, bool live, int K, int nblocks, int types, uint8_t * s_act) {
     int4 w; float d; unsigned usum;
     b200_q8_1_half16(f, lane, w, d, usum);
-    if (!live) return;
-    const float d16 = __half2float(__float2half_rn(d)), s16 = __half2float(__float2half_rn(__fmul_rn(d, (float) (int) usum)));
-    uint8_t * a = s_act;
-    if (types & 1) { gs_traits<B200_TYPE_Q4_K>::store_unit(a, K, nblocks, u16 >> 1, u16 & 1, w, d16, s16); a += gs_traits<B200_TYPE_Q4_K>::act_bytes(K); }
-    if (types & 2)   gs_traits<B200_TYPE_Q6_K>::store_unit(a, K, nblocks, u16 >> 1, u16 & 1, w, d16, s16);
+    if (live) ch_store_unit(u16, w, __half2float(__float2half_rn(d)), __half2float(__float2half_rn(__fmul_rn(d, (float) (int) usum))), K, nblocks, types, s_act);
+}
+
+
+// One warp, one q4_K stage (CH_R = 4 rows x 8 blocks of 256 weights, rows CH_Q4K_CHUNK bytes apart at st): lane = (block bl = lane & 7,
+// pair bit = (lane >> 3) & 1, row half = lane >> 4).  In pass `it` the lane takes the sub-block pair pp = 2 it + pair bit -- 64 weights, the
+// 32 bytes qs[32 pp ..] whose low nibbles are sub-block 2 pp and whose high nibbles are sub-block 2 pp + 1 (ggml-quants.c:1352-1374) -- of its
+// block in the TWO rows 2 (lane >> 4) + {0, 1}: all lanes sit in the same branch of get_scale_min_k4 (ggml-quants.c:703-710), one lane owns
+// whole sub-blocks (both 6-bit scale / min pairs are decoded once, not once per 16-byte half as gs_traits does), and the two row sums of a
+// lane drop the first step of the cross-lane reduction.  acc[0], acc[1]: rows 2 (lane >> 4), 2 (lane >> 4) + 1.
+// Activation image: gs_traits<B200_TYPE_Q4_K>::store_unit (planes of 16-byte units [c][gb], then (dA(2p), s(2p), dA(2p+1) / 16, s(2p+1))[p][gb]).
+static __device__ __forceinline__ void ch_consume_q4k(uint32_t st, int lane, uint32_t act, int K, int nblocks, int c, float (&acc)[2]) {
+    const int bl = lane & 7, gb = c * GS_CB + bl, pb = (lane >> 3) & 1;
+    const uint32_t rows = st + (uint32_t) (lane >> 4) * (2 * CH_Q4K_CHUNK) + bl * 144;
+#pragma unroll
+    for (int it = 0; it < 2; ++it) {
+        const int pp = 2 * it + pb, sh = 16 * pb;
+        const int4 a0l = lds128(act + ((2 * pp) * nblocks + gb) * 16), a0h = lds128(act + ((2 * pp + 1) * nblocks + gb) * 16);
+        const int4 a1l = lds128(act + (K >> 1) + ((2 * pp) * nblocks + gb) * 16), a1h = lds128(act + (K >> 1) + ((2 * pp + 1) * nblocks + gb) * 16);
+        const int4 dsr = lds128(act + K + (pp * nblocks + gb) * 16);
+        const float dA0 = __int_as_float(dsr.x), sA0 = __int_as_float(dsr.y), dA1 = __int_as_float(dsr.z), sA1 = __int_as_float(dsr.w);
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+            const uint32_t base = rows + r * CH_Q4K_CHUNK;
+            const int4 hdr = lds128(base);
+            const int4 qa  = lds128(base + 16 + pp * 32), qb = lds128(base + 32 + pp * 32);
+            const unsigned s0 = (unsigned) hdr.y, s1 = (unsigned) hdr.z, s2 = (unsigned) hdr.w;
+            int sc0, sc1, m0, m1;
+            if (it == 0) {
+                sc0 = (s0 >> sh) & 63;  sc1 = (s0 >> (sh + 8)) & 63;
+                m0  = (s1 >> sh) & 63;  m1  = (s1 >> (sh + 8)) & 63;
+            } else {
+                sc0 = ((s2 >> sh) & 0xF)        | (((s0 >> (sh + 6)) & 3) << 4);
+                sc1 = ((s2 >> (sh + 8)) & 0xF)  | (((s0 >> (sh + 14)) & 3) << 4);
+                m0  = ((s2 >> (sh + 4)) & 0xF)  | (((s1 >> (sh + 6)) & 3) << 4);
+                m1  = ((s2 >> (sh + 12)) & 0xF) | (((s1 >> (sh + 14)) & 3) << 4);
+            }
+            int i0 = __dp4a(qa.x & 0x0F0F0F0F, a0l.x, 0), j0 = __dp4a(qb.x & 0x0F0F0F0F, a0h.x, 0);
+            i0 = __dp4a(qa.y & 0x0F0F0F0F, a0l.y, i0); j0 = __dp4a(qb.y & 0x0F0F0F0F, a0h.y, j0);
+            i0 = __dp4a(qa.z & 0x0F0F0F0F, a0l.z, i0); j0 = __dp4a(qb.z & 0x0F0F0F0F, a0h.z, j0);
+            i0 = __dp4a(qa.w & 0x0F0F0F0F, a0l.w, i0); j0 = __dp4a(qb.w & 0x0F0F0F0F, a0h.w, j0);
+            int i1 = dp4a_us((unsigned) qa.x & 0xF0F0F0F0u, a1l.x, 0), j1 = dp4a_us((unsigned) qb.x & 0xF0F0F0F0u, a1h.x, 0);
+            i1 = dp4a_us((unsigned) qa.y & 0xF0F0F0F0u, a1l.y, i1); j1 = dp4a_us((unsigned) qb.y & 0xF0F0F0F0u, a1h.y, j1);
+            i1 = dp4a_us((unsigned) qa.z & 0xF0F0F0F0u, a1l.z, i1); j1 = dp4a_us((unsigned) qb.z & 0xF0F0F0F0u, a1h.z, j1);
+            i1 = dp4a_us((unsigned) qa.w & 0xF0F0F0F0u, a1l.w, i1); j1 = dp4a_us((unsigned) qb.w & 0xF0F0F0F0u, a1h.w, j1);
+            const float2 dm = __half22float2(*(const __half2 *) &hdr.x);
+            const float t = (float) (sc0 * (i0 + j0)) * dA0 + (float) (sc1 * (i1 + j1)) * dA1;      // (dA1 carries the 1/16 of the unshifted high nibbles)
+            const float u = (float) m0 * sA0 + (float) m1 * sA1;
+            acc[r] = fmaf(dm.x, t, acc[r]);
+            acc[r] = fmaf(-dm.y, u, acc[r]);
+        }
+    }
 }
 
 template <int CH_NW>
 __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_constant__ ch_args P) {
     constexpr int CH_NT = CH_NW * 32;
     extern __shared__ __align__(128) uint8_t smem[];
-    // layout: ring [nslot][slot_bytes] | activation image(s) [act_bytes] | psum [CH_PSUM] f32 | red [32] f32 | full[nslot] mbarriers
+    // layout: ring [nslot][slot_bytes] | activation image(s) [act_bytes] | psum [CH_PSUM] f32 | red [32] f32 | full[nslot] mbarriers | stage table [CH_MAXST] u32
     uint8_t *  s_act  = smem + (size_t) P.nslot * P.slot_bytes;
     float *    s_psum = (float *) (s_act + P.act_bytes);
     float *    s_red  = s_psum + CH_PSUM;
     uint64_t * s_bar  = (uint64_t *) (s_red + 32);
+    uint32_t * s_tab  = (uint32_t *) (s_bar + P.nslot);
     const uint32_t ring = smem_u32(smem), full0 = smem_u32(s_bar);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, tid = threadIdx.x;
     const int G = gridDim.x, cta = blockIdx.x;
@@ -120,7 +215,7 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
     // The CTA's stages form ONE sequence over all phases (phase by phase, unit by unit, tile by tile, K chunk by K chunk); stage s lives in
     // ring slot s % nslot, and slot q belongs to warp q % CH_NW for the whole launch.  A warp that has consumed stage s re-arms the slot with
     // stage s + nslot at once -- whatever phase that belongs to -- so at a phase boundary the ring already holds (or is receiving) the next
-    // phase's first nslot stages.  Sixteen issuers, each overlapping its copies with the others' dot products: a dedicated producer
+    // phase's first nslot stages.  Sixteen issuers, each overlapping its request with the others' dot products: a dedicated producer
     // thread managed one stage per ~650 ns (an in-order chain of ~150 dependent instructions, measured), i.e. 2.3 TB/s over the GPU.
     int cum[CH_MAXPH + 1];                            // first stage of every phase in this CTA's sequence
     cum[0] = 0;
@@ -129,50 +224,64 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
         int n = 0;
         if (p < P.nph) {
             const ch_phase & ph = P.ph[p];
-            int first = cta - ph.off; if (first < 0) first += G;
-            const int nu = first < ph.nunits ? (ph.nunits - first + G - 1) / G : 0;
+            int ft = cta - ph.off; if (ft < 0) ft += G;
+            const int nt = ph.nunits - ph.ng8, nu = ph.gpc * 8 + (ft < nt ? (nt - ft + G - 1) / G : 0);
             n = nu * (ph.epilogue == B200_CHAIN_Y_SWIGLU ? 2 : 1) * ph.nch;
         }
         cum[p + 1] = cum[p] + n;
     }
     const int total = (P.dbg & 2) ? 0 : cum[CH_MAXPH];
-    // stage sl of phase ph -> (segment, first row, K chunk): no division (nch_inv), SWIGLU tiles alternate gate / up
+    // stage sl of phase ph -> (segment, first row, K chunk, local unit): no division (nch_inv), SWIGLU tiles alternate gate / up
     auto decode = [&](const ch_phase & ph, int sl, int & sg, int & row, int & c, int & k) {
         const int tile = (int) (((unsigned) sl * ph.nch_inv) >> 16);
         c = sl - tile * ph.nch;
-        int first = cta - ph.off; if (first < 0) first += G;
-        if (ph.epilogue == B200_CHAIN_Y_SWIGLU) { k = tile >> 1; sg = tile & 1; row = (first + k * G) * CH_R; }
-        else { k = tile; ch_locate(ph, first + k * G, 0, sg, row); }
+        int f = cta - ph.off; if (f < 0) f += G;
+        if (ph.epilogue == B200_CHAIN_Y_SWIGLU) { k = tile >> 1; sg = tile & 1; row = ch_unit(ph, k, f, f, G) * CH_R; }
+        else { k = tile; ch_locate(ph, ch_unit(ph, k, f, f, G), sg, row); }
     };
-    auto issue = [&](int s, int slot) {               // one lane: fetch stage s into its slot -- ONE tensor request of CH_R row chunks
+    // The stage table: what stage s of this CTA fetches and for whom, worked out ONCE by as many threads as there are stages (the walk from
+    // a stage number to its tensor coordinates is ~120 dependent instructions; done at every refill by one lane it was a fifth of the loop).
+    // Entry: first row (18 bits) | tensor map (3) << 18 | q6_K << 21 | K chunk (5) << 22 | segment (2) << 27.
+    for (int s = tid; s < total; s += CH_NT) {
         int p = 0, base = 0;
 #pragma unroll
         for (int q = 1; q < CH_MAXPH; ++q) if (s >= cum[q]) { p = q; base = cum[q]; }
         const ch_phase & ph = P.ph[p];
         int sg, row, c, k; decode(ph, s - base, sg, row, c, k);
         const ch_seg & S = ph.seg[sg];
-        const uint32_t cb = S.q6 ? CH_Q6K_CHUNK : CH_Q4K_CHUNK;
+        s_tab[s] = (uint32_t) row | ((uint32_t) S.map << 18) | ((uint32_t) (S.q6 != 0) << 21) | ((uint32_t) c << 22) | ((uint32_t) sg << 27);
+    }
+    __syncthreads();
+    auto issue = [&](int s, int slot) {               // one lane: fetch stage s into its slot -- ONE tensor request of CH_R row chunks
+        const uint32_t e = s_tab[s];
+        const uint32_t cb = (e >> 21) & 1u ? CH_Q6K_CHUNK : CH_Q4K_CHUNK;
         const uint32_t bar = full0 + 8 * slot, dst = ring + slot * P.slot_bytes;
         if (P.trace && cta == 0 && s < 1024) P.trace[32 * (1 + P.trace_cap) + 1024 + s] = ch_now();   // (measurement only)
         mbar_arrive_expect_tx(bar, cb * CH_R);
-        tma_load_2d(dst, &P.map[S.map], c * (int) (cb >> 3), row, bar);
+        tma_load_2d(dst, &P.map[(e >> 18) & 7u], (int) (((e >> 22) & 31u) * (cb >> 3)), (int) (e & 0x3ffffu), bar);
     };
     // first lap: weights do not depend on the kernel in front (PDL): the ring fills under its tail
     if (lane == 0) for (int q = warp; q < P.nslot && q < total; q += CH_NW) issue(q, q);
     // this warp's cursor in the stage sequence: it owns the slots q with q % CH_NW == warp and meets them lap after lap
     int my_slot = warp, my_lap = 0;
 
-    // ------------------------------------------------ consumers ------------------------------------------------
+    // ------------------------------------------------ the phases ------------------------------------------------
     unsigned long long * rec = nullptr;               // (measurement only) words 2 + 5 p + j: phase p entered, input complete, image built, stages done, published
     if (P.trace && tid == 0) rec = b200_trace_open(P.trace, P.trace_cap, P.nph, 0xC4A1);
 #define CH_STAMP(j) do { if (rec) rec[2 + 5 * p + (j)] = ch_now(); } while (0)
     int s_base = 0;                                   // stages of this CTA before the current phase
-    unsigned target = 0;
+    unsigned target = 0, tag = 0;
+    // this thread's 16 values of the NEXT residual ADD's addend: fetched right at the start when it comes from outside, afterwards the sum
+    // itself (out_add) for the ADD after that.  It never has to be read back from memory in mid-launch: the graph allocator likes to hand
+    // an addend's block, dead after its ADD, to one of the results of the very phase that adds it
+    float hkeep[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) hkeep[i] = 0.0f;
     for (int p = 0; p < P.nph; ++p) {
         const ch_phase & ph = P.ph[p];
         const int K = ph.K, nblocks = K >> 8, nu16 = K >> 4;
         CH_STAMP(0);
-        // what does not depend on the phase before is fetched ahead of the hand-over: the norm weight, and the residual if it is older
+        // what does not depend on the phase before is fetched ahead of the hand-over: the norm weight, and a residual from outside
         // (every CTA reads the same lines at the same moment: ~9 B/clk per SM of L2 broadcast bandwidth, measured -- bytes on the critical path count)
         const bool normp = ph.prologue != B200_CHAIN_X_PLAIN, addp = ph.prologue == B200_CHAIN_X_ADD_NORM_MUL, live = normp && tid < nu16;
         float4 gpre[4], bpre[4];
@@ -181,62 +290,133 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
             gpre[j] = bpre[j] = make_float4(0.f, 0.f, 0.f, 0.f);
             if (live) gpre[j] = __ldg((const float4 *) (ph.normw + (size_t) tid * 16 + 4 * j));
         }
-        if (p == 0) asm volatile("griddepcontrol.wait;" ::: "memory");
-        if (live && addp && ph.in1_early) {
+        if (p == 0) {
+            asm volatile("griddepcontrol.wait;" ::: "memory");
+            asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(tag) : "l"(P.sync + 3));
+            tag += 1u;                                // this launch's hand-over tag: differs from whatever an earlier launch left in the areas
+            if (P.pre_in1 >= 0 && tid < (P.ph[P.pre_in1].K >> 4)) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) bpre[j] = ch_ldcg4(ph.in1 + (size_t) tid * 16 + 4 * j);
+                for (int j = 0; j < 4; ++j) { const float4 v = ch_ldcg4(P.ph[P.pre_in1].in1 + (size_t) tid * 16 + 4 * j); hkeep[4 * j] = v.x; hkeep[4 * j + 1] = v.y; hkeep[4 * j + 2] = v.z; hkeep[4 * j + 3] = v.w; }
+            }
         }
-        // (1) the phase's input is complete: the previous kernel (phase 0), or every CTA's results of the phase before
-        if (p > 0) {
+        if (live && addp) {
+            if (ph.in1_kept || p == P.pre_in1) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) bpre[j] = make_float4(hkeep[4 * j], hkeep[4 * j + 1], hkeep[4 * j + 2], hkeep[4 * j + 3]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) bpre[j] = ch_ldcg4(ph.in1 + (size_t) tid * 16 + 4 * j);
+            }
+        }
+        // (1) CH_IN_BARRIER only: every CTA has stored and released the results of the phase before
+        if (ph.in_mode == CH_IN_BARRIER) {
             if (tid == 0) {
-                unsigned long long t0 = 0;
-                unsigned v, n = 0;
+                ch_watch w; unsigned v;
                 while (true) {
                     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(P.sync) : "memory");
                     if (v >= target) break;
-                    if ((++n & 0x3ffu) == 0) { const unsigned long long t = ch_now(); if (!t0) t0 = t; else if (t - t0 > CH_TIMEOUT_NS) ch_die(P.sync, 0x200u + p); }
+                    if (w.spin(P.sync, 0x200u + p)) break;
                 }
             }
             ch_bar_consumers();
         }
         CH_STAMP(1);
         // (2) this CTA's q8_1 image of the activation column
-        if (ph.prologue == B200_CHAIN_X_PLAIN) {
-            float4 v[4], nx[4];
-            int base = tid & ~31;
-            if (base < nu16) {
-#pragma unroll
-                for (int j = 0; j < 4; ++j) v[j] = base + lane < nu16 ? ch_ldcg4(ph.in0 + (size_t) (base + lane) * 16 + 4 * j) : make_float4(0.f, 0.f, 0.f, 0.f);
+        const uint8_t * llin = P.ll + (size_t) (p > 0 ? p - 1 : 0) * CH_LL_BYTES;
+        if (!normp && ph.in_mode == CH_IN_LL_Q8) {
+            // the SWIGLU phase before quantized its own 32-row blocks: 10 (word, tag) pairs per block (8 quant words, (d, s), pad)
+            const int nq16 = ph.nq8 >> 4;
+            for (int u = tid; u < nq16; u += CH_NT) {
+                const uint8_t * b = llin + (size_t) (u >> 1) * 80;
+                uint4 q0, q1, ds;
+                ch_watch w;
+                while (true) {
+                    q0 = ch_ll_load2(b + (u & 1) * 32); q1 = ch_ll_load2(b + (u & 1) * 32 + 16); ds = ch_ll_load2(b + 64);
+                    if (q0.y == tag && q0.w == tag && q1.y == tag && q1.w == tag && ds.y == tag) break;
+                    if (w.spin(P.sync, 0x400u + p)) break;
+                }
+                const float2 f = __half22float2(*(const __half2 *) &ds.x);
+                ch_store_unit(u, make_int4((int) q0.x, (int) q0.z, (int) q1.x, (int) q1.z), f.x, f.y, K, nblocks, ph.types, s_act);
             }
-            while (base < nu16) {
-                const int u = base + lane, nb = base + CH_NT;
-                if (nb < nu16) {
+            // its tail rows (not whole blocks per CTA) come as f32 pairs behind the block area: at most a few units, one warp
+            const int ntail16 = nu16 - nq16;
+            if (ntail16 > 0 && warp == CH_NW - 1) {
+                const uint8_t * tl = llin + (size_t) (ph.nq8 >> 5) * 80;
+                for (int u0 = 0; u0 < ntail16; u0 += 32) {
+                    const int u = u0 + lane; const bool on = u < ntail16;
+                    float f[16];
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) nx[j] = nb + lane < nu16 ? ch_ldcg4(ph.in0 + (size_t) (nb + lane) * 16 + 4 * j) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    for (int i = 0; i < 16; ++i) f[i] = 0.0f;
+                    if (on) {
+                        ch_watch w;
+                        while (true) {
+                            bool ok = true;
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) { const uint4 v = ch_ll_load2(tl + ((size_t) u * 16 + 2 * j) * 8); f[2 * j] = __uint_as_float(v.x); f[2 * j + 1] = __uint_as_float(v.z); ok = ok && v.y == tag && v.w == tag; }
+                            if (ok) break;
+                            if (w.spin(P.sync, 0x500u + p)) break;
+                        }
+                    }
+                    ch_quant_store(f, lane, nq16 + u, on, K, nblocks, ph.types, s_act);
                 }
-                const float f[16] = { v[0].x, v[0].y, v[0].z, v[0].w, v[1].x, v[1].y, v[1].z, v[1].w, v[2].x, v[2].y, v[2].z, v[2].w, v[3].x, v[3].y, v[3].z, v[3].w };
+            }
+        } else if (!normp) {
+            // plain column (from outside, after the barrier, or as (value, tag) pairs): double-buffered rounds of 16 values per thread
+            const bool pairs = ph.in_mode == CH_IN_LL_F32;
+            auto load16 = [&](int u, float (&f)[16]) {
+                if (!pairs) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) { const float4 v = ch_ldcg4(ph.in0 + (size_t) u * 16 + 4 * j); f[4 * j] = v.x; f[4 * j + 1] = v.y; f[4 * j + 2] = v.z; f[4 * j + 3] = v.w; }
+                } else {
+                    ch_watch w;
+                    while (true) {
+                        bool ok = true;
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) { const uint4 v = ch_ll_load2(llin + ((size_t) u * 16 + 2 * j) * 8); f[2 * j] = __uint_as_float(v.x); f[2 * j + 1] = __uint_as_float(v.z); ok = ok && v.y == tag && v.w == tag; }
+                        if (ok) break;
+                        if (w.spin(P.sync, 0x600u + p)) break;
+                    }
+                }
+            };
+            for (int base = tid & ~31; base < nu16; base += CH_NT) {
+                const int u = base + lane;
+                float f[16];
+#pragma unroll
+                for (int i = 0; i < 16; ++i) f[i] = 0.0f;
+                if (u < nu16) load16(u, f);
                 ch_quant_store(f, lane, u, u < nu16, K, nblocks, ph.types, s_act);
-                if (nb < nu16) {
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) v[j] = nx[j];
-                }
-                base = nb;
             }
         } else {
             // h = in0 (+ in1); n = h / sqrt(mean(h^2) + eps); x = n * normw.  K <= 16 * CH_NT: thread = one 16-value unit
-            const bool add = addp;
             float h[16], g[16];
+            if (live && ph.in_mode == CH_IN_LL_F32) {
+                ch_watch w;
+                while (true) {
+                    bool ok = true;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) { const uint4 v = ch_ll_load2(llin + ((size_t) tid * 16 + 2 * j) * 8); h[2 * j] = __uint_as_float(v.x); h[2 * j + 1] = __uint_as_float(v.z); ok = ok && v.y == tag && v.w == tag; }
+                    if (ok) break;
+                    if (w.spin(P.sync, 0x700u + p)) break;
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float4 a = live ? ch_ldcg4(ph.in0 + (size_t) tid * 16 + 4 * j) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    h[4 * j] = a.x; h[4 * j + 1] = a.y; h[4 * j + 2] = a.z; h[4 * j + 3] = a.w;
+                }
+            }
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-                const float4 gg = gpre[j];
-                if (live) {
-                    a = ch_ldcg4(ph.in0 + (size_t) tid * 16 + 4 * j);
-                    if (add) { const float4 b = ph.in1_early ? bpre[j] : ch_ldcg4(ph.in1 + (size_t) tid * 16 + 4 * j); a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w; }
-                }
-                h[4 * j] = a.x; h[4 * j + 1] = a.y; h[4 * j + 2] = a.z; h[4 * j + 3] = a.w;
-                g[4 * j] = gg.x; g[4 * j + 1] = gg.y; g[4 * j + 2] = gg.z; g[4 * j + 3] = gg.w;
+                if (!live) { h[4 * j] = h[4 * j + 1] = h[4 * j + 2] = h[4 * j + 3] = 0.0f; }
+                h[4 * j] += bpre[j].x; h[4 * j + 1] += bpre[j].y; h[4 * j + 2] += bpre[j].z; h[4 * j + 3] += bpre[j].w;   // (zeros without ADD)
+                g[4 * j] = gpre[j].x; g[4 * j + 1] = gpre[j].y; g[4 * j + 2] = gpre[j].z; g[4 * j + 3] = gpre[j].w;
             }
+            if (addp) {
+#pragma unroll
+                for (int i = 0; i < 16; ++i) hkeep[i] = h[i];
+            }
+            if (rec && p == 1 && h[0] == 12345.678f) rec[25] = 1;       // (measurement only: the loads have landed when the stamp below is taken)
+            if (rec && p == 1) rec[26] = ch_now();
             float ss = 0.0f;
 #pragma unroll
             for (int i = 0; i < 16; ++i) ss = fmaf(h[i], h[i], ss);
@@ -246,13 +426,14 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
             float tot = 0.0f;
 #pragma unroll
             for (int i = 0; i < CH_NW; ++i) tot += s_red[i];
+            if (rec && p == 1) rec[27] = ch_now();
             const float scale = rsqrtf(tot / (float) K + ph.eps);
             float x[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) x[i] = h[i] * scale;
             // the three nodes' values are stored once, each by another CTA
             if (live) {
-                if (add && ph.out_add && cta == 0) {
+                if (addp && ph.out_add && cta == 0) {
 #pragma unroll
                     for (int j = 0; j < 4; ++j) *(float4 *) (ph.out_add + (size_t) tid * 16 + 4 * j) = make_float4(h[4 * j], h[4 * j + 1], h[4 * j + 2], h[4 * j + 3]);
                 }
@@ -268,6 +449,7 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
                 for (int j = 0; j < 4; ++j) *(float4 *) (ph.out_mul + (size_t) tid * 16 + 4 * j) = make_float4(x[4 * j], x[4 * j + 1], x[4 * j + 2], x[4 * j + 3]);
             }
             ch_quant_store(x, lane, tid, live, K, nblocks, ph.types, s_act);
+            if (rec && p == 1) rec[28] = ch_now();
         }
         ch_bar_consumers();
         CH_STAMP(2);
@@ -275,8 +457,8 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
         if (p == P.nph - 1) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
         // (3) this warp's stages of the phase
-        int first = cta - ph.off; if (first < 0) first += G;
-        const int nunits_l = first < ph.nunits ? (ph.nunits - first + G - 1) / G : 0;
+        int f0 = cta - ph.off; if (f0 < 0) f0 += G;
+        const int ntl = ph.nunits - ph.ng8, nunits_l = ph.gpc * 8 + (f0 < ntl ? (ntl - f0 + G - 1) / G : 0);
         const int nst = total ? cum[p + 1] - cum[p] : 0;
         const uint32_t act4 = smem_u32(s_act), act6 = act4 + ((ph.types & 1) ? (uint32_t) gs_traits<B200_TYPE_Q4_K>::act_bytes(K) : 0u);
         // A ring slot always belongs to the same warp (slot % CH_NW), whatever the lap: a warp then meets the laps of a slot in order, and its
@@ -284,26 +466,32 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
         while (true) {
             const int s = my_lap * P.nslot + my_slot, sl = s - s_base;
             if (sl >= nst) break;
-            int sg, row, c, k; decode(ph, sl, sg, row, c, k);
-            const bool q6 = ph.seg[sg].q6 != 0;
+            const uint32_t e = s_tab[s];
+            const bool q6 = (e >> 21) & 1u;
+            const int c = (int) ((e >> 22) & 31u);
             ch_mbar_wait(full0 + 8 * my_slot, (uint32_t) my_lap & 1u, P.sync, 0x300u + p);
             if (P.trace && cta == 0 && lane == 0 && s < 1024) P.trace[32 * (1 + P.trace_cap) + s] = ch_now();   // (measurement only)
-            float acc[CH_R];
-#pragma unroll
-            for (int r = 0; r < CH_R; ++r) acc[r] = 0.0f;
             const uint32_t st = ring + my_slot * P.slot_bytes;
-            const int bl = lane & 7, gb = c * GS_CB + bl;
-            if (!(P.dbg & 1)) {
-                if (q6) gs_traits<B200_TYPE_Q6_K>::consume<CH_R, CH_R>(st, CH_Q6K_CHUNK, bl, gb, lane, act6, K, nblocks, acc);
-                else    gs_traits<B200_TYPE_Q4_K>::consume<CH_R, CH_R>(st, CH_Q4K_CHUNK, bl, gb, lane, act4, K, nblocks, acc);
+            float a0, a1;                              // this lane's sums of rows 2 (lane >> 4) + {0, 1}
+            if (q6) {
+                float acc[CH_R];
+#pragma unroll
+                for (int r = 0; r < CH_R; ++r) acc[r] = 0.0f;
+                const int bl = lane & 7, gb = c * GS_CB + bl;
+                if (!(P.dbg & 1)) gs_traits<B200_TYPE_Q6_K>::consume<CH_R, CH_R>(st, CH_Q6K_CHUNK, bl, gb, lane, act6, K, nblocks, acc);
+                // every lane has all four rows: halve the number of values a lane carries
+                const bool hi16 = lane & 16;
+                a0 = hi16 ? acc[2] : acc[0]; a1 = hi16 ? acc[3] : acc[1];
+                const float b0 = hi16 ? acc[0] : acc[2], b1 = hi16 ? acc[1] : acc[3];
+                a0 += __shfl_xor_sync(0xffffffffu, b0, 16); a1 += __shfl_xor_sync(0xffffffffu, b1, 16);   // lanes < 16: rows 0, 1; lanes >= 16: rows 2, 3
+            } else {
+                float acc[2] = { 0.0f, 0.0f };
+                if (!(P.dbg & 1)) ch_consume_q4k(st, lane, act4, K, nblocks, c, acc);
+                a0 = acc[0]; a1 = acc[1];
             }
             __syncwarp();                              // every lane is done reading the slot
             if (lane == 0 && s + P.nslot < total) issue(s + P.nslot, my_slot);
-            // 4 sums over 32 lanes in 6 shuffles: halve the number of values a lane carries, then a plain butterfly
-            const bool hi16 = lane & 16, hi8 = lane & 8;
-            float a0 = hi16 ? acc[2] : acc[0], b0 = hi16 ? acc[0] : acc[2];
-            float a1 = hi16 ? acc[3] : acc[1], b1 = hi16 ? acc[1] : acc[3];
-            a0 += __shfl_xor_sync(0xffffffffu, b0, 16); a1 += __shfl_xor_sync(0xffffffffu, b1, 16);   // lanes < 16: rows 0, 1; lanes >= 16: rows 2, 3
+            const bool hi8 = lane & 8;
             float a = hi8 ? a1 : a0, b = hi8 ? a0 : a1;
             a += __shfl_xor_sync(0xffffffffu, b, 8);                                                    // row = 2 * (lane >> 4) + ((lane >> 3) & 1)
             a += __shfl_xor_sync(0xffffffffu, a, 4); a += __shfl_xor_sync(0xffffffffu, a, 2); a += __shfl_xor_sync(0xffffffffu, a, 1);
@@ -315,38 +503,62 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
         ch_bar_consumers();
         CH_STAMP(3);
 
-        // (4) sum the K chunks of every row in chunk order, finish the node(s), publish
+        // (4) sum the K chunks of every row in chunk order, finish the node(s), publish for the next phase
+        uint8_t * llout = P.ll + (size_t) p * CH_LL_BYTES;
         if (ph.epilogue == B200_CHAIN_Y_SWIGLU) {
-            for (int t = tid; t < nunits_l * CH_R; t += CH_NT) {
+            auto row_of = [&](int t, float & gsum, float & usum) {       // local row t = 4 k + r
                 const int k = t / CH_R, r = t - k * CH_R;
-                float gsum = 0.0f, usum = 0.0f;
+                gsum = 0.0f; usum = 0.0f;
                 for (int c = 0; c < ph.nch; ++c) { gsum += s_psum[((2 * k) * ph.nch + c) * CH_R + r]; usum += s_psum[((2 * k + 1) * ph.nch + c) * CH_R + r]; }
-                const int row = (first + k * G) * CH_R + r;
-                ph.seg[0].dst[row] = gsum; ph.seg[1].dst[row] = usum;
-                ph.glu[row] = b200_swiglu1(gsum, usum);
+                return ch_unit(ph, k, f0, f0, G) * CH_R + r;
+            };
+            const int nrow_g = ph.out_mode == CH_IN_LL_Q8 ? ph.gpc * 32 : 0;
+            // the CTA's whole 32-row blocks: one warp per block, lane = row: gate, up, glu, and the block's q8_1 form for ffn_down
+            for (int b0 = warp * 32; b0 < nrow_g; b0 += CH_NT) {
+                float gsum, usum;
+                const int row = row_of(b0 + lane, gsum, usum);
+                const float v = b200_swiglu1(gsum, usum);
+                ph.seg[0].dst[row] = gsum; ph.seg[1].dst[row] = usum; ph.glu[row] = v;
+                int q, isum; float d;
+                q8_1_block<B200_Q8_1_X86>(v, q, d, isum);
+                unsigned wq = (unsigned) q & 0xffu;
+                wq |= __shfl_down_sync(0xffffffffu, wq, 1) << 8;
+                wq |= __shfl_down_sync(0xffffffffu, wq, 2) << 16;
+                uint8_t * blk = llout + (size_t) (row >> 5) * 80;         // (the warp's 32 rows are one aligned block)
+                if ((lane & 3) == 0) ch_ll_store(blk + (lane >> 2) * 8, wq, tag);
+                if (lane == 1) { const __half2 ds = q8_1_ds(d, isum); ch_ll_store(blk + 64, *(const unsigned *) &ds, tag); }
+            }
+            for (int t = nrow_g + tid; t < nunits_l * CH_R; t += CH_NT) {
+                float gsum, usum;
+                const int row = row_of(t, gsum, usum);
+                const float v = b200_swiglu1(gsum, usum);
+                ph.seg[0].dst[row] = gsum; ph.seg[1].dst[row] = usum; ph.glu[row] = v;
+                if (ph.out_mode == CH_IN_LL_F32) ch_ll_store(llout + (size_t) row * 8, __float_as_uint(v), tag);
+                else if (ph.out_mode == CH_IN_LL_Q8) ch_ll_store(llout + (size_t) (ph.ng8 * CH_R >> 5) * 80 + (size_t) (row - ph.ng8 * CH_R) * 8, __float_as_uint(v), tag);
             }
         } else {
             for (int t = tid; t < nunits_l * CH_R; t += CH_NT) {
                 const int k = t / CH_R, r = t - k * CH_R;
                 float sum = 0.0f;
                 for (int c = 0; c < ph.nch; ++c) sum += s_psum[(k * ph.nch + c) * CH_R + r];
-                int sg, row; ch_locate(ph, first + k * G, 0, sg, row);
+                int sg, row; ch_locate(ph, ch_unit(ph, k, f0, f0, G), sg, row);
                 ph.seg[sg].dst[row + r] = sum;
+                if (ph.out_mode == CH_IN_LL_F32) ch_ll_store(llout + (size_t) (row + r) * 8, __float_as_uint(sum), tag);   // (single-segment phases only)
             }
         }
-        if (p + 1 < P.nph) {
+        if (ph.out_mode == CH_IN_BARRIER) {
             ch_bar_consumers();                       // every thread's stores are ordered before thread 0's release (CTA barrier), whose
-            if (tid == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" :: "l"(P.sync) : "memory");   // release (cumulative over the barrier) makes them visible GPU-wide
+            if (tid == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" :: "l"(P.sync) : "memory");   // cumulativity makes them visible GPU-wide
             target += (unsigned) G;
         }
         CH_STAMP(4);
     }
-    // the last CTA to finish re-arms the counters for the next launch (every CTA has passed every wait by then)
+    // the last CTA to finish re-arms the counters and advances the epoch for the next launch (every CTA has passed every wait by then)
     if (P.nph > 1) {
         ch_bar_consumers();
         if (tid == 0) {
             const unsigned done = atomicAdd(P.sync + 1, 1u);
-            if (done == (unsigned) G - 1) { P.sync[0] = 0u; P.sync[1] = 0u; __threadfence(); }
+            if (done == (unsigned) G - 1) { P.sync[0] = 0u; P.sync[1] = 0u; P.sync[3] = tag; __threadfence(); }
         }
     }
 }
@@ -361,24 +573,35 @@ static bool ch_weight_ok(const b200_tensor * w) {
     if (w->type == B200_TYPE_Q6_K) return (w->flags & B200_TENSOR_REPACKED) && w->nb[0] == 210;
     return false;
 }
+static int64_t s_rows_max(const b200_chain_phase & s) { int64_t m = 0; for (int i = 0; i < s.n_w; ++i) m = s.w[i]->ne[1] > m ? s.w[i]->ne[1] : m; return m; }
+static bool ch_overlap(const void * a, size_t na, const b200_tensor * t) {
+    if (!a || !t) return false;
+    const char * a0 = (const char *) a, * b0 = (const char *) t->data;
+    return a0 < b0 + b200_tensor_span(t) && b0 < a0 + na;
+}
 
-// fills the kernel arguments; B200_ERR_UNSUPPORTED (with a reason) when the chain is not one this kernel takes
 typedef CUresult (*encode_tiled_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
                                     const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
                                     CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 encode_tiled_fn b200_get_encode_tiled();            // b200_gemm.cu
 
-static int ch_nw() { static int v = -1; if (v < 0) { const char * e = getenv("GGML_B200_CHAIN_WARPS"); v = e ? atoi(e) : 16; if (v != 16 && v != 24 && v != 28) v = 16; } return v; }
+static int ch_nw() { static int v = -1; if (v < 0) { const char * e = getenv("GGML_B200_CHAIN_WARPS"); v = e ? atoi(e) : 16; if (v != 16 && v != 24) v = 16; } return v; }
+// GGML_B200_CHAIN_HANDOVER=ll switches to the flag-in-data hand-over.  Default: the arrival counter.  Measured on Llama-3-8B layers (scripts/chain_bench.py
+// --trace): a poll of the data costs a full L2 round trip under the weight stream (~1.2 us) and the first one usually comes too early, so the
+// flag-in-data form (0.5 + 2.6 + 2.3 us per boundary) is no faster than release / acquire on one counter (1.5 + 1.3 + 2.0 us).
+static bool ch_force_barrier() { static int v = -1; if (v < 0) { const char * e = getenv("GGML_B200_CHAIN_HANDOVER"); v = !(e && e[0] == 'l'); } return v != 0; }
+
+// fills the kernel arguments; B200_ERR_UNSUPPORTED (with a reason) when the chain is not one this kernel takes
 static int ch_build(b200_ctx * ctx, const b200_chain_phase * phases, int n, ch_args & A, size_t & smem) {
-    const int nw = ch_nw();
     if (!phases || n < 1 || n > CH_MAXPH) { b200_set_error("decode_chain: 1..%d phases", CH_MAXPH); return B200_ERR_UNSUPPORTED; }
-    const int G = ctx->sm_count;
+    const int G = ctx->sm_count, nw = ch_nw();
     if (G < 3) { b200_set_error("decode_chain: needs at least 3 SMs"); return B200_ERR_UNSUPPORTED; }
     memset(&A, 0, sizeof(A));
     A.nph = n;
     int off = 0, slot = 0, act = 0, nmaps = 0;
     encode_tiled_fn encode = b200_get_encode_tiled();
     if (!encode) { b200_set_error("decode_chain: cuTensorMapEncodeTiled not available from the driver"); return B200_ERR_UNSUPPORTED; }
+    // ---- pass 1: shapes, weights, tensor maps
     for (int p = 0; p < n; ++p) {
         const b200_chain_phase & s = phases[p];
         ch_phase & d = A.ph[p];
@@ -423,28 +646,83 @@ static int ch_build(b200_ctx * ctx, const b200_chain_phase * phases, int n, ch_a
                 b200_set_error("decode_chain: phase %d: norm prologue wants aligned f32 columns of K <= %d", p, 16 * 32 * nw); return B200_ERR_UNSUPPORTED;
             }
             d.in1 = add ? (const float *) s.in1->data : nullptr; d.normw = (const float *) s.normw->data;
-            d.in1_early = 1;
-            if (add && p > 0) {
-                const b200_chain_phase & q = phases[p - 1];
-                const b200_tensor * outs[7] = { q.dst[0], q.n_w > 1 ? q.dst[1] : nullptr, q.n_w > 2 ? q.dst[2] : nullptr, q.out_add, q.out_norm, q.out_mul, q.glu };
-                const char * a0 = (const char *) s.in1->data, * a1 = a0 + K * 4;
-                for (const b200_tensor * o : outs) if (o) { const char * b0 = (const char *) o->data, * b1 = b0 + b200_tensor_span(o); if (a0 < b1 && b0 < a1) d.in1_early = 0; }
-            }
             d.out_add = add && s.out_add ? (float *) s.out_add->data : nullptr;
             d.out_norm = s.out_norm ? (float *) s.out_norm->data : nullptr; d.out_mul = s.out_mul ? (float *) s.out_mul->data : nullptr;
         } else if (s.prologue != B200_CHAIN_X_PLAIN) { b200_set_error("decode_chain: phase %d: unknown prologue %d", p, s.prologue); return B200_ERR_UNSUPPORTED; }
-        d.off = off;
-        off = (off + d.nunits) % G;
-        const int tpu = s.epilogue == B200_CHAIN_Y_SWIGLU ? 2 : 1;
-        const int stages_max = ((d.nunits + G - 1) / G) * tpu * d.nch;
-        if (stages_max * CH_R > CH_PSUM || stages_max >= 4096) { b200_set_error("decode_chain: phase %d: %d stages per CTA exceed the partial-sum table", p, stages_max); return B200_ERR_UNSUPPORTED; }
         int a = 0;
         if (d.types & 1) a += (int) gs_traits<B200_TYPE_Q4_K>::act_bytes((int) K);
         if (d.types & 2) a += (int) gs_traits<B200_TYPE_Q6_K>::act_bytes((int) K);
         act = max(act, a);
     }
+    // ---- pass 2: how every phase gets its inputs.  The flag-in-data hand-over needs in0 to be exactly what the phase before publishes
+    // (its single result column, or its glu) and in1 to come from outside or from the last residual sum (kept in registers); anything
+    // else that was written earlier in this launch forces the fence-and-counter form for the whole chain.
+    bool ll = !ch_force_barrier();
+    int last_add = -1;
+    A.pre_in1 = -1;
+    for (int p = 0; p < n; ++p) {
+        const b200_chain_phase & s = phases[p];
+        ch_phase & d = A.ph[p];
+        const size_t kb = (size_t) d.K * 4;
+        d.in_mode = CH_IN_EXTERNAL; d.in1_kept = 0;
+        bool in1_inside = false;
+        for (int q = 0; q < p; ++q) {
+            const b200_chain_phase & e = phases[q];
+            const b200_tensor * outs[7] = { e.dst[0], e.n_w > 1 ? e.dst[1] : nullptr, e.n_w > 2 ? e.dst[2] : nullptr, e.out_add, e.out_norm, e.out_mul, e.glu };
+            for (int o = 0; o < 7; ++o) {
+                if (!outs[o]) continue;
+                if (ch_overlap(s.in0->data, kb, outs[o])) {
+                    const bool direct = q == p - 1 && s.in0->data == outs[o]->data &&
+                                        ((o == 0 && e.n_w == 1 && e.epilogue == B200_CHAIN_Y_PLAIN) || (o == 6 && e.epilogue == B200_CHAIN_Y_SWIGLU));
+                    d.in_mode = CH_IN_BARRIER;
+                    if (direct && ll) d.in_mode = (o == 6 && s.prologue == B200_CHAIN_X_PLAIN && d.K % 32 == 0) ? CH_IN_LL_Q8 : CH_IN_LL_F32;
+                    else ll = false;
+                }
+                if (d.in1 && ch_overlap(s.in1->data, kb, outs[o])) {
+                    if (o == 3 && q == last_add && s.in1->data == outs[o]->data && phases[q].w[0]->ne[0] == d.K) d.in1_kept = 1;
+                    else { ll = false; in1_inside = true; }
+                }
+                if (q < p - 1 && s.normw && ch_overlap(s.normw->data, kb, outs[o])) ll = false;
+            }
+        }
+        if (s.prologue == B200_CHAIN_X_ADD_NORM_MUL) {
+            if (last_add < 0 && !in1_inside && !d.in1_kept) A.pre_in1 = p;        // the chain's first ADD, addend from outside: fetched at the start
+            last_add = p;
+        }
+    }
+    for (int p = 0; p < n; ++p) {
+        ch_phase & d = A.ph[p];
+        if (!ll && d.in_mode != CH_IN_EXTERNAL) d.in_mode = CH_IN_BARRIER;
+        if (p > 0) A.ph[p - 1].out_mode = d.in_mode == CH_IN_EXTERNAL ? (ll ? CH_IN_EXTERNAL : CH_IN_BARRIER) : d.in_mode;
+    }
+    if (!ll) {
+        for (int p = 0; p + 1 < n; ++p) A.ph[p].out_mode = CH_IN_BARRIER;             // one counter for the whole launch: every boundary arrives
+        for (int p = 1; p < n; ++p) {
+            A.ph[p].in_mode = CH_IN_BARRIER;
+        }
+    }
+    // ---- pass 3: who owns which rows
+    int stages_total = 0;
+    for (int p = 0; p < n; ++p) {
+        ch_phase & d = A.ph[p];
+        d.ng8 = 0; d.gpc = 0;
+        if (d.out_mode == CH_IN_LL_Q8) {
+            d.gpc = (d.nunits / 8) / G;               // whole 32-row blocks per CTA; the remainder goes round-robin
+            d.ng8 = d.gpc * G * 8;
+            A.ph[p + 1].nq8 = d.ng8 * CH_R;
+        }
+        d.off = off;
+        off = (off + d.nunits - d.ng8) % G;
+        const int tpu = d.epilogue == B200_CHAIN_Y_SWIGLU ? 2 : 1;
+        const int stages_max = (d.gpc * 8 + (d.nunits - d.ng8 + G - 1) / G) * tpu * d.nch;
+        if (stages_max * CH_R > CH_PSUM || stages_max >= 4096) { b200_set_error("decode_chain: phase %d: %d stages per CTA exceed the partial-sum table", p, stages_max); return B200_ERR_UNSUPPORTED; }
+        stages_total += stages_max;
+        if (d.nch > 31 || s_rows_max(phases[p]) >= (1 << 18)) { b200_set_error("decode_chain: phase %d: matrix too large for the stage table", p); return B200_ERR_UNSUPPORTED; }
+        if ((size_t) d.K * 8 > CH_LL_BYTES) { b200_set_error("decode_chain: phase %d: K = %d exceeds the hand-over area", p, d.K); return B200_ERR_UNSUPPORTED; }
+    }
+    if (stages_total > CH_MAXST) { b200_set_error("decode_chain: %d stages per CTA exceed the stage table", stages_total); return B200_ERR_UNSUPPORTED; }
     act = (act + 127) & ~127;
-    const size_t fixed = (size_t) act + CH_PSUM * 4 + 32 * 4, smem_max = 227 * 1024;
+    const size_t fixed = (size_t) act + CH_PSUM * 4 + 32 * 4 + CH_MAXST * 4, smem_max = 227 * 1024;
     int nslot = (int) ((smem_max - fixed) / ((size_t) slot + 8));
     if (nslot > 255) nslot = 255;
     { static int cap = -1; if (cap < 0) { const char * e = getenv("GGML_B200_CHAIN_SLOTS"); cap = e ? atoi(e) : 0; } if (cap > 0 && nslot > cap) nslot = cap; }
@@ -452,6 +730,20 @@ static int ch_build(b200_ctx * ctx, const b200_chain_phase * phases, int n, ch_a
     A.slot_bytes = slot; A.nslot = nslot; A.act_bytes = act;
     smem = (size_t) nslot * slot + fixed + (size_t) nslot * 8;
     return B200_OK;
+}
+
+// 0, or the code of the first wait that ran out in a chain launched on this context (0x100 ring slot, 0x200 arrival counter, 0x300 stage,
+// 0x400-0x700 hand-over polls; + phase); synchronizes.  A nonzero code means the results of that launch are garbage.
+extern "C" int b200_decode_chain_error(b200_ctx * ctx) {
+    if (!ctx || !ctx->scratch[7]) return 0;
+    unsigned w[8] = {};
+    if (cudaSetDevice(ctx->device) != cudaSuccess || cudaStreamSynchronize(ctx->stream) != cudaSuccess ||
+        cudaMemcpy(w, ctx->scratch[7], sizeof(w), cudaMemcpyDeviceToHost) != cudaSuccess) { cudaGetLastError(); return -1; }
+    if (w[2] || w[4]) {                                  // re-arm for the next launch
+        cudaMemset(ctx->scratch[7], 0, 256);
+        b200_set_error("decode_chain: a wait timed out (code 0x%x)", w[2]);
+    }
+    return (int) w[2];
 }
 
 extern "C" int b200_decode_chain_supported(b200_ctx * ctx, const b200_chain_phase * phases, int n_phases) {
@@ -467,12 +759,13 @@ extern "C" int b200_decode_chain(b200_ctx * ctx, const b200_chain_phase * phases
     size_t smem;
     int rc = ch_build(ctx, phases, n_phases, A, smem);
     if (rc != B200_OK) return rc;
-    // the arrival counters: scratch slot 7, zeroed when it is (re)allocated, re-armed by the kernel itself
-    const bool fresh = ctx->scratch[7] == nullptr;
-    unsigned * sync = (unsigned *) b200_scratch(ctx, 7, 256);
-    if (!sync) return B200_ERR_ALLOC;
-    if (fresh) B200_CUDA_TRY(cudaMemsetAsync(sync, 0, 256, ctx->stream));
-    A.sync = sync;
+    // counters + hand-over areas: scratch slot 7, zeroed when it is (re)allocated; the kernel re-arms the counters and advances the epoch itself
+    const size_t sbytes = 256 + (size_t) CH_MAXPH * CH_LL_BYTES;
+    const bool fresh = ctx->scratch[7] == nullptr || ctx->scratch_size[7] < sbytes;
+    uint8_t * sc = (uint8_t *) b200_scratch(ctx, 7, sbytes);
+    if (!sc) return B200_ERR_ALLOC;
+    if (fresh) B200_CUDA_TRY(cudaMemsetAsync(sc, 0, sbytes, ctx->stream));
+    A.sync = (unsigned *) sc; A.ll = sc + 256;
     A.trace = ctx->trace; A.trace_cap = ctx->trace_cap;
     { static int dbg = -1; if (dbg < 0) { const char * e = getenv("GGML_B200_CHAIN_DBG"); dbg = e ? atoi(e) : 0; } A.dbg = dbg; }
     const int nw = ch_nw();
@@ -480,7 +773,6 @@ extern "C" int b200_decode_chain(b200_ctx * ctx, const b200_chain_phase * phases
     if (!attr_done[ctx->device & 63]) {
         B200_CUDA_TRY(cudaFuncSetAttribute(k_decode_chain<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         B200_CUDA_TRY(cudaFuncSetAttribute(k_decode_chain<24>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        B200_CUDA_TRY(cudaFuncSetAttribute(k_decode_chain<28>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_done[ctx->device & 63] = true;
     }
     cudaLaunchConfig_t cfg = {};
@@ -492,9 +784,8 @@ extern "C" int b200_decode_chain(b200_ctx * ctx, const b200_chain_phase * phases
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = ctx->pdl ? 1 : 0;
-    if (nw == 28)      B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_decode_chain<28>, A));
-    else if (nw == 24) B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_decode_chain<24>, A));
-    else               B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_decode_chain<16>, A));
+    if (nw == 24) B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_decode_chain<24>, A));
+    else          B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_decode_chain<16>, A));
     for (int p = 0; p < n_phases; ++p) {
         const b200_chain_phase & s = phases[p];
         for (int i = 0; i < s.n_w; ++i) b200_note_write(ctx, s.dst[i]->data, b200_tensor_span(s.dst[i]));

@@ -70,7 +70,7 @@ def lib():
         "b200_quantize_q8_1": (i, [vp, vp, sz, vp, i64, i64, i]),
         "b200_mul_mat": (i, [vp, tp, tp, tp]), "b200_mul_mat_noalloc": (i, [vp, tp, tp, tp]), "b200_noalloc_scratch_bytes": (sz, []),
         "b200_mul_mat_multi": (i, [vp, C.POINTER(tp), i, tp, C.POINTER(tp)]),
-        "b200_decode_chain": (i, [vp, C.POINTER(ChainPhase), i]), "b200_decode_chain_supported": (i, [vp, C.POINTER(ChainPhase), i]),
+        "b200_decode_chain": (i, [vp, C.POINTER(ChainPhase), i]), "b200_decode_chain_supported": (i, [vp, C.POINTER(ChainPhase), i]), "b200_decode_chain_error": (i, [vp]),
         "b200_mul_mat_gate_up_swiglu": (i, [vp, tp, tp, tp, tp, tp, tp]),
         "b200_repack_supported": (i, [i, i64]), "b200_repack": (i, [vp, i, vp, i64, i64, sz]), "b200_unrepack": (i, [vp, i, vp, i64, i64, sz]), "b200_mul_mat_id": (i, [vp, tp, tp, tp, tp]),
         "b200_flash_attn_ext": (i, [vp, tp, tp, tp, tp, tp, tp, f, f, f]),
@@ -330,6 +330,10 @@ class Context:
         """b200_decode_chain: the dependent MUL_MAT groups of one token between two attention operators as ONE persistent kernel"""
         arr, _keep = program
         _check(lib().b200_decode_chain(self.h, arr, len(arr)), "decode_chain")
+
+    def decode_chain_error(self):
+        """0, or the code of the first bounded wait that ran out inside a chain kernel since the last call (synchronizes)"""
+        return lib().b200_decode_chain_error(self.h)
 
     def decode_chain_supported(self, program):
         arr, _keep = program

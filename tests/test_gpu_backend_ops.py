@@ -124,7 +124,10 @@ def test_layer_fusions_bit_identical(vtype):
     os.makedirs(OUT, exist_ok=True)
     subprocess.check_call(["g++", "-std=c++17", "-O1", "-I" + os.path.join(ROOT, "include"), os.path.join(ROOT, "tests", "fusion_probe.cpp"), "-o", exe, "-ldl"])
     outs = []
-    for tag, extra in (("fused", {"GGML_B200_GRAPH_STATS": "1"}), ("plain", {"GGML_B200_NO_FUSE": "1", "GGML_B200_GRAPHS": "0"})):
+    # "fused": every fusion but the persistent decode chain (bit-identical to node by node); "chain": the chain too (its GEMV sums in another
+    # order: compared within 1e-6 NMSE per dump); "plain": node by node
+    for tag, extra in (("fused", {"GGML_B200_GRAPH_STATS": "1", "GGML_B200_NO_CHAIN": "1"}), ("plain", {"GGML_B200_NO_FUSE": "1", "GGML_B200_GRAPHS": "0"}),
+                       ("chain", {"GGML_B200_GRAPH_STATS": "1"})):
         f = os.path.join(OUT, f"fusion_probe_{vtype}_{tag}.bin")
         p = subprocess.run([exe, PLUGIN, f, str(vtype)], env=dict(os.environ, **extra), stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
         assert p.returncode == 0 and "fusion_probe: OK" in p.stdout, p.stdout[-2000:]
@@ -135,8 +138,18 @@ def test_layer_fusions_bit_identical(vtype):
             assert abs(iq - ik) == 1 or vtype == 12, order                  # equal weight types side by side
             assert "gate+up+glu 2" in p.stdout and "rope/set_rows 4" in p.stdout and "add+norm+mul 4" in p.stdout, p.stdout   # every fusion fired (2 node walks)
             assert "1 recorded, 4 replayed" in p.stdout, p.stdout           # first run launch by launch, second recorded, four graph launches
+        if tag == "chain":
+            assert "decode chains 2" in p.stdout, p.stdout                  # ffn_gate / ffn_up / SwiGLU / ffn_down went out as one kernel (2 node walks)
         outs.append(open(f, "rb").read())
         os.remove(f)
-    assert len(outs[0]) == len(outs[1]) and len(outs[0]) > 0
+    assert len(outs[0]) == len(outs[1]) == len(outs[2]) and len(outs[0]) > 0
     assert outs[0] == outs[1]
+    # the dump is f32 node outputs and two f16 caches; the chain only touches f32 columns, the rest stays bit-identical
+    import numpy as np
+    a32, c32 = np.frombuffer(outs[1], dtype=np.float32), np.frombuffer(outs[2], dtype=np.float32)
+    same = a32.view(np.uint32) == c32.view(np.uint32)
+    diff = ~same
+    assert diff.sum() > 0                                                   # (it really ran another kernel)
+    ref = a32[diff].astype(np.float64); got = c32[diff].astype(np.float64)
+    assert np.isfinite(got).all() and ((ref - got) ** 2).sum() / (ref ** 2).sum() < 1e-6
 

@@ -85,6 +85,7 @@ def test_decode_chain_vs_oracle(ctx, B, orc, t_v, t_down):
         lc.set_inputs(attn_out, inp_sa)
         lc.clear_outputs()
         lc.run()
+        assert ctx.decode_chain_error() == 0
         got = lc.outputs()
         exact = host_layer(orc, W, types, dims, attn_out, inp_sa, norm_ffn, norm_attn, 1e-5, O.ACT_Q8_1)
         for name in lc.OUTPUTS:
@@ -112,6 +113,7 @@ def test_decode_chain_llama8b_shapes_vs_node_by_node(ctx, B):
     lc.clear_outputs()
     for _ in range(3):
         lc.run()
+    assert ctx.decode_chain_error() == 0
     got = lc.outputs()
     # node by node: the device matmuls on the chain's own intermediate columns (each checks one phase in isolation)
     def mm(name, x_t, M):
