@@ -77,12 +77,12 @@ def wbytes(t, K, M):
 def random_blocks(rng, t, nblocks):
     raw = rng.integers(0, 256, size=(nblocks, TSIZE[t]), dtype=np.uint8)
     if t == Q4_K:
-        raw[:, 0:2] = (rng.uniform(0.1, 1, nblocks) * 2e-3).astype(np.float16).view(np.uint8).reshape(nblocks, 2)
-        raw[:, 2:4] = (rng.uniform(0.1, 1, nblocks) * 2e-3).astype(np.float16).view(np.uint8).reshape(nblocks, 2)
+        raw[:, 0:2] = (rng.uniform(0.1, 1, nblocks) * 4e-4).astype(np.float16).view(np.uint8).reshape(nblocks, 2)
+        raw[:, 2:4] = (rng.uniform(0.1, 1, nblocks) * 4e-4).astype(np.float16).view(np.uint8).reshape(nblocks, 2)
     elif t in (Q4_0, Q8_0):
         raw[:, 0:2] = (rng.uniform(-1, 1, nblocks) * (2e-3 if t == Q4_0 else 2e-4)).astype(np.float16).view(np.uint8).reshape(nblocks, 2)
     else:
-        raw[:, 208:210] = (rng.uniform(-1, 1, nblocks) * 1e-3).astype(np.float16).view(np.uint8).reshape(nblocks, 2)
+        raw[:, 208:210] = (rng.uniform(-1, 1, nblocks) * 2e-4).astype(np.float16).view(np.uint8).reshape(nblocks, 2)
     return raw.reshape(-1)
 
 
@@ -134,16 +134,21 @@ class HotPathModel:
     """The hot-path nodes of one llama decode/prefill step over device-resident random-init Q4_K_M weights.
     rank/world: split-mode=row shard (rows [lo, hi) of every weight); world == 1 is the whole model."""
 
-    def __init__(self, B, ctx, cfg, n_tokens, depth, rank=0, world=1, seed=1234, alloc=None, dist=None, quant="q4_k_m"):
+    def __init__(self, B, ctx, cfg, n_tokens, depth, rank=0, world=1, seed=1234, alloc=None, dist=None, quant="q4_k_m", chain=True):
         self.B, self.ctx, self.cfg, self.N = B, ctx, cfg, n_tokens
         self.quant = quant
         self.moe = cfg.get("n_expert", 0)
+        self.replicas = 1
         if self.moe and world > 1:
-            raise SystemExit("MUL_MAT_ID does not shard (the reference asserts against split buffers, ggml-cuda.cu:2274): replicas only")
+            # MUL_MAT_ID does not shard (the reference asserts against split buffers, ggml-cuda.cu:2274): every rank runs its own replica
+            # of the whole model on its own token stream (SURVEY 8(e): "replicas / layer split first"); no data-path collective
+            self.replicas, world, rank, dist = world, 1, 0, None
         self.rank, self.world = rank, world
         from row_split import RowSplit                      # partition rule + gather shared with tests/test_row_split_gloo.py
         self.rs = RowSplit(dist, world, rank, 32)
-        rng = np.random.default_rng(seed + rank)
+        # row split: every rank draws the SAME stream, builds the same virtual full-size weights and keeps rows [lo, hi) of each; the activations
+        # are replicated.  (Replicas of a MoE model are independent jobs: their own streams.)
+        rng = np.random.default_rng(seed + (rank if self.replicas > 1 else 0))
         types, out_type = q4_k_m_layer_types(cfg, quant)
         shapes = weight_shapes(cfg)
         used = {t for lt in types for t in lt.values()} | {out_type}
@@ -155,11 +160,16 @@ class HotPathModel:
             ml = hi - lo
             w = ctx.empty(t, [K, ml] if ne == 1 else [K, ml, ne])
             nb, blk = w.nbytes, TSIZE[t]
+            full = wbytes(t, K, M) * ne           # the unsplit weight; this rank keeps bytes [a, b) of it
+            a = wbytes(t, K, lo) if ne == 1 else 0
+            b = a + nb
             off = 0
-            while off < nb:                       # tile the random pool at random block-aligned offsets
+            while off < full:                     # tile the random pool at random block-aligned offsets
                 start = int(rng.integers(0, pool[t].size // blk // 2)) * blk
-                n = min(nb - off, pool[t].size - start)
-                ctx.h2d(w.ptr + off, pool[t][start:start + n])
+                n = min(full - off, pool[t].size - start)
+                x0, x1 = max(off, a), min(off + n, b)
+                if x0 < x1:
+                    ctx.h2d(w.ptr + (x0 - a), pool[t][start + (x0 - off): start + (x1 - off)])
                 off += n
             self.weight_bytes += nb if ne == 1 else nb * cfg["n_expert_used"] // ne
             ctx.repack(w)                         # load-time repack (q6_K -> 16-byte aligned group layout), as set_tensor does
@@ -215,6 +225,40 @@ class HotPathModel:
         self.kv_bytes_per_layer = 2 * self.n_kv * kvd * 2
         ctx.synchronize()
         self.gather = None          # set by the multi-GPU driver: gather(full_tensor, lo, hi) after a sharded matmul
+        self.chains = None
+        if chain and N == 1 and world == 1 and not self.moe and not os.environ.get("B200_BENCH_NO_CHAIN"):
+            self._build_chains(rng)
+
+    def _build_chains(self, rng):
+        """One b200_decode_chain program per layer: everything between two attention operators of the llama graph (src/models/llama.cpp:40-130)
+        -- wo, +residual, ffn_norm, ffn_gate / ffn_up, SwiGLU, ffn_down, +ffn_inp, attn_norm of the next layer, its wq / wk / wv (the last
+        layer: output_norm and the output head) -- with the data really flowing from node to node.  None when the kernel declines the model
+        (other weight types): then the matmuls go out one launch per group as before."""
+        B, ctx, cfg = self.B, self.ctx, self.cfg
+        e, f = cfg["n_embd"], cfg["n_ff"]
+        col = lambda n: ctx.empty(F32, [n])
+        normw = lambda: ctx.upload(F32, [e], rng.uniform(0.5, 1.5, e).astype(np.float32))
+        self.resid = [col(e), col(e)]                       # l_out of layer il - 1 / il (ping-pong); resid[0] starts as the token's embedding row
+        ctx.h2d(self.resid[0].ptr, rng.standard_normal(e).astype(np.float32))
+        self.ffn_inp = col(e)
+        q1, k1, v1 = (t.view([t.ne[0], 1, 1, 1], [4, t.ne[0] * 4, t.ne[0] * 4, t.ne[0] * 4]) for t in (self.q, self.k, self.v))
+        cols = {n: getattr(self, n).view([getattr(self, n).ne[0], 1, 1, 1], [4] + [getattr(self, n).ne[0] * 4] * 3) for n in ("attn", "o", "g", "u", "ff", "d", "logits")}
+        chains = []
+        for il, L in enumerate(self.layers):
+            last = il == len(self.layers) - 1
+            tail_w = [self.output[0]] if last else [self.layers[il + 1][n][0] for n in ("wq", "wk", "wv")]
+            tail_d = [cols["logits"]] if last else [q1, k1, v1]
+            ph = [dict(w=[L["wo"][0]], dst=[cols["o"]], in0=cols["attn"]),
+                  dict(w=[L["gate"][0], L["up"][0]], dst=[cols["g"], cols["u"]], glu=cols["ff"], epilogue=B.Y_SWIGLU, prologue=B.X_ADD_NORM_MUL, eps=1e-5,
+                       in0=cols["o"], in1=self.resid[il % 2], normw=normw(), out_add=self.ffn_inp),
+                  dict(w=[L["down"][0]], dst=[cols["d"]], in0=cols["ff"]),
+                  dict(w=tail_w, dst=tail_d, prologue=B.X_ADD_NORM_MUL, eps=1e-5, in0=cols["d"], in1=self.ffn_inp, normw=normw(), out_add=self.resid[(il + 1) % 2])]
+            prog = ctx.chain_program(ph)
+            if not ctx.decode_chain_supported(prog):
+                return
+            chains.append(prog)
+        self.chains = chains
+        self._keep = (q1, k1, v1, cols)
 
     def _mm(self, w, x, dst):
         wt, lo, hi = w
@@ -251,6 +295,17 @@ class HotPathModel:
     def step(self, attention=True):
         """issue every MUL_MAT and FLASH_ATTN_EXT node of one llama graph evaluation on the ctx stream"""
         c = self.ctx
+        if self.chains is not None:
+            # the persistent decode chain: wq / wk / wv of layer 0, then per layer FLASH_ATTN_EXT + ONE kernel for everything up to the next
+            # layer's wq / wk / wv (the last one ends with the output head)
+            L0 = self.layers[0]
+            c.note_write(self.x)
+            self._mm_group([L0["wq"], L0["wk"], L0["wv"]], self.x, [self.q, self.k, self.v])
+            for il in range(len(self.layers)):
+                if attention:
+                    c.flash_attn_ext(self.qview, self.kviews[il], self.vviews[il], self.mask, None, self.attn4, self.scale)
+                c.decode_chain(self.chains[il])
+            return
         fuse = True      # wq/wk/wv and gate/up share src1: one launch per run of equal weight types (GEMV at n=1, GEMM at n=512)
         # In the real graph every matmul input is rewritten by the glue op in front of it (RMS_NORM, attention, SwiGLU), so its cached
         # q8_1 / bf16 image is stale each time.  The synthetic step reuses fixed input buffers: drop the cache at every point where the
@@ -294,15 +349,15 @@ class HotPathModel:
 
 
 def traffic_per_launch(algorithmic_bytes_per_launch):
-    """DRAM bytes per launch of the dominant kernel: dram__bytes_read.sum + dram__bytes_write.sum of the committed
-    `ncu --set full` capture (profiles/*_traffic.json) relative to the algorithmic bytes of the same launches, applied to
-    this run's per-launch algorithmic bytes.  None when no capture is committed."""
+    """(DRAM bytes per launch of the dominant kernel, where the figure comes from).  It is NOT a live counter: ncu cannot run inside the
+    timed region, so the ratio dram__bytes_read.sum + dram__bytes_write.sum over algorithmic bytes of the newest committed `ncu --set full`
+    capture (profiles/*_traffic.json) is applied to this run's algorithmic bytes per launch.  (None, why) when no capture is committed."""
     try:
         cands = sorted(f for f in os.listdir(os.path.join(ROOT, "profiles")) if f.endswith("_traffic.json"))
         d = json.load(open(os.path.join(ROOT, "profiles", cands[-1])))
-        return algorithmic_bytes_per_launch * float(d["traffic_over_algorithmic"])
-    except Exception:
-        return None
+        return algorithmic_bytes_per_launch * float(d["traffic_over_algorithmic"]), f"profiles/{cands[-1]} ratio {float(d['traffic_over_algorithmic']):.4f} (ncu --set full of {d.get('kernel', 'the decode GEMV')}) x this run's algorithmic bytes; not measured live"
+    except Exception as ex:
+        return None, f"no committed capture ({type(ex).__name__})"
 
 
 # ------------------------------------------------------------------------------------------------------------
@@ -320,8 +375,15 @@ def cpu_baseline(cfg, depth, budget_s=20.0, steps=5, warmup=3, quant="q4_k_m"):
         raise RuntimeError("no CPU baseline for the MUL_MAT_ID workload in this harness")
     types, out_type = q4_k_m_layer_types(cfg, quant)
     n_kv = ((depth + 1 + 255) // 256) * 256
-    if O.have_reference():
-        ref = O.Reference()
+    isa = "avx2"
+    try:
+        flags = open("/proc/cpuinfo").read()
+        if all(n in flags for n in ("avx512f", "avx512_vnni", "avx512_bf16", "avx512vbmi", "avx_vnni")) and O.have_reference("avx512"):
+            isa = "avx512"                                  # the same reference sources compiled for the host's AVX-512 VNNI/BF16 (oracle/Makefile ISA=avx512)
+    except OSError:
+        pass
+    if O.have_reference(isa):
+        ref = O.Reference(isa)
         ops = {}
 
         def mm(t, K, M):
@@ -363,7 +425,7 @@ def cpu_baseline(cfg, depth, budget_s=20.0, steps=5, warmup=3, quant="q4_k_m"):
         for op in list(ops.values()) + [fa]:
             op.free()
         return 1e6 / total_us, "reference", cores, (f"one layer of each of the {len(variants)} {quant.upper()} tensor-type variants (7 MUL_MAT + FLASH_ATTN_EXT, n=1, "
-                                                    f"n_kv={n_kv}) + output head on ggml-cpu (oracle/_ref, OpenMP, {cores} threads), mean of {done} timed steps after {max(warmup, 1)} warm-up, x{cfg['n_layer']} layers")
+                                                    f"n_kv={n_kv}) + output head on ggml-cpu (oracle/_ref/{isa}, OpenMP, {cores} threads), mean of {done} timed steps after {max(warmup, 1)} warm-up, x{cfg['n_layer']} layers")
     # port: the scalar oracle on one core, one q4_K ffn_down GEMV, scaled by bytes
     orc = O.Oracle()
     K, M = shapes["down"]
@@ -375,20 +437,44 @@ def cpu_baseline(cfg, depth, budget_s=20.0, steps=5, warmup=3, quant="q4_k_m"):
     return 1.0 / (dt * total_bytes / w.nbytes), "port", 1, f"scalar oracle, q4_K {M}x{K} GEMV on 1 core scaled by weight bytes"
 
 
+def metric_name(cfg, quant):
+    return f"tg128 tok/s, {pretty(cfg)} {quant.upper()} (llama-bench tg128: one decode token per step)"
+
+
+def bench_config(cfg, args):
+    """what both arms run -- kept identical so the driver can compare the lines"""
+    n_kv = ((args.depth + 1 + 255) // 256) * 256
+    return {"workload": f"{cfg['name']}-{args.quant} tg128: one decode token per step (llama-bench -n 128 -fa 1), random-init GGUF weights",
+            "tensor_types": "Q4_K_M mix: q4_K, q6_K on attn_v/ffn_down of half the layers, q6_K output" if args.quant == "q4_k_m" else args.quant + " weights",
+            "depth": args.depth, "n_kv": n_kv}
+
+
 def run_reference(args):
+    """the reference's own CPU implementation on this box's host cores: its llama-bench binary with -ngl 0 (oracle/_ref, compiled in place; the
+    AVX-512 build when the host runs it), else a sampled layer of ggml-cpu graphs through oracle/ref_driver.c"""
     cfg = MODELS[args.model]
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     t0 = time.time()
-    tps, kind, cores, sample = cpu_baseline(cfg, args.depth, budget_s=150.0, steps=args.steps, warmup=args.warmup, quant=args.quant)
-    line = {"impl": "reference", "metric": f"tg128 tok/s (llama-bench, {pretty(cfg)} {args.quant.upper()})", "value": tps, "unit": "tok/s", "n_gpus": args.gpus,
+    args.lb_reps = 2
+    lb = llama_bench_through_plugin(args, budget_s=400, ngl=0) if not cfg.get("n_expert") or True else {"unavailable": "-"}
+    extra = {}
+    if "tg128" in lb:
+        tps, kind, cores = lb["tg128"]["value"], "reference", lb["threads"]
+        sample = f"{lb['command']}: 128 generated tokens x 2 repetitions after llama-bench's own warm-up run, {lb['build']}, {cores} threads"
+        extra = {"llama_bench": lb}
+    else:
+        tps, kind, cores, sample = cpu_baseline(cfg, args.depth, budget_s=150.0, steps=args.steps, warmup=args.warmup, quant=args.quant)
+        extra = {"llama_bench": lb}
+    line = {"impl": "reference", "metric": metric_name(cfg, args.quant), "value": tps, "unit": "tok/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / tps, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "int8 dot / f32 accumulate (q8_0, q8_K activations)", "data": "synthetic",
-            "config": {"workload": f"{cfg['name']}-{args.quant} tg128 decode hot path (MUL_MAT + FLASH_ATTN_EXT nodes)", "depth": args.depth},
+            "config": bench_config(cfg, args),
             "cpu_baseline": {"value": tps, "unit": "tok/s", "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": tps, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "wall_s": time.time() - t0}
+    line.update(extra)
     print(json.dumps(line), flush=True)
 
 
@@ -413,13 +499,14 @@ def run_b200(args):
 
     keep = []
     peer = None
+    replicas = world if (cfg.get("n_expert") and world > 1) else 1       # MUL_MAT_ID does not shard: N independent replicas, no data-path collective
     use_nccl = bool(os.environ.get("B200_BENCH_NCCL"))     # baseline: torch.distributed all-gather after every sharded matmul
-    if world > 1 and not use_nccl:
+    if world > 1 and not use_nccl and replicas == 1:
         from row_split import PeerExchange                   # the product: all-gather fused into the GEMV epilogue over NVLink peer memory
         peer = PeerExchange(ctx, dist, world, rank, 64 << 20)
 
     def alloc(t, ne):
-        if world == 1:
+        if world == 1 or replicas > 1:
             return ctx.empty(t, ne)
         if peer is not None:
             return peer.alloc(t, ne)
@@ -431,7 +518,7 @@ def run_b200(args):
 
     tg = HotPathModel(B, ctx, cfg, 1, args.depth, rank, world, alloc=alloc, dist=dist, quant=args.quant)
     tg.peer = peer
-    if world > 1 and peer is None:
+    if world > 1 and peer is None and replicas == 1:
         ext = torch.cuda.ExternalStream(ctx.stream, device=f"cuda:{local}")
 
         def gather(full, M, N):
@@ -468,7 +555,7 @@ def run_b200(args):
             t = torch.tensor([ms], device=f"cuda:{local}"); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms = float(t.item())
         return ms / steps, graph, ctx.launches - n0
 
-    use_graph = (world == 1 or peer is not None) and not args.no_graph     # the peer exchange is all device-side: it captures
+    use_graph = (world == 1 or peer is not None or replicas > 1) and not args.no_graph     # the peer exchange is all device-side: it captures
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -505,7 +592,7 @@ def run_b200(args):
     def mm_only():
         tg.step(attention=False)
     gemv_ms_step = None
-    if world == 1:
+    if use_graph:                                           # (every rank replays its own graph; with the peer exchange they meet inside the kernels)
         mm_only(); ctx.synchronize()
         l0 = ctx.launches_by_kind()
         ctx.graph_begin(); mm_only(); g2 = ctx.graph_end()
@@ -519,6 +606,10 @@ def run_b200(args):
             ctx.graph_launch(g2)
         ctx.record(e1)
         gemv_ms_step = ctx.elapsed_ms(e0, e1) / 10
+        if dist:
+            t = torch.tensor([gemv_ms_step], device=f"cuda:{local}"); dist.all_reduce(t, op=dist.ReduceOp.MAX); gemv_ms_step = float(t.item())
+    roof_how = "CUDA events around 10 replays of a graph holding only the MUL_MAT kernels of one token (max over ranks)" if use_graph else \
+               "sum of the per-launch CUDA-event brackets of the MUL_MAT kernels, 3 eager steps (no graph in this mode: launch gaps excluded)"
     ctx.profile(True)
     for _ in range(3):
         tg.step()
@@ -528,33 +619,78 @@ def run_b200(args):
         gemv_ms_step = (prof.get("gemv", (0.0, 0))[0] + prof.get("gemv_id", (0.0, 0))[0]) / 3
         gemv_n, other_n = (prof.get("gemv", (0.0, 0))[1] + prof.get("gemv_id", (0.0, 0))[1]) // 3, 0
     shapes = weight_shapes(cfg)
-    act_bytes = sum(K * 4 + M * 4 for lt in tg.layers for (K, M) in [shapes[n] for n in shapes]) // max(world, 1)   # (MoE: x2 on the expert tensors, < 0.1 % of the bytes)
+    act_bytes = sum(K * 4 + M * 4 for lt in tg.layers for (K, M) in [shapes[n] for n in shapes]) // max(tg.world, 1)   # (MoE: x2 on the expert tensors, < 0.1 % of the bytes)
     gemv_bytes_step = tg.weight_bytes + act_bytes
     achieved = gemv_bytes_step / (gemv_ms_step * 1e-3) / 1e9 if gemv_ms_step > 0 else 0.0
 
+    # ---- row split only: the gathered results of one step must be the unsplit ones.  Every rank runs the step once more; all ranks must hold
+    # identical columns; rank 0 builds the same model unsplit (same stream of random blocks), runs the same step and compares every matmul
+    # result of the last layer and the logits word for word.
+    split_check = None
+    if world > 1 and replicas == 1:
+        import hashlib
+        names = ("q", "k", "v", "o", "g", "u", "d", "logits")
+        tg.step(); ctx.synchronize()
+        mine = {n: ctx.download(getattr(tg, n)).reshape(-1).copy() for n in names}
+        digest = hashlib.sha1(b"".join(mine[n].tobytes() for n in names)).hexdigest()
+        digests = [None] * world
+        dist.all_gather_object(digests, digest)
+        ok = [len(set(digests)) == 1]
+        if rank == 0:
+            one = HotPathModel(B, ctx, cfg, 1, args.depth, 0, 1, quant=args.quant, chain=False)
+            one.step(); ctx.synchronize()
+            whole = {n: ctx.download(getattr(one, n)).reshape(-1).copy() for n in names}
+            del one
+            diff = {n: int((whole[n].view(np.uint32) != mine[n].view(np.uint32)).sum()) for n in names}
+            err = {n: float(((whole[n].astype(np.float64) - mine[n]) ** 2).sum() / max((whole[n].astype(np.float64) ** 2).sum(), 1e-300)) for n in names}
+            # (the unsplit model may pick another GEMV kernel for a shape than the sharded one does: a different summation order, a few last-bit
+            # differences; anything beyond that is a wrong or missing row)
+            ok[0] = ok[0] and max(err.values()) < 1e-9 and all(np.isfinite(mine[n]).all() for n in names)
+            split_check = {"ranks_identical": len(set(digests)) == 1, "nmse_vs_unsplit_max": max(err.values()), "words_differing_from_unsplit": diff,
+                           "exchange_error": int(ctx.exchange_error(peer.ex)) if peer is not None else 0}
+        dist.broadcast_object_list(ok, src=0)
+        if not ok[0]:
+            if rank == 0:
+                print(json.dumps({"error": "row-split results differ from the unsplit model", "split_check": split_check}), file=sys.stderr, flush=True)
+            dist.barrier(); dist.destroy_process_group()
+            sys.exit(1)
+
     result = None
     if rank == 0:
-        tps = 1e3 / ms_tg
-        total_bytes = tg.weight_bytes * world + tg.kv_bytes_per_layer * cfg["n_layer"]
+        tps = replicas * 1e3 / ms_tg
+        total_bytes = tg.weight_bytes * (world if replicas == 1 else 1) + tg.kv_bytes_per_layer * cfg["n_layer"]
+        chain = tg.chains is not None
+        kernel_name = ("k_decode_chain: one persistent kernel per layer for wo, +residual, ffn_norm, ffn_gate / ffn_up, SwiGLU, ffn_down, +ffn_inp, attn_norm, wq / wk / wv "
+                       "(TMA tensor requests into one shared-memory ring, dp4a dots, q8_1 quantization and the glue in the phase prologues)") if chain else \
+                      "decode dequant-GEMV with fused q8_1 quantization: k_gemv_q4k_mma (raw q4_K, TMA boxes + int8 mma.sync) and k_gemv_stream (q6_K / long-row q4_K, TMA-streamed dp4a)"
+        traffic, traffic_src = traffic_per_launch(gemv_bytes_step / max(gemv_n, 1))
         result = {
-            "metric": f"tg128 tok/s (llama-bench, {pretty(cfg)} {args.quant.upper()})", "value": tps, "unit": "tok/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms_tg, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "int8 dot (mma.sync / dp4a) with f32 accumulate over q8_1 activations; f16 KV, f32 softmax", "data": "synthetic",
-            "config": {"workload": f"{cfg['name']}-{args.quant} tg128: all MUL_MAT{'_ID' if cfg.get('n_expert') else ''} + FLASH_ATTN_EXT nodes of one decode token ({cfg['n_layer']} layers + output head); glue ops not included",
-                       "tensor_types": "Q4_K_M mix: q4_K, q6_K on attn_v/ffn_down of half the layers, q6_K output" if args.quant == "q4_k_m" else args.quant + " weights", "depth": args.depth, "n_kv": tg.n_kv,
-                       "parallelism": (f"row-split tp{world}, all-gather " + ("fused into the GEMV epilogue (NVLink peer stores)" if peer is not None else "by NCCL")) if world > 1 else "single GPU", "cuda_graph": bool(graph),
-                       "l2": f"weights {tg.weight_bytes * world / 1e9:.1f} GB >> 126 MB L2, streamed once per step"},
-            "hbm_bytes_per_step": total_bytes, "hbm_frac_whole_step": total_bytes / world / (ms_tg * 1e-3) / 1e9 / hbm_gbs,
-            "roofline": {"kernel": "decode dequant-GEMV with fused q8_1 quantization: k_gemv_q4k_mma (raw q4_K, TMA boxes + int8 mma.sync) and k_gemv_stream (q6_K / long-row q4_K, TMA-streamed dp4a)", "bound": "hbm", "achieved": achieved, "peak": hbm_gbs, "unit": "GB/s",
-                         "frac": achieved / hbm_gbs, "traffic": traffic_per_launch(gemv_bytes_step / max(gemv_n, 1)), "algorithmic_bytes_per_launch": gemv_bytes_step / max(gemv_n, 1), "peak_source": f"{peak_src} (MEASURED_PEAKS.json hbm_gbs)",
+            # BASELINE.json's metric is llama-bench tg128 / pp512.  `value` is the device-resident form of tg128 (the hot path of one token as a CUDA
+            # graph, inputs in HBM); `e2e` is the reference's llama-bench itself through the plugin (host token ids in, host logits out) when its
+            # binary is present, else the flat C-ABI with host buffers; llama_bench_tg128 / llama_bench_pp512 carry the tool's own figures
+            "metric": metric_name(cfg, args.quant), "value": tps, "unit": "tok/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_tg, "higher_is_better": True, "scaling": "weak" if replicas > 1 else "strong", "vs_baseline": None,
+            "dtype": "int8 dot (dp4a / mma.sync) with f32 accumulate over q8_1 activations; f16 KV, f32 softmax", "data": "synthetic",
+            "config": dict(bench_config(cfg, args), **({} if world == 1 else {"parallelism": (f"{replicas} independent replicas (MUL_MAT_ID does not shard, ggml-cuda.cu:2274), no collective" if replicas > 1 else
+                                       f"row-split tp{world}, all-gather " + ("fused into the GEMV epilogue (NVLink peer stores)" if peer is not None else "by NCCL"))})),
+            "value_is": f"every MUL_MAT{'_ID' if cfg.get('n_expert') else ''} and FLASH_ATTN_EXT node of one decode token ({cfg['n_layer']} layers + output head) through the flat C-ABI, one CUDA graph, inputs resident in HBM" +
+                        ("; the ADD / RMS_NORM / MUL / SwiGLU nodes between them run inside the chain kernel; ROPE, KV-cache writes and the embedding lookup are only in e2e" if chain else "; glue ops only in e2e"),
+            "cuda_graph": bool(graph), "l2": f"weights {tg.weight_bytes * (world if replicas == 1 else 1) / 1e9:.1f} GB >> 126 MB L2, streamed once per step: no flush needed",
+            "hbm_bytes_per_step": total_bytes, "hbm_frac_whole_step": total_bytes / (world if replicas == 1 else 1) / (ms_tg * 1e-3) / 1e9 / hbm_gbs,
+            "roofline": {"kernel": kernel_name, "bound": "hbm", "achieved": achieved, "peak": hbm_gbs, "unit": "GB/s",
+                         "frac": achieved / hbm_gbs, "traffic": traffic, "traffic_source": traffic_src, "algorithmic_bytes_per_launch": gemv_bytes_step / max(gemv_n, 1),
+                         "peak_source": f"{peak_src} (MEASURED_PEAKS.json hbm_gbs: a COPY, half reads half writes; read-only streams reach 7.1-7.3 TB/s on this part, profiles/r2_membw_ceilings.txt)",
                          "launches_per_step": gemv_n, "other_launches_in_timed_graph": other_n, "ms_per_step": gemv_ms_step,
-                         "algorithmic_bytes_per_step": gemv_bytes_step,
-                         "how": "CUDA events around 10 replays of a graph holding only the MUL_MAT nodes of one token"},
+                         "algorithmic_bytes_per_step": gemv_bytes_step, "how": roof_how},
             "kernel_ms_per_step_event_bracketed": {k: v[0] / 3 for k, v in prof.items()},
-            "e2e": {"value": 1e3 / e2e_ms, "unit": "tok/s", "h2d_bytes_per_step": e * 4, "d2h_bytes_per_step": cfg["n_vocab"] * 4, "ms_per_step": e2e_ms},
+            "e2e": {"value": replicas * 1e3 / e2e_ms, "unit": "tok/s", "h2d_bytes_per_step": e * 4, "d2h_bytes_per_step": cfg["n_vocab"] * 4, "ms_per_step": e2e_ms,
+                    "how": "flat C-ABI (b200_*), pinned H2D of the embedding row + graph replay + D2H of the logits + sync per token"},
             "gpu_launches": launches_per_step * args.steps, "gpu_launches_per_step": launches_per_step, "clocks": clocks,
         }
+        if split_check is not None:
+            result["split_check"] = split_check
     # ---- secondary: pp512 (prefill) on one GPU
+    tg_weight_bytes, tg_kv_bytes = tg.weight_bytes, tg.kv_bytes_per_layer * cfg["n_layer"]
     if world == 1 and not args.no_pp:
         del tg
         pp = HotPathModel(B, ctx, cfg, 512, args.depth, quant=args.quant)
@@ -574,36 +710,72 @@ def run_b200(args):
                 result["cpu_baseline"] = {"value": v, "unit": "tok/s", "cores": cores, "kind": kind, "sample": sample}
             except Exception as ex:                      # the baseline is a reported number, never a reason to lose the GPU line
                 result["cpu_baseline"] = {"value": None, "unit": "tok/s", "cores": os.cpu_count(), "kind": "unavailable", "sample": repr(ex)}
-        if world == 1 and not args.no_llama_bench:
-            result["llama_bench"] = llama_bench_through_plugin(args)
+        if not args.no_llama_bench:
+            # the tool BASELINE.json's metric is named after, through the plugin, pinned to this rank's GPU
+            lb = llama_bench_through_plugin(args, device=local)
+            result["llama_bench"] = lb
+            if "tg128" in lb:
+                result["llama_bench_tg128"] = {"value": lb["tg128"]["value"], "stddev": lb["tg128"]["stddev"], "unit": "tok/s", "n_gpus": 1,
+                                               "roofline_frac": lb["tg128"]["value"] * (tg_weight_bytes + tg_kv_bytes) / 1e9 / hbm_gbs,
+                                               "note": "whole llama graph (hot ops + ROPE, KV writes, embedding, sampling sync) by the reference's llama-bench through GGML_BACKEND_PATH; frac = (weight + KV-cache bytes one token reads) x tok/s / measured HBM copy peak"}
+                if world == 1:
+                    result["e2e_flat_api"] = result["e2e"]
+                    result["e2e"] = {"value": lb["tg128"]["value"], "unit": "tok/s", "h2d_bytes_per_step": 4, "d2h_bytes_per_step": cfg["n_vocab"] * 4, "ms_per_step": 1e3 / lb["tg128"]["value"],
+                                     "how": "the reference's own llama-bench (-n 128 -fa 1 -ngl 99) through the plugin: host token id in, graph_compute, logits to host, sync per token"}
+            if "pp512" in lb:
+                fl = 2.0 * 512 * sum(K * M for (K, M) in weight_shapes(cfg).values()) * cfg["n_layer"]
+                result["llama_bench_pp512"] = {"value": lb["pp512"]["value"], "stddev": lb["pp512"]["stddev"], "unit": "tok/s", "n_gpus": 1,
+                                               "roofline_frac": fl / (512.0 / lb["pp512"]["value"]) / 1e12 / tf_sust, "note": "matmul flops of a 512-token ubatch / its whole time / sustained bf16 peak"}
         print(json.dumps(result), flush=True)
     if dist:
         dist.barrier(); dist.destroy_process_group()
 
 
-def llama_bench_through_plugin(args, budget_s=420):
+def ref_build_dir():
+    """oracle/_ref/<isa>: the AVX-512 build of the reference when this host runs it (the boxes have AVX-512 VNNI / BF16), else the AVX2 one"""
+    try:
+        flags = open("/proc/cpuinfo").read()
+    except OSError:
+        flags = ""
+    for isa, need in (("avx512", ("avx512f", "avx512_vnni", "avx512_bf16", "avx512vbmi", "avx_vnni")), ("avx2", ())):
+        d = os.path.join(ROOT, "oracle", "_ref", isa)
+        if all(n in flags for n in need) and os.path.exists(os.path.join(d, "llama-bench")):
+            return d, isa
+    return os.path.join(ROOT, "oracle", "_ref", "avx2"), "avx2"
+
+
+def llama_bench_through_plugin(args, budget_s=420, device=0, ngl=99):
     """Supporting evidence beside the hot-path numbers: the reference's OWN llama-bench binary (oracle/_ref/avx2/llama-bench, compiled
     in place from the unmodified reference by `make -C oracle llama`; nothing of /root/reference is read at run time) on a random-block
     GGUF of the same model (scripts/make_gguf.py), with libggml-b200.so loaded through GGML_BACKEND_PATH -- every node of the llama graph
     (hot ops + glue ops) runs on the device.  Absent binary or any failure -> {"unavailable": why}; never fatal."""
     import subprocess, tempfile, time
-    lb = os.path.join(ROOT, "oracle", "_ref", "avx2", "llama-bench")
+    refdir, isa = ref_build_dir() if ngl == 0 else (os.path.join(ROOT, "oracle", "_ref", "avx2"), "avx2")
+    lb = os.path.join(refdir, "llama-bench")
     plugin = os.path.join(ROOT, "super-llama.cpp_b200", "libggml-b200.so")
     if not os.path.exists(lb):
         return {"unavailable": "oracle/_ref/avx2/llama-bench not built (make -C oracle llama, needs the reference sources at build time)"}
-    if args.model not in ("8b", "tinyllama"):
-        return {"unavailable": f"scripts/make_gguf.py writes 8b and tinyllama only, not {args.model}"}
+    if args.model not in ("8b", "tinyllama", "70b", "mixtral"):
+        return {"unavailable": f"scripts/make_gguf.py does not write {args.model}"}
     t0 = time.time()
     gguf = os.path.join(tempfile.gettempdir(), f"b200-bench-{args.model}-{args.quant}-{os.getpid()}.gguf")
     try:
         subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "make_gguf.py"), "--model", args.model, "--quant", args.quant, "-o", gguf],
                        check=True, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, timeout=budget_s / 2)
-        cmd = [lb, "-m", gguf, "-p", "512", "-n", "128", "-r", "3", "-fa", "1", "-ngl", "99", "-t", str(os.cpu_count() or 1), "-o", "json"] + (["-d", str(args.depth)] if args.depth else [])
-        p = subprocess.run(cmd, env=dict(os.environ, GGML_BACKEND_PATH=plugin), stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=max(30, budget_s - (time.time() - t0)))
+        cmd = [lb, "-m", gguf, "-p", "512", "-n", "128", "-r", str(getattr(args, "lb_reps", 3)), "-fa", "1", "-ngl", str(ngl), "-t", str(os.cpu_count() or 1), "-o", "json"] + (["-d", str(args.depth)] if args.depth else [])
+        env = dict(os.environ)
+        if ngl:
+            # one device only: llama-bench would otherwise spread the layers over every visible GPU (-sm layer)
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            env.update(GGML_BACKEND_PATH=plugin, CUDA_VISIBLE_DEVICES=(vis.split(",")[device] if vis else str(device)))
+        else:
+            env.pop("GGML_BACKEND_PATH", None)
+        p = subprocess.run(cmd, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=max(30, budget_s - (time.time() - t0)))
         rows = json.loads(p.stdout[p.stdout.index("["):])
-        if "B200" not in str(rows[0].get("backends")):
+        if ngl and "B200" not in str(rows[0].get("backends")):
             return {"unavailable": f"llama-bench did not pick the plugin up (backends: {rows[0].get('backends')})"}
-        out = {"command": " ".join(cmd[:1] + ["-m", "<random-block GGUF>"] + cmd[3:]), "backend": rows[0].get("backends"), "model": rows[0].get("model_type"), "data": "random GGUF blocks, no_vocab tokenizer, random token ids"}
+        out = {"command": " ".join(cmd[:1] + ["-m", "<random-block GGUF>"] + cmd[3:]), "backend": rows[0].get("backends"), "model": rows[0].get("model_type"), "data": "random GGUF blocks, no_vocab tokenizer, random token ids",
+               "build": f"oracle/_ref/{isa} (the reference compiled in place, {'AVX-512 VNNI/BF16' if isa == 'avx512' else 'x86-64-v3'})", "threads": os.cpu_count() or 1}
         for r in rows:
             name = f"pp{r['n_prompt']}" if r.get("n_prompt") else f"tg{r['n_gen']}"
             out[name] = {"value": r["avg_ts"], "stddev": r["stddev_ts"], "unit": "tok/s"}

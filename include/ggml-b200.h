@@ -179,6 +179,22 @@ B200_API int b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const b2
                                  const b200_tensor * v, const b200_tensor * mask, const b200_tensor * sinks,
                                  b200_tensor * dst, float scale, float max_bias, float logit_softcap);
 
+// The same operator over a PAGED KV cache (intended semantics: src/llama-kv-cache-paged.cpp:137-196 -- a layer's cache is a set of
+// fixed-size pages of `page_size` consecutive positions, allocated on demand, not one contiguous buffer).  k / v describe the page POOL:
+// data = first row of physical page 0, nb[1] = stride between consecutive token rows inside the pool, nb[2] = head stride, ne[1] = n_kv
+// (the LOGICAL number of keys attended).  Logical key t lives in pool row table[t / page_tokens] * page_tokens + t % page_tokens.
+// Query batches of at most 8 tokens (the decode kernels); larger batches: B200_ERR_UNSUPPORTED.  table == identity gives exactly
+// b200_flash_attn_ext's result (same kernels, same order of operations).
+typedef struct b200_kv_pages {
+    const int32_t * table;        // device array [n_pages]: logical page -> physical page of the pool
+    int32_t         n_pages;      // >= ceil(n_kv / page_tokens)
+    int32_t         page_tokens;  // power of two, >= 16
+    int64_t         pool_tokens;  // token rows the pool holds (bounds for the TMA descriptors)
+} b200_kv_pages;
+B200_API int b200_flash_attn_ext_paged(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v,
+                                       const b200_kv_pages * pages, const b200_tensor * mask, const b200_tensor * sinks,
+                                       b200_tensor * dst, float scale, float max_bias, float logit_softcap);
+
 // ---- load-time weight repack (DESIGN.md "HBM layout"): in place, size- and stride-preserving, exactly invertible ------
 // q6_K rows whose length is a multiple of 2048 are permuted per group of 8 blocks into a 16-byte aligned field-major
 // layout; the caller then sets B200_TENSOR_REPACKED in b200_tensor.flags.  Other types are consumed in GGUF layout.

@@ -43,7 +43,7 @@ def blocks(rng, t, K, M):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--model", default="tinyllama", choices=["tinyllama", "8b"])
+    ap.add_argument("--model", default="tinyllama", choices=["tinyllama", "8b", "70b", "mixtral"])
     ap.add_argument("--quant", default="q4_0", choices=["q4_0", "q8_0", "q4_k_m"])
     ap.add_argument("--layers", type=int, default=0, help="override the layer count (smoke runs)")
     ap.add_argument("-o", "--out", required=True)
@@ -57,10 +57,13 @@ def main():
     rng = np.random.default_rng(1234)
     w = gguf.GGUFWriter(a.out, "llama")
     w.add_name(f"{cfg['name']}-random-{a.quant}")
-    w.add_context_length(8192 if a.model == "8b" else 2048)
+    w.add_context_length(2048 if a.model == "tinyllama" else 8192)
     w.add_embedding_length(e); w.add_block_count(nl); w.add_feed_forward_length(f)
     w.add_head_count(nh); w.add_head_count_kv(nkv); w.add_rope_dimension_count(hd)
-    w.add_layer_norm_rms_eps(1e-5); w.add_rope_freq_base(500000.0 if a.model == "8b" else 10000.0)
+    w.add_layer_norm_rms_eps(1e-5); w.add_rope_freq_base(10000.0 if a.model == "tinyllama" else 1e6 if a.model == "mixtral" else 500000.0)
+    ne = cfg.get("n_expert", 0)
+    if ne:                                                 # LLM_ARCH_LLAMA with experts = Mixtral (src/models/llama.cpp:100-137: build_moe_ffn)
+        w.add_expert_count(ne); w.add_expert_used_count(cfg["n_expert_used"])
     w.add_vocab_size(nv)
     w.add_file_type({"q4_0": 2, "q8_0": 7, "q4_k_m": 15}[a.quant])                                 # LLAMA_FTYPE_MOSTLY_*
     w.add_tokenizer_model("no_vocab")
@@ -68,6 +71,9 @@ def main():
 
     def q(name, t, K, M):
         w.add_tensor(name, blocks(rng, t, K, M), raw_dtype=QTYPE[t])
+
+    def q3(name, t, K, M, n):                              # stacked expert matrices [K, M, n_expert]
+        w.add_tensor(name, np.stack([blocks(rng, t, K, M) for _ in range(n)]), raw_dtype=QTYPE[t])
 
     def norm(name, n):
         w.add_tensor(name, np.ones(n, dtype=np.float32))
@@ -79,7 +85,11 @@ def main():
         q(p + "attn_q.weight", lt["wq"], e, e); q(p + "attn_k.weight", lt["wk"], e, kvd); q(p + "attn_v.weight", lt["wv"], e, kvd)
         q(p + "attn_output.weight", lt["wo"], e, e)
         norm(p + "ffn_norm.weight", e)
-        q(p + "ffn_gate.weight", lt["gate"], e, f); q(p + "ffn_up.weight", lt["up"], e, f); q(p + "ffn_down.weight", lt["down"], f, e)
+        if ne:
+            w.add_tensor(p + "ffn_gate_inp.weight", (rng.standard_normal((ne, e)) / np.sqrt(e)).astype(np.float32))      # the router, f32 as llama-quantize leaves it
+            q3(p + "ffn_gate_exps.weight", lt["gate"], e, f, ne); q3(p + "ffn_up_exps.weight", lt["up"], e, f, ne); q3(p + "ffn_down_exps.weight", lt["down"], f, e, ne)
+        else:
+            q(p + "ffn_gate.weight", lt["gate"], e, f); q(p + "ffn_up.weight", lt["up"], e, f); q(p + "ffn_down.weight", lt["down"], f, e)
     norm("output_norm.weight", e)
     q("output.weight", out_type, e, nv)
     w.write_header_to_file(); w.write_kv_data_to_file(); w.write_tensors_to_file(); w.close()

@@ -497,6 +497,34 @@ extern "C" int b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const 
     return rc;
 }
 
+extern "C" int b200_flash_attn_ext_paged(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_kv_pages * pages,
+                                         const b200_tensor * mask, const b200_tensor * sinks, b200_tensor * dst, float scale, float max_bias, float logit_softcap) {
+    if (!ctx || !q || !k || !v || !dst || !pages || !pages->table) { b200_set_error("flash_attn_ext_paged: null argument"); return B200_ERR_INVALID; }
+    B200_CUDA_TRY(cudaSetDevice(ctx->device));
+    const int64_t DK = k->ne[0], DV = v->ne[0], KV = k->ne[1];
+    const int pt = pages->page_tokens;
+    if (pt < 16 || (pt & (pt - 1)) || pages->n_pages < 0 || (int64_t) pages->n_pages * pt < KV || pages->pool_tokens < pt) {
+        b200_set_error("flash_attn_ext_paged: page_tokens %d (power of two >= 16), n_pages %d, pool_tokens %lld do not cover %lld keys", pt, pages->n_pages,
+                       (long long) pages->pool_tokens, (long long) KV);
+        return B200_ERR_INVALID;
+    }
+    if (q->ne[0] != DK || v->ne[1] != KV || dst->ne[0] != DV || dst->ne[1] != q->ne[2] || dst->ne[2] != q->ne[1] || dst->ne[3] != q->ne[3] ||
+        k->ne[2] <= 0 || q->ne[2] % k->ne[2] != 0 || q->ne[2] % v->ne[2] != 0 || k->ne[3] != 1 || v->ne[3] != 1) {
+        b200_set_error("flash_attn_ext_paged: shape mismatch"); return B200_ERR_INVALID;
+    }
+    if (q->type != B200_TYPE_F32 || k->type != B200_TYPE_F16 || v->type != B200_TYPE_F16 || dst->type != B200_TYPE_F32 || (mask && mask->type != B200_TYPE_F16) ||
+        q->nb[0] != 4 || k->nb[0] != 2 || v->nb[0] != 2 || dst->nb[0] != 4) {
+        b200_set_error("flash_attn_ext_paged: types outside the hot path"); return B200_ERR_UNSUPPORTED;
+    }
+    if (mask && (mask->ne[0] < KV || mask->ne[1] < q->ne[1])) { b200_set_error("flash_attn_ext_paged: mask too small"); return B200_ERR_INVALID; }
+    int rc = B200_ERR_UNSUPPORTED;
+    if (b200_fattn_gqa_supported(q, k, v, mask, dst)) rc = b200_launch_fattn_gqa(ctx, q, k, v, mask, sinks, dst, scale, max_bias, logit_softcap, pages);
+    if (rc == B200_ERR_UNSUPPORTED && b200_fattn_dec_supported(q, k, v)) rc = b200_launch_fattn_dec(ctx, q, k, v, mask, sinks, dst, scale, max_bias, logit_softcap, pages);
+    if (rc == B200_ERR_UNSUPPORTED) b200_set_error("flash_attn_ext_paged: only query batches of <= 8 tokens with f16 K/V of head size 64 / 128 / 256");
+    b200_note_write(ctx, dst->data, b200_tensor_span(dst));
+    return rc;
+}
+
 // ---- row split helper: ggml-cuda.cu:777-803 semantics -----------------------------------------
 extern "C" int b200_split_row_range(int64_t nrows, const float * tensor_split, int world, int rank, int64_t rounding,
                                     int64_t * row_low, int64_t * row_high) {

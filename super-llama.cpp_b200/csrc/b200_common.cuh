@@ -314,10 +314,11 @@ int b200_launch_fattn_vec(b200_ctx * ctx, const b200_tensor * q, const b200_tens
 bool b200_fattn_dec_supported(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v);
 int  b200_launch_fattn_dec(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v,
                            const b200_tensor * mask, const b200_tensor * sinks, b200_tensor * dst,
-                           float scale, float max_bias, float softcap);
+                           float scale, float max_bias, float softcap, const b200_kv_pages * pages = nullptr);
 bool b200_fattn_gqa_supported(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask, const b200_tensor * dst);
 int  b200_launch_fattn_gqa(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v,
-                           const b200_tensor * mask, const b200_tensor * sinks, b200_tensor * dst, float scale, float max_bias, float softcap);
+                           const b200_tensor * mask, const b200_tensor * sinks, b200_tensor * dst, float scale, float max_bias, float softcap,
+                           const b200_kv_pages * pages = nullptr);
 bool b200_fattn_tc_supported(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v, const b200_tensor * mask, const b200_tensor * dst);
 int  b200_launch_fattn_tc(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v,
                           const b200_tensor * mask, const b200_tensor * sinks, b200_tensor * dst,

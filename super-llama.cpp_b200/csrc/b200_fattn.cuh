@@ -14,6 +14,7 @@ struct fattn_args {
     int64_t N, H, KV;
     int64_t rk2, rk3, rv2, rv3;                    // broadcast ratios
     float scale, max_bias, softcap, m0, m1; uint32_t n_head_log2;
+    const int32_t * pages; int page_shift;         // paged KV cache (b200_flash_attn_ext_paged): logical page -> physical page; NULL = contiguous
 };
 
 
@@ -36,7 +37,18 @@ static inline void fattn_fill_args(fattn_args & p, const b200_tensor * q, const 
     p.n_head_log2 = 1u << (uint32_t) floorf(log2f((float) p.H));
     p.m0 = powf(2.0f, -(max_bias) / p.n_head_log2);
     p.m1 = powf(2.0f, -(max_bias / 2.0f) / p.n_head_log2);
+    p.pages = nullptr; p.page_shift = 0;
+}
+static inline void fattn_set_pages(fattn_args & p, const b200_kv_pages * pg) {
+    if (!pg) return;
+    p.pages = pg->table; p.page_shift = 0;
+    while ((1 << p.page_shift) < pg->page_tokens) ++p.page_shift;
+}
 
+// pool row of logical key ic (identity without a page table)
+static __device__ __forceinline__ int64_t fattn_row(const fattn_args & p, int64_t ic) {
+    if (!p.pages) return ic;
+    return ((int64_t) p.pages[ic >> p.page_shift] << p.page_shift) | (ic & (((int64_t) 1 << p.page_shift) - 1));
 }
 
 // ALiBi slope of head h (ops.cpp:8138-8139)

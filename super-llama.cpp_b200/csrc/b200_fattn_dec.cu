@@ -73,8 +73,9 @@ __global__ void __launch_bounds__(FD_WARPS * 32, 1) k_fattn_dec(const fattn_args
         if (lane == 0) mbar_arrive_expect_tx(bar, (uint32_t) __popc(live) * (uint32_t) (DKb + DVb));
         __syncwarp();
         if (ok) {
-            bulk_g2s(st + lane * KROW, kbase + ic * p.k_nb1, (uint32_t) DKb, bar);
-            bulk_g2s(st + FD_TILE * KROW + lane * DVb, vbase + ic * p.v_nb1, (uint32_t) DVb, bar);
+            const int64_t row = fattn_row(p, ic);                  // (paged cache: the page table is followed per row)
+            bulk_g2s(st + lane * KROW, kbase + row * p.k_nb1, (uint32_t) DKb, bar);
+            bulk_g2s(st + FD_TILE * KROW + lane * DVb, vbase + row * p.v_nb1, (uint32_t) DVb, bar);
         }
     };
 
@@ -227,9 +228,10 @@ bool b200_fattn_dec_supported(const b200_tensor * q, const b200_tensor * k, cons
 
 int b200_launch_fattn_dec(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v,
                           const b200_tensor * mask, const b200_tensor * sinks, b200_tensor * dst,
-                          float scale, float max_bias, float softcap) {
+                          float scale, float max_bias, float softcap, const b200_kv_pages * pages) {
     fattn_args p;
     fattn_fill_args(p, q, k, v, mask, sinks, dst, scale, max_bias, softcap);
+    fattn_set_pages(p, pages);
     const int64_t S = q->ne[3];
     if (p.N == 0 || p.H == 0 || S == 0) return B200_OK;
     if (p.H > 65535 || S > 65535) { b200_set_error("fattn: H or S exceeds grid limits"); return B200_ERR_UNSUPPORTED; }

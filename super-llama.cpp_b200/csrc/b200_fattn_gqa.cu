@@ -89,7 +89,7 @@ __global__ void __launch_bounds__(GA_WARPS * 32, 1) k_fattn_gqa(const fattn_args
         if (lane == 0) {
             const uint32_t bar = bar0 + 8 * stage, st = ring + stage * STAGE;
             mbar_arrive_expect_tx(bar, STAGE);
-            const int k0 = tile * GA_TILE;
+            const int k0 = (int) fattn_row(p, (int64_t) tile * GA_TILE);      // (paged cache: a 16-key tile never straddles a page)
 #pragma unroll
             for (int b = 0; b < NB; ++b) {
                 tma_load_4d(st + b * BOX, &tmap_k, b * 64, x.k_swap ? hkv : k0, x.k_swap ? k0 : hkv, sk, bar);
@@ -380,10 +380,11 @@ bool b200_fattn_gqa_supported(const b200_tensor * q, const b200_tensor * k, cons
 
 // 4-D fp16 map over a K or V view [D, n_kv, n_head_kv, s]; the two middle dimensions are ordered by stride (the KV cache interleaves
 // heads inside a token row, plain tensors do not); box = 64 values x GA_TILE tokens of one head
-static bool ga_make_map(encode_tiled_fn encode, CUtensorMap * map, const b200_tensor * t, int * swap) {
+static bool ga_make_map(encode_tiled_fn encode, CUtensorMap * map, const b200_tensor * t, int * swap, int64_t tokens) {
     *swap = (t->ne[2] > 1 && t->nb[2] < t->nb[1]) ? 1 : 0;
     const int a = *swap ? 2 : 1, b = *swap ? 1 : 2;
     cuuint64_t dim[4] = { (cuuint64_t) t->ne[0], (cuuint64_t) t->ne[a], (cuuint64_t) t->ne[b], (cuuint64_t) t->ne[3] };
+    dim[*swap ? 2 : 1] = (cuuint64_t) tokens;                              // (paged cache: the rows of the pool, not the keys attended)
     cuuint64_t str[3] = { (cuuint64_t) t->nb[a], (cuuint64_t) t->nb[b], (cuuint64_t) t->nb[3] };
     if (dim[2] == 1) str[1] = str[0] * dim[1];                             // strides of extent-1 dimensions only have to be well formed
     if (dim[3] == 1) str[2] = str[1] * dim[2];
@@ -396,17 +397,21 @@ static bool ga_make_map(encode_tiled_fn encode, CUtensorMap * map, const b200_te
 // returns B200_ERR_UNSUPPORTED (without setting the error text) when the tensor maps cannot be built: the caller falls back
 int b200_launch_fattn_gqa(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v,
                           const b200_tensor * mask, const b200_tensor * sinks, b200_tensor * dst,
-                          float scale, float max_bias, float softcap) {
+                          float scale, float max_bias, float softcap, const b200_kv_pages * pages) {
     encode_tiled_fn encode = b200_get_encode_tiled();
     if (!encode) return B200_ERR_UNSUPPORTED;
+    // with a page table the rows past the last key of a partly filled tile are real pool memory, not zero fill: whole tiles only
+    if (pages && (k->ne[1] % GA_TILE != 0 || pages->page_tokens % GA_TILE != 0)) return B200_ERR_UNSUPPORTED;
     fattn_args p;
     fattn_fill_args(p, q, k, v, mask, sinks, dst, scale, max_bias, softcap);
+    fattn_set_pages(p, pages);
     const int64_t S = q->ne[3], Hkv = k->ne[2];
     if (p.N == 0 || p.H == 0 || S == 0) return B200_OK;
     ga_extra x;
     x.G = (int) (p.H / Hkv); x.nrows = (int) p.N * x.G;
     CUtensorMap tk, tv;
-    if (!ga_make_map(encode, &tk, k, &x.k_swap) || !ga_make_map(encode, &tv, v, &x.v_swap)) return B200_ERR_UNSUPPORTED;
+    const int64_t rows = pages ? pages->pool_tokens : k->ne[1];
+    if (!ga_make_map(encode, &tk, k, &x.k_swap, rows) || !ga_make_map(encode, &tv, v, &x.v_swap, rows)) return B200_ERR_UNSUPPORTED;
     x.ntiles = (int) ((p.KV + GA_TILE - 1) / GA_TILE);
     // A 16-key tile is ~0.9 us of dependent ldmatrix / mma / softmax work for its warp and the split merge costs ~4 us once, so contexts
     // are cut finely: as many splits as one wave of CTAs allows (one CTA per SM, >= 1 tile per warp), then the FEWEST splits that

@@ -164,6 +164,43 @@ __global__ void __launch_bounds__(256) k_scale(const float * x, float * y, int64
     if (i < n) y[i] = fmaf(x[i], s, b);
 }
 
+// ---- the MoE router's small ops (src/llama-graph.cpp:1097-1300: argsort_top_k of the expert probabilities, sum / clamp of the chosen weights) ----
+// ARGSORT (ggml-cpu/ops.cpp ggml_compute_forward_argsort_f32): dst[rank] = index.  One CTA per row, thread i ranks element i by counting
+// the elements that go before it (ties: lower index first, i.e. a stable order); rows of at most 1024 elements.
+__global__ void __launch_bounds__(1024) k_argsort(const gl_view s, const gl_view d, int desc) {
+    GL_PDL();
+    __shared__ float row[1024];
+    int64_t i1, i2, i3; gl_unrow(blockIdx.x, s, i1, i2, i3);
+    const float * sr = (const float *) (s.p + i1 * s.nb[1] + i2 * s.nb[2] + i3 * s.nb[3]);
+    int32_t * dr = (int32_t *) (d.p + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]);
+    const int n = (int) s.ne[0], i = threadIdx.x;
+    if (i < n) row[i] = sr[i];
+    __syncthreads();
+    if (i >= n) return;
+    const float v = row[i];
+    int rank = 0;
+    for (int j = 0; j < n; ++j) { const float w = row[j]; rank += desc ? (w > v || (w == v && j < i)) : (w < v || (w == v && j < i)); }
+    dr[rank] = i;
+}
+// SUM_ROWS: dst[0, i1, i2, i3] = sum over i0; one warp per row
+__global__ void __launch_bounds__(256) k_sum_rows(const gl_view s, const gl_view d, int64_t nrows) {
+    GL_PDL();
+    const int64_t r = (int64_t) blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (r >= nrows) return;
+    int64_t i1, i2, i3; gl_unrow(r, s, i1, i2, i3);
+    const float * sr = (const float *) (s.p + i1 * s.nb[1] + i2 * s.nb[2] + i3 * s.nb[3]);
+    float acc = 0.0f;
+    for (int64_t i = threadIdx.x & 31; i < s.ne[0]; i += 32) acc += sr[i];
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) *(float *) (d.p + i1 * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3]) = acc;
+}
+// CLAMP (contiguous)
+__global__ void __launch_bounds__(256) k_clamp(const float * x, float * y, int64_t n, float lo, float hi) {
+    GL_PDL();
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { const float v = x[i]; y[i] = v < lo ? lo : v > hi ? hi : v; }
+}
+
 // ---- ROPE (GGML_ROPE_TYPE_NORMAL = 0: pairs (2i, 2i+1); NEOX = 2: pairs (i, i + n_dims/2)), YaRN as ops.cpp:5524-5547 -----------------
 struct gl_rope { int n_dims, neox; float freq_scale, ext_factor, attn_factor, theta_scale, corr0, corr1; const int32_t * pos; const float * ff; };
 // head rows [h0, h1) of token i2, batch i3: the angle of a pair depends on the position and the pair only, so it is evaluated once and
@@ -423,6 +460,12 @@ bool b200_glue_supports(const struct ggml_tensor * op) {
                    gl_contig_rows(op, 4) && gl_same_shape(a, op) && gl_can_repeat(b, a) && gl_grid_ok(op);
         case GGML_OP_SCALE:
             return a->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && gl_contiguous(a, 4) && gl_contiguous(op, 4);
+        case GGML_OP_ARGSORT:
+            return a->type == GGML_TYPE_F32 && op->type == GGML_TYPE_I32 && gl_contig_rows(a, 4) && gl_contig_rows(op, 4) && a->ne[0] <= 1024 && gl_same_shape(a, op) && gl_nrows(op) <= 0x7fffffff;
+        case GGML_OP_SUM_ROWS:
+            return a->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && gl_contig_rows(a, 4) && op->ne[0] == 1 && gl_nrows(a) == gl_nrows(op) && gl_nrows(op) <= 0x7fffffff;
+        case GGML_OP_CLAMP:
+            return a->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && gl_contiguous(a, 4) && gl_contiguous(op, 4);
         case GGML_OP_UNARY:
             return op->op_params[0] == GGML_UNARY_OP_SILU && a->type == GGML_TYPE_F32 && op->type == GGML_TYPE_F32 && gl_contiguous(a, 4) && gl_contiguous(op, 4);
         case GGML_OP_SOFT_MAX: {
@@ -592,6 +635,18 @@ int b200_glue_compute(b200_ctx * ctx, struct ggml_tensor * op) {
             float s, bias; memcpy(&s, op->op_params, 4); memcpy(&bias, op->op_params + 1, 4);
             const int64_t n = gl_nelem(op);
             GL_LAUNCH(gl_launch(ctx, k_scale, dim3((unsigned) ((n + 255) / 256)), 256, (const float *) a->data, (float *) op->data, n, s, bias));
+            return B200_OK;
+        }
+        case GGML_OP_ARGSORT:
+            GL_LAUNCH(gl_launch(ctx, k_argsort, dim3(rows), (unsigned) ((a->ne[0] + 31) / 32 * 32), gl_of(a), gl_of(op), (int) (op->op_params[0] == 1)));     // GGML_SORT_ORDER_DESC = 1
+            return B200_OK;
+        case GGML_OP_SUM_ROWS:
+            GL_LAUNCH(gl_launch(ctx, k_sum_rows, dim3((unsigned) ((gl_nrows(a) + 7) / 8)), 256, gl_of(a), gl_of(op), gl_nrows(a)));
+            return B200_OK;
+        case GGML_OP_CLAMP: {
+            float lo, hi; memcpy(&lo, op->op_params, 4); memcpy(&hi, op->op_params + 1, 4);
+            const int64_t n = gl_nelem(op);
+            GL_LAUNCH(gl_launch(ctx, k_clamp, dim3((unsigned) ((n + 255) / 256)), 256, (const float *) a->data, (float *) op->data, n, lo, hi));
             return B200_OK;
         }
         case GGML_OP_UNARY: {

@@ -35,6 +35,11 @@ class Exchange(C.Structure):
     _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("base", C.c_void_p * 8), ("ctrl_off", C.c_size_t)]
 
 
+class KvPages(C.Structure):
+    """b200_kv_pages: page table of a paged KV cache (logical page -> physical page of the pool)"""
+    _fields_ = [("table", C.c_void_p), ("n_pages", C.c_int32), ("page_tokens", C.c_int32), ("pool_tokens", C.c_int64)]
+
+
 class ChainPhase(C.Structure):
     """b200_chain_phase: one MUL_MAT group of the persistent decode chain with its prologue / epilogue"""
     _fields_ = [("prologue", C.c_int32), ("epilogue", C.c_int32), ("n_w", C.c_int32), ("eps", C.c_float),
@@ -74,6 +79,7 @@ def lib():
         "b200_mul_mat_gate_up_swiglu": (i, [vp, tp, tp, tp, tp, tp, tp]),
         "b200_repack_supported": (i, [i, i64]), "b200_repack": (i, [vp, i, vp, i64, i64, sz]), "b200_unrepack": (i, [vp, i, vp, i64, i64, sz]), "b200_mul_mat_id": (i, [vp, tp, tp, tp, tp]),
         "b200_flash_attn_ext": (i, [vp, tp, tp, tp, tp, tp, tp, f, f, f]),
+        "b200_flash_attn_ext_paged": (i, [vp, tp, tp, tp, C.POINTER(KvPages), tp, tp, tp, f, f, f]),
         "b200_ctx_launch_count_kind": (C.c_uint64, [vp, i]), "b200_ctx_profile": (i, [vp, i]),
         "b200_ctx_profile_get": (i, [vp, i, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]),
         "b200_event_create": (vp, []), "b200_event_destroy": (i, [vp]), "b200_event_record": (i, [vp, vp]),
@@ -386,6 +392,16 @@ class Context:
     def mul_mat_id(self, as_, b, ids, dst):
         ca, cb, ci, cd = as_.c(), b.c(), ids.c(), dst.c()
         _check(lib().b200_mul_mat_id(self.h, C.byref(ca), C.byref(cb), C.byref(ci), C.byref(cd)), "mul_mat_id")
+
+    def flash_attn_ext_paged(self, q, k, v, table, page_tokens, pool_tokens, mask, sinks, dst, scale, max_bias=0.0, logit_softcap=0.0):
+        """k / v describe the page pool (ne[1] = keys attended); table: device int32 tensor, logical page -> physical page"""
+        cq, ck, cv, cd = q.c(), k.c(), v.c(), dst.c()
+        cm = mask.c() if mask is not None else None
+        cs = sinks.c() if sinks is not None else None
+        pg = KvPages(table.ptr, int(table.ne[0]), page_tokens, pool_tokens)
+        _check(lib().b200_flash_attn_ext_paged(self.h, C.byref(cq), C.byref(ck), C.byref(cv), C.byref(pg),
+                                               C.byref(cm) if cm is not None else None, C.byref(cs) if cs is not None else None,
+                                               C.byref(cd), scale, max_bias, logit_softcap), "flash_attn_ext_paged")
 
     def flash_attn_ext(self, q, k, v, mask, sinks, dst, scale, max_bias=0.0, logit_softcap=0.0):
         cq, ck, cv, cd = q.c(), k.c(), v.c(), dst.c()

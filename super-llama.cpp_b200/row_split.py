@@ -76,6 +76,30 @@ class PeerExchange:
         self.cursor = 0
         dist.barrier()                                       # nobody signals before everybody has zeroed and mapped
 
+    @classmethod
+    def local_group(cls, ctxs, arena_bytes):
+        """N exchanges inside ONE process: rank r is ctxs[r] (its own stream; the contexts may all sit on one device), the arenas are
+        plain allocations of that process, so no IPC handles are passed.  The kernels cannot tell the difference: they only see
+        base[0..world) -- which is what lets a one-GPU box exercise the exchange epilogue and the receive kernels."""
+        world = len(ctxs)
+        out = []
+        for rank, ctx in enumerate(ctxs):
+            self = cls.__new__(cls)
+            self.ctx, self.world, self.rank = ctx, world, rank
+            self.arena_bytes = (arena_bytes + 255) // 256 * 256
+            total = 3 * self.arena_bytes + cls.CTRL_BYTES
+            self.base = ctx.malloc(total)
+            B._check(B.lib().b200_memset(ctx.h, self.base, 0, total), "memset")
+            ctx.synchronize()
+            self.cursor = 0
+            out.append(self)
+        for self in out:
+            self.ex = B.Exchange()
+            self.ex.world, self.ex.rank, self.ex.ctrl_off = world, self.rank, self.arena_bytes
+            for r in range(world):
+                self.ex.base[r] = out[r].base
+        return out
+
     def alloc(self, t, ne):
         """carve a tensor out of the arena: same offset on every rank (every rank allocates in the same order)"""
         dt = B.DeviceTensor(self.ctx, t, ne, ptr=self.base + self.cursor)

@@ -83,7 +83,8 @@ def test_backend_ops_with_load_time_repack(op):
     assert ok >= 100
 
 
-GLUE_OPS = ["RMS_NORM", "RMS_NORM_MUL_ADD", "ADD_RMS_NORM", "SOFT_MAX", "SILU", "ADD", "MUL", "SCALE", "ROPE", "SET_ROWS", "GET_ROWS", "CPY", "CONT", "SWIGLU"]
+GLUE_OPS = ["RMS_NORM", "RMS_NORM_MUL_ADD", "ADD_RMS_NORM", "SOFT_MAX", "SILU", "ADD", "MUL", "SCALE", "ROPE", "SET_ROWS", "GET_ROWS", "CPY", "CONT", "SWIGLU",
+            "ARGSORT", "SUM_ROWS", "CLAMP"]
 
 
 @pytest.mark.parametrize("op", GLUE_OPS)

@@ -205,3 +205,42 @@ def test_flash_attn_gqa_decode_kernel_all_shapes():
                         "-k", "not prefill and not all_shapes"], env=env, cwd=root, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
 
+
+
+@pytest.mark.parametrize("n_kv,n_past", [(8704, 8192), (10240, 9728)])
+def test_flash_attn_prefill_8k_depth_vs_reference(ctx, B, n_kv, n_past):
+    """BASELINE.json configs[2] (pp2048 @ d8192, n_ubatch 512): the first and the last micro-batch's attention, 32 query heads over
+    8 kv heads of 128, K/V as strided views of a 10240-token cache (heads interleaved inside a token row), causal mask.  Checked
+    against the compiled reference itself (oracle/_ref, ggml-cpu's FLASH_ATTN_EXT with its fp16 K/V arithmetic): NMSE < 5e-4,
+    the bar of tests/test-backend-ops.cpp:6080-6082."""
+    if not O.have_reference():
+        pytest.skip("oracle/_ref not built")
+    ref = O.Reference()
+    rng = np.random.default_rng(n_kv)
+    H, Hk, D, kv_size, n_batch = 32, 8, 128, 10240, 512
+    cache_k = rng.standard_normal((kv_size, Hk, D)).astype(np.float16)
+    cache_v = rng.standard_normal((kv_size, Hk, D)).astype(np.float16)
+    q = rng.standard_normal((1, H, n_batch, D)).astype(np.float32)
+    mask = causal_mask(n_batch, n_kv, n_past)
+    sc = 1.0 / np.sqrt(D)
+    dq = ctx.upload(B.F32, [D, n_batch, H, 1], q)
+    dck = ctx.upload(B.F16, [D * Hk, kv_size], cache_k)
+    dcv = ctx.upload(B.F16, [D * Hk, kv_size], cache_v)
+    tok, head = Hk * D * 2, D * 2
+    kview = dck.view([D, n_kv, Hk, 1], [2, tok, head, tok * kv_size])
+    vview = dcv.view([D, n_kv, Hk, 1], [2, tok, head, tok * kv_size])
+    dm = ctx.upload(B.F16, [n_kv, mask.shape[2], 1, 1], mask)
+    dd = ctx.empty(B.F32, [D, H, n_batch, 1])
+    ctx.flash_attn_ext(dq, kview, vview, dm, None, dd, sc)
+    got = ctx.download(dd).reshape(1, n_batch, H, D)
+    assert np.isfinite(got).all()
+    kc = np.ascontiguousarray(cache_k[:n_kv].transpose(1, 0, 2))[None]
+    vc = np.ascontiguousarray(cache_v[:n_kv].transpose(1, 0, 2))[None]
+    want = ref.flash_attn_ext(q, kc, vc, mask, None, sc)
+    assert O.nmse(want, got) < 5e-4
+    # the rows of one query over its own visible keys only: a second, size-independent check (softmax weights sum to 1, so the
+    # output of a query lies inside the per-dimension range of the V rows it can see)
+    vis = cache_v[: n_past + 1].astype(np.float32)
+    assert (got[0, 0] <= vis.max(axis=0).reshape(Hk, 1, D).repeat(H // Hk, 1).reshape(H, D) + 1e-3).all()
+    for d in (dq, dck, dcv, dm, dd):
+        d.free()

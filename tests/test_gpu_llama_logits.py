@@ -44,7 +44,10 @@ def nmse(ref, got):
 # GQA-grouped tensor-core decode attention) and crosses 768
 # n_step 4: every decode step carries four positions of the sequence (MUL_MAT with 4 columns, attention with 4 queries, 4 cache rows written)
 @pytest.mark.parametrize("model,quant,layers,n_prompt,n_step", [("8b", "q4_k_m", 4, 250, 1), ("tinyllama", "q4_0", 6, 250, 1), ("tinyllama", "q8_0", 4, 250, 1),
-                                                              ("8b", "q4_k_m", 2, 760, 1), ("8b", "q4_k_m", 2, 230, 4)])
+                                                              ("8b", "q4_k_m", 2, 760, 1), ("8b", "q4_k_m", 2, 230, 4),
+                                                              # 70B shapes (n_embd 8192, n_ff 28672, 64:8 heads) and the Mixtral router + 8 experts
+                                                              # (MUL_MAT_ID, ARGSORT top-2, GET_ROWS of the weights, SUM_ROWS / CLAMP / DIV), two layers each
+                                                              ("70b", "q4_k_m", 2, 250, 1), ("mixtral", "q4_k_m", 2, 250, 1)])
 def test_llama_logits_plugin_vs_ggml_cpu(model, quant, layers, n_prompt, n_step):
     _run_case(model, quant, layers, n_prompt, n_step, {})
 
