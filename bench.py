@@ -353,7 +353,8 @@ def traffic_per_launch(algorithmic_bytes_per_launch):
     timed region, so the ratio dram__bytes_read.sum + dram__bytes_write.sum over algorithmic bytes of the newest committed `ncu --set full`
     capture (profiles/*_traffic.json) is applied to this run's algorithmic bytes per launch.  (None, why) when no capture is committed."""
     try:
-        cands = sorted(f for f in os.listdir(os.path.join(ROOT, "profiles")) if f.endswith("_traffic.json"))
+        import re
+        cands = sorted((f for f in os.listdir(os.path.join(ROOT, "profiles")) if f.endswith("_traffic.json")), key=lambda f: [int(x) for x in re.findall(r"\d+", f)[:2]])
         d = json.load(open(os.path.join(ROOT, "profiles", cands[-1])))
         return algorithmic_bytes_per_launch * float(d["traffic_over_algorithmic"]), f"profiles/{cands[-1]} ratio {float(d['traffic_over_algorithmic']):.4f} (ncu --set full of {d.get('kernel', 'the decode GEMV')}) x this run's algorithmic bytes; not measured live"
     except Exception as ex:

@@ -10,6 +10,7 @@
 #include "b200_common.cuh"
 #include "b200_glue.cuh"   // non-hot-path ops so whole llama graphs stay on the device
 #include "../../include/ggml-b200-abi.h"
+#include "b200_split.h"
 #include <string>
 #include <vector>
 #include <mutex>
@@ -64,7 +65,9 @@ static b200_tensor to_b200(const ggml_tensor * t) {
 
 // ---- registry state -----------------------------------------------------------------------------
 struct b200_device_ctx {
-    int device; std::string name, description;
+    int device;                             // CUDA device
+    int index;                              // position in the registry (with GGML_B200_FAKE_DEVICES several entries share one CUDA device)
+    std::string name, description;
     ggml_backend_buffer_type buft;          // default device buffer type
     ggml_backend_device      dev;
 };
@@ -75,6 +78,10 @@ struct b200_buffer_ctx { int device; void * base; std::mutex mu; std::unordered_
 struct b200_graph_entry { uint64_t h1, h2; int n_nodes; void * exec; int seen; int failed; uint64_t used; };
 struct b200_backend_ctx {
     int device; b200_ctx * ctx; std::string name;
+    int index = 0;                                     // registry position of this backend's device
+    // split-mode row (split_mul_mat): one helper context (= stream) per other device, created on first use, and the events that order
+    // them against this backend's stream
+    b200_ctx * peer[B200_SPLIT_MAX_DEVICES] = {}; cudaEvent_t ev_main = nullptr, ev_peer[B200_SPLIT_MAX_DEVICES] = {};
     std::vector<b200_graph_entry> graphs; uint64_t graphs_epoch = 0, tick = 0, n_replayed = 0, n_captured = 0, n_eager = 0;
     // GGML_B200_GRAPH_STATS: device time of every replay (event pairs, read in be_free) and host time spent inside graph_compute
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> replay_events; double host_us = 0;
@@ -100,12 +107,20 @@ static int repack_mode() {
     if (m < 0) { const char * e = getenv("GGML_B200_REPACK"); m = !e ? 1 : !strcmp(e, "all") ? 2 : atoi(e) ? 1 : 0; }
     return m;
 }
-static b200_ctx * util_ctx(int device) {                   // one helper context per device for the repack kernels
+b200_ctx * b200_util_ctx(int device) {                      // one helper context per CUDA device for the repack kernels
     static std::mutex mu; static b200_ctx * ctxs[B200_MAX_DEVICES] = {};
     std::lock_guard<std::mutex> g(mu);
     if (!ctxs[device]) ctxs[device] = b200_ctx_create(device);
     return ctxs[device];
 }
+static b200_ctx * util_ctx(int device) { return b200_util_ctx(device); }
+int b200_repack_policy(const ggml_backend_buffer * b) {
+    const int mode = repack_mode();
+    return mode == 2 || (mode == 1 && b->usage == GGML_BACKEND_BUFFER_USAGE_WEIGHTS);
+}
+int                b200_logical_devices()        { return (int) g_reg_ctx.devices.size(); }
+int                b200_logical_to_cuda(int i)   { return g_reg_ctx.devices[i]->device; }
+ggml_backend_dev_t b200_logical_dev(int i)       { return &g_reg_ctx.devices[i]->dev; }
 static bool tensor_is_repacked(const ggml_tensor * t) {
     const ggml_tensor * base = t->view_src ? t->view_src : t;
     if (!base->buffer || !buft_is_b200(base->buffer->buft) || t_blck(base->type) <= 1) return false;
@@ -256,6 +271,11 @@ static void be_free(ggml_backend_t be) {
             if (b200_ctx_profile_get(c->ctx, k, &ms, &n) == B200_OK && n) fprintf(stderr, "ggml-b200 profile: %-14s %8llu launches %10.3f ms  %8.2f us each\n", kinds[k], (unsigned long long) n, ms, ms * 1e3 / n);
         }
     }
+    for (int i = 0; i < B200_SPLIT_MAX_DEVICES; ++i) {
+        if (c->peer[i]) { b200_ctx_synchronize(c->peer[i]); b200_ctx_destroy(c->peer[i]); }
+        if (c->ev_peer[i]) { cudaSetDevice(b200_logical_to_cuda(i)); cudaEventDestroy(c->ev_peer[i]); }
+    }
+    if (c->ev_main) { cudaSetDevice(c->device); cudaEventDestroy(c->ev_main); }
     b200_ctx_destroy(c->ctx); delete c; delete be;
 }
 static void be_set_tensor_async(ggml_backend_t be, ggml_tensor * t, const void * data, size_t off, size_t n) {
@@ -403,7 +423,8 @@ static bool chain_col(const ggml_tensor * t) {
     return t && t->type == GGML_TYPE_F32 && t->ne[1] == 1 && t->ne[2] == 1 && t->ne[3] == 1 && t->nb[0] == 4 && t->data && ((uintptr_t) t->data & 15) == 0;
 }
 static bool chain_weight(const ggml_tensor * w) {
-    return w && (w->type == GGML_TYPE_Q4_K || w->type == GGML_TYPE_Q6_K) && w->ne[2] == 1 && w->ne[3] == 1 && w->ne[0] % 2048 == 0 && w->ne[1] % 4 == 0 && w->data;
+    return w && (w->type == GGML_TYPE_Q4_K || w->type == GGML_TYPE_Q6_K) && w->ne[2] == 1 && w->ne[3] == 1 && w->ne[0] % 2048 == 0 && w->ne[1] % 4 == 0 && w->data &&
+           !b200_split_of(w);
 }
 struct chain_build {
     b200_chain_phase ph[B200_CHAIN_MAX_PHASES];
@@ -549,12 +570,62 @@ static int try_chain(b200_backend_ctx * c, ggml_cgraph * g, int i) {
     for (int k = i; k <= last; ++k) if (!op_is_view((int) g->nodes[k]->op)) b200_note_write(c->ctx, g->nodes[k]->data, tensor_nbytes(g->nodes[k]));
     return last;
 }
+// MUL_MAT whose weight lives in the row-split buffer type (b200_split.cpp): every device of the registry multiplies ITS rows of the weight
+// with the activation -- read in place from this backend's device over NVLink peer access -- and stores its rows of the result straight
+// into this backend's dst (peer stores): the all-gather of the reference's split path (ggml-cuda.cu:1451-1769: copy src1 to every device,
+// compute, copy the dst slices back) happens inside the kernels' own loads and stores.  Ordering: the other devices' streams wait for an
+// event recorded on this stream (the activation is ready), this stream waits for one event per device (its rows have landed).
+static int split_mul_mat(b200_backend_ctx * c, ggml_tensor * node) {
+    const ggml_tensor * w = node->src[0], * x = node->src[1];
+    const b200_split_extra * e = (const b200_split_extra *) w->extra;
+    if (!e || w->ne[2] * w->ne[3] != 1) { b200_set_error("row-split MUL_MAT: weight without slices or with batch dimensions"); return B200_ERR_UNSUPPORTED; }
+    if (!c->ev_main) B200_CHECK(cudaEventCreateWithFlags(&c->ev_main, cudaEventDisableTiming));
+    B200_CHECK(cudaEventRecord(c->ev_main, c->ctx->stream));
+    const b200_tensor bx = to_b200(x);
+    int rc = B200_OK;
+    for (int i = 0; i < e->n && rc == B200_OK; ++i) {
+        const b200_split_slice & s = e->s[i];
+        if (s.hi <= s.lo) continue;
+        b200_ctx * ctx = c->ctx;
+        if (i != c->index) {
+            if (!c->peer[i]) {
+                c->peer[i] = b200_ctx_create(b200_logical_to_cuda(i));
+                if (!c->peer[i]) return B200_ERR_ALLOC;
+                B200_CHECK(cudaSetDevice(b200_logical_to_cuda(i)));
+                B200_CHECK(cudaEventCreateWithFlags(&c->ev_peer[i], cudaEventDisableTiming));
+            }
+            ctx = c->peer[i];
+            B200_CHECK(cudaSetDevice(ctx->device));
+            B200_CHECK(cudaStreamWaitEvent(ctx->stream, c->ev_main, 0));
+            b200_ctx_invalidate(ctx);                         // its cached activation images were made from older contents of these addresses
+        }
+        b200_tensor bw; bw.data = s.data; bw.type = (int32_t) w->type; bw.flags = s.repacked ? B200_TENSOR_REPACKED : 0;
+        bw.ne[0] = w->ne[0]; bw.ne[1] = s.hi - s.lo; bw.ne[2] = bw.ne[3] = 1;
+        bw.nb[0] = w->nb[0]; bw.nb[1] = w->nb[1]; bw.nb[2] = bw.nb[3] = w->nb[1] * (size_t) bw.ne[1];
+        b200_tensor bd = to_b200(node);
+        bd.data = (char *) node->data + s.lo * sizeof(float); bd.ne[0] = s.hi - s.lo;
+        rc = b200_mul_mat(ctx, &bw, &bx, &bd);
+        if (i != c->index) {
+            B200_CHECK(cudaEventRecord(c->ev_peer[i], ctx->stream));
+            B200_CHECK(cudaSetDevice(c->device));
+            B200_CHECK(cudaStreamWaitEvent(c->ctx->stream, c->ev_peer[i], 0));
+        }
+    }
+    B200_CHECK(cudaSetDevice(c->device));
+    b200_note_write(c->ctx, node->data, tensor_nbytes(node));
+    return rc;
+}
+
 static enum ggml_status run_nodes(b200_backend_ctx * c, ggml_cgraph * g) {
     c->ctx->qcache.valid = 0; c->ctx->mcache.valid = 0;      // tensors may have been rewritten through buffer set_tensor since the last graph
     for (int i = 0; i < g->n_nodes; ++i) {
         ggml_tensor * node = g->nodes[i];
         if (op_is_view((int) node->op) || tensor_nelements(node) == 0) continue;
         int rc;
+        if (node->op == GGML_OP_MUL_MAT && b200_split_of(node->src[0])) {
+            if ((rc = split_mul_mat(c, node)) != B200_OK) { B200_LOG("graph_compute: row-split node %d (%s) failed: %s", i, node->name, b200_last_error()); return GGML_STATUS_FAILED; }
+            continue;
+        }
         // decode: the whole run of a layer's nodes between two attention operators as one persistent kernel
         if ((node->op == GGML_OP_MUL_MAT || node->op == GGML_OP_ADD) && node->ne[1] == 1 && (rc = try_chain(c, g, i)) >= 0) { c->n_fuse[1] += 1; i = rc; continue; }
         // MUL_MAT nodes that follow each other (views in between do no work) and read the same src1 -- ffn_gate / ffn_up, attn_v / attn_k
@@ -566,7 +637,7 @@ static enum ggml_status run_nodes(b200_backend_ctx * c, ggml_cgraph * g) {
             for (int j = i + 1; j < g->n_nodes && ng < 3; ++j) {
                 ggml_tensor * nj = g->nodes[j];
                 if (op_is_view((int) nj->op) || tensor_nelements(nj) == 0) continue;
-                if (nj->op != GGML_OP_MUL_MAT || nj->src[1] != node->src[1] || nj->src[0]->type != node->src[0]->type) break;
+                if (nj->op != GGML_OP_MUL_MAT || nj->src[1] != node->src[1] || nj->src[0]->type != node->src[0]->type || b200_split_of(nj->src[0])) break;
                 bool clash = false;
                 for (int k = 0; k < ng && !clash; ++k) {
                     const ggml_tensor * nk = g->nodes[group[k]];
@@ -781,7 +852,9 @@ static ggml_backend_t dev_init_backend(ggml_backend_dev_t d, const char *) {
     b200_ctx * ctx = b200_ctx_create(c->device);
     if (ctx && getenv("GGML_B200_PROFILE")) b200_ctx_profile(ctx, 1);
     if (!ctx) { B200_LOG("init_backend: %s", b200_last_error()); return nullptr; }
-    return new ggml_backend{ &g_guid, k_backend_iface, d, new b200_backend_ctx{ c->device, ctx, c->name } };
+    b200_backend_ctx * bc = new b200_backend_ctx{ c->device, ctx, c->name };
+    bc->index = c->index;
+    return new ggml_backend{ &g_guid, k_backend_iface, d, bc };
 }
 static ggml_backend_buffer_type_t dev_buft(ggml_backend_dev_t d) { return &((b200_device_ctx *) d->context)->buft; }
 static ggml_backend_buffer_type_t dev_host_buft(ggml_backend_dev_t) { return &g_host_buft; }
@@ -821,6 +894,11 @@ static bool op_declined(const ggml_tensor * op) {
 }
 static bool dev_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
     if (op_declined(op)) return false;
+    // row-split tensors are weights of plain MUL_MATs and nothing else (as ggml-cuda.cu:4304-4311, :4371-4374)
+    for (int i = 0; i < GGML_MAX_SRC; ++i) {
+        if (!op->src[i] || !op->src[i]->buffer || !b200_buft_is_split(op->src[i]->buffer->buft)) continue;
+        if (op->op != GGML_OP_MUL_MAT || i != 0 || op->src[0]->ne[2] * op->src[0]->ne[3] != 1 || op->src[0]->view_src) return false;
+    }
     switch ((int) op->op) {
         case GGML_OP_NONE: case GGML_OP_RESHAPE: case GGML_OP_VIEW: case GGML_OP_PERMUTE: case GGML_OP_TRANSPOSE:
             return true;
@@ -852,7 +930,7 @@ static bool dev_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
 }
 static bool dev_supports_buft(ggml_backend_dev_t d, ggml_backend_buffer_type_t buft) {
     if (buft_is_b200_host(buft)) return false;   // host tensors are copied in by the scheduler
-    return buft_is_b200(buft) && buft->device == d;
+    return (buft_is_b200(buft) || b200_buft_is_split(buft)) && buft->device == d;
 }
 static bool dev_offload_op(ggml_backend_dev_t, const ggml_tensor * op) {
     // as ggml-cuda.cu:4493-4500: worth shipping host-resident weights over only for real batches
@@ -897,11 +975,15 @@ extern "C" B200_API ggml_backend_reg_t ggml_backend_b200_reg(void) {
     std::call_once(once, [] {
         g_reg.api_version = GGML_BACKEND_API_VERSION; g_reg.iface = k_reg_iface; g_reg.context = &g_reg_ctx;
         g_host_buft.iface = k_hbuft_iface; g_host_buft.device = nullptr; g_host_buft.context = nullptr;
-        const int n = b200_device_count();
+        const int n_cuda = b200_device_count();
+        // GGML_B200_FAKE_DEVICES=N: list N devices, dealt round-robin onto the GPUs that exist, so that a one-GPU box can run the
+        // multi-device paths (split-mode row, layer split) end to end; each keeps its own stream, buffers and row slices
+        const char * fake = getenv("GGML_B200_FAKE_DEVICES");
+        const int n = (fake && atoi(fake) > 0 && n_cuda > 0) ? atoi(fake) : n_cuda;
         for (int i = 0; i < n && i < B200_MAX_DEVICES; ++i) {
-            cudaDeviceProp prop; if (cudaGetDeviceProperties(&prop, i) != cudaSuccess) continue;
+            cudaDeviceProp prop; if (cudaGetDeviceProperties(&prop, i % n_cuda) != cudaSuccess) continue;
             b200_device_ctx * d = new b200_device_ctx;
-            d->device = i; d->name = "B200_" + std::to_string(i); d->description = prop.name;
+            d->device = i % n_cuda; d->index = (int) g_reg_ctx.devices.size(); d->name = "B200_" + std::to_string(i); d->description = prop.name;
             d->dev.iface = k_device_iface; d->dev.reg = &g_reg; d->dev.context = d;
             d->buft.iface = k_buft_iface; d->buft.device = &d->dev; d->buft.context = d;
             g_reg_ctx.devices.push_back(d);

@@ -64,7 +64,10 @@ def test_flash_attn_paged_shuffled_pages(ctx, B, D, n_batch, n_kv, page, identit
     ck = dck.view([D, n_kv, Hk, 1], [2, tok, head, tok * n_kv]); cv = dcv.view([D, n_kv, Hk, 1], [2, tok, head, tok * n_kv])
     ctx.flash_attn_ext(dq, ck, cv, dm, None, dd, sc)
     flat = ctx.download(dd).reshape(1, n_batch, H, D)
-    assert np.array_equal(flat.view(np.uint32), got.view(np.uint32))
+    if n_kv % 16 == 0:                                         # (else the two calls take different kernels: the comparison with the oracle below decides)
+        assert np.array_equal(flat.view(np.uint32), got.view(np.uint32))
+    else:
+        assert O.nmse(flat, got) < 1e-6
     want = O.Oracle().flash_attn_ext(q, gk.transpose(1, 0, 2)[None], gv.transpose(1, 0, 2)[None], mask, None, sc)
     assert O.nmse(want, got) < 1e-6
     for d in (dq, dpk, dpv, dt, dm, dd, dck, dcv):
