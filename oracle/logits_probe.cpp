@@ -18,6 +18,7 @@ int main(int argc, char ** argv) {
     llama_backend_init();
     llama_model_params mp = llama_model_default_params();
     mp.n_gpu_layers = ngl;
+    if (getenv("LOGITS_PROBE_SPLIT_ROW")) mp.split_mode = LLAMA_SPLIT_MODE_ROW;   // -sm row: weight matrices in the backend's split buffer type (src/llama-model.cpp:393-411)
     mp.use_mmap = false;                                   // the loader's chunked async upload path: exercises the plugin's load-time repack hook
     llama_model * model = llama_model_load_from_file(argv[1], mp);
     if (!model) { fprintf(stderr, "logits_probe: cannot load %s\n", argv[1]); return 1; }

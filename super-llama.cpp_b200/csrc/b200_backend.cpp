@@ -81,7 +81,7 @@ struct b200_backend_ctx {
     int index = 0;                                     // registry position of this backend's device
     // split-mode row (split_mul_mat): one helper context (= stream) per other device, created on first use, and the events that order
     // them against this backend's stream
-    b200_ctx * peer[B200_SPLIT_MAX_DEVICES] = {}; cudaEvent_t ev_main = nullptr, ev_peer[B200_SPLIT_MAX_DEVICES] = {};
+    b200_ctx * peer[B200_SPLIT_MAX_DEVICES] = {}; cudaEvent_t ev_main = nullptr, ev_peer[B200_SPLIT_MAX_DEVICES] = {}; uint64_t n_split = 0;
     std::vector<b200_graph_entry> graphs; uint64_t graphs_epoch = 0, tick = 0, n_replayed = 0, n_captured = 0, n_eager = 0;
     // GGML_B200_GRAPH_STATS: device time of every replay (event pairs, read in be_free) and host time spent inside graph_compute
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> replay_events; double host_us = 0;
@@ -262,6 +262,8 @@ static void be_free(ggml_backend_t be) {
     if (getenv("GGML_B200_GRAPH_STATS"))
         fprintf(stderr, "ggml-b200 fusions (launches saved while walking nodes): matmul groups %llu, add+norm+mul %llu, rope/set_rows %llu, gate+up+glu %llu, decode chains %llu\n",
                 (unsigned long long) c->n_fuse[0], (unsigned long long) c->n_fuse[2], (unsigned long long) c->n_fuse[3], (unsigned long long) c->n_fuse[4], (unsigned long long) c->n_fuse[1]);
+    if (getenv("GGML_B200_GRAPH_STATS") && c->n_split)
+        fprintf(stderr, "ggml-b200 split: %s ran %llu row-split MUL_MATs over %d devices\n", c->name.c_str(), (unsigned long long) c->n_split, b200_logical_devices());
     if (getenv("GGML_B200_PROFILE") || getenv("GGML_B200_GRAPH_STATS"))
         fprintf(stderr, "ggml-b200 graphs: %llu computed launch by launch, %llu recorded, %llu replayed\n", (unsigned long long) c->n_eager, (unsigned long long) c->n_captured, (unsigned long long) c->n_replayed);
     if (getenv("GGML_B200_PROFILE")) {                           // per-kernel-kind device time of everything this backend launched
@@ -613,6 +615,7 @@ static int split_mul_mat(b200_backend_ctx * c, ggml_tensor * node) {
     }
     B200_CHECK(cudaSetDevice(c->device));
     b200_note_write(c->ctx, node->data, tensor_nbytes(node));
+    ++c->n_split;
     return rc;
 }
 

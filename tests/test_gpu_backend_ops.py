@@ -115,6 +115,21 @@ def test_chunked_async_upload_repacks(wtype, K, M, chunk):
         assert "repacked chunked=1 whole=1" in p.stdout, p.stdout
 
 
+@pytest.mark.parametrize("ndev,wtype,K,M,split", [(2, 12, 4096, 4096, []), (4, 14, 4096, 1024, []), (3, 12, 2048, 6144, [3, 1, 2]), (8, 14, 4096, 14336, []),
+                                                   (2, 8, 1024, 640, []), (4, 2, 512, 96, [])])
+def test_split_buffer_type_row_slices(ndev, wtype, K, M, split):
+    """split-mode=row through the plugin ABI (tests/split_probe.cpp): the registry's "ggml_backend_split_buffer_type" (src/llama-model.cpp:393-411)
+    with ndev devices listed on the GPUs present (GGML_B200_FAKE_DEVICES): whole-tensor set / get, per-slice load-time repack, MUL_MAT with
+    every device in turn as the main one, decode column and prefill batch, against the same weight in a plain buffer"""
+    exe = os.path.join(OUT, "split_probe")
+    os.makedirs(OUT, exist_ok=True)
+    if not os.path.exists(exe):
+        subprocess.check_call(["g++", "-std=c++17", "-O1", "-I" + os.path.join(ROOT, "include"), os.path.join(ROOT, "tests", "split_probe.cpp"), "-o", exe, "-ldl"])
+    p = subprocess.run([exe, PLUGIN, str(wtype), str(K), str(M)] + [str(v) for v in split], env=dict(os.environ, GGML_B200_FAKE_DEVICES=str(ndev)),
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+    assert p.returncode == 0 and "split_probe: OK" in p.stdout, p.stdout[-3000:]
+
+
 @pytest.mark.parametrize("vtype", [12, 14])
 def test_layer_fusions_bit_identical(vtype):
     """what be_graph_optimize / be_graph_compute do to the head of a llama layer -- weight matmuls of one activation pulled together and

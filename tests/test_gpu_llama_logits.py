@@ -58,6 +58,30 @@ def test_llama_logits_without_flash_attention():
     _run_case("tinyllama", "q4_0", 4, 250, 1, {"LOGITS_PROBE_NO_FA": "1"})
 
 
+@pytest.mark.parametrize("ndev", [2, 4])
+def test_llama_logits_split_mode_row(ndev):
+    """-sm row (src/llama-model.cpp:393-411): the weight matrices live in the plugin's split buffer type, rows divided among `ndev` devices
+    (listed on the GPUs present, GGML_B200_FAKE_DEVICES, so a one-GPU box runs it too), layers and KV cache dealt over the devices by the
+    reference's own loader; every split MUL_MAT runs on all devices with peer reads / peer stores (b200_backend.cpp: split_mul_mat).
+    The logits must agree with ggml-cpu's within the q8_1 bar and with the single-device plugin run."""
+    if not os.path.exists(PROBE):
+        pytest.skip("oracle/_ref/avx2/logits_probe not built")
+    os.makedirs(OUT, exist_ok=True)
+    gguf = os.path.join(OUT, "probe-8b-q4_k_m-split.gguf")
+    subprocess.check_call([os.sys.executable, os.path.join(ROOT, "scripts", "make_gguf.py"), "--model", "8b", "--quant", "q4_k_m", "--layers", "4", "-o", gguf], stdout=subprocess.DEVNULL)
+    try:
+        cpu, _ = run_probe(gguf, "cpu_split", 0)
+        one, _ = run_probe(gguf, "b200_one", 99)
+        row, log = run_probe(gguf, "b200_row", 99, {"GGML_B200_FAKE_DEVICES": str(ndev), "LOGITS_PROBE_SPLIT_ROW": "1", "GGML_B200_GRAPH_STATS": "1"})
+    finally:
+        os.remove(gguf)
+    assert np.isfinite(row).all()
+    ran = [l for l in log.splitlines() if "row-split MUL_MATs" in l]          # the loader really placed the weights in the split buffer type
+    assert ran and all(f"over {ndev} devices" in l for l in ran), log[-3000:]
+    assert max(nmse(cpu[i], row[i]) for i in range(1 + N_DECODE)) < 2e-3
+    assert max(nmse(one[i], row[i]) for i in range(1 + N_DECODE)) < 1e-4
+
+
 def _run_case(model, quant, layers, n_prompt, n_step, probe_env):
     if not os.path.exists(PROBE):
         pytest.skip("oracle/_ref/avx2/logits_probe not built (make -C oracle llama; needs /root/reference at build time)")
