@@ -5,6 +5,7 @@
 // the B200 plugin (GGML_BACKEND_PATH, -ngl 99), and compares: the end-to-end parity check of the drop-in, through the reference's
 // graph builder, scheduler, allocator and KV cache (include/llama.h:437-996 for the calls used).
 // usage: logits_probe <model.gguf> <out.bin> <ngl> <n_prompt> <n_decode> [tokens per decode step = 1]
+#include <string.h>
 #include "llama.h"
 #include "ggml-backend.h"
 #include <cstdio>
@@ -27,6 +28,12 @@ int main(int argc, char ** argv) {
     cp.n_threads = 8; cp.n_threads_batch = 8;
     cp.flash_attn_type = getenv("LOGITS_PROBE_NO_FA") ? LLAMA_FLASH_ATTN_TYPE_DISABLED : LLAMA_FLASH_ATTN_TYPE_ENABLED;   // -fa 0: attention as MUL_MAT + SOFT_MAX + MUL_MAT, V cache transposed
     cp.no_perf = true;
+    auto kv_type = [](const char * e, ggml_type def) {           // -ctk / -ctv: the KV cache as q8_0 / q4_0 blocks (SET_ROWS quantizes, FLASH_ATTN_EXT reads them)
+        const char * v = getenv(e);
+        if (!v) return def;
+        return !strcmp(v, "q8_0") ? GGML_TYPE_Q8_0 : !strcmp(v, "q4_0") ? GGML_TYPE_Q4_0 : def;
+    };
+    cp.type_k = kv_type("LOGITS_PROBE_CTK", cp.type_k); cp.type_v = kv_type("LOGITS_PROBE_CTV", cp.type_v);
     llama_context * ctx = llama_init_from_model(model, cp);
     if (!ctx) { fprintf(stderr, "logits_probe: cannot create a context\n"); return 1; }
     const int n_vocab = llama_vocab_n_tokens(llama_model_get_vocab(model));

@@ -236,9 +236,16 @@ class Reference:
         return dst.reshape(n_tokens, n_used, M)
 
     def flash_attn_ext(self, q, k, v, mask=None, sinks=None, scale=1.0, max_bias=0.0, softcap=0.0, prec=0,
-                       threads=None, reps=1):
-        q = _f32(q); k = np.ascontiguousarray(k, dtype=np.float16); v = np.ascontiguousarray(v, dtype=np.float16)
-        S, H, N, DK = q.shape; Sk, Hk, KV, _ = k.shape; DV = v.shape[-1]
+                       threads=None, reps=1, kv_type=None, kv_shape=None):
+        """kv_type (one ggml type for K and V, as the reference's own test builds them) + kv_shape = (Sk, Hk, KV, DK, DV): k / v are raw blocks"""
+        q = _f32(q)
+        S, H, N, DK = q.shape
+        if kv_type is None:
+            k = np.ascontiguousarray(k, dtype=np.float16); v = np.ascontiguousarray(v, dtype=np.float16)
+            Sk, Hk, KV, _ = k.shape; DV = v.shape[-1]
+        else:
+            k = np.ascontiguousarray(k, dtype=np.uint8); v = np.ascontiguousarray(v, dtype=np.uint8)
+            Sk, Hk, KV, _, DV = kv_shape
         if mask is not None:
             mask = np.ascontiguousarray(mask, dtype=np.float16); Sm, Hm, Nm, _ = mask.shape
         else:
@@ -246,7 +253,7 @@ class Reference:
         if sinks is not None:
             sinks = _f32(sinks)
         dst = np.empty((S, N, H, DV), dtype=np.float32)
-        us = self.lib.refd_flash_attn_ext(_p(q), _p(k), _p(v), F16, _p(mask), _p(sinks), _p(dst), DK, DV, N, H, S, KV, Hk, Sk,
+        us = self.lib.refd_flash_attn_ext(_p(q), _p(k), _p(v), F16 if kv_type is None else kv_type, _p(mask), _p(sinks), _p(dst), DK, DV, N, H, S, KV, Hk, Sk,
                                           Nm, Hm, Sm, scale, max_bias, softcap, prec, threads or self.threads, reps)
         assert us >= 0
         self.last_us = us

@@ -475,6 +475,17 @@ extern "C" int b200_flash_attn_ext(b200_ctx * ctx, const b200_tensor * q, const 
         k->ne[2] <= 0 || q->ne[2] % k->ne[2] != 0 || q->ne[2] % v->ne[2] != 0 || q->ne[3] % k->ne[3] != 0 || q->ne[3] % v->ne[3] != 0) {
         b200_set_error("flash_attn_ext: shape mismatch"); return B200_ERR_INVALID;
     }
+    if (k->type != B200_TYPE_F16 || v->type != B200_TYPE_F16) {              // quantized KV cache (b200_fattn_q.cu)
+        if (q->type != B200_TYPE_F32 || dst->type != B200_TYPE_F32 || (mask && mask->type != B200_TYPE_F16) || q->nb[0] != 4 || dst->nb[0] != 4 ||
+            !b200_fattn_kvq_supported(q, k, v)) {
+            b200_set_error("flash_attn_ext: K/V types outside f16 and q8_0 / q4_0 at head size 64 / 128 (DK=%lld DV=%lld)", (long long) DK, (long long) DV);
+            return B200_ERR_UNSUPPORTED;
+        }
+        if (mask && (mask->ne[0] < k->ne[1] || mask->ne[1] < q->ne[1])) { b200_set_error("flash_attn_ext: mask too small"); return B200_ERR_INVALID; }
+        const int rcq = b200_launch_fattn_kvq(ctx, q, k, v, mask, sinks, dst, scale, max_bias, logit_softcap);
+        b200_note_write(ctx, dst->data, b200_tensor_span(dst));
+        return rcq;
+    }
     if (q->type != B200_TYPE_F32 || k->type != B200_TYPE_F16 || v->type != B200_TYPE_F16 || dst->type != B200_TYPE_F32 ||
         (mask && mask->type != B200_TYPE_F16) || q->nb[0] != 4 || k->nb[0] != 2 || v->nb[0] != 2 || dst->nb[0] != 4 ||
         DK % 64 != 0 || DV % 64 != 0 || DK > 256 || (DV != 64 && DV != 128 && DV != 256) ||

@@ -918,8 +918,13 @@ static bool dev_supports_op(ggml_backend_dev_t, const ggml_tensor * op) {
         case GGML_OP_FLASH_ATTN_EXT: {
             const ggml_tensor * q = op->src[0], * k = op->src[1], * v = op->src[2], * m = op->src[3];
             const int64_t DK = k->ne[0], DV = v->ne[0];
-            if (q->type != GGML_TYPE_F32 || k->type != GGML_TYPE_F16 || v->type != GGML_TYPE_F16 || op->type != GGML_TYPE_F32) return false;
+            if (q->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32) return false;
             if (m && m->type != GGML_TYPE_F16) return false;
+            if (k->type != GGML_TYPE_F16 || v->type != GGML_TYPE_F16) {          // quantized KV cache: q8_0 / q4_0 at head size 64 / 128 (b200_fattn_q.cu)
+                if (q->nb[0] != 4 || q->ne[2] > 65535 || q->ne[3] > 65535) return false;
+                const b200_tensor bq = to_b200(q), bk = to_b200(k), bv = to_b200(v);
+                return b200_fattn_kvq_supported(&bq, &bk, &bv);
+            }
             if (DK % 64 != 0 || DK > 256 || (DV != 64 && DV != 128 && DV != 256)) return false;
             if (q->nb[0] != 4 || k->nb[0] != 2 || v->nb[0] != 2) return false;
             if (k->nb[1] % 16 || k->nb[2] % 16 || k->nb[3] % 16 || v->nb[1] % 4 || v->nb[2] % 4 || v->nb[3] % 4) return false;

@@ -323,6 +323,9 @@ bool b200_fattn_tc_supported(const b200_tensor * q, const b200_tensor * k, const
 int  b200_launch_fattn_tc(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v,
                           const b200_tensor * mask, const b200_tensor * sinks, b200_tensor * dst,
                           float scale, float max_bias, float softcap);     // B200_ERR_UNSUPPORTED = use another kernel
+bool b200_fattn_kvq_supported(const b200_tensor * q, const b200_tensor * k, const b200_tensor * v);      // q8_0 / q4_0 K and V (b200_fattn_q.cu)
+int  b200_launch_fattn_kvq(b200_ctx * ctx, const b200_tensor * q, const b200_tensor * k, const b200_tensor * v,
+                           const b200_tensor * mask, const b200_tensor * sinks, b200_tensor * dst, float scale, float max_bias, float softcap);
 bool b200_gemv_stream_supported(const b200_tensor * w, const b200_tensor * x);
 // peers of a row-split MUL_MAT: the low-latency mirror (8 bytes per arena float) of every rank's arena, our own arena and its
 // control words, and the full f32 columns (inside our arena) that the kernel receives after it has sent its own rows

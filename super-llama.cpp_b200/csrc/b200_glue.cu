@@ -280,6 +280,51 @@ __global__ void __launch_bounds__(256) k_set_rows(const gl_view s, const gl_view
     }
 }
 
+// SET_ROWS into a quantized cache (llama.cpp -ctk / -ctv q8_0, q4_0): thread = one 32-element block, quantize_row_q8_0_ref / q4_0_ref
+// (ggml/src/ggml-quants.c:200-222, 38-74), what ggml-cpu's set_rows calls through from_float (ops.cpp, ggml_compute_forward_set_rows_f32)
+template <int Q4>
+__global__ void __launch_bounds__(256) k_set_rows_q(const gl_view s, const gl_view idx, const gl_view d, int nblk, int64_t total) {
+    GL_PDL();
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    const int b = (int) (i % nblk); const int64_t r = i / nblk;
+    int64_t i1, i2, i3; gl_unrow(r, s, i1, i2, i3);
+    const int64_t row = *(const int64_t *) (idx.p + i1 * idx.nb[0] + (i2 % idx.ne[1]) * idx.nb[1] + (i3 % idx.ne[2]) * idx.nb[2]);
+    const float * sr = (const float *) (s.p + i1 * s.nb[1] + i2 * s.nb[2] + i3 * s.nb[3]) + b * 32;
+    unsigned short * o = (unsigned short *) (d.p + row * d.nb[1] + i2 * d.nb[2] + i3 * d.nb[3] + (size_t) b * (Q4 ? 18 : 34));
+    float v[32];
+    #pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] = sr[j];
+    if (!Q4) {
+        float amax = 0.0f;
+        #pragma unroll
+        for (int j = 0; j < 32; ++j) amax = fmaxf(amax, fabsf(v[j]));
+        const float dd = amax / 127.0f, id = dd != 0.0f ? 1.0f / dd : 0.0f;
+        o[0] = __half_as_ushort(__float2half_rn(dd));
+        #pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const int q0 = (int) roundf(v[2 * j] * id), q1 = (int) roundf(v[2 * j + 1] * id);
+            o[1 + j] = (unsigned short) ((q0 & 0xff) | ((q1 & 0xff) << 8));
+        }
+    } else {
+        float amax = 0.0f, mx = 0.0f;
+        #pragma unroll
+        for (int j = 0; j < 32; ++j) if (amax < fabsf(v[j])) { amax = fabsf(v[j]); mx = v[j]; }
+        const float dd = mx / -8.0f, id = dd != 0.0f ? 1.0f / dd : 0.0f;
+        o[0] = __half_as_ushort(__float2half_rn(dd));
+        #pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            unsigned w = 0;
+            #pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                const int lo = min(15, (int) (signed char) (v[2 * j + k] * id + 8.5f)), hi = min(15, (int) (signed char) (v[2 * j + k + 16] * id + 8.5f));
+                w |= (unsigned) ((lo & 0xf) | ((hi & 0xf) << 4)) << (8 * k);
+            }
+            o[1 + j] = (unsigned short) w;
+        }
+    }
+}
+
 // ---- GET_ROWS (f32 rows): dst[:, i10, i11, i12] = src0[:, ids[i10, i11, i12], i11, i12] -------------------------------------------------
 __global__ void __launch_bounds__(256) k_get_rows_f32(const gl_view s, const gl_view idx, const gl_view d, int chunks) {
     GL_PDL();
@@ -484,6 +529,10 @@ bool b200_glue_supports(const struct ggml_tensor * op) {
             return a->ne[0] % 2 == 0 && op->op_params[1] % 2 == 0 && op->op_params[1] <= a->ne[0] && a->ne[1] <= 0x7fffffff && gl_grid_ok(op);
         }
         case GGML_OP_SET_ROWS:
+            if (op->type == GGML_TYPE_Q8_0 || op->type == GGML_TYPE_Q4_0)      // the quantized KV cache
+                return a->type == GGML_TYPE_F32 && b->type == GGML_TYPE_I64 && gl_contig_rows(a, 4) && a->ne[0] % 32 == 0 && a->ne[0] == op->ne[0] &&
+                       op->nb[0] == (op->type == GGML_TYPE_Q8_0 ? 34u : 18u) && !(op->nb[1] & 1) && !(op->nb[2] & 1) && !(op->nb[3] & 1) && !((uintptr_t) op->data & 1) &&
+                       gl_nelem(a) / 32 < ((int64_t) 1 << 38);
             return a->type == GGML_TYPE_F32 && b->type == GGML_TYPE_I64 && (op->type == GGML_TYPE_F16 || op->type == GGML_TYPE_F32) &&
                    gl_contig_rows(a, 4) && op->nb[0] == gl_esize(op->type) && gl_grid_ok(a);
         case GGML_OP_GET_ROWS:
@@ -671,6 +720,14 @@ int b200_glue_compute(b200_ctx * ctx, struct ggml_tensor * op) {
             return B200_OK;
         }
         case GGML_OP_SET_ROWS: {
+            if (op->type == GGML_TYPE_Q8_0 || op->type == GGML_TYPE_Q4_0) {
+                const int nblk = (int) (a->ne[0] / 32); const int64_t total = gl_nrows(a) * nblk;
+                if (total == 0) return B200_OK;
+                const dim3 qgrid((unsigned) ((total + 255) / 256));
+                if (op->type == GGML_TYPE_Q8_0) GL_LAUNCH(gl_launch(ctx, k_set_rows_q<0>, qgrid, 256, gl_of(a), gl_of(b), gl_of(op), nblk, total));
+                else                            GL_LAUNCH(gl_launch(ctx, k_set_rows_q<1>, qgrid, 256, gl_of(a), gl_of(b), gl_of(op), nblk, total));
+                return B200_OK;
+            }
             const unsigned srows = (unsigned) gl_nrows(a);
             const int sch = (int) ((a->ne[0] + GL_CHUNK - 1) / GL_CHUNK);
             const bool vec = gl_vec_ok(a) && ((uintptr_t) op->data & 15) == 0 && op->nb[1] % 16 == 0 && op->nb[2] % 16 == 0 && op->nb[3] % 16 == 0;

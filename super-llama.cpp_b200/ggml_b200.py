@@ -438,14 +438,22 @@ class Context:
         self.mul_mat_id(da, db, di, dd)
         return self.download(dd).reshape(n_tokens, n_used, M)
 
-    def flash_attn_ext_host(self, q, k, v, mask=None, sinks=None, scale=1.0, max_bias=0.0, softcap=0.0):
-        """q[S,H,N,DK] f32, k[Sk,Hk,KV,DK] f16, v[Sk,Hk,KV,DV] f16, mask[Sm,Hm,Nm,KV] f16 -> dst[S,N,H,DV]."""
+    def flash_attn_ext_host(self, q, k, v, mask=None, sinks=None, scale=1.0, max_bias=0.0, softcap=0.0, kv_type=None, kv_shape=None):
+        """q[S,H,N,DK] f32, k[Sk,Hk,KV,DK] f16, v[Sk,Hk,KV,DV] f16, mask[Sm,Hm,Nm,KV] f16 -> dst[S,N,H,DV].
+        Quantized cache: kv_type = (type of K, type of V) or one type, k / v the raw GGUF blocks (uint8), kv_shape = (Sk, Hk, KV, DK, DV)."""
         q = np.ascontiguousarray(q, dtype=np.float32)
-        k = np.ascontiguousarray(k, dtype=np.float16); v = np.ascontiguousarray(v, dtype=np.float16)
-        S, H, N, DK = q.shape; Sk, Hk, KV, _ = k.shape; DV = v.shape[-1]
+        S, H, N, DK = q.shape
+        if kv_type is None:
+            k = np.ascontiguousarray(k, dtype=np.float16); v = np.ascontiguousarray(v, dtype=np.float16)
+            Sk, Hk, KV, _ = k.shape; DV = v.shape[-1]
+            tk = tv = F16
+        else:
+            tk, tv = kv_type if isinstance(kv_type, (tuple, list)) else (kv_type, kv_type)
+            Sk, Hk, KV, _, DV = kv_shape
+            k = np.ascontiguousarray(k, dtype=np.uint8); v = np.ascontiguousarray(v, dtype=np.uint8)
         dq = self.upload(F32, [DK, N, H, S], q)
-        dk = self.upload(F16, [DK, KV, Hk, Sk], k)
-        dv = self.upload(F16, [DV, KV, Hk, Sk], v)
+        dk = self.upload(tk, [DK, KV, Hk, Sk], k)
+        dv = self.upload(tv, [DV, KV, Hk, Sk], v)
         dm = ds = None
         if mask is not None:
             mask = np.ascontiguousarray(mask, dtype=np.float16); Sm, Hm, Nm, _ = mask.shape

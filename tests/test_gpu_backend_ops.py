@@ -65,7 +65,7 @@ def test_backend_ops_mul_mat_id():
 
 def test_backend_ops_flash_attn_ext():
     rc, txt = run_harness("FLASH_ATTN_EXT", timeout=3000)
-    must = lambda l: "type_KV=f16" in l and re.search(r"hsk=(64|128),", l) and re.search(r"hsv=(64|128),", l)
+    must = lambda l: re.search(r"type_KV=(f16|q8_0|q4_0)", l) and re.search(r"hsk=(64|128),", l) and re.search(r"hsv=(64|128),", l)   # (quantized caches: b200_fattn_q.cu)
     ok, passed, total, fail, holes = summarize(txt, must)
     assert rc == 0 and passed == total and not fail, "\n".join(fail[:20])
     assert not holes, "north-star FLASH_ATTN_EXT cases declined:\n" + "\n".join(holes[:20])

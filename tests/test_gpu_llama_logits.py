@@ -58,6 +58,32 @@ def test_llama_logits_without_flash_attention():
     _run_case("tinyllama", "q4_0", 4, 250, 1, {"LOGITS_PROBE_NO_FA": "1"})
 
 
+@pytest.mark.parametrize("ctk,ctv", [("q8_0", "q8_0"), ("q4_0", "q4_0")])
+def test_llama_logits_quantized_kv_cache(ctk, ctv):
+    """-ctk / -ctv: the KV cache holds q8_0 / q4_0 blocks.  SET_ROWS quantizes the new K / V rows on the device
+    (b200_glue.cu: k_set_rows_q), the prompt's FLASH_ATTN_EXT expands the views to f16 in front of the tensor-core kernel, the decode
+    steps read the blocks in place (b200_fattn_q.cu); ggml-cpu runs the same graph with its own quantized-cache attention."""
+    if not os.path.exists(PROBE):
+        pytest.skip("oracle/_ref/avx2/logits_probe not built")
+    os.makedirs(OUT, exist_ok=True)
+    gguf = os.path.join(OUT, f"probe-8b-q4_k_m-{ctk}.gguf")
+    subprocess.check_call([os.sys.executable, os.path.join(ROOT, "scripts", "make_gguf.py"), "--model", "8b", "--quant", "q4_k_m", "--layers", "3", "-o", gguf], stdout=subprocess.DEVNULL)
+    env = {"LOGITS_PROBE_CTK": ctk, "LOGITS_PROBE_CTV": ctv}
+    try:
+        cpu, _ = run_probe(gguf, "cpu_kvq", 0, dict(env))
+        dev, log = run_probe(gguf, "b200_kvq", 99, dict(env, GGML_B200_GRAPH_STATS="1"))
+        f16, _ = run_probe(gguf, "b200_f16kv", 99)
+    finally:
+        os.remove(gguf)
+    assert np.isfinite(cpu).all() and np.isfinite(dev).all() and cpu.std() > 1e-3
+    errs = [nmse(cpu[i], dev[i]) for i in range(1 + N_DECODE)]
+    assert max(errs) < 2e-3, errs
+    assert not np.array_equal(dev, f16)                                   # the cache type really reached the graph
+    # the whole graph stayed on the device: decode steps were recorded into CUDA graphs and replayed
+    rec = [l for l in log.splitlines() if "recorded" in l and "replayed" in l]
+    assert rec and int(rec[-1].split(" replayed")[0].split()[-1]) >= N_DECODE - 4, log[-2000:]
+
+
 @pytest.mark.parametrize("ndev", [2, 4])
 def test_llama_logits_split_mode_row(ndev):
     """-sm row (src/llama-model.cpp:393-411): the weight matrices live in the plugin's split buffer type, rows divided among `ndev` devices
