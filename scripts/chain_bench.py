@@ -26,6 +26,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--model", default="8b"); ap.add_argument("--mix", default="q4_k_m"); ap.add_argument("--layers", type=int, default=8)
 ap.add_argument("--reps", type=int, default=20); ap.add_argument("--ncu", action="store_true"); ap.add_argument("--tag", default="")
 ap.add_argument("--no-separate", action="store_true"); ap.add_argument("--trace", action="store_true")
+ap.add_argument("--norm-outputs", action="store_true", help="also store the RMS_NORM / MUL node values (dead in the real graph): the kernel then takes the plain hand-over")
 a = ap.parse_args()
 n_embd, n_ff, n_kv = DIMS[a.model]
 ctx = B.Context(0); rng = np.random.default_rng(0)
@@ -43,7 +44,7 @@ for il in range(2 if a.ncu else a.layers):
     tv = td = B.Q6_K if more else B.Q4_K
     W = {"wo": weight(B.Q4_K, n_embd, n_embd), "gate": weight(B.Q4_K, n_embd, n_ff), "up": weight(B.Q4_K, n_embd, n_ff), "down": weight(td, n_ff, n_embd),
          "q": weight(B.Q4_K, n_embd, n_embd), "k": weight(B.Q4_K, n_embd, n_kv), "v": weight(tv, n_embd, n_kv)}
-    lc = LayerChain(ctx, n_embd, n_ff, n_kv, W, np.ones(n_embd, np.float32), np.ones(n_embd, np.float32))
+    lc = LayerChain(ctx, n_embd, n_ff, n_kv, W, np.ones(n_embd, np.float32), np.ones(n_embd, np.float32), norm_outputs=a.norm_outputs)
     lc.set_inputs(rng.standard_normal(n_embd).astype(np.float32), rng.standard_normal(n_embd).astype(np.float32))
     layers.append(lc)
 ctx.synchronize()

@@ -23,6 +23,13 @@
 //     A second hand-over form is kept behind GGML_B200_CHAIN_HANDOVER=ll: the validity flag INSIDE the data (8-byte (value, tag)
 //     stores are single transactions, the reader polls the data itself, the residual stays in registers, gate / up's epilogue publishes
 //     q8_1 blocks so that ffn_down fetches 1.25 bytes per activation).  It measured no faster (see ch_force_barrier) and is not the default.
+//   * owner-side hand-over (default where the chain has the llama shape; CH_IN_BQ8 / CH_IN_BQ8N): a boundary cost 4.5-6 us with every CTA
+//     fetching the whole f32 column (57 KB per CTA in front of ffn_down: 8.5 MB of L2 traffic), normalising and quantizing it 148 times over
+//     (profiles/r2_run2_chain_bench_trace.txt: publish 1.5-2.8, wait 0.9, build 2.0-2.5 us).  Now the CTA that OWNS 32 consecutive result rows
+//     -- a whole q8_1 block of the next phase's activation -- finishes them itself: residual ADD (the residual of its rows lives in a
+//     register for the whole launch), multiplication with the norm weight, sum of squares of its rows, q8_1 quantization, and publishes
+//     32 quants + (d, sum) + the partial sum of squares.  RMS_NORM's scale is one scalar of the whole column: q8_1(scale * y) has the quants
+//     of q8_1(y) and the block scale scale * d, so the readers add up K / 32 partial sums, fetch 1.25 bytes per activation and only rescale d.
 // Bound: HBM.  Algorithmic bytes = sum over the chain's weights of M * K * bytes_per_block / 256.
 #include "b200_common.cuh"
 #include "b200_ptx.cuh"
@@ -45,7 +52,17 @@
 enum { CH_IN_EXTERNAL = 0,   // written before this launch: plain loads
        CH_IN_BARRIER  = 1,   // written by the phase before, plain f32: grid-wide arrival counter, then plain loads (general fallback)
        CH_IN_LL_F32   = 2,   // (value, tag) pairs of the phase before
-       CH_IN_LL_Q8    = 3 }; // q8_1 blocks of the SWIGLU phase before (10 (word, tag) pairs per block) + (value, tag) pairs of its tail rows
+       CH_IN_LL_Q8    = 3,   // q8_1 blocks of the SWIGLU phase before (10 (word, tag) pairs per block) + (value, tag) pairs of its tail rows
+       CH_IN_BQ8      = 4,   // arrival counter, then plain loads of the q8_1 blocks the SWIGLU phase before quantized itself (+ its f32 tail rows)
+       CH_IN_BQ8N     = 5 }; // arrival counter, then q8_1 blocks of (result + residual) * norm weight and per-block sums of squares from the row owners
+// (The two owner-side forms were also tried with the validity flag in the data -- 12 (word, tag) pairs per block, no fence in the producer, no
+// counter, the readers poll the records: 47.0 against 44.0 us per 8B layer in the same build.  148 x 512 polling threads compete with the
+// producers' stores, and the poll loops cost the kernel 14 registers.  Removed.)
+// hand-over area of a phase in the owner-side forms: 32 quants per block | (d f32, sum i32) per block | sum of squares per block | f32 tail rows
+#define CH_HQ    0
+#define CH_HDS   (64 * 1024)
+#define CH_HSS   (80 * 1024)
+#define CH_HTAIL (96 * 1024)
 
 struct ch_seg { const uint8_t * w; size_t nb1; float * dst; int M; int q6; int map; };      // map: index of the weight's 2-D tensor map
 struct ch_phase {
@@ -55,9 +72,11 @@ struct ch_phase {
     float * out_add, * out_norm, * out_mul, * glu;
     float eps;
     // units of CH_R rows (SWIGLU: CH_R rows of gate AND of up).  Units [0, ng8) go to the CTAs in groups of 8 consecutive units (32 rows
-    // = whole q8_1 blocks: only there a CTA can quantize its own results), gpc groups each; units [ng8, nunits) one by one, round-robin
-    int nunits, ng8, gpc;
-    int off;               // group g belongs to CTA (g + off) % G, tail unit u to CTA (u - ng8 + off) % G
+    // = whole q8_1 blocks: only there a CTA can quantize its own results), ngrp = ng8 / 8 groups in all; units [ng8, nunits) one by one, round-robin
+    int nunits, ng8, ngrp;
+    int off, toff;         // group g belongs to CTA (g + off) % G, tail unit u to CTA (u - ng8 + toff) % G
+    // CH_IN_BQ8N as out_mode: what the NEXT phase's ADD + RMS_NORM + MUL need from the row owner
+    const float * nx_normw, * nx_in1; float * nx_out_add;
     int nch;               // K / 2048
     unsigned nch_inv;      // ceil(65536 / nch): x / nch == (x * nch_inv) >> 16 for x < 4096
     int types;             // bit 0: a q4_K activation image is needed, bit 1: a q6_K one
@@ -70,6 +89,7 @@ struct ch_args {
     ch_phase ph[CH_MAXPH];
     int nph, slot_bytes, nslot, act_bytes;
     int pre_in1;           // the phase whose addend (in1) comes from outside the launch and is fetched at the very start, or -1
+    int own_in1;           // CH_IN_BQ8N: the producing phase whose row owners fetch their rows of an addend from outside at the very start, or -1
     unsigned * sync;       // [0] phase arrivals (CH_IN_BARRIER), [1] CTAs done, [2] error code, [3] hand-over epoch, [4] abort
     uint8_t * ll;          // hand-over areas, CH_LL_BYTES per phase
     int dbg;               // GGML_B200_CHAIN_DBG (measurement only): 1 skip the dot products, 2 no weight traffic
@@ -116,10 +136,36 @@ static __device__ __forceinline__ uint4 ch_ll_load2(const void * p) {      // tw
 template <int NT> static __device__ __forceinline__ void ch_bar_n() { asm volatile("bar.sync 1, %0;" :: "n"(NT) : "memory"); }
 #define ch_bar_consumers() ch_bar_n<CH_NT>()
 
-// local unit k of a CTA -> global unit (see ch_phase); fg / ft = the CTA's first group / first tail unit
-static __device__ __forceinline__ int ch_unit(const ch_phase & ph, int k, int fg, int ft, int G) {
-    const int kg = ph.gpc * 8;
-    return k < kg ? ((k >> 3) * G + fg) * 8 + (k & 7) : ph.ng8 + ft + (k - kg) * G;
+// what a CTA owns of a phase: fg / ft = its first group / first tail unit, gl = its whole groups, nu = its units
+struct ch_own { int fg, ft, gl, nu; };
+static __device__ __forceinline__ ch_own ch_owned(const ch_phase & ph, int cta, int G) {
+    ch_own o;
+    o.fg = cta - ph.off;  if (o.fg < 0) o.fg += G;
+    o.ft = cta - ph.toff; if (o.ft < 0) o.ft += G;
+    o.gl = o.fg < ph.ngrp ? (ph.ngrp - o.fg + G - 1) / G : 0;
+    const int nt = ph.nunits - ph.ng8;
+    o.nu = o.gl * 8 + (o.ft < nt ? (nt - o.ft + G - 1) / G : 0);
+    return o;
+}
+// local unit k of a CTA -> global unit (see ch_phase)
+static __device__ __forceinline__ int ch_unit(const ch_phase & ph, int k, const ch_own & o, int G) {
+    const int kg = o.gl * 8;
+    return k < kg ? ((k >> 3) * G + o.fg) * 8 + (k & 7) : ph.ng8 + o.ft + (k - kg) * G;
+}
+static __device__ __forceinline__ int4 ch_ldcg_i4(const void * p) {
+    int4 r;
+    asm volatile("ld.global.cg.v4.s32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+static __device__ __forceinline__ int2 ch_ldcg_i2(const void * p) {
+    int2 r;
+    asm volatile("ld.global.cg.v2.s32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+    return r;
+}
+static __device__ __forceinline__ float ch_ldcg_f(const void * p) {
+    float r;
+    asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(r) : "l"(p));
+    return r;
 }
 // unit -> (segment, first row inside it); PLAIN phases concatenate the segments' rows, SWIGLU phases pair them (sg = tile parity)
 static __device__ __forceinline__ void ch_locate(const ch_phase & ph, int u, int & sg, int & row) {
@@ -191,7 +237,7 @@ static __device__ __forceinline__ void ch_consume_q4k(uint32_t st, int lane, uin
     }
 }
 
-template <int CH_NW>
+template <int CH_NW, bool TR>      // TR: the measurement hooks (b200_debug_trace, GGML_B200_CHAIN_DBG) are compiled in
 __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_constant__ ch_args P) {
     constexpr int CH_NT = CH_NW * 32;
     extern __shared__ __align__(128) uint8_t smem[];
@@ -224,20 +270,18 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
         int n = 0;
         if (p < P.nph) {
             const ch_phase & ph = P.ph[p];
-            int ft = cta - ph.off; if (ft < 0) ft += G;
-            const int nt = ph.nunits - ph.ng8, nu = ph.gpc * 8 + (ft < nt ? (nt - ft + G - 1) / G : 0);
-            n = nu * (ph.epilogue == B200_CHAIN_Y_SWIGLU ? 2 : 1) * ph.nch;
+            n = ch_owned(ph, cta, G).nu * (ph.epilogue == B200_CHAIN_Y_SWIGLU ? 2 : 1) * ph.nch;
         }
         cum[p + 1] = cum[p] + n;
     }
-    const int total = (P.dbg & 2) ? 0 : cum[CH_MAXPH];
+    const int total = (TR && (P.dbg & 2)) ? 0 : cum[CH_MAXPH];
     // stage sl of phase ph -> (segment, first row, K chunk, local unit): no division (nch_inv), SWIGLU tiles alternate gate / up
     auto decode = [&](const ch_phase & ph, int sl, int & sg, int & row, int & c, int & k) {
         const int tile = (int) (((unsigned) sl * ph.nch_inv) >> 16);
         c = sl - tile * ph.nch;
-        int f = cta - ph.off; if (f < 0) f += G;
-        if (ph.epilogue == B200_CHAIN_Y_SWIGLU) { k = tile >> 1; sg = tile & 1; row = ch_unit(ph, k, f, f, G) * CH_R; }
-        else { k = tile; ch_locate(ph, ch_unit(ph, k, f, f, G), sg, row); }
+        const ch_own o = ch_owned(ph, cta, G);
+        if (ph.epilogue == B200_CHAIN_Y_SWIGLU) { k = tile >> 1; sg = tile & 1; row = ch_unit(ph, k, o, G) * CH_R; }
+        else { k = tile; ch_locate(ph, ch_unit(ph, k, o, G), sg, row); }
     };
     // The stage table: what stage s of this CTA fetches and for whom, worked out ONCE by as many threads as there are stages (the walk from
     // a stage number to its tensor coordinates is ~120 dependent instructions; done at every refill by one lane it was a fifth of the loop).
@@ -256,19 +300,21 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
         const uint32_t e = s_tab[s];
         const uint32_t cb = (e >> 21) & 1u ? CH_Q6K_CHUNK : CH_Q4K_CHUNK;
         const uint32_t bar = full0 + 8 * slot, dst = ring + slot * P.slot_bytes;
-        if (P.trace && cta == 0 && s < 1024) P.trace[32 * (1 + P.trace_cap) + 1024 + s] = ch_now();   // (measurement only)
+        if (TR && P.trace && cta == 0 && s < 1024) P.trace[32 * (1 + P.trace_cap) + 1024 + s] = ch_now();   // (measurement only)
         mbar_arrive_expect_tx(bar, cb * CH_R);
         tma_load_2d(dst, &P.map[(e >> 18) & 7u], (int) (((e >> 22) & 31u) * (cb >> 3)), (int) (e & 0x3ffffu), bar);
     };
     // first lap: weights do not depend on the kernel in front (PDL): the ring fills under its tail
     if (lane == 0) for (int q = warp; q < P.nslot && q < total; q += CH_NW) issue(q, q);
-    // this warp's cursor in the stage sequence: it owns the slots q with q % CH_NW == warp and meets them lap after lap
+    // this warp's cursor in the stage sequence: it owns the slots q with q % CH_NW == warp and meets them lap after lap.  (Stages dealt
+    // round-robin over the warps instead -- slot s % nslot handed from warp to warp behind a per-slot "lap issued" word -- measured 2-3 us per
+    // layer SLOWER although it balances short phases: a slow warp then stalls the warp that inherits its slot.)
     int my_slot = warp, my_lap = 0;
 
     // ------------------------------------------------ the phases ------------------------------------------------
     unsigned long long * rec = nullptr;               // (measurement only) words 2 + 5 p + j: phase p entered, input complete, image built, stages done, published
-    if (P.trace && tid == 0) rec = b200_trace_open(P.trace, P.trace_cap, P.nph, 0xC4A1);
-#define CH_STAMP(j) do { if (rec) rec[2 + 5 * p + (j)] = ch_now(); } while (0)
+    if (TR && P.trace && tid == 0) rec = b200_trace_open(P.trace, P.trace_cap, P.nph, 0xC4A1);
+#define CH_STAMP(j) do { if (TR && rec) rec[2 + 5 * p + (j)] = ch_now(); } while (0)
     int s_base = 0;                                   // stages of this CTA before the current phase
     unsigned target = 0, tag = 0;
     // this thread's 16 values of the NEXT residual ADD's addend: fetched right at the start when it comes from outside, afterwards the sum
@@ -277,13 +323,21 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
     float hkeep[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) hkeep[i] = 0.0f;
+    // owner-side hand-over (CH_IN_BQ8N): thread t < 32 * (groups of this CTA) is row t of those groups in every producing phase -- same rows
+    // each time -- and carries that row's residual from one ADD to the next in a register
+    float keep = 0.0f;
     for (int p = 0; p < P.nph; ++p) {
         const ch_phase & ph = P.ph[p];
         const int K = ph.K, nblocks = K >> 8, nu16 = K >> 4;
+        const ch_own own = ch_owned(ph, cta, G);
         CH_STAMP(0);
         // what does not depend on the phase before is fetched ahead of the hand-over: the norm weight, and a residual from outside
         // (every CTA reads the same lines at the same moment: ~9 B/clk per SM of L2 broadcast bandwidth, measured -- bytes on the critical path count)
-        const bool normp = ph.prologue != B200_CHAIN_X_PLAIN, addp = ph.prologue == B200_CHAIN_X_ADD_NORM_MUL, live = normp && tid < nu16;
+        const bool own_in = ph.in_mode == CH_IN_BQ8N;            // the row owners of the phase before did ADD, norm weight and quantization
+        const bool normp = ph.prologue != B200_CHAIN_X_PLAIN && !own_in, addp = ph.prologue == B200_CHAIN_X_ADD_NORM_MUL && !own_in, live = normp && tid < nu16;
+        const bool own_out = ph.out_mode == CH_IN_BQ8N && tid < own.gl * 32;      // (warp-uniform: whole groups)
+        float nwpre = 0.0f;                                      // the next phase's norm weight of this thread's row
+        if (own_out) nwpre = __ldg(ph.nx_normw + ch_unit(ph, tid >> 2, own, G) * CH_R + (tid & 3));
         float4 gpre[4], bpre[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -298,6 +352,11 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
 #pragma unroll
                 for (int j = 0; j < 4; ++j) { const float4 v = ch_ldcg4(P.ph[P.pre_in1].in1 + (size_t) tid * 16 + 4 * j); hkeep[4 * j] = v.x; hkeep[4 * j + 1] = v.y; hkeep[4 * j + 2] = v.z; hkeep[4 * j + 3] = v.w; }
             }
+            if (P.own_in1 >= 0) {                             // the first owner-side ADD's addend comes from outside: this thread's row of it
+                const ch_phase & pq = P.ph[P.own_in1];
+                const ch_own oq = ch_owned(pq, cta, G);
+                if (tid < oq.gl * 32) keep = ch_ldcg_f(pq.nx_in1 + ch_unit(pq, tid >> 2, oq, G) * CH_R + (tid & 3));
+            }
         }
         if (live && addp) {
             if (ph.in1_kept || p == P.pre_in1) {
@@ -309,7 +368,7 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
             }
         }
         // (1) CH_IN_BARRIER only: every CTA has stored and released the results of the phase before
-        if (ph.in_mode == CH_IN_BARRIER) {
+        if (ph.in_mode == CH_IN_BARRIER || ph.in_mode == CH_IN_BQ8 || ph.in_mode == CH_IN_BQ8N) {
             if (tid == 0) {
                 ch_watch w; unsigned v;
                 while (true) {
@@ -323,7 +382,74 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
         CH_STAMP(1);
         // (2) this CTA's q8_1 image of the activation column
         const uint8_t * llin = P.ll + (size_t) (p > 0 ? p - 1 : 0) * CH_LL_BYTES;
-        if (!normp && ph.in_mode == CH_IN_LL_Q8) {
+        if (own_in) {
+            // (result + residual) * norm weight arrives as q8_1 blocks whose scale still lacks RMS_NORM's factor; the block sums of squares give it.
+            // This thread's units (K <= 64 CH_NT) are in flight while the sum is reduced
+            const uint8_t * hq = llin + CH_HQ, * hds = llin + CH_HDS, * hss = llin + CH_HSS;
+            int4 w[4]; int2 ds[4];
+            float ssp = 0.0f;
+            {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int u = tid + i * CH_NT;
+                    w[i] = make_int4(0, 0, 0, 0); ds[i] = make_int2(0, 0);
+                    if (u < nu16) { w[i] = ch_ldcg_i4(hq + (size_t) u * 16); ds[i] = ch_ldcg_i2(hds + (size_t) (u >> 1) * 8); }
+                }
+                for (int b = tid; b < (K >> 5); b += CH_NT) ssp += ch_ldcg_f(hss + (size_t) b * 4);
+            }
+            ssp = warp_sum(ssp);
+            if (lane == 0) s_red[warp] = ssp;
+            ch_bar_consumers();
+            float tot = 0.0f;
+#pragma unroll
+            for (int i = 0; i < CH_NW; ++i) tot += s_red[i];
+            const float scale = rsqrtf(tot / (float) K + ph.eps);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int u = tid + i * CH_NT;
+                if (u < nu16) {
+                    const float d = __int_as_float(ds[i].x) * scale;
+                    ch_store_unit(u, w[i], __half2float(__float2half_rn(d)), __half2float(__float2half_rn(__fmul_rn(d, (float) ds[i].y))), K, nblocks, ph.types, s_act);
+                }
+            }
+        } else if (ph.in_mode == CH_IN_BQ8) {
+            // the SWIGLU phase before quantized its own 32-row blocks: 32 quants + (d, sum) per block, plain loads behind the arrival counter
+            const int nq16 = ph.nq8 >> 4;
+            const uint8_t * hq = llin + CH_HQ, * hds = llin + CH_HDS;
+            for (int u0 = tid; u0 < nq16; u0 += 4 * CH_NT) {
+                int4 w[4]; int2 ds[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int u = u0 + i * CH_NT;
+                    w[i] = make_int4(0, 0, 0, 0); ds[i] = make_int2(0, 0);
+                    if (u < nq16) { w[i] = ch_ldcg_i4(hq + (size_t) u * 16); ds[i] = ch_ldcg_i2(hds + (size_t) (u >> 1) * 8); }
+                }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int u = u0 + i * CH_NT;
+                    if (u < nq16) {
+                        const float d = __int_as_float(ds[i].x);
+                        ch_store_unit(u, w[i], __half2float(__float2half_rn(d)), __half2float(__float2half_rn(__fmul_rn(d, (float) ds[i].y))), K, nblocks, ph.types, s_act);
+                    }
+                }
+            }
+            // its tail rows (not whole blocks per CTA) come as f32: at most a few units, one warp
+            const int ntail16 = nu16 - nq16;
+            if (ntail16 > 0 && warp == CH_NW - 1) {
+                const float * tl = (const float *) (llin + CH_HTAIL);
+                for (int u0 = 0; u0 < ntail16; u0 += 32) {
+                    const int u = u0 + lane; const bool on = u < ntail16;
+                    float f[16];
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) f[i] = 0.0f;
+                    if (on) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) { const float4 v = ch_ldcg4(tl + (size_t) u * 16 + 4 * j); f[4 * j] = v.x; f[4 * j + 1] = v.y; f[4 * j + 2] = v.z; f[4 * j + 3] = v.w; }
+                    }
+                    ch_quant_store(f, lane, nq16 + u, on, K, nblocks, ph.types, s_act);
+                }
+            }
+        } else if (!normp && ph.in_mode == CH_IN_LL_Q8) {
             // the SWIGLU phase before quantized its own 32-row blocks: 10 (word, tag) pairs per block (8 quant words, (d, s), pad)
             const int nq16 = ph.nq8 >> 4;
             for (int u = tid; u < nq16; u += CH_NT) {
@@ -457,8 +583,7 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
         if (p == P.nph - 1) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
         // (3) this warp's stages of the phase
-        int f0 = cta - ph.off; if (f0 < 0) f0 += G;
-        const int ntl = ph.nunits - ph.ng8, nunits_l = ph.gpc * 8 + (f0 < ntl ? (ntl - f0 + G - 1) / G : 0);
+        const int nunits_l = own.nu;
         const int nst = total ? cum[p + 1] - cum[p] : 0;
         const uint32_t act4 = smem_u32(s_act), act6 = act4 + ((ph.types & 1) ? (uint32_t) gs_traits<B200_TYPE_Q4_K>::act_bytes(K) : 0u);
         // A ring slot always belongs to the same warp (slot % CH_NW), whatever the lap: a warp then meets the laps of a slot in order, and its
@@ -470,7 +595,7 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
             const bool q6 = (e >> 21) & 1u;
             const int c = (int) ((e >> 22) & 31u);
             ch_mbar_wait(full0 + 8 * my_slot, (uint32_t) my_lap & 1u, P.sync, 0x300u + p);
-            if (P.trace && cta == 0 && lane == 0 && s < 1024) P.trace[32 * (1 + P.trace_cap) + s] = ch_now();   // (measurement only)
+            if (TR && P.trace && cta == 0 && lane == 0 && s < 1024) P.trace[32 * (1 + P.trace_cap) + s] = ch_now();   // (measurement only)
             const uint32_t st = ring + my_slot * P.slot_bytes;
             float a0, a1;                              // this lane's sums of rows 2 (lane >> 4) + {0, 1}
             if (q6) {
@@ -478,7 +603,7 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
 #pragma unroll
                 for (int r = 0; r < CH_R; ++r) acc[r] = 0.0f;
                 const int bl = lane & 7, gb = c * GS_CB + bl;
-                if (!(P.dbg & 1)) gs_traits<B200_TYPE_Q6_K>::consume<CH_R, CH_R>(st, CH_Q6K_CHUNK, bl, gb, lane, act6, K, nblocks, acc);
+                if (!(TR && (P.dbg & 1))) gs_traits<B200_TYPE_Q6_K>::consume<CH_R, CH_R>(st, CH_Q6K_CHUNK, bl, gb, lane, act6, K, nblocks, acc);
                 // every lane has all four rows: halve the number of values a lane carries
                 const bool hi16 = lane & 16;
                 a0 = hi16 ? acc[2] : acc[0]; a1 = hi16 ? acc[3] : acc[1];
@@ -486,7 +611,7 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
                 a0 += __shfl_xor_sync(0xffffffffu, b0, 16); a1 += __shfl_xor_sync(0xffffffffu, b1, 16);   // lanes < 16: rows 0, 1; lanes >= 16: rows 2, 3
             } else {
                 float acc[2] = { 0.0f, 0.0f };
-                if (!(P.dbg & 1)) ch_consume_q4k(st, lane, act4, K, nblocks, c, acc);
+                if (!(TR && (P.dbg & 1))) ch_consume_q4k(st, lane, act4, K, nblocks, c, acc);
                 a0 = acc[0]; a1 = acc[1];
             }
             __syncwarp();                              // every lane is done reading the slot
@@ -510,9 +635,9 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
                 const int k = t / CH_R, r = t - k * CH_R;
                 gsum = 0.0f; usum = 0.0f;
                 for (int c = 0; c < ph.nch; ++c) { gsum += s_psum[((2 * k) * ph.nch + c) * CH_R + r]; usum += s_psum[((2 * k + 1) * ph.nch + c) * CH_R + r]; }
-                return ch_unit(ph, k, f0, f0, G) * CH_R + r;
+                return ch_unit(ph, k, own, G) * CH_R + r;
             };
-            const int nrow_g = ph.out_mode == CH_IN_LL_Q8 ? ph.gpc * 32 : 0;
+            const int nrow_g = (ph.out_mode == CH_IN_LL_Q8 || ph.out_mode == CH_IN_BQ8) ? own.gl * 32 : 0;
             // the CTA's whole 32-row blocks: one warp per block, lane = row: gate, up, glu, and the block's q8_1 form for ffn_down
             for (int b0 = warp * 32; b0 < nrow_g; b0 += CH_NT) {
                 float gsum, usum;
@@ -524,9 +649,14 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
                 unsigned wq = (unsigned) q & 0xffu;
                 wq |= __shfl_down_sync(0xffffffffu, wq, 1) << 8;
                 wq |= __shfl_down_sync(0xffffffffu, wq, 2) << 16;
-                uint8_t * blk = llout + (size_t) (row >> 5) * 80;         // (the warp's 32 rows are one aligned block)
-                if ((lane & 3) == 0) ch_ll_store(blk + (lane >> 2) * 8, wq, tag);
-                if (lane == 1) { const __half2 ds = q8_1_ds(d, isum); ch_ll_store(blk + 64, *(const unsigned *) &ds, tag); }
+                if (ph.out_mode == CH_IN_BQ8) {                            // (the warp's 32 rows are one aligned block)
+                    if ((lane & 3) == 0) *(unsigned *) (llout + CH_HQ + (size_t) (row >> 5) * 32 + lane) = wq;
+                    if (lane == 1) *(int2 *) (llout + CH_HDS + (size_t) (row >> 5) * 8) = make_int2(__float_as_int(d), isum);
+                } else {
+                    uint8_t * blk = llout + (size_t) (row >> 5) * 80;
+                    if ((lane & 3) == 0) ch_ll_store(blk + (lane >> 2) * 8, wq, tag);
+                    if (lane == 1) { const __half2 ds = q8_1_ds(d, isum); ch_ll_store(blk + 64, *(const unsigned *) &ds, tag); }
+                }
             }
             for (int t = nrow_g + tid; t < nunits_l * CH_R; t += CH_NT) {
                 float gsum, usum;
@@ -535,18 +665,41 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
                 ph.seg[0].dst[row] = gsum; ph.seg[1].dst[row] = usum; ph.glu[row] = v;
                 if (ph.out_mode == CH_IN_LL_F32) ch_ll_store(llout + (size_t) row * 8, __float_as_uint(v), tag);
                 else if (ph.out_mode == CH_IN_LL_Q8) ch_ll_store(llout + (size_t) (ph.ng8 * CH_R >> 5) * 80 + (size_t) (row - ph.ng8 * CH_R) * 8, __float_as_uint(v), tag);
+                else if (ph.out_mode == CH_IN_BQ8) *(float *) (llout + CH_HTAIL + (size_t) (row - ph.ng8 * CH_R) * 4) = v;
+            }
+        } else if (ph.out_mode == CH_IN_BQ8N) {
+            // thread = one row of this CTA's groups (whole q8_1 blocks of the next phase's activation; warp = group): the matmul result, the
+            // residual sum h, and h * norm weight as a q8_1 block with the block's sum of squares of h next to it
+            if (own_out) {
+                const int k = tid >> 2, r = tid & 3;
+                float sum = 0.0f;
+                for (int c = 0; c < ph.nch; ++c) sum += s_psum[(k * ph.nch + c) * CH_R + r];
+                const int row = ch_unit(ph, k, own, G) * CH_R + r;
+                ph.seg[0].dst[row] = sum;
+                const float h = sum + keep;
+                if (ph.nx_out_add) ph.nx_out_add[row] = h;
+                keep = h;
+                const float ss = warp_sum(h * h);
+                int q, isum; float d;
+                q8_1_block<B200_Q8_1_X86>(h * nwpre, q, d, isum);
+                unsigned wq = (unsigned) q & 0xffu;
+                wq |= __shfl_down_sync(0xffffffffu, wq, 1) << 8;
+                wq |= __shfl_down_sync(0xffffffffu, wq, 2) << 16;
+                if ((lane & 3) == 0) *(unsigned *) (llout + CH_HQ + (size_t) (row >> 5) * 32 + lane) = wq;
+                if (lane == 1) *(int2 *) (llout + CH_HDS + (size_t) (row >> 5) * 8) = make_int2(__float_as_int(d), isum);
+                if (lane == 2) *(float *) (llout + CH_HSS + (size_t) (row >> 5) * 4) = ss;
             }
         } else {
             for (int t = tid; t < nunits_l * CH_R; t += CH_NT) {
                 const int k = t / CH_R, r = t - k * CH_R;
                 float sum = 0.0f;
                 for (int c = 0; c < ph.nch; ++c) sum += s_psum[(k * ph.nch + c) * CH_R + r];
-                int sg, row; ch_locate(ph, ch_unit(ph, k, f0, f0, G), sg, row);
+                int sg, row; ch_locate(ph, ch_unit(ph, k, own, G), sg, row);
                 ph.seg[sg].dst[row + r] = sum;
                 if (ph.out_mode == CH_IN_LL_F32) ch_ll_store(llout + (size_t) (row + r) * 8, __float_as_uint(sum), tag);   // (single-segment phases only)
             }
         }
-        if (ph.out_mode == CH_IN_BARRIER) {
+        if (ph.out_mode == CH_IN_BARRIER || ph.out_mode == CH_IN_BQ8 || ph.out_mode == CH_IN_BQ8N) {
             ch_bar_consumers();                       // every thread's stores are ordered before thread 0's release (CTA barrier), whose
             if (tid == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" :: "l"(P.sync) : "memory");   // cumulativity makes them visible GPU-wide
             target += (unsigned) G;
@@ -590,8 +743,14 @@ static int ch_nw() { static int v = -1; if (v < 0) { const char * e = getenv("GG
 // --trace): a poll of the data costs a full L2 round trip under the weight stream (~1.2 us) and the first one usually comes too early, so the
 // flag-in-data form (0.5 + 2.6 + 2.3 us per boundary) is no faster than release / acquire on one counter (1.5 + 1.3 + 2.0 us).
 static bool ch_force_barrier() { static int v = -1; if (v < 0) { const char * e = getenv("GGML_B200_CHAIN_HANDOVER"); v = !(e && e[0] == 'l'); } return v != 0; }
+// GGML_B200_CHAIN_OWNER=0 (measurement only) keeps every boundary in the plain form: f32 column through memory, every CTA normalises and quantizes it
+static bool ch_owner_on() { static int v = -1; if (v < 0) { const char * e = getenv("GGML_B200_CHAIN_OWNER"); v = !(e && e[0] == '0'); } return v != 0; }
+// whole 32-row groups dealt round-robin over G CTAs: the busiest CTA may carry at most 16 % more than the average
+static bool ch_groups_balanced(int ngroups, int G) { const int per = (ngroups + G - 1) / G; return ngroups > 0 && (long long) per * G * 100 <= (long long) ngroups * 116 && per <= 16; }
 
 // fills the kernel arguments; B200_ERR_UNSUPPORTED (with a reason) when the chain is not one this kernel takes
+static size_t kb_of(int K) { return (size_t) K * 4; }
+static bool ch_is_own_norm(int mode) { return mode == CH_IN_BQ8N; }
 static int ch_build(b200_ctx * ctx, const b200_chain_phase * phases, int n, ch_args & A, size_t & smem) {
     if (!phases || n < 1 || n > CH_MAXPH) { b200_set_error("decode_chain: 1..%d phases", CH_MAXPH); return B200_ERR_UNSUPPORTED; }
     const int G = ctx->sm_count, nw = ch_nw();
@@ -659,13 +818,15 @@ static int ch_build(b200_ctx * ctx, const b200_chain_phase * phases, int n, ch_a
     // else that was written earlier in this launch forces the fence-and-counter form for the whole chain.
     bool ll = !ch_force_barrier();
     int last_add = -1;
-    A.pre_in1 = -1;
+    A.pre_in1 = -1; A.own_in1 = -1;
+    int dkind[CH_MAXPH] = {}, in1_class[CH_MAXPH] = {}, add_before[CH_MAXPH] = {};   // in0 = the phase before's single result (1) / glu (2); addend: outside (0), the last ADD's sum (1), other (2)
     for (int p = 0; p < n; ++p) {
         const b200_chain_phase & s = phases[p];
         ch_phase & d = A.ph[p];
         const size_t kb = (size_t) d.K * 4;
         d.in_mode = CH_IN_EXTERNAL; d.in1_kept = 0;
         bool in1_inside = false;
+        add_before[p] = last_add;
         for (int q = 0; q < p; ++q) {
             const b200_chain_phase & e = phases[q];
             const b200_tensor * outs[7] = { e.dst[0], e.n_w > 1 ? e.dst[1] : nullptr, e.n_w > 2 ? e.dst[2] : nullptr, e.out_add, e.out_norm, e.out_mul, e.glu };
@@ -675,6 +836,7 @@ static int ch_build(b200_ctx * ctx, const b200_chain_phase * phases, int n, ch_a
                     const bool direct = q == p - 1 && s.in0->data == outs[o]->data &&
                                         ((o == 0 && e.n_w == 1 && e.epilogue == B200_CHAIN_Y_PLAIN) || (o == 6 && e.epilogue == B200_CHAIN_Y_SWIGLU));
                     d.in_mode = CH_IN_BARRIER;
+                    if (direct) dkind[p] = o == 0 ? 1 : 2;
                     if (direct && ll) d.in_mode = (o == 6 && s.prologue == B200_CHAIN_X_PLAIN && d.K % 32 == 0) ? CH_IN_LL_Q8 : CH_IN_LL_F32;
                     else ll = false;
                 }
@@ -685,6 +847,7 @@ static int ch_build(b200_ctx * ctx, const b200_chain_phase * phases, int n, ch_a
                 if (q < p - 1 && s.normw && ch_overlap(s.normw->data, kb, outs[o])) ll = false;
             }
         }
+        in1_class[p] = d.in1_kept ? 1 : in1_inside ? 2 : 0;
         if (s.prologue == B200_CHAIN_X_ADD_NORM_MUL) {
             if (last_add < 0 && !in1_inside && !d.in1_kept) A.pre_in1 = p;        // the chain's first ADD, addend from outside: fetched at the start
             last_add = p;
@@ -701,20 +864,51 @@ static int ch_build(b200_ctx * ctx, const b200_chain_phase * phases, int n, ch_a
             A.ph[p].in_mode = CH_IN_BARRIER;
         }
     }
+    // ---- pass 2b: owner-side hand-over where a boundary has the llama shape (see the head of this file)
+    if (!ll && ch_owner_on()) {
+        int plan[CH_MAXPH] = {}, prev_own = -1;       // prev_own: the phase that produced the last owner-side ADD
+        for (int p = 1; p < n; ++p) {
+            const b200_chain_phase & s = phases[p], & e = phases[p - 1];
+            const ch_phase & d = A.ph[p], & pd = A.ph[p - 1];
+            if (dkind[p] == 2 && s.prologue == B200_CHAIN_X_PLAIN && d.K % 32 == 0) { plan[p] = CH_IN_BQ8; continue; }
+            if (dkind[p] != 1 || s.prologue != B200_CHAIN_X_ADD_NORM_MUL || s.out_norm || s.out_mul || d.K % 32 != 0 || pd.nseg != 1 || !ch_groups_balanced(d.K / 32, G)) continue;
+            // the sum is stored while other CTAs may still read the producing phase's inputs
+            if (s.out_add && (ch_overlap(s.out_add->data, kb_of(d.K), e.in0) || ch_overlap(s.out_add->data, kb_of(d.K), e.in1) || ch_overlap(s.out_add->data, kb_of(d.K), e.normw))) continue;
+            const int ownn = CH_IN_BQ8N;
+            if (in1_class[p] == 0 && add_before[p] < 0 && prev_own < 0) { plan[p] = ownn; prev_own = p - 1; }
+            else if (in1_class[p] == 1 && prev_own >= 0 && add_before[p] == prev_own + 1 && A.ph[prev_own].nunits == pd.nunits) { plan[p] = ownn; prev_own = p - 1; }
+        }
+        // an ADD that expects the last sum in every CTA's registers cannot follow an ADD that only the row owners computed
+        bool ok = true;
+        for (int p = 1; p < n; ++p)
+            if (A.ph[p].in1_kept && !ch_is_own_norm(plan[p]) && add_before[p] >= 1 && ch_is_own_norm(plan[add_before[p]])) ok = false;
+        for (int p = 1; p < n; ++p) {
+            if (!plan[p] || (ch_is_own_norm(plan[p]) && !ok)) continue;
+            const b200_chain_phase & s = phases[p];
+            ch_phase & d = A.ph[p], & pd = A.ph[p - 1];
+            d.in_mode = plan[p]; pd.out_mode = plan[p];
+            if (ch_is_own_norm(plan[p])) {
+                pd.nx_normw = (const float *) s.normw->data; pd.nx_in1 = (const float *) s.in1->data; pd.nx_out_add = s.out_add ? (float *) s.out_add->data : nullptr;
+                if (in1_class[p] == 0) { A.own_in1 = p - 1; if (A.pre_in1 == p) A.pre_in1 = -1; }
+                d.in1_kept = 0;
+            }
+        }
+    }
     // ---- pass 3: who owns which rows
     int stages_total = 0;
     for (int p = 0; p < n; ++p) {
         ch_phase & d = A.ph[p];
-        d.ng8 = 0; d.gpc = 0;
-        if (d.out_mode == CH_IN_LL_Q8) {
-            d.gpc = (d.nunits / 8) / G;               // whole 32-row blocks per CTA; the remainder goes round-robin
-            d.ng8 = d.gpc * G * 8;
-            A.ph[p + 1].nq8 = d.ng8 * CH_R;
-        }
-        d.off = off;
+        d.ng8 = 0; d.ngrp = 0;
+        if (d.out_mode == CH_IN_LL_Q8 || d.out_mode == CH_IN_BQ8) {
+            d.ngrp = (d.nunits / 8) / G * G;          // whole 32-row blocks, the same number for every CTA; the remainder goes round-robin
+            A.ph[p + 1].nq8 = d.ngrp * 8 * CH_R;
+        } else if (ch_is_own_norm(d.out_mode)) d.ngrp = d.nunits / 8;      // every row: the norm needs all sums of squares from the owners
+        d.ng8 = d.ngrp * 8;
+        d.off = 0; d.toff = off;
         off = (off + d.nunits - d.ng8) % G;
+        if (ch_is_own_norm(d.out_mode)) off = d.ngrp % G;                   // round-robin units of the next phase start with the CTAs this one left idle
         const int tpu = d.epilogue == B200_CHAIN_Y_SWIGLU ? 2 : 1;
-        const int stages_max = (d.gpc * 8 + (d.nunits - d.ng8 + G - 1) / G) * tpu * d.nch;
+        const int stages_max = ((d.ngrp + G - 1) / G * 8 + (d.nunits - d.ng8 + G - 1) / G) * tpu * d.nch;
         if (stages_max * CH_R > CH_PSUM || stages_max >= 4096) { b200_set_error("decode_chain: phase %d: %d stages per CTA exceed the partial-sum table", p, stages_max); return B200_ERR_UNSUPPORTED; }
         stages_total += stages_max;
         if (d.nch > 31 || s_rows_max(phases[p]) >= (1 << 18)) { b200_set_error("decode_chain: phase %d: matrix too large for the stage table", p); return B200_ERR_UNSUPPORTED; }
@@ -726,7 +920,7 @@ static int ch_build(b200_ctx * ctx, const b200_chain_phase * phases, int n, ch_a
     int nslot = (int) ((smem_max - fixed) / ((size_t) slot + 8));
     if (nslot > 255) nslot = 255;
     { static int cap = -1; if (cap < 0) { const char * e = getenv("GGML_B200_CHAIN_SLOTS"); cap = e ? atoi(e) : 0; } if (cap > 0 && nslot > cap) nslot = cap; }
-    if (nslot < 16) { b200_set_error("decode_chain: shared memory holds only %d stages", nslot); return B200_ERR_UNSUPPORTED; }
+    if (nslot < nw) { b200_set_error("decode_chain: shared memory holds only %d stages", nslot); return B200_ERR_UNSUPPORTED; }
     A.slot_bytes = slot; A.nslot = nslot; A.act_bytes = act;
     smem = (size_t) nslot * slot + fixed + (size_t) nslot * 8;
     return B200_OK;
@@ -771,8 +965,10 @@ extern "C" int b200_decode_chain(b200_ctx * ctx, const b200_chain_phase * phases
     const int nw = ch_nw();
     static bool attr_done[64] = {};
     if (!attr_done[ctx->device & 63]) {
-        B200_CUDA_TRY(cudaFuncSetAttribute(k_decode_chain<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        B200_CUDA_TRY(cudaFuncSetAttribute(k_decode_chain<24>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        B200_CUDA_TRY(cudaFuncSetAttribute(k_decode_chain<16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        B200_CUDA_TRY(cudaFuncSetAttribute(k_decode_chain<24, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        B200_CUDA_TRY(cudaFuncSetAttribute(k_decode_chain<16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        B200_CUDA_TRY(cudaFuncSetAttribute(k_decode_chain<24, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_done[ctx->device & 63] = true;
     }
     cudaLaunchConfig_t cfg = {};
@@ -784,8 +980,9 @@ extern "C" int b200_decode_chain(b200_ctx * ctx, const b200_chain_phase * phases
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = ctx->pdl ? 1 : 0;
-    if (nw == 24) B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_decode_chain<24>, A));
-    else          B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_decode_chain<16>, A));
+    const bool tr = A.trace != nullptr || A.dbg != 0;
+    if (nw == 24) { if (tr) B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_decode_chain<24, true>, A)); else B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_decode_chain<24, false>, A)); }
+    else          { if (tr) B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_decode_chain<16, true>, A)); else B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_decode_chain<16, false>, A)); }
     for (int p = 0; p < n_phases; ++p) {
         const b200_chain_phase & s = phases[p];
         for (int i = 0; i < s.n_w; ++i) b200_note_write(ctx, s.dst[i]->data, b200_tensor_span(s.dst[i]));

@@ -81,7 +81,7 @@ __global__ void __launch_bounds__(FQ_WARPS * 32) k_fattn_kvq(const fattn_args p,
     const int64_t hk = blockIdx.y, iq3 = blockIdx.z;
     const int nr = min(R, x.rows - rg * R);                  // live rows of this CTA
 
-    // ---- the query rows -> q8_0 (quantize_row_q8_0, ggml-quants.c:200-222): warp w takes rows w, w + FQ_WARPS, ...
+    // ---- the query rows -> q8_0 (quantize_row_q8_0 as the x86 CPU backend runs it, arch/x86/quants.c:290-385): warp w takes rows w, w + FQ_WARPS, ...
     constexpr int EPL = D / 32, LPB = 32 / EPL;              // elements per lane, lanes per 32-element block
     for (int r = warp; r < R; r += FQ_WARPS) {
         float v[EPL];
@@ -99,10 +99,10 @@ __global__ void __launch_bounds__(FQ_WARPS * 32) k_fattn_kvq(const fattn_args p,
         for (int e = 0; e < EPL; ++e) amax = fmaxf(amax, fabsf(v[e]));
 #pragma unroll
         for (int o = 1; o < LPB; o <<= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-        const float d = amax / 127.0f, id = d != 0.0f ? 1.0f / d : 0.0f;
+        const float d = __fdiv_rn(amax, 127.0f), id = amax != 0.0f ? __fdiv_rn(127.0f, amax) : 0.0f;      // the x86 body: 127 / amax, nearest even
         int q[EPL], sum = 0; unsigned packed = 0;
 #pragma unroll
-        for (int e = 0; e < EPL; ++e) { q[e] = (int) roundf(v[e] * id); sum += q[e]; packed |= ((unsigned) q[e] & 0xffu) << (8 * (e & 3)); }
+        for (int e = 0; e < EPL; ++e) { q[e] = __float2int_rn(__fmul_rn(v[e], id)); sum += q[e]; packed |= ((unsigned) q[e] & 0xffu) << (8 * (e & 3)); }
 #pragma unroll
         for (int o = 1; o < LPB; o <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
         if (EPL == 4) sqw[r][lane] = (int) packed;

@@ -280,8 +280,9 @@ __global__ void __launch_bounds__(256) k_set_rows(const gl_view s, const gl_view
     }
 }
 
-// SET_ROWS into a quantized cache (llama.cpp -ctk / -ctv q8_0, q4_0): thread = one 32-element block, quantize_row_q8_0_ref / q4_0_ref
-// (ggml/src/ggml-quants.c:200-222, 38-74), what ggml-cpu's set_rows calls through from_float (ops.cpp, ggml_compute_forward_set_rows_f32)
+// SET_ROWS into a quantized cache (llama.cpp -ctk / -ctv q8_0, q4_0): thread = one 32-element block, quantized as ggml-cpu's set_rows does
+// through from_float (ops.cpp, ggml_compute_forward_set_rows_f32): q8_0 with the x86 body's arithmetic, q4_0 by quantize_row_q4_0_ref
+// (ggml/src/ggml-quants.c:38-74; it has no SIMD form)
 template <int Q4>
 __global__ void __launch_bounds__(256) k_set_rows_q(const gl_view s, const gl_view idx, const gl_view d, int nblk, int64_t total) {
     GL_PDL();
@@ -299,11 +300,12 @@ __global__ void __launch_bounds__(256) k_set_rows_q(const gl_view s, const gl_vi
         float amax = 0.0f;
         #pragma unroll
         for (int j = 0; j < 32; ++j) amax = fmaxf(amax, fabsf(v[j]));
-        const float dd = amax / 127.0f, id = dd != 0.0f ? 1.0f / dd : 0.0f;
+        // as the x86 quantize_row_q8_0 the CPU backend runs (arch/x86/quants.c:290-385): id = 127 / amax, round to nearest even
+        const float dd = __fdiv_rn(amax, 127.0f), id = amax != 0.0f ? __fdiv_rn(127.0f, amax) : 0.0f;
         o[0] = __half_as_ushort(__float2half_rn(dd));
         #pragma unroll
         for (int j = 0; j < 16; ++j) {
-            const int q0 = (int) roundf(v[2 * j] * id), q1 = (int) roundf(v[2 * j + 1] * id);
+            const int q0 = __float2int_rn(__fmul_rn(v[2 * j], id)), q1 = __float2int_rn(__fmul_rn(v[2 * j + 1], id));
             o[1 + j] = (unsigned short) ((q0 & 0xff) | ((q1 & 0xff) << 8));
         }
     } else {

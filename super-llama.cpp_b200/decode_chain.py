@@ -18,7 +18,9 @@ class LayerChain:
 
     NAMES = ("wo", "gate", "up", "down", "q", "k", "v")
 
-    def __init__(self, ctx, n_embd, n_ff, n_kv, weights, norm_ffn, norm_attn, eps=1e-5, repack=True, tail="qkv"):
+    def __init__(self, ctx, n_embd, n_ff, n_kv, weights, norm_ffn, norm_attn, eps=1e-5, repack=True, tail="qkv", norm_outputs=True):
+        """norm_outputs=False: the RMS_NORM and MUL node values are dead, as in the real llama graph where only the matmuls read them (the
+        plugin passes NULL for them, b200_backend.cpp try_chain) -- the shape the kernel's owner-side hand-over takes"""
         self.ctx, self.n_embd, self.n_ff, self.n_kv, self.eps = ctx, n_embd, n_ff, n_kv, eps
         shape = {"wo": (n_embd, n_embd), "gate": (n_embd, n_ff), "up": (n_embd, n_ff), "down": (n_ff, n_embd),
                  "q": (n_embd, n_embd), "k": (n_embd, n_kv), "v": (n_embd, n_kv)}
@@ -44,13 +46,16 @@ class LayerChain:
         ph = [
             dict(w=[self.w["wo"]], dst=[self.wo_out], in0=self.attn_out),
             dict(w=[self.w["gate"], self.w["up"]], dst=[self.gate, self.up], glu=self.glu, epilogue=B.Y_SWIGLU, prologue=B.X_ADD_NORM_MUL, eps=eps,
-                 in0=self.wo_out, in1=self.inp_sa, normw=self.norm_ffn, out_add=self.ffn_inp, out_norm=self.ffn_normed, out_mul=self.ffn_x),
+                 in0=self.wo_out, in1=self.inp_sa, normw=self.norm_ffn, out_add=self.ffn_inp,
+                 out_norm=self.ffn_normed if norm_outputs else None, out_mul=self.ffn_x if norm_outputs else None),
             dict(w=[self.w["down"]], dst=[self.down_out], in0=self.glu),
         ]
         if tail == "qkv":
             ph.append(dict(w=[self.w["q"], self.w["k"], self.w["v"]], dst=[self.q, self.k, self.v], prologue=B.X_ADD_NORM_MUL, eps=eps,
-                           in0=self.down_out, in1=self.ffn_inp, normw=self.norm_attn, out_add=self.l_out, out_norm=self.attn_normed, out_mul=self.attn_x))
+                           in0=self.down_out, in1=self.ffn_inp, normw=self.norm_attn, out_add=self.l_out,
+                           out_norm=self.attn_normed if norm_outputs else None, out_mul=self.attn_x if norm_outputs else None))
         self.phases = ph
+        self.norm_outputs = norm_outputs
         self.program = ctx.chain_program(ph)
 
     def weight_bytes(self):
@@ -66,8 +71,10 @@ class LayerChain:
 
     OUTPUTS = ("wo_out", "ffn_inp", "ffn_normed", "ffn_x", "gate", "up", "glu", "down_out", "l_out", "attn_normed", "attn_x", "q", "k", "v")
 
+    DEAD = ("ffn_normed", "ffn_x", "attn_normed", "attn_x")
+
     def outputs(self):
-        return {n: self.ctx.download(getattr(self, n)) for n in self.OUTPUTS}
+        return {n: self.ctx.download(getattr(self, n)) for n in self.OUTPUTS if self.norm_outputs or n not in self.DEAD}
 
     def clear_outputs(self, byte=0xff):
         for n in self.OUTPUTS:
