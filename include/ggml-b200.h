@@ -203,6 +203,28 @@ B200_API int b200_repack(b200_ctx * ctx, int type, void * data, int64_t k, int64
 B200_API int b200_unrepack(b200_ctx * ctx, int type, void * data, int64_t k, int64_t nrows, size_t row_stride);
 
 // ---- split-mode=row across processes: MUL_MAT fused with its all-gather over NVLink peer memory ------------------------------
+// ---- weight load path: file -> pinned staging ring -> device, repack overlapped, per-GPU sharded reads --------------------
+// Replaces the upload loop of llama_model_loader::load_all_data (src/llama-model-loader.cpp:1136-1186: one host thread alternating between
+// read() into a 1 MiB pinned buffer and ggml_backend_tensor_set_async) and, for split-mode=row, ggml_backend_cuda_split_buffer_set_tensor
+// (ggml/src/ggml-cuda/ggml-cuda.cu:900-937: the whole tensor arrives on the host, every device's row slice is copied out of it).
+// An item is a byte range of the file and where it goes inside a device tensor; a reader thread fills a ring of n_buffers pinned buffers of
+// chunk_bytes while the caller's thread issues the host-to-device copies on a copy stream of its own; an item with repack != 0 (a whole
+// tensor of a type b200_repack_supported) is re-laid out on ctx's stream as soon as its last chunk has been issued, overlapping the next
+// tensor's transfer, and gets B200_TENSOR_REPACKED set.  Returns after everything has landed.  chunk_bytes 0 = 4 MiB, n_buffers 0 = 8; reader threads: GGML_B200_LOAD_THREADS (default 4).
+typedef struct b200_load_item {
+    int64_t       file_offset;   // first byte of the range in the file
+    size_t        nbytes;
+    b200_tensor * dst;           // device tensor; bytes go to dst->data + dst_offset
+    size_t        dst_offset;
+    int32_t       repack;
+} b200_load_item;
+typedef struct b200_load_stats { double seconds, read_seconds; uint64_t bytes, chunks; } b200_load_stats;   // wall time, time inside pread, bytes uploaded
+B200_API int b200_load_file(b200_ctx * ctx, const char * path, const b200_load_item * items, int n_items, size_t chunk_bytes, int n_buffers,
+                            b200_load_stats * stats);
+// the item of rows [row_lo, row_hi) of a [ne0, nrows] tensor of `type` stored at file_offset: what one device of a row split reads
+// (row_lo / row_hi from b200_split_row_range); the caller fills dst (a tensor of row_hi - row_lo rows) and repack
+B200_API int b200_load_row_slice(int type, int64_t ne0, int64_t file_offset, int64_t row_lo, int64_t row_hi, b200_load_item * item);
+
 // One process per GPU.  Every rank allocates an identical "exchange arena" (b200_malloc), publishes it with b200_peer_handle
 // (a cudaIpcMemHandle, 64 bytes, exchanged by the host program) and maps the others with b200_peer_open.  Arena layout:
 //   [0, ctrl_off)                         tensors (dst of the row-split matmuls), same offsets on every rank

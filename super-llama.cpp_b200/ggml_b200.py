@@ -35,6 +35,14 @@ class Exchange(C.Structure):
     _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("base", C.c_void_p * 8), ("ctrl_off", C.c_size_t)]
 
 
+class LoadItem(C.Structure):          # b200_load_item
+    _fields_ = [("file_offset", C.c_int64), ("nbytes", C.c_size_t), ("dst", C.c_void_p), ("dst_offset", C.c_size_t), ("repack", C.c_int32)]
+
+
+class LoadStats(C.Structure):         # b200_load_stats
+    _fields_ = [("seconds", C.c_double), ("read_seconds", C.c_double), ("bytes", C.c_uint64), ("chunks", C.c_uint64)]
+
+
 class KvPages(C.Structure):
     """b200_kv_pages: page table of a paged KV cache (logical page -> physical page of the pool)"""
     _fields_ = [("table", C.c_void_p), ("n_pages", C.c_int32), ("page_tokens", C.c_int32), ("pool_tokens", C.c_int64)]
@@ -93,6 +101,8 @@ def lib():
         "b200_mul_mat_rowsplit": (i, [vp, tp, tp, tp, i64, C.POINTER(Exchange)]),
         "b200_mul_mat_rowsplit_multi": (i, [vp, C.POINTER(tp), i, tp, C.POINTER(tp), C.POINTER(i64), C.POINTER(Exchange)]),
         "b200_exchange_error": (i, [vp, C.POINTER(Exchange)]),
+        "b200_load_file": (i, [vp, C.c_char_p, C.POINTER(LoadItem), i, sz, i, C.POINTER(LoadStats)]),
+        "b200_load_row_slice": (i, [i, i64, i64, i64, i64, C.POINTER(LoadItem)]),
         "ggml_backend_init": (vp, []), "ggml_backend_score": (i, []), "ggml_backend_b200_reg": (vp, []),
     }
     for name, (res, args) in sig.items():
@@ -392,6 +402,20 @@ class Context:
     def mul_mat_id(self, as_, b, ids, dst):
         ca, cb, ci, cd = as_.c(), b.c(), ids.c(), dst.c()
         _check(lib().b200_mul_mat_id(self.h, C.byref(ca), C.byref(cb), C.byref(ci), C.byref(cd)), "mul_mat_id")
+
+    def load_file(self, path, items, chunk_bytes=0, n_buffers=0):
+        """b200_load_file: items = [(file_offset, nbytes, device tensor, dst_offset, repack)]; file -> pinned ring -> device with the repack of
+        a finished tensor overlapping the next one's transfer.  Returns (seconds, seconds inside pread, bytes, chunks)."""
+        arr = (LoadItem * max(1, len(items)))()
+        keep = []
+        for a, (off, n, t, doff, rp) in zip(arr, items):
+            c = t.c(); keep.append(c)
+            a.file_offset, a.nbytes, a.dst, a.dst_offset, a.repack = off, n, C.addressof(c), doff, int(rp)
+        st = LoadStats()
+        _check(lib().b200_load_file(self.h, os.fsencode(path), arr, len(items), chunk_bytes, n_buffers, C.byref(st)), "load_file")
+        for (off, n, t, doff, rp), c in zip(items, keep):
+            t.flags = c.flags                       # B200_TENSOR_REPACKED where the loader re-laid the tensor out
+        return st.seconds, st.read_seconds, st.bytes, st.chunks
 
     def flash_attn_ext_paged(self, q, k, v, table, page_tokens, pool_tokens, mask, sinks, dst, scale, max_bias=0.0, logit_softcap=0.0):
         """k / v describe the page pool (ne[1] = keys attended); table: device int32 tensor, logical page -> physical page"""
