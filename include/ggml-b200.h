@@ -155,6 +155,22 @@ B200_API size_t b200_noalloc_scratch_bytes(void);
 #define B200_CHAIN_MAX_PHASES 6
 enum b200_chain_prologue { B200_CHAIN_X_PLAIN = 0, B200_CHAIN_X_ADD_NORM_MUL = 1, B200_CHAIN_X_NORM_MUL = 2 };
 enum b200_chain_epilogue { B200_CHAIN_Y_PLAIN = 0, B200_CHAIN_Y_SWIGLU = 1 };
+/* What follows result i of the chain's LAST phase in a llama layer's decode graph (one token): ROPE of the Q / K head rows
+ * (ggml_compute_forward_rope_f32, ggml/src/ggml-cpu/ops.cpp:5524-5790; the adjacent-pair form, no YaRN mixing) and the KV-cache write of
+ * the K / V rows (SET_ROWS f32 -> f16, src/llama-kv-cache.cpp:1008-1058), finished by the CTA that owns the rows.  kind: */
+enum b200_chain_tail { B200_CHAIN_T_NONE = 0, B200_CHAIN_T_ROPE = 1, B200_CHAIN_T_ROPE_CACHE = 2, B200_CHAIN_T_CACHE = 3 };
+typedef struct b200_chain_rope {
+    int32_t         kind;
+    int32_t         skip_dst;                               /* dst[i] itself is dead and its memory belongs to another result's ROPE by now: do not store it */
+    int32_t         head_dim, n_dims;                       /* row length of the rope tensor; rotated dims (even, <= head_dim) */
+    float           freq_scale, theta_scale, attn_factor;   /* angle of pair j: pos * theta_scale^j / freq_factors[j] * freq_scale; cos / sin scaled by attn_factor */
+    const int32_t * pos;                                    /* device: the token's position */
+    const float *   freq_factors;                           /* device, n_dims / 2 entries, or NULL */
+    float *         out;                                    /* device: the ROPE node's result column (may be dst[i] itself) */
+    const int64_t * cache_idx;                              /* device: the cache row SET_ROWS names (one entry) */
+    void *          cache;                                  /* f16 cache tensor; its row r starts at cache + r * cache_nb1 */
+    size_t          cache_nb1;
+} b200_chain_rope;
 typedef struct b200_chain_phase {
     int32_t prologue, epilogue, n_w;
     float   eps;
@@ -162,6 +178,7 @@ typedef struct b200_chain_phase {
     b200_tensor *       dst[3];
     const b200_tensor * in0, * in1, * normw;
     b200_tensor *       out_add, * out_norm, * out_mul, * glu;
+    const b200_chain_rope * tail[3];                        /* last phase only, B200_CHAIN_Y_PLAIN: NULL or what happens to dst[i] afterwards */
 } b200_chain_phase;
 B200_API int b200_decode_chain(b200_ctx * ctx, const b200_chain_phase * phases, int n_phases);
 B200_API int b200_decode_chain_supported(b200_ctx * ctx, const b200_chain_phase * phases, int n_phases);   // 1 / 0

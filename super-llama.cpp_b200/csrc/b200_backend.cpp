@@ -429,6 +429,7 @@ static bool chain_weight(const ggml_tensor * w) {
            !b200_split_of(w);
 }
 struct chain_build {
+    b200_chain_rope tail[3];                          // ROPE / KV-cache write behind the last phase's wq / wk / wv (chain_tail)
     b200_chain_phase ph[B200_CHAIN_MAX_PHASES];
     b200_tensor t[B200_CHAIN_MAX_PHASES][16];         // storage behind the pointers: w[3], dst[3], in0, in1, normw, out_add, out_norm, out_mul, glu
     int n = 0;
@@ -477,6 +478,41 @@ static int chain_group(ggml_cgraph * g, int j, const ggml_tensor * x, chain_buil
         P.w[i] = &cb.t[ph][i]; P.dst[i] = &cb.t[ph][3 + i];
     }
     return last;
+}
+static bool chain_tail_on() { static int v = -1; if (v < 0) { const char * e = getenv("GGML_B200_NO_CHAIN_TAIL"); v = (e && atoi(e)) ? 0 : 1; } return v != 0; }
+static bool bytes_overlap(const void * a, size_t na, const void * b, size_t nb) {
+    return a && b && (const char *) a < (const char *) b + nb && (const char *) b < (const char *) a + na;
+}
+// The chain's last phase is wq / wk / wv and node `at` opens [ROPE(Q)] ROPE(K) SET_ROWS(K) SET_ROWS(V) on exactly their results (one token):
+// the row owners of the chain kernel rotate the Q / K rows and write the K / V cache rows themselves.  Returns the SET_ROWS(V) index, or -1
+static int chain_tail(ggml_cgraph * g, int at, chain_build & cb) {
+    if (!chain_tail_on() || at < 0 || g->nodes[at]->op != GGML_OP_ROPE) return -1;
+    b200_chain_phase & P = cb.ph[cb.n - 1];
+    if (P.n_w != 3 || P.epilogue != B200_CHAIN_Y_PLAIN) return -1;
+    const int j1 = next_work(g, at), j2 = j1 < 0 ? -1 : next_work(g, j1), j3 = j2 < 0 ? -1 : next_work(g, j2);
+    if (j3 < 0 || g->nodes[j1]->op != GGML_OP_ROPE) return -1;
+    ggml_tensor * sk = g->nodes[j2], * sv = g->nodes[j3];
+    if (sk->op != GGML_OP_SET_ROWS || sv->op != GGML_OP_SET_ROWS || !sk->src[0] || !sv->src[0]) return -1;
+    const bool first_is_k = sk->src[0]->data == g->nodes[at]->data;
+    ggml_tensor * rk = first_is_k ? g->nodes[at] : g->nodes[j1], * rq = first_is_k ? g->nodes[j1] : g->nodes[at];
+    b200_chain_rope plan[3]; bool dead_in[3];
+    if (b200_glue_rope_kv_plan(rq, rk, sk, sv, plan, dead_in) != B200_OK) {
+        static int said = 0;
+        if (!said++ && getenv("GGML_B200_DEBUG")) B200_LOG("decode chain: rope / KV-store tail declined at node %d (%s): %s", at, g->nodes[at]->name, b200_last_error());
+        return -1;
+    }
+    const void * in[3] = { rq->src[0]->data, rk->src[0]->data, sv->src[0]->data };
+    const int64_t n_in[3] = { tensor_nelements(rq->src[0]), tensor_nelements(rk->src[0]), tensor_nelements(sv->src[0]) };
+    int which[3] = { -1, -1, -1 };
+    for (int i = 0; i < 3; ++i) for (int k = 0; k < 3; ++k) if (P.dst[i]->data == in[k] && P.dst[i]->ne[0] == n_in[k]) which[i] = k;
+    if (which[0] < 0 || which[1] < 0 || which[2] < 0 || which[0] == which[1] || which[0] == which[2] || which[1] == which[2]) return -1;
+    // the rotated rows are stored while other CTAs may still be reading the phase's own inputs
+    const ggml_tensor * outs[2] = { rq, rk };
+    const b200_tensor * ins[4] = { P.in0, P.in1, P.normw, P.out_add };
+    for (const ggml_tensor * o : outs) for (const b200_tensor * t : ins) if (t && bytes_overlap(o->data, tensor_nbytes(o), t->data, (size_t) t->ne[0] * 4)) return -1;
+    for (int k = 0; k < 3; ++k) { cb.tail[k] = plan[k]; cb.tail[k].skip_dst = dead_in[k] ? 1 : 0; }
+    for (int i = 0; i < 3; ++i) P.tail[i] = &cb.tail[which[i]];
+    return j3;
 }
 static int try_chain(b200_backend_ctx * c, ggml_cgraph * g, int i) {
     if (!chain_on() || fuse_off()) return -1;
@@ -563,6 +599,9 @@ static int try_chain(b200_backend_ctx * c, ggml_cgraph * g, int i) {
     }
     { static int said = 0; if (said < 12 && getenv("GGML_B200_DEBUG")) { ++said; B200_LOG("decode chain at node %d (%s): %d phases, stopped at node %d (%s) for reason %d", i, g->nodes[i]->name, cb.n, at, at >= 0 && at < g->n_nodes ? g->nodes[at]->name : "-", why); } }
     if (cb.n < 2) return -1;
+    const int tail_end = why == 15 ? chain_tail(g, at, cb) : -1;
+    if (tail_end >= 0 && !b200_decode_chain_supported(c->ctx, cb.ph, cb.n)) { for (int k = 0; k < 3; ++k) cb.ph[cb.n - 1].tail[k] = nullptr; }
+    else if (tail_end >= 0) { last = tail_end; c->n_fuse[3] += 3; }
     if (!b200_decode_chain_supported(c->ctx, cb.ph, cb.n)) {
         static int said = 0;
         if (!said++ && getenv("GGML_B200_DEBUG")) B200_LOG("decode chain declined at node %d (%s): %s", i, g->nodes[i]->name, b200_last_error());

@@ -84,11 +84,15 @@ struct ch_phase {
     int in1_kept;          // in1 is the out_add column of an earlier phase of this launch: still in registers
     int nq8;               // CH_IN_LL_Q8: the first nq8 activations arrive as q8_1 blocks, the rest as f32 pairs
 };
+// the tail of the last phase (b200_chain_rope): ROPE of the rows of result i and / or their f16 copy into a KV-cache row
+struct ch_tail { int kind, nodst, head_dim, n_dims; float fs, ts, af; const int32_t * pos; const float * ff; float * out; const long long * cidx; char * cache; size_t cnb1; };
 struct ch_args {
     CUtensorMap map[CH_MAXMAPS];   // per weight matrix: rows of nb1 bytes as 8-byte elements, box = one K chunk x CH_R rows: ONE request per stage
     ch_phase ph[CH_MAXPH];
     int nph, slot_bytes, nslot, act_bytes;
     int pre_in1;           // the phase whose addend (in1) comes from outside the launch and is fetched at the very start, or -1
+    int tail_phase;        // the phase whose results get tail[] applied by their row owners (the last one), or -1
+    ch_tail tail[CH_MAXSEG];
     int own_in1;           // CH_IN_BQ8N: the producing phase whose row owners fetch their rows of an addend from outside at the very start, or -1
     unsigned * sync;       // [0] phase arrivals (CH_IN_BARRIER), [1] CTAs done, [2] error code, [3] hand-over epoch, [4] abort
     uint8_t * ll;          // hand-over areas, CH_LL_BYTES per phase
@@ -689,6 +693,41 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
                 if (lane == 1) *(int2 *) (llout + CH_HDS + (size_t) (row >> 5) * 8) = make_int2(__float_as_int(d), isum);
                 if (lane == 2) *(float *) (llout + CH_HSS + (size_t) (row >> 5) * 4) = ss;
             }
+        } else if (p == P.tail_phase) {
+            // the layer's last matmuls with what the graph does to their rows next: ROPE (adjacent pairs: both rows of a pair sit in one unit,
+            // i.e. in neighbouring lanes) and the f16 copy into the KV-cache row the SET_ROWS index names.  Same expressions as gl_rope_rows (b200_glue.cu)
+            for (int t0 = warp * 32; t0 < nunits_l * CH_R; t0 += CH_NT) {
+                const int t = t0 + lane; const bool on = t < nunits_l * CH_R;
+                const int k = t / CH_R, r = t - k * CH_R;
+                float sum = 0.0f;
+                int sg = 0, row = 0;
+                if (on) {
+                    for (int c = 0; c < ph.nch; ++c) sum += s_psum[(k * ph.nch + c) * CH_R + r];
+                    ch_locate(ph, ch_unit(ph, k, own, G), sg, row);
+                }
+                const float other = __shfl_xor_sync(0xffffffffu, sum, 1);
+                if (!on) continue;
+                const int rw = row + r;
+                const ch_tail & T = P.tail[sg];
+                const bool rope = T.kind == B200_CHAIN_T_ROPE || T.kind == B200_CHAIN_T_ROPE_CACHE;
+                if (!(rope && T.out == ph.seg[sg].dst) && !T.nodst) ph.seg[sg].dst[rw] = sum;        // (a ROPE in place leaves only its own value there)
+                float y = sum;
+                if (rope) {
+                    const int d = rw % T.head_dim, ip = d >> 1;
+                    if (d < T.n_dims) {
+                        const float pos = (float) __ldg(T.pos);
+                        const float theta = T.fs * (pos * powf(T.ts, (float) ip) / (T.ff ? __ldg(T.ff + ip) : 1.0f));
+                        float sn, cs; sincosf(theta, &sn, &cs); sn *= T.af; cs *= T.af;
+                        const float x0 = (d & 1) ? other : sum, x1 = (d & 1) ? sum : other;
+                        y = (d & 1) ? x0 * sn + x1 * cs : x0 * cs - x1 * sn;
+                    }
+                    T.out[rw] = y;
+                }
+                if (T.kind == B200_CHAIN_T_ROPE_CACHE || T.kind == B200_CHAIN_T_CACHE) {
+                    const long long crow = *T.cidx;
+                    ((__half *) (T.cache + (size_t) crow * T.cnb1))[rw] = __float2half_rn(y);
+                }
+            }
         } else {
             for (int t = tid; t < nunits_l * CH_R; t += CH_NT) {
                 const int k = t / CH_R, r = t - k * CH_R;
@@ -812,6 +851,29 @@ static int ch_build(b200_ctx * ctx, const b200_chain_phase * phases, int n, ch_a
         if (d.types & 1) a += (int) gs_traits<B200_TYPE_Q4_K>::act_bytes((int) K);
         if (d.types & 2) a += (int) gs_traits<B200_TYPE_Q6_K>::act_bytes((int) K);
         act = max(act, a);
+    }
+    // ---- the tail of the last phase
+    A.tail_phase = -1;
+    for (int p = 0; p < n; ++p) {
+        const b200_chain_phase & s = phases[p];
+        bool any = false;
+        for (int i = 0; i < s.n_w; ++i) any = any || (s.tail[i] && s.tail[i]->kind != B200_CHAIN_T_NONE);
+        if (!any) continue;
+        if (p != n - 1 || s.epilogue != B200_CHAIN_Y_PLAIN) { b200_set_error("decode_chain: phase %d: only the last phase, without GLU, takes a tail", p); return B200_ERR_UNSUPPORTED; }
+        A.tail_phase = p;
+        for (int i = 0; i < s.n_w; ++i) {
+            ch_tail & T = A.tail[i];
+            const b200_chain_rope * r = s.tail[i];
+            if (!r || r->kind == B200_CHAIN_T_NONE) { T.kind = B200_CHAIN_T_NONE; continue; }
+            const int64_t M = s.w[i]->ne[1];
+            const bool rope = r->kind == B200_CHAIN_T_ROPE || r->kind == B200_CHAIN_T_ROPE_CACHE, cache = r->kind == B200_CHAIN_T_ROPE_CACHE || r->kind == B200_CHAIN_T_CACHE;
+            if ((!rope && !cache) || (rope && (r->head_dim <= 0 || r->head_dim % 2 || M % r->head_dim || r->n_dims < 0 || r->n_dims % 2 || r->n_dims > r->head_dim || !r->pos || !r->out)) ||
+                (cache && (!r->cache || !r->cache_idx || r->cache_nb1 < (size_t) M * 2 || ((uintptr_t) r->cache & 1) || (r->cache_nb1 & 1)))) {
+                b200_set_error("decode_chain: phase %d: malformed tail of result %d", p, i); return B200_ERR_INVALID;
+            }
+            T.kind = r->kind; T.nodst = r->skip_dst; T.head_dim = r->head_dim; T.n_dims = r->n_dims; T.fs = r->freq_scale; T.ts = r->theta_scale; T.af = r->attn_factor;
+            T.pos = r->pos; T.ff = r->freq_factors; T.out = rope ? r->out : nullptr; T.cidx = (const long long *) r->cache_idx; T.cache = (char *) r->cache; T.cnb1 = r->cache_nb1;
+        }
     }
     // ---- pass 2: how every phase gets its inputs.  The flag-in-data hand-over needs in0 to be exactly what the phase before publishes
     // (its single result column, or its glu) and in1 to come from outside or from the last residual sum (kept in registers); anything
@@ -963,6 +1025,8 @@ extern "C" int b200_decode_chain(b200_ctx * ctx, const b200_chain_phase * phases
     A.trace = ctx->trace; A.trace_cap = ctx->trace_cap;
     { static int dbg = -1; if (dbg < 0) { const char * e = getenv("GGML_B200_CHAIN_DBG"); dbg = e ? atoi(e) : 0; } A.dbg = dbg; }
     const int nw = ch_nw();
+    { static int said = 0; if (said < 6 && getenv("GGML_B200_DEBUG")) { ++said; char m[128]; int o = 0; for (int p = 0; p < n_phases; ++p) o += snprintf(m + o, sizeof(m) - o, " %d>%d", A.ph[p].in_mode, A.ph[p].out_mode);
+        fprintf(stderr, "ggml-b200: decode chain of %d phases, hand-over in>out per phase:%s, tail phase %d, %d ring slots\n", n_phases, m, A.tail_phase, A.nslot); } }
     static bool attr_done[64] = {};
     if (!attr_done[ctx->device & 63]) {
         B200_CUDA_TRY(cudaFuncSetAttribute(k_decode_chain<16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));

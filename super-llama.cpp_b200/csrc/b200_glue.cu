@@ -601,7 +601,9 @@ static bool gl_same_view(const ggml_tensor * a, const ggml_tensor * b) { return 
 
 // [ROPE(Q)] + ROPE(K) + SET_ROWS(K) + SET_ROWS(V) as one launch (rq may be NULL); B200_ERR_UNSUPPORTED when the nodes do not have the
 // shape of a llama layer's KV-cache update
-int b200_glue_rope_kv(b200_ctx * ctx, struct ggml_tensor * rq, struct ggml_tensor * rk, struct ggml_tensor * sk, struct ggml_tensor * sv) {
+// in_regs (the decode chain's tail): the three inputs never come from memory there, so an output may lie over another section's input -- the
+// allocator hands ROPE(Q)'s result the block Kcur has just left -- and dead_in[i] reports which inputs (0 Q, 1 K, 2 V) are overwritten that way
+static int gl_rope_kv_check(struct ggml_tensor * rq, struct ggml_tensor * rk, struct ggml_tensor * sk, struct ggml_tensor * sv, bool in_regs = false, bool * dead_in = nullptr) {
     if (!rk || !sk || !sv || rk->op != GGML_OP_ROPE || sk->op != GGML_OP_SET_ROWS || sv->op != GGML_OP_SET_ROWS || (rq && rq->op != GGML_OP_ROPE)) { b200_set_error("rope_kv: check 1"); return B200_ERR_UNSUPPORTED; }
     if (!b200_glue_supports(rk) || !b200_glue_supports(sk) || !b200_glue_supports(sv) || (rq && !b200_glue_supports(rq))) { b200_set_error("rope_kv: check 2"); return B200_ERR_UNSUPPORTED; }
     const ggml_tensor * ks = sk->src[0], * vs = sv->src[0], * kidx = sk->src[1], * vidx = sv->src[1];
@@ -616,9 +618,45 @@ int b200_glue_rope_kv(b200_ctx * ctx, struct ggml_tensor * rq, struct ggml_tenso
     for (int o = 0; o < 4; ++o) for (int i = 0; i < 4; ++i) {
         if (!outs[o] || o == i) continue;
         if (outs[i] && o < i && !gl_span_disjoint(outs[o], outs[i])) { b200_set_error("rope_kv: output %d (%s) overlaps output %d (%s)", o, outs[o]->name, i, outs[i]->name); return B200_ERR_UNSUPPORTED; }
-        if (ins[i] && !gl_span_disjoint(outs[o], ins[i])) { b200_set_error("rope_kv: output %d (%s) overlaps input %d (%s)", o, outs[o]->name, i, ins[i]->name); return B200_ERR_UNSUPPORTED; }
+        if (ins[i] && !gl_span_disjoint(outs[o], ins[i])) {
+            if (in_regs && o < 2) { if (dead_in) dead_in[i == 3 ? 2 : i] = true; continue; }       // (a rope result over a dead matmul result; the cache tensors never)
+            b200_set_error("rope_kv: output %d (%s) overlaps input %d (%s)", o, outs[o]->name, i, ins[i]->name); return B200_ERR_UNSUPPORTED;
+        }
     }
     for (int o = 0; o < 4; ++o) if (outs[o] && (!gl_span_disjoint(outs[o], kidx) || !gl_span_disjoint(outs[o], vidx) || !gl_span_disjoint(outs[o], rk->src[1]))) { b200_set_error("rope_kv: check 9"); return B200_ERR_UNSUPPORTED; }
+    return B200_OK;
+}
+// The same four nodes as the tail of a decode chain (b200_chain_rope x 3: Q, K, V): one token, adjacent-pair ROPE without YaRN mixing.  The
+// chain kernel's row owners then rotate and store the rows themselves (b200_chain.cu); B200_ERR_UNSUPPORTED = keep them as a launch of their own
+int b200_glue_rope_kv_plan(struct ggml_tensor * rq, struct ggml_tensor * rk, struct ggml_tensor * sk, struct ggml_tensor * sv, b200_chain_rope * out, bool * dead_in) {
+    if (!rq) { b200_set_error("rope_kv plan: no ROPE(Q)"); return B200_ERR_UNSUPPORTED; }
+    dead_in[0] = dead_in[1] = dead_in[2] = false;
+    const int rc = gl_rope_kv_check(rq, rk, sk, sv, true, dead_in);
+    if (rc != B200_OK) return rc;
+    const ggml_tensor * ks = sk->src[0], * vs = sv->src[0], * kidx = sk->src[1], * vidx = sv->src[1];
+    const ggml_tensor * ropes[2] = { rq, rk };
+    for (int i = 0; i < 2; ++i) {
+        const ggml_tensor * r = ropes[i];
+        const gl_rope g = gl_rope_params(r);
+        if (r->ne[2] != 1 || r->ne[3] != 1 || g.neox || r->op_params[2] != 0 || g.ext_factor != 0.0f || g.n_dims % 2 || g.n_dims > r->ne[0] || r->ne[0] % 2 ||
+            !gl_contiguous(r, 4) || !gl_contiguous(r->src[0], 4) || r->src[1]->type != GGML_TYPE_I32) { b200_set_error("rope_kv plan: not a one-token adjacent-pair rope"); return B200_ERR_UNSUPPORTED; }
+        b200_chain_rope & o = out[i];
+        memset(&o, 0, sizeof o);
+        o.kind = i == 0 ? B200_CHAIN_T_ROPE : B200_CHAIN_T_ROPE_CACHE;
+        o.head_dim = (int32_t) r->ne[0]; o.n_dims = g.n_dims; o.freq_scale = g.freq_scale; o.theta_scale = g.theta_scale; o.attn_factor = g.attn_factor;
+        o.pos = g.pos; o.freq_factors = g.ff; o.out = (float *) r->data;
+    }
+    if (ks->ne[1] != 1 || vs->ne[1] != 1 || kidx->type != GGML_TYPE_I64 || vidx->type != GGML_TYPE_I64) { b200_set_error("rope_kv plan: more than one cache row"); return B200_ERR_UNSUPPORTED; }
+    out[1].cache_idx = (const int64_t *) kidx->data; out[1].cache = sk->data; out[1].cache_nb1 = sk->nb[1];
+    memset(&out[2], 0, sizeof out[2]);
+    out[2].kind = B200_CHAIN_T_CACHE; out[2].cache_idx = (const int64_t *) vidx->data; out[2].cache = sv->data; out[2].cache_nb1 = sv->nb[1];
+    return B200_OK;
+}
+
+int b200_glue_rope_kv(b200_ctx * ctx, struct ggml_tensor * rq, struct ggml_tensor * rk, struct ggml_tensor * sk, struct ggml_tensor * sv) {
+    const int rcc = gl_rope_kv_check(rq, rk, sk, sv);
+    if (rcc != B200_OK) return rcc;
+    const ggml_tensor * ks = sk->src[0], * vs = sv->src[0], * kidx = sk->src[1], * vidx = sv->src[1];
     gl_rope_kv a;
     memset(&a, 0, sizeof a);
     if (rq) {

@@ -18,7 +18,7 @@ class LayerChain:
 
     NAMES = ("wo", "gate", "up", "down", "q", "k", "v")
 
-    def __init__(self, ctx, n_embd, n_ff, n_kv, weights, norm_ffn, norm_attn, eps=1e-5, repack=True, tail="qkv", norm_outputs=True):
+    def __init__(self, ctx, n_embd, n_ff, n_kv, weights, norm_ffn, norm_attn, eps=1e-5, repack=True, tail="qkv", norm_outputs=True, rope=None):
         """norm_outputs=False: the RMS_NORM and MUL node values are dead, as in the real llama graph where only the matmuls read them (the
         plugin passes NULL for them, b200_backend.cpp try_chain) -- the shape the kernel's owner-side hand-over takes"""
         self.ctx, self.n_embd, self.n_ff, self.n_kv, self.eps = ctx, n_embd, n_ff, n_kv, eps
@@ -54,6 +54,19 @@ class LayerChain:
             ph.append(dict(w=[self.w["q"], self.w["k"], self.w["v"]], dst=[self.q, self.k, self.v], prologue=B.X_ADD_NORM_MUL, eps=eps,
                            in0=self.down_out, in1=self.ffn_inp, normw=self.norm_attn, out_add=self.l_out,
                            out_norm=self.attn_normed if norm_outputs else None, out_mul=self.attn_x if norm_outputs else None))
+            if rope is not None:
+                # what the llama graph does to wq / wk / wv's rows next (b200_chain_rope): ROPE(Q), ROPE(K) + the f16 K row of the cache, the f16 V row.
+                # rope = dict(head_dim, n_dims, theta_scale, freq_scale, attn_factor, kv_size[, in_place])
+                hd, kvs = rope["head_dim"], rope["kv_size"]
+                self.rope = rope
+                self.pos = ctx.malloc(4); self.kidx = ctx.malloc(8); self.vidx = ctx.malloc(8)
+                self.q_rope = self.q if rope.get("in_place") else col(n_embd)
+                self.k_rope = self.k if rope.get("in_place") else col(n_kv)
+                self.k_cache = ctx.empty(B.F16, [n_kv, kvs]); self.v_cache = ctx.empty(B.F16, [n_kv, kvs])
+                common = dict(head_dim=hd, n_dims=rope["n_dims"], freq_scale=rope["freq_scale"], theta_scale=rope["theta_scale"], attn_factor=rope["attn_factor"], pos=self.pos)
+                ph[-1]["tail"] = [dict(kind=B.T_ROPE, out=self.q_rope.ptr, **common),
+                                  dict(kind=B.T_ROPE_CACHE, out=self.k_rope.ptr, cache_idx=self.kidx, cache=self.k_cache.ptr, cache_nb1=n_kv * 2, **common),
+                                  dict(kind=B.T_CACHE, cache_idx=self.vidx, cache=self.v_cache.ptr, cache_nb1=n_kv * 2)]
         self.phases = ph
         self.norm_outputs = norm_outputs
         self.program = ctx.chain_program(ph)
@@ -65,6 +78,9 @@ class LayerChain:
         self.ctx.h2d(self.attn_out.ptr, np.ascontiguousarray(attn_out, dtype=np.float32))
         self.ctx.h2d(self.inp_sa.ptr, np.ascontiguousarray(inp_sa, dtype=np.float32))
         self.ctx.note_write(self.attn_out); self.ctx.note_write(self.inp_sa)
+
+    def set_position(self, pos, cache_row):
+        self.ctx.h2d(self.pos, np.int32([pos])); self.ctx.h2d(self.kidx, np.int64([cache_row])); self.ctx.h2d(self.vidx, np.int64([cache_row]))
 
     def run(self):
         self.ctx.decode_chain(self.program)

@@ -48,12 +48,22 @@ class KvPages(C.Structure):
     _fields_ = [("table", C.c_void_p), ("n_pages", C.c_int32), ("page_tokens", C.c_int32), ("pool_tokens", C.c_int64)]
 
 
+class ChainRope(C.Structure):
+    """b200_chain_rope: ROPE / KV-cache write of one result of the chain's last phase, done by the CTA that owns the rows"""
+    _fields_ = [("kind", C.c_int32), ("skip_dst", C.c_int32), ("head_dim", C.c_int32), ("n_dims", C.c_int32), ("freq_scale", C.c_float), ("theta_scale", C.c_float), ("attn_factor", C.c_float),
+                ("pos", C.c_void_p), ("freq_factors", C.c_void_p), ("out", C.c_void_p), ("cache_idx", C.c_void_p), ("cache", C.c_void_p), ("cache_nb1", C.c_size_t)]
+
+
+T_NONE, T_ROPE, T_ROPE_CACHE, T_CACHE = 0, 1, 2, 3
+
+
 class ChainPhase(C.Structure):
     """b200_chain_phase: one MUL_MAT group of the persistent decode chain with its prologue / epilogue"""
     _fields_ = [("prologue", C.c_int32), ("epilogue", C.c_int32), ("n_w", C.c_int32), ("eps", C.c_float),
                 ("w", C.POINTER(_Tensor) * 3), ("dst", C.POINTER(_Tensor) * 3),
                 ("in0", C.POINTER(_Tensor)), ("in1", C.POINTER(_Tensor)), ("normw", C.POINTER(_Tensor)),
-                ("out_add", C.POINTER(_Tensor)), ("out_norm", C.POINTER(_Tensor)), ("out_mul", C.POINTER(_Tensor)), ("glu", C.POINTER(_Tensor))]
+                ("out_add", C.POINTER(_Tensor)), ("out_norm", C.POINTER(_Tensor)), ("out_mul", C.POINTER(_Tensor)), ("glu", C.POINTER(_Tensor)),
+                ("tail", C.POINTER(ChainRope) * 3)]
 
 
 X_PLAIN, X_ADD_NORM_MUL, X_NORM_MUL = 0, 1, 2
@@ -340,6 +350,10 @@ class Context:
                 pt = ptr(ph.get(name))
                 if pt is not None:
                     setattr(a, name, pt)
+            for k, tl in enumerate(ph.get("tail", ())):          # dicts of b200_chain_rope fields (device pointers as ints), or None
+                if tl is not None:
+                    r = ChainRope(**tl); keep.append(r)
+                    a.tail[k] = C.pointer(r)
         return arr, keep
 
     def decode_chain(self, program):

@@ -150,6 +150,58 @@ def test_decode_chain_owner_side_handover(ctx, B, orc, dims, t_v, t_down):
             assert O.nmse(want, got[out]) < NMSE_HARNESS, f"rep {rep} {name} vs ggml-cpu numerics"
 
 
+@pytest.mark.parametrize("in_place", [False, True])
+@pytest.mark.parametrize("n_dims", [128, 64])
+def test_decode_chain_rope_and_kv_cache_tail(ctx, B, in_place, n_dims):
+    """the chain's last phase with what a llama layer does to wq / wk / wv's rows next (b200_chain_rope): ROPE(Q), ROPE(K) -> f16 K-cache row,
+    V -> f16 V-cache row, done by the row owners.  Expected values: the same chain WITHOUT the tail, then ggml_compute_forward_rope_f32's
+    adjacent-pair rotation (ggml-cpu/ops.cpp:5524-5790) and the f16 rounding of SET_ROWS in numpy."""
+    rng = np.random.default_rng(31 + n_dims)
+    dims = (4096, 14336, 1024); hd = 128
+    base = 500000.0
+    rope = dict(head_dim=hd, n_dims=n_dims, theta_scale=float(np.float32(base) ** np.float32(-2.0 / n_dims)), freq_scale=1.0, attn_factor=1.0, kv_size=64, in_place=in_place)
+    from decode_chain import LayerChain
+    types = {"wo": O.Q4_K, "gate": O.Q4_K, "up": O.Q4_K, "down": O.Q6_K, "q": O.Q4_K, "k": O.Q4_K, "v": O.Q6_K}
+    shape = {"wo": (4096, 4096), "gate": (4096, 14336), "up": (4096, 14336), "down": (14336, 4096), "q": (4096, 4096), "k": (4096, 1024), "v": (4096, 1024)}
+    W = {n: (types[n], O.random_blocks(rng, types[n], *shape[n], scale=0.0028)) for n in types}
+    nf = rng.uniform(0.5, 1.5, 4096).astype(np.float32); na = rng.uniform(0.5, 1.5, 4096).astype(np.float32)
+    plain = LayerChain(ctx, *dims, W, nf, na, norm_outputs=False)
+    tail = LayerChain(ctx, *dims, W, nf, na, norm_outputs=False, rope=rope)
+    assert ctx.decode_chain_supported(tail.program)
+    attn_out = rng.uniform(-1, 1, 4096).astype(np.float32); inp_sa = rng.uniform(-2, 2, 4096).astype(np.float32)
+    for pos, crow in ((0, 0), (37, 5), (4099, 63)):
+        for lc in (plain, tail):
+            lc.set_inputs(attn_out, inp_sa); lc.clear_outputs()
+        ctx.memset(tail.k_cache.ptr, 0xff, tail.k_cache.nbytes); ctx.memset(tail.v_cache.ptr, 0xff, tail.v_cache.nbytes)
+        tail.set_position(pos, crow)
+        plain.run(); tail.run()
+        assert ctx.decode_chain_error() == 0
+        want = plain.outputs()
+        q, k, v = want["q"], want["k"], want["v"]
+        def rot(x):
+            x = x.reshape(-1, hd).astype(np.float32).copy()
+            ip = np.arange(n_dims // 2, dtype=np.float32)
+            theta = (np.float32(pos) * np.power(np.float32(rope["theta_scale"]), ip)).astype(np.float32)
+            cs, sn = np.cos(theta.astype(np.float64)).astype(np.float32), np.sin(theta.astype(np.float64)).astype(np.float32)
+            x0, x1 = x[:, 0:n_dims:2].copy(), x[:, 1:n_dims:2].copy()
+            x[:, 0:n_dims:2] = x0 * cs - x1 * sn; x[:, 1:n_dims:2] = x0 * sn + x1 * cs
+            return x.reshape(-1)
+        got_q, got_k = ctx.download(tail.q_rope), ctx.download(tail.k_rope)
+        # the angle goes through powf / sincosf on the device: a relative error of 1e-6 in an angle of 4e3 rad is 4e-3 rad
+        atol = 1e-5 + 4e-6 * pos
+        assert np.allclose(got_q, rot(q), rtol=1e-5, atol=atol * np.abs(q).max()), (pos, np.abs(got_q - rot(q)).max())
+        assert np.allclose(got_k, rot(k), rtol=1e-5, atol=atol * np.abs(k).max())
+        assert np.array_equal(ctx.download(tail.v), v)
+        if not in_place:
+            assert np.array_equal(ctx.download(tail.q), q) and np.array_equal(ctx.download(tail.k), k)      # the matmul nodes' own values
+        kc = ctx.download(tail.k_cache, np.float16).reshape(rope["kv_size"], 1024); vc = ctx.download(tail.v_cache, np.float16).reshape(rope["kv_size"], 1024)
+        assert np.array_equal(kc[crow], got_k.astype(np.float16)) and np.array_equal(vc[crow], v.astype(np.float16))
+        other = np.delete(np.arange(rope["kv_size"]), crow)
+        assert (kc[other].view(np.uint16) == 0xffff).all() and (vc[other].view(np.uint16) == 0xffff).all()   # no other cache row touched
+        for name in ("wo_out", "ffn_inp", "gate", "up", "glu", "down_out", "l_out"):
+            assert np.array_equal(ctx.download(getattr(tail, name)), want[name]), name
+
+
 def test_decode_chain_llama8b_shapes_vs_node_by_node(ctx, B):
     """Llama-3-8B shapes with the Q4_K_M mix (q6_K attn_v / ffn_down), compared with the separate launches of the flat API"""
     rng = np.random.default_rng(77)
