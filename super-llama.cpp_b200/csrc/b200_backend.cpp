@@ -73,7 +73,7 @@ struct b200_device_ctx {
 };
 struct b200_reg_ctx { std::vector<b200_device_ctx *> devices; };
 // `repacked`: weight tensors of this buffer that set_tensor re-laid out for the kernels (b200_repack): the load-time repack hook
-struct b200_buffer_ctx { int device; void * base; std::mutex mu; std::unordered_set<const void *> repacked; };
+struct b200_buffer_ctx { int device; void * base; std::mutex mu; std::unordered_set<const void *> repacked; std::atomic<int> n_repacked{0}; };   // n_repacked: size of the set, readable without the lock
 // one instantiated CUDA graph per ggml graph this backend has computed before (be_graph_compute)
 struct b200_graph_entry { uint64_t h1, h2; int n_nodes; void * exec; int seen; int failed; uint64_t used; };
 struct b200_backend_ctx {
@@ -137,6 +137,7 @@ static void tensor_repack(ggml_backend_buffer_t b, const ggml_tensor * t, bool i
     if (rc != B200_OK || b200_ctx_synchronize(u) != B200_OK) { fprintf(stderr, "ggml-b200: repack failed: %s\n", b200_last_error()); abort(); }
     std::lock_guard<std::mutex> g(c->mu);
     if (inverse) c->repacked.erase(t->data); else c->repacked.insert(t->data);
+    c->n_repacked.store((int) c->repacked.size());
     ++g_layout_epoch;
 }
 static bool tensor_wants_repack(ggml_backend_buffer_t b, const ggml_tensor * t) {
@@ -156,6 +157,13 @@ static void buf_free(ggml_backend_buffer_t b) {
 }
 static void * buf_get_base(ggml_backend_buffer_t b) { return ((b200_buffer_ctx *) b->context)->base; }
 static enum ggml_status buf_init_tensor(ggml_backend_buffer_t b, ggml_tensor * t) {
+    // a tensor that starts its life at an address forgets what an earlier tenant of that address was (compute buffers under
+    // GGML_B200_REPACK=all hand one block to tensors of different shapes: the layout mark must not outlive the tensor it was made for)
+    if (t->view_src == nullptr && ((b200_buffer_ctx *) b->context)->n_repacked.load(std::memory_order_relaxed) != 0) {   // (the graph allocator calls this for every node of every graph)
+        b200_buffer_ctx * c = (b200_buffer_ctx *) b->context;
+        std::lock_guard<std::mutex> g(c->mu);
+        if (c->repacked.erase(t->data)) { c->n_repacked.store((int) c->repacked.size()); ++g_layout_epoch; }
+    }
     // quantized rows may be padded by get_alloc_size: zero the tail so padded reads are defined (as ggml-cuda.cu:640-656)
     if (t->view_src == nullptr && t_blck(t->type) > 1) {
         const size_t orig = tensor_nbytes(t), padded = b->buft->iface.get_alloc_size(b->buft, t);
@@ -165,7 +173,11 @@ static enum ggml_status buf_init_tensor(ggml_backend_buffer_t b, ggml_tensor * t
 }
 static void buf_memset_tensor(ggml_backend_buffer_t b, ggml_tensor * t, uint8_t v, size_t off, size_t n) {
     b200_buffer_ctx * c = (b200_buffer_ctx *) b->context; B200_CHECK(cudaSetDevice(c->device));
+    const ggml_tensor * base = t->view_src ? t->view_src : t;
+    const bool was = tensor_is_repacked(t);                  // (offset, length) name GGUF bytes: a re-laid-out weight goes back first, as in set_tensor
+    if (was && !(off == 0 && n == tensor_nbytes(t))) tensor_repack(b, base, true);
     B200_CHECK(cudaMemsetAsync((char *) t->data + off, v, n, cudaStreamPerThread)); B200_CHECK(cudaStreamSynchronize(cudaStreamPerThread));
+    if (was && !(off == 0 && n == tensor_nbytes(t))) tensor_repack(b, base, false);
 }
 static void buf_set_tensor(ggml_backend_buffer_t b, ggml_tensor * t, const void * data, size_t off, size_t n) {
     b200_buffer_ctx * c = (b200_buffer_ctx *) b->context; B200_CHECK(cudaSetDevice(c->device));
@@ -980,9 +992,17 @@ static bool dev_supports_buft(ggml_backend_dev_t d, ggml_backend_buffer_type_t b
     return (buft_is_b200(buft) || b200_buft_is_split(buft)) && buft->device == d;
 }
 static bool dev_offload_op(ggml_backend_dev_t, const ggml_tensor * op) {
-    // as ggml-cuda.cu:4493-4500: worth shipping host-resident weights over only for real batches
-    const int min_batch = 32;
-    return (op->ne[1] >= min_batch && op->op != GGML_OP_GET_ROWS) || (op->op == GGML_OP_MUL_MAT_ID && op->ne[2] >= min_batch);
+    // worth shipping host-resident weights over only for real batches; the batch size of an op as the reference counts it
+    // (get_op_batch_size, ggml/src/ggml-cuda/ggml-cuda.cu:4675-4694)
+    const int64_t min_batch = 32;
+    int64_t batch;
+    switch ((int) op->op) {
+        case GGML_OP_GET_ROWS:   batch = 0; break;
+        case GGML_OP_MUL_MAT:    batch = op->ne[1]; break;
+        case GGML_OP_MUL_MAT_ID: case GGML_OP_ROPE: batch = op->ne[2]; break;
+        default:                 batch = op->ne[1] * op->ne[2] * op->ne[3]; break;
+    }
+    return batch >= min_batch;
 }
 static ggml_backend_event_t dev_event_new(ggml_backend_dev_t d) {
     b200_device_ctx * c = (b200_device_ctx *) d->context; B200_CHECK(cudaSetDevice(c->device));

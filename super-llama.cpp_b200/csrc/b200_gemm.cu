@@ -349,7 +349,15 @@ __global__ void __launch_bounds__(GM_THREADS, 2) k_gemm_q(const gm_args p, const
         const int c_begin = MT == 2 ? 0 : grp * (BN / 2), c_end = MT == 2 ? BN : c_begin + BN / 2;   // MT=1: the groups split the columns
         float * drow = p.seg[sg].dst + mm;
         if (ksplit == 2 && kpart == 1) {                                     // the other half's stores must be visible before we add
-            while (*(volatile unsigned *) (p.flags + split_j) == 0u) { }
+            // bounded (2 s): the other half's CTA has a lower block index and is resident or done when this one runs, but a launch that was
+            // cut short must not leave this one spinning for ever; a wait that ran out is recorded in flags[1024] and the tile's sum is wrong
+            unsigned long long t0 = 0; unsigned polls = 0;
+            while (*(volatile unsigned *) (p.flags + split_j) == 0u) {
+                if ((++polls & 0x3ffu) != 0) continue;
+                unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                if (!t0) t0 = t;
+                else if (t - t0 > 2000000000ull) { if (threadIdx.x % 32 == 0) atomicExch(p.flags + 1024, 1u); break; }
+            }
             __threadfence();
         }
         for (int c0 = c_begin; c0 < c_end; c0 += 16) {
@@ -606,9 +614,9 @@ static int gemm_launch(b200_ctx * ctx, const b200_tensor * const * ws, int nseg,
         const int64_t nsplit = (can_split && left && 2 * left <= ctx->sm_count && left <= 1024 && work / 2 + 10.0 < work) ? left : 0;
         if (nsplit) {
             const bool fresh = ctx->scratch[6] == nullptr;
-            p.flags = (unsigned *) b200_scratch(ctx, 6, 1024 * sizeof(unsigned));          // fixed size, zeroed once, re-armed by the kernel
+            p.flags = (unsigned *) b200_scratch(ctx, 6, 1025 * sizeof(unsigned));          // fixed size, zeroed once, re-armed by the kernel; [1024]: a wait ran out
             if (!p.flags) return B200_ERR_ALLOC;
-            if (fresh) B200_CUDA_TRY(cudaMemsetAsync(p.flags, 0, 1024 * sizeof(unsigned), ctx->stream));
+            if (fresh) B200_CUDA_TRY(cudaMemsetAsync(p.flags, 0, 1025 * sizeof(unsigned), ctx->stream));
         }
         p.lin = 1; p.n_unsplit = (int) (tiles - nsplit);
         grid = dim3((unsigned) (tiles + nsplit), 1, 1);
