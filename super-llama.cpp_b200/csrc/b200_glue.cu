@@ -234,13 +234,21 @@ static __device__ __forceinline__ void gl_rope_rows(const gl_view & x, const gl_
         }
         float sn, cs; sincosf(theta, &sn, &cs); sn *= mscale; cs *= mscale;
         const int64_t ia = r.neox ? ip : i0, ib = r.neox ? ip + r.n_dims / 2 : i0 + 1;
-        for (int64_t h = h0; h < h1; ++h) {
-            const float * xr = (const float *) (xb + h * x.nb[1]); float * yr = (float *) (yb + h * y.nb[1]);
-            const float x0 = xr[ia], x1 = xr[ib];
-            const float y0 = x0 * cs - x1 * sn, y1 = x0 * sn + x1 * cs;
-            yr[ia] = y0; yr[ib] = y1;
-            __half * ch = cache(h);
-            if (ch) { ch[ia] = __float2half_rn(y0); ch[ib] = __float2half_rn(y1); }
+        // heads in groups of 8: all 16 loads of a group are issued before the first store (one head after the other cost a memory latency
+        // per head: ROPE was 0.66 ms of a 13.5 ms pp512 ubatch)
+        for (int64_t hg = h0; hg < h1; hg += 8) {
+            float x0[8], x1[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) if (hg + j < h1) { const float * xr = (const float *) (xb + (hg + j) * x.nb[1]); x0[j] = xr[ia]; x1[j] = xr[ib]; }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) if (hg + j < h1) {
+                const int64_t h = hg + j;
+                float * yr = (float *) (yb + h * y.nb[1]);
+                const float y0 = x0[j] * cs - x1[j] * sn, y1 = x0[j] * sn + x1[j] * cs;
+                yr[ia] = y0; yr[ib] = y1;
+                __half * ch = cache(h);
+                if (ch) { ch[ia] = __float2half_rn(y0); ch[ib] = __float2half_rn(y1); }
+            }
         }
     }
 }
