@@ -8,9 +8,10 @@
 // read + 2 written + 2 read per element, against 1.06 here.
 //
 //  * k_fattn_kvq<TK, TV, D, R> -- query batches of <= 8 tokens.  One CTA per (kv head, group of R query rows of that kv head's GQA group,
-//    KV split); lane = key for the scores (the lane walks its own K row: 34 words for q8_0 / head 128), online softmax per row across the
-//    warp, probabilities through shared memory, lane = element group for P.V; 4 warps take KV tiles of 32 keys round-robin and merge through
-//    shared memory, KV splits merge in k_fattn_combine (b200_fattn_dec.cu).  Bound: HBM; algorithmic bytes per kv head and layer:
+//    KV split); every warp stages its tiles of 32 keys -- the K and V rows as they lie in the cache -- into a two-stage shared-memory ring with
+//    cp.async, one tile ahead; lane = key for the scores (34 words of its K row for q8_0 / head 128), online softmax per row across the
+//    warp, probabilities through shared memory, lane = element group for P.V, four keys per round; 4 warps take tiles round-robin and merge
+//    through shared memory, KV splits merge in k_fattn_combine (b200_fattn_dec.cu).  Bound: HBM; algorithmic bytes per kv head and layer:
 //    n_kv * (row_size(TK, D) + row_size(TV, D)) -- 2 * 136 B per key at head 128 / q8_0, each read once.
 //  * larger batches (prefill): k_dequant_kv expands this call's K / V views to f16 rows in scratch memory and the f16 kernels run on those
 //    (the tensor-core kernel is compute bound there, the conversion is ~1 % of its time).
@@ -33,6 +34,22 @@ static __device__ __forceinline__ uint32_t fq_word_at(const uint32_t * W, int by
     return (byte & 2) ? __funnelshift_r(W[byte >> 2], W[(byte >> 2) + 1], 16) : W[byte >> 2];
 }
 
+static __device__ __forceinline__ uint32_t fq_lds32(uint32_t a) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+static __device__ __forceinline__ unsigned short fq_lds16(uint32_t a) { unsigned short v; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a)); return v; }
+// 32 key rows of NWORDS 32-bit words each (row r of the tile at g + r * nb1) -> shared memory, rows NWORDS * 4 bytes apart, asynchronously:
+// consecutive lanes copy consecutive words of a row.  Rows beyond the cache's end are not touched
+template <int NWORDS>
+static __device__ __forceinline__ void fq_stage(uint32_t dst, const char * g, size_t nb1, int rows, int lane) {
+    for (int r = 0; r < rows; ++r) {
+        const char * gr = g + (size_t) r * nb1;
+#pragma unroll
+        for (int j = 0; j < (NWORDS + 31) / 32; ++j) {
+            const int w = lane + 32 * j;
+            if (w < NWORDS) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(dst + (uint32_t) (r * NWORDS + w) * 4u), "l"(gr + 4 * w) : "memory");
+        }
+    }
+}
+
 // element e (0 .. D/32-1 .. ) of lane: which element of the V row a lane accumulates.  q8_0: lane owns the 16-bit units 2 lane (+ 64 for
 // D = 128); q4_0: one 16-bit unit of nibble bytes = elements (j, j + 1, j + 16, j + 17) of a block
 template <int TV, int D> struct fq_vmap;
@@ -40,12 +57,12 @@ template <int D> struct fq_vmap<B200_TYPE_Q8_0, D> {
     static constexpr int NE = D / 32;   // accumulators per lane: 2 per 64 elements
     static __device__ __forceinline__ bool active(int) { return true; }
     static __device__ __forceinline__ int elem(int lane, int e) { return (e >> 1) * 64 + 2 * lane + (e & 1); }
-    static __device__ __forceinline__ void load(const char * vrow, int lane, float (&v)[NE]) {
+    static __device__ __forceinline__ void load(uint32_t vrow, int lane, float (&v)[NE]) {      // vrow: the row in shared memory
 #pragma unroll
         for (int h = 0; h < D / 64; ++h) {
             const int b = 2 * h + (lane >> 4);
-            const unsigned short qs = __ldg((const unsigned short *) (vrow + b * 34 + 2 + 2 * (lane & 15)));
-            const float d = __half2float(__ushort_as_half(__ldg((const unsigned short *) (vrow + b * 34))));
+            const unsigned short qs = fq_lds16(vrow + b * 34 + 2 + 2 * (lane & 15));
+            const float d = __half2float(__ushort_as_half(fq_lds16(vrow + b * 34)));
             v[2 * h]     = d * (float) (int) (signed char) (qs & 0xff);
             v[2 * h + 1] = d * (float) (int) (signed char) (qs >> 8);
         }
@@ -55,11 +72,11 @@ template <int D> struct fq_vmap<B200_TYPE_Q4_0, D> {
     static constexpr int NE = 4;
     static __device__ __forceinline__ bool active(int lane) { return lane < D / 4; }
     static __device__ __forceinline__ int elem(int lane, int e) { return (lane >> 3) * 32 + 2 * (lane & 7) + (e & 1) + (e >> 1) * 16; }
-    static __device__ __forceinline__ void load(const char * vrow, int lane, float (&v)[NE]) {
+    static __device__ __forceinline__ void load(uint32_t vrow, int lane, float (&v)[NE]) {
         if (!active(lane)) { v[0] = v[1] = v[2] = v[3] = 0.0f; return; }
         const int b = lane >> 3;
-        const unsigned short qs = __ldg((const unsigned short *) (vrow + b * 18 + 2 + 2 * (lane & 7)));
-        const float d = __half2float(__ushort_as_half(__ldg((const unsigned short *) (vrow + b * 18))));
+        const unsigned short qs = fq_lds16(vrow + b * 18 + 2 + 2 * (lane & 7));
+        const float d = __half2float(__ushort_as_half(fq_lds16(vrow + b * 18)));
         v[0] = d * (float) ((int) (qs & 0xf) - 8);        v[1] = d * (float) ((int) ((qs >> 8) & 0xf) - 8);
         v[2] = d * (float) ((int) ((qs >> 4) & 0xf) - 8); v[3] = d * (float) ((int) (qs >> 12) - 8);
     }
@@ -68,7 +85,13 @@ template <int D> struct fq_vmap<B200_TYPE_Q4_0, D> {
 template <int TK, int TV, int D, int R>
 __global__ void __launch_bounds__(FQ_WARPS * 32) k_fattn_kvq(const fattn_args p, const fq_extra x) {
     constexpr int NB = D / 32, KBS = fq_type<TK>::BS, NW = NB * KBS / 4;       // blocks per row, K block bytes, words per K row
+    constexpr int VBS = fq_type<TV>::BS, NWV = NB * VBS / 4;                   // V block bytes, words per V row
     constexpr int NE = fq_vmap<TV, D>::NE;
+    // per warp: two stages of (32 K rows | 32 V rows) as they lie in the cache, filled by cp.async one tile ahead of the arithmetic.
+    // (One stage and four CTAs per SM instead of two: 249 against 195 us at 131 k keys -- the kernel is bound by its ~1800 instructions per
+    // tile, two thirds of them the P.V loop, not by latency.)
+    extern __shared__ __align__(16) uint8_t fq_ring[];
+    constexpr uint32_t STAGE = 32u * (NW + NWV) * 4u;
     __shared__ __align__(16) int   sqw[R][D / 4];            // query rows as q8_0 quants
     __shared__ float sdq[R][NB];                             // their block scales (fp16-rounded, as the reference stores them)
     __shared__ int   ssq[R][NB];                             // sum of a block's quants (q4_0: the -8 offset)
@@ -133,7 +156,22 @@ __global__ void __launch_bounds__(FQ_WARPS * 32) k_fattn_kvq(const fattn_args p,
     }
 
     const int t0 = split * x.tiles_per_split, t1 = min(x.ntiles, t0 + x.tiles_per_split);
-    for (int t = t0 + warp; t < t1; t += FQ_WARPS) {
+    const uint32_t ring = (uint32_t) __cvta_generic_to_shared(fq_ring) + (uint32_t) warp * 2u * STAGE;
+    auto stage_tile = [&](int t, int st) {                   // whole warp; one commit group per tile (possibly empty)
+        if (t < t1) {
+            const int rows = (int) min((int64_t) 32, p.KV - (int64_t) t * 32);
+            fq_stage<NW>(ring + st * STAGE, kbase + (size_t) t * 32 * p.k_nb1, p.k_nb1, rows, lane);
+            fq_stage<NWV>(ring + st * STAGE + 32u * NW * 4u, vbase + (size_t) t * 32 * p.v_nb1, p.v_nb1, rows, lane);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    stage_tile(t0 + warp, 0);
+    int st = 0;
+    for (int t = t0 + warp; t < t1; t += FQ_WARPS, st ^= 1) {
+        stage_tile(t + FQ_WARPS, st ^ 1);                    // the next tile's bytes travel while this one is multiplied
+        asm volatile("cp.async.wait_group 1;" ::: "memory");
+        __syncwarp();
+        const uint32_t kst = ring + st * STAGE, vst = kst + 32u * NW * 4u;
         const int64_t ic = (int64_t) t * 32 + lane;
         const bool valid = ic < p.KV;
         float mv[R]; bool any = false;
@@ -147,10 +185,9 @@ __global__ void __launch_bounds__(FQ_WARPS * 32) k_fattn_kvq(const fattn_args p,
 #pragma unroll
         for (int r = 0; r < R; ++r) s[r] = 0.0f;
         if (any) {
-            const uint32_t * kr = (const uint32_t *) (kbase + fattn_row(p, ic) * p.k_nb1);
             uint32_t W[NW + 1];
 #pragma unroll
-            for (int i = 0; i < NW; ++i) W[i] = __ldg(kr + i);
+            for (int i = 0; i < NW; ++i) W[i] = fq_lds32(kst + (uint32_t) (lane * NW + i) * 4u);
             W[NW] = 0;
 #pragma unroll
             for (int b = 0; b < NB; ++b) {
@@ -210,27 +247,40 @@ __global__ void __launch_bounds__(FQ_WARPS * 32) k_fattn_kvq(const fattn_args p,
                 tile_live = true;
             }
         }
-        if (!tile_live) continue;                            // whole tile masked for every row (warp-uniform)
         bool nz = false;
 #pragma unroll
         for (int r = 0; r < R; ++r) { sp[warp][lane][r] = pr[r]; nz = nz || pr[r] != 0.0f; }
-        const unsigned live = __ballot_sync(0xffffffffu, nz);
+        const unsigned live = tile_live ? __ballot_sync(0xffffffffu, nz) : 0u;       // (a tile masked for every row: nothing to add; warp-uniform)
         __syncwarp();
-        for (unsigned bits = live; bits; bits &= bits - 1) {
-            const int j = __ffs(bits) - 1;
-            const char * vrow = vbase + fattn_row(p, (int64_t) t * 32 + j) * p.v_nb1;
-            float v[NE];
-            fq_vmap<TV, D>::load(vrow, lane, v);
-            float pj[R];
+        if (live) {
+            // every key of the tile that exists (its row was staged: finite values), four at a time so that their shared-memory loads are in
+            // flight together; a masked key carries p = 0.  (One key per round, picked from the ballot, left the loop waiting on one load
+            // after the other: 483 GB/s at 131 k keys.)
+            const int rows = (int) min((int64_t) 32, p.KV - (int64_t) t * 32);
+            for (int j0 = 0; j0 < rows; j0 += 4) {
+                float v[4][NE], pj[4][R];
 #pragma unroll
-            for (int r4 = 0; r4 < R; r4 += 4) { const float4 f = *(const float4 *) &sp[warp][j][r4]; pj[r4] = f.x; pj[r4 + 1] = f.y; pj[r4 + 2] = f.z; pj[r4 + 3] = f.w; }
+                for (int u = 0; u < 4; ++u) {
+                    const int j = min(j0 + u, rows - 1);             // (a repeated last key gets p = 0 below)
+                    fq_vmap<TV, D>::load(vst + (uint32_t) j * NWV * 4u, lane, v[u]);
 #pragma unroll
-            for (int r = 0; r < R; ++r)
+                    for (int r4 = 0; r4 < R; r4 += 4) {
+                        const float4 f = *(const float4 *) &sp[warp][j][r4];
+                        const bool on = j0 + u < rows;
+                        pj[u][r4] = on ? f.x : 0.0f; pj[u][r4 + 1] = on ? f.y : 0.0f; pj[u][r4 + 2] = on ? f.z : 0.0f; pj[u][r4 + 3] = on ? f.w : 0.0f;
+                    }
+                }
 #pragma unroll
-                for (int e = 0; e < NE; ++e) acc[r][e] = fmaf(pj[r], v[e], acc[r][e]);
+                for (int u = 0; u < 4; ++u)
+#pragma unroll
+                    for (int r = 0; r < R; ++r)
+#pragma unroll
+                        for (int e = 0; e < NE; ++e) acc[r][e] = fmaf(pj[u][r], v[u][e], acc[r][e]);
+            }
         }
-        __syncwarp();
+        __syncwarp();                                        // every lane is done with this stage before the next tile lands in it
     }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
 
     // ---- merge the warps
 #pragma unroll
@@ -315,7 +365,7 @@ bool b200_fattn_kvq_supported(const b200_tensor * q, const b200_tensor * k, cons
     if ((D != 64 && D != 128) || v->ne[0] != D || q->ne[0] != D) return false;
     if (k->nb[0] != b200_type_size(k->type) || v->nb[0] != b200_type_size(v->type)) return false;
     if ((k->nb[1] & 3) || (k->nb[2] & 3) || (k->nb[3] & 3) || ((uintptr_t) k->data & 3)) return false;      // the lane reads its K row as 32-bit words
-    if ((v->nb[1] & 1) || (v->nb[2] & 1) || (v->nb[3] & 1) || ((uintptr_t) v->data & 1)) return false;
+    if ((v->nb[1] & 3) || (v->nb[2] & 3) || (v->nb[3] & 3) || ((uintptr_t) v->data & 3)) return false;      // ... and both are staged in 4-byte copies
     if (k->nb[1] < b200_row_size(k->type, D) || v->nb[1] < b200_row_size(v->type, D)) return false;
     if (q->ne[2] % k->ne[2] != 0 || k->ne[2] != v->ne[2] || k->ne[3] != v->ne[3]) return false;
     return true;
@@ -323,8 +373,15 @@ bool b200_fattn_kvq_supported(const b200_tensor * q, const b200_tensor * k, cons
 
 template <int TK, int TV, int D>
 static int fq_launch(b200_ctx * ctx, const fattn_args & p, const fq_extra & x, dim3 grid) {
-    if (x.rows <= 4) B200_LAUNCH(ctx, B200_K_FATTN, k_fattn_kvq<TK, TV, D, 4><<<grid, FQ_WARPS * 32, 0, ctx->stream>>>(p, x));
-    else             B200_LAUNCH(ctx, B200_K_FATTN, k_fattn_kvq<TK, TV, D, 8><<<grid, FQ_WARPS * 32, 0, ctx->stream>>>(p, x));
+    constexpr size_t ring = (size_t) FQ_WARPS * 2 * 32 * ((D / 32) * (fq_type<TK>::BS + fq_type<TV>::BS));      // two stages of K and V rows per warp
+    static bool attr_done[64] = {};
+    if (!attr_done[ctx->device & 63]) {
+        B200_CUDA_TRY(cudaFuncSetAttribute(k_fattn_kvq<TK, TV, D, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) ring));
+        B200_CUDA_TRY(cudaFuncSetAttribute(k_fattn_kvq<TK, TV, D, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) ring));
+        attr_done[ctx->device & 63] = true;
+    }
+    if (x.rows <= 4) B200_LAUNCH(ctx, B200_K_FATTN, k_fattn_kvq<TK, TV, D, 4><<<grid, FQ_WARPS * 32, ring, ctx->stream>>>(p, x));
+    else             B200_LAUNCH(ctx, B200_K_FATTN, k_fattn_kvq<TK, TV, D, 8><<<grid, FQ_WARPS * 32, ring, ctx->stream>>>(p, x));
     return B200_OK;
 }
 template <int TK, int TV>
@@ -371,7 +428,7 @@ int b200_launch_fattn_kvq(b200_ctx * ctx, const b200_tensor * q, const b200_tens
     x.rows = (int) (p.N * x.gqa);
     const int R = x.rows <= 4 ? 4 : 8, ngroups = (x.rows + R - 1) / R;
     x.ntiles = (int) ((p.KV + 31) / 32);
-    // KV splits until the grid covers the SMs twice, at least 8 tiles (256 keys, two per warp) per split
+    // KV splits until the grid covers the SMs twice (two CTAs per SM are resident), at least 8 tiles (256 keys, two per warp) per split
     const int64_t base = (int64_t) ngroups * k->ne[2] * S;
     int nsplit = (int) ((2 * ctx->sm_count + base - 1) / base);
     if (nsplit > x.ntiles / 8) nsplit = x.ntiles / 8;
