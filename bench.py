@@ -639,6 +639,8 @@ def run_b200(args):
         ok = [len(set(digests)) == 1]
         if rank == 0:
             one = HotPathModel(B, ctx, cfg, 1, args.depth, 0, 1, quant=args.quant, chain=False)
+            for n in ("x", "h", "ff", "attn"):             # the same inputs, as they are NOW (the e2e leg above uploaded its own embedding row into x)
+                ctx.h2d(getattr(one, n).ptr, ctx.download(getattr(tg, n)).reshape(-1))
             one.step(); ctx.synchronize()
             whole = {n: ctx.download(getattr(one, n)).reshape(-1).copy() for n in names}
             del one

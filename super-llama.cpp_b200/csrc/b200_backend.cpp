@@ -628,20 +628,46 @@ static int try_chain(b200_backend_ctx * c, ggml_cgraph * g, int i) {
 // into this backend's dst (peer stores): the all-gather of the reference's split path (ggml-cuda.cu:1451-1769: copy src1 to every device,
 // compute, copy the dst slices back) happens inside the kernels' own loads and stores.  Ordering: the other devices' streams wait for an
 // event recorded on this stream (the activation is ready), this stream waits for one event per device (its rows have landed).
-static int split_mul_mat(b200_backend_ctx * c, ggml_tensor * node) {
-    const ggml_tensor * w = node->src[0], * x = node->src[1];
-    const b200_split_extra * e = (const b200_split_extra *) w->extra;
-    if (!e || w->ne[2] * w->ne[3] != 1) { b200_set_error("row-split MUL_MAT: weight without slices or with batch dimensions"); return B200_ERR_UNSUPPORTED; }
-    if (!c->ev_main) B200_CHECK(cudaEventCreateWithFlags(&c->ev_main, cudaEventDisableTiming));
+// Up to three MUL_MATs of the same activation go out behind ONE hand-over (one event each way per device instead of one per node); each
+// device takes its slices of all of them in one b200_mul_mat_multi call.  Everything here is stream-ordered (events, no host wait), so
+// the whole exchange records into a CUDA graph: a wait on an event of a capturing stream pulls the peer's stream into the capture, and the
+// wait on the peer's event joins it again before the capture ends.
+static inline void pdl_hold(b200_ctx * ctx) { if (ctx->pdl) { ctx->pdl_hold = ctx->pdl; ctx->pdl = 0; } }   // the next launch waits for ALL it depends on
+static int split_mul_mat(b200_backend_ctx * c, ggml_tensor * const * nodes, int n) {
+    const ggml_tensor * x = nodes[0]->src[1];
+    const b200_split_extra * e[3];
+    for (int k = 0; k < n; ++k) {
+        const ggml_tensor * w = nodes[k]->src[0];
+        e[k] = (const b200_split_extra *) w->extra;
+        if (!e[k] || w->ne[2] * w->ne[3] != 1) { b200_set_error("row-split MUL_MAT: weight without slices or with batch dimensions"); return B200_ERR_UNSUPPORTED; }
+    }
+    if (!c->ev_main) {
+        if (c->ctx->capturing) { b200_set_error("row-split MUL_MAT: events must exist before a graph is recorded"); return B200_ERR_UNSUPPORTED; }
+        B200_CHECK(cudaEventCreateWithFlags(&c->ev_main, cudaEventDisableTiming));
+    }
     B200_CHECK(cudaEventRecord(c->ev_main, c->ctx->stream));
     const b200_tensor bx = to_b200(x);
     int rc = B200_OK;
-    for (int i = 0; i < e->n && rc == B200_OK; ++i) {
-        const b200_split_slice & s = e->s[i];
-        if (s.hi <= s.lo) continue;
+    for (int i = 0; i < e[0]->n && rc == B200_OK; ++i) {
+        b200_tensor bw[3], bd[3]; const b200_tensor * wp[3]; b200_tensor * dp[3]; int cnt = 0;
+        for (int k = 0; k < n; ++k) {
+            if (i >= e[k]->n) continue;
+            const b200_split_slice & s = e[k]->s[i];
+            if (s.hi <= s.lo) continue;
+            const ggml_tensor * w = nodes[k]->src[0];
+            b200_tensor & W = bw[cnt]; b200_tensor & D = bd[cnt];
+            W.data = s.data; W.type = (int32_t) w->type; W.flags = s.repacked ? B200_TENSOR_REPACKED : 0;
+            W.ne[0] = w->ne[0]; W.ne[1] = s.hi - s.lo; W.ne[2] = W.ne[3] = 1;
+            W.nb[0] = w->nb[0]; W.nb[1] = w->nb[1]; W.nb[2] = W.nb[3] = w->nb[1] * (size_t) W.ne[1];
+            D = to_b200(nodes[k]);
+            D.data = (char *) nodes[k]->data + s.lo * sizeof(float); D.ne[0] = s.hi - s.lo;
+            wp[cnt] = &W; dp[cnt] = &D; ++cnt;
+        }
+        if (!cnt) continue;
         b200_ctx * ctx = c->ctx;
         if (i != c->index) {
             if (!c->peer[i]) {
+                if (c->ctx->capturing) { b200_set_error("row-split MUL_MAT: a peer context must exist before a graph is recorded"); return B200_ERR_UNSUPPORTED; }
                 c->peer[i] = b200_ctx_create(b200_logical_to_cuda(i));
                 if (!c->peer[i]) return B200_ERR_ALLOC;
                 B200_CHECK(cudaSetDevice(b200_logical_to_cuda(i)));
@@ -651,22 +677,19 @@ static int split_mul_mat(b200_backend_ctx * c, ggml_tensor * node) {
             B200_CHECK(cudaSetDevice(ctx->device));
             B200_CHECK(cudaStreamWaitEvent(ctx->stream, c->ev_main, 0));
             b200_ctx_invalidate(ctx);                         // its cached activation images were made from older contents of these addresses
+            pdl_hold(ctx);
         }
-        b200_tensor bw; bw.data = s.data; bw.type = (int32_t) w->type; bw.flags = s.repacked ? B200_TENSOR_REPACKED : 0;
-        bw.ne[0] = w->ne[0]; bw.ne[1] = s.hi - s.lo; bw.ne[2] = bw.ne[3] = 1;
-        bw.nb[0] = w->nb[0]; bw.nb[1] = w->nb[1]; bw.nb[2] = bw.nb[3] = w->nb[1] * (size_t) bw.ne[1];
-        b200_tensor bd = to_b200(node);
-        bd.data = (char *) node->data + s.lo * sizeof(float); bd.ne[0] = s.hi - s.lo;
-        rc = b200_mul_mat(ctx, &bw, &bx, &bd);
+        rc = cnt == 1 ? b200_mul_mat(ctx, wp[0], &bx, dp[0]) : b200_mul_mat_multi(ctx, wp, cnt, &bx, dp);
         if (i != c->index) {
             B200_CHECK(cudaEventRecord(c->ev_peer[i], ctx->stream));
             B200_CHECK(cudaSetDevice(c->device));
             B200_CHECK(cudaStreamWaitEvent(c->ctx->stream, c->ev_peer[i], 0));
+            pdl_hold(c->ctx);
         }
     }
     B200_CHECK(cudaSetDevice(c->device));
-    b200_note_write(c->ctx, node->data, tensor_nbytes(node));
-    ++c->n_split;
+    for (int k = 0; k < n; ++k) b200_note_write(c->ctx, nodes[k]->data, tensor_nbytes(nodes[k]));
+    c->n_split += n;
     return rc;
 }
 
@@ -677,7 +700,20 @@ static enum ggml_status run_nodes(b200_backend_ctx * c, ggml_cgraph * g) {
         if (op_is_view((int) node->op) || tensor_nelements(node) == 0) continue;
         int rc;
         if (node->op == GGML_OP_MUL_MAT && b200_split_of(node->src[0])) {
-            if ((rc = split_mul_mat(c, node)) != B200_OK) { B200_LOG("graph_compute: row-split node %d (%s) failed: %s", i, node->name, b200_last_error()); return GGML_STATUS_FAILED; }
+            // the row-split matmuls that follow and read the same activation (wq / wk / wv, ffn_gate / ffn_up after be_graph_optimize) share
+            // the hand-over; same rule as below: a member's dst may not overlap what the members before it read or write
+            ggml_tensor * grp[3] = { node, nullptr, nullptr }; int ngr = 1, last = i;
+            for (int j = i + 1; j < g->n_nodes && ngr < 3 && !fuse_off(); ++j) {
+                ggml_tensor * nj = g->nodes[j];
+                if (op_is_view((int) nj->op) || tensor_nelements(nj) == 0) continue;
+                if (nj->op != GGML_OP_MUL_MAT || nj->src[1] != node->src[1] || !b200_split_of(nj->src[0])) break;
+                bool clash = false;
+                for (int k = 0; k < ngr && !clash; ++k) clash = ranges_overlap(nj, grp[k]) || ranges_overlap(nj, grp[k]->src[1]);
+                if (clash) break;
+                grp[ngr++] = nj; last = j;
+            }
+            if ((rc = split_mul_mat(c, grp, ngr)) != B200_OK) { B200_LOG("graph_compute: row-split node %d (%s) failed: %s", i, node->name, b200_last_error()); return GGML_STATUS_FAILED; }
+            i = last;
             continue;
         }
         // decode: the whole run of a layer's nodes between two attention operators as one persistent kernel
@@ -741,6 +777,7 @@ static enum ggml_status run_nodes(b200_backend_ctx * c, ggml_cgraph * g) {
 // depends on identity only.  Recorded graphs are dropped when a scratch block moved (b200_ctx_scratch_generation) or a weight
 // changed layout / a buffer was freed (g_layout_epoch).  Only small-batch graphs on plain device buffers (no row-split peers) are
 // recorded; GGML_B200_GRAPHS=0 turns it off.
+static bool split_graphs_on() { static int v = -1; if (v < 0) { const char * e = getenv("GGML_B200_SPLIT_GRAPHS"); v = (e && !atoi(e)) ? 0 : 1; } return v != 0; }
 static bool graphs_on() { static int v = -1; if (v < 0) { const char * e = getenv("GGML_B200_GRAPHS"); v = (e && !atoi(e)) ? 0 : 1; } return v != 0; }
 static inline void hash_mix(uint64_t & h1, uint64_t & h2, uint64_t v) {
     h1 = (h1 ^ v) * 0x100000001b3ull; h1 ^= h1 >> 29;
@@ -763,7 +800,11 @@ static bool graph_identity(const ggml_cgraph * g, uint64_t & h1, uint64_t & h2) 
         for (int k = 0; k < GGML_MAX_SRC; ++k) {
             const ggml_tensor * s = n->src[k];
             if (!s) { hash_mix(h1, h2, 0x5eedull + k); continue; }
-            if (s->buffer && !buft_is_b200(s->buffer->buft)) return false;             // row-split weights: peers, events, staging
+            if (s->buffer && !buft_is_b200(s->buffer->buft)) {
+                // a row-split weight of a MUL_MAT records too (its slices hang off ->extra; events order the peers' streams); anything else does not
+                if (!(k == 0 && n->op == GGML_OP_MUL_MAT && b200_split_of(s) && split_graphs_on())) return false;
+                hash_mix(h1, h2, (uint64_t) (uintptr_t) s->extra);
+            }
             hash_tensor(h1, h2, s);
         }
         // prefill-sized work is not launch-bound and its paths may size scratch by content
@@ -778,7 +819,8 @@ static enum ggml_status be_graph_compute(ggml_backend_t be, ggml_cgraph * g) {
     if (cudaSetDevice(c->device) != cudaSuccess) return GGML_STATUS_FAILED;
     uint64_t h1, h2;
     if (!graphs_on() || c->ctx->profile || c->ctx->trace || c->ctx->capturing || !graph_identity(g, h1, h2)) { ++c->n_eager; return run_nodes(c, g); }
-    const uint64_t epoch = g_layout_epoch.load() * 0x10001ull + b200_ctx_scratch_generation(c->ctx);
+    uint64_t epoch = g_layout_epoch.load() * 0x10001ull + b200_ctx_scratch_generation(c->ctx);
+    for (b200_ctx * p : c->peer) if (p) epoch += 0x101ull * b200_ctx_scratch_generation(p) + 1;       // (a peer appearing or growing a block is a new epoch)
     if (epoch != c->graphs_epoch) {                            // recordings are stale; what was seen before is recorded again right away
         B200_CHECK(cudaStreamSynchronize(c->ctx->stream));
         for (auto & x : c->graphs) { if (x.exec) b200_graph_destroy(x.exec); x.exec = nullptr; x.failed = 0; }
@@ -800,7 +842,9 @@ static enum ggml_status be_graph_compute(ggml_backend_t be, ggml_cgraph * g) {
     if (!e->exec && !e->failed) {
         if (b200_graph_begin(c->ctx) != B200_OK) { e->failed = 1; cudaGetLastError(); }
         else {
+            for (b200_ctx * p : c->peer) if (p) p->capturing = 1;                  // their streams join the capture through the hand-over events
             const enum ggml_status st = run_nodes(c, g);
+            for (b200_ctx * p : c->peer) if (p) { p->capturing = 0; b200_ctx_invalidate(p); }
             void * exec = b200_graph_end(c->ctx);
             c->ctx->qcache.valid = 0; c->ctx->mcache.valid = 0;
             if (st == GGML_STATUS_SUCCESS && exec) { e->exec = exec; ++c->n_captured; }

@@ -73,6 +73,7 @@ struct b200_ctx {
     struct { const void * data; int64_t ne[4]; size_t nb[4]; size_t span; int64_t n; int valid; } mcache;
     int          attr_done[16];
     int          pdl;                // launch the streaming GEMV with programmatic dependent launch (GGML_B200_NO_PDL=1 disables)
+    int          pdl_hold;           // != 0: pdl is off for ONE launch (the first behind a cross-stream event wait: its edge must be a full one) and comes back as this
     // device-side timeline of the decode GEMV kernels (b200_debug_trace; measurement only, NULL in production)
     unsigned long long * trace; int trace_cap;
 };
@@ -104,6 +105,7 @@ void   b200_prof_end(b200_ctx * ctx);
 // every kernel launch is written   B200_LAUNCH(ctx, KIND, kernel<<<grid, block, smem, ctx->stream>>>(args));
 #define B200_LAUNCH(ctx, kind, ...) do { if ((ctx)->profile) b200_prof_begin((ctx), (kind)); __VA_ARGS__; \
         if ((ctx)->profile) b200_prof_end(ctx); (ctx)->launches++; (ctx)->launches_kind[kind]++; \
+        if ((ctx)->pdl_hold) { (ctx)->pdl = (ctx)->pdl_hold; (ctx)->pdl_hold = 0; } \
         cudaError_t e_ = cudaGetLastError(); if (e_ != cudaSuccess) { \
         b200_set_error("%s:%d: kernel launch -> %s", __FILE__, __LINE__, cudaGetErrorString(e_)); return B200_ERR_CUDA; } } while (0)
 

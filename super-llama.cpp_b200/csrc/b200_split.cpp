@@ -163,7 +163,10 @@ ggml_backend_buffer_type_t b200_split_buffer_type(int main_device, const float *
         for (int i = 0; i < n && same; ++i) same = c->start[i] == want.start[i];
         if (same) return b;
     }
-    want.name = "B200_Split";
+    // the name carries the main device (as ggml-cuda.cu:1095 does): llama's loader keys its per-buffer-type contexts by NAME
+    // (ggml_backend_buft_comparator), so two split types with one name would collapse into the one that was listed first and every
+    // layer's matmuls would run on that device's backend, away from the rest of the layer
+    want.name = "B200_" + std::to_string(main_device) + "_Split";
     ggml_backend_buffer_type * b = new ggml_backend_buffer_type{ k_split_buft_iface, b200_logical_dev(main_device), new split_buft_ctx(want) };
     made.push_back(b);
     return b;
