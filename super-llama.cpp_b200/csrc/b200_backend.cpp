@@ -11,6 +11,7 @@
 #include "b200_glue.cuh"   // non-hot-path ops so whole llama graphs stay on the device
 #include "../../include/ggml-b200-abi.h"
 #include "b200_split.h"
+#include <chrono>
 #include <string>
 #include <vector>
 #include <mutex>
@@ -83,6 +84,7 @@ struct b200_backend_ctx {
     // them against this backend's stream
     b200_ctx * peer[B200_SPLIT_MAX_DEVICES] = {}; cudaEvent_t ev_main = nullptr, ev_peer[B200_SPLIT_MAX_DEVICES] = {}; uint64_t n_split = 0;
     std::vector<b200_graph_entry> graphs; uint64_t graphs_epoch = 0, tick = 0, n_replayed = 0, n_captured = 0, n_eager = 0;
+    uint64_t host_ns_compute = 0, host_ns_identity = 0, host_calls = 0;   // GGML_B200_GRAPH_STATS: host time inside graph_compute / its identity hash
     // GGML_B200_GRAPH_STATS: device time of every replay (event pairs, read in be_free) and host time spent inside graph_compute
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> replay_events; double host_us = 0;
     uint64_t n_fuse[5] = { 0, 0, 0, 0, 0 };          // launches saved by: matmul groups, [1] = decode chains launched, ADD+RMS_NORM+MUL, ROPE/SET_ROWS, gate+up+GLU (counted while walking nodes)
@@ -262,6 +264,7 @@ static bool buft_is_b200_host(ggml_backend_buffer_type_t buft) { return buft->if
 // ---- backend (stream) ---------------------------------------------------------------------------------
 static ggml_guid g_guid = { 0xb2, 0x00, 0x5a, 0x10, 0x0a, 0x67, 0x67, 0x6d, 0x6c, 0x2d, 0x62, 0x32, 0x30, 0x30, 0x00, 0x01 };
 
+static uint64_t g_optimize_ns = 0, g_optimize_calls = 0;
 static const char * be_name(ggml_backend_t be) { return ((b200_backend_ctx *) be->context)->name.c_str(); }
 static void be_free(ggml_backend_t be) {
     b200_backend_ctx * c = (b200_backend_ctx *) be->context;
@@ -274,6 +277,9 @@ static void be_free(ggml_backend_t be) {
     if (getenv("GGML_B200_GRAPH_STATS"))
         fprintf(stderr, "ggml-b200 fusions (launches saved while walking nodes): matmul groups %llu, add+norm+mul %llu, rope/set_rows %llu, gate+up+glu %llu, decode chains %llu\n",
                 (unsigned long long) c->n_fuse[0], (unsigned long long) c->n_fuse[2], (unsigned long long) c->n_fuse[3], (unsigned long long) c->n_fuse[4], (unsigned long long) c->n_fuse[1]);
+    if (getenv("GGML_B200_GRAPH_STATS") && c->host_calls)
+        fprintf(stderr, "ggml-b200 host: %llu graph_compute calls, %.1f us each on the host (%.1f us of it the identity hash); graph_optimize %.1f us per call\n", (unsigned long long) c->host_calls,
+                c->host_ns_compute * 1e-3 / c->host_calls, c->host_ns_identity * 1e-3 / c->host_calls, g_optimize_calls ? g_optimize_ns * 1e-3 / g_optimize_calls : 0.0);
     if (getenv("GGML_B200_GRAPH_STATS") && c->n_split)
         fprintf(stderr, "ggml-b200 split: %s ran %llu row-split MUL_MATs over %d devices\n", c->name.c_str(), (unsigned long long) c->n_split, b200_logical_devices());
     if (getenv("GGML_B200_PROFILE") || getenv("GGML_B200_GRAPH_STATS"))
@@ -779,46 +785,77 @@ static enum ggml_status run_nodes(b200_backend_ctx * c, ggml_cgraph * g) {
 // recorded; GGML_B200_GRAPHS=0 turns it off.
 static bool split_graphs_on() { static int v = -1; if (v < 0) { const char * e = getenv("GGML_B200_SPLIT_GRAPHS"); v = (e && !atoi(e)) ? 0 : 1; } return v != 0; }
 static bool graphs_on() { static int v = -1; if (v < 0) { const char * e = getenv("GGML_B200_GRAPHS"); v = (e && !atoi(e)) ? 0 : 1; } return v != 0; }
-static inline void hash_mix(uint64_t & h1, uint64_t & h2, uint64_t v) {
-    h1 = (h1 ^ v) * 0x100000001b3ull; h1 ^= h1 >> 29;
-    h2 = (h2 + v) * 0x9e3779b97f4a7c15ull; h2 ^= h2 >> 32;
-}
-static inline void hash_tensor(uint64_t & h1, uint64_t & h2, const ggml_tensor * t) {
-    hash_mix(h1, h2, (uint64_t) (uintptr_t) t->data); hash_mix(h1, h2, ((uint64_t) t->type << 32) | (uint32_t) t->op);
-    for (int i = 0; i < 4; ++i) { hash_mix(h1, h2, (uint64_t) t->ne[i]); hash_mix(h1, h2, (uint64_t) t->nb[i]); }
-}
+// The walk runs once per token in front of the replay, with the GPU idle (llama synchronizes after every token): 60 us for the ~1100
+// nodes of an 8B decode graph when every value went through one dependent multiply chain and every source was hashed in full again
+// (GGML_B200_GRAPH_STATS, profiles/r2_run13).  So: four independent accumulators (the multiplies overlap), and a tensor that was
+// is one of the eight nodes in front -- most sources are -- only contributes WHICH of them it is (its own walk hashed it in full).  Nothing
+// here depends on where the tensor structs themselves live: llama rebuilds them for every token.
+struct id_hasher {
+    uint64_t a[4] = { 0xcbf29ce484222325ull, 0x84222325cbf29ce4ull, 0x9e3779b97f4a7c15ull, 0xc2b2ae3d27d4eb4full };
+    unsigned n = 0;
+    inline void mix(uint64_t v) { uint64_t & h = a[n++ & 3]; h = (h ^ v) * 0x100000001b3ull; h ^= h >> 29; }
+    inline void tensor(const ggml_tensor * t) {
+        mix((uint64_t) (uintptr_t) t->data); mix(((uint64_t) t->type << 32) | (uint32_t) t->op);
+        for (int i = 0; i < 4; ++i) { mix((uint64_t) t->ne[i]); mix((uint64_t) t->nb[i]); }
+    }
+    inline void finish(uint64_t & h1, uint64_t & h2) const {
+        h1 = a[0] ^ (a[1] << 13 | a[1] >> 51) ^ (a[2] << 29 | a[2] >> 35) ^ (a[3] << 47 | a[3] >> 17);
+        h2 = a[0] * 0x9e3779b97f4a7c15ull + a[1] * 0xc2b2ae3d27d4eb4full + a[2] * 0x165667b19e3779f9ull + a[3] * 0x27d4eb2f165667c5ull + n;
+    }
+};
 static bool graph_identity(const ggml_cgraph * g, uint64_t & h1, uint64_t & h2) {
-    h1 = 0xcbf29ce484222325ull; h2 = 0x84222325cbf29ce4ull;
+    id_hasher H;
     int work = 0;
     for (int i = 0; i < g->n_nodes; ++i) {
         const ggml_tensor * n = g->nodes[i];
-        hash_tensor(h1, h2, n);
+        H.tensor(n);
         if (op_is_view((int) n->op)) continue;
         ++work;
         if (n->buffer && !buft_is_b200(n->buffer->buft)) return false;
-        for (int k = 0; k < (int) (GGML_MAX_OP_PARAMS / sizeof(int32_t)); k += 2) hash_mix(h1, h2, ((uint64_t) (uint32_t) n->op_params[k] << 32) | (uint32_t) n->op_params[k + 1]);
+        for (int k = 0; k < (int) (GGML_MAX_OP_PARAMS / sizeof(int32_t)); k += 2) H.mix(((uint64_t) (uint32_t) n->op_params[k] << 32) | (uint32_t) n->op_params[k + 1]);
+        unsigned present = 0;
         for (int k = 0; k < GGML_MAX_SRC; ++k) {
             const ggml_tensor * s = n->src[k];
-            if (!s) { hash_mix(h1, h2, 0x5eedull + k); continue; }
+            if (!s) continue;
+            present |= 1u << k;
             if (s->buffer && !buft_is_b200(s->buffer->buft)) {
                 // a row-split weight of a MUL_MAT records too (its slices hang off ->extra; events order the peers' streams); anything else does not
                 if (!(k == 0 && n->op == GGML_OP_MUL_MAT && b200_split_of(s) && split_graphs_on())) return false;
-                hash_mix(h1, h2, (uint64_t) (uintptr_t) s->extra);
+                H.mix((uint64_t) (uintptr_t) s->extra);
             }
-            hash_tensor(h1, h2, s);
+            int back = 0;
+            for (int j = 1; j <= 8 && j <= i && !back; ++j) if (g->nodes[i - j] == s) back = j;
+            if (back) H.mix(0xbac0ull | (unsigned) back); else H.tensor(s);
         }
+        H.mix(0x5eed0000ull | present);
         // prefill-sized work is not launch-bound and its paths may size scratch by content
         const int64_t tokens = n->op == GGML_OP_MUL_MAT ? n->ne[1] * n->ne[2] * n->ne[3] : n->op == GGML_OP_MUL_MAT_ID ? n->ne[2] * n->ne[3] :
                                n->op == GGML_OP_FLASH_ATTN_EXT ? n->ne[2] * n->ne[3] : 0;         // (attention result: [head size, heads, tokens])
         if (tokens > 64) return false;
     }
+    H.finish(h1, h2);
     return work >= 2;
 }
+static enum ggml_status be_graph_compute_(ggml_backend_t be, ggml_cgraph * g);
+static inline uint64_t host_now_ns() { return (uint64_t) std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 static enum ggml_status be_graph_compute(ggml_backend_t be, ggml_cgraph * g) {
+    static const bool stats = getenv("GGML_B200_GRAPH_STATS") != nullptr;
+    if (!stats) return be_graph_compute_(be, g);
+    b200_backend_ctx * c = (b200_backend_ctx *) be->context;
+    const uint64_t t0 = host_now_ns();
+    const enum ggml_status st = be_graph_compute_(be, g);
+    c->host_ns_compute += host_now_ns() - t0; ++c->host_calls;
+    return st;
+}
+static enum ggml_status be_graph_compute_(ggml_backend_t be, ggml_cgraph * g) {
     b200_backend_ctx * c = (b200_backend_ctx *) be->context;
     if (cudaSetDevice(c->device) != cudaSuccess) return GGML_STATUS_FAILED;
     uint64_t h1, h2;
-    if (!graphs_on() || c->ctx->profile || c->ctx->trace || c->ctx->capturing || !graph_identity(g, h1, h2)) { ++c->n_eager; return run_nodes(c, g); }
+    static const bool stats = getenv("GGML_B200_GRAPH_STATS") != nullptr;
+    const uint64_t ti = stats ? host_now_ns() : 0;
+    const bool same = graphs_on() && !c->ctx->profile && !c->ctx->trace && !c->ctx->capturing && graph_identity(g, h1, h2);
+    if (stats) c->host_ns_identity += host_now_ns() - ti;
+    if (!same) { ++c->n_eager; return run_nodes(c, g); }
     uint64_t epoch = g_layout_epoch.load() * 0x10001ull + b200_ctx_scratch_generation(c->ctx);
     for (b200_ctx * p : c->peer) if (p) epoch += 0x101ull * b200_ctx_scratch_generation(p) + 1;       // (a peer appearing or growing a block is a new epoch)
     if (epoch != c->graphs_epoch) {                            // recordings are stale; what was seen before is recorded again right away
@@ -856,7 +893,6 @@ static enum ggml_status be_graph_compute(ggml_backend_t be, ggml_cgraph * g) {
         }
     }
     if (e->exec) {
-        static const bool stats = getenv("GGML_B200_GRAPH_STATS") != nullptr;
         cudaEvent_t e0 = nullptr, e1 = nullptr;
         if (stats && c->replay_events.size() < 8192) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, c->ctx->stream); }
         const int rc = b200_graph_launch(c->ctx, e->exec);
@@ -885,9 +921,16 @@ static void be_event_wait(ggml_backend_t be, ggml_backend_event_t ev) {
 static bool is_weight_leaf(const ggml_tensor * w) {
     return w && w->op == GGML_OP_NONE && w->view_src == nullptr && w->buffer && w->buffer->usage == GGML_BACKEND_BUFFER_USAGE_WEIGHTS;
 }
+static void graph_optimize_(ggml_cgraph * g);
 static void be_graph_optimize(ggml_backend_t, ggml_cgraph * g) {
     static const bool off = [] { const char * e = getenv("GGML_B200_NO_REORDER"); return e && atoi(e); }();
     if (off || fuse_off()) return;
+    static const bool stats = getenv("GGML_B200_GRAPH_STATS") != nullptr;
+    const uint64_t t0 = stats ? host_now_ns() : 0;
+    graph_optimize_(g);
+    if (stats) { g_optimize_ns += host_now_ns() - t0; ++g_optimize_calls; }
+}
+static void graph_optimize_(ggml_cgraph * g) {
     for (int i = 0; i < g->n_nodes; ++i) {
         ggml_tensor * a = g->nodes[i];
         if (a->op != GGML_OP_MUL_MAT || !is_weight_leaf(a->src[0])) continue;
