@@ -134,7 +134,7 @@ class HotPathModel:
     """The hot-path nodes of one llama decode/prefill step over device-resident random-init Q4_K_M weights.
     rank/world: split-mode=row shard (rows [lo, hi) of every weight); world == 1 is the whole model."""
 
-    def __init__(self, B, ctx, cfg, n_tokens, depth, rank=0, world=1, seed=1234, alloc=None, dist=None, quant="q4_k_m", chain=True):
+    def __init__(self, B, ctx, cfg, n_tokens, depth, rank=0, world=1, seed=1234, alloc=None, dist=None, quant="q4_k_m", chain=True, peer=None):
         self.B, self.ctx, self.cfg, self.N = B, ctx, cfg, n_tokens
         self.quant = quant
         self.moe = cfg.get("n_expert", 0)
@@ -226,10 +226,21 @@ class HotPathModel:
         ctx.synchronize()
         self.gather = None          # set by the multi-GPU driver: gather(full_tensor, lo, hi) after a sharded matmul
         self.chains = None
-        if chain and N == 1 and world == 1 and not self.moe and not os.environ.get("B200_BENCH_NO_CHAIN"):
-            self._build_chains(rng)
+        self.peer = peer
+        self.chain_splits = None
+        # chain: True = the default form on one GPU, the row-split form (b200_decode_chain_split: the all-gather inside the kernel's hand-over)
+        # over the peer exchange's arenas on several; "split" = the row-split form's arithmetic on ONE GPU (what the split check compares with)
+        split_form = (world > 1 and peer is not None) or chain == "split"
+        if chain and N == 1 and (world == 1 or peer is not None) and not self.moe and not os.environ.get("B200_BENCH_NO_CHAIN") and \
+           not (world > 1 and os.environ.get("B200_BENCH_NO_SPLIT_CHAIN")):
+            self._build_chains(rng, alloc, split_form)
 
-    def _build_chains(self, rng):
+    def reset_state(self):
+        """the residual stream the chains carry from step to step, back to its first value (so that two models can be compared after any number of steps)"""
+        if self.chains is not None:
+            self.ctx.h2d(self.resid[0].ptr, self.resid0_host)
+
+    def _build_chains(self, rng, alloc=None, split_form=False):
         """One b200_decode_chain program per layer: everything between two attention operators of the llama graph (src/models/llama.cpp:40-130)
         -- wo, +residual, ffn_norm, ffn_gate / ffn_up, SwiGLU, ffn_down, +ffn_inp, attn_norm of the next layer, its wq / wk / wv (the last
         layer: output_norm and the output head) -- with the data really flowing from node to node.  None when the kernel declines the model
@@ -239,7 +250,17 @@ class HotPathModel:
         col = lambda n: ctx.empty(F32, [n])
         normw = lambda: ctx.upload(F32, [e], rng.uniform(0.5, 1.5, e).astype(np.float32))
         self.resid = [col(e), col(e)]                       # l_out of layer il - 1 / il (ping-pong); resid[0] starts as the token's embedding row
-        ctx.h2d(self.resid[0].ptr, rng.standard_normal(e).astype(np.float32))
+        self.resid0_host = rng.standard_normal(e).astype(np.float32)
+        ctx.h2d(self.resid[0].ptr, self.resid0_host)
+        ll_ptrs = ll_bytes = None
+        if split_form:
+            # the hand-over areas: inside the exchange arena (same offset on every rank, mapped by every rank) / a plain zeroed block on one GPU
+            ll_bytes = int(B.lib().b200_decode_chain_split_bytes(cfg["n_vocab"]))
+            ll = (alloc or (lambda t, ne: ctx.empty(t, ne)))(F32, [ll_bytes // 4])
+            B._check(B.lib().b200_memset(ctx.h, ll.ptr, 0, ll_bytes), "memset")
+            ll_ptrs = [ll.ptr] if self.world == 1 else [int(self.peer.ex.base[r]) + (ll.ptr - self.peer.base) for r in range(self.world)]
+            self._ll = ll
+        splits = []
         self.ffn_inp = col(e)
         q1, k1, v1 = (t.view([t.ne[0], 1, 1, 1], [4, t.ne[0] * 4, t.ne[0] * 4, t.ne[0] * 4]) for t in (self.q, self.k, self.v))
         cols = {n: getattr(self, n).view([getattr(self, n).ne[0], 1, 1, 1], [4] + [getattr(self, n).ne[0] * 4] * 3) for n in ("attn", "o", "g", "u", "ff", "d", "logits")}
@@ -254,10 +275,19 @@ class HotPathModel:
                   dict(w=[L["down"][0]], dst=[cols["d"]], in0=cols["ff"]),
                   dict(w=tail_w, dst=tail_d, prologue=B.X_ADD_NORM_MUL, eps=1e-5, in0=cols["d"], in1=self.ffn_inp, normw=normw(), out_add=self.resid[(il + 1) % 2])]
             prog = ctx.chain_program(ph)
-            if not ctx.decode_chain_supported(prog):
+            if split_form:
+                tail_lo = [self.output[1]] if last else [self.layers[il + 1][n][1] for n in ("wq", "wk", "wv")]
+                sp = ctx.chain_split(self.world, self.rank, ll_ptrs, ll_bytes, [[L["wo"][1]], [L["gate"][1], L["up"][1]], [L["down"][1]], tail_lo])
+                if not ctx.decode_chain_split_supported(prog, sp):
+                    if self.rank == 0:
+                        print("bench: row-split decode chain declined:", B.lib().b200_last_error().decode(), file=sys.stderr)
+                    return
+                splits.append(sp)
+            elif not ctx.decode_chain_supported(prog):
                 return
             chains.append(prog)
         self.chains = chains
+        self.chain_splits = splits if split_form else None
         self._keep = (q1, k1, v1, cols)
 
     def _mm(self, w, x, dst):
@@ -304,7 +334,7 @@ class HotPathModel:
             for il in range(len(self.layers)):
                 if attention:
                     c.flash_attn_ext(self.qview, self.kviews[il], self.vviews[il], self.mask, None, self.attn4, self.scale)
-                c.decode_chain(self.chains[il])
+                c.decode_chain(self.chains[il], self.chain_splits[il] if self.chain_splits else None)
             return
         fuse = True      # wq/wk/wv and gate/up share src1: one launch per run of equal weight types (GEMV at n=1, GEMM at n=512)
         # In the real graph every matmul input is rewritten by the glue op in front of it (RMS_NORM, attention, SwiGLU), so its cached
@@ -517,8 +547,7 @@ def run_b200(args):
         dt.torch = buf
         return dt
 
-    tg = HotPathModel(B, ctx, cfg, 1, args.depth, rank, world, alloc=alloc, dist=dist, quant=args.quant)
-    tg.peer = peer
+    tg = HotPathModel(B, ctx, cfg, 1, args.depth, rank, world, alloc=alloc, dist=dist, quant=args.quant, peer=peer)
     if world > 1 and peer is None and replicas == 1:
         ext = torch.cuda.ExternalStream(ctx.stream, device=f"cuda:{local}")
 
@@ -631,19 +660,30 @@ def run_b200(args):
     if world > 1 and replicas == 1:
         import hashlib
         names = ("q", "k", "v", "o", "g", "u", "d", "logits")
+        chained = tg.chains is not None
+        # (with the chain, gate / up leave the kernel as their SwiGLU product: every rank holds only its own rows of g and u)
+        # and wo's / ffn_down's results are handed on as quantized blocks by their row owners: the same holds for o and d)
+        Ll = tg.layers[-1]
+        part = {"g": Ll["gate"][1:], "u": Ll["up"][1:], "o": Ll["wo"][1:], "d": Ll["down"][1:]} if chained else {}
+        tg.reset_state()
         tg.step(); ctx.synchronize()
         mine = {n: ctx.download(getattr(tg, n)).reshape(-1).copy() for n in names}
-        digest = hashlib.sha1(b"".join(mine[n].tobytes() for n in names)).hexdigest()
+        digest = hashlib.sha1(b"".join(mine[n].tobytes() for n in names if n not in part)).hexdigest()
         digests = [None] * world
         dist.all_gather_object(digests, digest)
         ok = [len(set(digests)) == 1]
         if rank == 0:
-            one = HotPathModel(B, ctx, cfg, 1, args.depth, 0, 1, quant=args.quant, chain=False)
-            for n in ("x", "h", "ff", "attn"):             # the same inputs, as they are NOW (the e2e leg above uploaded its own embedding row into x)
+            # the unsplit model: separate launches / the chain in the same hand-over form on one GPU (then every word must be equal: a row's
+            # dot product is summed in the same order whichever rank or CTA owns it)
+            one = HotPathModel(B, ctx, cfg, 1, args.depth, 0, 1, quant=args.quant, chain="split" if chained else False)
+            for n in ("x",) if chained else ("x", "h", "ff", "attn"):   # the same inputs, as they are NOW (the e2e leg above uploaded its own embedding row into x)
                 ctx.h2d(getattr(one, n).ptr, ctx.download(getattr(tg, n)).reshape(-1))
+            one.reset_state()
             one.step(); ctx.synchronize()
             whole = {n: ctx.download(getattr(one, n)).reshape(-1).copy() for n in names}
             del one
+            for n, (lo, hi) in part.items():
+                mine[n], whole[n] = mine[n][lo:hi], whole[n][lo:hi]
             diff = {n: int((whole[n].view(np.uint32) != mine[n].view(np.uint32)).sum()) for n in names}
             err = {n: float(((whole[n].astype(np.float64) - mine[n]) ** 2).sum() / max((whole[n].astype(np.float64) ** 2).sum(), 1e-300)) for n in names}
             # (the unsplit model may pick another GEMV kernel for a shape than the sharded one does: a different summation order, a few last-bit

@@ -182,6 +182,24 @@ typedef struct b200_chain_phase {
 } b200_chain_phase;
 B200_API int b200_decode_chain(b200_ctx * ctx, const b200_chain_phase * phases, int n_phases);
 B200_API int b200_decode_chain_supported(b200_ctx * ctx, const b200_chain_phase * phases, int n_phases);   // 1 / 0
+/* The chain ROW-SPLIT over the GPUs of one node, one process per GPU (the decode form of the reference's split-mode row,
+ * ggml/src/ggml-cuda/ggml-cuda.cu:1451-1769, where every MUL_MAT is followed by a copy of the dst slices back to the main device): every
+ * rank launches the same program; its weights w[i] hold rows [row_lo[p][i], row_lo[p][i] + w[i]->ne[1]) (multiples of 32) of result i of
+ * phase p, dst[i] / glu / in0 are the FULL columns.  The all-gather is the hand-over between the phases itself: a result row is stored as
+ * a (value, tag) pair into EVERY rank's hand-over area (NVLink peer stores), each rank's CTAs poll their own copy.  ll[r] = rank r's area
+ * (b200_decode_chain_split_bytes(rows of the last phase's results) bytes, zeroed once, peer-mapped in this process); after the launch
+ * every rank holds the full last-phase results, the full in0 columns, and its own rows of everything else.  No ROPE / KV-cache tail.
+ * world == 1 is allowed (same arithmetic on one GPU: what the split results are compared with, bit for bit). */
+#define B200_CHAIN_SPLIT_MAX_PEERS 8
+typedef struct b200_chain_split {
+    int32_t  world, rank;
+    void *   ll[B200_CHAIN_SPLIT_MAX_PEERS];
+    uint64_t ll_bytes;
+    int64_t  row_lo[B200_CHAIN_MAX_PHASES][3];
+} b200_chain_split;
+B200_API int    b200_decode_chain_split(b200_ctx * ctx, const b200_chain_phase * phases, int n_phases, const b200_chain_split * split);
+B200_API int    b200_decode_chain_split_supported(b200_ctx * ctx, const b200_chain_phase * phases, int n_phases, const b200_chain_split * split);
+B200_API size_t b200_decode_chain_split_bytes(int64_t last_rows);
 /* every wait inside the chain kernel is bounded (2 s): 0, or the code of the first wait that ran out since the last call (synchronizes) */
 B200_API int b200_decode_chain_error(b200_ctx * ctx);
 // as[K, M, n_expert], b[K, n_used|1, n_tokens] f32, ids[n_used, n_tokens] i32 -> dst[M, n_used, n_tokens]

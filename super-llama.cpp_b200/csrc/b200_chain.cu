@@ -54,7 +54,9 @@ enum { CH_IN_EXTERNAL = 0,   // written before this launch: plain loads
        CH_IN_LL_F32   = 2,   // (value, tag) pairs of the phase before
        CH_IN_LL_Q8    = 3,   // q8_1 blocks of the SWIGLU phase before (10 (word, tag) pairs per block) + (value, tag) pairs of its tail rows
        CH_IN_BQ8      = 4,   // arrival counter, then plain loads of the q8_1 blocks the SWIGLU phase before quantized itself (+ its f32 tail rows)
-       CH_IN_BQ8N     = 5 }; // arrival counter, then q8_1 blocks of (result + residual) * norm weight and per-block sums of squares from the row owners
+       CH_IN_BQ8N     = 5,   // arrival counter, then q8_1 blocks of (result + residual) * norm weight and per-block sums of squares from the row owners
+       CH_IN_LQ8N     = 6 }; // row split only: the same records from the row owners of EVERY rank as 11 (word, tag) pairs per block (8 quant words, d, sum, sum of squares), polled
+#define CH_LQ_REC 96         // bytes per CH_IN_LQ8N record (12 pairs, the last one unused)
 // (The two owner-side forms were also tried with the validity flag in the data -- 12 (word, tag) pairs per block, no fence in the producer, no
 // counter, the readers poll the records: 47.0 against 44.0 us per 8B layer in the same build.  148 x 512 polling threads compete with the
 // producers' stores, and the poll loops cost the kernel 14 registers.  Removed.)
@@ -64,7 +66,7 @@ enum { CH_IN_EXTERNAL = 0,   // written before this launch: plain loads
 #define CH_HSS   (80 * 1024)
 #define CH_HTAIL (96 * 1024)
 
-struct ch_seg { const uint8_t * w; size_t nb1; float * dst; int M; int q6; int map; };      // map: index of the weight's 2-D tensor map
+struct ch_seg { const uint8_t * w; size_t nb1; float * dst; int M; int q6; int map; int row0; };      // map: index of the weight's 2-D tensor map; row0: row-split launches: the row of the FULL result this rank's row 0 is (dst already points there)
 struct ch_phase {
     int prologue, epilogue, K, nseg;
     ch_seg seg[CH_MAXSEG];
@@ -96,6 +98,14 @@ struct ch_args {
     int own_in1;           // CH_IN_BQ8N: the producing phase whose row owners fetch their rows of an addend from outside at the very start, or -1
     unsigned * sync;       // [0] phase arrivals (CH_IN_BARRIER), [1] CTAs done, [2] error code, [3] hand-over epoch, [4] abort
     uint8_t * ll;          // hand-over areas, CH_LL_BYTES per phase
+    // Row split over several GPUs (b200_decode_chain_split; one process per GPU, every rank launches the same chain on its own rows of every
+    // weight): a result row goes as a (value, tag) pair into the hand-over area of EVERY rank (NVLink peer stores: an aligned 8-byte store is
+    // one transaction, the tag validates the value, no fence and no counter -- a system-scope fence measured ~7 us), and every rank's CTAs poll
+    // their own copy exactly as they do on one GPU: the all-gather IS the hand-over.  llr[r] = rank r's areas as mapped here (llr[rank] == ll).
+    // The last phase's results are needed in full by whatever follows the launch: published the same way into the area behind the phases'
+    // (fin_off), and unpacked into the plain f32 columns fin[i].dst by all CTAs before the kernel ends.
+    int nrank; uint8_t * llr[B200_MAX_PEERS];
+    int fin_total; unsigned fin_off; struct { float * dst; int M; int base; } fin[CH_MAXSEG];
     int dbg;               // GGML_B200_CHAIN_DBG (measurement only): 1 skip the dot products, 2 no weight traffic
     unsigned long long * trace; int trace_cap;   // b200_debug_trace (measurement only): per CTA and phase, globaltimer at 5 points
 };
@@ -136,6 +146,11 @@ static __device__ __forceinline__ uint4 ch_ll_load2(const void * p) {      // tw
     uint4 r;
     asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
     return r;
+}
+// the same pair into every rank's copy of a hand-over area (one GPU: one plain store)
+template <bool SP> static __device__ __forceinline__ void ch_ll_pub(const ch_args & P, size_t off, unsigned v, unsigned tag) {
+    if (!SP || P.nrank <= 1) { ch_ll_store(P.ll + off, v, tag); return; }
+    for (int r = 0; r < P.nrank; ++r) ch_ll_store(P.llr[r] + off, v, tag);
 }
 template <int NT> static __device__ __forceinline__ void ch_bar_n() { asm volatile("bar.sync 1, %0;" :: "n"(NT) : "memory"); }
 #define ch_bar_consumers() ch_bar_n<CH_NT>()
@@ -241,7 +256,7 @@ static __device__ __forceinline__ void ch_consume_q4k(uint32_t st, int lane, uin
     }
 }
 
-template <int CH_NW, bool TR>      // TR: the measurement hooks (b200_debug_trace, GGML_B200_CHAIN_DBG) are compiled in
+template <int CH_NW, bool TR, bool SP = false>      // TR: the measurement hooks (b200_debug_trace, GGML_B200_CHAIN_DBG) are compiled in; SP: row split over several GPUs
 __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_constant__ ch_args P) {
     constexpr int CH_NT = CH_NW * 32;
     extern __shared__ __align__(128) uint8_t smem[];
@@ -337,9 +352,9 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
         CH_STAMP(0);
         // what does not depend on the phase before is fetched ahead of the hand-over: the norm weight, and a residual from outside
         // (every CTA reads the same lines at the same moment: ~9 B/clk per SM of L2 broadcast bandwidth, measured -- bytes on the critical path count)
-        const bool own_in = ph.in_mode == CH_IN_BQ8N;            // the row owners of the phase before did ADD, norm weight and quantization
+        const bool own_in = ph.in_mode == CH_IN_BQ8N || (SP && ph.in_mode == CH_IN_LQ8N);   // the row owners of the phase before did ADD, norm weight and quantization
         const bool normp = ph.prologue != B200_CHAIN_X_PLAIN && !own_in, addp = ph.prologue == B200_CHAIN_X_ADD_NORM_MUL && !own_in, live = normp && tid < nu16;
-        const bool own_out = ph.out_mode == CH_IN_BQ8N && tid < own.gl * 32;      // (warp-uniform: whole groups)
+        const bool own_out = (ph.out_mode == CH_IN_BQ8N || (SP && ph.out_mode == CH_IN_LQ8N)) && tid < own.gl * 32;      // (warp-uniform: whole groups)
         float nwpre = 0.0f;                                      // the next phase's norm weight of this thread's row
         if (own_out) nwpre = __ldg(ph.nx_normw + ch_unit(ph, tid >> 2, own, G) * CH_R + (tid & 3));
         float4 gpre[4], bpre[4];
@@ -386,7 +401,46 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
         CH_STAMP(1);
         // (2) this CTA's q8_1 image of the activation column
         const uint8_t * llin = P.ll + (size_t) (p > 0 ? p - 1 : 0) * CH_LL_BYTES;
-        if (own_in) {
+        if (SP && ph.in_mode == CH_IN_LQ8N) {
+            // the owner-side records of all ranks, validated word by word by their tags: this thread's units (K <= 64 CH_NT), then the norm's scale as below
+            int4 w[4]; int2 ds[4];
+            float ssp = 0.0f;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int u = tid + i * CH_NT;
+                w[i] = make_int4(0, 0, 0, 0); ds[i] = make_int2(0, 0);
+                if (u < nu16) {
+                    const uint8_t * rec = llin + (size_t) (u >> 1) * CH_LQ_REC;
+                    ch_watch wt;
+                    while (true) {
+                        const uint4 q0 = ch_ll_load2(rec + (u & 1) * 32), q1 = ch_ll_load2(rec + (u & 1) * 32 + 16), dd = ch_ll_load2(rec + 64);
+                        unsigned sv = 0, st = tag;
+                        if (!(u & 1)) asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(sv), "=r"(st) : "l"(rec + 80) : "memory");
+                        if (q0.y == tag && q0.w == tag && q1.y == tag && q1.w == tag && dd.y == tag && dd.w == tag && st == tag) {
+                            w[i] = make_int4((int) q0.x, (int) q0.z, (int) q1.x, (int) q1.z); ds[i] = make_int2((int) dd.x, (int) dd.z);
+                            if (!(u & 1)) ssp += __uint_as_float(sv);
+                            break;
+                        }
+                        if (wt.spin(P.sync, 0x900u + p)) break;
+                    }
+                }
+            }
+            ssp = warp_sum(ssp);
+            if (lane == 0) s_red[warp] = ssp;
+            ch_bar_consumers();
+            float tot = 0.0f;
+#pragma unroll
+            for (int i = 0; i < CH_NW; ++i) tot += s_red[i];
+            const float scale = rsqrtf(tot / (float) K + ph.eps);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int u = tid + i * CH_NT;
+                if (u < nu16) {
+                    const float d = __int_as_float(ds[i].x) * scale;
+                    ch_store_unit(u, w[i], __half2float(__float2half_rn(d)), __half2float(__float2half_rn(__fmul_rn(d, (float) ds[i].y))), K, nblocks, ph.types, s_act);
+                }
+            }
+        } else if (own_in) {
             // (result + residual) * norm weight arrives as q8_1 blocks whose scale still lacks RMS_NORM's factor; the block sums of squares give it.
             // This thread's units (K <= 64 CH_NT) are in flight while the sum is reduced
             const uint8_t * hq = llin + CH_HQ, * hds = llin + CH_HDS, * hss = llin + CH_HSS;
@@ -506,6 +560,10 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
                         if (ok) break;
                         if (w.spin(P.sync, 0x600u + p)) break;
                     }
+                    if (SP && P.nrank > 1 && cta == 0) {            // row split: the gathered column also becomes the plain f32 tensor it is in the graph
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) *(float4 *) ((float *) ph.in0 + (size_t) u * 16 + 4 * j) = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+                    }
                 }
             };
             for (int base = tid & ~31; base < nu16; base += CH_NT) {
@@ -527,6 +585,10 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
                     for (int j = 0; j < 8; ++j) { const uint4 v = ch_ll_load2(llin + ((size_t) tid * 16 + 2 * j) * 8); h[2 * j] = __uint_as_float(v.x); h[2 * j + 1] = __uint_as_float(v.z); ok = ok && v.y == tag && v.w == tag; }
                     if (ok) break;
                     if (w.spin(P.sync, 0x700u + p)) break;
+                }
+                if (SP && P.nrank > 1 && cta == 0) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) *(float4 *) ((float *) ph.in0 + (size_t) tid * 16 + 4 * j) = make_float4(h[4 * j], h[4 * j + 1], h[4 * j + 2], h[4 * j + 3]);
                 }
             } else {
 #pragma unroll
@@ -657,9 +719,9 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
                     if ((lane & 3) == 0) *(unsigned *) (llout + CH_HQ + (size_t) (row >> 5) * 32 + lane) = wq;
                     if (lane == 1) *(int2 *) (llout + CH_HDS + (size_t) (row >> 5) * 8) = make_int2(__float_as_int(d), isum);
                 } else {
-                    uint8_t * blk = llout + (size_t) (row >> 5) * 80;
-                    if ((lane & 3) == 0) ch_ll_store(blk + (lane >> 2) * 8, wq, tag);
-                    if (lane == 1) { const __half2 ds = q8_1_ds(d, isum); ch_ll_store(blk + 64, *(const unsigned *) &ds, tag); }
+                    const size_t blk = (size_t) p * CH_LL_BYTES + (size_t) (((SP ? ph.seg[0].row0 : 0) + row) >> 5) * 80;
+                    if ((lane & 3) == 0) ch_ll_pub<SP>(P, blk + (lane >> 2) * 8, wq, tag);
+                    if (lane == 1) { const __half2 ds = q8_1_ds(d, isum); ch_ll_pub<SP>(P, blk + 64, *(const unsigned *) &ds, tag); }
                 }
             }
             for (int t = nrow_g + tid; t < nunits_l * CH_R; t += CH_NT) {
@@ -667,11 +729,11 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
                 const int row = row_of(t, gsum, usum);
                 const float v = b200_swiglu1(gsum, usum);
                 ph.seg[0].dst[row] = gsum; ph.seg[1].dst[row] = usum; ph.glu[row] = v;
-                if (ph.out_mode == CH_IN_LL_F32) ch_ll_store(llout + (size_t) row * 8, __float_as_uint(v), tag);
+                if (ph.out_mode == CH_IN_LL_F32) ch_ll_pub<SP>(P, (size_t) p * CH_LL_BYTES + (size_t) ((SP ? ph.seg[0].row0 : 0) + row) * 8, __float_as_uint(v), tag);
                 else if (ph.out_mode == CH_IN_LL_Q8) ch_ll_store(llout + (size_t) (ph.ng8 * CH_R >> 5) * 80 + (size_t) (row - ph.ng8 * CH_R) * 8, __float_as_uint(v), tag);
                 else if (ph.out_mode == CH_IN_BQ8) *(float *) (llout + CH_HTAIL + (size_t) (row - ph.ng8 * CH_R) * 4) = v;
             }
-        } else if (ph.out_mode == CH_IN_BQ8N) {
+        } else if (ph.out_mode == CH_IN_BQ8N || (SP && ph.out_mode == CH_IN_LQ8N)) {
             // thread = one row of this CTA's groups (whole q8_1 blocks of the next phase's activation; warp = group): the matmul result, the
             // residual sum h, and h * norm weight as a q8_1 block with the block's sum of squares of h next to it
             if (own_out) {
@@ -689,9 +751,17 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
                 unsigned wq = (unsigned) q & 0xffu;
                 wq |= __shfl_down_sync(0xffffffffu, wq, 1) << 8;
                 wq |= __shfl_down_sync(0xffffffffu, wq, 2) << 16;
-                if ((lane & 3) == 0) *(unsigned *) (llout + CH_HQ + (size_t) (row >> 5) * 32 + lane) = wq;
-                if (lane == 1) *(int2 *) (llout + CH_HDS + (size_t) (row >> 5) * 8) = make_int2(__float_as_int(d), isum);
-                if (lane == 2) *(float *) (llout + CH_HSS + (size_t) (row >> 5) * 4) = ss;
+                if (SP && ph.out_mode == CH_IN_LQ8N) {
+                    const size_t rec = (size_t) p * CH_LL_BYTES + (size_t) ((ph.seg[0].row0 + row) >> 5) * CH_LQ_REC;
+                    if ((lane & 3) == 0) ch_ll_pub<SP>(P, rec + (lane >> 2) * 8, wq, tag);
+                    if (lane == 1) ch_ll_pub<SP>(P, rec + 64, (unsigned) __float_as_int(d), tag);
+                    if (lane == 2) ch_ll_pub<SP>(P, rec + 72, (unsigned) isum, tag);
+                    if (lane == 3) ch_ll_pub<SP>(P, rec + 80, __float_as_uint(ss), tag);
+                } else {
+                    if ((lane & 3) == 0) *(unsigned *) (llout + CH_HQ + (size_t) (row >> 5) * 32 + lane) = wq;
+                    if (lane == 1) *(int2 *) (llout + CH_HDS + (size_t) (row >> 5) * 8) = make_int2(__float_as_int(d), isum);
+                    if (lane == 2) *(float *) (llout + CH_HSS + (size_t) (row >> 5) * 4) = ss;
+                }
             }
         } else if (p == P.tail_phase) {
             // the layer's last matmuls with what the graph does to their rows next: ROPE (adjacent pairs: both rows of a pair sit in one unit,
@@ -735,7 +805,8 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
                 for (int c = 0; c < ph.nch; ++c) sum += s_psum[(k * ph.nch + c) * CH_R + r];
                 int sg, row; ch_locate(ph, ch_unit(ph, k, own, G), sg, row);
                 ph.seg[sg].dst[row + r] = sum;
-                if (ph.out_mode == CH_IN_LL_F32) ch_ll_store(llout + (size_t) (row + r) * 8, __float_as_uint(sum), tag);   // (single-segment phases only)
+                if (ph.out_mode == CH_IN_LL_F32) ch_ll_pub<SP>(P, (size_t) p * CH_LL_BYTES + (size_t) ((SP ? ph.seg[0].row0 : 0) + row + r) * 8, __float_as_uint(sum), tag);   // (single-segment phases only)
+                else if (SP && P.fin_total && p == P.nph - 1) ch_ll_pub<SP>(P, (size_t) P.fin_off + (size_t) (P.fin[sg].base + ph.seg[sg].row0 + row + r) * 8, __float_as_uint(sum), tag);
             }
         }
         if (ph.out_mode == CH_IN_BARRIER || ph.out_mode == CH_IN_BQ8 || ph.out_mode == CH_IN_BQ8N) {
@@ -744,6 +815,25 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
             target += (unsigned) G;
         }
         CH_STAMP(4);
+    }
+    // row split: the last phase's results, gathered from every rank, as plain f32 columns (this rank's own rows were stored above: skipped)
+    if (SP && P.fin_total) {
+        const uint8_t * fin = P.ll + P.fin_off;
+        for (int i = cta * CH_NT + tid; i < P.fin_total; i += G * CH_NT) {
+            int sg = 0;
+            if (i >= P.fin[1].base && P.fin[1].M) sg = 1;
+            if (i >= P.fin[2].base && P.fin[2].M) sg = 2;
+            const int row = i - P.fin[sg].base;
+            const ch_seg & S = P.ph[P.nph - 1].seg[sg];
+            if (row >= S.row0 && row < S.row0 + S.M) continue;
+            ch_watch w; unsigned v, t;
+            while (true) {
+                asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(v), "=r"(t) : "l"(fin + (size_t) i * 8) : "memory");
+                if (t == tag) break;
+                if (w.spin(P.sync, 0x800u)) break;
+            }
+            P.fin[sg].dst[row] = __uint_as_float(v);
+        }
     }
     // the last CTA to finish re-arms the counters and advances the epoch for the next launch (every CTA has passed every wait by then)
     if (P.nph > 1) {
@@ -789,10 +879,15 @@ static bool ch_groups_balanced(int ngroups, int G) { const int per = (ngroups + 
 
 // fills the kernel arguments; B200_ERR_UNSUPPORTED (with a reason) when the chain is not one this kernel takes
 static size_t kb_of(int K) { return (size_t) K * 4; }
-static bool ch_is_own_norm(int mode) { return mode == CH_IN_BQ8N; }
-static int ch_build(b200_ctx * ctx, const b200_chain_phase * phases, int n, ch_args & A, size_t & smem) {
+static bool ch_is_own_norm(int mode) { return mode == CH_IN_BQ8N || mode == CH_IN_LQ8N; }
+// row split (sp): result i of phase p is the FULL column dst[i]; this rank's weight holds its rows [row_lo, row_lo + w->ne[1])
+static bool ch_col_part_ok(const b200_tensor * t, int64_t lo, int64_t n) {
+    return t && t->type == B200_TYPE_F32 && t->nb[0] == 4 && lo >= 0 && lo % 32 == 0 && t->ne[0] >= lo + n && t->ne[1] == 1 && t->ne[2] == 1 && t->ne[3] == 1 && ((uintptr_t) t->data & 15) == 0;
+}
+static int ch_build(b200_ctx * ctx, const b200_chain_phase * phases, int n, ch_args & A, size_t & smem, const b200_chain_split * sp = nullptr) {
+    if (sp && (sp->world < 1 || sp->world > B200_MAX_PEERS || sp->rank < 0 || sp->rank >= sp->world)) { b200_set_error("decode_chain_split: bad world / rank"); return B200_ERR_INVALID; }
     if (!phases || n < 1 || n > CH_MAXPH) { b200_set_error("decode_chain: 1..%d phases", CH_MAXPH); return B200_ERR_UNSUPPORTED; }
-    const int G = ctx->sm_count, nw = ch_nw();
+    const int G = ctx->sm_count, nw = sp ? 16 : ch_nw();
     if (G < 3) { b200_set_error("decode_chain: needs at least 3 SMs"); return B200_ERR_UNSUPPORTED; }
     memset(&A, 0, sizeof(A));
     A.nph = n;
@@ -810,8 +905,9 @@ static int ch_build(b200_ctx * ctx, const b200_chain_phase * phases, int n, ch_a
         int64_t Mtot = 0;
         for (int i = 0; i < s.n_w; ++i) {
             if (!ch_weight_ok(s.w[i]) || s.w[i]->ne[0] != K) { b200_set_error("decode_chain: phase %d weight %d is not raw q4_K / repacked q6_K with K %% 2048 == 0, M %% 4 == 0", p, i); return B200_ERR_UNSUPPORTED; }
-            if (!ch_col_ok(s.dst[i], s.w[i]->ne[1])) { b200_set_error("decode_chain: phase %d result %d is not an f32 column of %lld", p, i, (long long) s.w[i]->ne[1]); return B200_ERR_UNSUPPORTED; }
-            d.seg[i].w = (const uint8_t *) s.w[i]->data; d.seg[i].nb1 = s.w[i]->nb[1]; d.seg[i].dst = (float *) s.dst[i]->data; d.seg[i].M = (int) s.w[i]->ne[1];
+            const int64_t lo = sp ? sp->row_lo[p][i] : 0;
+            if (sp ? !ch_col_part_ok(s.dst[i], lo, s.w[i]->ne[1]) : !ch_col_ok(s.dst[i], s.w[i]->ne[1])) { b200_set_error("decode_chain: phase %d result %d is not an f32 column of %lld", p, i, (long long) s.w[i]->ne[1]); return B200_ERR_UNSUPPORTED; }
+            d.seg[i].w = (const uint8_t *) s.w[i]->data; d.seg[i].nb1 = s.w[i]->nb[1]; d.seg[i].dst = (float *) s.dst[i]->data + lo; d.seg[i].M = (int) s.w[i]->ne[1]; d.seg[i].row0 = (int) lo;
             d.seg[i].q6 = s.w[i]->type == B200_TYPE_Q6_K;
             d.types |= d.seg[i].q6 ? 2 : 1;
             const int cb = d.seg[i].q6 ? CH_Q6K_CHUNK : CH_Q4K_CHUNK;
@@ -831,8 +927,9 @@ static int ch_build(b200_ctx * ctx, const b200_chain_phase * phases, int n, ch_a
             Mtot += s.w[i]->ne[1];
         }
         if (s.epilogue == B200_CHAIN_Y_SWIGLU) {
-            if (s.n_w != 2 || s.w[0]->ne[1] != s.w[1]->ne[1] || !ch_col_ok(s.glu, s.w[0]->ne[1])) { b200_set_error("decode_chain: phase %d: SWIGLU wants gate, up of equal M and a glu column", p); return B200_ERR_UNSUPPORTED; }
-            d.glu = (float *) s.glu->data; d.nunits = (int) (s.w[0]->ne[1] / CH_R);
+            const int64_t lo = sp ? sp->row_lo[p][0] : 0;
+            if (s.n_w != 2 || s.w[0]->ne[1] != s.w[1]->ne[1] || (sp ? (!ch_col_part_ok(s.glu, lo, s.w[0]->ne[1]) || sp->row_lo[p][1] != lo) : !ch_col_ok(s.glu, s.w[0]->ne[1]))) { b200_set_error("decode_chain: phase %d: SWIGLU wants gate, up of equal M and a glu column", p); return B200_ERR_UNSUPPORTED; }
+            d.glu = (float *) s.glu->data + lo; d.nunits = (int) (s.w[0]->ne[1] / CH_R);
         } else if (s.epilogue == B200_CHAIN_Y_PLAIN) d.nunits = (int) (Mtot / CH_R);
         else { b200_set_error("decode_chain: phase %d: unknown epilogue %d", p, s.epilogue); return B200_ERR_UNSUPPORTED; }
         if (!ch_col_ok(s.in0, K)) { b200_set_error("decode_chain: phase %d: in0 is not an aligned f32 column of %lld", p, (long long) K); return B200_ERR_UNSUPPORTED; }
@@ -859,6 +956,7 @@ static int ch_build(b200_ctx * ctx, const b200_chain_phase * phases, int n, ch_a
         bool any = false;
         for (int i = 0; i < s.n_w; ++i) any = any || (s.tail[i] && s.tail[i]->kind != B200_CHAIN_T_NONE);
         if (!any) continue;
+        if (sp) { b200_set_error("decode_chain_split: no ROPE / KV-cache tail on a row-split chain"); return B200_ERR_UNSUPPORTED; }
         if (p != n - 1 || s.epilogue != B200_CHAIN_Y_PLAIN) { b200_set_error("decode_chain: phase %d: only the last phase, without GLU, takes a tail", p); return B200_ERR_UNSUPPORTED; }
         A.tail_phase = p;
         for (int i = 0; i < s.n_w; ++i) {
@@ -878,7 +976,7 @@ static int ch_build(b200_ctx * ctx, const b200_chain_phase * phases, int n, ch_a
     // ---- pass 2: how every phase gets its inputs.  The flag-in-data hand-over needs in0 to be exactly what the phase before publishes
     // (its single result column, or its glu) and in1 to come from outside or from the last residual sum (kept in registers); anything
     // else that was written earlier in this launch forces the fence-and-counter form for the whole chain.
-    bool ll = !ch_force_barrier();
+    bool ll = sp ? true : !ch_force_barrier();       // across GPUs only the flag-in-data form exists
     int last_add = -1;
     A.pre_in1 = -1; A.own_in1 = -1;
     int dkind[CH_MAXPH] = {}, in1_class[CH_MAXPH] = {}, add_before[CH_MAXPH] = {};   // in0 = the phase before's single result (1) / glu (2); addend: outside (0), the last ADD's sum (1), other (2)
@@ -899,7 +997,7 @@ static int ch_build(b200_ctx * ctx, const b200_chain_phase * phases, int n, ch_a
                                         ((o == 0 && e.n_w == 1 && e.epilogue == B200_CHAIN_Y_PLAIN) || (o == 6 && e.epilogue == B200_CHAIN_Y_SWIGLU));
                     d.in_mode = CH_IN_BARRIER;
                     if (direct) dkind[p] = o == 0 ? 1 : 2;
-                    if (direct && ll) d.in_mode = (o == 6 && s.prologue == B200_CHAIN_X_PLAIN && d.K % 32 == 0) ? CH_IN_LL_Q8 : CH_IN_LL_F32;
+                    if (direct && ll) d.in_mode = (!sp && o == 6 && s.prologue == B200_CHAIN_X_PLAIN && d.K % 32 == 0) ? CH_IN_LL_Q8 : CH_IN_LL_F32;
                     else ll = false;
                 }
                 if (d.in1 && ch_overlap(s.in1->data, kb, outs[o])) {
@@ -920,6 +1018,49 @@ static int ch_build(b200_ctx * ctx, const b200_chain_phase * phases, int n, ch_a
         if (!ll && d.in_mode != CH_IN_EXTERNAL) d.in_mode = CH_IN_BARRIER;
         if (p > 0) A.ph[p - 1].out_mode = d.in_mode == CH_IN_EXTERNAL ? (ll ? CH_IN_EXTERNAL : CH_IN_BARRIER) : d.in_mode;
     }
+    if (sp) {
+        // every boundary must be a direct hand-over (the phase before's single result or its glu), and a rank's rows of a handed-over column
+        // one contiguous range: then the (value, tag) pairs of all ranks tile the next phase's activation
+        for (int p = 1; p < n; ++p) if (!ll || A.ph[p].in_mode != CH_IN_LL_F32) { b200_set_error("decode_chain_split: phase %d does not take its activation straight from the phase before", p); return B200_ERR_UNSUPPORTED; }
+        if (phases[n - 1].epilogue != B200_CHAIN_Y_PLAIN) { b200_set_error("decode_chain_split: the last phase must be a plain one"); return B200_ERR_UNSUPPORTED; }
+        A.nrank = sp->world;
+        for (int r = 0; r < sp->world; ++r) { if (!sp->ll[r]) { b200_set_error("decode_chain_split: hand-over area of rank %d missing", r); return B200_ERR_INVALID; } A.llr[r] = (uint8_t *) sp->ll[r]; }
+        int base = 0;
+        for (int i = 0; i < phases[n - 1].n_w; ++i) { A.fin[i].dst = (float *) phases[n - 1].dst[i]->data; A.fin[i].M = (int) phases[n - 1].dst[i]->ne[0]; A.fin[i].base = base; base += A.fin[i].M; }
+        A.fin_total = sp->world > 1 ? base : 0;
+        A.fin_off = (unsigned) ((size_t) CH_MAXPH * CH_LL_BYTES);
+        if ((size_t) A.fin_off + (size_t) base * 8 > sp->ll_bytes) { b200_set_error("decode_chain_split: hand-over area of %llu bytes is too small", (unsigned long long) sp->ll_bytes); return B200_ERR_INVALID; }
+        // owner-side hand-over where a boundary has the llama shape, as pass 2b below does on one GPU, with the records validated by tags
+        // (CH_IN_LL_Q8 behind SWIGLU, CH_IN_LQ8N in front of an ADD + RMS_NORM + MUL): every CTA polls 1.25-3 bytes per activation instead
+        // of 8 and does not normalise and quantize the column itself.  GGML_B200_CHAIN_SPLIT_OWNER=0 keeps every boundary as f32 pairs.
+        static const bool owner_off = [] { const char * e = getenv("GGML_B200_CHAIN_SPLIT_OWNER"); return e && e[0] == '0'; }();
+        int prev_own = -1;
+        for (int p = 1; p < n && !owner_off; ++p) {
+            const b200_chain_phase & s = phases[p], & e = phases[p - 1];
+            ch_phase & d = A.ph[p], & pd = A.ph[p - 1];
+            if (d.K % 32 != 0 || pd.nunits % 8 != 0) continue;
+            bool lo_ok = true;
+            for (int i = 0; i < pd.nseg; ++i) lo_ok = lo_ok && pd.seg[i].row0 % 32 == 0;
+            if (!lo_ok) continue;
+            if (dkind[p] == 2 && s.prologue == B200_CHAIN_X_PLAIN) { d.in_mode = pd.out_mode = CH_IN_LL_Q8; continue; }
+            if (dkind[p] != 1 || s.prologue != B200_CHAIN_X_ADD_NORM_MUL || s.out_norm || s.out_mul || pd.nseg != 1) continue;
+            if (s.out_add && (ch_overlap(s.out_add->data, kb_of(d.K), e.in0) || ch_overlap(s.out_add->data, kb_of(d.K), e.in1) || ch_overlap(s.out_add->data, kb_of(d.K), e.normw))) continue;
+            const bool first = in1_class[p] == 0 && add_before[p] < 0 && prev_own < 0;
+            const bool next  = in1_class[p] == 1 && prev_own >= 0 && add_before[p] == prev_own + 1 && A.ph[prev_own].nunits == pd.nunits && A.ph[prev_own].seg[0].row0 == pd.seg[0].row0;
+            if (!first && !next) continue;
+            d.in_mode = pd.out_mode = CH_IN_LQ8N;
+            const int r0 = pd.seg[0].row0;                 // the owners index these by their LOCAL row
+            pd.nx_normw = (const float *) s.normw->data + r0; pd.nx_in1 = (const float *) s.in1->data + r0; pd.nx_out_add = s.out_add ? (float *) s.out_add->data + r0 : nullptr;
+            if (first) { A.own_in1 = p - 1; if (A.pre_in1 == p) A.pre_in1 = -1; }
+            d.in1_kept = 0;
+            prev_own = p - 1;
+        }
+        // an ADD that expects the last sum in every CTA's registers cannot follow an ADD that only the row owners computed
+        for (int p = 1; p < n; ++p)
+            if (A.ph[p].in1_kept && A.ph[p].in_mode != CH_IN_LQ8N && add_before[p] >= 1 && A.ph[add_before[p]].in_mode == CH_IN_LQ8N) {
+                b200_set_error("decode_chain_split: phase %d adds a sum that only the row owners hold", p); return B200_ERR_UNSUPPORTED;
+            }
+    } else A.nrank = 1;
     if (!ll) {
         for (int p = 0; p + 1 < n; ++p) A.ph[p].out_mode = CH_IN_BARRIER;             // one counter for the whole launch: every boundary arrives
         for (int p = 1; p < n; ++p) {
@@ -961,12 +1102,16 @@ static int ch_build(b200_ctx * ctx, const b200_chain_phase * phases, int n, ch_a
     for (int p = 0; p < n; ++p) {
         ch_phase & d = A.ph[p];
         d.ng8 = 0; d.ngrp = 0;
-        if (d.out_mode == CH_IN_LL_Q8 || d.out_mode == CH_IN_BQ8) {
+        if (sp && d.out_mode == CH_IN_LL_Q8) {
+            d.ngrp = d.nunits / 8;                    // row split: every rank's rows as whole blocks (no f32 tail rows in the middle of the column)
+            A.ph[p + 1].nq8 = A.ph[p + 1].K;
+        } else if (d.out_mode == CH_IN_LL_Q8 || d.out_mode == CH_IN_BQ8) {
             d.ngrp = (d.nunits / 8) / G * G;          // whole 32-row blocks, the same number for every CTA; the remainder goes round-robin
             A.ph[p + 1].nq8 = d.ngrp * 8 * CH_R;
         } else if (ch_is_own_norm(d.out_mode)) d.ngrp = d.nunits / 8;      // every row: the norm needs all sums of squares from the owners
         d.ng8 = d.ngrp * 8;
         d.off = 0; d.toff = off;
+        if (sp && d.out_mode == CH_IN_LL_Q8) { d.off = off; off = (off + d.ngrp) % G; }      // few groups per rank: start where the phase before stopped
         off = (off + d.nunits - d.ng8) % G;
         if (ch_is_own_norm(d.out_mode)) off = d.ngrp % G;                   // round-robin units of the next phase start with the CTAs this one left idle
         const int tpu = d.epilogue == B200_CHAIN_Y_SWIGLU ? 2 : 1;
@@ -1008,12 +1153,24 @@ extern "C" int b200_decode_chain_supported(b200_ctx * ctx, const b200_chain_phas
     return ch_build(ctx, phases, n_phases, A, smem) == B200_OK;
 }
 
-extern "C" int b200_decode_chain(b200_ctx * ctx, const b200_chain_phase * phases, int n_phases) {
+static int ch_launch(b200_ctx * ctx, const b200_chain_phase * phases, int n_phases, const b200_chain_split * sp);
+extern "C" int b200_decode_chain(b200_ctx * ctx, const b200_chain_phase * phases, int n_phases) { return ch_launch(ctx, phases, n_phases, nullptr); }
+extern "C" int b200_decode_chain_split(b200_ctx * ctx, const b200_chain_phase * phases, int n_phases, const b200_chain_split * split) {
+    if (!split) { b200_set_error("decode_chain_split: null split"); return B200_ERR_INVALID; }
+    return ch_launch(ctx, phases, n_phases, split);
+}
+extern "C" size_t b200_decode_chain_split_bytes(int64_t last_rows) { return (size_t) CH_MAXPH * CH_LL_BYTES + (size_t) (last_rows > 0 ? last_rows : 0) * 8; }
+extern "C" int b200_decode_chain_split_supported(b200_ctx * ctx, const b200_chain_phase * phases, int n_phases, const b200_chain_split * split) {
+    if (!ctx || !split) return 0;
+    ch_args A; size_t smem;
+    return ch_build(ctx, phases, n_phases, A, smem, split) == B200_OK;
+}
+static int ch_launch(b200_ctx * ctx, const b200_chain_phase * phases, int n_phases, const b200_chain_split * sp) {
     if (!ctx) { b200_set_error("decode_chain: null context"); return B200_ERR_INVALID; }
     B200_CUDA_TRY(cudaSetDevice(ctx->device));
     ch_args A;
     size_t smem;
-    int rc = ch_build(ctx, phases, n_phases, A, smem);
+    int rc = ch_build(ctx, phases, n_phases, A, smem, sp);
     if (rc != B200_OK) return rc;
     // counters + hand-over areas: scratch slot 7, zeroed when it is (re)allocated; the kernel re-arms the counters and advances the epoch itself
     const size_t sbytes = 256 + (size_t) CH_MAXPH * CH_LL_BYTES;
@@ -1021,7 +1178,8 @@ extern "C" int b200_decode_chain(b200_ctx * ctx, const b200_chain_phase * phases
     uint8_t * sc = (uint8_t *) b200_scratch(ctx, 7, sbytes);
     if (!sc) return B200_ERR_ALLOC;
     if (fresh) B200_CUDA_TRY(cudaMemsetAsync(sc, 0, sbytes, ctx->stream));
-    A.sync = (unsigned *) sc; A.ll = sc + 256;
+    A.sync = (unsigned *) sc; A.ll = sp ? (uint8_t *) sp->ll[sp->rank] : sc + 256;      // (row split: the areas live where the peers can reach them)
+    if (!sp) A.llr[0] = A.ll;
     A.trace = ctx->trace; A.trace_cap = ctx->trace_cap;
     { static int dbg = -1; if (dbg < 0) { const char * e = getenv("GGML_B200_CHAIN_DBG"); dbg = e ? atoi(e) : 0; } A.dbg = dbg; }
     const int nw = ch_nw();
@@ -1037,7 +1195,7 @@ extern "C" int b200_decode_chain(b200_ctx * ctx, const b200_chain_phase * phases
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned) ctx->sm_count);
-    cfg.blockDim = dim3(nw * 32);
+    cfg.blockDim = dim3((sp ? 16 : nw) * 32);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = ctx->stream;
     cudaLaunchAttribute attr[1];
@@ -1045,6 +1203,11 @@ extern "C" int b200_decode_chain(b200_ctx * ctx, const b200_chain_phase * phases
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr; cfg.numAttrs = ctx->pdl ? 1 : 0;
     const bool tr = A.trace != nullptr || A.dbg != 0;
+    if (sp) {
+        static bool sp_attr[64] = {};
+        if (!sp_attr[ctx->device & 63]) { B200_CUDA_TRY(cudaFuncSetAttribute(k_decode_chain<16, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024)); sp_attr[ctx->device & 63] = true; }
+        B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_decode_chain<16, false, true>, A));
+    } else
     if (nw == 24) { if (tr) B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_decode_chain<24, true>, A)); else B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_decode_chain<24, false>, A)); }
     else          { if (tr) B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_decode_chain<16, true>, A)); else B200_LAUNCH(ctx, B200_K_GEMV, cudaLaunchKernelEx(&cfg, k_decode_chain<16, false>, A)); }
     for (int p = 0; p < n_phases; ++p) {

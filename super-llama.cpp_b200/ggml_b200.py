@@ -66,6 +66,11 @@ class ChainPhase(C.Structure):
                 ("tail", C.POINTER(ChainRope) * 3)]
 
 
+class ChainSplit(C.Structure):
+    """b200_chain_split: the decode chain row-split over the GPUs of one node (one process per GPU); ll[r] = rank r's hand-over area"""
+    _fields_ = [("world", C.c_int32), ("rank", C.c_int32), ("ll", C.c_void_p * 8), ("ll_bytes", C.c_uint64), ("row_lo", (C.c_int64 * 3) * 6)]
+
+
 X_PLAIN, X_ADD_NORM_MUL, X_NORM_MUL = 0, 1, 2
 Y_PLAIN, Y_SWIGLU = 0, 1
 
@@ -94,6 +99,8 @@ def lib():
         "b200_mul_mat": (i, [vp, tp, tp, tp]), "b200_mul_mat_noalloc": (i, [vp, tp, tp, tp]), "b200_noalloc_scratch_bytes": (sz, []),
         "b200_mul_mat_multi": (i, [vp, C.POINTER(tp), i, tp, C.POINTER(tp)]),
         "b200_decode_chain": (i, [vp, C.POINTER(ChainPhase), i]), "b200_decode_chain_supported": (i, [vp, C.POINTER(ChainPhase), i]), "b200_decode_chain_error": (i, [vp]),
+        "b200_decode_chain_split": (i, [vp, C.POINTER(ChainPhase), i, C.POINTER(ChainSplit)]), "b200_decode_chain_split_supported": (i, [vp, C.POINTER(ChainPhase), i, C.POINTER(ChainSplit)]),
+        "b200_decode_chain_split_bytes": (C.c_size_t, [C.c_int64]),
         "b200_mul_mat_gate_up_swiglu": (i, [vp, tp, tp, tp, tp, tp, tp]),
         "b200_repack_supported": (i, [i, i64]), "b200_repack": (i, [vp, i, vp, i64, i64, sz]), "b200_unrepack": (i, [vp, i, vp, i64, i64, sz]), "b200_mul_mat_id": (i, [vp, tp, tp, tp, tp]),
         "b200_flash_attn_ext": (i, [vp, tp, tp, tp, tp, tp, tp, f, f, f]),
@@ -356,10 +363,29 @@ class Context:
                     a.tail[k] = C.pointer(r)
         return arr, keep
 
-    def decode_chain(self, program):
-        """b200_decode_chain: the dependent MUL_MAT groups of one token between two attention operators as ONE persistent kernel"""
+    def decode_chain(self, program, split=None):
+        """b200_decode_chain: the dependent MUL_MAT groups of one token between two attention operators as ONE persistent kernel.
+        split (ChainSplit): b200_decode_chain_split -- this rank's rows of every weight, the all-gather inside the hand-over"""
         arr, _keep = program
-        _check(lib().b200_decode_chain(self.h, arr, len(arr)), "decode_chain")
+        if split is not None:
+            _check(lib().b200_decode_chain_split(self.h, arr, len(arr), C.byref(split)), "decode_chain_split")
+        else:
+            _check(lib().b200_decode_chain(self.h, arr, len(arr)), "decode_chain")
+
+    def chain_split(self, world, rank, ll_ptrs, ll_bytes, row_lo):
+        """row_lo: per phase, the first row this rank holds of each result"""
+        sp = ChainSplit()
+        sp.world, sp.rank, sp.ll_bytes = world, rank, ll_bytes
+        for r, pt in enumerate(ll_ptrs):
+            sp.ll[r] = pt
+        for p, los in enumerate(row_lo):
+            for k, lo in enumerate(los):
+                sp.row_lo[p][k] = lo
+        return sp
+
+    def decode_chain_split_supported(self, program, split):
+        arr, _keep = program
+        return bool(lib().b200_decode_chain_split_supported(self.h, arr, len(arr), C.byref(split)))
 
     def decode_chain_error(self):
         """0, or the code of the first bounded wait that ran out inside a chain kernel since the last call (synchronizes)"""
