@@ -18,18 +18,24 @@ class LayerChain:
 
     NAMES = ("wo", "gate", "up", "down", "q", "k", "v")
 
-    def __init__(self, ctx, n_embd, n_ff, n_kv, weights, norm_ffn, norm_attn, eps=1e-5, repack=True, tail="qkv", norm_outputs=True, rope=None):
+    def __init__(self, ctx, n_embd, n_ff, n_kv, weights, norm_ffn, norm_attn, eps=1e-5, repack=True, tail="qkv", norm_outputs=True, rope=None, split=None):
         """norm_outputs=False: the RMS_NORM and MUL node values are dead, as in the real llama graph where only the matmuls read them (the
-        plugin passes NULL for them, b200_backend.cpp try_chain) -- the shape the kernel's owner-side hand-over takes"""
+        plugin passes NULL for them, b200_backend.cpp try_chain) -- the shape the kernel's owner-side hand-over takes.
+        split = dict(world, rank, ll_ptrs, ll_bytes, ranges={name: (lo, hi)}[, alloc]): the row-split form (b200_decode_chain_split); `weights` then
+        hold this rank's rows [lo, hi) of every matrix, the columns stay full size (alloc: where the peers can reach... only the hand-over
+        areas ll_ptrs have to be; the columns are private)"""
         self.ctx, self.n_embd, self.n_ff, self.n_kv, self.eps = ctx, n_embd, n_ff, n_kv, eps
         shape = {"wo": (n_embd, n_embd), "gate": (n_embd, n_ff), "up": (n_embd, n_ff), "down": (n_ff, n_embd),
                  "q": (n_embd, n_embd), "k": (n_embd, n_kv), "v": (n_embd, n_kv)}
+        self.split = None
         self.w = {}
         for name in self.NAMES:
             if name not in weights:
                 continue
             t, host = weights[name]
             K, M = shape[name]
+            if split is not None:
+                lo, hi = split["ranges"][name]; M = hi - lo
             dw = ctx.upload(t, [K, M], host)
             if repack:
                 ctx.repack(dw)                      # q6_K -> group-SoA (what the plugin's load-time hook does); q4_K stays raw
@@ -70,6 +76,13 @@ class LayerChain:
         self.phases = ph
         self.norm_outputs = norm_outputs
         self.program = ctx.chain_program(ph)
+        if split is not None:
+            lo = lambda n: split["ranges"][n][0]
+            row_lo = [[lo("wo")], [lo("gate"), lo("up")], [lo("down")]] + ([[lo("q"), lo("k"), lo("v")]] if tail == "qkv" else [])
+            self.split = ctx.chain_split(split["world"], split["rank"], split["ll_ptrs"], split["ll_bytes"], row_lo)
+
+    def supported(self):
+        return self.ctx.decode_chain_split_supported(self.program, self.split) if self.split is not None else self.ctx.decode_chain_supported(self.program)
 
     def weight_bytes(self):
         return sum(w.nbytes for w in self.w.values())
@@ -83,7 +96,7 @@ class LayerChain:
         self.ctx.h2d(self.pos, np.int32([pos])); self.ctx.h2d(self.kidx, np.int64([cache_row])); self.ctx.h2d(self.vidx, np.int64([cache_row]))
 
     def run(self):
-        self.ctx.decode_chain(self.program)
+        self.ctx.decode_chain(self.program, self.split)
 
     OUTPUTS = ("wo_out", "ffn_inp", "ffn_normed", "ffn_x", "gate", "up", "glu", "down_out", "l_out", "attn_normed", "attn_x", "q", "k", "v")
 
