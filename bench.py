@@ -678,10 +678,16 @@ def run_b200(args):
             one = HotPathModel(B, ctx, cfg, 1, args.depth, 0, 1, quant=args.quant, chain="split" if chained else False)
             for n in ("x",) if chained else ("x", "h", "ff", "attn"):   # the same inputs, as they are NOW (the e2e leg above uploaded its own embedding row into x)
                 ctx.h2d(getattr(one, n).ptr, ctx.download(getattr(tg, n)).reshape(-1))
+            # (a model whose unsplit form the chain kernel declines -- 70B's output head is 868 stages per CTA on one GPU, the table holds 640 --
+            # has no unsplit counterpart in the same arithmetic: then only the ranks are compared with each other; the same widths are covered
+            # word for word by tests/test_gpu_chain_split.py)
+            no_ref = chained and one.chains is None
             one.reset_state()
             one.step(); ctx.synchronize()
             whole = {n: ctx.download(getattr(one, n)).reshape(-1).copy() for n in names}
             del one
+            if no_ref:
+                whole = {n: mine[n].copy() for n in names}
             for n, (lo, hi) in part.items():
                 mine[n], whole[n] = mine[n][lo:hi], whole[n][lo:hi]
             diff = {n: int((whole[n].view(np.uint32) != mine[n].view(np.uint32)).sum()) for n in names}
@@ -689,7 +695,9 @@ def run_b200(args):
             # (the unsplit model may pick another GEMV kernel for a shape than the sharded one does: a different summation order, a few last-bit
             # differences; anything beyond that is a wrong or missing row)
             ok[0] = ok[0] and max(err.values()) < 1e-9 and all(np.isfinite(mine[n]).all() for n in names)
-            split_check = {"ranks_identical": len(set(digests)) == 1, "nmse_vs_unsplit_max": max(err.values()), "words_differing_from_unsplit": diff,
+            split_check = {"ranks_identical": len(set(digests)) == 1, "nmse_vs_unsplit_max": None if no_ref else max(err.values()), "words_differing_from_unsplit": None if no_ref else diff,
+                           "unsplit_reference": "none: the chain kernel declines this model unsplit on one GPU (ranks compared with each other only)" if no_ref else
+                                                ("the chain in the same hand-over form on one GPU" if chained else "separate launches on one GPU"),
                            "exchange_error": int(ctx.exchange_error(peer.ex)) if peer is not None else 0}
         dist.broadcast_object_list(ok, src=0)
         if not ok[0]:
@@ -715,7 +723,8 @@ def run_b200(args):
             "warmup": args.warmup, "ms_per_step": ms_tg, "higher_is_better": True, "scaling": "weak" if replicas > 1 else "strong", "vs_baseline": None,
             "dtype": "int8 dot (dp4a / mma.sync) with f32 accumulate over q8_1 activations; f16 KV, f32 softmax", "data": "synthetic",
             "config": dict(bench_config(cfg, args), **({} if world == 1 else {"parallelism": (f"{replicas} independent replicas (MUL_MAT_ID does not shard, ggml-cuda.cu:2274), no collective" if replicas > 1 else
-                                       f"row-split tp{world}, all-gather " + ("fused into the GEMV epilogue (NVLink peer stores)" if peer is not None else "by NCCL"))})),
+                                       f"row-split tp{world}, all-gather " + ("inside the persistent chain kernel's hand-over between its phases (row owners publish q8_1 records as (word, tag) pairs into every rank's area over NVLink; b200_decode_chain_split), layer 0's wq / wk / wv fused into the GEMV epilogue" if peer is not None and chain else
+                                                                              "fused into the GEMV epilogue (NVLink peer stores)" if peer is not None else "by NCCL"))})),
             "value_is": f"every MUL_MAT{'_ID' if cfg.get('n_expert') else ''} and FLASH_ATTN_EXT node of one decode token ({cfg['n_layer']} layers + output head) through the flat C-ABI, one CUDA graph, inputs resident in HBM" +
                         ("; the ADD / RMS_NORM / MUL / SwiGLU nodes between them run inside the chain kernel; ROPE, KV-cache writes and the embedding lookup are only in e2e" if chain else "; glue ops only in e2e"),
             "cuda_graph": bool(graph), "l2": f"weights {tg.weight_bytes * (world if replicas == 1 else 1) / 1e9:.1f} GB >> 126 MB L2, streamed once per step: no flush needed",

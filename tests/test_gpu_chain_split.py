@@ -44,10 +44,10 @@ from row_split import RowSplit, PeerExchange
 dist.init_process_group("gloo")
 rank, world = dist.get_rank(), dist.get_world_size()
 ctx = B.Context(rank)
-peer = PeerExchange(ctx, dist, world, rank, 16 << 20)
+peer = PeerExchange(ctx, dist, world, rank, 24 << 20)
 rs = RowSplit(dist, world, rank, 32)
 ok = True
-for dims, t_v, t_down in (((2048, 6144, 512), O.Q4_K, O.Q6_K), ((4096, 14336, 1024), O.Q6_K, O.Q4_K)):
+for dims, t_v, t_down in (((2048, 6144, 512), O.Q4_K, O.Q6_K), ((4096, 14336, 1024), O.Q6_K, O.Q4_K), ((8192, 28672, 1024), O.Q4_K, O.Q6_K)):
     rng = np.random.default_rng(dims[0] + t_down)
     types, shape, W, nf, na = layer_weights(rng, dims, t_v, t_down)
     ll_bytes = int(B.lib().b200_decode_chain_split_bytes(dims[0] + 2 * dims[2]))
