@@ -104,7 +104,7 @@ struct ch_args {
     // their own copy exactly as they do on one GPU: the all-gather IS the hand-over.  llr[r] = rank r's areas as mapped here (llr[rank] == ll).
     // The last phase's results are needed in full by whatever follows the launch: published the same way into the area behind the phases'
     // (fin_off), and unpacked into the plain f32 columns fin[i].dst by all CTAs before the kernel ends.
-    int nrank; uint8_t * llr[B200_MAX_PEERS];
+    int nrank; uint8_t * llr[B200_MAX_PEERS]; int poll_ns;      // poll_ns: GGML_B200_CHAIN_POLL_NS, pause between two failed polls of a record (row split)
     int fin_total; unsigned fin_off; struct { float * dst; int M; int base; } fin[CH_MAXSEG];
     int dbg;               // GGML_B200_CHAIN_DBG (measurement only): 1 skip the dot products, 2 no weight traffic
     unsigned long long * trace; int trace_cap;   // b200_debug_trace (measurement only): per CTA and phase, globaltimer at 5 points
@@ -422,6 +422,7 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
                             break;
                         }
                         if (wt.spin(P.sync, 0x900u + p)) break;
+                        if (P.poll_ns) __nanosleep(P.poll_ns);
                     }
                 }
             }
@@ -518,6 +519,7 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
                     q0 = ch_ll_load2(b + (u & 1) * 32); q1 = ch_ll_load2(b + (u & 1) * 32 + 16); ds = ch_ll_load2(b + 64);
                     if (q0.y == tag && q0.w == tag && q1.y == tag && q1.w == tag && ds.y == tag) break;
                     if (w.spin(P.sync, 0x400u + p)) break;
+                    if (SP && P.poll_ns) __nanosleep(P.poll_ns);
                 }
                 const float2 f = __half22float2(*(const __half2 *) &ds.x);
                 ch_store_unit(u, make_int4((int) q0.x, (int) q0.z, (int) q1.x, (int) q1.z), f.x, f.y, K, nblocks, ph.types, s_act);
@@ -1180,6 +1182,9 @@ static int ch_launch(b200_ctx * ctx, const b200_chain_phase * phases, int n_phas
     if (fresh) B200_CUDA_TRY(cudaMemsetAsync(sc, 0, sbytes, ctx->stream));
     A.sync = (unsigned *) sc; A.ll = sp ? (uint8_t *) sp->ll[sp->rank] : sc + 256;      // (row split: the areas live where the peers can reach them)
     if (!sp) A.llr[0] = A.ll;
+    // a failed poll of a record is followed by a pause: 148 CTAs x 256 threads re-reading the same lines compete with the peers' incoming stores
+    // (two GPUs, 8B: 666 tok/s without, 665 / 674 / 683 / 679 / 668 / 630 with 50 / 200 / 500 / 1000 / 2000 / 4000 ns)
+    { static int pn = -1; if (pn < 0) { const char * e = getenv("GGML_B200_CHAIN_POLL_NS"); pn = e ? atoi(e) : 500; } A.poll_ns = pn; }
     A.trace = ctx->trace; A.trace_cap = ctx->trace_cap;
     { static int dbg = -1; if (dbg < 0) { const char * e = getenv("GGML_B200_CHAIN_DBG"); dbg = e ? atoi(e) : 0; } A.dbg = dbg; }
     const int nw = ch_nw();
