@@ -558,6 +558,8 @@ def run_b200(args):
         tg.gather = gather
 
     def timed(model, steps, warmup, use_graph):
+        if dist:
+            dist.barrier()                                  # the ranks meet inside the kernels (bounded waits): nobody starts seconds ahead of the others
         for _ in range(max(warmup, 1)):
             model.step()
         ctx.synchronize()
@@ -622,6 +624,8 @@ def run_b200(args):
     def mm_only():
         tg.step(attention=False)
     gemv_ms_step = None
+    if dist:
+        ctx.synchronize(); dist.barrier()
     if use_graph:                                           # (every rank replays its own graph; with the peer exchange they meet inside the kernels)
         mm_only(); ctx.synchronize()
         l0 = ctx.launches_by_kind()
@@ -640,6 +644,8 @@ def run_b200(args):
             t = torch.tensor([gemv_ms_step], device=f"cuda:{local}"); dist.all_reduce(t, op=dist.ReduceOp.MAX); gemv_ms_step = float(t.item())
     roof_how = "CUDA events around 10 replays of a graph holding only the MUL_MAT kernels of one token (max over ranks)" if use_graph else \
                "sum of the per-launch CUDA-event brackets of the MUL_MAT kernels, 3 eager steps (no graph in this mode: launch gaps excluded)"
+    if dist:
+        ctx.synchronize(); dist.barrier()
     ctx.profile(True)
     for _ in range(3):
         tg.step()
@@ -665,6 +671,7 @@ def run_b200(args):
         # and wo's / ffn_down's results are handed on as quantized blocks by their row owners: the same holds for o and d)
         Ll = tg.layers[-1]
         part = {"g": Ll["gate"][1:], "u": Ll["up"][1:], "o": Ll["wo"][1:], "d": Ll["down"][1:]} if chained else {}
+        ctx.synchronize(); dist.barrier()
         tg.reset_state()
         tg.step(); ctx.synchronize()
         mine = {n: ctx.download(getattr(tg, n)).reshape(-1).copy() for n in names}
