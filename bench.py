@@ -155,8 +155,8 @@ class HotPathModel:
         pool = {t: random_blocks(rng, t, (48 << 20) // TSIZE[t]) for t in used}
         self.weight_bytes = 0          # bytes of weights one token reads (MoE: the experts it routes to)
 
-        def make_weight(t, K, M, ne=1):
-            lo, hi = self.rs.row_range(M)
+        def make_weight(t, K, M, ne=1, whole=False):
+            lo, hi = (0, M) if whole else self.rs.row_range(M)
             ml = hi - lo
             w = ctx.empty(t, [K, ml] if ne == 1 else [K, ml, ne])
             nb, blk = w.nbytes, TSIZE[t]
@@ -175,9 +175,15 @@ class HotPathModel:
             ctx.repack(w)                         # load-time repack (q6_K -> 16-byte aligned group layout), as set_tensor does
             return w, lo, hi
 
+        # B200_BENCH_WHOLE_QKV=1 (measurement only): under the row-split chain wq / wk / wv stay WHOLE on every rank (14 MB of 131 per 8B layer), so the
+        # one exchange of a layer that is a pure gather -- attention is replicated and needs q / k / v in full -- disappears.  Measured: 695 vs 684
+        # tok/s on two GPUs, 756.8 vs 756.7 on eight: the gather hides behind the launch of the attention kernel; not the default.
+        self.whole_qkv = world > 1 and peer is not None and bool(chain) and n_tokens == 1 and not self.moe and bool(os.environ.get("B200_BENCH_WHOLE_QKV")) and \
+                         not os.environ.get("B200_BENCH_NO_CHAIN") and not os.environ.get("B200_BENCH_NO_SPLIT_CHAIN")
         self.layers = []
         for lt in types:
-            self.layers.append({name: make_weight(lt[name], *shapes[name], ne=(self.moe if self.moe and name in ("gate", "up", "down") else 1)) for name in shapes})
+            self.layers.append({name: make_weight(lt[name], *shapes[name], ne=(self.moe if self.moe and name in ("gate", "up", "down") else 1),
+                                                  whole=self.whole_qkv and name in ("wq", "wk", "wv")) for name in shapes})
         self.output = make_weight(out_type, cfg["n_embd"], cfg["n_vocab"])
         ctx.synchronize()
 
@@ -304,7 +310,9 @@ class HotPathModel:
 
     def _mm_group(self, ws, x, dsts):
         """MUL_MATs that share src1: one fused launch per run of equal weight types (the plugin fuses the same nodes)"""
-        if self.world > 1:
+        if self.world > 1 and all(w[1] == 0 and w[2] == d.ne[0] for w, d in zip(ws, dsts)):
+            pass                                             # whole on every rank: computed locally, like on one GPU (below)
+        elif self.world > 1:
             if getattr(self, "peer", None) is not None and dsts[0].ne[1] == 1:
                 self.peer.mul_mat_multi([w[0] for w in ws], x, dsts, [w[1] for w in ws])   # one launch per run of equal types, exchange included
                 return

@@ -1029,7 +1029,10 @@ static int ch_build(b200_ctx * ctx, const b200_chain_phase * phases, int n, ch_a
         for (int r = 0; r < sp->world; ++r) { if (!sp->ll[r]) { b200_set_error("decode_chain_split: hand-over area of rank %d missing", r); return B200_ERR_INVALID; } A.llr[r] = (uint8_t *) sp->ll[r]; }
         int base = 0;
         for (int i = 0; i < phases[n - 1].n_w; ++i) { A.fin[i].dst = (float *) phases[n - 1].dst[i]->data; A.fin[i].M = (int) phases[n - 1].dst[i]->ne[0]; A.fin[i].base = base; base += A.fin[i].M; }
-        A.fin_total = sp->world > 1 ? base : 0;
+        // a last phase whose weights every rank holds in full (wq / wk / wv replicated: 14 MB per 8B layer against an exchange of ~8 us) needs no gather
+        bool whole = true;
+        for (int i = 0; i < phases[n - 1].n_w; ++i) whole = whole && A.ph[n - 1].seg[i].row0 == 0 && A.ph[n - 1].seg[i].M == A.fin[i].M;
+        A.fin_total = sp->world > 1 && !whole ? base : 0;
         A.fin_off = (unsigned) ((size_t) CH_MAXPH * CH_LL_BYTES);
         if ((size_t) A.fin_off + (size_t) base * 8 > sp->ll_bytes) { b200_set_error("decode_chain_split: hand-over area of %llu bytes is too small", (unsigned long long) sp->ll_bytes); return B200_ERR_INVALID; }
         // owner-side hand-over where a boundary has the llama shape, as pass 2b below does on one GPU, with the records validated by tags
