@@ -298,6 +298,11 @@ B200_API int b200_split_row_range(int64_t nrows, const float * tensor_split, int
 // llama_multi_gpu_strategy (llama-multi-gpu.h:84-91); values other than the three below plan like MEMORY_BALANCED (llama-multi-gpu.cpp:170-185)
 enum b200_layer_strategy { B200_LAYERS_ROUND_ROBIN = 0, B200_LAYERS_MEMORY_BALANCED = 1, B200_LAYERS_TENSOR_PARALLEL = 4 };
 // llama_layer_assignment (llama-multi-gpu.h:75-81); split_gpu_ids[0 .. n_split) are the GPUs a split layer spans, the rest -1
+/* sizeof of a public struct as this library was compiled: what a binding (ctypes, cgo, JNI) checks its own mirror against before the first call.
+ * which: 0 b200_tensor, 1 b200_chain_rope, 2 b200_chain_phase, 3 b200_chain_split, 4 b200_kv_pages, 5 b200_load_item, 6 b200_load_stats,
+ * 7 b200_exchange, 8 b200_layer_assignment; anything else: 0 */
+B200_API size_t b200_abi_sizeof(int which);
+
 typedef struct b200_layer_assignment {
     int32_t  layer_id, gpu_id;
     uint64_t memory_required;

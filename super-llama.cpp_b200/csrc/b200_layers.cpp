@@ -73,3 +73,19 @@ extern "C" B200_API int b200_plan_tensor_split(const b200_layer_assignment * pla
     for (int g = 0; g < n_gpus; ++g) tensor_split[g] = n > 0 ? (float) (share[g] / n) : 0.0f;
     return B200_OK;
 }
+
+// what a binding checks its mirrors of the public structs against (include/ggml-b200.h: b200_abi_sizeof)
+extern "C" B200_API size_t b200_abi_sizeof(int which) {
+    switch (which) {
+        case 0: return sizeof(b200_tensor);
+        case 1: return sizeof(b200_chain_rope);
+        case 2: return sizeof(b200_chain_phase);
+        case 3: return sizeof(b200_chain_split);
+        case 4: return sizeof(b200_kv_pages);
+        case 5: return sizeof(b200_load_item);
+        case 6: return sizeof(b200_load_stats);
+        case 7: return sizeof(b200_exchange);
+        case 8: return sizeof(b200_layer_assignment);
+    }
+    return 0;
+}

@@ -100,7 +100,7 @@ def lib():
         "b200_mul_mat_multi": (i, [vp, C.POINTER(tp), i, tp, C.POINTER(tp)]),
         "b200_decode_chain": (i, [vp, C.POINTER(ChainPhase), i]), "b200_decode_chain_supported": (i, [vp, C.POINTER(ChainPhase), i]), "b200_decode_chain_error": (i, [vp]),
         "b200_decode_chain_split": (i, [vp, C.POINTER(ChainPhase), i, C.POINTER(ChainSplit)]), "b200_decode_chain_split_supported": (i, [vp, C.POINTER(ChainPhase), i, C.POINTER(ChainSplit)]),
-        "b200_decode_chain_split_bytes": (C.c_size_t, [C.c_int64]),
+        "b200_decode_chain_split_bytes": (C.c_size_t, [C.c_int64]), "b200_abi_sizeof": (C.c_size_t, [i]),
         "b200_mul_mat_gate_up_swiglu": (i, [vp, tp, tp, tp, tp, tp, tp]),
         "b200_repack_supported": (i, [i, i64]), "b200_repack": (i, [vp, i, vp, i64, i64, sz]), "b200_unrepack": (i, [vp, i, vp, i64, i64, sz]), "b200_mul_mat_id": (i, [vp, tp, tp, tp, tp]),
         "b200_flash_attn_ext": (i, [vp, tp, tp, tp, tp, tp, tp, f, f, f]),
@@ -564,3 +564,8 @@ def plan_tensor_split(plan, n_gpus):
     ts = (C.c_float * n_gpus)()
     _check(lib().b200_plan_tensor_split(arr, len(plan), n_gpus, ts), "plan_tensor_split")
     return list(ts)
+
+
+def abi_mirrors():
+    """which -> ctypes mirror, in b200_abi_sizeof's numbering (tests/test_struct_mirrors.py compares the sizes without a GPU)"""
+    return {0: _Tensor, 1: ChainRope, 2: ChainPhase, 3: ChainSplit, 4: KvPages, 5: LoadItem, 6: LoadStats, 7: Exchange, 8: _LayerAssignment}
