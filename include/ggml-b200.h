@@ -189,7 +189,9 @@ B200_API int b200_decode_chain_supported(b200_ctx * ctx, const b200_chain_phase 
  * a (value, tag) pair into EVERY rank's hand-over area (NVLink peer stores), each rank's CTAs poll their own copy.  ll[r] = rank r's area
  * (b200_decode_chain_split_bytes(rows of the last phase's results) bytes, zeroed once, peer-mapped in this process); after the launch
  * every rank holds the full last-phase results, the full in0 columns, and its own rows of everything else.  No ROPE / KV-cache tail.
- * world == 1 is allowed (same arithmetic on one GPU: what the split results are compared with, bit for bit). */
+ * world == 1 is allowed (same arithmetic on one GPU: what the split results are compared with, bit for bit).  The tags that validate the
+ * records count the launches through THESE areas (the counter is the last word block of the rank's own area): every rank must run the
+ * same sequence of launches over a given set of areas, and nothing else it launches matters. */
 #define B200_CHAIN_SPLIT_MAX_PEERS 8
 typedef struct b200_chain_split {
     int32_t  world, rank;

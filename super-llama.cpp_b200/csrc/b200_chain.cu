@@ -104,6 +104,8 @@ struct ch_args {
     // their own copy exactly as they do on one GPU: the all-gather IS the hand-over.  llr[r] = rank r's areas as mapped here (llr[rank] == ll).
     // The last phase's results are needed in full by whatever follows the launch: published the same way into the area behind the phases'
     // (fin_off), and unpacked into the plain f32 columns fin[i].dst by all CTAs before the kernel ends.
+    unsigned * epoch;      // row split: the launch counter the tags come from lives in the last 64 bytes of this rank's OWN hand-over area, so it counts
+                           // the launches through THESE areas only -- the ranks' tags stay equal whatever else a rank launches on its context
     int nrank; uint8_t * llr[B200_MAX_PEERS]; int poll_ns;      // poll_ns: GGML_B200_CHAIN_POLL_NS, pause between two failed polls of a record (row split)
     int fin_total; unsigned fin_off; struct { float * dst; int M; int base; } fin[CH_MAXSEG];
     int dbg;               // GGML_B200_CHAIN_DBG (measurement only): 1 skip the dot products, 2 no weight traffic
@@ -365,7 +367,7 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
         }
         if (p == 0) {
             asm volatile("griddepcontrol.wait;" ::: "memory");
-            asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(tag) : "l"(P.sync + 3));
+            asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(tag) : "l"(SP ? P.epoch : P.sync + 3));
             tag += 1u;                                // this launch's hand-over tag: differs from whatever an earlier launch left in the areas
             if (P.pre_in1 >= 0 && tid < (P.ph[P.pre_in1].K >> 4)) {
 #pragma unroll
@@ -842,7 +844,7 @@ __global__ void __launch_bounds__(CH_NW * 32, 1) k_decode_chain(const __grid_con
         ch_bar_consumers();
         if (tid == 0) {
             const unsigned done = atomicAdd(P.sync + 1, 1u);
-            if (done == (unsigned) G - 1) { P.sync[0] = 0u; P.sync[1] = 0u; P.sync[3] = tag; __threadfence(); }
+            if (done == (unsigned) G - 1) { P.sync[0] = 0u; P.sync[1] = 0u; if (SP) *P.epoch = tag; else P.sync[3] = tag; __threadfence(); }
         }
     }
 }
@@ -1034,7 +1036,8 @@ static int ch_build(b200_ctx * ctx, const b200_chain_phase * phases, int n, ch_a
         for (int i = 0; i < phases[n - 1].n_w; ++i) whole = whole && A.ph[n - 1].seg[i].row0 == 0 && A.ph[n - 1].seg[i].M == A.fin[i].M;
         A.fin_total = sp->world > 1 && !whole ? base : 0;
         A.fin_off = (unsigned) ((size_t) CH_MAXPH * CH_LL_BYTES);
-        if ((size_t) A.fin_off + (size_t) base * 8 > sp->ll_bytes) { b200_set_error("decode_chain_split: hand-over area of %llu bytes is too small", (unsigned long long) sp->ll_bytes); return B200_ERR_INVALID; }
+        A.epoch = (unsigned *) ((uint8_t *) sp->ll[sp->rank] + sp->ll_bytes - 64);
+        if (sp->ll_bytes % 64 != 0 || (size_t) A.fin_off + (size_t) base * 8 + 64 > sp->ll_bytes) { b200_set_error("decode_chain_split: hand-over area of %llu bytes is too small", (unsigned long long) sp->ll_bytes); return B200_ERR_INVALID; }
         // owner-side hand-over where a boundary has the llama shape, as pass 2b below does on one GPU, with the records validated by tags
         // (CH_IN_LL_Q8 behind SWIGLU, CH_IN_LQ8N in front of an ADD + RMS_NORM + MUL): every CTA polls 1.25-3 bytes per activation instead
         // of 8 and does not normalise and quantize the column itself.  GGML_B200_CHAIN_SPLIT_OWNER=0 keeps every boundary as f32 pairs.
@@ -1164,7 +1167,7 @@ extern "C" int b200_decode_chain_split(b200_ctx * ctx, const b200_chain_phase * 
     if (!split) { b200_set_error("decode_chain_split: null split"); return B200_ERR_INVALID; }
     return ch_launch(ctx, phases, n_phases, split);
 }
-extern "C" size_t b200_decode_chain_split_bytes(int64_t last_rows) { return (size_t) CH_MAXPH * CH_LL_BYTES + (size_t) (last_rows > 0 ? last_rows : 0) * 8; }
+extern "C" size_t b200_decode_chain_split_bytes(int64_t last_rows) { return (((size_t) CH_MAXPH * CH_LL_BYTES + (size_t) (last_rows > 0 ? last_rows : 0) * 8 + 63) & ~(size_t) 63) + 64; }
 extern "C" int b200_decode_chain_split_supported(b200_ctx * ctx, const b200_chain_phase * phases, int n_phases, const b200_chain_split * split) {
     if (!ctx || !split) return 0;
     ch_args A; size_t smem;
