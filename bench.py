@@ -11,8 +11,11 @@ host->device copy of the token's embedding row from pinned memory and the device
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--depth D] [--no-pp]
 
 Multi-GPU (torchrun, one rank per GPU): split-mode=row tensor parallelism -- every rank owns rows
-[row_low, row_high) of each weight (b200_split_row_range, reference ggml-cuda.cu:777-803) and the row slices are
-all-gathered with NCCL; scaling is "strong" (one model, one token stream).
+[row_low, row_high) of each weight (b200_split_row_range, reference ggml-cuda.cu:777-803).  The all-gather lives inside
+the kernels: the decode chain's hand-over between its phases (b200_decode_chain_split: row owners publish q8_1 records
+as (word, tag) pairs into every rank's area over NVLink peer memory), the GEMV epilogue for layer 0's wq / wk / wv;
+torch.distributed carries the IPC handles, the barriers and the max-over-ranks of the timings (B200_BENCH_NCCL=1: one
+NCCL all-gather per matmul, the baseline).  Scaling is "strong" (one model, one token stream).
 --impl reference times the reference's own ggml-cpu implementation of the same ops on the host cores
 (oracle/_ref, compiled in place from /root/reference; the oracle port if that is absent).
 """
