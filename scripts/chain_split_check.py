@@ -12,7 +12,8 @@ ctx = B.Context(0)
 cfg = bench.MODELS[os.environ.get("MODEL", "8b")]
 names = ("q", "k", "v", "o", "d", "logits")
 res, ms = {}, {}
-for form in ("split", False, True):
+FORMS = [{"split": "split", "separate": False, "default": True}[f] for f in os.environ.get("FORMS", "split,separate,default").split(",")]
+for form in FORMS:
     m = bench.HotPathModel(B, ctx, cfg, 1, 0, 0, 1, chain=form)
     assert (m.chains is not None) == bool(form), (form, B.lib().b200_last_error().decode())
     m.reset_state(); m.step(); ctx.synchronize()
@@ -31,6 +32,8 @@ for form in ("split", False, True):
     ctx.record(e1)
     ms[form] = ctx.elapsed_ms(e0, e1) / 20
     del m
+if len(FORMS) < 3:
+    print({str(k): round(v, 4) for k, v in ms.items()}, "ms per step (graph)"); sys.exit(0)
 nm = lambda a, b: float(((a.astype(np.float64) - b) ** 2).sum() / max((a.astype(np.float64) ** 2).sum(), 1e-300))
 for n in names:
     print(f"{n:7s} nmse split-form vs default chain {nm(res[True][n], res['split'][n]):.3e}   finite {np.isfinite(res['split'][n]).all()}   (default chain vs separate launches, which do not pass data from node to node: {nm(res[False][n], res[True][n]):.1e})")
